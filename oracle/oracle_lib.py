@@ -1,0 +1,264 @@
+"""ctypes binding of oracle/liboracle.so (the CPU oracle — TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+CALIB_DTYPE = np.dtype([("K", "<f8", (9,)), ("R", "<f8", (9,)), ("t", "<f8", (3,)), ("dist", "<f8", (5,))])
+assert KP_DTYPE.itemsize == 28 and CALIB_DTYPE.itemsize == 26 * 8
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    src = os.path.join(_HERE, "mcs_oracle.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        L = _LIB
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_extractor_destroy.argtypes = [C.c_void_p]
+        L.orc_extractor_set_orientation.argtypes = [C.c_void_p, C.c_int]
+        L.orc_extractor_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_extractor_last_total.argtypes = [C.c_void_p]
+        L.orc_level_size.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_get_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orc_get_level_padded.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_num_candidates.argtypes = [C.c_void_p, C.c_int]
+        L.orc_get_candidates.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_num_level_kps.argtypes = [C.c_void_p, C.c_int]
+        L.orc_resize_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.orc_gauss7_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_gauss_kernel_fixed.argtypes = [C.c_int, C.c_double, C.c_void_p]
+        L.orc_fast9.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_distribute_octtree.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.orc_std_sort_nodes.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_hamming256.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_bf_match.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 5
+        L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
+                                        C.c_float, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_triangulate_pixels.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_triangulate_pair_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_triangulate_rows.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                           C.c_int] + [C.c_void_p] * 6
+        L.orc_process_rig.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                      C.c_void_p, C.c_void_p]
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def resize_linear(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear_u8(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), dw, dh, dw)
+    return dst
+
+
+def gauss7(src):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty_like(src)
+    lib().orc_gauss7_u8(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), src.shape[1])
+    return dst
+
+
+def gauss_kernel_fixed(n=7, sigma=2.0):
+    out = np.zeros(n, np.int32)
+    lib().orc_gauss_kernel_fixed(n, sigma, _p(out))
+    return out
+
+
+def fast9(img, threshold):
+    """cv::FAST(img, th, nms=True) on a (possibly strided) 2-D uint8 view; returns int32 [n,3] (x, y, score)."""
+    assert img.dtype == np.uint8 and img.strides[1] == 1
+    h, w = img.shape
+    cap = (w * h) // 4 + 16
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orc_fast9(C.c_void_p(img.ctypes.data), w, h, img.strides[0], threshold, _p(out), cap)
+    return out[:n].copy()
+
+
+class Extractor:
+    """Mirror of ORBextractor (MCSlam/include/MCSlam/ORBextractor.h:44-112)."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self.h = lib().orc_extractor_create(nfeatures, scale, nlevels, ini_th, min_th)
+        self.scale = np.zeros(nlevels, np.float32)
+        self.inv_scale = np.zeros(nlevels, np.float32)
+        self.sigma2 = np.zeros(nlevels, np.float32)
+        self.inv_sigma2 = np.zeros(nlevels, np.float32)
+        self.quota = np.zeros(nlevels, np.int32)
+        self.umax = np.zeros(16, np.int32)
+        lib().orc_extractor_tables(self.h, _p(self.scale), _p(self.inv_scale), _p(self.sigma2), _p(self.inv_sigma2),
+                                   _p(self.quota), _p(self.umax))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_extractor_destroy(self.h)
+            self.h = None
+
+    def set_orientation(self, on):
+        lib().orc_extractor_set_orientation(self.h, int(on))
+
+    def __call__(self, image, lapping=(0, 0)):
+        """Returns (monoIndex, keypoints[KP_DTYPE], descriptors[n,32])."""
+        image = np.ascontiguousarray(image, np.uint8)
+        h, w = image.shape
+        cap = self.nfeatures + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        mono = lib().orc_extract(self.h, _p(image), w, h, w, lapping[0], lapping[1], _p(kps), _p(desc), cap)
+        if mono < 0:
+            return mono, kps[:0], desc[:0]
+        n = lib().orc_extractor_last_total(self.h)
+        return mono, kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l, blurred=False):
+        w, h = C.c_int(), C.c_int()
+        lib().orc_level_size(self.h, l, C.byref(w), C.byref(h))
+        out = np.zeros((h.value, w.value), np.uint8)
+        n = lib().orc_get_level(self.h, l, int(blurred), _p(out))
+        return out if n else None
+
+    def level_padded(self, l):
+        w, h = C.c_int(), C.c_int()
+        lib().orc_level_size(self.h, l, C.byref(w), C.byref(h))
+        out = np.zeros((h.value + 38, w.value + 38), np.uint8)
+        lib().orc_get_level_padded(self.h, l, _p(out))
+        return out
+
+    def candidates(self, l):
+        n = lib().orc_num_candidates(self.h, l)
+        out = np.zeros((max(n, 1), 3), np.float32)
+        lib().orc_get_candidates(self.h, l, _p(out))
+        return out[:n]
+
+    def level_counts(self):
+        return np.array([lib().orc_num_level_kps(self.h, l) for l in range(self.nlevels)], np.int32)
+
+
+def distribute_octtree(xyr, minX, maxX, minY, maxY, N):
+    xyr = np.ascontiguousarray(xyr, np.float32)
+    keep = np.zeros(len(xyr) + 8, np.int32)
+    n = lib().orc_distribute_octtree(_p(xyr), len(xyr), minX, maxX, minY, maxY, N, _p(keep))
+    return keep[:n].copy()
+
+
+def std_sort_nodes(sizes, ulx):
+    """libstdc++ std::sort with compareNodes (ORBextractor.cpp:537-552); returns the permutation."""
+    sizes = np.ascontiguousarray(sizes, np.int32)
+    ulx = np.ascontiguousarray(ulx, np.int32)
+    perm = np.zeros(len(sizes), np.int32)
+    lib().orc_std_sort_nodes(_p(sizes), _p(ulx), len(sizes), _p(perm))
+    return perm
+
+
+def bf_match(q, t, dist_thresh=75.0, ratio=0.85):
+    """BruteForceMatch (MultiCameraFrame.cpp:1024-1086). Returns idx1, idx2, best_d, second_d, best_i."""
+    q = np.ascontiguousarray(q, np.uint8)
+    t = np.ascontiguousarray(t, np.uint8)
+    nq, nt = len(q), len(t)
+    i1 = np.zeros(max(nq, 1), np.uint32)
+    i2 = np.zeros(max(nq, 1), np.uint32)
+    bd = np.zeros(max(nq, 1), np.int32)
+    sd = np.zeros(max(nq, 1), np.int32)
+    bi = np.zeros(max(nq, 1), np.int32)
+    n = lib().orc_bf_match(_p(q), nq, _p(t), nt, dist_thresh, ratio, _p(i1), _p(i2), _p(bd), _p(sd), _p(bi))
+    return i1[:n].copy(), i2[:n].copy(), bd[:nq], sd[:nq], bi[:nq]
+
+
+def _ptr_array(arrs):
+    return (C.c_void_p * len(arrs))(*[a.ctypes.data if a is not None else None for a in arrs])
+
+
+def intra_matches(descs, kps, calib, sigma2, use_epipolar=False, dist_thresh=75.0, ratio=0.85):
+    """computeIntraMatches(matches, old) (MultiCameraFrame.cpp:1100-1288). Returns rows [M, num_cams] int32, pair_counts."""
+    nc = len(descs)
+    descs = [np.ascontiguousarray(d, np.uint8) for d in descs]
+    kps = [np.ascontiguousarray(k, KP_DTYPE) for k in kps]
+    n = np.array([len(d) for d in descs], np.int32)
+    cap = int(n.sum()) + 1
+    rows = np.full((cap, nc), -1, np.int32)
+    pc = np.zeros(nc * (nc - 1) // 2, np.int32)
+    calib = np.ascontiguousarray(calib, CALIB_DTYPE)
+    sigma2 = np.ascontiguousarray(sigma2, np.float32)
+    M = lib().orc_intra_matches(nc, _ptr_array(descs), _ptr_array(kps), _p(n), _p(calib), _p(sigma2), int(use_epipolar), dist_thresh,
+                                ratio, _p(rows), cap, _p(pc))
+    assert M >= 0
+    return rows[:M].copy(), pc
+
+
+def triangulate_pixels(calib, view_inds, xs, ys):
+    calib = np.ascontiguousarray(calib, CALIB_DTYPE)
+    vi = np.ascontiguousarray(view_inds, np.int32)
+    xs = np.ascontiguousarray(xs, np.float64)
+    ys = np.ascontiguousarray(ys, np.float64)
+    X = np.zeros(3, np.float64)
+    lib().orc_triangulate_pixels(_p(calib), _p(vi), _p(xs), _p(ys), len(vi), _p(X))
+    return X
+
+
+def triangulate_pair_f32(calib, cam1, cam2, p1, p2):
+    calib = np.ascontiguousarray(calib, CALIB_DTYPE)
+    p1 = np.ascontiguousarray(p1, np.float32)
+    p2 = np.ascontiguousarray(p2, np.float32)
+    out = np.zeros((len(p1), 3), np.float32)
+    lib().orc_triangulate_pair_f32(_p(calib), cam1, cam2, _p(p1), _p(p2), len(p1), _p(out))
+    return out
+
+
+def triangulate_rows(calib, kps, descs, rows, masks=None):
+    """obtainLfFeatures triangulation block (FrontEnd.cpp:249-370). masks: list of float32 [h,w] or None."""
+    nc = len(kps)
+    calib = np.ascontiguousarray(calib, CALIB_DTYPE)
+    kps = [np.ascontiguousarray(k, KP_DTYPE) for k in kps]
+    descs = [np.ascontiguousarray(d, np.uint8) for d in descs]
+    rows = np.ascontiguousarray(rows, np.int32).reshape(-1, nc)
+    M = len(rows)
+    mw = mh = 0
+    mp = None
+    if masks is not None:
+        masks = [np.ascontiguousarray(m, np.float32) for m in masks]
+        mh, mw = masks[0].shape
+        mp = _ptr_array(masks)
+    rows_out = np.zeros((max(M, 1), nc), np.int32)
+    status = np.zeros(max(M, 1), np.uint8)
+    nviews = np.zeros(max(M, 1), np.int32)
+    xyz = np.zeros((max(M, 1), 3), np.float64)
+    uv = np.zeros((max(M, 1), 2), np.float32)
+    rep = np.zeros(max(M, 1), np.int32)
+    acc = lib().orc_triangulate_rows(nc, _p(calib), _ptr_array(kps), _ptr_array(descs), mp, mw, mh, _p(rows), M, _p(rows_out),
+                                     _p(status), _p(nviews), _p(xyz), _p(uv), _p(rep))
+    return dict(accepted=acc, rows=rows_out[:M], status=status[:M], nviews=nviews[:M], xyz=xyz[:M], uv_ref=uv[:M], rep_cam=rep[:M])
+
+
+def process_rig(extractors, images, calib, threads=None, do_match=True, do_triangulate=True):
+    """Whole CPU front-end for one rig frame (timed cpu_baseline). images: [C,h,w] uint8."""
+    images = np.ascontiguousarray(images, np.uint8)
+    nc, h, w = images.shape
+    calib = np.ascontiguousarray(calib, CALIB_DTYPE)
+    hs = (C.c_void_p * nc)(*[e.h for e in extractors])
+    counts = np.zeros(nc, np.int32)
+    acc = C.c_int(0)
+    M = lib().orc_process_rig(hs, nc, _p(images), w, h, _p(calib), nc if threads is None else threads, int(do_match),
+                              int(do_triangulate), _p(counts), C.byref(acc))
+    return M, counts, acc.value
