@@ -1,0 +1,206 @@
+/* mcslam_b200.h — C ABI of the B200-native MC-SLAM front-end hot path (ORB extract -> intra-rig match -> triangulate).
+ *
+ * Drop-in boundary for the two C++ classes the reference front-end calls directly (it has no plugin/FFI layer):
+ *   ORBextractor        /root/reference/MCSlam/include/MCSlam/ORBextractor.h:44-112
+ *   MultiCameraFrame    /root/reference/MCSlam/src/MultiCameraFrame.cpp:203 (extractFeaturesParallel), :1024 (BruteForceMatch),
+ *                       :1100 (computeIntraMatches(vector<IntraMatch>&, bool)), :411/:481 (triangulate*), and the
+ *                       triangulation block of FrontEnd::obtainLfFeatures, MCSlam/src/FrontEnd.cpp:249-370.
+ * Plain pointers and sizes only; no torch / OpenCV types.  The C++ adaptor with the reference's method signatures is
+ * mc-slam_b200/host/mcslam_adaptor.hpp; the binding a maintainer adds is shown in INTEGRATION.md.
+ *
+ * Every entry point runs hand-written sm_100a CUDA kernels.  There is no CPU fallback: without a CUDA device the
+ * create calls fail (NULL + mcs_last_error()).
+ *
+ * Error convention: functions returning int give >= 0 on success and a negative MCS_ERR_* code on failure; the reference's
+ * own conventions are kept where it has them (-1 for an empty image, ORBextractor.cpp:1090-1091).
+ */
+#ifndef MCSLAM_B200_H
+#define MCSLAM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCS_API __attribute__((visibility("default")))
+
+#define MCS_ERR_EMPTY -1    /* empty image: same value ORBextractor::operator() returns (ORBextractor.cpp:1091) */
+#define MCS_ERR_CAPACITY -2 /* caller buffer / configured capacity too small */
+#define MCS_ERR_ARG -3      /* invalid argument */
+#define MCS_ERR_CUDA -4     /* CUDA runtime error; text in mcs_last_error() */
+#define MCS_ERR_STATE -5    /* stage called before its producer stage */
+
+#define MCS_MAX_LEVELS 16
+#define MCS_MAX_CAMS 8
+
+/* POD mirror of cv::KeyPoint, same field order and size (28 bytes). */
+typedef struct mcs_keypoint {
+    float x, y;       /* pt, in level-0 pixel coordinates (pt *= mvScaleFactor[level], ORBextractor.cpp:1149-1151) */
+    float size;       /* (int)(31 * scale[level])  (ORBextractor.cpp:879, :889) */
+    float angle;      /* 0 in parity mode (ORBextractor.cpp:475); IC_Angle degrees when orientation is enabled */
+    float response;   /* FAST corner score */
+    int32_t octave;   /* pyramid level */
+    int32_t class_id; /* -1 */
+} mcs_keypoint;
+
+/* Per-camera calibration, the fields of CamArrayConfig (MCDataUtils/include/MCDataUtils/CamArrayConfig.h:24), all f64,
+ * row-major.  X_cam = R * X_ref + t. */
+typedef struct mcs_calib {
+    double K[9];
+    double R[9];
+    double t[3];
+    double dist[5]; /* dist[0] == 0 => keypoint undistortion is a copy (MultiCameraFrame.cpp:302-305) */
+} mcs_calib;
+
+MCS_API const char* mcs_last_error(void); /* thread-local, never NULL */
+MCS_API int mcs_device_count(void);
+MCS_API const char* mcs_version(void);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * ORBextractor  (replaces `new ORBextractor(nFeatures, fScaleFactor, nLevels, fIniThFAST, fMinThFAST)`, FrontEnd.h:190)
+ * One handle per concurrent caller, like the reference's one object per camera thread (MultiCameraFrame.cpp:234).
+ * max_images = how many same-sized images one batched call may carry (1 for the plain operator()).
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct mcs_extractor mcs_extractor;
+
+MCS_API mcs_extractor* mcs_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast,
+                                            int device, int max_width, int max_height, int max_images);
+MCS_API void mcs_extractor_destroy(mcs_extractor* ex);
+
+/* 0 = shipped behaviour (angle 0, un-steered BRIEF); 1 = IC_Angle + steered rBRIEF (ORBextractor.cpp:75-102, :106-145). */
+MCS_API int mcs_extractor_set_orientation(mcs_extractor* ex, int enable);
+
+/* Output capacity (keypoints per image) a caller must provide: nfeatures + 3 * nlevels rounded up. */
+MCS_API int mcs_extractor_capacity(const mcs_extractor* ex);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea)  (ORBextractor.cpp:1085-1171).
+ * image: CV_8UC1 host pixels, `stride` bytes per row.  mask is accepted and ignored exactly as the reference does
+ * (ORBextractor.h:56).  lapping = {x0, x1}: keypoints with x0 <= pt.x <= x1 are written from the back (:1153-1157).
+ * keypoints[capacity], descriptors[capacity*32].  *n_total = number of keypoints written (mono + stereo).
+ * Returns monoIndex (:1170), MCS_ERR_EMPTY for an empty image, or another negative code. */
+MCS_API int mcs_extract(mcs_extractor* ex, const uint8_t* image, int width, int height, int stride, const uint8_t* mask_ignored,
+                        const int lapping[2], mcs_keypoint* keypoints, uint8_t* descriptors, int capacity, int* n_total);
+
+/* The same for n_images same-sized images in one launch sequence (replaces the thread-per-camera fan-out,
+ * MultiCameraFrame.cpp:212-227).  images: n_images planes, `image_stride` bytes apart.  keypoints[n_images*capacity],
+ * descriptors[n_images*capacity*32], mono_index[n_images], n_total[n_images]. */
+MCS_API int mcs_extract_batch(mcs_extractor* ex, const uint8_t* images, int n_images, int width, int height, int stride,
+                              size_t image_stride, const int lapping[2], mcs_keypoint* keypoints, uint8_t* descriptors, int capacity,
+                              int* mono_index, int* n_total);
+
+/* GetLevels / GetScaleFactor(s) / GetInverseScaleFactors / GetScaleSigmaSquares / GetInverseScaleSigmaSquares
+ * (ORBextractor.h:61-81) and mnFeaturesPerLevel.  Each array has nlevels entries; NULL pointers are skipped. */
+MCS_API int mcs_extractor_get_tables(const mcs_extractor* ex, int* nlevels, float* scale_factors, float* inv_scale_factors,
+                                     float* level_sigma2, float* inv_level_sigma2, int* features_per_level);
+
+/* Observers of mvImagePyramid (ORBextractor.h:89) for image `image_index` of the last call.
+ * kind 0 = level pixels (w x h), 1 = level with its 19 px REFLECT_101 frame ((w+38) x (h+38)), 2 = 7x7 Gaussian-blurred level. */
+MCS_API int mcs_extractor_level_size(const mcs_extractor* ex, int level, int* width, int* height);
+MCS_API int mcs_extractor_download_level(mcs_extractor* ex, int image_index, int level, int kind, uint8_t* dst, int dst_stride);
+
+/* Stage observers for parity tests: FAST candidates of (image, level) before the octree (vToDistributeKeys,
+ * ORBextractor.cpp:864-867) as int32 triples (x, y, score) in ROI coordinates, in unspecified order. */
+MCS_API int mcs_extractor_download_candidates(mcs_extractor* ex, int image_index, int level, int32_t* xys, int capacity);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Multi-camera rig frame(s)  (replaces MultiCameraFrame's extract / intra-match / triangulate methods)
+ * A rig handle owns device workspace for up to max_frames rig frames of num_cams cameras and one CUDA stream.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct mcs_rig mcs_rig;
+
+typedef struct mcs_rig_config {
+    int num_cams;       /* <= MCS_MAX_CAMS (the reference hard-codes 5 in IntraMatch, MultiCameraFrame.h:44) */
+    int width, height;  /* every camera of the rig has the same size */
+    int nfeatures;      /* ORBextractor.nFeatures */
+    float scale_factor; /* ORBextractor.scaleFactor */
+    int nlevels;        /* ORBextractor.nLevels */
+    int ini_th_fast;    /* ORBextractor.iniThFAST */
+    int min_th_fast;    /* ORBextractor.minThFAST */
+    int max_frames;     /* rig frames per call (batch capacity) */
+    int device;         /* CUDA device ordinal */
+} mcs_rig_config;
+
+MCS_API mcs_rig* mcs_rig_create(const mcs_rig_config* cfg, const mcs_calib* calib /* [num_cams] */);
+MCS_API void mcs_rig_destroy(mcs_rig* rig);
+MCS_API int mcs_rig_feature_capacity(const mcs_rig* rig);  /* keypoints per camera */
+MCS_API int mcs_rig_row_capacity(const mcs_rig* rig);      /* IntraMatch rows per frame */
+MCS_API int mcs_rig_set_orientation(mcs_rig* rig, int enable);
+
+/* Stage A — extractFeaturesParallel()/extractFeatures() for n_frames rig frames (MultiCameraFrame.cpp:203, :266).
+ * images: host, [n_frames][num_cams][height][width] u8 tightly packed.  Results stay on the device. */
+MCS_API int mcs_rig_extract(mcs_rig* rig, const uint8_t* images, int n_frames);
+/* The same with images already resident in device memory (bench `value` leg); layout as above. */
+MCS_API int mcs_rig_extract_device(mcs_rig* rig, const void* d_images, int n_frames);
+
+/* image_kps[cam] / image_descriptors[cam] of frame `frame`.  Returns the keypoint count. */
+MCS_API int mcs_rig_get_features(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, uint8_t* descriptors, int capacity);
+
+/* Stage B1 — BruteForceMatch(img1_ind, img2_ind, dist_thresh, neigh_ratio, indices_1, indices_2, kps1, kps2)
+ * (MultiCameraFrame.cpp:1024-1086): knn k=2 Hamming, keep iff d0 < ratio*d1 and not d0 > dist_thresh, query order.
+ * kps1/kps2 may be NULL.  Returns the number of matches. */
+MCS_API int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float dist_thresh, float neigh_ratio,
+                                      uint32_t* indices_1, uint32_t* indices_2, mcs_keypoint* kps1, mcs_keypoint* kps2, int capacity);
+
+/* Stage B2 — computeIntraMatches(matches, old) (MultiCameraFrame.cpp:1100-1288) for the first n_frames frames:
+ * all camera pairs i<j through BruteForceMatch(i, j, dist_thresh, neigh_ratio) (the reference passes 75, 0.85),
+ * optional epipolar gate (old = true), merge into IntraMatch rows.  Results stay on the device. */
+MCS_API int mcs_rig_compute_intra_matches(mcs_rig* rig, int n_frames, int old_epipolar, float dist_thresh, float neigh_ratio);
+/* rows: int32 [capacity][num_cams] = IntraMatch::matchIndex (-1 = not seen).  Returns the row count M. */
+MCS_API int mcs_rig_get_intra_matches(mcs_rig* rig, int frame, int32_t* rows, int capacity);
+
+/* Stage C — triangulation block of FrontEnd::obtainLfFeatures (FrontEnd.cpp:249-370) for the first n_frames frames:
+ * mask filter (keep iff mask(int y, int x) < 0.7; masks = host float [n_frames][num_cams][height][width] or NULL for the
+ * all-zero masks the app ships), normalised coordinates, N-view DLT (cv::sfm::triangulatePoints), depth gate 0.5 < z < 40,
+ * uv_ref through K0, representative descriptor. */
+MCS_API int mcs_rig_triangulate(mcs_rig* rig, int n_frames, const float* masks);
+MCS_API int mcs_rig_triangulate_device_masks(mcs_rig* rig, int n_frames, const void* d_masks);
+typedef struct mcs_landmarks {
+    int32_t* rows;      /* [capacity][num_cams] matchIndex after the mask filter */
+    uint8_t* accepted;  /* [capacity] 1 = pushed to intraMatches (passed the depth gate) */
+    int32_t* n_views;   /* [capacity] views left after the mask filter (n_rays) */
+    double* xyz;        /* [capacity][3] point3D (f64) — valid when n_views >= 2 */
+    float* uv_ref;      /* [capacity][2] */
+    int32_t* rep_cam;   /* [capacity] camera whose descriptor is the representative one (matchDesc), -1 if none */
+} mcs_landmarks;
+MCS_API int mcs_rig_get_landmarks(mcs_rig* rig, int frame, mcs_landmarks* out, int capacity); /* returns M */
+
+/* MultiCameraFrame::triangulateIntraMatches(x, view_inds, pt) (MultiCameraFrame.cpp:411-441): N-view DLT of pixel
+ * coordinates through K[R|t].  xs/ys: [n_points][n_views]; xyz: [n_points][3]. */
+MCS_API int mcs_rig_triangulate_nview(mcs_rig* rig, const int* view_inds, int n_views, const double* xs, const double* ys, int n_points,
+                                      double* xyz);
+/* MultiCameraFrame::triangulate(kps_1, kps_2, pts3D, cam1, cam2) (MultiCameraFrame.cpp:481-507): 2-view f32 DLT. */
+MCS_API int mcs_rig_triangulate_pair(mcs_rig* rig, int cam1, int cam2, const float* pts1 /*[n][2]*/, const float* pts2, int n_points,
+                                     float* xyz /*[n][3]*/);
+
+/* Whole path in one call with HOST buffers (upload -> A -> B -> C -> download of counts, rows and landmarks): the call
+ * FrontEnd::processFrame makes, FrontEnd.cpp:991-1028.  Returns 0; per-frame results are read with the getters above. */
+MCS_API int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* masks, int n_frames, int old_epipolar);
+/* Same, inputs resident in device memory, nothing copied back (results are read with the getters). */
+MCS_API int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar);
+
+/* Compact per-frame summary copied back by mcs_rig_process: n keypoints per camera, M rows, accepted landmarks. */
+MCS_API int mcs_rig_get_counts(mcs_rig* rig, int frame, int* kp_counts /*[num_cams]*/, int* n_rows, int* n_accepted);
+
+/* Stream / timing plumbing for harnesses. */
+MCS_API void* mcs_rig_stream(mcs_rig* rig);                 /* cudaStream_t the rig launches on */
+MCS_API int mcs_rig_synchronize(mcs_rig* rig);
+MCS_API long long mcs_rig_kernel_launches(const mcs_rig* rig); /* kernels launched by this handle since creation */
+/* Device-time (ms, CUDA events on the rig's stream) of each stage of the last process/stage call:
+ * [0] upload, [1] pyramid, [2] FAST, [3] octree, [4] blur, [5] describe, [6] match, [7] merge, [8] triangulate, [9] download */
+MCS_API int mcs_rig_stage_times(mcs_rig* rig, float* ms10);
+MCS_API int mcs_rig_set_profiling(mcs_rig* rig, int enable); /* record the per-stage events (adds event overhead) */
+
+/* Plain device-memory helpers so harnesses written without a CUDA binding can stage resident inputs. */
+MCS_API void* mcs_device_malloc(int device, size_t bytes);
+MCS_API void mcs_device_free(int device, void* p);
+MCS_API int mcs_device_upload(int device, void* dst, const void* src, size_t bytes);
+MCS_API int mcs_device_download(int device, void* dst, const void* src, size_t bytes);
+MCS_API void* mcs_host_alloc_pinned(size_t bytes);
+MCS_API void mcs_host_free_pinned(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCSLAM_B200_H */
