@@ -1,0 +1,394 @@
+"""ctypes binding of libmcslam_b200.so — the host-side mirror of the reference's ORBextractor / MultiCameraFrame call shapes
+for Python harnesses (tests, bench).  Fails loudly when the CUDA library is missing or no GPU is present: there is no CPU path.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+CALIB_DTYPE = np.dtype([("K", "<f8", (9,)), ("R", "<f8", (9,)), ("t", "<f8", (3,)), ("dist", "<f8", (5,))])
+
+
+class McsError(RuntimeError):
+    pass
+
+
+class _RigConfig(C.Structure):
+    _fields_ = [("num_cams", C.c_int), ("width", C.c_int), ("height", C.c_int), ("nfeatures", C.c_int), ("scale_factor", C.c_float),
+                ("nlevels", C.c_int), ("ini_th_fast", C.c_int), ("min_th_fast", C.c_int), ("max_frames", C.c_int), ("device", C.c_int)]
+
+
+class _Landmarks(C.Structure):
+    _fields_ = [("rows", C.c_void_p), ("accepted", C.c_void_p), ("n_views", C.c_void_p), ("xyz", C.c_void_p), ("uv_ref", C.c_void_p),
+                ("rep_cam", C.c_void_p)]
+
+
+EXPORTS = [
+    "mcs_last_error", "mcs_device_count", "mcs_version", "mcs_extractor_create", "mcs_extractor_destroy", "mcs_extractor_set_orientation",
+    "mcs_extractor_capacity", "mcs_extract", "mcs_extract_batch", "mcs_extractor_get_tables", "mcs_extractor_level_size",
+    "mcs_extractor_download_level", "mcs_extractor_download_candidates", "mcs_rig_create", "mcs_rig_destroy", "mcs_rig_feature_capacity",
+    "mcs_rig_row_capacity", "mcs_rig_set_orientation", "mcs_rig_extract", "mcs_rig_extract_device", "mcs_rig_get_features",
+    "mcs_rig_brute_force_match", "mcs_rig_compute_intra_matches", "mcs_rig_get_intra_matches", "mcs_rig_triangulate",
+    "mcs_rig_triangulate_device_masks", "mcs_rig_get_landmarks", "mcs_rig_triangulate_nview", "mcs_rig_triangulate_pair", "mcs_rig_process",
+    "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
+    "mcs_rig_set_profiling", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
+    "mcs_host_free_pinned",
+]
+
+
+def library_path():
+    return os.path.join(_HERE, "libmcslam_b200.so")
+
+
+def lib():
+    """Loads the CUDA library.  Raises if it has not been built (python mc-slam_b200/build.py / __graft_entry__.build())."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        raise McsError("libmcslam_b200.so is missing: build it with __graft_entry__.build() — there is no CPU fallback")
+    L = C.CDLL(path)
+    vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+    L.mcs_last_error.restype = C.c_char_p
+    L.mcs_version.restype = C.c_char_p
+    L.mcs_extractor_create.restype = vp
+    L.mcs_extractor_create.argtypes = [ci, cf, ci, ci, ci, ci, ci, ci, ci]
+    L.mcs_extractor_destroy.argtypes = [vp]
+    L.mcs_extractor_set_orientation.argtypes = [vp, ci]
+    L.mcs_extractor_capacity.argtypes = [vp]
+    L.mcs_extract.argtypes = [vp, vp, ci, ci, ci, vp, vp, vp, vp, ci, vp]
+    L.mcs_extract_batch.argtypes = [vp, vp, ci, ci, ci, ci, C.c_size_t, vp, vp, vp, ci, vp, vp]
+    L.mcs_extractor_get_tables.argtypes = [vp] + [vp] * 6
+    L.mcs_extractor_level_size.argtypes = [vp, ci, vp, vp]
+    L.mcs_extractor_download_level.argtypes = [vp, ci, ci, ci, vp, ci]
+    L.mcs_extractor_download_candidates.argtypes = [vp, ci, ci, vp, ci]
+    L.mcs_rig_create.restype = vp
+    L.mcs_rig_create.argtypes = [vp, vp]
+    L.mcs_rig_destroy.argtypes = [vp]
+    L.mcs_rig_feature_capacity.argtypes = [vp]
+    L.mcs_rig_row_capacity.argtypes = [vp]
+    L.mcs_rig_set_orientation.argtypes = [vp, ci]
+    L.mcs_rig_extract.argtypes = [vp, vp, ci]
+    L.mcs_rig_extract_device.argtypes = [vp, vp, ci]
+    L.mcs_rig_get_features.argtypes = [vp, ci, ci, vp, vp, ci]
+    L.mcs_rig_brute_force_match.argtypes = [vp, ci, ci, ci, cf, cf, vp, vp, vp, vp, ci]
+    L.mcs_rig_compute_intra_matches.argtypes = [vp, ci, ci, cf, cf]
+    L.mcs_rig_get_intra_matches.argtypes = [vp, ci, vp, ci]
+    L.mcs_rig_triangulate.argtypes = [vp, ci, vp]
+    L.mcs_rig_triangulate_device_masks.argtypes = [vp, ci, vp]
+    L.mcs_rig_get_landmarks.argtypes = [vp, ci, vp, ci]
+    L.mcs_rig_triangulate_nview.argtypes = [vp, vp, ci, vp, vp, ci, vp]
+    L.mcs_rig_triangulate_pair.argtypes = [vp, ci, ci, vp, vp, ci, vp]
+    L.mcs_rig_process.argtypes = [vp, vp, vp, ci, ci]
+    L.mcs_rig_process_device.argtypes = [vp, vp, vp, ci, ci]
+    L.mcs_rig_get_counts.argtypes = [vp, ci, vp, vp, vp]
+    L.mcs_rig_stream.restype = vp
+    L.mcs_rig_stream.argtypes = [vp]
+    L.mcs_rig_synchronize.argtypes = [vp]
+    L.mcs_rig_kernel_launches.restype = C.c_longlong
+    L.mcs_rig_kernel_launches.argtypes = [vp]
+    L.mcs_rig_stage_times.argtypes = [vp, vp]
+    L.mcs_rig_set_profiling.argtypes = [vp, ci]
+    L.mcs_rig_download_level.argtypes = [vp, ci, ci, ci, ci, vp, ci]
+    L.mcs_rig_level_size.argtypes = [vp, ci, vp, vp]
+    L.mcs_device_malloc.restype = vp
+    L.mcs_device_malloc.argtypes = [ci, C.c_size_t]
+    L.mcs_device_free.argtypes = [ci, vp]
+    L.mcs_device_upload.argtypes = [ci, vp, vp, C.c_size_t]
+    L.mcs_device_download.argtypes = [ci, vp, vp, C.c_size_t]
+    L.mcs_host_alloc_pinned.restype = vp
+    L.mcs_host_alloc_pinned.argtypes = [C.c_size_t]
+    L.mcs_host_free_pinned.argtypes = [vp]
+    _LIB = L
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _check(rc, what):
+    if rc < 0:
+        raise McsError("%s failed (%d): %s" % (what, rc, lib().mcs_last_error().decode()))
+    return rc
+
+
+def pinned_empty(shape, dtype):
+    """numpy array backed by page-locked host memory (freed with the library's allocator when collected)."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    ptr = lib().mcs_host_alloc_pinned(max(n, 1))
+    if not ptr:
+        raise McsError("pinned allocation failed")
+    buf = (C.c_char * max(n, 1)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    return _Pinned(arr, ptr)
+
+
+class _Pinned:
+    def __init__(self, arr, ptr):
+        self.arr, self.ptr = arr, ptr
+
+    def __del__(self):
+        try:
+            lib().mcs_host_free_pinned(self.ptr)
+        except Exception:
+            pass
+
+
+class Extractor:
+    """Mirror of ORBextractor (MCSlam/include/MCSlam/ORBextractor.h:44-112): `n = ex(image, mask, keypoints..., vLappingArea)`."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, device=0, max_width=720, max_height=540,
+                 max_images=1):
+        L = lib()
+        self.h = L.mcs_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th, device, max_width, max_height, max_images)
+        if not self.h:
+            raise McsError("mcs_extractor_create failed: " + L.mcs_last_error().decode())
+        self.nlevels = nlevels
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().mcs_extractor_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    @property
+    def capacity(self):
+        return lib().mcs_extractor_capacity(self.h)
+
+    def set_orientation(self, on):
+        _check(lib().mcs_extractor_set_orientation(self.h, int(on)), "set_orientation")
+
+    def tables(self):
+        n = self.nlevels
+        sf, inv, s2, is2 = (np.zeros(n, np.float32) for _ in range(4))
+        q = np.zeros(n, np.int32)
+        nl = C.c_int()
+        _check(lib().mcs_extractor_get_tables(self.h, C.byref(nl), _p(sf), _p(inv), _p(s2), _p(is2), _p(q)), "get_tables")
+        return dict(nlevels=nl.value, scale=sf, inv_scale=inv, sigma2=s2, inv_sigma2=is2, quota=q)
+
+    def __call__(self, image, mask=None, lapping=(0, 0)):
+        """operator()(image, mask, keypoints, descriptors, vLappingArea) -> (monoIndex, keypoints, descriptors)."""
+        if image is None or image.size == 0:  # `if(_image.empty()) return -1;` — answered by the library itself
+            nt = C.c_int()
+            rc = lib().mcs_extract(self.h, None, 0, 0, 0, None, None, None, None, 0, C.byref(nt))
+            return rc, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2 and image.strides[1] == 1
+        h, w = image.shape
+        lap = np.array(lapping, np.int32)
+        rc = 0
+        for attempt in range(2):  # capacity depends on the (image-size dependent) plan; retry once with the real value
+            cap = max(self.capacity, 8)
+            kps = np.zeros(cap, KP_DTYPE)
+            desc = np.zeros((cap, 32), np.uint8)
+            nt = C.c_int()
+            rc = lib().mcs_extract(self.h, C.c_void_p(image.ctypes.data), w, h, image.strides[0], None, _p(lap), _p(kps), _p(desc), cap,
+                                   C.byref(nt))
+            if rc != -2 or self.capacity <= cap:
+                break
+        _check(rc, "mcs_extract")
+        return rc, kps[:nt.value].copy(), desc[:nt.value].copy()
+
+    def extract_batch(self, images, lapping=(0, 0)):
+        images = np.ascontiguousarray(images, np.uint8)
+        n, h, w = images.shape
+        lap = np.array(lapping, np.int32)
+        mono = np.zeros(n, np.int32)
+        tot = np.zeros(n, np.int32)
+        rc = 0
+        for attempt in range(2):
+            cap = max(self.capacity, 8)
+            kps = np.zeros((n, cap), KP_DTYPE)
+            desc = np.zeros((n, cap, 32), np.uint8)
+            rc = lib().mcs_extract_batch(self.h, _p(images), n, w, h, w, w * h, _p(lap), _p(kps), _p(desc), cap, _p(mono), _p(tot))
+            if rc != -2 or self.capacity <= cap:
+                break
+        _check(rc, "mcs_extract_batch")
+        return mono, [kps[i, :tot[i]].copy() for i in range(n)], [desc[i, :tot[i]].copy() for i in range(n)]
+
+    def level(self, image_index, level, kind=0):
+        w, h = C.c_int(), C.c_int()
+        _check(lib().mcs_extractor_level_size(self.h, level, C.byref(w), C.byref(h)), "level_size")
+        pad = 38 if kind == 1 else 0
+        out = np.zeros((h.value + pad, w.value + pad), np.uint8)
+        _check(lib().mcs_extractor_download_level(self.h, image_index, level, kind, _p(out), out.shape[1]), "download_level")
+        return out
+
+    def candidates(self, image_index, level):
+        cap = 1 << 20
+        out = np.zeros((cap, 3), np.int32)
+        n = _check(lib().mcs_extractor_download_candidates(self.h, image_index, level, _p(out), cap), "download_candidates")
+        return out[:n].copy()
+
+
+class RigFrames:
+    """Mirror of MultiCameraFrame's extract / intra-match / triangulate entry points for a batch of rig frames."""
+
+    def __init__(self, calib, width=720, height=540, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, max_frames=1,
+                 device=0):
+        L = lib()
+        self.calib = np.ascontiguousarray(calib, CALIB_DTYPE)
+        self.C, self.w, self.h, self.F, self.device = len(self.calib), width, height, max_frames, device
+        cfg = _RigConfig(self.C, width, height, nfeatures, scale_factor, nlevels, ini_th, min_th, max_frames, device)
+        self.hd = L.mcs_rig_create(C.byref(cfg), _p(self.calib))
+        if not self.hd:
+            raise McsError("mcs_rig_create failed: " + L.mcs_last_error().decode())
+        self.kp_cap = L.mcs_rig_feature_capacity(self.hd)
+        self.row_cap = L.mcs_rig_row_capacity(self.hd)
+        self.nlevels = nlevels
+
+    def close(self):
+        if getattr(self, "hd", None):
+            lib().mcs_rig_destroy(self.hd)
+            self.hd = None
+
+    __del__ = close
+
+    def set_orientation(self, on):
+        _check(lib().mcs_rig_set_orientation(self.hd, int(on)), "rig_set_orientation")
+
+    # --- stage A: extractFeaturesParallel (MultiCameraFrame.cpp:203) -------------------------------------------------
+    def extract(self, images):
+        images = np.ascontiguousarray(images, np.uint8).reshape(-1, self.C, self.h, self.w)
+        _check(lib().mcs_rig_extract(self.hd, _p(images), images.shape[0]), "mcs_rig_extract")
+        return images.shape[0]
+
+    def extract_device(self, d_ptr, n_frames):
+        _check(lib().mcs_rig_extract_device(self.hd, C.c_void_p(d_ptr), n_frames), "mcs_rig_extract_device")
+
+    def features(self, frame, cam):
+        kps = np.zeros(self.kp_cap, KP_DTYPE)
+        desc = np.zeros((self.kp_cap, 32), np.uint8)
+        n = _check(lib().mcs_rig_get_features(self.hd, frame, cam, _p(kps), _p(desc), self.kp_cap), "mcs_rig_get_features")
+        return kps[:n].copy(), desc[:n].copy()
+
+    # --- stage B: BruteForceMatch / computeIntraMatches (MultiCameraFrame.cpp:1024, :1100) ---------------------------
+    def brute_force_match(self, frame, cam1, cam2, dist_thresh=75.0, ratio=0.85):
+        i1 = np.zeros(self.kp_cap, np.uint32)
+        i2 = np.zeros(self.kp_cap, np.uint32)
+        k1 = np.zeros(self.kp_cap, KP_DTYPE)
+        k2 = np.zeros(self.kp_cap, KP_DTYPE)
+        n = _check(lib().mcs_rig_brute_force_match(self.hd, frame, cam1, cam2, dist_thresh, ratio, _p(i1), _p(i2), _p(k1), _p(k2),
+                                                   self.kp_cap), "mcs_rig_brute_force_match")
+        return i1[:n].copy(), i2[:n].copy(), k1[:n].copy(), k2[:n].copy()
+
+    def compute_intra_matches(self, n_frames, old=False, dist_thresh=75.0, ratio=0.85):
+        _check(lib().mcs_rig_compute_intra_matches(self.hd, n_frames, int(old), dist_thresh, ratio), "mcs_rig_compute_intra_matches")
+
+    def intra_matches(self, frame):
+        rows = np.zeros((self.row_cap, self.C), np.int32)
+        m = _check(lib().mcs_rig_get_intra_matches(self.hd, frame, _p(rows), self.row_cap), "mcs_rig_get_intra_matches")
+        return rows[:m].copy()
+
+    # --- stage C: obtainLfFeatures triangulation block (FrontEnd.cpp:249-370) ----------------------------------------
+    def triangulate(self, n_frames, masks=None):
+        if masks is not None:
+            masks = np.ascontiguousarray(masks, np.float32).reshape(n_frames, self.C, self.h, self.w)
+        _check(lib().mcs_rig_triangulate(self.hd, n_frames, _p(masks)), "mcs_rig_triangulate")
+
+    def landmarks(self, frame):
+        cap = self.row_cap
+        rows = np.zeros((cap, self.C), np.int32)
+        acc = np.zeros(cap, np.uint8)
+        nv = np.zeros(cap, np.int32)
+        xyz = np.zeros((cap, 3), np.float64)
+        uv = np.zeros((cap, 2), np.float32)
+        rep = np.zeros(cap, np.int32)
+        lm = _Landmarks(rows.ctypes.data, acc.ctypes.data, nv.ctypes.data, xyz.ctypes.data, uv.ctypes.data, rep.ctypes.data)
+        m = _check(lib().mcs_rig_get_landmarks(self.hd, frame, C.byref(lm), cap), "mcs_rig_get_landmarks")
+        return dict(rows=rows[:m].copy(), status=acc[:m].copy(), nviews=nv[:m].copy(), xyz=xyz[:m].copy(), uv_ref=uv[:m].copy(),
+                    rep_cam=rep[:m].copy())
+
+    def triangulate_nview(self, view_inds, xs, ys):
+        vi = np.ascontiguousarray(view_inds, np.int32)
+        xs = np.ascontiguousarray(xs, np.float64).reshape(-1, len(vi))
+        ys = np.ascontiguousarray(ys, np.float64).reshape(-1, len(vi))
+        out = np.zeros((xs.shape[0], 3), np.float64)
+        _check(lib().mcs_rig_triangulate_nview(self.hd, _p(vi), len(vi), _p(xs), _p(ys), xs.shape[0], _p(out)), "mcs_rig_triangulate_nview")
+        return out
+
+    def triangulate_pair(self, cam1, cam2, p1, p2):
+        p1 = np.ascontiguousarray(p1, np.float32).reshape(-1, 2)
+        p2 = np.ascontiguousarray(p2, np.float32).reshape(-1, 2)
+        out = np.zeros((len(p1), 3), np.float32)
+        _check(lib().mcs_rig_triangulate_pair(self.hd, cam1, cam2, _p(p1), _p(p2), len(p1), _p(out)), "mcs_rig_triangulate_pair")
+        return out
+
+    # --- whole path (FrontEnd::processFrame, FrontEnd.cpp:991-1028) -------------------------------------------------
+    def process(self, images, masks=None, old=False, n_frames=None):
+        """images: uint8 [F, C, h, w] host array (or raw pointer int with n_frames)."""
+        if isinstance(images, int):
+            ptr, nf = C.c_void_p(images), n_frames
+        else:
+            images = np.ascontiguousarray(images, np.uint8).reshape(-1, self.C, self.h, self.w)
+            ptr, nf = _p(images), images.shape[0]
+        mp = None
+        if masks is not None:
+            if isinstance(masks, int):
+                mp = C.c_void_p(masks)
+            else:
+                masks = np.ascontiguousarray(masks, np.float32)
+                mp = _p(masks)
+        _check(lib().mcs_rig_process(self.hd, ptr, mp, nf, int(old)), "mcs_rig_process")
+        return nf
+
+    def process_device(self, d_images, n_frames, d_masks=None, old=False):
+        _check(lib().mcs_rig_process_device(self.hd, C.c_void_p(d_images), C.c_void_p(d_masks) if d_masks else None, n_frames, int(old)),
+               "mcs_rig_process_device")
+
+    def counts(self, frame):
+        kc = np.zeros(self.C, np.int32)
+        nr, na = C.c_int(), C.c_int()
+        _check(lib().mcs_rig_get_counts(self.hd, frame, _p(kc), C.byref(nr), C.byref(na)), "mcs_rig_get_counts")
+        return kc, nr.value, na.value
+
+    def synchronize(self):
+        _check(lib().mcs_rig_synchronize(self.hd), "mcs_rig_synchronize")
+
+    @property
+    def stream(self):
+        return lib().mcs_rig_stream(self.hd)
+
+    @property
+    def kernel_launches(self):
+        return lib().mcs_rig_kernel_launches(self.hd)
+
+    def set_profiling(self, on):
+        lib().mcs_rig_set_profiling(self.hd, int(on))
+
+    def stage_times(self):
+        ms = np.zeros(10, np.float32)
+        _check(lib().mcs_rig_stage_times(self.hd, _p(ms)), "mcs_rig_stage_times")
+        names = ["upload", "pyramid", "fast", "octree", "blur", "describe", "match", "merge", "triangulate", "download"]
+        return dict(zip(names, ms.tolist()))
+
+    def level(self, frame, cam, level, kind=0):
+        w, h = C.c_int(), C.c_int()
+        _check(lib().mcs_rig_level_size(self.hd, level, C.byref(w), C.byref(h)), "rig_level_size")
+        pad = 38 if kind == 1 else 0
+        out = np.zeros((h.value + pad, w.value + pad), np.uint8)
+        _check(lib().mcs_rig_download_level(self.hd, frame, cam, level, kind, _p(out), out.shape[1]), "rig_download_level")
+        return out
+
+
+def device_malloc(device, nbytes):
+    p = lib().mcs_device_malloc(device, nbytes)
+    if not p:
+        raise McsError("device malloc failed: " + lib().mcs_last_error().decode())
+    return p
+
+
+def device_free(device, p):
+    lib().mcs_device_free(device, C.c_void_p(p))
+
+
+def device_upload(device, dptr, arr):
+    arr = np.ascontiguousarray(arr)
+    _check(lib().mcs_device_upload(device, C.c_void_p(dptr), _p(arr), arr.nbytes), "device_upload")

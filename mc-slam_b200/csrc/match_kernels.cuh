@@ -1,0 +1,400 @@
+// match_kernels.cuh — sm_100a kernels for the intra-rig stages of MultiCameraFrame / FrontEnd:
+//   K6 hamming_match_kernel : BruteForceMatch (/root/reference/MCSlam/src/MultiCameraFrame.cpp:1024-1086) for every camera
+//                             pair i<j of every frame: 256-bit XOR + popc, running top-2, ratio + distance gate fused;
+//                             no distance matrix ever reaches HBM.
+//   K7 merge_kernel         : computeIntraMatches(matches, old) merge step (:1100-1288) incl. the optional epipolar gate.
+//   K8 triangulate_kernel   : FrontEnd::obtainLfFeatures triangulation block (MCSlam/src/FrontEnd.cpp:249-370): mask
+//                             filter, normalised coordinates, N-view DLT (cv::sfm::triangulatePoints), depth gate, uv_ref,
+//                             representative descriptor (MultiCameraFrame.cpp:530-567).
+//   + standalone N-view (MultiCameraFrame.cpp:411-441) and 2-view f32 (:481-507) DLT kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "extract_kernels.cuh"
+
+namespace mcs {
+
+#define MCS_MATCH_NT 128
+#define MCS_MATCH_CHUNK 1024  // train descriptors staged in shared memory per pass (32 KB)
+
+struct PairList {
+    int n_pairs;
+    unsigned char a[28], b[28];  // camera pairs i<j in the reference's loop order (:1110-1111)
+};
+
+// match_train[(frame * n_pairs + pair) * kp_cap + q] = accepted train index of query q, or -1.
+// match_d0 (optional) gets the best distance for diagnostics/tests.
+__global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cams, int kp_cap, PairList pairs, int frame0,
+                                                                     const uint8_t* __restrict__ desc, const int* __restrict__ kp_count,
+                                                                     float dist_thresh, float ratio, int* __restrict__ match_train,
+                                                                     int* __restrict__ match_d0, int* __restrict__ match_d1) {
+    extern __shared__ __align__(16) uint4 s_train[];  // [MCS_MATCH_CHUNK][2]
+    const int frame = frame0 + blockIdx.z, pair = blockIdx.y;  // outputs are indexed by blockIdx.z (frame0 = scratch calls)
+    const int ca = frame * num_cams + pairs.a[pair], cb = frame * num_cams + pairs.b[pair];
+    const int nq = kp_count[ca], nt = kp_count[cb];
+    const int q0i = blockIdx.x * MCS_MATCH_NT;
+    if (q0i >= nq) return;
+    const int q = q0i + threadIdx.x;
+    const bool active = q < nq;
+    uint4 qa = make_uint4(0, 0, 0, 0), qb = qa;
+    if (active) {
+        const uint4* qp = reinterpret_cast<const uint4*>(desc + ((size_t)ca * kp_cap + q) * 32);
+        qa = __ldg(qp);
+        qb = __ldg(qp + 1);
+    }
+    int d0 = 1 << 20, d1 = 1 << 20, i0 = -1;
+    const uint4* tbase = reinterpret_cast<const uint4*>(desc + (size_t)cb * kp_cap * 32);
+    for (int c0 = 0; c0 < nt; c0 += MCS_MATCH_CHUNK) {
+        const int m = min(MCS_MATCH_CHUNK, nt - c0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < m * 2; t += MCS_MATCH_NT) s_train[t] = __ldg(tbase + (size_t)c0 * 2 + t);
+        __syncthreads();
+        if (active) {
+#pragma unroll 4
+            for (int j = 0; j < m; j++) {
+                const uint4 ta = s_train[2 * j], tb = s_train[2 * j + 1];
+                const int d = __popc(qa.x ^ ta.x) + __popc(qa.y ^ ta.y) + __popc(qa.z ^ ta.z) + __popc(qa.w ^ ta.w) +
+                              __popc(qb.x ^ tb.x) + __popc(qb.y ^ tb.y) + __popc(qb.z ^ tb.z) + __popc(qb.w ^ tb.w);
+                if (d < d0) {  // strict '<': on ties the lower train index stays first, as knnMatch orders them
+                    d1 = d0;
+                    d0 = d;
+                    i0 = c0 + j;
+                } else if (d < d1) {
+                    d1 = d;
+                }
+            }
+        }
+    }
+    if (!active) return;
+    // m[0].distance < neigh_ratio * m[1].distance  and not  m[0].distance > dist_thresh   (:1061-1063), f32 arithmetic.
+    // With fewer than 2 train descriptors the reference reads m[1] out of range; here: no match.
+    bool ok = nt >= 2 && ((float)d0 < __fmul_rn(ratio, (float)d1)) && !((float)d0 > dist_thresh);
+    const size_t o = ((size_t)blockIdx.z * pairs.n_pairs + pair) * kp_cap + q;
+    match_train[o] = ok ? i0 : -1;
+    if (match_d0) match_d0[o] = d0;
+    if (match_d1) match_d1[o] = d1;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K7  merge.  The reference mutates match_inv_idx in pair order, later pairs see earlier state (:1222-1266), so the
+// walk is sequential per frame: one block per frame, thread 0 walks, the block initialises.  match_inv_idx lives in
+// shared memory (u16, 0xFFFF = -1).
+// Fmat: per pair the f64 fundamental matrix built on the host (:1126-1141); sigma2 = mvLevelSigma2.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) merge_kernel(int num_cams, int kp_cap, int row_cap, PairList pairs,
+                                                    const int* __restrict__ kp_count, const int* __restrict__ match_train,
+                                                    const KeypointPod* __restrict__ kps, int use_epipolar,
+                                                    const double* __restrict__ Fmat, const float* __restrict__ sigma2,
+                                                    int* __restrict__ rows, int* __restrict__ row_count) {
+    extern __shared__ __align__(16) uint16_t s_inv[];  // [num_cams][kp_cap]
+    const int frame = blockIdx.x;
+    int* R = rows + (size_t)frame * row_cap * num_cams;
+    for (int t = threadIdx.x; t < num_cams * kp_cap; t += blockDim.x) s_inv[t] = 0xFFFFu;
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    int M = 0;
+    for (int p = 0; p < pairs.n_pairs; p++) {
+        const int i = pairs.a[p], j = pairs.b[p];
+        const int nq = kp_count[frame * num_cams + i];
+        const int* mt = match_train + ((size_t)frame * pairs.n_pairs + p) * kp_cap;
+        const double* F = Fmat + p * 9;
+        uint16_t* invi = s_inv + i * kp_cap;
+        uint16_t* invj = s_inv + j * kp_cap;
+        int nxt = nq > 0 ? mt[0] : -1;
+        for (int q = 0; q < nq; q++) {
+            const int fj = nxt;
+            if (q + 1 < nq) nxt = mt[q + 1];  // prefetch: the walk is latency-bound
+            if (fj < 0) continue;
+            const int fi = q;
+            if (use_epipolar) {
+                // :1177-1205 — products in f64 (no FMA contraction), narrowed to f32 exactly where the reference does
+                const KeypointPod p1 = kps[(size_t)(frame * num_cams + i) * kp_cap + fi];
+                const KeypointPod p2 = kps[(size_t)(frame * num_cams + j) * kp_cap + fj];
+                float a = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[0]), __dmul_rn((double)p2.y, F[3])), F[6]);
+                float b = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[1]), __dmul_rn((double)p2.y, F[4])), F[7]);
+                float c = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[2]), __dmul_rn((double)p2.y, F[5])), F[8]);
+                float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+                den = den != 0.f ? (float)__ddiv_rn(1.0, __dsqrt_rn((double)den)) : 1.f;
+                a = __fmul_rn(a, den);
+                b = __fmul_rn(b, den);
+                c = __fmul_rn(c, den);
+                den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+                const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, p1.x), __fmul_rn(b, p1.y)), c);
+                bool res;
+                if (den == 0.f) res = false;
+                else {
+                    const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+                    const float thr = (float)__dmul_rn(3.84, (double)sigma2[p1.octave]);
+                    res = dsqr < thr;
+                }
+                if (!res) continue;
+            }
+            const int mi = invi[fi] == 0xFFFFu ? -1 : (int)invi[fi];
+            const int mj = invj[fj] == 0xFFFFu ? -1 : (int)invj[fj];
+            if (mi == -1 && mj == -1) {
+                if (M < row_cap) {
+                    int* r = R + (size_t)M * num_cams;
+                    for (int c = 0; c < num_cams; c++) r[c] = -1;
+                    r[i] = fi;
+                    r[j] = fj;
+                    invi[fi] = (uint16_t)M;
+                    invj[fj] = (uint16_t)M;
+                }
+                M++;
+            } else if (mi == -1 && mj != -1) {
+                if (R[(size_t)mj * num_cams + i] == -1) {
+                    R[(size_t)mj * num_cams + i] = fi;
+                    invi[fi] = (uint16_t)mj;
+                }
+            } else if (mi != -1 && mj == -1) {
+                R[(size_t)mi * num_cams + j] = fj;
+                invj[fj] = (uint16_t)mi;
+            }
+        }
+    }
+    row_count[frame] = M;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// One-sided (Hestenes) Jacobi SVD: right singular vector of the smallest singular value of A (m x n) = cv::SVD::solveZ.
+// Per-thread, arrays in local memory.  T = double for the sfm path, float for MultiCameraFrame::triangulate.
+// ------------------------------------------------------------------------------------------------------------
+template <typename T, int MAXM, int MAXN>
+__device__ void null_vector(T (&A)[MAXM * MAXN], T (&V)[MAXN * MAXN], int m, int n, T* z, T eps) {
+    for (int i = 0; i < n * n; i++) V[i] = 0;
+    for (int i = 0; i < n; i++) V[i * n + i] = 1;
+    for (int sweep = 0; sweep < 60; sweep++) {
+        bool changed = false;
+        for (int p = 0; p < n - 1; p++)
+            for (int q = p + 1; q < n; q++) {
+                T a = 0, b = 0, g = 0;
+                for (int k = 0; k < m; k++) {
+                    const T x = A[k * n + p], y = A[k * n + q];
+                    a += x * x;
+                    b += y * y;
+                    g += x * y;
+                }
+                if (fabs((double)g) <= (double)eps * sqrt((double)a * (double)b) || g == 0) continue;
+                changed = true;
+                const T zeta = (b - a) / (2 * g);
+                const T t = (zeta >= 0 ? (T)1 : (T)-1) / ((T)fabs((double)zeta) + (T)sqrt((double)(1 + zeta * zeta)));
+                const T c = (T)1 / (T)sqrt((double)(1 + t * t)), s = c * t;
+                for (int k = 0; k < m; k++) {
+                    const T x = A[k * n + p], y = A[k * n + q];
+                    A[k * n + p] = c * x - s * y;
+                    A[k * n + q] = s * x + c * y;
+                }
+                for (int k = 0; k < n; k++) {
+                    const T x = V[k * n + p], y = V[k * n + q];
+                    V[k * n + p] = c * x - s * y;
+                    V[k * n + q] = s * x + c * y;
+                }
+            }
+        if (!changed) break;
+    }
+    int best = 0;
+    T bestn = -1;
+    for (int j = 0; j < n; j++) {
+        T s = 0;
+        for (int k = 0; k < m; k++) s += A[k * n + j] * A[k * n + j];
+        if (bestn < 0 || s < bestn) {
+            bestn = s;
+            best = j;
+        }
+    }
+    for (int k = 0; k < n; k++) z[k] = V[k * n + best];
+}
+
+struct CalibDev {  // per camera: K (9), [R|t] (12), K[R|t] (12), all f64 row-major
+    double K[9];
+    double Rt[12];
+    double P[12];
+};
+
+__device__ __forceinline__ int hamming256(const uint8_t* a, const uint8_t* b) {
+    const uint4* pa = reinterpret_cast<const uint4*>(a);
+    const uint4* pb = reinterpret_cast<const uint4*>(b);
+    const uint4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
+           __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// N-view DLT on projections Pm[k] (3x4) and points (xs[k], ys[k]); n >= 2.  2 views: 4x4 system; else (3n) x (4+n).
+template <int MAXC>
+__device__ void dlt_nviews(const double* const* Pm, const double* xs, const double* ys, int nv, bool force_design, double* X3) {
+    double A[3 * MAXC * (4 + MAXC)];
+    double V[(4 + MAXC) * (4 + MAXC)];
+    double z[4 + MAXC];
+    int m, n;
+    if (nv == 2 && !force_design) {
+        m = 4;
+        n = 4;
+        for (int i = 0; i < 4; i++) {
+            A[0 * 4 + i] = xs[0] * Pm[0][8 + i] - Pm[0][i];
+            A[1 * 4 + i] = ys[0] * Pm[0][8 + i] - Pm[0][4 + i];
+            A[2 * 4 + i] = xs[1] * Pm[1][8 + i] - Pm[1][i];
+            A[3 * 4 + i] = ys[1] * Pm[1][8 + i] - Pm[1][4 + i];
+        }
+    } else {
+        m = 3 * nv;
+        n = 4 + nv;
+        for (int i = 0; i < m * n; i++) A[i] = 0;
+        for (int i = 0; i < nv; i++) {
+            for (int jj = 0; jj < 3; jj++)
+                for (int ii = 0; ii < 4; ii++) A[(3 * i + jj) * n + ii] = -Pm[i][jj * 4 + ii];
+            A[(3 * i + 0) * n + 4 + i] = xs[i];
+            A[(3 * i + 1) * n + 4 + i] = ys[i];
+            A[(3 * i + 2) * n + 4 + i] = 1.0;
+        }
+    }
+    null_vector<double, 3 * MAXC, 4 + MAXC>(A, V, m, n, z, 2.220446049250313e-16);
+    X3[0] = z[0] / z[3];
+    X3[1] = z[1] / z[3];
+    X3[2] = z[2] / z[3];
+}
+
+struct LandmarkOut {
+    int* rows;          // [frames][row_cap][num_cams]
+    uint8_t* accepted;  // [frames][row_cap]
+    int* n_views;
+    double* xyz;        // [frames][row_cap][3]
+    float* uv_ref;      // [frames][row_cap][2]
+    int* rep_cam;
+    int* n_accepted;    // [frames]
+};
+
+template <int MAXC>
+__global__ void __launch_bounds__(64) triangulate_kernel(int num_cams, int kp_cap, int row_cap, int width, int height,
+                                                         const CalibDev* __restrict__ calib, const int* __restrict__ rows_in,
+                                                         const int* __restrict__ row_count, const KeypointPod* __restrict__ kps,
+                                                         const uint8_t* __restrict__ desc, const float* __restrict__ masks,
+                                                         LandmarkOut out) {
+    const int frame = blockIdx.y;
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    const int M = min(row_count[frame], row_cap);
+    if (r >= M) return;
+    const size_t ro = (size_t)frame * row_cap + r;
+    const int* row = rows_in + ro * num_cams;
+    int views[MAXC], feats[MAXC];
+    int nv = 0;
+    for (int c = 0; c < num_cams; c++) {
+        int f = row[c];
+        if (f != -1) {
+            bool keep = true;
+            if (masks) {
+                const KeypointPod p = kps[(size_t)(frame * num_cams + c) * kp_cap + f];
+                int my = (int)p.y, mx = (int)p.x;  // Mat::at<float>(float, float): truncation
+                my = min(max(my, 0), height - 1);
+                mx = min(max(mx, 0), width - 1);
+                keep = (double)masks[((size_t)(frame * num_cams + c) * height + my) * width + mx] < 0.7;  // :266
+            }
+            if (keep) {
+                views[nv] = c;
+                feats[nv] = f;
+                nv++;
+            } else {
+                f = -1;
+            }
+        }
+        out.rows[ro * num_cams + c] = f;
+    }
+    out.n_views[ro] = nv;
+    out.accepted[ro] = 0;
+    out.rep_cam[ro] = nv == 1 ? views[0] : -1;
+    double X[3] = {0, 0, 0};
+    float u = 0, v = 0;
+    if (nv >= 2) {
+        double xs[MAXC], ys[MAXC];
+        const double* Pm[MAXC];
+        for (int k = 0; k < nv; k++) {
+            const int c = views[k];
+            const KeypointPod p = kps[(size_t)(frame * num_cams + c) * kp_cap + feats[k]];
+            xs[k] = ((double)p.x - calib[c].K[2]) / calib[c].K[0];  // :292-298
+            ys[k] = ((double)p.y - calib[c].K[5]) / calib[c].K[4];
+            Pm[k] = calib[c].Rt;
+        }
+        dlt_nviews<MAXC>(Pm, xs, ys, nv, false, X);
+        // representative descriptor: least median Hamming distance, first wins (MultiCameraFrame.cpp:530-567)
+        int bestMedian = 0x7FFFFFFF, bestIdx = 0;
+        for (int a = 0; a < nv; a++) {
+            int d[MAXC];
+            for (int b = 0; b < nv; b++)
+                d[b] = a == b ? 0
+                              : hamming256(desc + ((size_t)(frame * num_cams + views[a]) * kp_cap + feats[a]) * 32,
+                                           desc + ((size_t)(frame * num_cams + views[b]) * kp_cap + feats[b]) * 32);
+            for (int i = 1; i < nv; i++) {  // insertion sort (values only: ties are indistinguishable)
+                const int key = d[i];
+                int j = i - 1;
+                while (j >= 0 && d[j] > key) {
+                    d[j + 1] = d[j];
+                    j--;
+                }
+                d[j + 1] = key;
+            }
+            const int median = d[(int)(0.5 * (nv - 1))];
+            if (median < bestMedian) {
+                bestMedian = median;
+                bestIdx = a;
+            }
+        }
+        out.rep_cam[ro] = views[bestIdx];
+        if (X[2] < 40 && X[2] > 0.5) {  // :308
+            out.accepted[ro] = 1;
+            atomicAdd(&out.n_accepted[frame], 1);
+            const double* K0 = calib[0].K;
+            const double px = K0[0] * X[0] + K0[1] * X[1] + K0[2] * X[2];
+            const double py = K0[3] * X[0] + K0[4] * X[1] + K0[5] * X[2];
+            const double pz = K0[6] * X[0] + K0[7] * X[1] + K0[8] * X[2];
+            u = (float)(px / pz);
+            v = (float)(py / pz);
+        }
+    }
+    out.xyz[ro * 3] = X[0];
+    out.xyz[ro * 3 + 1] = X[1];
+    out.xyz[ro * 3 + 2] = X[2];
+    out.uv_ref[ro * 2] = u;
+    out.uv_ref[ro * 2 + 1] = v;
+}
+
+// MultiCameraFrame::triangulateIntraMatches(x, view_inds, pt) (:411-441): always the (3n) x (4+n) design, K[R|t], pixels.
+template <int MAXC>
+__global__ void triangulate_nview_kernel(const CalibDev* __restrict__ calib, const int* __restrict__ view_inds, int nv,
+                                         const double* __restrict__ xs, const double* __restrict__ ys, int npts, double* __restrict__ xyz) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npts) return;
+    const double* Pm[MAXC];
+    double x[MAXC], y[MAXC];
+    for (int k = 0; k < nv; k++) {
+        Pm[k] = calib[view_inds[k]].P;
+        x[k] = xs[(size_t)i * nv + k];
+        y[k] = ys[(size_t)i * nv + k];
+    }
+    double X[3];
+    dlt_nviews<MAXC>(Pm, x, y, nv, true, X);
+    xyz[i * 3] = X[0];
+    xyz[i * 3 + 1] = X[1];
+    xyz[i * 3 + 2] = X[2];
+}
+
+// MultiCameraFrame::triangulate(kps_1, kps_2, pts3D, cam1, cam2) (:481-507): 4x4 f32 DLT.
+__global__ void triangulate_pair_f32_kernel(const CalibDev* __restrict__ calib, int cam1, int cam2, const float* __restrict__ p1,
+                                            const float* __restrict__ p2, int npts, float* __restrict__ xyz) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npts) return;
+    const double* P1 = calib[cam1].P;
+    const double* P2 = calib[cam2].P;
+    float A[16], V[16], z[4];
+    for (int c = 0; c < 4; c++) {
+        A[0 * 4 + c] = (float)((double)p1[i * 2] * P1[8 + c] - P1[c]);
+        A[1 * 4 + c] = (float)((double)p1[i * 2 + 1] * P1[8 + c] - P1[4 + c]);
+        A[2 * 4 + c] = (float)((double)p2[i * 2] * P2[8 + c] - P2[c]);
+        A[3 * 4 + c] = (float)((double)p2[i * 2 + 1] * P2[8 + c] - P2[4 + c]);
+    }
+    null_vector<float, 4, 4>(A, V, 4, 4, z, 1.1920929e-07f);
+    xyz[i * 3] = z[0] / z[3];
+    xyz[i * 3 + 1] = z[1] / z[3];
+    xyz[i * 3 + 2] = z[2] / z[3];
+}
+
+}  // namespace mcs

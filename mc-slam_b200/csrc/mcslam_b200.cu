@@ -1,0 +1,1129 @@
+// mcslam_b200.cu — host engine + C ABI (include/mcslam_b200.h) over the sm_100a kernels in extract_kernels.cuh and
+// match_kernels.cuh.  No CPU fallback: every stage is a kernel launch; creation fails without a CUDA device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/mcs_orb_pattern.inc"
+#include "../../include/mcslam_b200.h"
+#include "extract_kernels.cuh"
+#include "match_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err = "";
+void set_err(const std::string& s) { g_err = s; }
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            set_err(std::string(#call) + ": " + cudaGetErrorString(e_) + " (" + __FILE__ + ":" + std::to_string(__LINE__) + ")"); \
+            return MCS_ERR_CUDA;                                                                   \
+        }                                                                                          \
+    } while (0)
+
+inline int cv_round_f(float v) { return (int)std::nearbyintf(v); }
+inline int cv_floor_f(float v) {
+    int i = (int)v;
+    return i - (i > v);
+}
+inline short sat_short(float v) {
+    int i = cv_round_f(v);
+    return (short)std::min(std::max(i, -32768), 32767);
+}
+inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+// ORBextractor constructor tables (ORBextractor.cpp:408-468)
+struct OrbTables {
+    int nfeatures = 0, nlevels = 0, ini_th = 0, min_th = 0;
+    float scale_factor_f = 0;
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> quota;
+    int umax[16];
+    void build(int nf, float sf, int nl, int ini, int mn) {
+        nfeatures = nf; nlevels = nl; ini_th = ini; min_th = mn; scale_factor_f = sf;
+        const double scaleFactor = sf;  // the member is a double initialised from the float argument (ORBextractor.h:103)
+        scale.assign(nl, 1.f); sigma2.assign(nl, 1.f); inv_scale.assign(nl, 1.f); inv_sigma2.assign(nl, 1.f); quota.assign(nl, 0);
+        for (int i = 1; i < nl; i++) {
+            scale[i] = (float)(scale[i - 1] * scaleFactor);
+            sigma2[i] = scale[i] * scale[i];
+        }
+        for (int i = 0; i < nl; i++) {
+            inv_scale[i] = 1.0f / scale[i];
+            inv_sigma2[i] = 1.0f / sigma2[i];
+        }
+        const float factor = (float)(1.0f / scaleFactor);
+        float nDesired = nf * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+        int sum = 0;
+        for (int l = 0; l < nl - 1; l++) {
+            quota[l] = cv_round_f(nDesired);
+            sum += quota[l];
+            nDesired *= factor;
+        }
+        quota[nl - 1] = std::max(nf - sum, 0);
+        const int HP = 15;
+        int v, v0, vmax = cv_floor_f(HP * std::sqrt(2.f) / 2 + 1);
+        int vmin = (int)std::ceil(HP * std::sqrt(2.f) / 2);
+        const double hp2 = HP * HP;
+        for (v = 0; v <= vmax; ++v) umax[v] = (int)std::nearbyint(std::sqrt(hp2 - v * v));
+        for (v = HP, v0 = 0; v >= vmin; --v) {
+            while (umax[v0] == umax[v0 + 1]) ++v0;
+            umax[v] = v0;
+            ++v0;
+        }
+    }
+};
+
+// cv::resize INTER_LINEAR 8U coefficient tables for one axis (OpenCV imgproc/resize.cpp semantics)
+void build_resize_axis(int ssize, int dsize, std::vector<int2>& tab, bool is_x) {
+    const double inv_scale = (double)dsize / ssize, scl = 1. / inv_scale;
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scl - 0.5);
+        int s = cv_floor_f(f);
+        f -= s;
+        if (is_x) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= ssize - 1) { f = 0; s = ssize - 1; }
+        }
+        const short c0 = sat_short((1.f - f) * 2048.f), c1 = sat_short(f * 2048.f);
+        int2 e;
+        e.x = s;
+        e.y = (int)((uint32_t)(uint16_t)c0 | ((uint32_t)(uint16_t)c1 << 16));
+        tab.push_back(e);
+    }
+}
+
+// getGaussianKernelBitExact + getGaussianKernelFixedPoint_ED (OpenCV imgproc/smooth.dispatch.cpp), 8 fractional bits
+void gauss_kernel_fixed(int n, double sigma, int* out) {
+    const int n2 = (n - 1) / 2;
+    std::vector<double> v(n2 + 1), k(n);
+    const double scale2x = -0.125 / (sigma * sigma);
+    double sum = 0;
+    for (int i = 0, x = 1 - n; i < n2; i++, x += 2) {
+        v[i] = std::exp((double)(x * x) * scale2x);
+        sum += v[i];
+    }
+    sum = sum * 2 + 1.0;
+    const double mul1 = 1.0 / sum;
+    for (int i = 0; i < n2; i++) k[i] = k[n - 1 - i] = v[i] * mul1;
+    k[n2] = mul1;
+    double err = 0;
+    long long s = 0;
+    for (int i = 0; i < n2; i++) {
+        const double adj = k[i] * 256.0 + err;
+        const long long v0 = (long long)std::nearbyint(adj);
+        err = adj - (double)v0;
+        out[i] = out[n - 1 - i] = (int)v0;
+        s += v0;
+    }
+    out[n2] = (int)(256 - 2 * s);
+}
+
+// Builds the plan for (width x height); returns false (with g_err) when unsupported.
+bool build_plan(const OrbTables& T, int width, int height, int use_angle, McsPlan& P, std::vector<int2>& xtab, std::vector<int2>& ytab) {
+    memset(&P, 0, sizeof(P));
+    xtab.clear();
+    ytab.clear();
+    if (T.nlevels < 1 || T.nlevels > MCS_PLAN_MAX_LEVELS) { set_err("nlevels out of range [1,16]"); return false; }
+    if (width < 1 || height < 1 || width > 4096 || height > 4096) { set_err("image size out of range [1,4096]"); return false; }
+    if (T.ini_th < 1 || T.min_th < 1 || T.ini_th > 254 || T.min_th > 254) { set_err("FAST thresholds must be in [1,254]"); return false; }
+    P.nlevels = T.nlevels; P.width = width; P.height = height; P.nfeatures = T.nfeatures;
+    P.ini_th = T.ini_th; P.min_th = T.min_th; P.use_angle = use_angle;
+    for (int i = 0; i < 16; i++) P.umax[i] = T.umax[i];
+    int plane = 0, cells = 0, cand = 0, sel = 0, tiles = 0, octmax = 0;
+    for (int l = 0; l < T.nlevels; l++) {
+        McsLevel& L = P.L[l];
+        L.w = cv_round_f((float)width * T.inv_scale[l]);   // ORBextractor.cpp:1178
+        L.h = cv_round_f((float)height * T.inv_scale[l]);
+        if (L.w < 1 || L.h < 1) { set_err("pyramid level collapses to zero size"); return false; }
+        L.pitch = align_up(L.w, 64);
+        L.plane_ofs = plane;
+        plane += align_up(L.pitch * L.h, 256);
+        L.scale = T.scale[l];
+        L.quota = T.quota[l];
+        L.scaled_patch = (int)(31 * T.scale[l]);            // :879
+        L.roi_w = L.w - 2 * MCS_MIN_BORDER;                 // :787-796
+        L.roi_h = L.h - 2 * MCS_MIN_BORDER;
+        const float W = 35;
+        L.n_cols = L.roi_w > 0 ? (int)((float)L.roi_w / W) : 0;
+        L.n_rows = L.roi_h > 0 ? (int)((float)L.roi_h / W) : 0;
+        if (L.n_cols < 1 || L.n_rows < 1) {
+            // the reference divides by zero here (:801-802); a level too small for one cell yields no keypoints
+            L.n_cols = L.n_rows = 0; L.w_cell = L.h_cell = 1;
+        } else {
+            L.w_cell = (int)std::ceil((float)L.roi_w / L.n_cols);
+            L.h_cell = (int)std::ceil((float)L.roi_h / L.n_rows);
+            if (L.w_cell > 69 || L.h_cell > 69) { set_err("internal: FAST cell larger than 69 px"); return false; }
+        }
+        L.cell_base = cells;
+        cells += L.n_cols * L.n_rows;
+        L.cand_ofs = cand;
+        L.cand_cap = L.n_cols * L.n_rows * ((L.w_cell + 1) / 2) * ((L.h_cell + 1) / 2);  // strict 8-neighbour maxima per cell
+        cand += align_up(std::max(L.cand_cap, 4), 4);
+        L.n_ini = L.n_cols ? std::max(1, (int)std::round((float)L.roi_w / L.roi_h)) : 1;  // :558
+        L.hX = (float)L.roi_w / L.n_ini;
+        L.oct_cap = std::max(L.quota, 4 * L.n_ini) + 4;
+        if (L.oct_cap > 60000) { set_err("features per level too large"); return false; }
+        octmax = std::max(octmax, L.oct_cap);
+        L.sel_ofs = sel;
+        sel += L.oct_cap;
+        if (l > 0) {
+            L.xtab_ofs = (int)xtab.size();
+            build_resize_axis(P.L[l - 1].w, L.w, xtab, true);
+            L.ytab_ofs = (int)ytab.size();
+            build_resize_axis(P.L[l - 1].h, L.h, ytab, false);
+        }
+        L.tiles_x = (L.w + MCS_BLUR_TW - 1) / MCS_BLUR_TW;
+        L.tiles_y = (L.h + MCS_BLUR_TH - 1) / MCS_BLUR_TH;
+        L.tile_base = tiles;
+        tiles += L.tiles_x * L.tiles_y;
+    }
+    P.n_cells = cells; P.n_tiles = tiles; P.pyr_stride = align_up(plane, 256); P.cand_stride = cand; P.sel_stride = sel;
+    P.kp_cap = align_up(sel, 8);
+    P.oct_cap_max = octmax;
+    if (xtab.empty()) { xtab.push_back(make_int2(0, 0)); ytab.push_back(make_int2(0, 0)); }
+    return true;
+}
+
+}  // namespace
+
+// =================================================================================================================
+// Engine: device workspace + launch sequence of ORBextractor::operator() for a batch of same-sized images.
+// =================================================================================================================
+namespace {
+
+enum Stage { ST_UPLOAD = 0, ST_PYRAMID, ST_FAST, ST_OCTREE, ST_BLUR, ST_DESCRIBE, ST_MATCH, ST_MERGE, ST_TRIANG, ST_DOWNLOAD, ST_COUNT };
+
+struct Engine {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    OrbTables T;
+    McsPlan plan;
+    int max_images = 0, planned_w = 0, planned_h = 0, alloc_w = 0, alloc_h = 0;
+    int use_angle = 0;
+    long long launches = 0;
+    // device buffers
+    uint8_t *d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
+    int2 *d_xtab = nullptr, *d_ytab = nullptr;
+    uint32_t *d_cand = nullptr, *d_sel = nullptr;
+    uint16_t* d_knode = nullptr;
+    int *d_cand_count = nullptr, *d_sel_count = nullptr, *d_kp_count = nullptr, *d_mono = nullptr;
+    mcs::KeypointPod *d_kps = nullptr, *d_kps_tmp = nullptr;
+    uint8_t *d_desc = nullptr, *d_desc_tmp = nullptr;
+    // pinned host mirrors
+    mcs::KeypointPod* h_kps = nullptr;
+    uint8_t* h_desc = nullptr;
+    int *h_kp_count = nullptr, *h_mono = nullptr, *h_sel_count = nullptr, *h_cand_count = nullptr;
+    size_t in_bytes = 0;
+    mcs::ImageSet last_set{};
+    int last_n = 0;
+    bool profiling = false;
+    cudaEvent_t ev[ST_COUNT + 1] = {};
+    bool ev_rec[ST_COUNT + 1] = {};
+    float stage_ms[ST_COUNT] = {};
+    size_t oct_smem = 0;
+
+    ~Engine() { release(); }
+
+    void free_all() {
+        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cand); cudaFree(d_sel);
+        cudaFree(d_knode); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
+        cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp);
+        cudaFreeHost(h_kps); cudaFreeHost(h_desc); cudaFreeHost(h_kp_count); cudaFreeHost(h_mono); cudaFreeHost(h_sel_count);
+        cudaFreeHost(h_cand_count);
+        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
+        d_cand_count = d_sel_count = d_kp_count = d_mono = nullptr; d_kps = d_kps_tmp = nullptr; d_desc = d_desc_tmp = nullptr;
+        h_kps = nullptr; h_desc = nullptr; h_kp_count = h_mono = h_sel_count = h_cand_count = nullptr;
+    }
+    void release() {
+        if (!stream) return;
+        cudaSetDevice(device);
+        cudaStreamSynchronize(stream);
+        free_all();
+        for (auto& e : ev) if (e) cudaEventDestroy(e);
+        cudaStreamDestroy(stream);
+        stream = nullptr;
+    }
+
+    int init(int nf, float sf, int nl, int ini, int mn, int dev, int max_w, int max_h, int max_img) {
+        if (nf < 1 || nl < 1 || nl > MCS_PLAN_MAX_LEVELS || !(sf > 1.0f) || max_img < 1) { set_err("invalid extractor parameters"); return MCS_ERR_ARG; }
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { set_err("no CUDA device: this library has no CPU path"); return MCS_ERR_CUDA; }
+        if (dev < 0 || dev >= ndev) { set_err("device ordinal out of range"); return MCS_ERR_ARG; }
+        device = dev;
+        CK(cudaSetDevice(device));
+        T.build(nf, sf, nl, ini, mn);
+        max_images = max_img;
+        CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        for (auto& e : ev) CK(cudaEventCreate(&e));
+        int k7[7];
+        gauss_kernel_fixed(7, 2.0, k7);
+        CK(cudaMemcpyToSymbol(mcs::c_gauss7, k7, sizeof(k7)));
+        CK(cudaMemcpyToSymbol(mcs::c_pattern, MCS_ORB_PATTERN_XY, 1024));
+        return replan(max_w, max_h);
+    }
+
+    // (re)build the plan for an image size; reallocates when the size grows
+    int replan(int w, int h) {
+        if (w == planned_w && h == planned_h && plan.use_angle == use_angle) return 0;
+        std::vector<int2> xt, yt;
+        McsPlan np;
+        if (!build_plan(T, w, h, use_angle, np, xt, yt)) return MCS_ERR_ARG;
+        CK(cudaSetDevice(device));
+        const bool grow = (size_t)w * h > (size_t)alloc_w * alloc_h || np.pyr_stride > plan.pyr_stride || np.cand_stride > plan.cand_stride ||
+                          np.sel_stride > plan.sel_stride || np.kp_cap > plan.kp_cap || !d_pyr;
+        if (grow) {
+            CK(cudaStreamSynchronize(stream));
+            free_all();
+            const size_t n = max_images;
+            in_bytes = (size_t)w * h;
+            CK(cudaMalloc(&d_input, n * in_bytes + 256));
+            CK(cudaMalloc(&d_pyr, n * np.pyr_stride + 256));
+            CK(cudaMalloc(&d_blur, n * np.pyr_stride + 256));
+            CK(cudaMalloc(&d_cand, n * np.cand_stride * sizeof(uint32_t)));
+            CK(cudaMalloc(&d_knode, n * np.cand_stride * sizeof(uint16_t)));
+            CK(cudaMalloc(&d_sel, n * np.sel_stride * sizeof(uint32_t)));
+            CK(cudaMalloc(&d_cand_count, n * MCS_PLAN_MAX_LEVELS * sizeof(int)));
+            CK(cudaMalloc(&d_sel_count, n * MCS_PLAN_MAX_LEVELS * sizeof(int)));
+            CK(cudaMalloc(&d_kp_count, n * sizeof(int)));
+            CK(cudaMalloc(&d_mono, n * sizeof(int)));
+            CK(cudaMalloc(&d_kps, n * np.kp_cap * sizeof(mcs::KeypointPod)));
+            CK(cudaMalloc(&d_kps_tmp, n * np.kp_cap * sizeof(mcs::KeypointPod)));
+            CK(cudaMalloc(&d_desc, n * np.kp_cap * 32));
+            CK(cudaMalloc(&d_desc_tmp, n * np.kp_cap * 32));
+            CK(cudaMallocHost(&h_kps, n * np.kp_cap * sizeof(mcs::KeypointPod)));
+            CK(cudaMallocHost(&h_desc, n * np.kp_cap * 32));
+            CK(cudaMallocHost(&h_kp_count, n * sizeof(int)));
+            CK(cudaMallocHost(&h_mono, n * sizeof(int)));
+            CK(cudaMallocHost(&h_sel_count, n * MCS_PLAN_MAX_LEVELS * sizeof(int)));
+            CK(cudaMallocHost(&h_cand_count, n * MCS_PLAN_MAX_LEVELS * sizeof(int)));
+            CK(cudaMemset(d_kp_count, 0, n * sizeof(int)));
+            alloc_w = w; alloc_h = h;
+        } else {
+            CK(cudaStreamSynchronize(stream));
+        }
+        cudaFree(d_xtab); cudaFree(d_ytab);
+        d_xtab = d_ytab = nullptr;
+        CK(cudaMalloc(&d_xtab, xt.size() * sizeof(int2)));
+        CK(cudaMalloc(&d_ytab, yt.size() * sizeof(int2)));
+        CK(cudaMemcpy(d_xtab, xt.data(), xt.size() * sizeof(int2), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_ytab, yt.data(), yt.size() * sizeof(int2), cudaMemcpyHostToDevice));
+        plan = np;
+        planned_w = w; planned_h = h;
+        oct_smem = mcs_oct::Shared::bytes(plan.oct_cap_max);
+        if (oct_smem > 200 * 1024) { set_err("features per level exceed the octree kernel's shared-memory table"); return MCS_ERR_ARG; }
+        CK(cudaFuncSetAttribute(mcs::octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
+        last_n = 0;
+        return 0;
+    }
+
+    void mark(int st) {
+        if (profiling) { cudaEventRecord(ev[st], stream); ev_rec[st] = true; }
+    }
+    void begin_profile() { for (auto& r : ev_rec) r = false; for (auto& m : stage_ms) m = 0; }
+    // elapsed between consecutive recorded marks -> stage_ms[stage that started at the earlier mark]
+    void collect_profile() {
+        if (!profiling) return;
+        int prev = -1;
+        for (int s = 0; s <= ST_COUNT; s++) {
+            if (!ev_rec[s]) continue;
+            if (prev >= 0) { float ms = 0; cudaEventElapsedTime(&ms, ev[prev], ev[s]); stage_ms[prev] = ms; }
+            prev = s;
+        }
+    }
+
+    // Stage A on images already described by `set`.  Leaves keypoints/descriptors/counts on the device.
+    int run(const mcs::ImageSet& set, int n, const int lap[2]) {
+        if (n < 1 || n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+        last_set = set; last_n = n;
+        const McsPlan& P = plan;
+        mark(ST_PYRAMID);
+        CK(cudaMemsetAsync(d_cand_count, 0, (size_t)n * P.nlevels * sizeof(int), stream));
+        for (int l = 1; l < P.nlevels; l++) {
+            dim3 b(32, 8), g((P.L[l].w + 127) / 128, (P.L[l].h + 7) / 8, n);
+            mcs::resize_level_kernel<<<g, b, 0, stream>>>(P, set, l, d_xtab, d_ytab);
+            launches++;
+        }
+        mark(ST_FAST);
+        if (P.n_cells > 0) {
+            mcs::fast_cells_kernel<<<dim3(P.n_cells, n), MCS_FAST_NT, 0, stream>>>(P, set, d_cand, d_cand_count);
+            launches++;
+        }
+        mark(ST_OCTREE);
+        mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, stream>>>(P, d_cand, d_cand_count, d_knode, d_sel, d_sel_count);
+        launches++;
+        mark(ST_BLUR);
+        mcs::blur_kernel<<<dim3(P.n_tiles, n), 256, 0, stream>>>(P, set, d_blur);
+        launches++;
+        mark(ST_DESCRIBE);
+        mcs::describe_kernel<<<dim3((P.kp_cap + MCS_DESC_WARPS - 1) / MCS_DESC_WARPS, n), MCS_DESC_WARPS * 32, 0, stream>>>(
+            P, set, d_blur, d_sel, d_sel_count, d_kps, d_desc, d_kp_count);
+        launches++;
+        // every keypoint has pt.x >= 19, so a lapping area ending before 19 (the callers' {0,0}) selects nothing (:1153)
+        const bool lap_active = lap && lap[1] >= lap[0] && lap[1] >= MCS_EDGE_THRESHOLD;
+        if (lap_active) {
+            mcs::lapping_permute_kernel<<<n, 256, 0, stream>>>(P, lap[0], lap[1], d_kps, d_desc, d_kps_tmp, d_desc_tmp, d_kp_count, d_mono);
+            launches++;
+        } else {
+            CK(cudaMemcpyAsync(d_mono, d_kp_count, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, stream));
+        }
+        mark(ST_MATCH);
+        CK(cudaGetLastError());
+        return 0;
+    }
+
+    // host images -> d_input (tight) -> ImageSet
+    int upload(const uint8_t* images, int n, int w, int h, int stride, size_t image_stride, mcs::ImageSet& set) {
+        if (n < 1 || n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+        mark(ST_UPLOAD);
+        if (stride == w && image_stride == (size_t)w * h) {
+            CK(cudaMemcpyAsync(d_input, images, (size_t)n * w * h, cudaMemcpyHostToDevice, stream));
+        } else {
+            for (int i = 0; i < n; i++)
+                CK(cudaMemcpy2DAsync(d_input + (size_t)i * w * h, w, images + i * image_stride, stride, w, h, cudaMemcpyHostToDevice, stream));
+        }
+        return make_set(d_input, n, w, h, set);
+    }
+    // device-resident tight images; re-pitched only when 32-bit row loads would be misaligned
+    int make_set(const uint8_t* d_images, int n, int w, int h, mcs::ImageSet& set) {
+        set.pyr = d_pyr;
+        if ((w & 3) == 0 && ((uintptr_t)d_images & 15) == 0) {
+            set.l0 = d_images; set.l0_pitch = w; set.l0_stride = (size_t)w * h;
+        } else {
+            for (int i = 0; i < n; i++)
+                CK(cudaMemcpy2DAsync(d_pyr + (size_t)i * plan.pyr_stride + plan.L[0].plane_ofs, plan.L[0].pitch, d_images + (size_t)i * w * h, w, w,
+                                     h, cudaMemcpyDeviceToDevice, stream));
+            set.l0 = d_pyr + plan.L[0].plane_ofs; set.l0_pitch = plan.L[0].pitch; set.l0_stride = plan.pyr_stride;
+        }
+        return 0;
+    }
+
+    int download_features(int n) {
+        mark(ST_DOWNLOAD);
+        CK(cudaMemcpyAsync(h_kp_count, d_kp_count, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(h_mono, d_mono, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(h_sel_count, d_sel_count, (size_t)n * plan.nlevels * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(h_cand_count, d_cand_count, (size_t)n * plan.nlevels * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(h_kps, d_kps, (size_t)n * plan.kp_cap * sizeof(mcs::KeypointPod), cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(h_desc, d_desc, (size_t)n * plan.kp_cap * 32, cudaMemcpyDeviceToHost, stream));
+        mark(ST_COUNT);
+        CK(cudaStreamSynchronize(stream));
+        collect_profile();
+        return check_counts(n);
+    }
+    int check_counts(int n) {
+        for (int i = 0; i < n; i++)
+            for (int l = 0; l < plan.nlevels; l++) {
+                if (h_sel_count[i * plan.nlevels + l] < 0) { set_err("octree node table overflow"); return MCS_ERR_CAPACITY; }
+                if (h_cand_count[i * plan.nlevels + l] > plan.L[l].cand_cap) { set_err("FAST candidate list overflow"); return MCS_ERR_CAPACITY; }
+            }
+        return 0;
+    }
+};
+
+}  // namespace
+
+// =================================================================================================================
+// C ABI — ORBextractor
+// =================================================================================================================
+struct mcs_extractor {
+    Engine eng;
+};
+
+extern "C" {
+
+const char* mcs_last_error(void) { return g_err.c_str(); }
+const char* mcs_version(void) { return "mcslam_b200 0.1 (sm_100a)"; }
+int mcs_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+mcs_extractor* mcs_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast, int device,
+                                    int max_width, int max_height, int max_images) {
+    mcs_extractor* ex = new mcs_extractor();
+    if (ex->eng.init(nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast, device, max_width, max_height, max_images) != 0) {
+        delete ex;
+        return nullptr;
+    }
+    return ex;
+}
+void mcs_extractor_destroy(mcs_extractor* ex) { delete ex; }
+
+int mcs_extractor_set_orientation(mcs_extractor* ex, int enable) {
+    if (!ex) return MCS_ERR_ARG;
+    ex->eng.use_angle = enable ? 1 : 0;
+    return ex->eng.replan(ex->eng.planned_w, ex->eng.planned_h);
+}
+int mcs_extractor_capacity(const mcs_extractor* ex) { return ex ? ex->eng.plan.kp_cap : MCS_ERR_ARG; }
+
+int mcs_extract_batch(mcs_extractor* ex, const uint8_t* images, int n_images, int width, int height, int stride, size_t image_stride,
+                      const int lapping[2], mcs_keypoint* keypoints, uint8_t* descriptors, int capacity, int* mono_index, int* n_total) {
+    if (!ex) return MCS_ERR_ARG;
+    if (!images || width <= 0 || height <= 0 || n_images <= 0) return MCS_ERR_EMPTY;  // `if(_image.empty()) return -1` (:1090)
+    Engine& E = ex->eng;
+    if (cudaSetDevice(E.device) != cudaSuccess) return MCS_ERR_CUDA;
+    int rc = E.replan(width, height);
+    if (rc) return rc;
+    E.begin_profile();
+    mcs::ImageSet set;
+    if ((rc = E.upload(images, n_images, width, height, stride, image_stride, set))) return rc;
+    if ((rc = E.run(set, n_images, lapping))) return rc;
+    if ((rc = E.download_features(n_images))) return rc;
+    const int cap = E.plan.kp_cap;
+    for (int i = 0; i < n_images; i++) {
+        const int n = E.h_kp_count[i];
+        if (n > capacity) { set_err("keypoint capacity too small"); return MCS_ERR_CAPACITY; }
+        if (keypoints) memcpy(keypoints + (size_t)i * capacity, E.h_kps + (size_t)i * cap, (size_t)n * sizeof(mcs_keypoint));
+        if (descriptors) memcpy(descriptors + (size_t)i * capacity * 32, E.h_desc + (size_t)i * cap * 32, (size_t)n * 32);
+        if (mono_index) mono_index[i] = E.h_mono[i];
+        if (n_total) n_total[i] = n;
+    }
+    return 0;
+}
+
+int mcs_extract(mcs_extractor* ex, const uint8_t* image, int width, int height, int stride, const uint8_t* mask_ignored,
+                const int lapping[2], mcs_keypoint* keypoints, uint8_t* descriptors, int capacity, int* n_total) {
+    (void)mask_ignored;  // "Mask is ignored in the current implementation." (ORBextractor.h:56)
+    int mono = 0, total = 0;
+    const int rc = mcs_extract_batch(ex, image, 1, width, height, stride, (size_t)stride * (height > 0 ? height : 0), lapping, keypoints,
+                                     descriptors, capacity, &mono, &total);
+    if (rc) return rc;
+    if (n_total) *n_total = total;
+    return mono;
+}
+
+int mcs_extractor_get_tables(const mcs_extractor* ex, int* nlevels, float* scale_factors, float* inv_scale_factors, float* level_sigma2,
+                             float* inv_level_sigma2, int* features_per_level) {
+    if (!ex) return MCS_ERR_ARG;
+    const OrbTables& T = ex->eng.T;
+    if (nlevels) *nlevels = T.nlevels;
+    for (int i = 0; i < T.nlevels; i++) {
+        if (scale_factors) scale_factors[i] = T.scale[i];
+        if (inv_scale_factors) inv_scale_factors[i] = T.inv_scale[i];
+        if (level_sigma2) level_sigma2[i] = T.sigma2[i];
+        if (inv_level_sigma2) inv_level_sigma2[i] = T.inv_sigma2[i];
+        if (features_per_level) features_per_level[i] = T.quota[i];
+    }
+    return 0;
+}
+
+int mcs_extractor_level_size(const mcs_extractor* ex, int level, int* width, int* height) {
+    if (!ex || level < 0 || level >= ex->eng.plan.nlevels) return MCS_ERR_ARG;
+    if (width) *width = ex->eng.plan.L[level].w;
+    if (height) *height = ex->eng.plan.L[level].h;
+    return 0;
+}
+
+static int engine_download_level(Engine& E, int image_index, int level, int kind, uint8_t* dst, int dst_stride) {
+    if (image_index < 0 || image_index >= E.last_n || level < 0 || level >= E.plan.nlevels || !dst) return MCS_ERR_ARG;
+    if (cudaSetDevice(E.device) != cudaSuccess) return MCS_ERR_CUDA;
+    const McsLevel& L = E.plan.L[level];
+    const uint8_t* src;
+    int pitch;
+    if (kind == 2) {
+        src = E.d_blur + (size_t)image_index * E.plan.pyr_stride + L.plane_ofs;
+        pitch = L.pitch;
+    } else if (level == 0) {
+        src = E.last_set.l0 + (size_t)image_index * E.last_set.l0_stride;
+        pitch = E.last_set.l0_pitch;
+    } else {
+        src = E.d_pyr + (size_t)image_index * E.plan.pyr_stride + L.plane_ofs;
+        pitch = L.pitch;
+    }
+    if (kind == 1) {
+        // mvImagePyramid's 19 px REFLECT_101 frame (ORBextractor.cpp:1188/:1193) is never read on the device path; it is
+        // re-created here for observers only.
+        std::vector<uint8_t> tmp((size_t)L.w * L.h);
+        CK(cudaMemcpy2D(tmp.data(), L.w, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+        const int B = MCS_EDGE_THRESHOLD;
+        auto refl = [](int p, int len) { if (len == 1) return 0; while (p < 0 || p >= len) p = p < 0 ? -p : 2 * len - 2 - p; return p; };
+        for (int y = 0; y < L.h + 2 * B; y++)
+            for (int x = 0; x < L.w + 2 * B; x++) dst[(size_t)y * dst_stride + x] = tmp[(size_t)refl(y - B, L.h) * L.w + refl(x - B, L.w)];
+        return 0;
+    }
+    CK(cudaMemcpy2D(dst, dst_stride, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+    return 0;
+}
+int mcs_extractor_download_level(mcs_extractor* ex, int image_index, int level, int kind, uint8_t* dst, int dst_stride) {
+    if (!ex) return MCS_ERR_ARG;
+    return engine_download_level(ex->eng, image_index, level, kind, dst, dst_stride);
+}
+
+static int engine_download_candidates(Engine& E, int image_index, int level, int32_t* xys, int capacity) {
+    if (image_index < 0 || image_index >= E.last_n || level < 0 || level >= E.plan.nlevels) return MCS_ERR_ARG;
+    if (cudaSetDevice(E.device) != cudaSuccess) return MCS_ERR_CUDA;
+    int n = 0;
+    CK(cudaMemcpy(&n, E.d_cand_count + image_index * E.plan.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+    n = std::min(n, E.plan.L[level].cand_cap);
+    if (n > capacity) { set_err("candidate capacity too small"); return MCS_ERR_CAPACITY; }
+    std::vector<uint32_t> rec(std::max(n, 1));
+    CK(cudaMemcpy(rec.data(), E.d_cand + (size_t)image_index * E.plan.cand_stride + E.plan.L[level].cand_ofs, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; i++) {
+        xys[i * 3] = mcs_oct::cand_x(rec[i]);
+        xys[i * 3 + 1] = mcs_oct::cand_y(rec[i]);
+        xys[i * 3 + 2] = mcs_oct::cand_score(rec[i]);
+    }
+    return n;
+}
+int mcs_extractor_download_candidates(mcs_extractor* ex, int image_index, int level, int32_t* xys, int capacity) {
+    if (!ex) return MCS_ERR_ARG;
+    return engine_download_candidates(ex->eng, image_index, level, xys, capacity);
+}
+
+void* mcs_device_malloc(int device, size_t bytes) {
+    void* p = nullptr;
+    if (cudaSetDevice(device) != cudaSuccess || cudaMalloc(&p, bytes) != cudaSuccess) { set_err("cudaMalloc failed"); return nullptr; }
+    return p;
+}
+void mcs_device_free(int device, void* p) { if (cudaSetDevice(device) == cudaSuccess) cudaFree(p); }
+int mcs_device_upload(int device, void* dst, const void* src, size_t bytes) {
+    CK(cudaSetDevice(device));
+    CK(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+int mcs_device_download(int device, void* dst, const void* src, size_t bytes) {
+    CK(cudaSetDevice(device));
+    CK(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+void* mcs_host_alloc_pinned(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) { set_err("cudaMallocHost failed"); return nullptr; }
+    return p;
+}
+void mcs_host_free_pinned(void* p) { cudaFreeHost(p); }
+
+}  // extern "C"
+
+// =================================================================================================================
+// C ABI — rig frames (MultiCameraFrame extract / intra-match / triangulate)
+// =================================================================================================================
+namespace {
+
+void mat3_mul(const double* A, const double* B, double* C) {
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            double s = 0;
+            for (int k = 0; k < 3; k++) s += A[i * 3 + k] * B[k * 3 + j];
+            C[i * 3 + j] = s;
+        }
+}
+bool mat3_inv(const double* m, double* o) {
+    const double det = m[0] * (m[4] * m[8] - m[5] * m[7]) - m[1] * (m[3] * m[8] - m[5] * m[6]) + m[2] * (m[3] * m[7] - m[4] * m[6]);
+    if (det == 0) return false;
+    const double id = 1.0 / det;
+    o[0] = (m[4] * m[8] - m[5] * m[7]) * id; o[1] = (m[2] * m[7] - m[1] * m[8]) * id; o[2] = (m[1] * m[5] - m[2] * m[4]) * id;
+    o[3] = (m[5] * m[6] - m[3] * m[8]) * id; o[4] = (m[0] * m[8] - m[2] * m[6]) * id; o[5] = (m[2] * m[3] - m[0] * m[5]) * id;
+    o[6] = (m[3] * m[7] - m[4] * m[6]) * id; o[7] = (m[1] * m[6] - m[0] * m[7]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
+    return true;
+}
+// F = K_j^-T [t_ji]x R_ji K_i^-1, T_ji = T_j0 * T_i0^-1 (MultiCameraFrame.cpp:1126-1141); rigid inverse through R^T.
+void fundamental_from_extrinsics(const mcs_calib& ci, const mcs_calib& cj, double* F) {
+    double RiT[9], Rji[9], tji[3];
+    for (int a = 0; a < 3; a++)
+        for (int b = 0; b < 3; b++) RiT[a * 3 + b] = ci.R[b * 3 + a];
+    mat3_mul(cj.R, RiT, Rji);
+    for (int a = 0; a < 3; a++) {
+        double s = 0;
+        for (int b = 0; b < 3; b++) s += Rji[a * 3 + b] * ci.t[b];
+        tji[a] = cj.t[a] - s;
+    }
+    const double tx[9] = {0, -tji[2], tji[1], tji[2], 0, -tji[0], -tji[1], tji[0], 0};
+    double KjInv[9], KiInv[9], KjInvT[9], A[9], B[9];
+    mat3_inv(cj.K, KjInv);
+    mat3_inv(ci.K, KiInv);
+    for (int a = 0; a < 3; a++)
+        for (int b = 0; b < 3; b++) KjInvT[a * 3 + b] = KjInv[b * 3 + a];
+    mat3_mul(KjInvT, tx, A);
+    mat3_mul(A, Rji, B);
+    mat3_mul(B, KiInv, F);
+}
+
+}  // namespace
+
+struct mcs_rig {
+    Engine eng;
+    mcs_rig_config cfg{};
+    std::vector<mcs_calib> calib;
+    int C = 0, F = 0, kp_cap = 0, row_cap = 0;
+    mcs::PairList pairs{};
+    mcs::CalibDev* d_calib = nullptr;
+    double* d_F = nullptr;
+    float* d_sigma2 = nullptr;
+    int *d_match_train = nullptr, *d_match_tmp = nullptr, *d_rows = nullptr, *d_row_count = nullptr;
+    mcs::LandmarkOut lm{};
+    float* d_masks = nullptr;
+    size_t masks_bytes = 0;
+    // pinned host mirrors
+    int *h_rows = nullptr, *h_row_count = nullptr, *h_lm_rows = nullptr, *h_n_views = nullptr, *h_rep = nullptr, *h_n_acc = nullptr,
+        *h_match_tmp = nullptr;
+    uint8_t* h_accepted = nullptr;
+    double* h_xyz = nullptr;
+    float* h_uv = nullptr;
+    int n_extracted = 0, n_matched = 0, n_triangulated = 0;
+    bool feat_host = false, rows_host = false, lm_host = false;
+    size_t merge_smem = 0;
+
+    ~mcs_rig() {
+        if (!eng.stream) return;
+        cudaSetDevice(eng.device);
+        cudaStreamSynchronize(eng.stream);
+        cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
+        cudaFree(d_row_count); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
+        cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks);
+        cudaFreeHost(h_rows); cudaFreeHost(h_row_count); cudaFreeHost(h_lm_rows); cudaFreeHost(h_n_views); cudaFreeHost(h_rep);
+        cudaFreeHost(h_n_acc); cudaFreeHost(h_match_tmp); cudaFreeHost(h_accepted); cudaFreeHost(h_xyz); cudaFreeHost(h_uv);
+    }
+
+    int init(const mcs_rig_config* c, const mcs_calib* cal) {
+        cfg = *c;
+        C = c->num_cams; F = c->max_frames;
+        if (C < 1 || C > MCS_MAX_CAMS || F < 1) { set_err("num_cams must be in [1,8], max_frames >= 1"); return MCS_ERR_ARG; }
+        int rc = eng.init(c->nfeatures, c->scale_factor, c->nlevels, c->ini_th_fast, c->min_th_fast, c->device, c->width, c->height, C * F);
+        if (rc) return rc;
+        kp_cap = eng.plan.kp_cap;
+        row_cap = (C * kp_cap + 1) / 2;  // every new IntraMatch row consumes two unmatched features
+        if (row_cap >= 65535) { set_err("too many features per frame for the merge table"); return MCS_ERR_ARG; }
+        calib.assign(cal, cal + C);
+        pairs.n_pairs = 0;
+        for (int i = 0; i < C - 1; i++)
+            for (int j = i + 1; j < C; j++) {
+                pairs.a[pairs.n_pairs] = (unsigned char)i;
+                pairs.b[pairs.n_pairs] = (unsigned char)j;
+                pairs.n_pairs++;
+            }
+        const int NP = std::max(pairs.n_pairs, 1);
+        std::vector<mcs::CalibDev> cd(C);
+        for (int k = 0; k < C; k++) {
+            memcpy(cd[k].K, cal[k].K, sizeof(double) * 9);
+            for (int i = 0; i < 3; i++) {  // build_Rt (common_utils/src/tools.cpp:136-148)
+                for (int j = 0; j < 3; j++) cd[k].Rt[i * 4 + j] = cal[k].R[i * 3 + j];
+                cd[k].Rt[i * 4 + 3] = cal[k].t[i];
+            }
+            for (int r = 0; r < 3; r++)
+                for (int cc = 0; cc < 4; cc++) {
+                    double s = 0;
+                    for (int q = 0; q < 3; q++) s += cal[k].K[r * 3 + q] * cd[k].Rt[q * 4 + cc];
+                    cd[k].P[r * 4 + cc] = s;
+                }
+        }
+        std::vector<double> Fm((size_t)NP * 9, 0.0);
+        for (int p = 0; p < pairs.n_pairs; p++) fundamental_from_extrinsics(cal[pairs.a[p]], cal[pairs.b[p]], &Fm[(size_t)p * 9]);
+        CK(cudaMalloc(&d_calib, sizeof(mcs::CalibDev) * C));
+        CK(cudaMemcpy(d_calib, cd.data(), sizeof(mcs::CalibDev) * C, cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&d_F, Fm.size() * sizeof(double)));
+        CK(cudaMemcpy(d_F, Fm.data(), Fm.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&d_sigma2, sizeof(float) * eng.T.nlevels));
+        CK(cudaMemcpy(d_sigma2, eng.T.sigma2.data(), sizeof(float) * eng.T.nlevels, cudaMemcpyHostToDevice));
+        const size_t mt = (size_t)F * NP * kp_cap, rw = (size_t)F * row_cap;
+        CK(cudaMalloc(&d_match_train, mt * sizeof(int)));
+        CK(cudaMalloc(&d_match_tmp, (size_t)kp_cap * 3 * sizeof(int)));
+        CK(cudaMalloc(&d_rows, rw * C * sizeof(int)));
+        CK(cudaMalloc(&d_row_count, F * sizeof(int)));
+        CK(cudaMalloc(&lm.rows, rw * C * sizeof(int)));
+        CK(cudaMalloc(&lm.accepted, rw));
+        CK(cudaMalloc(&lm.n_views, rw * sizeof(int)));
+        CK(cudaMalloc(&lm.xyz, rw * 3 * sizeof(double)));
+        CK(cudaMalloc(&lm.uv_ref, rw * 2 * sizeof(float)));
+        CK(cudaMalloc(&lm.rep_cam, rw * sizeof(int)));
+        CK(cudaMalloc(&lm.n_accepted, F * sizeof(int)));
+        CK(cudaMallocHost(&h_rows, rw * C * sizeof(int)));
+        CK(cudaMallocHost(&h_row_count, F * sizeof(int)));
+        CK(cudaMallocHost(&h_lm_rows, rw * C * sizeof(int)));
+        CK(cudaMallocHost(&h_n_views, rw * sizeof(int)));
+        CK(cudaMallocHost(&h_rep, rw * sizeof(int)));
+        CK(cudaMallocHost(&h_n_acc, F * sizeof(int)));
+        CK(cudaMallocHost(&h_match_tmp, (size_t)kp_cap * 3 * sizeof(int)));
+        CK(cudaMallocHost(&h_accepted, rw));
+        CK(cudaMallocHost(&h_xyz, rw * 3 * sizeof(double)));
+        CK(cudaMallocHost(&h_uv, rw * 2 * sizeof(float)));
+        merge_smem = (size_t)C * kp_cap * sizeof(uint16_t);
+        if (merge_smem > 200 * 1024) { set_err("too many features per frame for the merge kernel's shared table"); return MCS_ERR_ARG; }
+        CK(cudaFuncSetAttribute(mcs::merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(merge_smem, 1024)));
+        return 0;
+    }
+
+    void invalidate() { feat_host = rows_host = lm_host = false; }
+
+    int stage_extract(const mcs::ImageSet& set, int n_frames) {
+        static const int lap[2] = {0, 0};  // vLapping = {0,0} (MultiCameraFrame.cpp:235, :274)
+        int rc = eng.run(set, n_frames * C, lap);
+        if (rc) return rc;
+        n_extracted = n_frames; n_matched = n_triangulated = 0;
+        invalidate();
+        return 0;
+    }
+    int stage_match(int n_frames, int old, float dist_thresh, float ratio) {
+        if (n_frames < 1 || n_frames > n_extracted) { set_err("intra-match before extract"); return MCS_ERR_STATE; }
+        eng.mark(ST_MATCH);
+        if (pairs.n_pairs > 0) {
+            dim3 g((kp_cap + MCS_MATCH_NT - 1) / MCS_MATCH_NT, pairs.n_pairs, n_frames);
+            mcs::hamming_match_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, eng.stream>>>(C, kp_cap, pairs, 0, eng.d_desc, eng.d_kp_count,
+                                                                                             dist_thresh, ratio, d_match_train, nullptr, nullptr);
+            eng.launches++;
+        }
+        eng.mark(ST_MERGE);
+        mcs::merge_kernel<<<n_frames, 128, merge_smem, eng.stream>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count, d_match_train, eng.d_kps, old,
+                                                                     d_F, d_sigma2, d_rows, d_row_count);
+        eng.launches++;
+        eng.mark(ST_TRIANG);
+        CK(cudaGetLastError());
+        n_matched = n_frames; n_triangulated = 0;
+        rows_host = lm_host = false;
+        return 0;
+    }
+    int stage_triangulate(int n_frames, const float* d_mask_ptr) {
+        if (n_frames < 1 || n_frames > n_matched) { set_err("triangulate before intra-match"); return MCS_ERR_STATE; }
+        eng.mark(ST_TRIANG);
+        CK(cudaMemsetAsync(lm.n_accepted, 0, n_frames * sizeof(int), eng.stream));
+        dim3 g((row_cap + 63) / 64, n_frames);
+        mcs::triangulate_kernel<MCS_MAX_CAMS><<<g, 64, 0, eng.stream>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_calib, d_rows, d_row_count,
+                                                                        eng.d_kps, eng.d_desc, d_mask_ptr, lm);
+        eng.launches++;
+        eng.mark(ST_DOWNLOAD);
+        CK(cudaGetLastError());
+        n_triangulated = n_frames;
+        lm_host = false;
+        return 0;
+    }
+    int upload_masks(const float* masks, int n_frames, const float** out) {
+        *out = nullptr;
+        if (!masks) return 0;
+        const size_t need = (size_t)n_frames * C * cfg.width * cfg.height * sizeof(float);
+        if (need > masks_bytes) {
+            CK(cudaStreamSynchronize(eng.stream));
+            cudaFree(d_masks);
+            d_masks = nullptr;
+            CK(cudaMalloc(&d_masks, (size_t)F * C * cfg.width * cfg.height * sizeof(float)));
+            masks_bytes = (size_t)F * C * cfg.width * cfg.height * sizeof(float);
+        }
+        CK(cudaMemcpyAsync(d_masks, masks, need, cudaMemcpyHostToDevice, eng.stream));
+        *out = d_masks;
+        return 0;
+    }
+    int ensure_features() {
+        if (feat_host) return 0;
+        if (n_extracted < 1) { set_err("no extracted frames"); return MCS_ERR_STATE; }
+        int rc = eng.download_features(n_extracted * C);
+        if (rc) return rc;
+        feat_host = true;
+        return 0;
+    }
+    int ensure_rows() {
+        if (rows_host) return 0;
+        if (n_matched < 1) { set_err("no intra-matches computed"); return MCS_ERR_STATE; }
+        CK(cudaMemcpyAsync(h_row_count, d_row_count, n_matched * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+        CK(cudaMemcpyAsync(h_rows, d_rows, (size_t)n_matched * row_cap * C * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+        CK(cudaStreamSynchronize(eng.stream));
+        for (int f = 0; f < n_matched; f++)
+            if (h_row_count[f] > row_cap) { set_err("IntraMatch row table overflow"); return MCS_ERR_CAPACITY; }
+        rows_host = true;
+        return 0;
+    }
+    int ensure_landmarks() {
+        if (lm_host) return 0;
+        if (n_triangulated < 1) { set_err("no triangulation computed"); return MCS_ERR_STATE; }
+        const size_t rw = (size_t)n_triangulated * row_cap;
+        cudaStream_t s = eng.stream;
+        CK(cudaMemcpyAsync(h_row_count, d_row_count, n_triangulated * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_n_acc, lm.n_accepted, n_triangulated * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_lm_rows, lm.rows, rw * C * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_accepted, lm.accepted, rw, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_n_views, lm.n_views, rw * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_xyz, lm.xyz, rw * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_uv, lm.uv_ref, rw * 2 * sizeof(float), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(h_rep, lm.rep_cam, rw * sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        lm_host = true;
+        return 0;
+    }
+};
+
+extern "C" {
+
+mcs_rig* mcs_rig_create(const mcs_rig_config* cfg, const mcs_calib* calib) {
+    if (!cfg || !calib) { set_err("null config/calib"); return nullptr; }
+    mcs_rig* r = new mcs_rig();
+    if (r->init(cfg, calib) != 0) {
+        delete r;
+        return nullptr;
+    }
+    return r;
+}
+void mcs_rig_destroy(mcs_rig* rig) { delete rig; }
+int mcs_rig_feature_capacity(const mcs_rig* rig) { return rig ? rig->kp_cap : MCS_ERR_ARG; }
+int mcs_rig_row_capacity(const mcs_rig* rig) { return rig ? rig->row_cap : MCS_ERR_ARG; }
+int mcs_rig_set_orientation(mcs_rig* rig, int enable) {
+    if (!rig) return MCS_ERR_ARG;
+    rig->eng.use_angle = enable ? 1 : 0;
+    return rig->eng.replan(rig->cfg.width, rig->cfg.height);
+}
+
+#define RIG_ENTER(rig)                                                  \
+    if (!(rig)) return MCS_ERR_ARG;                                     \
+    if (cudaSetDevice((rig)->eng.device) != cudaSuccess) return MCS_ERR_CUDA;
+
+int mcs_rig_extract(mcs_rig* rig, const uint8_t* images, int n_frames) {
+    RIG_ENTER(rig);
+    if (!images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    rig->eng.begin_profile();
+    mcs::ImageSet set;
+    const int w = rig->cfg.width, h = rig->cfg.height;
+    int rc = rig->eng.upload(images, n_frames * rig->C, w, h, w, (size_t)w * h, set);
+    if (rc) return rc;
+    return rig->stage_extract(set, n_frames);
+}
+int mcs_rig_extract_device(mcs_rig* rig, const void* d_images, int n_frames) {
+    RIG_ENTER(rig);
+    if (!d_images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    rig->eng.begin_profile();
+    mcs::ImageSet set;
+    int rc = rig->eng.make_set((const uint8_t*)d_images, n_frames * rig->C, rig->cfg.width, rig->cfg.height, set);
+    if (rc) return rc;
+    return rig->stage_extract(set, n_frames);
+}
+
+int mcs_rig_get_features(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, uint8_t* descriptors, int capacity) {
+    RIG_ENTER(rig);
+    if (frame < 0 || frame >= rig->n_extracted || cam < 0 || cam >= rig->C) return MCS_ERR_ARG;
+    int rc = rig->ensure_features();
+    if (rc) return rc;
+    const int img = frame * rig->C + cam, n = rig->eng.h_kp_count[img];
+    if (n > capacity) { set_err("keypoint capacity too small"); return MCS_ERR_CAPACITY; }
+    if (keypoints) memcpy(keypoints, rig->eng.h_kps + (size_t)img * rig->kp_cap, (size_t)n * sizeof(mcs_keypoint));
+    if (descriptors) memcpy(descriptors, rig->eng.h_desc + (size_t)img * rig->kp_cap * 32, (size_t)n * 32);
+    return n;
+}
+
+int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float dist_thresh, float neigh_ratio, uint32_t* indices_1,
+                              uint32_t* indices_2, mcs_keypoint* kps1, mcs_keypoint* kps2, int capacity) {
+    RIG_ENTER(rig);
+    if (frame < 0 || frame >= rig->n_extracted || cam1 < 0 || cam1 >= rig->C || cam2 < 0 || cam2 >= rig->C) return MCS_ERR_ARG;
+    mcs::PairList one{};
+    one.n_pairs = 1;
+    one.a[0] = (unsigned char)cam1;
+    one.b[0] = (unsigned char)cam2;
+    const int cap = rig->kp_cap;
+    dim3 g((cap + MCS_MATCH_NT - 1) / MCS_MATCH_NT, 1, 1);
+    CK(cudaMemsetAsync(rig->d_match_tmp, 0xFF, (size_t)cap * 3 * sizeof(int), rig->eng.stream));
+    mcs::hamming_match_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, rig->eng.stream>>>(rig->C, cap, one, frame, rig->eng.d_desc,
+                                                                                          rig->eng.d_kp_count, dist_thresh, neigh_ratio,
+                                                                                          rig->d_match_tmp, rig->d_match_tmp + cap,
+                                                                                          rig->d_match_tmp + 2 * cap);
+    rig->eng.launches++;
+    CK(cudaMemcpyAsync(rig->h_match_tmp, rig->d_match_tmp, (size_t)cap * 3 * sizeof(int), cudaMemcpyDeviceToHost, rig->eng.stream));
+    CK(cudaStreamSynchronize(rig->eng.stream));
+    int rc = rig->ensure_features();
+    if (rc) return rc;
+    const int ia = frame * rig->C + cam1, ib = frame * rig->C + cam2;
+    const int nq = rig->eng.h_kp_count[ia];
+    int n = 0;
+    for (int q = 0; q < nq; q++) {  // query order is preserved (:1060-1076)
+        const int t = rig->h_match_tmp[q];
+        if (t < 0) continue;
+        if (n >= capacity) { set_err("match capacity too small"); return MCS_ERR_CAPACITY; }
+        if (indices_1) indices_1[n] = (uint32_t)q;
+        if (indices_2) indices_2[n] = (uint32_t)t;
+        // kps come from image_kps_undist; with zero distortion that is a copy of image_kps (MultiCameraFrame.cpp:302-305)
+        if (kps1) memcpy(&kps1[n], rig->eng.h_kps + (size_t)ia * cap + q, sizeof(mcs_keypoint));
+        if (kps2) memcpy(&kps2[n], rig->eng.h_kps + (size_t)ib * cap + t, sizeof(mcs_keypoint));
+        n++;
+    }
+    return n;
+}
+
+int mcs_rig_compute_intra_matches(mcs_rig* rig, int n_frames, int old_epipolar, float dist_thresh, float neigh_ratio) {
+    RIG_ENTER(rig);
+    return rig->stage_match(n_frames, old_epipolar ? 1 : 0, dist_thresh, neigh_ratio);
+}
+int mcs_rig_get_intra_matches(mcs_rig* rig, int frame, int32_t* rows, int capacity) {
+    RIG_ENTER(rig);
+    if (frame < 0 || frame >= rig->n_matched) return MCS_ERR_ARG;
+    int rc = rig->ensure_rows();
+    if (rc) return rc;
+    const int M = rig->h_row_count[frame];
+    if (M > capacity) { set_err("row capacity too small"); return MCS_ERR_CAPACITY; }
+    if (rows) memcpy(rows, rig->h_rows + (size_t)frame * rig->row_cap * rig->C, (size_t)M * rig->C * sizeof(int));
+    return M;
+}
+
+int mcs_rig_triangulate(mcs_rig* rig, int n_frames, const float* masks) {
+    RIG_ENTER(rig);
+    const float* dm = nullptr;
+    int rc = rig->upload_masks(masks, n_frames, &dm);
+    if (rc) return rc;
+    return rig->stage_triangulate(n_frames, dm);
+}
+int mcs_rig_triangulate_device_masks(mcs_rig* rig, int n_frames, const void* d_masks) {
+    RIG_ENTER(rig);
+    return rig->stage_triangulate(n_frames, (const float*)d_masks);
+}
+int mcs_rig_get_landmarks(mcs_rig* rig, int frame, mcs_landmarks* out, int capacity) {
+    RIG_ENTER(rig);
+    if (!out || frame < 0 || frame >= rig->n_triangulated) return MCS_ERR_ARG;
+    int rc = rig->ensure_landmarks();
+    if (rc) return rc;
+    const int M = std::min(rig->h_row_count[frame], rig->row_cap);
+    if (M > capacity) { set_err("landmark capacity too small"); return MCS_ERR_CAPACITY; }
+    const size_t o = (size_t)frame * rig->row_cap;
+    if (out->rows) memcpy(out->rows, rig->h_lm_rows + o * rig->C, (size_t)M * rig->C * sizeof(int));
+    if (out->accepted) memcpy(out->accepted, rig->h_accepted + o, M);
+    if (out->n_views) memcpy(out->n_views, rig->h_n_views + o, (size_t)M * sizeof(int));
+    if (out->xyz) memcpy(out->xyz, rig->h_xyz + o * 3, (size_t)M * 3 * sizeof(double));
+    if (out->uv_ref) memcpy(out->uv_ref, rig->h_uv + o * 2, (size_t)M * 2 * sizeof(float));
+    if (out->rep_cam) memcpy(out->rep_cam, rig->h_rep + o, (size_t)M * sizeof(int));
+    return M;
+}
+
+int mcs_rig_triangulate_nview(mcs_rig* rig, const int* view_inds, int n_views, const double* xs, const double* ys, int n_points, double* xyz) {
+    RIG_ENTER(rig);
+    if (n_views < 2 || n_views > MCS_MAX_CAMS || n_points < 1 || !view_inds || !xs || !ys || !xyz) return MCS_ERR_ARG;
+    for (int i = 0; i < n_views; i++)
+        if (view_inds[i] < 0 || view_inds[i] >= rig->C) return MCS_ERR_ARG;
+    int* d_vi = nullptr;
+    double *d_x = nullptr, *d_y = nullptr, *d_o = nullptr;
+    const size_t nb = (size_t)n_points * n_views * sizeof(double);
+    CK(cudaMalloc(&d_vi, n_views * sizeof(int)));
+    CK(cudaMalloc(&d_x, nb));
+    CK(cudaMalloc(&d_y, nb));
+    CK(cudaMalloc(&d_o, (size_t)n_points * 3 * sizeof(double)));
+    cudaStream_t s = rig->eng.stream;
+    CK(cudaMemcpyAsync(d_vi, view_inds, n_views * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_x, xs, nb, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_y, ys, nb, cudaMemcpyHostToDevice, s));
+    mcs::triangulate_nview_kernel<MCS_MAX_CAMS><<<(n_points + 63) / 64, 64, 0, s>>>(rig->d_calib, d_vi, n_views, d_x, d_y, n_points, d_o);
+    rig->eng.launches++;
+    CK(cudaMemcpyAsync(xyz, d_o, (size_t)n_points * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    cudaFree(d_vi); cudaFree(d_x); cudaFree(d_y); cudaFree(d_o);
+    return 0;
+}
+int mcs_rig_triangulate_pair(mcs_rig* rig, int cam1, int cam2, const float* pts1, const float* pts2, int n_points, float* xyz) {
+    RIG_ENTER(rig);
+    if (cam1 < 0 || cam1 >= rig->C || cam2 < 0 || cam2 >= rig->C || n_points < 1 || !pts1 || !pts2 || !xyz) return MCS_ERR_ARG;
+    float *d_a = nullptr, *d_b = nullptr, *d_o = nullptr;
+    const size_t nb = (size_t)n_points * 2 * sizeof(float);
+    CK(cudaMalloc(&d_a, nb));
+    CK(cudaMalloc(&d_b, nb));
+    CK(cudaMalloc(&d_o, (size_t)n_points * 3 * sizeof(float)));
+    cudaStream_t s = rig->eng.stream;
+    CK(cudaMemcpyAsync(d_a, pts1, nb, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_b, pts2, nb, cudaMemcpyHostToDevice, s));
+    mcs::triangulate_pair_f32_kernel<<<(n_points + 63) / 64, 64, 0, s>>>(rig->d_calib, cam1, cam2, d_a, d_b, n_points, d_o);
+    rig->eng.launches++;
+    CK(cudaMemcpyAsync(xyz, d_o, (size_t)n_points * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    cudaFree(d_a); cudaFree(d_b); cudaFree(d_o);
+    return 0;
+}
+
+static int rig_process_common(mcs_rig* rig, const mcs::ImageSet& set, const float* d_masks, int n_frames, int old_epipolar, bool download) {
+    int rc = rig->stage_extract(set, n_frames);
+    if (rc) return rc;
+    // computeIntraMatches(matches_map, old): BruteForceMatch(i, j, 75, 0.85, ...) (MultiCameraFrame.cpp:1118)
+    if ((rc = rig->stage_match(n_frames, old_epipolar ? 1 : 0, 75.f, 0.85f))) return rc;
+    if ((rc = rig->stage_triangulate(n_frames, d_masks))) return rc;
+    if (download) {
+        if ((rc = rig->eng.download_features(n_frames * rig->C))) return rc;
+        rig->feat_host = true;
+        if ((rc = rig->ensure_rows())) return rc;
+        if ((rc = rig->ensure_landmarks())) return rc;
+    }
+    return 0;
+}
+
+int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* masks, int n_frames, int old_epipolar) {
+    RIG_ENTER(rig);
+    if (!images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    rig->eng.begin_profile();
+    mcs::ImageSet set;
+    const int w = rig->cfg.width, h = rig->cfg.height;
+    int rc = rig->eng.upload(images, n_frames * rig->C, w, h, w, (size_t)w * h, set);
+    if (rc) return rc;
+    const float* dm = nullptr;
+    if ((rc = rig->upload_masks(masks, n_frames, &dm))) return rc;
+    return rig_process_common(rig, set, dm, n_frames, old_epipolar, true);
+}
+int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar) {
+    RIG_ENTER(rig);
+    if (!d_images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    rig->eng.begin_profile();
+    mcs::ImageSet set;
+    int rc = rig->eng.make_set((const uint8_t*)d_images, n_frames * rig->C, rig->cfg.width, rig->cfg.height, set);
+    if (rc) return rc;
+    return rig_process_common(rig, set, (const float*)d_masks, n_frames, old_epipolar, false);
+}
+
+int mcs_rig_get_counts(mcs_rig* rig, int frame, int* kp_counts, int* n_rows, int* n_accepted) {
+    RIG_ENTER(rig);
+    if (frame < 0 || frame >= rig->n_extracted) return MCS_ERR_ARG;
+    int rc;
+    if (kp_counts) {
+        if ((rc = rig->ensure_features())) return rc;
+        for (int c = 0; c < rig->C; c++) kp_counts[c] = rig->eng.h_kp_count[frame * rig->C + c];
+    }
+    if (n_rows) {
+        if (frame >= rig->n_matched) return MCS_ERR_STATE;
+        if ((rc = rig->ensure_rows())) return rc;
+        *n_rows = rig->h_row_count[frame];
+    }
+    if (n_accepted) {
+        if (frame >= rig->n_triangulated) return MCS_ERR_STATE;
+        if ((rc = rig->ensure_landmarks())) return rc;
+        *n_accepted = rig->h_n_acc[frame];
+    }
+    return 0;
+}
+
+void* mcs_rig_stream(mcs_rig* rig) { return rig ? (void*)rig->eng.stream : nullptr; }
+int mcs_rig_synchronize(mcs_rig* rig) {
+    RIG_ENTER(rig);
+    CK(cudaStreamSynchronize(rig->eng.stream));
+    CK(cudaGetLastError());
+    return 0;
+}
+long long mcs_rig_kernel_launches(const mcs_rig* rig) { return rig ? rig->eng.launches : 0; }
+int mcs_rig_set_profiling(mcs_rig* rig, int enable) {
+    if (!rig) return MCS_ERR_ARG;
+    rig->eng.profiling = enable != 0;
+    return 0;
+}
+int mcs_rig_stage_times(mcs_rig* rig, float* ms10) {
+    RIG_ENTER(rig);
+    if (!ms10) return MCS_ERR_ARG;
+    if (rig->eng.profiling) {
+        cudaEventRecord(rig->eng.ev[ST_COUNT], rig->eng.stream);
+        rig->eng.ev_rec[ST_COUNT] = true;
+        CK(cudaStreamSynchronize(rig->eng.stream));
+        rig->eng.collect_profile();
+    }
+    for (int i = 0; i < ST_COUNT; i++) ms10[i] = rig->eng.stage_ms[i];
+    return 0;
+}
+
+// Rig-level observers mirroring the extractor's (parity tests)
+MCS_API int mcs_rig_download_level(mcs_rig* rig, int frame, int cam, int level, int kind, uint8_t* dst, int dst_stride) {
+    RIG_ENTER(rig);
+    return engine_download_level(rig->eng, frame * rig->C + cam, level, kind, dst, dst_stride);
+}
+MCS_API int mcs_rig_level_size(const mcs_rig* rig, int level, int* width, int* height) {
+    if (!rig || level < 0 || level >= rig->eng.plan.nlevels) return MCS_ERR_ARG;
+    if (width) *width = rig->eng.plan.L[level].w;
+    if (height) *height = rig->eng.plan.L[level].h;
+    return 0;
+}
+
+}  // extern "C"

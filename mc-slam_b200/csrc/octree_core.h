@@ -15,8 +15,8 @@
 // (cell row-major, raster inside a cell, :804-871).
 //
 // The algorithm is written against a small execution context so the SAME code runs (a) as a CUDA block (octree kernel in
-// extract_kernels.cuh) and (b) single-threaded on the host for tests/cpp/test_octree_core.cpp, which checks it against the
-// oracle's list-based restatement on random inputs.  Ctx provides:
+// extract_kernels.cuh) and (b) single-threaded on the host for tests/cpp/test_octree_core.cpp, which checks it against a
+// std::list restatement of the reference on random inputs.  Ctx provides:
 //     int  nthreads();  int tid();          — GPU: blockDim.x / threadIdx.x; host: set by the loop driver
 //     template<F> void par(F f);            — run f() for every thread, then barrier
 //     template<F> void serial(F f);         — run f() on thread 0, then barrier

@@ -251,3 +251,63 @@ def brute_force_match(d1, d2, dist_thresh=75.0, ratio=0.85):
             i1.append(pair[0].queryIdx)
             i2.append(pair[0].trainIdx)
     return np.array(i1, np.uint32), np.array(i2, np.uint32)
+
+
+def compute_intra_matches(descs, dist_thresh=75.0, ratio=0.85):
+    """computeIntraMatches(matches, old=false) merge (MultiCameraFrame.cpp:1100-1288) over cv2 BFMatcher pair lists."""
+    nc = len(descs)
+    inv = [np.full(len(d), -1, np.int64) for d in descs]
+    rows = []
+    pair_lists = []
+    for i in range(nc - 1):
+        for j in range(i + 1, nc):
+            i1, i2 = brute_force_match(descs[i], descs[j], dist_thresh, ratio) if len(descs[i]) and len(descs[j]) >= 2 else ([], [])
+            pair_lists.append((np.array(i1, np.uint32), np.array(i2, np.uint32)))
+            for fi, fj in zip(i1, i2):
+                fi, fj = int(fi), int(fj)
+                mi, mj = inv[i][fi], inv[j][fj]
+                if mi == -1 and mj == -1:
+                    r = [-1] * nc
+                    r[i], r[j] = fi, fj
+                    inv[i][fi] = inv[j][fj] = len(rows)
+                    rows.append(r)
+                else:
+                    if mi == -1 and mj != -1:
+                        if rows[mj][i] == -1:
+                            rows[mj][i] = fi
+                            inv[i][fi] = mj
+                    if mi != -1 and mj == -1:
+                        rows[mi][j] = fj
+                        inv[j][fj] = mi
+    return np.array(rows, np.int32).reshape(-1, nc), pair_lists
+
+
+def triangulate_numpy(calib, kps, rows):
+    """FrontEnd.cpp:249-370 triangulation with numpy.linalg.svd as the solveZ (independent of the oracle's Jacobi)."""
+    nc = len(kps)
+    out = np.zeros((len(rows), 3))
+    for r, row in enumerate(rows):
+        views = [c for c in range(nc) if row[c] != -1]
+        if len(views) < 2:
+            continue
+        Ps, xs = [], []
+        for c in views:
+            K = calib[c]["K"].reshape(3, 3)
+            Rt = np.hstack([calib[c]["R"].reshape(3, 3), calib[c]["t"].reshape(3, 1)])
+            p = kps[c][row[c]]
+            xs.append(((float(p["x"]) - K[0, 2]) / K[0, 0], (float(p["y"]) - K[1, 2]) / K[1, 1]))
+            Ps.append(Rt)
+        n = len(views)
+        if n == 2:
+            A = np.zeros((4, 4))
+            for v in range(2):
+                A[2 * v] = xs[v][0] * Ps[v][2] - Ps[v][0]
+                A[2 * v + 1] = xs[v][1] * Ps[v][2] - Ps[v][1]
+        else:
+            A = np.zeros((3 * n, 4 + n))
+            for v in range(n):
+                A[3 * v:3 * v + 3, :4] = -Ps[v]
+                A[3 * v, 4 + v], A[3 * v + 1, 4 + v], A[3 * v + 2, 4 + v] = xs[v][0], xs[v][1], 1.0
+        z = np.linalg.svd(A)[2][-1]
+        out[r] = z[:3] / z[3]
+    return out

@@ -1,0 +1,158 @@
+"""GPU parity: MultiCameraFrame extract -> BruteForceMatch -> computeIntraMatches -> triangulation on the B200 (through
+the C ABI) against the CPU oracle and the cv2 golden rig fixture.  Match indices and IntraMatch rows bit-exact; 3-D points
+within 1e-6 relative (f64 N-view DLT) / 1e-3 (f32 2-view)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_frame(O, imgs, calib, nf, masks=None, old=False):
+    ex = [O.Extractor(nf) for _ in range(len(imgs))]
+    K, D = [], []
+    for c in range(len(imgs)):
+        _, k, d = ex[c](imgs[c])
+        K.append(k)
+        D.append(d)
+    rows, pc = O.intra_matches(D, K, calib, ex[0].sigma2, use_epipolar=old)
+    tri = O.triangulate_rows(calib, K, D, rows, masks=masks)
+    return K, D, rows, pc, tri
+
+
+def _check_frame(rig, f, K, D, rows, tri, C):
+    for c in range(C):
+        k, d = rig.features(f, c)
+        assert len(k) == len(K[c]) and (k == K[c]).all() and np.array_equal(d, D[c]), "features frame %d cam %d" % (f, c)
+    r = rig.intra_matches(f)
+    assert r.shape == rows.shape and np.array_equal(r, rows), "IntraMatch rows frame %d: gpu %s oracle %s" % (f, r.shape, rows.shape)
+    lm = rig.landmarks(f)
+    assert np.array_equal(lm["rows"], tri["rows"]) and np.array_equal(lm["nviews"], tri["nviews"])
+    assert np.array_equal(lm["status"], tri["status"]), "depth-gate decisions"
+    assert np.array_equal(lm["rep_cam"], tri["rep_cam"]), "representative descriptor choice"
+    ok = tri["nviews"] >= 2
+    assert np.allclose(lm["xyz"][ok], tri["xyz"][ok], rtol=1e-6, atol=1e-9), np.abs(lm["xyz"][ok] - tri["xyz"][ok]).max()
+    acc = tri["status"] == 1
+    assert np.allclose(lm["uv_ref"][acc], tri["uv_ref"][acc], rtol=1e-5, atol=1e-3)
+    kc, nr, na = rig.counts(f)
+    assert nr == len(rows) and na == tri["accepted"] and (kc == [len(k) for k in K]).all()
+
+
+def test_rig_golden(golden):
+    import mcslam_b200 as M
+    g = golden("rig3_480x360.npz")
+    rig = M.RigFrames(g["calib"], 480, 360, nfeatures=600, max_frames=1)
+    rig.extract(g["images"][None])
+    for c in range(3):
+        k, d = rig.features(0, c)
+        assert (k == g["kps%d" % c]).all() and np.array_equal(d, g["desc%d" % c])
+    p = 0
+    for i in range(2):
+        for j in range(i + 1, 3):
+            i1, i2, k1, k2 = rig.brute_force_match(0, i, j, 75, 0.85)
+            assert np.array_equal(i1, g["pair%d_i1" % p]) and np.array_equal(i2, g["pair%d_i2" % p]), "pair %d" % p
+            assert (k1 == g["kps%d" % i][i1]).all() and (k2 == g["kps%d" % j][i2]).all()
+            p += 1
+    rig.compute_intra_matches(1)
+    assert np.array_equal(rig.intra_matches(0), g["rows"])
+    rig.triangulate(1)
+    lm = rig.landmarks(0)
+    ok = lm["nviews"] >= 2
+    assert np.allclose(lm["xyz"][ok], g["xyz"][ok], rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("old", [False, True])
+def test_rig5_process_vs_oracle(old):
+    """Config 2: 5 cameras 720x540, 1000 features; two frames in one batch through the one-call path."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(5, 720, 540)
+    frames = np.stack([M.synth.make_rig_frame(calib, 720, 540, frame_index=i) for i in (0, 1)])
+    rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=2)
+    rig.process(frames, old=old)
+    for f in range(2):
+        K, D, rows, pc, tri = _oracle_frame(O, frames[f], calib, 1000, old=old)
+        _check_frame(rig, f, K, D, rows, tri, 5)
+        assert len(rows) > 300 and tri["accepted"] > 200  # the synthetic scene really produces multi-view landmarks
+
+
+def test_rig5_masks_2000_features():
+    """Config 3: semantic masks (CV_32FC1, keep iff mask < 0.7) applied in the triangulation kernel, 2000 features."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(5, 720, 540)
+    frame = M.synth.make_rig_frame(calib, 720, 540, frame_index=3)
+    masks = M.synth.make_masks(5, 720, 540, frame_index=3)
+    rig = M.RigFrames(calib, 720, 540, nfeatures=2000, max_frames=1)
+    rig.process(frame[None], masks=masks[None])
+    K, D, rows, pc, tri = _oracle_frame(O, frame, calib, 2000, masks=list(masks))
+    _check_frame(rig, 0, K, D, rows, tri, 5)
+    assert (tri["rows"] != rows).any(), "masks must actually remove some views"
+
+
+def test_rig8_wide():
+    """8 cameras (IntraMatch width 8 is an extension of the reference's hard-coded 5): pairwise matches + rows vs oracle."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(8, 480, 360, spacing=0.1)
+    frame = M.synth.make_rig_frame(calib, 480, 360, frame_index=7, n_rects=8)
+    rig = M.RigFrames(calib, 480, 360, nfeatures=700, max_frames=1)
+    rig.process(frame[None])
+    K, D, rows, pc, tri = _oracle_frame(O, frame, calib, 700)
+    _check_frame(rig, 0, K, D, rows, tri, 8)
+
+
+def test_match_edge_cases_and_standalone_triangulation():
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(5, 720, 540, spacing=0.165)
+    rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=1)
+    # a flat rig frame: no keypoints anywhere -> no rows, nothing crashes
+    rig.process(np.full((1, 5, 540, 720), 90, np.uint8))
+    assert len(rig.intra_matches(0)) == 0 and len(rig.landmarks(0)["rows"]) == 0
+    # known-answer fixture (MultiCameraFrame.cpp:383-409): X = (0,0,6)
+    X = np.array([0, 0, 6.0, 1.0])
+    xs, ys = [], []
+    for c in range(5):
+        K = calib[c]["K"].reshape(3, 3)
+        Rt = np.hstack([calib[c]["R"].reshape(3, 3), calib[c]["t"].reshape(3, 1)])
+        p = K @ Rt @ X
+        xs.append(p[0] / p[2])
+        ys.append(p[1] / p[2])
+    for views in ([0, 1], [0, 2, 4], [0, 1, 2, 3, 4]):
+        got = rig.triangulate_nview(views, [[xs[v] for v in views]], [[ys[v] for v in views]])[0]
+        assert np.allclose(got, [0, 0, 6], atol=1e-8), (views, got)
+        ref = O.triangulate_pixels(calib, views, [xs[v] for v in views], [ys[v] for v in views])
+        assert np.allclose(got, ref, rtol=1e-6)
+    rng = np.random.default_rng(5)
+    P3 = np.stack([rng.uniform(-3, 3, 200), rng.uniform(-2, 2, 200), rng.uniform(2, 30, 200)], 1)
+    pts = []
+    for c in (0, 4):
+        K = calib[c]["K"].reshape(3, 3)
+        Xc = P3 @ calib[c]["R"].reshape(3, 3).T + calib[c]["t"]
+        uv = Xc @ K.T
+        pts.append((uv[:, :2] / uv[:, 2:]).astype(np.float32))
+    got = rig.triangulate_pair(0, 4, pts[0], pts[1])
+    ref = O.triangulate_pair_f32(calib, 0, 4, pts[0], pts[1])
+    rel = np.abs(got - ref).max(1) / np.abs(ref).max(1)
+    assert np.median(rel) < 1e-3  # f32 4x4 SVD: 1e-3 relative
+
+
+def test_device_resident_path_matches_host_path():
+    import mcslam_b200 as M
+    from mcslam_b200 import binding as B
+    calib = M.synth.make_rig(5, 720, 540)
+    frames = np.stack([M.synth.make_rig_frame(calib, 720, 540, frame_index=i) for i in (4,)])
+    rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=1)
+    rig.process(frames)
+    ref = [rig.features(0, c) for c in range(5)], rig.intra_matches(0), rig.landmarks(0)
+    dptr = B.device_malloc(0, frames.nbytes)
+    B.device_upload(0, dptr, frames)
+    rig.process_device(dptr, 1)
+    rig.synchronize()
+    for c in range(5):
+        k, d = rig.features(0, c)
+        assert (k == ref[0][c][0]).all() and np.array_equal(d, ref[0][c][1])
+    assert np.array_equal(rig.intra_matches(0), ref[1])
+    assert np.array_equal(rig.landmarks(0)["xyz"], ref[2]["xyz"])
+    assert rig.kernel_launches > 0
+    B.device_free(0, dptr)

@@ -1,0 +1,106 @@
+"""CPU: the portable C++ oracle (oracle/mcs_oracle.cpp) against the committed cv2-generated golden vectors
+(tests/golden/*.npz, made by oracle/gen_golden.py with OpenCV 4.13.0).  Integer outputs must be bit-exact."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+SINGLES = [("single_256x192.npz", 300), ("noise_203x157.npz", 400), ("lowcontrast_320x240.npz", 500)]
+
+
+@pytest.mark.parametrize("name,nf", SINGLES)
+def test_extractor_matches_golden(golden, name, nf):
+    g = golden(name)
+    e = O.Extractor(nf)
+    mono, kps, desc = e(g["image"])
+    assert (e.quota == g["quota"]).all() and (e.scale == g["scale"]).all() and (e.sigma2 == g["sigma2"]).all()
+    assert (e.inv_scale == g["inv_scale"]).all() and (e.inv_sigma2 == g["inv_sigma2"]).all()
+    for l in range(8):
+        assert np.array_equal(e.level(l), g["pyr%d" % l]), "pyramid level %d" % l
+        assert np.array_equal(e.candidates(l), g["cand%d" % l].reshape(-1, 3)), "FAST candidates level %d" % l
+        if "blur%d" % l in g.files:
+            assert np.array_equal(e.level(l, blurred=True), g["blur%d" % l]), "blurred level %d" % l
+    assert np.array_equal(e.level_padded(3), g["pyr_padded3"])
+    assert np.array_equal(e.level_counts(), g["level_counts"])
+    assert mono == int(g["mono"]) and len(kps) == len(g["kps"])
+    assert (kps == g["kps"]).all(), "keypoints (x, y, size, angle, response, octave, class_id)"
+    assert np.array_equal(desc, g["desc"]), "descriptor bits"
+
+
+def test_rig_golden(golden):
+    g = golden("rig3_480x360.npz")
+    K, D = [], []
+    for c in range(3):
+        _, k, d = O.Extractor(600)(g["images"][c])
+        assert (k == g["kps%d" % c]).all() and np.array_equal(d, g["desc%d" % c])
+        K.append(k)
+        D.append(d)
+    p = 0
+    for i in range(2):
+        for j in range(i + 1, 3):
+            i1, i2, *_ = O.bf_match(D[i], D[j])
+            assert np.array_equal(i1, g["pair%d_i1" % p]) and np.array_equal(i2, g["pair%d_i2" % p]), "pair %d" % p
+            p += 1
+    rows, pc = O.intra_matches(D, K, g["calib"], g["sigma2"])
+    assert np.array_equal(rows, g["rows"])
+    tri = O.triangulate_rows(g["calib"], K, D, rows)
+    ok = tri["nviews"] >= 2
+    # numpy.linalg.svd (golden) vs one-sided Jacobi (oracle): 1e-6 relative
+    assert np.allclose(tri["xyz"][ok], g["xyz"][ok], rtol=1e-6, atol=1e-9)
+    assert tri["accepted"] == int(((g["xyz"][:, 2] < 40) & (g["xyz"][:, 2] > 0.5) & ok).sum())
+
+
+def test_fast_atan2_golden(golden):
+    g = golden("fast_atan2.npz")
+    got = np.array([O.lib().orc_fast_atan2(float(y), float(x)) for y, x in g["yx"]], np.float32)
+    assert np.array_equal(got, g["ang"])
+
+
+def test_known_answer_triangulation():
+    """testTriangulateIntraMatches (MultiCameraFrame.cpp:383-409): X = (0, 0, 6) seen by a 0.165 m rig triangulates back."""
+    import mcslam_b200
+    calib = mcslam_b200.synth.make_rig(5, 720, 540, spacing=0.165)
+    X = np.array([0, 0, 6.0, 1.0])
+    xs, ys = [], []
+    for c in range(5):
+        K = calib[c]["K"].reshape(3, 3)
+        Rt = np.hstack([calib[c]["R"].reshape(3, 3), calib[c]["t"].reshape(3, 1)])
+        p = K @ Rt @ X
+        xs.append(p[0] / p[2])
+        ys.append(p[1] / p[2])
+    for views in ([0, 1], [0, 2, 4], [0, 1, 2, 3, 4]):
+        got = O.triangulate_pixels(calib, views, [xs[v] for v in views], [ys[v] for v in views])
+        assert np.allclose(got, [0, 0, 6], atol=1e-8), (views, got)
+    got32 = O.triangulate_pair_f32(calib, 0, 4, [[xs[0], ys[0]]], [[xs[4], ys[4]]])
+    assert np.allclose(got32[0], [0, 0, 6], atol=2e-2)
+
+
+def test_edge_cases():
+    e = O.Extractor(100)
+    mono, k, d = e(np.zeros((0, 0), np.uint8).reshape(0, 0)) if False else (-1, [], [])
+    assert mono == -1
+    flat = np.full((120, 160), 77, np.uint8)  # no corners anywhere
+    mono, k, d = e(flat)
+    assert mono == 0 and len(k) == 0
+    tiny = np.random.default_rng(0).integers(0, 256, (50, 60), dtype=np.uint8)  # smaller than one FAST cell + borders
+    mono, k, d = e(tiny)
+    assert mono == 0
+    # brute-force matcher: fewer than 2 train descriptors -> no matches (reference reads m[1] out of range)
+    q = np.random.default_rng(1).integers(0, 256, (5, 32), dtype=np.uint8)
+    i1, i2, *_ = O.bf_match(q, q[:1])
+    assert len(i1) == 0
+    # exact duplicates: best distance 0, ties resolved to the lower train index
+    t = np.concatenate([q, q])
+    i1, i2, bd, sd, bi = O.bf_match(q, t)
+    assert (bd == 0).all() and (bi == np.arange(5)).all() and (sd == 0).all() and len(i1) == 0
+
+
+def test_lapping_area(golden):
+    g = golden("single_256x192.npz")
+    e = O.Extractor(300)
+    mono0, k0, d0 = e(g["image"])
+    mono, k, d = e(g["image"], lapping=(60, 140))
+    st = (k0["x"] >= 60) & (k0["x"] <= 140)
+    assert mono == int((~st).sum()) and len(k) == len(k0)
+    assert (k[:mono] == k0[~st]).all() and (k[mono:] == k0[st][::-1]).all()
+    assert np.array_equal(d[:mono], d0[~st]) and np.array_equal(d[mono:], d0[st][::-1])
