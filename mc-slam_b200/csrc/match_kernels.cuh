@@ -220,38 +220,49 @@ __device__ __forceinline__ int hamming256(const uint8_t* a, const uint8_t* b) {
            __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
-// N-view DLT on projections Pm[k] (3x4) and points (xs[k], ys[k]); n >= 2.  2 views: 4x4 system; else (3n) x (4+n).
+// 2-view DLT (cv::sfm::triangulatePoints with two views): 4x4 system rows x*P[2]-P[0], y*P[2]-P[1].
+// Kept out of line with scalar arguments: inlining it next to the design-matrix path made cicc -O3 (12.9) read the caller's
+// xs/ys/Pm arrays before they were written (observed on sm_100a: NaN for every 2-view row), see tools/dbg.
+__device__ __noinline__ void dlt_2views(const double* P0, const double* P1, double x0, double y0, double x1, double y1, double* X3) {
+    double A[16], V[16], z[4];
+#pragma unroll 1
+    for (int i = 0; i < 4; i++) {
+        A[0 * 4 + i] = x0 * P0[8 + i] - P0[i];
+        A[1 * 4 + i] = y0 * P0[8 + i] - P0[4 + i];
+        A[2 * 4 + i] = x1 * P1[8 + i] - P1[i];
+        A[3 * 4 + i] = y1 * P1[8 + i] - P1[4 + i];
+    }
+    null_vector<double, 4, 4>(A, V, 4, 4, z, 2.220446049250313e-16);
+    X3[0] = z[0] / z[3];
+    X3[1] = z[1] / z[3];
+    X3[2] = z[2] / z[3];
+}
+
+// N-view DLT, (3n) x (4+n) design [-P_i | x_i in column 4+i] (MultiCameraFrame.cpp:419-433), n >= 2.
 template <int MAXC>
-__device__ void dlt_nviews(const double* const* Pm, const double* xs, const double* ys, int nv, bool force_design, double* X3) {
+__device__ __noinline__ void dlt_design(const double* const* Pm, const double* xs, const double* ys, int nv, double* X3) {
     double A[3 * MAXC * (4 + MAXC)];
     double V[(4 + MAXC) * (4 + MAXC)];
     double z[4 + MAXC];
-    int m, n;
-    if (nv == 2 && !force_design) {
-        m = 4;
-        n = 4;
-        for (int i = 0; i < 4; i++) {
-            A[0 * 4 + i] = xs[0] * Pm[0][8 + i] - Pm[0][i];
-            A[1 * 4 + i] = ys[0] * Pm[0][8 + i] - Pm[0][4 + i];
-            A[2 * 4 + i] = xs[1] * Pm[1][8 + i] - Pm[1][i];
-            A[3 * 4 + i] = ys[1] * Pm[1][8 + i] - Pm[1][4 + i];
-        }
-    } else {
-        m = 3 * nv;
-        n = 4 + nv;
-        for (int i = 0; i < m * n; i++) A[i] = 0;
-        for (int i = 0; i < nv; i++) {
-            for (int jj = 0; jj < 3; jj++)
-                for (int ii = 0; ii < 4; ii++) A[(3 * i + jj) * n + ii] = -Pm[i][jj * 4 + ii];
-            A[(3 * i + 0) * n + 4 + i] = xs[i];
-            A[(3 * i + 1) * n + 4 + i] = ys[i];
-            A[(3 * i + 2) * n + 4 + i] = 1.0;
-        }
+    const int m = 3 * nv, n = 4 + nv;
+    for (int i = 0; i < m * n; i++) A[i] = 0;
+    for (int i = 0; i < nv; i++) {
+        for (int jj = 0; jj < 3; jj++)
+            for (int ii = 0; ii < 4; ii++) A[(3 * i + jj) * n + ii] = -Pm[i][jj * 4 + ii];
+        A[(3 * i + 0) * n + 4 + i] = xs[i];
+        A[(3 * i + 1) * n + 4 + i] = ys[i];
+        A[(3 * i + 2) * n + 4 + i] = 1.0;
     }
     null_vector<double, 3 * MAXC, 4 + MAXC>(A, V, m, n, z, 2.220446049250313e-16);
     X3[0] = z[0] / z[3];
     X3[1] = z[1] / z[3];
     X3[2] = z[2] / z[3];
+}
+
+template <int MAXC>
+__device__ __forceinline__ void dlt_nviews(const double* const* Pm, const double* xs, const double* ys, int nv, bool force_design, double* X3) {
+    if (nv == 2 && !force_design) dlt_2views(Pm[0], Pm[1], xs[0], ys[0], xs[1], ys[1], X3);
+    else dlt_design<MAXC>(Pm, xs, ys, nv, X3);
 }
 
 struct LandmarkOut {
