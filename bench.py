@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""bench.py — rig-frames/s of the MC-SLAM front-end hot path (ORB extract + intra-rig match + triangulate) on B200.
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0.  For N > 1 it is launched
+under torchrun (one rank per GPU); frames are sharded by rig frame, no collective on the data path (weak scaling: every
+rank processes its own batch of `--frames` rig frames per step).
+
+  value     : rig-frames/s, inputs resident in HBM, results left on the device (mcs_rig_process_device)
+  e2e       : rig-frames/s through the host-buffer C-ABI call (mcs_rig_process): pinned H2D of the images and D2H of
+              keypoints / descriptors / IntraMatch rows / landmarks inside the timed region
+  roofline  : dominant stage, algorithmic bytes (DESIGN.md "Algorithmic bytes") / its CUDA-event time, vs MEASURED_PEAKS.json
+  cpu_baseline : oracle/liboracle.so (CPU restatement of the reference path, kind "port") on a bounded sample, rank 0, N = 1
+`--impl reference` times that CPU path alone with all host threads (the reference itself needs OpenCV C++/Eigen/DBoW2 and
+cannot be compiled here).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOAD = "config2: 5-camera 720x540 rig, ORB(1000 features, 8 levels, 1.2, FAST 20/7) extract + 10-pair Hamming intra-match + N-view triangulation"
+W, H, NCAM, NFEAT = 720, 540, 5, 1000
+STAGES = ["upload", "pyramid", "fast", "octree", "blur", "describe", "match", "merge", "triangulate", "download"]
+
+
+def level_sizes(w, h, nlevels=8, scale=1.2):
+    """Level sizes as the reference constructor + ComputePyramid derive them (f32 running product, cvRound)."""
+    sf = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        sf.append(np.float32(np.float64(sf[-1]) * np.float64(np.float32(scale))))
+    out = []
+    for s in sf:
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
+
+
+def algorithmic_bytes(ncam=NCAM, w=W, h=H, nfeat=NFEAT):
+    """SURVEY.md 8(d) two-pass pixel model, per rig frame; also the per-stage split used for the dominant-kernel roofline."""
+    px = [a * b for a, b in level_sizes(w, h)]
+    allpx, src = sum(px), px[0]
+    per_cam = {
+        "pyramid": sum(px[:-1]) + sum(px[1:]),           # each level read once to make the next, levels 1..7 written once
+        "fast": allpx + 4 * 10 * nfeat // 4,             # every level read once; candidate records (4 B, ~2.5 per kept feature)
+        "octree": 4 * 10 * nfeat // 4 + 4 * nfeat,       # candidate records in, selected records out
+        "blur": 2 * allpx,                               # every level read and written once
+        "describe": (32 + 28 + 4) * nfeat,               # selected record in, descriptor + keypoint out
+    }
+    frame = {k: v * ncam for k, v in per_cam.items()}
+    frame["match"] = ncam * (ncam - 1) * nfeat * 32 + (ncam * (ncam - 1) // 2) * nfeat * 8
+    frame["merge"] = (ncam * (ncam - 1) // 2) * nfeat * 4 + 3000 * ncam * 4
+    frame["triangulate"] = 3000 * (4 * ncam + 24)
+    extract = ncam * (src + (allpx - src) + allpx + 60 * nfeat)
+    total = extract + frame["match"] + frame["triangulate"]
+    return total, frame
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0])); mx.append(float(c[1])); pw.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def make_workload(n_frames, distinct, rank):
+    """[n_frames, NCAM, H, W] u8.  `distinct` frames come from the synthetic scene generator (seed = 1234 + frame index,
+    SURVEY.md 8d); the rest of the batch are those frames cyclically shifted by 8k columns (all cameras alike, so the
+    cross-camera geometry is kept) — distinct pixel data per frame without minutes of ray casting."""
+    import mcslam_b200 as M
+    calib = M.synth.make_rig(NCAM, W, H)
+    base = [M.synth.make_rig_frame(calib, W, H, frame_index=rank * distinct + i) for i in range(distinct)]
+    frames = np.empty((n_frames, NCAM, H, W), np.uint8)
+    for f in range(n_frames):
+        frames[f] = np.roll(base[f % distinct], 8 * (f // distinct), axis=2)
+    return calib, frames
+
+
+def cpu_sample(calib, frames, seconds, threads_per_frame, pool_threads):
+    """Times the CPU oracle (oracle/liboracle.so: C++ restatement of ORBextractor + BruteForceMatch + merge + DLT) on as many
+    frames of the workload as fit in ~`seconds`.  threads_per_frame = 5 mirrors the reference's thread-per-camera fan-out
+    (MultiCameraFrame.cpp:212-227); pool_threads frames run concurrently."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_lib as O
+    from concurrent.futures import ThreadPoolExecutor
+    exs = [[O.Extractor(NFEAT) for _ in range(NCAM)] for _ in range(pool_threads)]
+    O.process_rig(exs[0], frames[0], calib, threads=threads_per_frame)  # warm-up (page-in, allocations)
+    done = 0
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(pool_threads) as tp:
+        while True:
+            list(tp.map(lambda i: O.process_rig(exs[i], frames[(done + i) % len(frames)], calib, threads=threads_per_frame),
+                        range(pool_threads)))
+            done += pool_threads
+            if time.perf_counter() - t0 >= seconds:
+                break
+    dt = time.perf_counter() - t0
+    return done / dt, done, dt
+
+
+def run_reference(args, rank):
+    """--impl reference: the CPU path on the box's host cores (oracle port; the reference cannot be compiled here)."""
+    if rank != 0:
+        return
+    ncores = os.cpu_count() or 1
+    pool = max(1, ncores // NCAM)
+    calib, frames = make_workload(max(pool, 2), 2, 0)
+    per_step = []
+    for s in range(args.warmup + args.steps):
+        fps, n, dt = cpu_sample(calib, frames, args.cpu_step_seconds, NCAM, pool)
+        if s >= args.warmup:
+            per_step.append((fps, n, dt))
+    fps = float(np.mean([p[0] for p in per_step]))
+    total, _ = algorithmic_bytes()
+    line = {
+        "impl": "reference", "metric": "rig-frames/sec (ORB extract+intra-match+triangulate)", "value": fps, "unit": "rig-frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * float(np.mean([p[2] for p in per_step])),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_step": int(np.mean([p[1] for p in per_step])), "note": "CPU only; bounded sample per step"},
+        "cpu_baseline": {"value": fps, "unit": "rig-frames/s", "cores": min(ncores, pool * NCAM), "kind": "port",
+                         "sample": "%d concurrent rig frames x %d camera threads, ~%.0f s per step" % (pool, NCAM, args.cpu_step_seconds)},
+        "e2e": {"value": fps, "unit": "rig-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def dist_setup(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_gpu(args, rank, world, local):
+    import mcslam_b200 as M
+    from mcslam_b200 import binding as B
+    if M.lib().mcs_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU arm)")
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    F = args.frames
+    calib, frames = make_workload(F, args.distinct, rank)
+    rig = M.RigFrames(calib, W, H, nfeatures=NFEAT, max_frames=F, device=local)
+    # pinned host staging (the e2e leg copies from here every step) + a resident device copy (the `value` leg)
+    pin = B.pinned_empty(frames.shape, np.uint8)
+    pin.arr[...] = frames
+    d_images = B.device_malloc(local, frames.nbytes)
+    B.device_upload(local, d_images, frames)
+
+    def barrier():
+        rig.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        import torch
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(fn, steps):
+        barrier()
+        rig.timer_start()
+        for _ in range(steps):
+            fn()
+        ms = rig.timer_stop()
+        barrier()
+        return max_over_ranks(ms)
+
+    dev_step = lambda: rig.process_device(d_images, F)            # noqa: E731
+    host_step = lambda: rig.process(pin.arr)                      # noqa: E731
+    for _ in range(max(args.warmup, 3)):
+        dev_step()
+    rig.synchronize()
+    launches0 = rig.kernel_launches
+    clocks = ClockSampler(local)
+    ms_dev = timed(dev_step, args.steps)
+    launches = rig.kernel_launches - launches0
+    for _ in range(max(args.warmup, 3)):
+        host_step()
+    ms_e2e = timed(host_step, args.steps)
+    clk = clocks.stop()
+    # per-stage device times (CUDA events between the stages on the rig's stream), same steps again with profiling on
+    rig.set_profiling(True)
+    acc = dict.fromkeys(STAGES, 0.0)
+    for _ in range(args.steps):
+        dev_step()
+        for k, v in rig.stage_times().items():
+            acc[k] += v
+    rig.set_profiling(False)
+    stage_ms = {k: v / args.steps for k, v in acc.items()}
+    kc, n_rows, n_acc = rig.counts(0)
+    d2h = rig_d2h_bytes(rig, F)
+    return dict(rig=rig, calib=calib, frames=frames, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches, clocks=clk, stage_ms=stage_ms,
+                counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, F=F, dist=dist)
+
+
+def rig_d2h_bytes(rig, F):
+    """Bytes mcs_rig_process copies back per call (counted from the copies in mcslam_b200.cu download_features/ensure_*)."""
+    C_, cap, rc = rig.C, rig.kp_cap, rig.row_cap
+    feats = F * C_ * (cap * (28 + 32) + 4 + 4 + 2 * 4 * rig.nlevels)
+    rows = F * (4 + rc * C_ * 4)
+    lms = F * (4 + 4) + F * rc * (C_ * 4 + 1 + 4 + 24 + 8 + 4)
+    return feats + rows + lms
+
+
+def parity_report(rig, calib, frames):
+    """Mismatch counts of rig frame 0 against the CPU oracle (keypoints, descriptor bits, IntraMatch rows, 3-D points)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_lib as O
+    ex = O.Extractor(NFEAT)
+    K, D, bad_kp, bad_bits = [], [], 0, 0
+    for c in range(rig.C):
+        k, d = rig.features(0, c)
+        _, k2, d2 = ex(frames[0, c])
+        K.append(k2); D.append(d2)
+        if len(k) != len(k2):
+            bad_kp += abs(len(k) - len(k2)) + 1
+            continue
+        bad_kp += int((k != k2).sum())
+        bad_bits += int(np.unpackbits(d ^ d2).sum())
+    rows, _ = O.intra_matches(D, K, calib, ex.sigma2)
+    got = rig.intra_matches(0)
+    bad_rows = -1 if got.shape != rows.shape else int((got != rows).any(axis=1).sum())
+    tri = O.triangulate_rows(calib, K, D, rows)
+    lm = rig.landmarks(0)
+    ok = tri["nviews"] >= 2
+    if bad_rows == 0 and np.array_equal(lm["status"], tri["status"]):
+        rel = np.abs(lm["xyz"][ok] - tri["xyz"][ok]) / np.maximum(np.abs(tri["xyz"][ok]), 1e-9)
+        max_rel = float(rel.max()) if rel.size else 0.0
+    else:
+        max_rel = None
+    return {"frame": 0, "mismatched_keypoints": bad_kp, "mismatched_descriptor_bits": bad_bits, "mismatched_intramatch_rows": bad_rows,
+            "xyz_max_rel_err": max_rel, "xyz_tolerance": 1e-6}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=64, help="rig frames per step per GPU (one batched launch sequence)")
+    ap.add_argument("--distinct", type=int, default=4, help="ray-cast scenes per rank; the batch is filled with shifted copies")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline sample length")
+    ap.add_argument("--cpu-step-seconds", type=float, default=6.0, help="--impl reference: seconds of CPU work per step")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the oracle parity check and the CPU baseline (profiling runs)")
+    args = ap.parse_args()
+    rank, world, local = dist_setup(args)
+    if args.gpus > 1 and world == 1 and "RANK" not in os.environ:
+        # launched bare with --gpus N: re-launch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
+               "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    r = run_gpu(args, rank, world, local)
+    F, steps = r["F"], args.steps
+    total_bytes, stage_bytes = algorithmic_bytes()
+    value = world * F * steps / (r["ms_dev"] / 1e3)
+    e2e = world * F * steps / (r["ms_e2e"] / 1e3)
+    if rank != 0:
+        if r["dist"] is not None:
+            r["dist"].destroy_process_group()
+        return
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback"
+    sm = r["stage_ms"]
+    kernels = {k: v for k, v in sm.items() if k not in ("upload", "download")}
+    dom = max(kernels, key=kernels.get)
+    launches_per_step = {"pyramid": 7}.get(dom, 1)
+    achieved = stage_bytes[dom] * F / (sm[dom] / 1e3) / 1e9
+    line = {
+        "metric": "rig-frames/sec (ORB extract+intra-match+triangulate)", "value": value, "unit": "rig-frames/s", "n_gpus": world,
+        "steps": steps, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": F, "distinct_scenes": args.distinct,
+                   "l2": "per-step working set (%.0f MB of images + pyramids + blurred pyramids per GPU) exceeds the 126 MB L2" %
+                         (F * NCAM * (W * H + 2 * 1.3e6) / 1e6),
+                   "sharding": "by rig frame, no collective"},
+        "e2e": {"value": e2e, "unit": "rig-frames/s", "h2d_bytes_per_step": int(F * NCAM * W * H), "d2h_bytes_per_step": int(r["d2h"]),
+                "ms_per_step": r["ms_e2e"] / steps},
+        "gpu_launches": int(r["launches"]),
+        "clocks": r["clocks"],
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": stage_bytes[dom] * F // launches_per_step,
+                     "launch_ms": sm[dom] / launches_per_step,
+                     "path": {"bytes_per_rig_frame": total_bytes, "achieved": total_bytes * value / world / 1e9,
+                              "frac": total_bytes * value / world / 1e9 / peak}},
+        "stage_ms_per_step": {k: round(v, 4) for k, v in sm.items()},
+        "counts_frame0": {"keypoints": r["counts"][0], "intramatch_rows": r["counts"][1], "landmarks": r["counts"][2]},
+    }
+    if world == 1 and not args.no_cpu:
+        line["parity"] = parity_report(r["rig"], r["calib"], r["frames"])
+        ncores = os.cpu_count() or 1
+        fps, n, dt = cpu_sample(r["calib"], r["frames"], args.cpu_seconds, NCAM, 1)
+        line["cpu_baseline"] = {"value": fps, "unit": "rig-frames/s", "cores": min(NCAM, ncores), "kind": "port",
+                                "sample": "%d rig frames of the workload in %.1f s, reference threading (1 thread per camera)" % (n, dt),
+                                "host_cores": ncores}
+    print(json.dumps(line), flush=True)
+    if r["dist"] is not None:
+        r["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -191,6 +191,10 @@ MCS_API long long mcs_rig_kernel_launches(const mcs_rig* rig); /* kernels launch
  * [0] upload, [1] pyramid, [2] FAST, [3] octree, [4] blur, [5] describe, [6] match, [7] merge, [8] triangulate, [9] download */
 MCS_API int mcs_rig_stage_times(mcs_rig* rig, float* ms10);
 MCS_API int mcs_rig_set_profiling(mcs_rig* rig, int enable); /* record the per-stage events (adds event overhead) */
+/* Stopwatch on the rig's own stream (torch.cuda.Event only sees torch's current stream): start records an event, stop records a
+ * second one, waits for it and returns the device time between the two in milliseconds. */
+MCS_API int mcs_rig_timer_start(mcs_rig* rig);
+MCS_API int mcs_rig_timer_stop(mcs_rig* rig, float* ms);
 
 /* Plain device-memory helpers so harnesses written without a CUDA binding can stage resident inputs. */
 MCS_API void* mcs_device_malloc(int device, size_t bytes);

@@ -672,11 +672,13 @@ struct mcs_rig {
     int n_extracted = 0, n_matched = 0, n_triangulated = 0;
     bool feat_host = false, rows_host = false, lm_host = false;
     size_t merge_smem = 0;
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
 
     ~mcs_rig() {
         if (!eng.stream) return;
         cudaSetDevice(eng.device);
         cudaStreamSynchronize(eng.stream);
+        if (t0) { cudaEventDestroy(t0); cudaEventDestroy(t1); }
         cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
         cudaFree(d_row_count); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
         cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks);
@@ -1111,6 +1113,21 @@ int mcs_rig_stage_times(mcs_rig* rig, float* ms10) {
         rig->eng.collect_profile();
     }
     for (int i = 0; i < ST_COUNT; i++) ms10[i] = rig->eng.stage_ms[i];
+    return 0;
+}
+
+int mcs_rig_timer_start(mcs_rig* rig) {
+    RIG_ENTER(rig);
+    if (!rig->t0) { CK(cudaEventCreate(&rig->t0)); CK(cudaEventCreate(&rig->t1)); }
+    CK(cudaEventRecord(rig->t0, rig->eng.stream));
+    return 0;
+}
+int mcs_rig_timer_stop(mcs_rig* rig, float* ms) {
+    RIG_ENTER(rig);
+    if (!rig->t0 || !ms) return MCS_ERR_STATE;
+    CK(cudaEventRecord(rig->t1, rig->eng.stream));
+    CK(cudaEventSynchronize(rig->t1));
+    CK(cudaEventElapsedTime(ms, rig->t0, rig->t1));
     return 0;
 }
 
