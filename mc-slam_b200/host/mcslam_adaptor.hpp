@@ -1,0 +1,276 @@
+// mcslam_adaptor.hpp — header-only C++17 host side over the C ABI (include/mcslam_b200.h) that keeps the call shapes of the two
+// reference classes the front-end uses, so FrontEnd code compiles against it unchanged:
+//   ORBextractor       /root/reference/MCSlam/include/MCSlam/ORBextractor.h:44-112
+//   MultiCameraFrame   /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h (extract / intra-match / triangulate subset)
+//   IntraMatch         /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h:42-57
+// Without OpenCV headers the containers are PODs (mcs_keypoint, byte vectors).  Define MCS_WITH_OPENCV before including this
+// file (in a build that has OpenCV) to get the cv::InputArray / cv::KeyPoint / cv::Mat overloads with the reference's exact
+// signatures.  There is no CPU path: every method launches the sm_100a kernels and throws std::runtime_error when the library
+// reports an error (the reference's own conventions are kept where it has them: operator() returns -1 for an empty image).
+#ifndef MCSLAM_ADAPTOR_HPP
+#define MCSLAM_ADAPTOR_HPP
+
+#include <array>
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/mcslam_b200.h"
+
+#ifdef MCS_WITH_OPENCV
+#include <opencv2/core/core.hpp>
+#include <opencv2/features2d/features2d.hpp>
+#endif
+
+namespace mcs_b200 {
+
+inline void check(int rc, const char* what) {
+    if (rc < 0) throw std::runtime_error(std::string(what) + ": " + mcs_last_error());
+}
+
+// ORBextractor.h:44-112.  One object per concurrent caller (the reference keeps one per camera thread, FrontEnd.h:190-193).
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0, int max_width = 720,
+                 int max_height = 540)
+        : nlevels_(nlevels), scaleFactor_(scaleFactor) {
+        h_ = mcs_extractor_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device, max_width, max_height, 1);
+        if (!h_) throw std::runtime_error(std::string("mcs_extractor_create: ") + mcs_last_error());
+        mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels); mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
+        mnFeaturesPerLevel.resize(nlevels);
+        int nl = 0;
+        check(mcs_extractor_get_tables(h_, &nl, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(),
+                                       mvInvLevelSigma2.data(), mnFeaturesPerLevel.data()), "mcs_extractor_get_tables");
+    }
+    ~ORBextractor() { mcs_extractor_destroy(h_); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // operator()(image, mask, keypoints, descriptors, vLappingArea) on raw CV_8UC1 pixels.  descriptors: n x 32 bytes, row-major.
+    // Returns monoIndex (ORBextractor.cpp:1170) or -1 for an empty image (:1090-1091).
+    int operator()(const uint8_t* image, int width, int height, int stride, const uint8_t* mask /*ignored, ORBextractor.h:56*/,
+                   std::vector<mcs_keypoint>& keypoints, std::vector<uint8_t>& descriptors, std::vector<int>& vLappingArea) {
+        if (!image || width <= 0 || height <= 0) return -1;
+        const int lap[2] = {vLappingArea.size() > 0 ? vLappingArea[0] : 0, vLappingArea.size() > 1 ? vLappingArea[1] : 0};
+        int rc = MCS_ERR_CAPACITY, total = 0;
+        for (int attempt = 0; attempt < 2 && rc == MCS_ERR_CAPACITY; attempt++) {  // capacity follows the image-size-dependent plan
+            const int cap = mcs_extractor_capacity(h_) > 8 ? mcs_extractor_capacity(h_) : 8;
+            keypoints.resize(cap);
+            descriptors.resize((size_t)cap * 32);
+            rc = mcs_extract(h_, image, width, height, stride, mask, lap, keypoints.data(), descriptors.data(), cap, &total);
+        }
+        if (rc == MCS_ERR_EMPTY) return -1;
+        check(rc, "mcs_extract");
+        keypoints.resize(total);              // _keypoints = vector<KeyPoint>(nkeypoints)  (:1118)
+        descriptors.resize((size_t)total * 32);  // _descriptors.create(nkeypoints, 32, CV_8U) (:1112)
+        return rc;
+    }
+
+#ifdef MCS_WITH_OPENCV
+    int operator()(cv::InputArray _image, cv::InputArray _mask, std::vector<cv::KeyPoint>& _keypoints, cv::OutputArray _descriptors,
+                   std::vector<int>& vLappingArea) {
+        (void)_mask;
+        if (_image.empty()) return -1;
+        cv::Mat image = _image.getMat();
+        CV_Assert(image.type() == CV_8UC1);  // ORBextractor.cpp:1094
+        std::vector<mcs_keypoint> k;
+        std::vector<uint8_t> d;
+        const int mono = (*this)(image.data, image.cols, image.rows, (int)image.step, nullptr, k, d, vLappingArea);
+        if (k.empty()) _descriptors.release();
+        else {
+            _descriptors.create((int)k.size(), 32, CV_8U);
+            std::memcpy(_descriptors.getMat().data, d.data(), d.size());
+        }
+        _keypoints.resize(k.size());
+        static_assert(sizeof(cv::KeyPoint) == sizeof(mcs_keypoint), "mcs_keypoint mirrors cv::KeyPoint");
+        if (!k.empty()) std::memcpy((void*)_keypoints.data(), k.data(), k.size() * sizeof(mcs_keypoint));
+        return mono;
+    }
+#endif
+
+    int GetLevels() { return nlevels_; }
+    float GetScaleFactor() { return scaleFactor_; }
+    std::vector<float> GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    // ORBextractor::DescriptorDistance (ORBextractor.cpp:1202-1218) on two 32-byte descriptors
+    static int DescriptorDistance(const uint8_t* a, const uint8_t* b) {
+        int d = 0;
+        for (int i = 0; i < 8; i++) {
+            uint32_t x, y;
+            std::memcpy(&x, a + 4 * i, 4);
+            std::memcpy(&y, b + 4 * i, 4);
+            d += __builtin_popcount(x ^ y);
+        }
+        return d;
+    }
+
+    // mvImagePyramid[level] (ORBextractor.h:89) of the last call, w x h tightly packed
+    std::vector<uint8_t> imagePyramidLevel(int level, int* w = nullptr, int* h = nullptr) {
+        int lw = 0, lh = 0;
+        check(mcs_extractor_level_size(h_, level, &lw, &lh), "mcs_extractor_level_size");
+        std::vector<uint8_t> out((size_t)lw * lh);
+        check(mcs_extractor_download_level(h_, 0, level, 0, out.data(), lw), "mcs_extractor_download_level");
+        if (w) *w = lw;
+        if (h) *h = lh;
+        return out;
+    }
+
+    double max_neighbor_ratio = 0.85;  // ORBextractor.h:90
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+    std::vector<int> mnFeaturesPerLevel;
+    mcs_extractor* handle() { return h_; }
+
+private:
+    mcs_extractor* h_ = nullptr;
+    int nlevels_;
+    float scaleFactor_;
+};
+
+// MultiCameraFrame.h:42-57.  The reference hard-codes 5 cameras; rigs with more cameras use matchIndexN.
+struct IntraMatch {
+    std::array<int, 5> matchIndex{{-1, -1, -1, -1, -1}};
+    std::vector<int> matchIndexN;  // [num_cams] (all cameras; equals matchIndex for num_cams <= 5)
+    float uv_ref[2] = {0, 0};
+    bool mono = true;
+    int n_rays = 0;
+    std::array<uint8_t, 32> matchDesc{};  // representative descriptor (MultiCameraFrame.cpp:530-567)
+    double point3D[3] = {0, 0, 0};
+};
+
+// The extract / intra-match / triangulate entry points of MultiCameraFrame for ONE rig frame (the class also batches frames
+// through process_frames for throughput).  Image data: num_cams CV_8UC1 planes of the same size, tightly packed.
+class MultiCameraFrame {
+public:
+    MultiCameraFrame(const std::vector<mcs_calib>& calib, int width, int height, int nfeatures, float scaleFactor, int nlevels,
+                     int iniThFAST, int minThFAST, int device = 0, int max_frames = 1)
+        : num_cams_((int)calib.size()), w_(width), h_img_(height) {
+        mcs_rig_config cfg{};
+        cfg.num_cams = num_cams_; cfg.width = width; cfg.height = height; cfg.nfeatures = nfeatures; cfg.scale_factor = scaleFactor;
+        cfg.nlevels = nlevels; cfg.ini_th_fast = iniThFAST; cfg.min_th_fast = minThFAST; cfg.max_frames = max_frames; cfg.device = device;
+        h_ = mcs_rig_create(&cfg, calib.data());
+        if (!h_) throw std::runtime_error(std::string("mcs_rig_create: ") + mcs_last_error());
+        kp_cap_ = mcs_rig_feature_capacity(h_);
+        row_cap_ = mcs_rig_row_capacity(h_);
+        image_kps.resize(num_cams_); image_kps_undist.resize(num_cams_); image_descriptors.resize(num_cams_);
+    }
+    ~MultiCameraFrame() { mcs_rig_destroy(h_); }
+    MultiCameraFrame(const MultiCameraFrame&) = delete;
+    MultiCameraFrame& operator=(const MultiCameraFrame&) = delete;
+
+    // setData (MultiCameraFrame.cpp:95-152) for already-gray 8-bit images: [num_cams][h][w]
+    void setData(const uint8_t* images) { images_ = images; }
+
+    // extractFeaturesParallel() (MultiCameraFrame.cpp:203-228): fills image_kps / image_kps_undist / image_descriptors.
+    // With zero distortion image_kps_undist is a copy (:302-305); distorted rigs are out of scope.
+    void extractFeaturesParallel() {
+        if (!images_) throw std::runtime_error("extractFeaturesParallel: setData first");
+        check(mcs_rig_extract(h_, images_, 1), "mcs_rig_extract");
+        for (int c = 0; c < num_cams_; c++) {
+            image_kps[c].resize(kp_cap_);
+            image_descriptors[c].resize((size_t)kp_cap_ * 32);
+            const int n = mcs_rig_get_features(h_, 0, c, image_kps[c].data(), image_descriptors[c].data(), kp_cap_);
+            check(n, "mcs_rig_get_features");
+            image_kps[c].resize(n);
+            image_descriptors[c].resize((size_t)n * 32);
+            image_kps_undist[c] = image_kps[c];
+        }
+    }
+    void extractFeatures() { extractFeaturesParallel(); }  // :266-298, same results without the thread fan-out
+
+    // BruteForceMatch(img1_ind, img2_ind, dist_thresh, neigh_ratio, indices_1, indices_2, kps_1, kps_2) (:1024-1086)
+    void BruteForceMatch(int img1_ind, int img2_ind, float dist_thresh, float neigh_ratio, std::vector<unsigned int>& indices_1,
+                         std::vector<unsigned int>& indices_2, std::vector<mcs_keypoint>& kps_1, std::vector<mcs_keypoint>& kps_2) {
+        indices_1.resize(kp_cap_); indices_2.resize(kp_cap_); kps_1.resize(kp_cap_); kps_2.resize(kp_cap_);
+        const int n = mcs_rig_brute_force_match(h_, 0, img1_ind, img2_ind, dist_thresh, neigh_ratio, indices_1.data(), indices_2.data(),
+                                                kps_1.data(), kps_2.data(), kp_cap_);
+        check(n, "mcs_rig_brute_force_match");
+        indices_1.resize(n); indices_2.resize(n); kps_1.resize(n); kps_2.resize(n);
+    }
+
+    // computeIntraMatches(matches, old) (:1100-1288)
+    void computeIntraMatches(std::vector<IntraMatch>& matches, bool old) {
+        check(mcs_rig_compute_intra_matches(h_, 1, old ? 1 : 0, 75.f, 0.85f), "mcs_rig_compute_intra_matches");
+        std::vector<int32_t> rows((size_t)row_cap_ * num_cams_);
+        const int M = mcs_rig_get_intra_matches(h_, 0, rows.data(), row_cap_);
+        check(M, "mcs_rig_get_intra_matches");
+        matches.assign(M, IntraMatch());
+        for (int r = 0; r < M; r++) fill_row(matches[r], &rows[(size_t)r * num_cams_]);
+    }
+
+    // Triangulation block of FrontEnd::obtainLfFeatures (FrontEnd.cpp:249-370): mask filter (masks: [num_cams][h][w] f32 or null),
+    // N-view DLT, depth gate.  Returns the accepted rows in order (what the reference pushes to currentFrame->intraMatches);
+    // single-view rows (mono candidates, :371-384) are returned in `mono_rows`.
+    void triangulateIntraMatches(const float* segMasks, std::vector<IntraMatch>& accepted, std::vector<IntraMatch>* mono_rows = nullptr) {
+        check(mcs_rig_triangulate(h_, 1, segMasks), "mcs_rig_triangulate");
+        const int cap = row_cap_;
+        std::vector<int32_t> rows((size_t)cap * num_cams_), nv(cap), rep(cap);
+        std::vector<uint8_t> acc(cap);
+        std::vector<double> xyz((size_t)cap * 3);
+        std::vector<float> uv((size_t)cap * 2);
+        mcs_landmarks lm{rows.data(), acc.data(), nv.data(), xyz.data(), uv.data(), rep.data()};
+        const int M = mcs_rig_get_landmarks(h_, 0, &lm, cap);
+        check(M, "mcs_rig_get_landmarks");
+        accepted.clear();
+        if (mono_rows) mono_rows->clear();
+        for (int r = 0; r < M; r++) {
+            if (!acc[r] && !(mono_rows && nv[r] == 1)) continue;
+            IntraMatch m;
+            fill_row(m, &rows[(size_t)r * num_cams_]);
+            m.n_rays = nv[r];
+            if (rep[r] >= 0) {
+                const int f = rows[(size_t)r * num_cams_ + rep[r]];
+                std::memcpy(m.matchDesc.data(), &image_descriptors[rep[r]][(size_t)f * 32], 32);
+            }
+            if (acc[r]) {
+                m.mono = false;
+                std::memcpy(m.point3D, &xyz[(size_t)r * 3], 24);
+                m.uv_ref[0] = uv[(size_t)r * 2]; m.uv_ref[1] = uv[(size_t)r * 2 + 1];
+                accepted.push_back(m);
+            } else {
+                mono_rows->push_back(m);
+            }
+        }
+    }
+
+    // triangulateIntraMatches(x, view_inds, pt) (:411-441): x = 2 x n pixel coordinates (row 0 = u, row 1 = v)
+    void triangulateIntraMatches(const double* x_2xn, std::vector<int> view_inds, double pt[3]) {
+        const int n = (int)view_inds.size();
+        check(mcs_rig_triangulate_nview(h_, view_inds.data(), n, x_2xn, x_2xn + n, 1, pt), "mcs_rig_triangulate_nview");
+    }
+    // triangulate(kps_1, kps_2, pts3D, cam1, cam2) (:481-507): points as (x, y) float pairs
+    void triangulate(const std::vector<std::array<float, 2>>& kps_1, const std::vector<std::array<float, 2>>& kps_2,
+                     std::vector<std::array<float, 3>>& pts3D, int cam1, int cam2) {
+        pts3D.resize(kps_1.size());
+        if (kps_1.empty()) return;
+        check(mcs_rig_triangulate_pair(h_, cam1, cam2, &kps_1[0][0], &kps_2[0][0], (int)kps_1.size(), &pts3D[0][0]), "mcs_rig_triangulate_pair");
+    }
+
+    // Throughput form of FrontEnd::processFrame (FrontEnd.cpp:991-1028) for n_frames rig frames in one launch sequence.
+    void process_frames(const uint8_t* images, const float* masks, int n_frames, bool old = false) {
+        check(mcs_rig_process(h_, images, masks, n_frames, old ? 1 : 0), "mcs_rig_process");
+    }
+
+    int num_cams_;
+    std::vector<std::vector<mcs_keypoint>> image_kps, image_kps_undist;
+    std::vector<std::vector<uint8_t>> image_descriptors;  // per camera n x 32 bytes
+    mcs_rig* handle() { return h_; }
+
+private:
+    void fill_row(IntraMatch& m, const int32_t* row) const {
+        m.matchIndexN.assign(row, row + num_cams_);
+        for (int c = 0; c < 5 && c < num_cams_; c++) m.matchIndex[c] = row[c];
+    }
+    mcs_rig* h_ = nullptr;
+    int w_, h_img_, kp_cap_ = 0, row_cap_ = 0;
+    const uint8_t* images_ = nullptr;
+};
+
+}  // namespace mcs_b200
+#endif

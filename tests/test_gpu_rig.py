@@ -156,3 +156,36 @@ def test_device_resident_path_matches_host_path():
     assert np.array_equal(rig.landmarks(0)["xyz"], ref[2]["xyz"])
     assert rig.kernel_launches > 0
     B.device_free(0, dptr)
+
+
+def test_cpp_adaptor_equals_oracle(tmp_path):
+    """The C++ host adaptor (mc-slam_b200/host/mcslam_adaptor.hpp: ORBextractor::operator(), MultiCameraFrame::extractFeaturesParallel /
+    computeIntraMatches / triangulateIntraMatches) driven from a C++ program, against the oracle on the same rig frame."""
+    import subprocess
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from test_host_side import _build_adaptor
+    exe = _build_adaptor(tmp_path)
+    calib = M.synth.make_rig(3, 320, 240)
+    frame = M.synth.make_rig_frame(calib, 320, 240, frame_index=5, n_rects=6)
+    (tmp_path / "im.bin").write_bytes(frame.tobytes())
+    (tmp_path / "im.bin.calib").write_bytes(np.ascontiguousarray(calib).tobytes())
+    out = subprocess.run([exe, str(tmp_path / "im.bin"), "3", "320", "240", str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    lines = (tmp_path / "o.txt").read_text().splitlines()
+    K, D, rows, pc, tri = _oracle_frame(O, frame, calib, 400)
+    head = lines[0].split()
+    assert int(head[1]) == len(K[0]) and int(head[3]) == len(K[0]) and int(head[5]) == 8
+    kp = [l.split() for l in lines if l.startswith("kp ")]
+    assert len(kp) == len(K[0])
+    for l, k, d in zip(kp, K[0], D[0]):
+        assert np.float32(l[1]) == k["x"] and np.float32(l[2]) == k["y"] and int(l[3]) == k["octave"] and np.float32(l[4]) == k["response"]
+        assert int(l[5]) == d[0]
+    rl = [list(map(int, l.split()[1:])) for l in lines if l.startswith("row ")]
+    assert len(rl) == len(rows) and all(r == [row[0], row[1], row[2]] for r, row in zip(rl, rows))
+    lm = [l.split() for l in lines if l.startswith("lm ")]
+    acc = tri["status"] == 1
+    assert len(lm) == int(acc.sum())
+    got = np.array([[float(v) for v in l[2:5]] for l in lm])
+    assert np.allclose(got, tri["xyz"][acc], rtol=1e-6, atol=1e-9)
+    assert [int(l[1]) for l in lm] == tri["nviews"][acc].tolist()

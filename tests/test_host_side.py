@@ -77,3 +77,26 @@ def test_synth_is_deterministic():
     assert np.array_equal(a, b) and a.std() > 10
     m = M.synth.make_masks(2, 160, 120, 1)
     assert 0.05 < m.mean() < 0.6 and set(np.unique(m)) <= {0.0, 1.0}
+
+
+def _build_adaptor(tmp_path):
+    import __graft_entry__ as G
+    so = G.build()
+    exe = str(tmp_path / "t_adaptor")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-o", exe, os.path.join(ROOT, "tests", "cpp", "test_adaptor.cpp"),
+                           so, "-Wl,-rpath," + os.path.dirname(so)])
+    return exe
+
+
+def test_cpp_adaptor_compiles_and_fails_loudly_without_gpu(tmp_path):
+    """The C++17 host adaptor (reference method signatures over the C ABI) builds with g++ alone; with no CUDA device its
+    constructors throw — there is no CPU path behind it."""
+    import mcslam_b200 as M
+    exe = _build_adaptor(tmp_path)
+    if M.lib().mcs_device_count() > 0:
+        pytest.skip("a GPU is present")
+    img = tmp_path / "im.bin"
+    img.write_bytes(bytes(16 * 16))
+    (tmp_path / "im.bin.calib").write_bytes(bytes(26 * 8))
+    out = subprocess.run([exe, str(img), "1", "16", "16", str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 3 and "no CUDA device" in out.stderr
