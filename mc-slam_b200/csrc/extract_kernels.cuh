@@ -79,6 +79,52 @@ __global__ void __launch_bounds__(256) resize_level_kernel(const __grid_constant
     *reinterpret_cast<uint32_t*>(dst + (size_t)dy * D.pitch + dx0) = outw;  // pitch % 64 == 0: row padding absorbs the tail
 }
 
+// Word-load variant used when the level-to-level scale is <= 2 (the 4 output pixels of a thread then read at most 12 consecutive
+// source bytes per row): 3 aligned 32-bit loads per source row instead of 8 byte loads, the 2-tap horizontal filter as one DP2A
+// (coefficients a0 | a1 << 16 from the table, pixels b0 | b1 << 8 cut out with a funnel shift).  Same arithmetic as above.
+__global__ void __launch_bounds__(256) resize_level_words_kernel(const __grid_constant__ McsPlan P, ImageSet S, int level,
+                                                                 const int2* __restrict__ xtab, const int2* __restrict__ ytab) {
+    const McsLevel& D = P.L[level];
+    const McsLevel& Sv = P.L[level - 1];
+    const int img = blockIdx.z;
+    const int dy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int dx0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (dy >= D.h || dx0 >= D.w) return;
+    int spitch;
+    const uint8_t* src = level_ptr(P, S, img, level - 1, spitch);
+    uint8_t* dst = S.pyr + (size_t)img * P.pyr_stride + D.plane_ofs;
+    const int2 yt = __ldg(&ytab[D.ytab_ofs + dy]);
+    const int sh = Sv.h, sw = Sv.w;
+    int sy0 = yt.x, sy1 = yt.x + 1;
+    sy0 = sy0 < 0 ? 0 : (sy0 < sh ? sy0 : sh - 1);
+    sy1 = sy1 < 0 ? 0 : (sy1 < sh ? sy1 : sh - 1);
+    const int b0 = (short)(yt.y & 0xFFFF), b1 = yt.y >> 16;
+    const uint32_t* r0 = reinterpret_cast<const uint32_t*>(src + (size_t)sy0 * spitch);
+    const uint32_t* r1 = reinterpret_cast<const uint32_t*>(src + (size_t)sy1 * spitch);
+    int2 xt[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) xt[k] = __ldg(&xtab[D.xtab_ofs + min(dx0 + k, D.w - 1)]);
+    const int lastw = ((sw + 3) >> 2) - 1;
+    const int wi = xt[0].x >> 2, wi1 = min(wi + 1, lastw), wi2 = min(wi + 2, lastw);
+    const uint32_t u0 = __ldg(r0 + wi), u1 = __ldg(r0 + wi1), u2 = __ldg(r0 + wi2);
+    const uint32_t v0 = __ldg(r1 + wi), v1 = __ldg(r1 + wi1), v2 = __ldg(r1 + wi2);
+    uint32_t outw = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int o = xt[k].x - 4 * wi;  // 0 .. 10 for scale <= 2; bytes o, o+1 (o+1 beyond the row end only ever meets coefficient 0)
+        const int wsel = o >> 2;         // word holding byte o
+        const int sft = (o & 3) * 8;
+        const uint32_t pu = __funnelshift_r(wsel == 0 ? u0 : (wsel == 1 ? u1 : u2), wsel == 0 ? u1 : u2, sft);
+        const uint32_t pv = __funnelshift_r(wsel == 0 ? v0 : (wsel == 1 ? v1 : v2), wsel == 0 ? v1 : v2, sft);
+        const int h0 = (int)__dp2a_lo((unsigned)xt[k].y, pu, 0u);
+        const int h1 = (int)__dp2a_lo((unsigned)xt[k].y, pv, 0u);
+        int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+        v = min(max(v, 0), 255);
+        outw |= (uint32_t)v << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(dst + (size_t)dy * D.pitch + dx0) = outw;  // pitch % 64 == 0: row padding absorbs the tail
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // K2  cv::GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) on 8U: 8.8 fixed-point kernel {18,34,48,56,48,34,18}/256,
 // exact integer accumulation, one rounding (v + 32768) >> 16.  Tile 64x16 + 3 px halo staged in shared memory,
@@ -86,10 +132,14 @@ __global__ void __launch_bounds__(256) resize_level_kernel(const __grid_constant
 // ------------------------------------------------------------------------------------------------------------
 __constant__ int c_gauss7[7];  // set by the host from the bit-exact kernel generator
 
+// Tile 128 x 32 outputs (+3 px halo) per block.  Pass H: 7-tap row filter as two DP4A per pixel on byte windows cut out of the
+// staged 32-bit words with funnel shifts; results (<= 65280, u16) are stored as vertical pairs (row 2p | row 2p+1 << 16).  Pass V:
+// 7-tap column filter as four DP2A per pixel on those pairs; one thread makes 4 x 2 pixels and stores two 32-bit words.
 __global__ void __launch_bounds__(256) blur_kernel(const __grid_constant__ McsPlan P, ImageSet S, uint8_t* __restrict__ blurred) {
-    constexpr int TW = MCS_BLUR_TW, TH = MCS_BLUR_TH, SW = TW + 6, SH = TH + 6;
-    __shared__ uint8_t s_in[SH][SW + 2];
-    __shared__ uint16_t s_h[SH][TW];
+    constexpr int TW = MCS_BLUR_TW, TH = MCS_BLUR_TH, NWI = TW / 4 + 2, RI = TH + 6, NP = RI / 2;
+    static_assert(TW == 128 && TH == 32, "tile geometry is baked into the index math");
+    __shared__ uint32_t s_in[RI][NWI];          // input words: column 0 = pixels x0-4 .. x0-1
+    __shared__ __align__(16) uint32_t s_pair[NP][TW];  // H-filtered rows as vertical pairs
     const int img = blockIdx.y;
     int level = 0;
 #pragma unroll 1
@@ -97,38 +147,71 @@ __global__ void __launch_bounds__(256) blur_kernel(const __grid_constant__ McsPl
         if ((int)blockIdx.x >= P.L[l].tile_base) level = l;
     const McsLevel& Lv = P.L[level];
     const int t = blockIdx.x - Lv.tile_base;
-    const int tx = (t % Lv.tiles_x) * TW, ty = (t / Lv.tiles_x) * TH;
+    const int x0 = (t % Lv.tiles_x) * TW, y0 = (t / Lv.tiles_x) * TH;
     int pitch;
     const uint8_t* src = level_ptr(P, S, img, level, pitch);
     const int w = Lv.w, h = Lv.h;
-    for (int i = threadIdx.x; i < SW * SH; i += blockDim.x) {
-        const int r = i / SW, c = i - r * SW;
-        const int gy = reflect101(ty + r - 3, h), gx = reflect101(tx + c - 3, w);
-        s_in[r][c] = src[(size_t)gy * pitch + gx];
+    for (int i = threadIdx.x; i < RI * NWI; i += 256) {
+        const int r = i / NWI, c = i - r * NWI;
+        const int gy = reflect101(y0 + r - 3, h), gx = x0 - 4 + 4 * c;
+        const uint8_t* row = src + (size_t)gy * pitch;
+        uint32_t v;
+        if (gx >= 0 && gx + 3 < w) {
+            v = __ldg(reinterpret_cast<const uint32_t*>(row + gx));
+        } else {  // words touching the left/right border: BORDER_REFLECT_101 per byte
+            v = (uint32_t)row[reflect101(gx, w)] | ((uint32_t)row[reflect101(gx + 1, w)] << 8) |
+                ((uint32_t)row[reflect101(gx + 2, w)] << 16) | ((uint32_t)row[reflect101(gx + 3, w)] << 24);
+        }
+        s_in[r][c] = v;
     }
     __syncthreads();
-    const int k0 = c_gauss7[0], k1 = c_gauss7[1], k2 = c_gauss7[2], k3 = c_gauss7[3];
-    for (int i = threadIdx.x; i < TW * SH; i += blockDim.x) {
-        const int r = i / TW, c = i - r * TW;
-        const uint8_t* p = &s_in[r][c];
-        s_h[r][c] = (uint16_t)(k0 * (p[0] + p[6]) + k1 * (p[1] + p[5]) + k2 * (p[2] + p[4]) + k3 * p[3]);
+    const uint32_t wA = (uint32_t)c_gauss7[0] | ((uint32_t)c_gauss7[1] << 8) | ((uint32_t)c_gauss7[2] << 16) | ((uint32_t)c_gauss7[3] << 24);
+    const uint32_t wB = (uint32_t)c_gauss7[4] | ((uint32_t)c_gauss7[5] << 8) | ((uint32_t)c_gauss7[6] << 16);
+    // pass H: item = (row pair p, word g) -> 4 pixels x 2 rows
+    for (int i = threadIdx.x; i < NP * (TW / 4); i += 256) {
+        const int p = i >> 5, g = i & 31;
+        uint32_t hv[2][4];
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+            const uint32_t W0 = s_in[2 * p + rr][g], W1 = s_in[2 * p + rr][g + 1], W2 = s_in[2 * p + rr][g + 2];
+            // pixel e of the word needs bytes (4g + e + 1) .. (4g + e + 7) of the staged row
+            hv[rr][0] = __dp4a(__funnelshift_r(W1, W2, 8), wB, __dp4a(__funnelshift_r(W0, W1, 8), wA, 0u));
+            hv[rr][1] = __dp4a(__funnelshift_r(W1, W2, 16), wB, __dp4a(__funnelshift_r(W0, W1, 16), wA, 0u));
+            hv[rr][2] = __dp4a(__funnelshift_r(W1, W2, 24), wB, __dp4a(__funnelshift_r(W0, W1, 24), wA, 0u));
+            hv[rr][3] = __dp4a(W2, wB, __dp4a(W1, wA, 0u));
+        }
+        uint4 o;
+        o.x = hv[0][0] | (hv[1][0] << 16);
+        o.y = hv[0][1] | (hv[1][1] << 16);
+        o.z = hv[0][2] | (hv[1][2] << 16);
+        o.w = hv[0][3] | (hv[1][3] << 16);
+        *reinterpret_cast<uint4*>(&s_pair[p][4 * g]) = o;
     }
     __syncthreads();
+    const uint32_t k0 = c_gauss7[0], k1 = c_gauss7[1], k2 = c_gauss7[2], k3 = c_gauss7[3], k4 = c_gauss7[4], k5 = c_gauss7[5], k6 = c_gauss7[6];
+    const uint32_t e0 = k0 | (k1 << 8), e1 = k2 | (k3 << 8), e2 = k4 | (k5 << 8), e3 = k6;               // even output row 2q
+    const uint32_t o0 = k0 << 8, o1 = k1 | (k2 << 8), o2 = k3 | (k4 << 8), o3 = k5 | (k6 << 8);          // odd output row 2q+1
     uint8_t* dst = blurred + (size_t)img * P.pyr_stride + Lv.plane_ofs;
-    // 4 pixels per thread -> one 32-bit store; TW*TH/4 = 256 threads
-    for (int i = threadIdx.x; i < (TW / 4) * TH; i += blockDim.x) {
-        const int r = i / (TW / 4), c4 = (i - r * (TW / 4)) * 4;
-        const int gy = ty + r, gx = tx + c4;
-        if (gy >= h || gx >= w) continue;
-        uint32_t outw = 0;
+    // pass V: item = (output row pair q, word g)
+    for (int i = threadIdx.x; i < (TH / 2) * (TW / 4); i += 256) {
+        const int q = i >> 5, g = i & 31;
+        const int gx = x0 + 4 * g, gy = y0 + 2 * q;
+        if (gx >= w || gy >= h) continue;
+        const uint4 a = *reinterpret_cast<const uint4*>(&s_pair[q][4 * g]);
+        const uint4 b = *reinterpret_cast<const uint4*>(&s_pair[q + 1][4 * g]);
+        const uint4 c = *reinterpret_cast<const uint4*>(&s_pair[q + 2][4 * g]);
+        const uint4 d = *reinterpret_cast<const uint4*>(&s_pair[q + 3][4 * g]);
+        const uint32_t pa[4] = {a.x, a.y, a.z, a.w}, pb[4] = {b.x, b.y, b.z, b.w}, pc[4] = {c.x, c.y, c.z, c.w}, pd[4] = {d.x, d.y, d.z, d.w};
+        uint32_t oe = 0, oo = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const int c = c4 + k;
-            const uint32_t a = (uint32_t)k0 * (s_h[r][c] + s_h[r + 6][c]) + (uint32_t)k1 * (s_h[r + 1][c] + s_h[r + 5][c]) +
-                               (uint32_t)k2 * (s_h[r + 2][c] + s_h[r + 4][c]) + (uint32_t)k3 * s_h[r + 3][c];
-            outw |= min((a + 32768u) >> 16, 255u) << (8 * k);
+            const uint32_t ve = __dp2a_lo(pd[k], e3, __dp2a_lo(pc[k], e2, __dp2a_lo(pb[k], e1, __dp2a_lo(pa[k], e0, 32768u))));
+            const uint32_t vo = __dp2a_lo(pd[k], o3, __dp2a_lo(pc[k], o2, __dp2a_lo(pb[k], o1, __dp2a_lo(pa[k], o0, 32768u))));
+            oe |= (ve >> 16) << (8 * k);
+            oo |= (vo >> 16) << (8 * k);
         }
-        *reinterpret_cast<uint32_t*>(dst + (size_t)gy * Lv.pitch + gx) = outw;  // pitch % 64 == 0 and gx % 4 == 0
+        *reinterpret_cast<uint32_t*>(dst + (size_t)gy * Lv.pitch + gx) = oe;  // pitch % 64 == 0 and gx % 4 == 0
+        if (gy + 1 < h) *reinterpret_cast<uint32_t*>(dst + (size_t)(gy + 1) * Lv.pitch + gx) = oo;
     }
 }
 
@@ -185,12 +268,42 @@ __device__ __forceinline__ int fast_strength(const uint8_t* c, int tp) {
     return max(dark, bright) - 1;
 }
 
+// One polarity only (sgn = +1: ring brighter than the centre, -1: darker): max over the 16 arcs of min over the arc of
+// sgn * (ring - v), minus 1.  Ring pixels are packed as ANTIPODAL pairs P_k = (e_k, e_{k+8}), e = 256 + sgn * (ring - v), so that
+// "next ring position" is the next word and wrapping past position 7 is a half-word swap: 8 swaps instead of 24 byte permutes.
+__device__ __forceinline__ int fast_strength_pol(const uint8_t* c, int tp, int sgn) {
+    const int v = c[0];
+    const uint32_t base = (uint32_t)(256 - sgn * v) * 0x00010001u;
+    uint32_t Pk[10];
+    Pk[0] = base + (uint32_t)sgn * ((uint32_t)c[3 * tp] | ((uint32_t)c[-3 * tp] << 16));           // ( 0, 3) | ( 0,-3)
+    Pk[1] = base + (uint32_t)sgn * ((uint32_t)c[3 * tp + 1] | ((uint32_t)c[-3 * tp - 1] << 16));   // ( 1, 3) | (-1,-3)
+    Pk[2] = base + (uint32_t)sgn * ((uint32_t)c[2 * tp + 2] | ((uint32_t)c[-2 * tp - 2] << 16));   // ( 2, 2) | (-2,-2)
+    Pk[3] = base + (uint32_t)sgn * ((uint32_t)c[tp + 3] | ((uint32_t)c[-tp - 3] << 16));           // ( 3, 1) | (-3,-1)
+    Pk[4] = base + (uint32_t)sgn * ((uint32_t)c[3] | ((uint32_t)c[-3] << 16));                     // ( 3, 0) | (-3, 0)
+    Pk[5] = base + (uint32_t)sgn * ((uint32_t)c[-tp + 3] | ((uint32_t)c[tp - 3] << 16));           // ( 3,-1) | (-3, 1)
+    Pk[6] = base + (uint32_t)sgn * ((uint32_t)c[-2 * tp + 2] | ((uint32_t)c[2 * tp - 2] << 16));   // ( 2,-2) | (-2, 2)
+    Pk[7] = base + (uint32_t)sgn * ((uint32_t)c[-3 * tp + 1] | ((uint32_t)c[3 * tp - 1] << 16));   // ( 1,-3) | (-1, 3)
+    Pk[8] = __byte_perm(Pk[0], 0, 0x1032);
+    Pk[9] = __byte_perm(Pk[1], 0, 0x1032);
+    uint32_t Q[14];
+#pragma unroll
+    for (int k = 0; k < 8; k++) Q[k] = __vimin3_u16x2(Pk[k], Pk[k + 1], Pk[k + 2]);  // min of 3 consecutive ring positions
+#pragma unroll
+    for (int k = 0; k < 6; k++) Q[8 + k] = __byte_perm(Q[k], 0, 0x1032);
+    uint32_t R[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) R[k] = __vimin3_u16x2(Q[k], Q[k + 3], Q[k + 6]);     // min of 9 consecutive ring positions
+    const uint32_t m = __vimax3_u16x2(__vimax3_u16x2(R[0], R[1], R[2]), __vimax3_u16x2(R[3], R[4], R[5]), __vmaxu2(R[6], R[7]));
+    return (int)max(m & 0xFFFFu, m >> 16) - 257;
+}
+
 __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                  uint32_t* __restrict__ cand, int* __restrict__ cand_count) {
     __shared__ __align__(16) uint8_t s_tile[MCS_FAST_MAXC * MCS_FAST_TP];
-    __shared__ uint8_t s_score[(MCS_FAST_MAXC - 4) * MCS_FAST_SP];
+    __shared__ __align__(16) uint8_t s_score[(MCS_FAST_MAXC - 4) * MCS_FAST_SP];
+    __shared__ uint16_t s_queue[(MCS_FAST_MAXC - 6) * (MCS_FAST_MAXC - 6)];  // pixels that pass the pre-test: polarity flags (bit 14 bright, 15 dark) | ly << 7 | lx
     __shared__ uint32_t s_surv[MCS_FAST_MAXSURV];
-    __shared__ int s_nsurv, s_cellmax;
+    __shared__ int s_nq, s_nsurv;
     const int img = blockIdx.y;
     int level = 0;
 #pragma unroll 1
@@ -205,8 +318,8 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
     const int maxX = min(iniX + Lv.w_cell + 6, maxBX), maxY = min(iniY + Lv.h_cell + 6, maxBY);
     const int cw = maxX - iniX, ch = maxY - iniY;  // sub-image handed to cv::FAST
     const int iw = cw - 6, ih = ch - 6;            // computed interior
-    if (threadIdx.x == 0) { s_nsurv = 0; s_cellmax = 0; }
     if (iw <= 0 || ih <= 0) return;
+    const int lane = threadIdx.x & 31;
     int pitch;
     const uint8_t* src = level_ptr(P, S, img, level, pitch);
     // stage the sub-image with aligned 32-bit loads
@@ -216,55 +329,84 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
         const uint32_t wv = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * pitch + a0) + c);
         *reinterpret_cast<uint32_t*>(&s_tile[r * MCS_FAST_TP + c * 4]) = wv;
     }
-    // zero score tile incl. 1 px frame: (iw + 2) x (ih + 2)
-    for (int t = threadIdx.x; t < (ih + 2) * MCS_FAST_SP; t += MCS_FAST_NT) s_score[t] = 0;
-    __syncthreads();
-    const int th = min(P.min_th, P.ini_th);  // weakest threshold any of the two FAST calls can use
-    for (int t = threadIdx.x; t < iw * ih; t += MCS_FAST_NT) {
-        const int ly = t / iw, lx = t - ly * iw;
-        const uint8_t* c = &s_tile[(ly + 3) * MCS_FAST_TP + lx + 3 + off];
-        const int v = c[0];
-        // necessary condition for a 9-arc: of each opposite ring pair at least one pixel is on the arc
-        const int p0 = c[3 * MCS_FAST_TP], p8 = c[-3 * MCS_FAST_TP], p4 = c[3], p12 = c[-3];
-        const int hi = v + th, lo = v - th;
-        const bool brightOK = (p0 > hi || p8 > hi) && (p4 > hi || p12 > hi);
-        const bool darkOK = (p0 < lo || p8 < lo) && (p4 < lo || p12 < lo);
-        if (brightOK || darkOK) {
-            const int s = fast_strength(c, MCS_FAST_TP);
-            if (s >= th && s > 0) s_score[(ly + 1) * MCS_FAST_SP + lx + 1] = (uint8_t)min(s, 255);
-        }
-    }
-    __syncthreads();
-    for (int t = threadIdx.x; t < iw * ih; t += MCS_FAST_NT) {
-        const int ly = t / iw, lx = t - ly * iw;
-        const uint8_t* q = &s_score[(ly + 1) * MCS_FAST_SP + lx + 1];
-        const int s = q[0];
-        if (s == 0) continue;
-        if (s > q[-1] && s > q[1] && s > q[-MCS_FAST_SP - 1] && s > q[-MCS_FAST_SP] && s > q[-MCS_FAST_SP + 1] &&
-            s > q[MCS_FAST_SP - 1] && s > q[MCS_FAST_SP] && s > q[MCS_FAST_SP + 1]) {
-            const int slot = atomicAdd(&s_nsurv, 1);
-            // keypoint in ROI coordinates: FAST x in the sub-image (lx + 3) shifted by j*wCell (:864-865)
-            if (slot < MCS_FAST_MAXSURV) s_surv[slot] = mcs_oct::pack_cand(lx + 3 + j * Lv.w_cell, ly + 3 + i * Lv.h_cell, s);
-            atomicMax(&s_cellmax, s);
-        }
-    }
-    __syncthreads();
-    const int ns = min(s_nsurv, MCS_FAST_MAXSURV);
-    const int keep_th = s_cellmax >= P.ini_th ? P.ini_th : P.min_th;  // FAST(iniTh) non-empty ? keep it : FAST(minTh)
+    const int npx = iw * ih;
+    const uint32_t magic = ((1u << 20) + iw - 1) / iw;  // t / iw == (t * magic) >> 20 for t < 76 * 76 (checked exhaustively)
+    const int npx_pad = (npx + MCS_FAST_NT - 1) / MCS_FAST_NT * MCS_FAST_NT;
     uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
     int* cnt = cand_count + img * P.nlevels + level;
-    for (int base = 0; base < ns; base += MCS_FAST_NT) {
-        const int t = base + threadIdx.x;
-        const uint32_t rec = t < ns ? s_surv[t] : 0;
-        const bool keep = t < ns && mcs_oct::cand_score(rec) >= keep_th;
-        const unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
-        if (m) {
-            const int lane = threadIdx.x & 31;
-            int pos = 0;
-            if (lane == 0) pos = atomicAdd(cnt, __popc(m));
-            pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(m & ((1u << lane) - 1));
-            if (keep && pos < Lv.cand_cap) out[pos] = rec;
+    // FAST(cell, iniThFAST); only if that finds nothing, FAST(cell, minThFAST)  (:825, :842-845)
+#pragma unroll 1
+    for (int phase = 0; phase < 2; phase++) {
+        const int th = phase == 0 ? P.ini_th : P.min_th;
+        if (threadIdx.x == 0) { s_nq = 0; s_nsurv = 0; }
+        // zero score tile incl. 1 px frame: (iw + 2) x (ih + 2)
+        for (int t = threadIdx.x; t < (ih + 2) * (MCS_FAST_SP / 4); t += MCS_FAST_NT) reinterpret_cast<uint32_t*>(s_score)[t] = 0;
+        __syncthreads();
+        // pass 1, every interior pixel: necessary condition for a 9-arc — of each opposite ring pair at least one pixel is on
+        // the arc (tested on the two axis pairs); survivors are queued so pass 2 runs on dense warps
+        for (int t = threadIdx.x; t < npx_pad; t += MCS_FAST_NT) {
+            bool pass = false;
+            int ly = 0, lx = 0, pol = 0;
+            if (t < npx) {
+                ly = (int)(((uint32_t)t * magic) >> 20);
+                lx = t - ly * iw;
+                const uint8_t* c = &s_tile[(ly + 3) * MCS_FAST_TP + lx + 3 + off];
+                const int v = c[0];
+                const int p0 = c[3 * MCS_FAST_TP], p8 = c[-3 * MCS_FAST_TP], p4 = c[3], p12 = c[-3];
+                const int hi = v + th, lo = v - th;
+                pol = (((p0 > hi || p8 > hi) && (p4 > hi || p12 > hi)) ? 0x4000 : 0) | (((p0 < lo || p8 < lo) && (p4 < lo || p12 < lo)) ? 0x8000 : 0);
+                pass = pol != 0;
+            }
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
+            if (m) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&s_nq, __popc(m));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (pass) s_queue[base + __popc(m & ((1u << lane) - 1))] = (uint16_t)(pol | (ly << 7) | lx);
+            }
         }
+        __syncthreads();
+        // pass 2, queued pixels: arc strength = cv::FAST's score; a corner at th  <=>  strength >= th
+        const int nq = s_nq;
+        for (int q = threadIdx.x; q < nq; q += MCS_FAST_NT) {
+            const int e = s_queue[q], ly = (e >> 7) & 0x7F, lx = e & 0x7F;
+            const uint8_t* c = &s_tile[(ly + 3) * MCS_FAST_TP + lx + 3 + off];
+            int sc = fast_strength_pol(c, MCS_FAST_TP, (e & 0x4000) ? 1 : -1);
+            if ((e & 0xC000) == 0xC000) sc = max(sc, fast_strength_pol(c, MCS_FAST_TP, -1));  // rare: both pre-tests passed
+            if (sc >= th && sc > 0) s_score[(ly + 1) * MCS_FAST_SP + lx + 1] = (uint8_t)min(sc, 255);
+        }
+        __syncthreads();
+        // pass 3, corners only: strict-'>' 8-neighbour NMS inside the computed interior (scores outside count as 0)
+        for (int q = threadIdx.x; q < nq; q += MCS_FAST_NT) {
+            const int e = s_queue[q], ly = (e >> 7) & 0x7F, lx = e & 0x7F;
+            const uint8_t* qp = &s_score[(ly + 1) * MCS_FAST_SP + lx + 1];
+            const int sc = qp[0];
+            if (sc == 0) continue;
+            if (sc > qp[-1] && sc > qp[1] && sc > qp[-MCS_FAST_SP - 1] && sc > qp[-MCS_FAST_SP] && sc > qp[-MCS_FAST_SP + 1] &&
+                sc > qp[MCS_FAST_SP - 1] && sc > qp[MCS_FAST_SP] && sc > qp[MCS_FAST_SP + 1]) {
+                const int slot = atomicAdd(&s_nsurv, 1);
+                // keypoint in ROI coordinates: FAST x in the sub-image (lx + 3) shifted by j*wCell (:864-865)
+                if (slot < MCS_FAST_MAXSURV) s_surv[slot] = mcs_oct::pack_cand(lx + 3 + j * Lv.w_cell, ly + 3 + i * Lv.h_cell, sc);
+            }
+        }
+        __syncthreads();
+        const int ns = min(s_nsurv, MCS_FAST_MAXSURV);
+        if (ns > 0) {
+            for (int base = 0; base < ns; base += MCS_FAST_NT) {
+                const int t = base + threadIdx.x;
+                const bool keep = t < ns;
+                const unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
+                if (m) {
+                    int pos = 0;
+                    if (lane == 0) pos = atomicAdd(cnt, __popc(m));
+                    pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(m & ((1u << lane) - 1));
+                    if (keep && pos < Lv.cand_cap) out[pos] = s_surv[t];
+                }
+            }
+            return;  // block-uniform
+        }
+        if (P.min_th >= P.ini_th) return;  // the retry could only find a subset of nothing
+        __syncthreads();
     }
 }
 
@@ -365,7 +507,9 @@ __global__ void __launch_bounds__(MCS_OCT_NT) octree_kernel(const __grid_constan
 // vLappingArea = {0,0}: every keypoint is "mono", written front to back).  A non-trivial lapping area is applied by
 // lapping_permute_kernel afterwards.
 // ------------------------------------------------------------------------------------------------------------
-__constant__ signed char c_pattern[1024];  // 512 (x, y) pairs, see include/mcs_orb_pattern.inc
+// 512 (x, y) pairs, see include/mcs_orb_pattern.inc.  Global (L1-cached), not __constant__: every lane reads a different
+// 32-byte slice, which the constant cache would serialise 32 ways.
+__device__ __align__(16) signed char g_pattern[1024];
 
 struct KeypointPod {
     float x, y, size, angle, response;
@@ -447,12 +591,17 @@ __global__ void __launch_bounds__(MCS_DESC_WARPS * 32) describe_kernel(const __g
     const uint8_t* bl = blurred + (size_t)img * P.pyr_stride + Lv.plane_ofs + (size_t)py * Lv.pitch + px;
     const int bp = Lv.pitch;
     int val = 0;
-    const signed char* pat = c_pattern + lane * 32;  // 16 points = 8 tests = 1 descriptor byte per lane
+    // 16 points = 8 tests = 1 descriptor byte per lane; test t = bytes (x0, y0, x1, y1) of word t
+    const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + lane * 2);
+    const uint4 pw1 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + lane * 2 + 1);
+    const uint32_t pw[8] = {pw0.x, pw0.y, pw0.z, pw0.w, pw1.x, pw1.y, pw1.z, pw1.w};
     if (!P.use_angle) {
 #pragma unroll
         for (int t = 0; t < 8; t++) {
-            const int t0 = bl[pat[4 * t + 1] * bp + pat[4 * t]];
-            const int t1 = bl[pat[4 * t + 3] * bp + pat[4 * t + 2]];
+            const int x0 = (int)(signed char)(pw[t]), y0 = (int)(signed char)(pw[t] >> 8);
+            const int x1 = (int)(signed char)(pw[t] >> 16), y1 = (int)(signed char)(pw[t] >> 24);
+            const int t0 = bl[y0 * bp + x0];
+            const int t1 = bl[y1 * bp + x1];
             val |= (t0 < t1) << t;
         }
     } else {
@@ -460,7 +609,8 @@ __global__ void __launch_bounds__(MCS_DESC_WARPS * 32) describe_kernel(const __g
         const float a = (float)cos((double)ang), b = (float)sin((double)ang);
 #pragma unroll
         for (int t = 0; t < 8; t++) {
-            const float x0 = pat[4 * t], y0 = pat[4 * t + 1], x1 = pat[4 * t + 2], y1 = pat[4 * t + 3];
+            const float x0 = (float)(signed char)(pw[t]), y0 = (float)(signed char)(pw[t] >> 8);
+            const float x1 = (float)(signed char)(pw[t] >> 16), y1 = (float)(signed char)(pw[t] >> 24);
             ry0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
             rx0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
             ry1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));

@@ -54,8 +54,15 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
 #pragma unroll 4
             for (int j = 0; j < m; j++) {
                 const uint4 ta = s_train[2 * j], tb = s_train[2 * j + 1];
-                const int d = __popc(qa.x ^ ta.x) + __popc(qa.y ^ ta.y) + __popc(qa.z ^ ta.z) + __popc(qa.w ^ ta.w) +
-                              __popc(qb.x ^ tb.x) + __popc(qb.y ^ tb.y) + __popc(qb.z ^ tb.z) + __popc(qb.w ^ tb.w);
+                // POPC issues at a quarter of the LOP3 rate, so the 8 XOR words go through a carry-save adder tree first
+                // (ones / twos / fours bit-planes): 4 POPC instead of 8.
+                const uint32_t x0 = qa.x ^ ta.x, x1 = qa.y ^ ta.y, x2 = qa.z ^ ta.z, x3 = qa.w ^ ta.w;
+                const uint32_t x4 = qb.x ^ tb.x, x5 = qb.y ^ tb.y, x6 = qb.z ^ tb.z, x7 = qb.w ^ tb.w;
+                const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 ^ x1));
+                const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 ^ x4));
+                const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 ^ s2));
+                const uint32_t t1 = c1 ^ c2 ^ c3, f1 = (c1 & c2) | (c3 & (c1 ^ c2));
+                const int d = __popc(s3) + __popc(x7) + 2 * __popc(t1) + 4 * __popc(f1);
                 if (d < d0) {  // strict '<': on ties the lower train index stays first, as knnMatch orders them
                     d1 = d0;
                     d0 = d;
@@ -86,27 +93,48 @@ __global__ void __launch_bounds__(128) merge_kernel(int num_cams, int kp_cap, in
                                                     const int* __restrict__ kp_count, const int* __restrict__ match_train,
                                                     const KeypointPod* __restrict__ kps, int use_epipolar,
                                                     const double* __restrict__ Fmat, const float* __restrict__ sigma2,
-                                                    int* __restrict__ rows, int* __restrict__ row_count) {
-    extern __shared__ __align__(16) uint16_t s_inv[];  // [num_cams][kp_cap]
+                                                    int* __restrict__ rows, int* __restrict__ row_count, int rows_in_smem) {
+    // dynamic shared: [num_cams][kp_cap] u16 match_inv_idx | [kp_cap] u32 compacted matches (fi | fj << 16) | optional row table
+    extern __shared__ __align__(16) uint16_t s_inv[];
+    __shared__ int s_nm, s_M;
     const int frame = blockIdx.x;
-    int* R = rows + (size_t)frame * row_cap * num_cams;
+    const int inv_elems = (num_cams * kp_cap + 1) & ~1;
+    uint32_t* s_list = reinterpret_cast<uint32_t*>(s_inv + inv_elems);
+    int* G = rows + (size_t)frame * row_cap * num_cams;
+    int* R = rows_in_smem ? reinterpret_cast<int*>(s_list + kp_cap) : G;
     for (int t = threadIdx.x; t < num_cams * kp_cap; t += blockDim.x) s_inv[t] = 0xFFFFu;
-    __syncthreads();
-    if (threadIdx.x != 0) return;
-    int M = 0;
+    if (threadIdx.x == 0) s_M = 0;
+    const int lane = threadIdx.x & 31;
     for (int p = 0; p < pairs.n_pairs; p++) {
         const int i = pairs.a[p], j = pairs.b[p];
         const int nq = kp_count[frame * num_cams + i];
         const int* mt = match_train + ((size_t)frame * pairs.n_pairs + p) * kp_cap;
+        __syncthreads();
+        if (threadIdx.x == 0) s_nm = 0;
+        __syncthreads();
+        // order-preserving compaction of the accepted matches of this pair (query order, :1060-1076); one warp keeps it simple
+        if (threadIdx.x < 32) {
+            int base = 0;
+            for (int q0 = 0; q0 < nq; q0 += 32) {
+                const int q = q0 + lane;
+                const int fj = q < nq ? __ldg(&mt[q]) : -1;
+                const unsigned m = __ballot_sync(0xFFFFFFFFu, fj >= 0);
+                if (fj >= 0) s_list[base + __popc(m & ((1u << lane) - 1))] = (uint32_t)q | ((uint32_t)fj << 16);
+                base += __popc(m);
+            }
+            if (lane == 0) s_nm = base;
+        }
+        __syncthreads();
+        if (threadIdx.x != 0) continue;
+        // the reference mutates match_inv_idx while it walks: later matches (and later pairs) see earlier state => sequential
+        const int nm = s_nm;
+        int M = s_M;
         const double* F = Fmat + p * 9;
         uint16_t* invi = s_inv + i * kp_cap;
         uint16_t* invj = s_inv + j * kp_cap;
-        int nxt = nq > 0 ? mt[0] : -1;
-        for (int q = 0; q < nq; q++) {
-            const int fj = nxt;
-            if (q + 1 < nq) nxt = mt[q + 1];  // prefetch: the walk is latency-bound
-            if (fj < 0) continue;
-            const int fi = q;
+        for (int e = 0; e < nm; e++) {
+            const uint32_t pr = s_list[e];
+            const int fi = (int)(pr & 0xFFFFu), fj = (int)(pr >> 16);
             if (use_epipolar) {
                 // :1177-1205 — products in f64 (no FMA contraction), narrowed to f32 exactly where the reference does
                 const KeypointPod p1 = kps[(size_t)(frame * num_cams + i) * kp_cap + fi];
@@ -152,8 +180,15 @@ __global__ void __launch_bounds__(128) merge_kernel(int num_cams, int kp_cap, in
                 invj[fj] = (uint16_t)mi;
             }
         }
+        s_M = M;
     }
-    row_count[frame] = M;
+    __syncthreads();
+    const int M = s_M;
+    if (threadIdx.x == 0) row_count[frame] = M;
+    if (rows_in_smem) {
+        const int n = min(M, row_cap) * num_cams;
+        for (int t = threadIdx.x; t < n; t += blockDim.x) G[t] = R[t];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -220,40 +255,109 @@ __device__ __forceinline__ int hamming256(const uint8_t* a, const uint8_t* b) {
            __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// Same algorithm and operation order as null_vector (so results stay bit-identical to the oracle's f64 Jacobi), with compile-time
+// sizes: exact-size arrays keep the per-thread footprint small (L1-resident), and for the small systems (UNROLL) the pair loops are
+// unrolled so A and V live in registers.
+template <typename T, int M, int N, bool UNROLL>
+__device__ __forceinline__ void null_vector_fixed(T (&A)[M * N], T* z, T eps) {
+    T V[N * N];
+#pragma unroll
+    for (int i = 0; i < N * N; i++) V[i] = 0;
+#pragma unroll
+    for (int i = 0; i < N; i++) V[i * N + i] = 1;
+#pragma unroll 1
+    for (int sweep = 0; sweep < 60; sweep++) {
+        bool changed = false;
+#pragma unroll(UNROLL ? N : 1)
+        for (int p = 0; p < N - 1; p++) {
+#pragma unroll(UNROLL ? N : 1)
+            for (int q = p + 1; q < N; q++) {
+                T a = 0, b = 0, g = 0;
+#pragma unroll
+                for (int k = 0; k < M; k++) {
+                    const T x = A[k * N + p], y = A[k * N + q];
+                    a += x * x;
+                    b += y * y;
+                    g += x * y;
+                }
+                if (fabs((double)g) <= (double)eps * sqrt((double)a * (double)b) || g == 0) continue;
+                changed = true;
+                const T zeta = (b - a) / (2 * g);
+                const T t = (zeta >= 0 ? (T)1 : (T)-1) / ((T)fabs((double)zeta) + (T)sqrt((double)(1 + zeta * zeta)));
+                const T c = (T)1 / (T)sqrt((double)(1 + t * t)), sn = c * t;
+#pragma unroll
+                for (int k = 0; k < M; k++) {
+                    const T x = A[k * N + p], y = A[k * N + q];
+                    A[k * N + p] = c * x - sn * y;
+                    A[k * N + q] = sn * x + c * y;
+                }
+#pragma unroll
+                for (int k = 0; k < N; k++) {
+                    const T x = V[k * N + p], y = V[k * N + q];
+                    V[k * N + p] = c * x - sn * y;
+                    V[k * N + q] = sn * x + c * y;
+                }
+            }
+        }
+        if (!changed) break;
+    }
+    int best = 0;
+    T bestn = -1;
+#pragma unroll
+    for (int j = 0; j < N; j++) {
+        T sq = 0;
+#pragma unroll
+        for (int k = 0; k < M; k++) sq += A[k * N + j] * A[k * N + j];
+        if (bestn < 0 || sq < bestn) {
+            bestn = sq;
+            best = j;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        T v = 0;
+#pragma unroll
+        for (int j = 0; j < N; j++) v = (j == best) ? V[k * N + j] : v;
+        z[k] = v;
+    }
+}
+
 // 2-view DLT (cv::sfm::triangulatePoints with two views): 4x4 system rows x*P[2]-P[0], y*P[2]-P[1].
 // Kept out of line with scalar arguments: inlining it next to the design-matrix path made cicc -O3 (12.9) read the caller's
 // xs/ys/Pm arrays before they were written (observed on sm_100a: NaN for every 2-view row), see tools/dbg.
 __device__ __noinline__ void dlt_2views(const double* P0, const double* P1, double x0, double y0, double x1, double y1, double* X3) {
-    double A[16], V[16], z[4];
-#pragma unroll 1
+    double A[16], z[4];
+#pragma unroll
     for (int i = 0; i < 4; i++) {
         A[0 * 4 + i] = x0 * P0[8 + i] - P0[i];
         A[1 * 4 + i] = y0 * P0[8 + i] - P0[4 + i];
         A[2 * 4 + i] = x1 * P1[8 + i] - P1[i];
         A[3 * 4 + i] = y1 * P1[8 + i] - P1[4 + i];
     }
-    null_vector<double, 4, 4>(A, V, 4, 4, z, 2.220446049250313e-16);
+    null_vector_fixed<double, 4, 4, true>(A, z, 2.220446049250313e-16);
     X3[0] = z[0] / z[3];
     X3[1] = z[1] / z[3];
     X3[2] = z[2] / z[3];
 }
 
-// N-view DLT, (3n) x (4+n) design [-P_i | x_i in column 4+i] (MultiCameraFrame.cpp:419-433), n >= 2.
-template <int MAXC>
-__device__ __noinline__ void dlt_design(const double* const* Pm, const double* xs, const double* ys, int nv, double* X3) {
-    double A[3 * MAXC * (4 + MAXC)];
-    double V[(4 + MAXC) * (4 + MAXC)];
-    double z[4 + MAXC];
-    const int m = 3 * nv, n = 4 + nv;
-    for (int i = 0; i < m * n; i++) A[i] = 0;
-    for (int i = 0; i < nv; i++) {
+// N-view DLT, (3n) x (4+n) design [-P_i | x_i in column 4+i] (MultiCameraFrame.cpp:419-433), n = NV >= 2.
+template <int NV>
+__device__ __noinline__ void dlt_design_fixed(const double* const* Pm, const double* xs, const double* ys, double* X3) {
+    constexpr int M = 3 * NV, N = 4 + NV;
+    double A[M * N], z[4];
+#pragma unroll
+    for (int i = 0; i < M * N; i++) A[i] = 0;
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+#pragma unroll
         for (int jj = 0; jj < 3; jj++)
-            for (int ii = 0; ii < 4; ii++) A[(3 * i + jj) * n + ii] = -Pm[i][jj * 4 + ii];
-        A[(3 * i + 0) * n + 4 + i] = xs[i];
-        A[(3 * i + 1) * n + 4 + i] = ys[i];
-        A[(3 * i + 2) * n + 4 + i] = 1.0;
+#pragma unroll
+            for (int ii = 0; ii < 4; ii++) A[(3 * i + jj) * N + ii] = -Pm[i][jj * 4 + ii];
+        A[(3 * i + 0) * N + 4 + i] = xs[i];
+        A[(3 * i + 1) * N + 4 + i] = ys[i];
+        A[(3 * i + 2) * N + 4 + i] = 1.0;
     }
-    null_vector<double, 3 * MAXC, 4 + MAXC>(A, V, m, n, z, 2.220446049250313e-16);
+    null_vector_fixed<double, M, N, (NV <= 3)>(A, z, 2.220446049250313e-16);
     X3[0] = z[0] / z[3];
     X3[1] = z[1] / z[3];
     X3[2] = z[2] / z[3];
@@ -261,8 +365,19 @@ __device__ __noinline__ void dlt_design(const double* const* Pm, const double* x
 
 template <int MAXC>
 __device__ __forceinline__ void dlt_nviews(const double* const* Pm, const double* xs, const double* ys, int nv, bool force_design, double* X3) {
-    if (nv == 2 && !force_design) dlt_2views(Pm[0], Pm[1], xs[0], ys[0], xs[1], ys[1], X3);
-    else dlt_design<MAXC>(Pm, xs, ys, nv, X3);
+    if (nv == 2 && !force_design) {
+        dlt_2views(Pm[0], Pm[1], xs[0], ys[0], xs[1], ys[1], X3);
+        return;
+    }
+    switch (nv) {
+        case 2: dlt_design_fixed<2>(Pm, xs, ys, X3); break;
+        case 3: dlt_design_fixed<3>(Pm, xs, ys, X3); break;
+        case 4: dlt_design_fixed<4>(Pm, xs, ys, X3); break;
+        case 5: dlt_design_fixed<5>(Pm, xs, ys, X3); break;
+        case 6: dlt_design_fixed<6>(Pm, xs, ys, X3); break;
+        case 7: dlt_design_fixed<7>(Pm, xs, ys, X3); break;
+        default: dlt_design_fixed<(MAXC < 8 ? MAXC : 8)>(Pm, xs, ys, X3); break;
+    }
 }
 
 struct LandmarkOut {

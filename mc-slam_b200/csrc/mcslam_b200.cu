@@ -266,7 +266,7 @@ struct Engine {
         int k7[7];
         gauss_kernel_fixed(7, 2.0, k7);
         CK(cudaMemcpyToSymbol(mcs::c_gauss7, k7, sizeof(k7)));
-        CK(cudaMemcpyToSymbol(mcs::c_pattern, MCS_ORB_PATTERN_XY, 1024));
+        CK(cudaMemcpyToSymbol(mcs::g_pattern, MCS_ORB_PATTERN_XY, 1024));
         return replan(max_w, max_h);
     }
 
@@ -348,7 +348,8 @@ struct Engine {
         CK(cudaMemsetAsync(d_cand_count, 0, (size_t)n * P.nlevels * sizeof(int), stream));
         for (int l = 1; l < P.nlevels; l++) {
             dim3 b(32, 8), g((P.L[l].w + 127) / 128, (P.L[l].h + 7) / 8, n);
-            mcs::resize_level_kernel<<<g, b, 0, stream>>>(P, set, l, d_xtab, d_ytab);
+            if (T.scale_factor_f <= 2.0f) mcs::resize_level_words_kernel<<<g, b, 0, stream>>>(P, set, l, d_xtab, d_ytab);
+            else mcs::resize_level_kernel<<<g, b, 0, stream>>>(P, set, l, d_xtab, d_ytab);
             launches++;
         }
         mark(ST_FAST);
@@ -672,6 +673,7 @@ struct mcs_rig {
     int n_extracted = 0, n_matched = 0, n_triangulated = 0;
     bool feat_host = false, rows_host = false, lm_host = false;
     size_t merge_smem = 0;
+    bool merge_rows_smem = false;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
 
     ~mcs_rig() {
@@ -748,8 +750,12 @@ struct mcs_rig {
         CK(cudaMallocHost(&h_accepted, rw));
         CK(cudaMallocHost(&h_xyz, rw * 3 * sizeof(double)));
         CK(cudaMallocHost(&h_uv, rw * 2 * sizeof(float)));
-        merge_smem = (size_t)C * kp_cap * sizeof(uint16_t);
+        // match_inv_idx (u16) + compacted match list + (when it fits) the IntraMatch row table itself
+        merge_smem = (size_t)((C * kp_cap + 1) & ~1) * sizeof(uint16_t) + (size_t)kp_cap * sizeof(uint32_t);
+        if (kp_cap >= 65535) { set_err("too many features per camera for the merge kernel"); return MCS_ERR_ARG; }
         if (merge_smem > 200 * 1024) { set_err("too many features per frame for the merge kernel's shared table"); return MCS_ERR_ARG; }
+        merge_rows_smem = merge_smem + (size_t)row_cap * C * sizeof(int) <= 100 * 1024;
+        if (merge_rows_smem) merge_smem += (size_t)row_cap * C * sizeof(int);
         CK(cudaFuncSetAttribute(mcs::merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(merge_smem, 1024)));
         return 0;
     }
@@ -775,7 +781,7 @@ struct mcs_rig {
         }
         eng.mark(ST_MERGE);
         mcs::merge_kernel<<<n_frames, 128, merge_smem, eng.stream>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count, d_match_train, eng.d_kps, old,
-                                                                     d_F, d_sigma2, d_rows, d_row_count);
+                                                                     d_F, d_sigma2, d_rows, d_row_count, merge_rows_smem ? 1 : 0);
         eng.launches++;
         eng.mark(ST_TRIANG);
         CK(cudaGetLastError());

@@ -10,8 +10,8 @@
 #define MCS_PLAN_MAX_LEVELS 16
 #define MCS_EDGE_THRESHOLD 19
 #define MCS_MIN_BORDER 16  // EDGE_THRESHOLD - 3
-#define MCS_BLUR_TW 64     // blur output tile
-#define MCS_BLUR_TH 16
+#define MCS_BLUR_TW 128    // blur output tile
+#define MCS_BLUR_TH 32
 
 struct McsLevel {
     int w, h, pitch;     // level image; pitch is a multiple of 64 bytes
