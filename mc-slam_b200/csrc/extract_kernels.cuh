@@ -227,46 +227,9 @@ __global__ void __launch_bounds__(256) blur_kernel(const __grid_constant__ McsPl
 // any, else maxima >= minTh.
 //
 // The arc minima use packed 16-bit lanes (d + 256 keeps both lanes positive) and 3-input min/max (VIMNMX3).
+// ring offsets of FAST 9/16 in OpenCV order: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
 // ------------------------------------------------------------------------------------------------------------
 #define MCS_FAST_NT 128
-#define MCS_FAST_TP 84   // shared tile pitch (bytes): <= 75 px + 3 alignment + slack, multiple of 4
-#define MCS_FAST_MAXC 76 // max sub-image side
-#define MCS_FAST_SP 72   // score tile pitch
-#define MCS_FAST_MAXSURV 1296
-
-__device__ __forceinline__ int fast_strength(const uint8_t* c, int tp) {
-    // ring offsets of FAST 9/16 in OpenCV order: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
-    const int v = c[0];
-    const uint32_t vb = (uint32_t)(v + 256) * 0x00010001u;
-    uint32_t W0[8], W1[8];
-    W0[0] = vb - ((uint32_t)c[3 * tp] | ((uint32_t)c[3 * tp + 1] << 16));
-    W0[1] = vb - ((uint32_t)c[2 * tp + 2] | ((uint32_t)c[tp + 3] << 16));
-    W0[2] = vb - ((uint32_t)c[3] | ((uint32_t)c[-tp + 3] << 16));
-    W0[3] = vb - ((uint32_t)c[-2 * tp + 2] | ((uint32_t)c[-3 * tp + 1] << 16));
-    W0[4] = vb - ((uint32_t)c[-3 * tp] | ((uint32_t)c[-3 * tp - 1] << 16));
-    W0[5] = vb - ((uint32_t)c[-2 * tp - 2] | ((uint32_t)c[-tp - 3] << 16));
-    W0[6] = vb - ((uint32_t)c[-3] | ((uint32_t)c[tp - 3] << 16));
-    W0[7] = vb - ((uint32_t)c[2 * tp - 2] | ((uint32_t)c[3 * tp - 1] << 16));
-#pragma unroll
-    for (int j = 0; j < 8; j++) W1[j] = __byte_perm(W0[j], W0[(j + 1) & 7], 0x5432);
-    uint32_t M0[8], X0[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-        M0[j] = __vimin3_u16x2(W0[j], W1[j], W0[(j + 1) & 7]);
-        X0[j] = __vimax3_u16x2(W0[j], W1[j], W0[(j + 1) & 7]);
-    }
-    uint32_t amin = 0, amax = 0xFFFFFFFFu;  // max over arcs of arc-min ; min over arcs of arc-max (per 16-bit lane)
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-        const uint32_t M1 = __byte_perm(M0[(j + 1) & 7], M0[(j + 2) & 7], 0x5432);
-        const uint32_t X1 = __byte_perm(X0[(j + 1) & 7], X0[(j + 2) & 7], 0x5432);
-        amin = __vmaxu2(amin, __vimin3_u16x2(M0[j], M1, M0[(j + 3) & 7]));
-        amax = __vminu2(amax, __vimax3_u16x2(X0[j], X1, X0[(j + 3) & 7]));
-    }
-    const int dark = (int)max(amin & 0xFFFFu, amin >> 16) - 256;     // max arc-min of  (v - x)
-    const int bright = 256 - (int)min(amax & 0xFFFFu, amax >> 16);   // max arc-min of -(v - x)
-    return max(dark, bright) - 1;
-}
 
 // One polarity only (sgn = +1: ring brighter than the centre, -1: darker): max over the 16 arcs of min over the arc of
 // sgn * (ring - v), minus 1.  Ring pixels are packed as ANTIPODAL pairs P_k = (e_k, e_{k+8}), e = 256 + sgn * (ring - v), so that
@@ -297,13 +260,22 @@ __device__ __forceinline__ int fast_strength_pol(const uint8_t* c, int tp, int s
     return (int)max(m & 0xFFFFu, m >> 16) - 257;
 }
 
+// Shared-memory carve-up (sizes from the plan's largest cell, so small-cell configurations keep high occupancy):
+//   tile  [ch][fast_tpw] u32   sub-image, staged so that sub-image column c sits at byte c + 1 (interior column 0 = byte 4: aligned)
+//   score [ih + 2][fast_sp] u8 corner scores with a 1 px zero frame
+//   flags [ih][G] u8           pass-1 result per group of 4 pixels: bit 2e = bright pre-test of pixel e, bit 2e+1 = dark
+//   queue u16                  one entry per (pixel, polarity) that passed: corner << 15 | dark << 14 | ly << 7 | lx
+//   surv  u32                  NMS survivors (packed candidates)
 __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                  uint32_t* __restrict__ cand, int* __restrict__ cand_count) {
-    __shared__ __align__(16) uint8_t s_tile[MCS_FAST_MAXC * MCS_FAST_TP];
-    __shared__ __align__(16) uint8_t s_score[(MCS_FAST_MAXC - 4) * MCS_FAST_SP];
-    __shared__ uint16_t s_queue[(MCS_FAST_MAXC - 6) * (MCS_FAST_MAXC - 6)];  // pixels that pass the pre-test: polarity flags (bit 14 bright, 15 dark) | ly << 7 | lx
-    __shared__ uint32_t s_surv[MCS_FAST_MAXSURV];
-    __shared__ int s_nq, s_nsurv;
+    extern __shared__ __align__(16) unsigned char s_fast[];
+    __shared__ int s_wsum[MCS_FAST_NT / 32], s_nsurv;
+    uint32_t* s_tile = reinterpret_cast<uint32_t*>(s_fast);
+    uint8_t* s_score = s_fast + P.fast_ofs_score;
+    uint8_t* s_flags = s_fast + P.fast_ofs_flags;
+    uint16_t* s_queue = reinterpret_cast<uint16_t*>(s_fast + P.fast_ofs_queue);
+    uint32_t* s_surv = reinterpret_cast<uint32_t*>(s_fast + P.fast_ofs_surv);
+    const int TPW = P.fast_tpw, TP = TPW * 4, SP = P.fast_sp;
     const int img = blockIdx.y;
     int level = 0;
 #pragma unroll 1
@@ -319,88 +291,127 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
     const int cw = maxX - iniX, ch = maxY - iniY;  // sub-image handed to cv::FAST
     const int iw = cw - 6, ih = ch - 6;            // computed interior
     if (iw <= 0 || ih <= 0) return;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int pitch;
     const uint8_t* src = level_ptr(P, S, img, level, pitch);
-    // stage the sub-image with aligned 32-bit loads
-    const int a0 = iniX & ~3, off = iniX - a0, nw = (off + cw + 3) >> 2;
-    for (int t = threadIdx.x; t < nw * ch; t += MCS_FAST_NT) {
-        const int r = t / nw, c = t - r * nw;
-        const uint32_t wv = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * pitch + a0) + c);
-        *reinterpret_cast<uint32_t*>(&s_tile[r * MCS_FAST_TP + c * 4]) = wv;
+    const int G = (iw + 3) >> 2;  // groups of 4 interior pixels per row
+    // stage the sub-image: shared word c of row r = image bytes (iniX - 1 + 4c) .. +3, cut out of two aligned 32-bit loads
+    {
+        const int nws = G + 2, gb = iniX - 1, aw = gb >> 2, sh = (gb & 3) * 8;
+        const uint32_t mg = ((1u << 20) + nws - 1) / nws;  // t / nws == (t * mg) >> 20 (t < 76 * 21)
+        for (int t = threadIdx.x; t < nws * ch; t += MCS_FAST_NT) {
+            const int r = (int)(((uint32_t)t * mg) >> 20), c = t - r * nws;
+            const uint32_t* g = reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * pitch) + aw + c;
+            s_tile[r * TPW + c] = __funnelshift_r(__ldg(g), __ldg(g + 1), sh);
+        }
     }
-    const int npx = iw * ih;
-    const uint32_t magic = ((1u << 20) + iw - 1) / iw;  // t / iw == (t * magic) >> 20 for t < 76 * 76 (checked exhaustively)
-    const int npx_pad = (npx + MCS_FAST_NT - 1) / MCS_FAST_NT * MCS_FAST_NT;
+    const int ngroups = G * ih;
+    const uint32_t mgG = ((1u << 20) + G - 1) / G;
     uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
     int* cnt = cand_count + img * P.nlevels + level;
     // FAST(cell, iniThFAST); only if that finds nothing, FAST(cell, minThFAST)  (:825, :842-845)
 #pragma unroll 1
     for (int phase = 0; phase < 2; phase++) {
         const int th = phase == 0 ? P.ini_th : P.min_th;
-        if (threadIdx.x == 0) { s_nq = 0; s_nsurv = 0; }
-        // zero score tile incl. 1 px frame: (iw + 2) x (ih + 2)
-        for (int t = threadIdx.x; t < (ih + 2) * (MCS_FAST_SP / 4); t += MCS_FAST_NT) reinterpret_cast<uint32_t*>(s_score)[t] = 0;
+        if (threadIdx.x == 0) s_nsurv = 0;
+        for (int t = threadIdx.x; t < (ih + 2) * (SP >> 2); t += MCS_FAST_NT) reinterpret_cast<uint32_t*>(s_score)[t] = 0;
         __syncthreads();
-        // pass 1, every interior pixel: necessary condition for a 9-arc — of each opposite ring pair at least one pixel is on
-        // the arc (tested on the two axis pairs); survivors are queued so pass 2 runs on dense warps
-        for (int t = threadIdx.x; t < npx_pad; t += MCS_FAST_NT) {
-            bool pass = false;
-            int ly = 0, lx = 0, pol = 0;
-            if (t < npx) {
-                ly = (int)(((uint32_t)t * magic) >> 20);
-                lx = t - ly * iw;
-                const uint8_t* c = &s_tile[(ly + 3) * MCS_FAST_TP + lx + 3 + off];
-                const int v = c[0];
-                const int p0 = c[3 * MCS_FAST_TP], p8 = c[-3 * MCS_FAST_TP], p4 = c[3], p12 = c[-3];
-                const int hi = v + th, lo = v - th;
-                pol = (((p0 > hi || p8 > hi) && (p4 > hi || p12 > hi)) ? 0x4000 : 0) | (((p0 < lo || p8 < lo) && (p4 < lo || p12 < lo)) ? 0x8000 : 0);
-                pass = pol != 0;
+        // pass 1, every interior pixel, 4 per thread on packed 16-bit lanes: necessary condition for a 9-arc — of each opposite
+        // ring pair at least one pixel is on the arc, tested on the two axis pairs:
+        //   bright: min(max(up, down), max(left, right)) > v + th        dark: max(min(up, down), min(left, right)) < v - th
+        const uint32_t K1 = (uint32_t)(0x8000 - th - 1) * 0x00010001u;  // bit 15 of (a + K1 - b) per lane  <=>  a - b > th
+        int my_count = 0;
+        for (int gi = threadIdx.x; gi < ngroups; gi += MCS_FAST_NT) {
+            const int ly = (int)(((uint32_t)gi * mgG) >> 20), g = gi - ly * G;
+            const uint32_t* row = s_tile + (ly + 3) * TPW + g;
+            const uint32_t W0 = row[0], W1 = row[1], W2 = row[2];
+            const uint32_t Up = row[1 - 3 * TPW], Dn = row[1 + 3 * TPW];
+            const uint32_t Lf = __funnelshift_r(W0, W1, 8), Rt = __funnelshift_r(W1, W2, 24);
+            uint32_t f = 0;
+#pragma unroll
+            for (int hpair = 0; hpair < 2; hpair++) {
+                const uint32_t sel = hpair ? 0x4342u : 0x4140u;
+                const uint32_t c2 = __byte_perm(W1, 0, sel), u2 = __byte_perm(Up, 0, sel), d2 = __byte_perm(Dn, 0, sel);
+                const uint32_t l2 = __byte_perm(Lf, 0, sel), r2 = __byte_perm(Rt, 0, sel);
+                const uint32_t bmin = __vminu2(__vmaxu2(u2, d2), __vmaxu2(l2, r2));
+                const uint32_t dmax = __vmaxu2(__vminu2(u2, d2), __vminu2(l2, r2));
+                const uint32_t Bf = bmin + K1 - c2, Df = c2 + K1 - dmax;
+                const uint32_t t2 = ((Bf >> 15) & 0x00010001u) | ((Df >> 14) & 0x00020002u);
+                f |= ((t2 | (t2 >> 14)) & 0xFu) << (4 * hpair);
             }
-            const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
-            if (m) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&s_nq, __popc(m));
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (pass) s_queue[base + __popc(m & ((1u << lane) - 1))] = (uint16_t)(pol | (ly << 7) | lx);
+            const int nvalid = min(4, iw - 4 * g);
+            f &= (1u << (2 * nvalid)) - 1u;
+            s_flags[gi] = (uint8_t)f;
+            my_count += __popc(f);
+        }
+        // block-wide exclusive scan of the per-thread entry counts -> queue offsets (deterministic order, no atomics)
+        int incl = my_count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int pos = incl - my_count, nq = 0;
+#pragma unroll
+        for (int w = 0; w < MCS_FAST_NT / 32; w++) {
+            const int ws = s_wsum[w];
+            if (w < warp) pos += ws;
+            nq += ws;
+        }
+        for (int gi = threadIdx.x; gi < ngroups; gi += MCS_FAST_NT) {
+            uint32_t f = s_flags[gi];
+            if (!f) continue;
+            const int ly = (int)(((uint32_t)gi * mgG) >> 20), g = gi - ly * G;
+            const uint32_t base = (uint32_t)((ly << 7) | (4 * g));
+            while (f) {
+                const int b = __ffs((int)f) - 1;
+                f &= f - 1;
+                s_queue[pos++] = (uint16_t)(((b & 1) << 14) | (base + (b >> 1)));
             }
         }
         __syncthreads();
-        // pass 2, queued pixels: arc strength = cv::FAST's score; a corner at th  <=>  strength >= th
-        const int nq = s_nq;
+        // pass 2, queued (pixel, polarity) entries on dense warps: arc strength = cv::FAST's score; corner at th <=> strength >= th.
+        // A pixel cannot be a bright and a dark corner at once (two 9-arcs do not fit in 16), so at most one entry per pixel scores.
         for (int q = threadIdx.x; q < nq; q += MCS_FAST_NT) {
             const int e = s_queue[q], ly = (e >> 7) & 0x7F, lx = e & 0x7F;
-            const uint8_t* c = &s_tile[(ly + 3) * MCS_FAST_TP + lx + 3 + off];
-            int sc = fast_strength_pol(c, MCS_FAST_TP, (e & 0x4000) ? 1 : -1);
-            if ((e & 0xC000) == 0xC000) sc = max(sc, fast_strength_pol(c, MCS_FAST_TP, -1));  // rare: both pre-tests passed
-            if (sc >= th && sc > 0) s_score[(ly + 1) * MCS_FAST_SP + lx + 1] = (uint8_t)min(sc, 255);
+            const uint8_t* c = reinterpret_cast<const uint8_t*>(s_tile) + (ly + 3) * TP + lx + 4;
+            const int sc = fast_strength_pol(c, TP, (e & 0x4000) ? -1 : 1);
+            if (sc >= th && sc > 0) {
+                s_score[(ly + 1) * SP + lx + 1] = (uint8_t)min(sc, 255);
+                s_queue[q] = (uint16_t)(e | 0x8000);
+            }
         }
         __syncthreads();
         // pass 3, corners only: strict-'>' 8-neighbour NMS inside the computed interior (scores outside count as 0)
         for (int q = threadIdx.x; q < nq; q += MCS_FAST_NT) {
-            const int e = s_queue[q], ly = (e >> 7) & 0x7F, lx = e & 0x7F;
-            const uint8_t* qp = &s_score[(ly + 1) * MCS_FAST_SP + lx + 1];
+            const int e = s_queue[q];
+            if (!(e & 0x8000)) continue;
+            const int ly = (e >> 7) & 0x7F, lx = e & 0x7F;
+            const uint8_t* qp = &s_score[(ly + 1) * SP + lx + 1];
             const int sc = qp[0];
-            if (sc == 0) continue;
-            if (sc > qp[-1] && sc > qp[1] && sc > qp[-MCS_FAST_SP - 1] && sc > qp[-MCS_FAST_SP] && sc > qp[-MCS_FAST_SP + 1] &&
-                sc > qp[MCS_FAST_SP - 1] && sc > qp[MCS_FAST_SP] && sc > qp[MCS_FAST_SP + 1]) {
+            const int n0 = max(max((int)qp[-SP - 1], (int)qp[-SP]), (int)qp[-SP + 1]);
+            const int n1 = max(max((int)qp[SP - 1], (int)qp[SP]), (int)qp[SP + 1]);
+            const int n2 = max((int)qp[-1], (int)qp[1]);
+            if (sc > max(max(n0, n1), n2)) {
                 const int slot = atomicAdd(&s_nsurv, 1);
                 // keypoint in ROI coordinates: FAST x in the sub-image (lx + 3) shifted by j*wCell (:864-865)
-                if (slot < MCS_FAST_MAXSURV) s_surv[slot] = mcs_oct::pack_cand(lx + 3 + j * Lv.w_cell, ly + 3 + i * Lv.h_cell, sc);
+                if (slot < P.fast_maxsurv) s_surv[slot] = mcs_oct::pack_cand(lx + 3 + j * Lv.w_cell, ly + 3 + i * Lv.h_cell, sc);
             }
         }
         __syncthreads();
-        const int ns = min(s_nsurv, MCS_FAST_MAXSURV);
+        const int ns = min(s_nsurv, P.fast_maxsurv);
         if (ns > 0) {
             for (int base = 0; base < ns; base += MCS_FAST_NT) {
                 const int t = base + threadIdx.x;
                 const bool keep = t < ns;
                 const unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
                 if (m) {
-                    int pos = 0;
-                    if (lane == 0) pos = atomicAdd(cnt, __popc(m));
-                    pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(m & ((1u << lane) - 1));
-                    if (keep && pos < Lv.cand_cap) out[pos] = s_surv[t];
+                    int p0 = 0;
+                    if (lane == 0) p0 = atomicAdd(cnt, __popc(m));
+                    p0 = __shfl_sync(0xFFFFFFFFu, p0, 0) + __popc(m & ((1u << lane) - 1));
+                    if (keep && p0 < Lv.cand_cap) out[p0] = s_surv[t];
                 }
             }
             return;  // block-uniform

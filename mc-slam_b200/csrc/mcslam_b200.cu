@@ -185,6 +185,21 @@ bool build_plan(const OrbTables& T, int width, int height, int use_angle, McsPla
         L.tile_base = tiles;
         tiles += L.tiles_x * L.tiles_y;
     }
+    {   // FAST shared-memory carve-up for the largest cell
+        int cwm = 7, chm = 7;
+        for (int l = 0; l < T.nlevels; l++)
+            if (P.L[l].n_cols > 0) { cwm = std::max(cwm, P.L[l].w_cell + 6); chm = std::max(chm, P.L[l].h_cell + 6); }
+        const int iwm = cwm - 6, ihm = chm - 6, G = (iwm + 3) / 4;
+        P.fast_tpw = (G + 3) | 1;  // words g .. g+2 of the widest row plus the second word of the staging funnel; odd pitch
+        P.fast_sp = align_up(iwm + 2, 4);
+        int o = align_up(P.fast_tpw * 4 * chm, 16);
+        P.fast_ofs_score = o; o += align_up(P.fast_sp * (ihm + 2), 16);
+        P.fast_ofs_flags = o; o += align_up(G * ihm, 16);
+        P.fast_ofs_queue = o; o += align_up(2 * iwm * ihm * 2, 16);
+        P.fast_maxsurv = ((iwm + 1) / 2) * ((ihm + 1) / 2);
+        P.fast_ofs_surv = o; o += P.fast_maxsurv * 4;
+        P.fast_smem_bytes = o;
+    }
     P.n_cells = cells; P.n_tiles = tiles; P.pyr_stride = align_up(plane, 256); P.cand_stride = cand; P.sel_stride = sel;
     P.kp_cap = align_up(sel, 8);
     P.oct_cap_max = octmax;
@@ -319,6 +334,8 @@ struct Engine {
         planned_w = w; planned_h = h;
         oct_smem = mcs_oct::Shared::bytes(plan.oct_cap_max);
         if (oct_smem > 200 * 1024) { set_err("features per level exceed the octree kernel's shared-memory table"); return MCS_ERR_ARG; }
+        if (plan.fast_smem_bytes > 200 * 1024) { set_err("internal: FAST cell too large for shared memory"); return MCS_ERR_ARG; }
+        CK(cudaFuncSetAttribute(mcs::fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.fast_smem_bytes, 1024)));
         CK(cudaFuncSetAttribute(mcs::octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
         last_n = 0;
         return 0;
@@ -354,7 +371,7 @@ struct Engine {
         }
         mark(ST_FAST);
         if (P.n_cells > 0) {
-            mcs::fast_cells_kernel<<<dim3(P.n_cells, n), MCS_FAST_NT, 0, stream>>>(P, set, d_cand, d_cand_count);
+            mcs::fast_cells_kernel<<<dim3(P.n_cells, n), MCS_FAST_NT, P.fast_smem_bytes, stream>>>(P, set, d_cand, d_cand_count);
             launches++;
         }
         mark(ST_OCTREE);

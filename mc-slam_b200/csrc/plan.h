@@ -48,6 +48,11 @@ struct McsPlan {
     int kp_cap;         // output keypoints per image (>= sum of oct_cap)
     int oct_cap_max;
     int use_angle;      // 0 = shipped behaviour (angle 0)
+    // FAST kernel shared-memory layout, sized for the largest cell of the plan (bytes unless noted)
+    int fast_tpw;       // tile pitch in 32-bit words
+    int fast_sp;        // score tile pitch
+    int fast_ofs_score, fast_ofs_flags, fast_ofs_queue, fast_ofs_surv, fast_smem_bytes;
+    int fast_maxsurv;   // survivor capacity (records)
     int umax[16];       // circular patch row half-widths for IC_Angle (ORBextractor.cpp:452-467)
     McsLevel L[MCS_PLAN_MAX_LEVELS];
 };
