@@ -390,20 +390,30 @@ struct LandmarkOut {
     int* n_accepted;    // [frames]
 };
 
+// ------------------------------------------------------------------------------------------------------------
+// K8  triangulation block of FrontEnd::obtainLfFeatures (FrontEnd.cpp:249-370), two kernels:
+//   tri_classify_kernel : one thread per IntraMatch row — mask filter (:265-273), n_rays, defaults; rows with >= 2 views are
+//                         appended to the work list of their view count, so that
+//   tri_solve_kernel<NV>: runs warps whose rows all have NV views (no divergence between system sizes, registers and shared
+//                         memory sized for exactly NV).  NV = 2 keeps the 4x4 system in registers; NV >= 3 keeps the
+//                         (3NV) x (4+NV) design matrix and V in shared memory as [element][thread] (conflict-free), columns p, q
+//                         of the current rotation in registers.  Same operation order as the oracle's one-sided Jacobi.
+// ------------------------------------------------------------------------------------------------------------
+#define MCS_TRI_NT 32
+
 template <int MAXC>
-__global__ void __launch_bounds__(64) triangulate_kernel(int num_cams, int kp_cap, int row_cap, int width, int height,
-                                                         const CalibDev* __restrict__ calib, const int* __restrict__ rows_in,
-                                                         const int* __restrict__ row_count, const KeypointPod* __restrict__ kps,
-                                                         const uint8_t* __restrict__ desc, const float* __restrict__ masks,
-                                                         LandmarkOut out) {
+__global__ void __launch_bounds__(128) tri_classify_kernel(int num_cams, int kp_cap, int row_cap, int width, int height,
+                                                           const int* __restrict__ rows_in, const int* __restrict__ row_count,
+                                                           const KeypointPod* __restrict__ kps, const float* __restrict__ masks,
+                                                           LandmarkOut out, int* __restrict__ lists, int* __restrict__ list_count,
+                                                           int list_stride) {
     const int frame = blockIdx.y;
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     const int M = min(row_count[frame], row_cap);
     if (r >= M) return;
     const size_t ro = (size_t)frame * row_cap + r;
     const int* row = rows_in + ro * num_cams;
-    int views[MAXC], feats[MAXC];
-    int nv = 0;
+    int nv = 0, first = -1;
     for (int c = 0; c < num_cams; c++) {
         int f = row[c];
         if (f != -1) {
@@ -416,8 +426,7 @@ __global__ void __launch_bounds__(64) triangulate_kernel(int num_cams, int kp_ca
                 keep = (double)masks[((size_t)(frame * num_cams + c) * height + my) * width + mx] < 0.7;  // :266
             }
             if (keep) {
-                views[nv] = c;
-                feats[nv] = f;
+                if (nv == 0) first = c;
                 nv++;
             } else {
                 f = -1;
@@ -427,29 +436,151 @@ __global__ void __launch_bounds__(64) triangulate_kernel(int num_cams, int kp_ca
     }
     out.n_views[ro] = nv;
     out.accepted[ro] = 0;
-    out.rep_cam[ro] = nv == 1 ? views[0] : -1;
-    double X[3] = {0, 0, 0};
-    float u = 0, v = 0;
-    if (nv >= 2) {
-        double xs[MAXC], ys[MAXC];
-        const double* Pm[MAXC];
-        for (int k = 0; k < nv; k++) {
+    out.rep_cam[ro] = nv == 1 ? first : -1;
+    out.xyz[ro * 3] = 0;
+    out.xyz[ro * 3 + 1] = 0;
+    out.xyz[ro * 3 + 2] = 0;
+    out.uv_ref[ro * 2] = 0;
+    out.uv_ref[ro * 2 + 1] = 0;
+    if (nv >= 2) lists[(size_t)nv * list_stride + atomicAdd(&list_count[nv], 1)] = (int)ro;
+}
+
+// null vector of the (3NV) x (4+NV) design in shared memory, element e of thread t at sm[e * MCS_TRI_NT + t]
+template <int NV>
+__device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double* z) {
+    constexpr int M = 3 * NV, N = 4 + NV, T = MCS_TRI_NT;
+    const double eps = 2.220446049250313e-16;
+#pragma unroll 1
+    for (int i = 0; i < N * N; i++) sV[i * T] = 0;
+#pragma unroll 1
+    for (int i = 0; i < N; i++) sV[(i * N + i) * T] = 1;
+#pragma unroll 1
+    for (int sweep = 0; sweep < 60; sweep++) {
+        bool changed = false;
+#pragma unroll 1
+        for (int p = 0; p < N - 1; p++) {
+#pragma unroll 1
+            for (int q = p + 1; q < N; q++) {
+                double xk[M], yk[M];
+                double a = 0, b = 0, g = 0;
+#pragma unroll
+                for (int k = 0; k < M; k++) {
+                    xk[k] = sA[(k * N + p) * T];
+                    yk[k] = sA[(k * N + q) * T];
+                }
+#pragma unroll
+                for (int k = 0; k < M; k++) {
+                    a += xk[k] * xk[k];
+                    b += yk[k] * yk[k];
+                    g += xk[k] * yk[k];
+                }
+                if (fabs(g) <= eps * sqrt(a * b) || g == 0) continue;
+                changed = true;
+                const double zeta = (b - a) / (2 * g);
+                const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1 + zeta * zeta));
+                const double c = 1.0 / sqrt(1 + t * t), sn = c * t;
+#pragma unroll
+                for (int k = 0; k < M; k++) {
+                    sA[(k * N + p) * T] = c * xk[k] - sn * yk[k];
+                    sA[(k * N + q) * T] = sn * xk[k] + c * yk[k];
+                }
+#pragma unroll
+                for (int k = 0; k < N; k++) {
+                    const double x = sV[(k * N + p) * T], y = sV[(k * N + q) * T];
+                    sV[(k * N + p) * T] = c * x - sn * y;
+                    sV[(k * N + q) * T] = sn * x + c * y;
+                }
+            }
+        }
+        if (!changed) break;
+    }
+    int best = 0;
+    double bestn = -1;
+#pragma unroll 1
+    for (int j = 0; j < N; j++) {
+        double sq = 0;
+#pragma unroll
+        for (int k = 0; k < M; k++) {
+            const double v = sA[(k * N + j) * T];
+            sq += v * v;
+        }
+        if (bestn < 0 || sq < bestn) {
+            bestn = sq;
+            best = j;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) z[k] = sV[(k * N + best) * T];
+}
+
+template <int NV, int NT = MCS_TRI_NT>
+__device__ __forceinline__ void tri_solve_class(double* s_tri, int block, int nblocks, int num_cams, int kp_cap, int row_cap,
+                                                const CalibDev* __restrict__ calib, const KeypointPod* __restrict__ kps,
+                                                const uint8_t* __restrict__ desc, const LandmarkOut& out, const int* __restrict__ lists,
+                                                const int* __restrict__ list_count, int list_stride) {
+    const int count = list_count[NV];
+    const int* list = lists + (size_t)NV * list_stride;
+    for (int e = block * NT + threadIdx.x; e < count; e += nblocks * NT) {
+        const size_t ro = (size_t)list[e];
+        const int frame = (int)(ro / row_cap);
+        int views[NV], feats[NV];
+        {
+            int n = 0;
+            for (int c = 0; c < num_cams; c++) {
+                const int f = out.rows[ro * num_cams + c];
+                if (f != -1 && n < NV) {
+                    views[n] = c;
+                    feats[n] = f;
+                    n++;
+                }
+            }
+        }
+        double xs[NV], ys[NV];
+#pragma unroll
+        for (int k = 0; k < NV; k++) {
             const int c = views[k];
             const KeypointPod p = kps[(size_t)(frame * num_cams + c) * kp_cap + feats[k]];
             xs[k] = ((double)p.x - calib[c].K[2]) / calib[c].K[0];  // :292-298
             ys[k] = ((double)p.y - calib[c].K[5]) / calib[c].K[4];
-            Pm[k] = calib[c].Rt;
         }
-        dlt_nviews<MAXC>(Pm, xs, ys, nv, false, X);
+        double X[3];
+        if (NV == 2) {
+            dlt_2views(calib[views[0]].Rt, calib[views[1]].Rt, xs[0], ys[0], xs[1], ys[1], X);
+        } else {
+            constexpr int M = 3 * NV, N = 4 + NV, T = MCS_TRI_NT;
+            double* sA = s_tri + threadIdx.x;
+            double* sV = sA + M * N * T;
+#pragma unroll 1
+            for (int i = 0; i < M * N; i++) sA[i * T] = 0;
+#pragma unroll
+            for (int i = 0; i < NV; i++) {
+                const double* Pm = calib[views[i]].Rt;
+#pragma unroll
+                for (int jj = 0; jj < 3; jj++)
+#pragma unroll
+                    for (int ii = 0; ii < 4; ii++) sA[((3 * i + jj) * N + ii) * T] = -Pm[jj * 4 + ii];
+                sA[((3 * i + 0) * N + 4 + i) * T] = xs[i];
+                sA[((3 * i + 1) * N + 4 + i) * T] = ys[i];
+                sA[((3 * i + 2) * N + 4 + i) * T] = 1.0;
+            }
+            double z[4];
+            null_vector_smem<NV>(sA, sV, z);
+            X[0] = z[0] / z[3];
+            X[1] = z[1] / z[3];
+            X[2] = z[2] / z[3];
+        }
         // representative descriptor: least median Hamming distance, first wins (MultiCameraFrame.cpp:530-567)
         int bestMedian = 0x7FFFFFFF, bestIdx = 0;
-        for (int a = 0; a < nv; a++) {
-            int d[MAXC];
-            for (int b = 0; b < nv; b++)
+#pragma unroll
+        for (int a = 0; a < NV; a++) {
+            int d[NV];
+#pragma unroll
+            for (int b = 0; b < NV; b++)
                 d[b] = a == b ? 0
                               : hamming256(desc + ((size_t)(frame * num_cams + views[a]) * kp_cap + feats[a]) * 32,
                                            desc + ((size_t)(frame * num_cams + views[b]) * kp_cap + feats[b]) * 32);
-            for (int i = 1; i < nv; i++) {  // insertion sort (values only: ties are indistinguishable)
+#pragma unroll
+            for (int i = 1; i < NV; i++) {  // insertion sort (values only: ties are indistinguishable)
                 const int key = d[i];
                 int j = i - 1;
                 while (j >= 0 && d[j] > key) {
@@ -458,13 +589,14 @@ __global__ void __launch_bounds__(64) triangulate_kernel(int num_cams, int kp_ca
                 }
                 d[j + 1] = key;
             }
-            const int median = d[(int)(0.5 * (nv - 1))];
+            const int median = d[(int)(0.5 * (NV - 1))];
             if (median < bestMedian) {
                 bestMedian = median;
                 bestIdx = a;
             }
         }
         out.rep_cam[ro] = views[bestIdx];
+        float u = 0, v = 0;
         if (X[2] < 40 && X[2] > 0.5) {  // :308
             out.accepted[ro] = 1;
             atomicAdd(&out.n_accepted[frame], 1);
@@ -475,12 +607,38 @@ __global__ void __launch_bounds__(64) triangulate_kernel(int num_cams, int kp_ca
             u = (float)(px / pz);
             v = (float)(py / pz);
         }
+        out.xyz[ro * 3] = X[0];
+        out.xyz[ro * 3 + 1] = X[1];
+        out.xyz[ro * 3 + 2] = X[2];
+        out.uv_ref[ro * 2] = u;
+        out.uv_ref[ro * 2 + 1] = v;
     }
-    out.xyz[ro * 3] = X[0];
-    out.xyz[ro * 3 + 1] = X[1];
-    out.xyz[ro * 3 + 2] = X[2];
-    out.uv_ref[ro * 2] = u;
-    out.uv_ref[ro * 2 + 1] = v;
+}
+
+// 2-view rows (the majority): 4x4 systems, no shared memory, wide blocks.  Launched on a second stream next to tri_solve_kernel.
+__global__ void __launch_bounds__(128) tri_solve2_kernel(int num_cams, int kp_cap, int row_cap, const CalibDev* __restrict__ calib,
+                                                         const KeypointPod* __restrict__ kps, const uint8_t* __restrict__ desc,
+                                                         LandmarkOut out, const int* __restrict__ lists,
+                                                         const int* __restrict__ list_count, int list_stride) {
+    tri_solve_class<2, 128>(nullptr, blockIdx.x, gridDim.x, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride);
+}
+
+// One launch for every view count >= 3: blockIdx.y = view-count class (NV = 3 + y), blockIdx.x = persistent block of that class,
+// so the long, latency-bound solves of the different classes overlap instead of queueing behind each other.
+__global__ void __launch_bounds__(MCS_TRI_NT) tri_solve_kernel(int num_cams, int kp_cap, int row_cap, const CalibDev* __restrict__ calib,
+                                                               const KeypointPod* __restrict__ kps, const uint8_t* __restrict__ desc,
+                                                               LandmarkOut out, const int* __restrict__ lists,
+                                                               const int* __restrict__ list_count, int list_stride) {
+    extern __shared__ __align__(16) double s_tri[];
+    const int b = blockIdx.x, nb = gridDim.x;
+    switch (blockIdx.y + 3) {
+        case 3: tri_solve_class<3>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        case 4: tri_solve_class<4>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        case 5: tri_solve_class<5>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        case 6: tri_solve_class<6>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        case 7: tri_solve_class<7>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        default: tri_solve_class<8>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+    }
 }
 
 // MultiCameraFrame::triangulateIntraMatches(x, view_inds, pt) (:411-441): always the (3n) x (4+n) design, K[R|t], pixels.

@@ -678,6 +678,10 @@ struct mcs_rig {
     double* d_F = nullptr;
     float* d_sigma2 = nullptr;
     int *d_match_train = nullptr, *d_match_tmp = nullptr, *d_rows = nullptr, *d_row_count = nullptr;
+    int *d_tri_lists = nullptr, *d_tri_counts = nullptr;  // triangulation work lists per view count
+    int tri_list_stride = 0, sm_count = 148;
+    cudaStream_t stream2 = nullptr;  // forked for the 2-view solver
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
     size_t masks_bytes = 0;
@@ -698,8 +702,10 @@ struct mcs_rig {
         cudaSetDevice(eng.device);
         cudaStreamSynchronize(eng.stream);
         if (t0) { cudaEventDestroy(t0); cudaEventDestroy(t1); }
+        if (stream2) { cudaStreamSynchronize(stream2); cudaStreamDestroy(stream2); }
+        if (ev_fork) { cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); }
         cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
-        cudaFree(d_row_count); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
+        cudaFree(d_row_count); cudaFree(d_tri_lists); cudaFree(d_tri_counts); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
         cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks);
         cudaFreeHost(h_rows); cudaFreeHost(h_row_count); cudaFreeHost(h_lm_rows); cudaFreeHost(h_n_views); cudaFreeHost(h_rep);
         cudaFreeHost(h_n_acc); cudaFreeHost(h_match_tmp); cudaFreeHost(h_accepted); cudaFreeHost(h_xyz); cudaFreeHost(h_uv);
@@ -750,6 +756,14 @@ struct mcs_rig {
         CK(cudaMalloc(&d_match_tmp, (size_t)kp_cap * 3 * sizeof(int)));
         CK(cudaMalloc(&d_rows, rw * C * sizeof(int)));
         CK(cudaMalloc(&d_row_count, F * sizeof(int)));
+        tri_list_stride = (int)rw;
+        CK(cudaMalloc(&d_tri_lists, (size_t)(MCS_MAX_CAMS + 1) * rw * sizeof(int)));
+        CK(cudaMalloc(&d_tri_counts, (MCS_MAX_CAMS + 1) * sizeof(int)));
+        CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, eng.device));
+        if ((rc = set_tri_smem())) return rc;
+        CK(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
         CK(cudaMalloc(&lm.rows, rw * C * sizeof(int)));
         CK(cudaMalloc(&lm.accepted, rw));
         CK(cudaMalloc(&lm.n_views, rw * sizeof(int)));
@@ -777,6 +791,11 @@ struct mcs_rig {
         return 0;
     }
 
+    static size_t tri_smem(int nv) { return nv <= 2 ? 0 : (size_t)(3 * nv * (4 + nv) + (4 + nv) * (4 + nv)) * sizeof(double) * MCS_TRI_NT; }
+    int set_tri_smem() {
+        CK(cudaFuncSetAttribute(mcs::tri_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem(MCS_MAX_CAMS)));
+        return 0;
+    }
     void invalidate() { feat_host = rows_host = lm_host = false; }
 
     int stage_extract(const mcs::ImageSet& set, int n_frames) {
@@ -810,10 +829,28 @@ struct mcs_rig {
         if (n_frames < 1 || n_frames > n_matched) { set_err("triangulate before intra-match"); return MCS_ERR_STATE; }
         eng.mark(ST_TRIANG);
         CK(cudaMemsetAsync(lm.n_accepted, 0, n_frames * sizeof(int), eng.stream));
-        dim3 g((row_cap + 63) / 64, n_frames);
-        mcs::triangulate_kernel<MCS_MAX_CAMS><<<g, 64, 0, eng.stream>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_calib, d_rows, d_row_count,
-                                                                        eng.d_kps, eng.d_desc, d_mask_ptr, lm);
+        CK(cudaMemsetAsync(d_tri_counts, 0, (MCS_MAX_CAMS + 1) * sizeof(int), eng.stream));
+        dim3 g((row_cap + 127) / 128, n_frames);
+        mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, eng.stream>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows, d_row_count, eng.d_kps,
+                                                                          d_mask_ptr, lm, d_tri_lists, d_tri_counts, tri_list_stride);
         eng.launches++;
+        // 2-view rows on a forked stream, every larger view count in one launch (blockIdx.y = class) on the main stream; persistent
+        // grid-stride blocks because the list lengths live on the device
+        if (C >= 2) {
+            CK(cudaEventRecord(ev_fork, eng.stream));
+            CK(cudaStreamWaitEvent(stream2, ev_fork, 0));
+            const int nb2 = std::max(1, std::min(sm_count * 8, (n_frames * row_cap + 127) / 128));
+            mcs::tri_solve2_kernel<<<nb2, 128, 0, stream2>>>(C, kp_cap, row_cap, d_calib, eng.d_kps, eng.d_desc, lm, d_tri_lists, d_tri_counts,
+                                                           tri_list_stride);
+            eng.launches++;
+            CK(cudaEventRecord(ev_join, stream2));
+            if (C >= 3) {
+                mcs::tri_solve_kernel<<<dim3(sm_count, C - 2), MCS_TRI_NT, tri_smem(C), eng.stream>>>(C, kp_cap, row_cap, d_calib, eng.d_kps, eng.d_desc,
+                                                                                                    lm, d_tri_lists, d_tri_counts, tri_list_stride);
+                eng.launches++;
+            }
+            CK(cudaStreamWaitEvent(eng.stream, ev_join, 0));
+        }
         eng.mark(ST_DOWNLOAD);
         CK(cudaGetLastError());
         n_triangulated = n_frames;
