@@ -230,6 +230,8 @@ __global__ void __launch_bounds__(256) blur_kernel(const __grid_constant__ McsPl
 // ring offsets of FAST 9/16 in OpenCV order: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
 // ------------------------------------------------------------------------------------------------------------
 #define MCS_FAST_NT 128
+#define MCS_FAST_TPW 21  // tile pitch in 32-bit words: sub-image <= 75 px + 1 + staging slack (compile-time so ring offsets are immediates)
+#define MCS_FAST_SP 72   // score tile pitch (bytes)
 
 // One polarity only (sgn = +1: ring brighter than the centre, -1: darker): max over the 16 arcs of min over the arc of
 // sgn * (ring - v), minus 1.  Ring pixels are packed as ANTIPODAL pairs P_k = (e_k, e_{k+8}), e = 256 + sgn * (ring - v), so that
@@ -275,7 +277,7 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
     uint8_t* s_flags = s_fast + P.fast_ofs_flags;
     uint16_t* s_queue = reinterpret_cast<uint16_t*>(s_fast + P.fast_ofs_queue);
     uint32_t* s_surv = reinterpret_cast<uint32_t*>(s_fast + P.fast_ofs_surv);
-    const int TPW = P.fast_tpw, TP = TPW * 4, SP = P.fast_sp;
+    constexpr int TPW = MCS_FAST_TPW, TP = TPW * 4, SP = MCS_FAST_SP;
     const int img = blockIdx.y;
     int level = 0;
 #pragma unroll 1
@@ -317,8 +319,8 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
         for (int t = threadIdx.x; t < (ih + 2) * (SP >> 2); t += MCS_FAST_NT) reinterpret_cast<uint32_t*>(s_score)[t] = 0;
         __syncthreads();
         // pass 1, every interior pixel, 4 per thread on packed 16-bit lanes: necessary condition for a 9-arc — of each opposite
-        // ring pair at least one pixel is on the arc, tested on the two axis pairs:
-        //   bright: min(max(up, down), max(left, right)) > v + th        dark: max(min(up, down), min(left, right)) < v - th
+        // ring pair at least one pixel is on the arc, tested on the axis and the diagonal pairs (4 of the 8):
+        //   bright: min over pairs of max(pair) > v + th        dark: max over pairs of min(pair) < v - th
         const uint32_t K1 = (uint32_t)(0x8000 - th - 1) * 0x00010001u;  // bit 15 of (a + K1 - b) per lane  <=>  a - b > th
         int my_count = 0;
         for (int gi = threadIdx.x; gi < ngroups; gi += MCS_FAST_NT) {
@@ -327,14 +329,22 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
             const uint32_t W0 = row[0], W1 = row[1], W2 = row[2];
             const uint32_t Up = row[1 - 3 * TPW], Dn = row[1 + 3 * TPW];
             const uint32_t Lf = __funnelshift_r(W0, W1, 8), Rt = __funnelshift_r(W1, W2, 24);
+            // diagonal ring pixels (+-2, +-2): rows y-2 and y+2, columns x-2 and x+2
+            const uint32_t A0 = row[-2 * TPW], A1 = row[1 - 2 * TPW], A2 = row[2 - 2 * TPW];
+            const uint32_t B0 = row[2 * TPW], B1 = row[1 + 2 * TPW], B2 = row[2 + 2 * TPW];
+            const uint32_t UL = __funnelshift_r(A0, A1, 16), UR = __funnelshift_r(A1, A2, 16);
+            const uint32_t DL = __funnelshift_r(B0, B1, 16), DR = __funnelshift_r(B1, B2, 16);
             uint32_t f = 0;
 #pragma unroll
             for (int hpair = 0; hpair < 2; hpair++) {
                 const uint32_t sel = hpair ? 0x4342u : 0x4140u;
                 const uint32_t c2 = __byte_perm(W1, 0, sel), u2 = __byte_perm(Up, 0, sel), d2 = __byte_perm(Dn, 0, sel);
                 const uint32_t l2 = __byte_perm(Lf, 0, sel), r2 = __byte_perm(Rt, 0, sel);
-                const uint32_t bmin = __vminu2(__vmaxu2(u2, d2), __vmaxu2(l2, r2));
-                const uint32_t dmax = __vmaxu2(__vminu2(u2, d2), __vminu2(l2, r2));
+                const uint32_t ul = __byte_perm(UL, 0, sel), dr = __byte_perm(DR, 0, sel);
+                const uint32_t ur = __byte_perm(UR, 0, sel), dl = __byte_perm(DL, 0, sel);
+                // the four opposite pairs (0,8) (4,12) (2,10) (6,14)
+                const uint32_t bmin = __vimin3_u16x2(__vminu2(__vmaxu2(u2, d2), __vmaxu2(l2, r2)), __vmaxu2(ul, dr), __vmaxu2(ur, dl));
+                const uint32_t dmax = __vimax3_u16x2(__vmaxu2(__vminu2(u2, d2), __vminu2(l2, r2)), __vminu2(ul, dr), __vminu2(ur, dl));
                 const uint32_t Bf = bmin + K1 - c2, Df = c2 + K1 - dmax;
                 const uint32_t t2 = ((Bf >> 15) & 0x00010001u) | ((Df >> 14) & 0x00020002u);
                 f |= ((t2 | (t2 >> 14)) & 0xFu) << (4 * hpair);
@@ -365,29 +375,48 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
             if (!f) continue;
             const int ly = (int)(((uint32_t)gi * mgG) >> 20), g = gi - ly * G;
             const uint32_t base = (uint32_t)((ly << 7) | (4 * g));
-            while (f) {
-                const int b = __ffs((int)f) - 1;
-                f &= f - 1;
-                s_queue[pos++] = (uint16_t)(((b & 1) << 14) | (base + (b >> 1)));
+#pragma unroll
+            for (int b = 0; b < 8; b++) {  // predicated stores: no divergent loop
+                if (f & (1u << b)) {
+                    s_queue[pos] = (uint16_t)(((b & 1) << 14) | (base + (b >> 1)));
+                    pos++;
+                }
             }
         }
         __syncthreads();
         // pass 2, queued (pixel, polarity) entries on dense warps: arc strength = cv::FAST's score; corner at th <=> strength >= th.
         // A pixel cannot be a bright and a dark corner at once (two 9-arcs do not fit in 16), so at most one entry per pixel scores.
-        for (int q = threadIdx.x; q < nq; q += MCS_FAST_NT) {
-            const int e = s_queue[q], ly = (e >> 7) & 0x7F, lx = e & 0x7F;
-            const uint8_t* c = reinterpret_cast<const uint8_t*>(s_tile) + (ly + 3) * TP + lx + 4;
-            const int sc = fast_strength_pol(c, TP, (e & 0x4000) ? -1 : 1);
-            if (sc >= th && sc > 0) {
-                s_score[(ly + 1) * SP + lx + 1] = (uint8_t)min(sc, 255);
-                s_queue[q] = (uint16_t)(e | 0x8000);
+        // Corners are re-queued densely at the front of s_queue (their slot is never ahead of an entry that is still unread: the
+        // barrier inside the round orders "everyone has read its entry" before "corner slots are written").
+        int ncorner = 0;
+        for (int q0 = 0; q0 < nq; q0 += MCS_FAST_NT) {
+            const int q = q0 + threadIdx.x;
+            int e = 0, sc = 0;
+            bool corner = false;
+            if (q < nq) {
+                e = s_queue[q];
+                const int ly = (e >> 7) & 0x7F, lx = e & 0x7F;
+                const uint8_t* c = reinterpret_cast<const uint8_t*>(s_tile) + (ly + 3) * TP + lx + 4;
+                sc = fast_strength_pol(c, TP, (e & 0x4000) ? -1 : 1);
+                corner = sc >= th && sc > 0;
+                if (corner) s_score[(ly + 1) * SP + lx + 1] = (uint8_t)min(sc, 255);
             }
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, corner);
+            if (lane == 0) s_wsum[warp] = __popc(m);
+            __syncthreads();
+            int ofs = ncorner + __popc(m & ((1u << lane) - 1));
+#pragma unroll
+            for (int w = 0; w < MCS_FAST_NT / 32; w++) {
+                const int ws = s_wsum[w];
+                if (w < warp) ofs += ws;
+                ncorner += ws;
+            }
+            if (corner) s_queue[ofs] = (uint16_t)(e & 0x3FFF);
+            __syncthreads();
         }
-        __syncthreads();
         // pass 3, corners only: strict-'>' 8-neighbour NMS inside the computed interior (scores outside count as 0)
-        for (int q = threadIdx.x; q < nq; q += MCS_FAST_NT) {
+        for (int q = threadIdx.x; q < ncorner; q += MCS_FAST_NT) {
             const int e = s_queue[q];
-            if (!(e & 0x8000)) continue;
             const int ly = (e >> 7) & 0x7F, lx = e & 0x7F;
             const uint8_t* qp = &s_score[(ly + 1) * SP + lx + 1];
             const int sc = qp[0];

@@ -450,10 +450,11 @@ template <int NV>
 __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double* z) {
     constexpr int M = 3 * NV, N = 4 + NV, T = MCS_TRI_NT;
     const double eps = 2.220446049250313e-16;
+    // only rows 0..3 of V are ever read (z = V[0..3][best]) and a rotation updates every row independently, so V is kept as 4 x N
 #pragma unroll 1
-    for (int i = 0; i < N * N; i++) sV[i * T] = 0;
-#pragma unroll 1
-    for (int i = 0; i < N; i++) sV[(i * N + i) * T] = 1;
+    for (int i = 0; i < 4 * N; i++) sV[i * T] = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) sV[(i * N + i) * T] = 1;
 #pragma unroll 1
     for (int sweep = 0; sweep < 60; sweep++) {
         bool changed = false;
@@ -485,7 +486,7 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
                     sA[(k * N + q) * T] = sn * xk[k] + c * yk[k];
                 }
 #pragma unroll
-                for (int k = 0; k < N; k++) {
+                for (int k = 0; k < 4; k++) {
                     const double x = sV[(k * N + p) * T], y = sV[(k * N + q) * T];
                     sV[(k * N + p) * T] = c * x - sn * y;
                     sV[(k * N + q) * T] = sn * x + c * y;
@@ -623,7 +624,7 @@ __global__ void __launch_bounds__(128) tri_solve2_kernel(int num_cams, int kp_ca
     tri_solve_class<2, 128>(nullptr, blockIdx.x, gridDim.x, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride);
 }
 
-// One launch for every view count >= 3: blockIdx.y = view-count class (NV = 3 + y), blockIdx.x = persistent block of that class,
+// One launch for every view count >= 3: blockIdx.y = view-count class (NV = num_cams - y), blockIdx.x = persistent block of that class,
 // so the long, latency-bound solves of the different classes overlap instead of queueing behind each other.
 __global__ void __launch_bounds__(MCS_TRI_NT) tri_solve_kernel(int num_cams, int kp_cap, int row_cap, const CalibDev* __restrict__ calib,
                                                                const KeypointPod* __restrict__ kps, const uint8_t* __restrict__ desc,
@@ -631,7 +632,7 @@ __global__ void __launch_bounds__(MCS_TRI_NT) tri_solve_kernel(int num_cams, int
                                                                const int* __restrict__ list_count, int list_stride) {
     extern __shared__ __align__(16) double s_tri[];
     const int b = blockIdx.x, nb = gridDim.x;
-    switch (blockIdx.y + 3) {
+    switch (num_cams - (int)blockIdx.y) {  // largest systems first: they run longest
         case 3: tri_solve_class<3>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
         case 4: tri_solve_class<4>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
         case 5: tri_solve_class<5>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;

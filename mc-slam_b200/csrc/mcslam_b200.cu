@@ -190,8 +190,9 @@ bool build_plan(const OrbTables& T, int width, int height, int use_angle, McsPla
         for (int l = 0; l < T.nlevels; l++)
             if (P.L[l].n_cols > 0) { cwm = std::max(cwm, P.L[l].w_cell + 6); chm = std::max(chm, P.L[l].h_cell + 6); }
         const int iwm = cwm - 6, ihm = chm - 6, G = (iwm + 3) / 4;
-        P.fast_tpw = (G + 3) | 1;  // words g .. g+2 of the widest row plus the second word of the staging funnel; odd pitch
-        P.fast_sp = align_up(iwm + 2, 4);
+        P.fast_tpw = MCS_FAST_TPW;  // compile-time pitches; only the row counts follow the plan
+        P.fast_sp = MCS_FAST_SP;
+        if (G + 2 > MCS_FAST_TPW || iwm + 2 > MCS_FAST_SP) { set_err("internal: FAST cell wider than the tile pitch"); return false; }
         int o = align_up(P.fast_tpw * 4 * chm, 16);
         P.fast_ofs_score = o; o += align_up(P.fast_sp * (ihm + 2), 16);
         P.fast_ofs_flags = o; o += align_up(G * ihm, 16);
@@ -791,7 +792,7 @@ struct mcs_rig {
         return 0;
     }
 
-    static size_t tri_smem(int nv) { return nv <= 2 ? 0 : (size_t)(3 * nv * (4 + nv) + (4 + nv) * (4 + nv)) * sizeof(double) * MCS_TRI_NT; }
+    static size_t tri_smem(int nv) { return nv <= 2 ? 0 : (size_t)(3 * nv * (4 + nv) + 4 * (4 + nv)) * sizeof(double) * MCS_TRI_NT; }
     int set_tri_smem() {
         CK(cudaFuncSetAttribute(mcs::tri_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem(MCS_MAX_CAMS)));
         return 0;
@@ -845,7 +846,7 @@ struct mcs_rig {
             eng.launches++;
             CK(cudaEventRecord(ev_join, stream2));
             if (C >= 3) {
-                mcs::tri_solve_kernel<<<dim3(sm_count, C - 2), MCS_TRI_NT, tri_smem(C), eng.stream>>>(C, kp_cap, row_cap, d_calib, eng.d_kps, eng.d_desc,
+                mcs::tri_solve_kernel<<<dim3(sm_count * 2, C - 2), MCS_TRI_NT, tri_smem(C), eng.stream>>>(C, kp_cap, row_cap, d_calib, eng.d_kps, eng.d_desc,
                                                                                                     lm, d_tri_lists, d_tri_counts, tri_list_stride);
                 eng.launches++;
             }
