@@ -36,7 +36,7 @@ EXPORTS = [
     "mcs_rig_brute_force_match", "mcs_rig_compute_intra_matches", "mcs_rig_get_intra_matches", "mcs_rig_triangulate",
     "mcs_rig_triangulate_device_masks", "mcs_rig_get_landmarks", "mcs_rig_triangulate_nview", "mcs_rig_triangulate_pair", "mcs_rig_process",
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
-    "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
+    "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned",
 ]
 
@@ -96,6 +96,7 @@ def lib():
     L.mcs_rig_stage_times.argtypes = [vp, vp]
     L.mcs_rig_set_profiling.argtypes = [vp, ci]
     L.mcs_rig_timer_start.argtypes = [vp]
+    L.mcs_rig_set_chunk_frames.argtypes = [vp, ci]
     L.mcs_rig_timer_stop.argtypes = [vp, vp]
     L.mcs_rig_download_level.argtypes = [vp, ci, ci, ci, ci, vp, ci]
     L.mcs_rig_level_size.argtypes = [vp, ci, vp, vp]
@@ -361,6 +362,9 @@ class RigFrames:
     @property
     def kernel_launches(self):
         return lib().mcs_rig_kernel_launches(self.hd)
+
+    def set_chunk_frames(self, n):
+        _check(lib().mcs_rig_set_chunk_frames(self.hd, int(n)), "mcs_rig_set_chunk_frames")
 
     def timer_start(self):
         _check(lib().mcs_rig_timer_start(self.hd), "mcs_rig_timer_start")

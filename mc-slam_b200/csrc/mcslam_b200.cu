@@ -357,81 +357,105 @@ struct Engine {
         }
     }
 
-    // Stage A on images already described by `set`.  Leaves keypoints/descriptors/counts on the device.
-    int run(const mcs::ImageSet& set, int n, const int lap[2]) {
-        if (n < 1 || n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
-        last_set = set; last_n = n;
+    // Stage A on images [img0, img0 + n) of the workspace, already described by `set0` (the set of image 0), on stream `st`
+    // (0 = the handle's main stream).  Leaves keypoints/descriptors/counts on the device.
+    int run(const mcs::ImageSet& set0, int n, const int lap[2], int img0 = 0, cudaStream_t st = nullptr) {
+        if (n < 1 || img0 < 0 || img0 + n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+        if (!st) st = stream;
+        last_set = set0; last_n = img0 == 0 ? n : std::max(last_n, img0 + n);
         const McsPlan& P = plan;
+        mcs::ImageSet set = set0;
+        set.l0 = set0.l0 + (size_t)img0 * set0.l0_stride;
+        set.pyr = set0.pyr + (size_t)img0 * P.pyr_stride;
+        uint32_t* cand = d_cand + (size_t)img0 * P.cand_stride;
+        uint16_t* knode = d_knode + (size_t)img0 * P.cand_stride;
+        uint32_t* sel = d_sel + (size_t)img0 * P.sel_stride;
+        int *cand_count = d_cand_count + (size_t)img0 * P.nlevels, *sel_count = d_sel_count + (size_t)img0 * P.nlevels;
+        uint8_t* blur = d_blur + (size_t)img0 * P.pyr_stride;
+        mcs::KeypointPod *kps = d_kps + (size_t)img0 * P.kp_cap, *kps_tmp = d_kps_tmp + (size_t)img0 * P.kp_cap;
+        uint8_t *desc = d_desc + (size_t)img0 * P.kp_cap * 32, *desc_tmp = d_desc_tmp + (size_t)img0 * P.kp_cap * 32;
+        int *kp_count = d_kp_count + img0, *mono = d_mono + img0;
         mark(ST_PYRAMID);
-        CK(cudaMemsetAsync(d_cand_count, 0, (size_t)n * P.nlevels * sizeof(int), stream));
+        CK(cudaMemsetAsync(cand_count, 0, (size_t)n * P.nlevels * sizeof(int), st));
         for (int l = 1; l < P.nlevels; l++) {
             dim3 b(32, 8), g((P.L[l].w + 127) / 128, (P.L[l].h + 7) / 8, n);
-            if (T.scale_factor_f <= 2.0f) mcs::resize_level_words_kernel<<<g, b, 0, stream>>>(P, set, l, d_xtab, d_ytab);
-            else mcs::resize_level_kernel<<<g, b, 0, stream>>>(P, set, l, d_xtab, d_ytab);
+            if (T.scale_factor_f <= 2.0f) mcs::resize_level_words_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
+            else mcs::resize_level_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
             launches++;
         }
         mark(ST_FAST);
         if (P.n_cells > 0) {
-            mcs::fast_cells_kernel<<<dim3(P.n_cells, n), MCS_FAST_NT, P.fast_smem_bytes, stream>>>(P, set, d_cand, d_cand_count);
+            mcs::fast_cells_kernel<<<dim3(P.n_cells, n), MCS_FAST_NT, P.fast_smem_bytes, st>>>(P, set, cand, cand_count);
             launches++;
         }
         mark(ST_OCTREE);
-        mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, stream>>>(P, d_cand, d_cand_count, d_knode, d_sel, d_sel_count);
+        mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
         launches++;
         mark(ST_BLUR);
-        mcs::blur_kernel<<<dim3(P.n_tiles, n), 256, 0, stream>>>(P, set, d_blur);
+        mcs::blur_kernel<<<dim3(P.n_tiles, n), 256, 0, st>>>(P, set, blur);
         launches++;
         mark(ST_DESCRIBE);
-        mcs::describe_kernel<<<dim3((P.kp_cap + MCS_DESC_WARPS - 1) / MCS_DESC_WARPS, n), MCS_DESC_WARPS * 32, 0, stream>>>(
-            P, set, d_blur, d_sel, d_sel_count, d_kps, d_desc, d_kp_count);
+        mcs::describe_kernel<<<dim3((P.kp_cap + MCS_DESC_WARPS - 1) / MCS_DESC_WARPS, n), MCS_DESC_WARPS * 32, 0, st>>>(
+            P, set, blur, sel, sel_count, kps, desc, kp_count);
         launches++;
         // every keypoint has pt.x >= 19, so a lapping area ending before 19 (the callers' {0,0}) selects nothing (:1153)
         const bool lap_active = lap && lap[1] >= lap[0] && lap[1] >= MCS_EDGE_THRESHOLD;
         if (lap_active) {
-            mcs::lapping_permute_kernel<<<n, 256, 0, stream>>>(P, lap[0], lap[1], d_kps, d_desc, d_kps_tmp, d_desc_tmp, d_kp_count, d_mono);
+            mcs::lapping_permute_kernel<<<n, 256, 0, st>>>(P, lap[0], lap[1], kps, desc, kps_tmp, desc_tmp, kp_count, mono);
             launches++;
         } else {
-            CK(cudaMemcpyAsync(d_mono, d_kp_count, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, stream));
+            CK(cudaMemcpyAsync(mono, kp_count, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
         }
         mark(ST_MATCH);
         CK(cudaGetLastError());
         return 0;
     }
 
-    // host images -> d_input (tight) -> ImageSet
-    int upload(const uint8_t* images, int n, int w, int h, int stride, size_t image_stride, mcs::ImageSet& set) {
-        if (n < 1 || n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+    // host images [img0, img0 + n) -> d_input (tight); `set` describes image 0 of the workspace
+    int upload(const uint8_t* images, int n, int w, int h, int stride, size_t image_stride, mcs::ImageSet& set, int img0 = 0,
+               cudaStream_t st = nullptr) {
+        if (n < 1 || img0 + n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+        if (!st) st = stream;
         mark(ST_UPLOAD);
+        uint8_t* dst = d_input + (size_t)img0 * w * h;
         if (stride == w && image_stride == (size_t)w * h) {
-            CK(cudaMemcpyAsync(d_input, images, (size_t)n * w * h, cudaMemcpyHostToDevice, stream));
+            CK(cudaMemcpyAsync(dst, images, (size_t)n * w * h, cudaMemcpyHostToDevice, st));
         } else {
             for (int i = 0; i < n; i++)
-                CK(cudaMemcpy2DAsync(d_input + (size_t)i * w * h, w, images + i * image_stride, stride, w, h, cudaMemcpyHostToDevice, stream));
+                CK(cudaMemcpy2DAsync(dst + (size_t)i * w * h, w, images + i * image_stride, stride, w, h, cudaMemcpyHostToDevice, st));
         }
-        return make_set(d_input, n, w, h, set);
+        return make_set(d_input, n, w, h, set, img0, st);
     }
-    // device-resident tight images; re-pitched only when 32-bit row loads would be misaligned
-    int make_set(const uint8_t* d_images, int n, int w, int h, mcs::ImageSet& set) {
+    // device-resident tight images (d_images = image 0); re-pitched only when 32-bit row loads would be misaligned
+    int make_set(const uint8_t* d_images, int n, int w, int h, mcs::ImageSet& set, int img0 = 0, cudaStream_t st = nullptr) {
+        if (!st) st = stream;
         set.pyr = d_pyr;
         if ((w & 3) == 0 && ((uintptr_t)d_images & 15) == 0) {
             set.l0 = d_images; set.l0_pitch = w; set.l0_stride = (size_t)w * h;
         } else {
-            for (int i = 0; i < n; i++)
+            for (int i = img0; i < img0 + n; i++)
                 CK(cudaMemcpy2DAsync(d_pyr + (size_t)i * plan.pyr_stride + plan.L[0].plane_ofs, plan.L[0].pitch, d_images + (size_t)i * w * h, w, w,
-                                     h, cudaMemcpyDeviceToDevice, stream));
+                                     h, cudaMemcpyDeviceToDevice, st));
             set.l0 = d_pyr + plan.L[0].plane_ofs; set.l0_pitch = plan.L[0].pitch; set.l0_stride = plan.pyr_stride;
         }
         return 0;
     }
 
+    // device -> pinned host mirrors for images [img0, img0 + n); asynchronous on `st`
+    int download_features_async(int img0, int n, cudaStream_t st) {
+        const size_t nl = plan.nlevels, cap = plan.kp_cap;
+        CK(cudaMemcpyAsync(h_kp_count + img0, d_kp_count + img0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_mono + img0, d_mono + img0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_sel_count + img0 * nl, d_sel_count + img0 * nl, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_cand_count + img0 * nl, d_cand_count + img0 * nl, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_kps + img0 * cap, d_kps + img0 * cap, (size_t)n * cap * sizeof(mcs::KeypointPod), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_desc + img0 * cap * 32, d_desc + img0 * cap * 32, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, st));
+        return 0;
+    }
     int download_features(int n) {
         mark(ST_DOWNLOAD);
-        CK(cudaMemcpyAsync(h_kp_count, d_kp_count, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, stream));
-        CK(cudaMemcpyAsync(h_mono, d_mono, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, stream));
-        CK(cudaMemcpyAsync(h_sel_count, d_sel_count, (size_t)n * plan.nlevels * sizeof(int), cudaMemcpyDeviceToHost, stream));
-        CK(cudaMemcpyAsync(h_cand_count, d_cand_count, (size_t)n * plan.nlevels * sizeof(int), cudaMemcpyDeviceToHost, stream));
-        CK(cudaMemcpyAsync(h_kps, d_kps, (size_t)n * plan.kp_cap * sizeof(mcs::KeypointPod), cudaMemcpyDeviceToHost, stream));
-        CK(cudaMemcpyAsync(h_desc, d_desc, (size_t)n * plan.kp_cap * 32, cudaMemcpyDeviceToHost, stream));
+        int rc = download_features_async(0, n, stream);
+        if (rc) return rc;
         mark(ST_COUNT);
         CK(cudaStreamSynchronize(stream));
         collect_profile();
@@ -679,10 +703,18 @@ struct mcs_rig {
     double* d_F = nullptr;
     float* d_sigma2 = nullptr;
     int *d_match_train = nullptr, *d_match_tmp = nullptr, *d_rows = nullptr, *d_row_count = nullptr;
-    int *d_tri_lists = nullptr, *d_tri_counts = nullptr;  // triangulation work lists per view count
+    // A slot = what one in-flight chunk of frames needs for itself: a stream, the forked stream of the 2-view solver with its
+    // fork/join events, and the triangulation work lists.  Slot 0 runs on the handle's main stream.
+    struct Slot {
+        cudaStream_t st = nullptr, st2 = nullptr;
+        cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
+        int *d_tri_lists = nullptr, *d_tri_counts = nullptr;
+    };
+    static constexpr int NSLOT = 3;
+    Slot slots[NSLOT];
+    cudaEvent_t ev_begin = nullptr;
     int tri_list_stride = 0, sm_count = 148;
-    cudaStream_t stream2 = nullptr;  // forked for the 2-view solver
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int chunk_frames = 16;  // frames per pipelined chunk (0 = no chunking)
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
     size_t masks_bytes = 0;
@@ -703,10 +735,16 @@ struct mcs_rig {
         cudaSetDevice(eng.device);
         cudaStreamSynchronize(eng.stream);
         if (t0) { cudaEventDestroy(t0); cudaEventDestroy(t1); }
-        if (stream2) { cudaStreamSynchronize(stream2); cudaStreamDestroy(stream2); }
-        if (ev_fork) { cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); }
+        for (int k = 0; k < NSLOT; k++) {
+            Slot& S = slots[k];
+            if (S.st && k > 0) { cudaStreamSynchronize(S.st); cudaStreamDestroy(S.st); }
+            if (S.st2) { cudaStreamSynchronize(S.st2); cudaStreamDestroy(S.st2); }
+            if (S.ev_fork) { cudaEventDestroy(S.ev_fork); cudaEventDestroy(S.ev_join); cudaEventDestroy(S.ev_done); }
+            cudaFree(S.d_tri_lists); cudaFree(S.d_tri_counts);
+        }
+        if (ev_begin) cudaEventDestroy(ev_begin);
         cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
-        cudaFree(d_row_count); cudaFree(d_tri_lists); cudaFree(d_tri_counts); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
+        cudaFree(d_row_count); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
         cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks);
         cudaFreeHost(h_rows); cudaFreeHost(h_row_count); cudaFreeHost(h_lm_rows); cudaFreeHost(h_n_views); cudaFreeHost(h_rep);
         cudaFreeHost(h_n_acc); cudaFreeHost(h_match_tmp); cudaFreeHost(h_accepted); cudaFreeHost(h_xyz); cudaFreeHost(h_uv);
@@ -758,13 +796,21 @@ struct mcs_rig {
         CK(cudaMalloc(&d_rows, rw * C * sizeof(int)));
         CK(cudaMalloc(&d_row_count, F * sizeof(int)));
         tri_list_stride = (int)rw;
-        CK(cudaMalloc(&d_tri_lists, (size_t)(MCS_MAX_CAMS + 1) * rw * sizeof(int)));
-        CK(cudaMalloc(&d_tri_counts, (MCS_MAX_CAMS + 1) * sizeof(int)));
         CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, eng.device));
         if ((rc = set_tri_smem())) return rc;
-        CK(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ev_begin, cudaEventDisableTiming));
+        for (int k = 0; k < NSLOT; k++) {
+            Slot& S = slots[k];
+            if (k == 0) S.st = eng.stream;
+            else CK(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking));
+            CK(cudaStreamCreateWithFlags(&S.st2, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&S.ev_fork, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&S.ev_join, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&S.ev_done, cudaEventDisableTiming));
+            CK(cudaMalloc(&S.d_tri_lists, (size_t)(MCS_MAX_CAMS + 1) * rw * sizeof(int)));
+            CK(cudaMalloc(&S.d_tri_counts, (MCS_MAX_CAMS + 1) * sizeof(int)));
+        }
+        if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
         CK(cudaMalloc(&lm.rows, rw * C * sizeof(int)));
         CK(cudaMalloc(&lm.accepted, rw));
         CK(cudaMalloc(&lm.n_views, rw * sizeof(int)));
@@ -799,63 +845,99 @@ struct mcs_rig {
     }
     void invalidate() { feat_host = rows_host = lm_host = false; }
 
-    int stage_extract(const mcs::ImageSet& set, int n_frames) {
+    // The three stages for frames [f0, f0 + nf) of the workspace on slot `k` (0 = main stream).  Every kernel indexes frames
+    // relative to the pointers it is given, so a chunk is the same launch with offset pointers.
+    int stage_extract(const mcs::ImageSet& set, int n_frames, int f0 = 0, int k = 0) {
         static const int lap[2] = {0, 0};  // vLapping = {0,0} (MultiCameraFrame.cpp:235, :274)
-        int rc = eng.run(set, n_frames * C, lap);
+        int rc = eng.run(set, n_frames * C, lap, f0 * C, slots[k].st);
         if (rc) return rc;
-        n_extracted = n_frames; n_matched = n_triangulated = 0;
+        n_extracted = f0 == 0 ? n_frames : std::max(n_extracted, f0 + n_frames);
+        if (f0 == 0) n_matched = n_triangulated = 0;
         invalidate();
         return 0;
     }
-    int stage_match(int n_frames, int old, float dist_thresh, float ratio) {
-        if (n_frames < 1 || n_frames > n_extracted) { set_err("intra-match before extract"); return MCS_ERR_STATE; }
+    int stage_match(int n_frames, int old, float dist_thresh, float ratio, int f0 = 0, int k = 0) {
+        if (n_frames < 1 || f0 + n_frames > n_extracted) { set_err("intra-match before extract"); return MCS_ERR_STATE; }
+        cudaStream_t st = slots[k].st;
+        const int NP = std::max(pairs.n_pairs, 1);
+        int* match_train = d_match_train + (size_t)f0 * NP * kp_cap;
         eng.mark(ST_MATCH);
         if (pairs.n_pairs > 0) {
             dim3 g((kp_cap + MCS_MATCH_NT - 1) / MCS_MATCH_NT, pairs.n_pairs, n_frames);
-            mcs::hamming_match_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, eng.stream>>>(C, kp_cap, pairs, 0, eng.d_desc, eng.d_kp_count,
-                                                                                             dist_thresh, ratio, d_match_train, nullptr, nullptr);
+            mcs::hamming_match_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, st>>>(C, kp_cap, pairs, f0, eng.d_desc, eng.d_kp_count, dist_thresh,
+                                                                                    ratio, match_train, nullptr, nullptr);
             eng.launches++;
         }
         eng.mark(ST_MERGE);
-        mcs::merge_kernel<<<n_frames, 128, merge_smem, eng.stream>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count, d_match_train, eng.d_kps, old,
-                                                                     d_F, d_sigma2, d_rows, d_row_count, merge_rows_smem ? 1 : 0);
+        mcs::merge_kernel<<<n_frames, 128, merge_smem, st>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
+                                                             eng.d_kps + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
+                                                             d_rows + (size_t)f0 * row_cap * C, d_row_count + f0, merge_rows_smem ? 1 : 0);
         eng.launches++;
         eng.mark(ST_TRIANG);
         CK(cudaGetLastError());
-        n_matched = n_frames; n_triangulated = 0;
+        n_matched = f0 == 0 ? n_frames : std::max(n_matched, f0 + n_frames);
+        if (f0 == 0) n_triangulated = 0;
         rows_host = lm_host = false;
         return 0;
     }
-    int stage_triangulate(int n_frames, const float* d_mask_ptr) {
-        if (n_frames < 1 || n_frames > n_matched) { set_err("triangulate before intra-match"); return MCS_ERR_STATE; }
+    mcs::LandmarkOut lm_at(int f0) const {
+        mcs::LandmarkOut o = lm;
+        const size_t r = (size_t)f0 * row_cap;
+        o.rows += r * C; o.accepted += r; o.n_views += r; o.xyz += r * 3; o.uv_ref += r * 2; o.rep_cam += r; o.n_accepted += f0;
+        return o;
+    }
+    int stage_triangulate(int n_frames, const float* d_mask_ptr, int f0 = 0, int k = 0) {
+        if (n_frames < 1 || f0 + n_frames > n_matched) { set_err("triangulate before intra-match"); return MCS_ERR_STATE; }
+        Slot& S = slots[k];
+        const mcs::LandmarkOut out = lm_at(f0);
+        const mcs::KeypointPod* kps = eng.d_kps + (size_t)f0 * C * kp_cap;
+        const uint8_t* desc = eng.d_desc + (size_t)f0 * C * kp_cap * 32;
+        const float* mask = d_mask_ptr ? d_mask_ptr + (size_t)f0 * C * cfg.width * cfg.height : nullptr;
         eng.mark(ST_TRIANG);
-        CK(cudaMemsetAsync(lm.n_accepted, 0, n_frames * sizeof(int), eng.stream));
-        CK(cudaMemsetAsync(d_tri_counts, 0, (MCS_MAX_CAMS + 1) * sizeof(int), eng.stream));
+        CK(cudaMemsetAsync(out.n_accepted, 0, n_frames * sizeof(int), S.st));
+        CK(cudaMemsetAsync(S.d_tri_counts, 0, (MCS_MAX_CAMS + 1) * sizeof(int), S.st));
         dim3 g((row_cap + 127) / 128, n_frames);
-        mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, eng.stream>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows, d_row_count, eng.d_kps,
-                                                                          d_mask_ptr, lm, d_tri_lists, d_tri_counts, tri_list_stride);
+        mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, S.st>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows + (size_t)f0 * row_cap * C,
+                                                                    d_row_count + f0, kps, mask, out, S.d_tri_lists, S.d_tri_counts, tri_list_stride);
         eng.launches++;
-        // 2-view rows on a forked stream, every larger view count in one launch (blockIdx.y = class) on the main stream; persistent
-        // grid-stride blocks because the list lengths live on the device
+        // 2-view rows on a forked stream, every larger view count in one launch (blockIdx.y = class) on the slot's stream;
+        // persistent grid-stride blocks because the list lengths live on the device
         if (C >= 2) {
-            CK(cudaEventRecord(ev_fork, eng.stream));
-            CK(cudaStreamWaitEvent(stream2, ev_fork, 0));
+            CK(cudaEventRecord(S.ev_fork, S.st));
+            CK(cudaStreamWaitEvent(S.st2, S.ev_fork, 0));
             const int nb2 = std::max(1, std::min(sm_count * 8, (n_frames * row_cap + 127) / 128));
-            mcs::tri_solve2_kernel<<<nb2, 128, 0, stream2>>>(C, kp_cap, row_cap, d_calib, eng.d_kps, eng.d_desc, lm, d_tri_lists, d_tri_counts,
-                                                           tri_list_stride);
+            mcs::tri_solve2_kernel<<<nb2, 128, 0, S.st2>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists, S.d_tri_counts, tri_list_stride);
             eng.launches++;
-            CK(cudaEventRecord(ev_join, stream2));
+            CK(cudaEventRecord(S.ev_join, S.st2));
             if (C >= 3) {
-                mcs::tri_solve_kernel<<<dim3(sm_count * 2, C - 2), MCS_TRI_NT, tri_smem(C), eng.stream>>>(C, kp_cap, row_cap, d_calib, eng.d_kps, eng.d_desc,
-                                                                                                    lm, d_tri_lists, d_tri_counts, tri_list_stride);
+                mcs::tri_solve_kernel<<<dim3(sm_count * 2, C - 2), MCS_TRI_NT, tri_smem(C), S.st>>>(C, kp_cap, row_cap, d_calib, kps, desc, out,
+                                                                                                  S.d_tri_lists, S.d_tri_counts, tri_list_stride);
                 eng.launches++;
             }
-            CK(cudaStreamWaitEvent(eng.stream, ev_join, 0));
+            CK(cudaStreamWaitEvent(S.st, S.ev_join, 0));
         }
         eng.mark(ST_DOWNLOAD);
         CK(cudaGetLastError());
-        n_triangulated = n_frames;
+        n_triangulated = f0 == 0 ? n_frames : std::max(n_triangulated, f0 + n_frames);
         lm_host = false;
+        return 0;
+    }
+    int download_rows_async(int f0, int nf, cudaStream_t st) {
+        CK(cudaMemcpyAsync(h_row_count + f0, d_row_count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_rows + (size_t)f0 * row_cap * C, d_rows + (size_t)f0 * row_cap * C, (size_t)nf * row_cap * C * sizeof(int),
+                           cudaMemcpyDeviceToHost, st));
+        return 0;
+    }
+    int download_landmarks_async(int f0, int nf, cudaStream_t st) {
+        const size_t o = (size_t)f0 * row_cap, rw = (size_t)nf * row_cap;
+        CK(cudaMemcpyAsync(h_row_count + f0, d_row_count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_n_acc + f0, lm.n_accepted + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_lm_rows + o * C, lm.rows + o * C, rw * C * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_accepted + o, lm.accepted + o, rw, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_n_views + o, lm.n_views + o, rw * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_xyz + o * 3, lm.xyz + o * 3, rw * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_uv + o * 2, lm.uv_ref + o * 2, rw * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_rep + o, lm.rep_cam + o, rw * sizeof(int), cudaMemcpyDeviceToHost, st));
         return 0;
     }
     int upload_masks(const float* masks, int n_frames, const float** out) {
@@ -884,9 +966,12 @@ struct mcs_rig {
     int ensure_rows() {
         if (rows_host) return 0;
         if (n_matched < 1) { set_err("no intra-matches computed"); return MCS_ERR_STATE; }
-        CK(cudaMemcpyAsync(h_row_count, d_row_count, n_matched * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
-        CK(cudaMemcpyAsync(h_rows, d_rows, (size_t)n_matched * row_cap * C * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+        int rc = download_rows_async(0, n_matched, eng.stream);
+        if (rc) return rc;
         CK(cudaStreamSynchronize(eng.stream));
+        return check_rows();
+    }
+    int check_rows() {
         for (int f = 0; f < n_matched; f++)
             if (h_row_count[f] > row_cap) { set_err("IntraMatch row table overflow"); return MCS_ERR_CAPACITY; }
         rows_host = true;
@@ -895,18 +980,62 @@ struct mcs_rig {
     int ensure_landmarks() {
         if (lm_host) return 0;
         if (n_triangulated < 1) { set_err("no triangulation computed"); return MCS_ERR_STATE; }
-        const size_t rw = (size_t)n_triangulated * row_cap;
-        cudaStream_t s = eng.stream;
-        CK(cudaMemcpyAsync(h_row_count, d_row_count, n_triangulated * sizeof(int), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_n_acc, lm.n_accepted, n_triangulated * sizeof(int), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_lm_rows, lm.rows, rw * C * sizeof(int), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_accepted, lm.accepted, rw, cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_n_views, lm.n_views, rw * sizeof(int), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_xyz, lm.xyz, rw * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_uv, lm.uv_ref, rw * 2 * sizeof(float), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(h_rep, lm.rep_cam, rw * sizeof(int), cudaMemcpyDeviceToHost, s));
-        CK(cudaStreamSynchronize(s));
+        int rc = download_landmarks_async(0, n_triangulated, eng.stream);
+        if (rc) return rc;
+        CK(cudaStreamSynchronize(eng.stream));
         lm_host = true;
+        return 0;
+    }
+
+    // Whole path for n_frames frames.  Large batches are cut into chunks of chunk_frames that rotate over NSLOT streams, so the
+    // upload of one chunk, the kernels of another and the download of a third overlap, and the latency-bound kernels (octree,
+    // merge, Jacobi) of one chunk hide behind the throughput-bound ones of its neighbours.  Everything is ordered against the
+    // main stream (fork at ev_begin, join at ev_done), so timers and synchronisation on the main stream cover all of it.
+    int process(const uint8_t* h_images, const uint8_t* d_images, const float* h_masks, const float* d_masks_in, int n_frames, int old,
+                bool download) {
+        const int w = cfg.width, h = cfg.height;
+        const float* dm = d_masks_in;
+        int rc;
+        if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
+        const bool chunked = chunk_frames > 0 && n_frames > chunk_frames && !eng.profiling;
+        const int step = chunked ? chunk_frames : n_frames;
+        mcs::ImageSet set{};
+        if (chunked) {
+            CK(cudaEventRecord(ev_begin, eng.stream));
+            for (int k = 1; k < NSLOT; k++) CK(cudaStreamWaitEvent(slots[k].st, ev_begin, 0));
+        }
+        int ci = 0;
+        for (int f0 = 0; f0 < n_frames; f0 += step, ci++) {
+            const int nf = std::min(step, n_frames - f0), k = chunked ? ci % NSLOT : 0;
+            cudaStream_t st = slots[k].st;
+            if (h_images) rc = eng.upload(h_images + (size_t)f0 * C * w * h, nf * C, w, h, w, (size_t)w * h, set, f0 * C, st);
+            else rc = eng.make_set(d_images, nf * C, w, h, set, f0 * C, st);
+            if (rc) return rc;
+            if ((rc = stage_extract(set, nf, f0, k))) return rc;
+            // computeIntraMatches(matches_map, old): BruteForceMatch(i, j, 75, 0.85, ...) (MultiCameraFrame.cpp:1118)
+            if ((rc = stage_match(nf, old, 75.f, 0.85f, f0, k))) return rc;
+            if ((rc = stage_triangulate(nf, dm, f0, k))) return rc;
+            if (download) {
+                if ((rc = eng.download_features_async(f0 * C, nf * C, st))) return rc;
+                if ((rc = download_rows_async(f0, nf, st))) return rc;
+                if ((rc = download_landmarks_async(f0, nf, st))) return rc;
+            }
+        }
+        if (chunked) {
+            for (int k = 1; k < NSLOT; k++) {
+                CK(cudaEventRecord(slots[k].ev_done, slots[k].st));
+                CK(cudaStreamWaitEvent(eng.stream, slots[k].ev_done, 0));
+            }
+        }
+        if (download) {
+            eng.mark(ST_COUNT);
+            CK(cudaStreamSynchronize(eng.stream));
+            eng.collect_profile();
+            if ((rc = eng.check_counts(n_frames * C))) return rc;
+            feat_host = true;
+            if ((rc = check_rows())) return rc;
+            lm_host = true;
+        }
         return 0;
     }
 };
@@ -1091,43 +1220,24 @@ int mcs_rig_triangulate_pair(mcs_rig* rig, int cam1, int cam2, const float* pts1
     return 0;
 }
 
-static int rig_process_common(mcs_rig* rig, const mcs::ImageSet& set, const float* d_masks, int n_frames, int old_epipolar, bool download) {
-    int rc = rig->stage_extract(set, n_frames);
-    if (rc) return rc;
-    // computeIntraMatches(matches_map, old): BruteForceMatch(i, j, 75, 0.85, ...) (MultiCameraFrame.cpp:1118)
-    if ((rc = rig->stage_match(n_frames, old_epipolar ? 1 : 0, 75.f, 0.85f))) return rc;
-    if ((rc = rig->stage_triangulate(n_frames, d_masks))) return rc;
-    if (download) {
-        if ((rc = rig->eng.download_features(n_frames * rig->C))) return rc;
-        rig->feat_host = true;
-        if ((rc = rig->ensure_rows())) return rc;
-        if ((rc = rig->ensure_landmarks())) return rc;
-    }
-    return 0;
-}
-
 int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* masks, int n_frames, int old_epipolar) {
     RIG_ENTER(rig);
     if (!images || n_frames < 1) return MCS_ERR_EMPTY;
     if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
     rig->eng.begin_profile();
-    mcs::ImageSet set;
-    const int w = rig->cfg.width, h = rig->cfg.height;
-    int rc = rig->eng.upload(images, n_frames * rig->C, w, h, w, (size_t)w * h, set);
-    if (rc) return rc;
-    const float* dm = nullptr;
-    if ((rc = rig->upload_masks(masks, n_frames, &dm))) return rc;
-    return rig_process_common(rig, set, dm, n_frames, old_epipolar, true);
+    return rig->process(images, nullptr, masks, nullptr, n_frames, old_epipolar ? 1 : 0, true);
 }
 int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar) {
     RIG_ENTER(rig);
     if (!d_images || n_frames < 1) return MCS_ERR_EMPTY;
     if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
     rig->eng.begin_profile();
-    mcs::ImageSet set;
-    int rc = rig->eng.make_set((const uint8_t*)d_images, n_frames * rig->C, rig->cfg.width, rig->cfg.height, set);
-    if (rc) return rc;
-    return rig_process_common(rig, set, (const float*)d_masks, n_frames, old_epipolar, false);
+    return rig->process(nullptr, (const uint8_t*)d_images, nullptr, (const float*)d_masks, n_frames, old_epipolar ? 1 : 0, false);
+}
+int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames) {
+    if (!rig || chunk_frames < 0) return MCS_ERR_ARG;
+    rig->chunk_frames = chunk_frames;
+    return 0;
 }
 
 int mcs_rig_get_counts(mcs_rig* rig, int frame, int* kp_counts, int* n_rows, int* n_accepted) {

@@ -189,3 +189,49 @@ def test_cpp_adaptor_equals_oracle(tmp_path):
     got = np.array([[float(v) for v in l[2:5]] for l in lm])
     assert np.allclose(got, tri["xyz"][acc], rtol=1e-6, atol=1e-9)
     assert [int(l[1]) for l in lm] == tri["nviews"][acc].tolist()
+
+
+def test_chunked_pipeline_equals_single_chunk():
+    """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
+    -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""
+    import mcslam_b200 as M
+    from mcslam_b200 import binding as B
+    calib = M.synth.make_rig(3, 320, 240)
+    base = [M.synth.make_rig_frame(calib, 320, 240, frame_index=20 + i, n_rects=5) for i in range(3)]
+    frames = np.stack([np.roll(base[i % 3], 8 * (i // 3), axis=2) for i in range(7)])
+    masks = np.stack([M.synth.make_masks(3, 320, 240, frame_index=i) for i in range(7)])
+    rig = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=7)
+
+    def snapshot():
+        out = []
+        for f in range(7):
+            feats = [rig.features(f, c) for c in range(3)]
+            lm = rig.landmarks(f)
+            out.append((feats, rig.intra_matches(f), lm, rig.counts(f)))
+        return out
+
+    def same(a, b):
+        for (fa, ra, la, ca), (fb, rb, lb, cb) in zip(a, b):
+            for (ka, da), (kb, db) in zip(fa, fb):
+                assert (ka == kb).all() and np.array_equal(da, db)
+            assert np.array_equal(ra, rb)
+            for k in la:
+                assert np.array_equal(la[k], lb[k]), k
+            assert (ca[0] == cb[0]).all() and ca[1:] == cb[1:]
+
+    rig.set_chunk_frames(0)
+    rig.process(frames, masks=masks)
+    ref = snapshot()
+    assert sum(len(r[1]) for r in ref) > 100
+    rig.set_chunk_frames(2)
+    rig.process(frames, masks=masks)
+    same(ref, snapshot())
+    d_img = B.device_malloc(0, frames.nbytes)
+    B.device_upload(0, d_img, frames)
+    d_msk = B.device_malloc(0, masks.nbytes)
+    B.device_upload(0, d_msk, masks)
+    rig.set_chunk_frames(3)
+    rig.process_device(d_img, 7, d_masks=d_msk)
+    same(ref, snapshot())
+    B.device_free(0, d_img)
+    B.device_free(0, d_msk)
