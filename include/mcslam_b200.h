@@ -181,7 +181,7 @@ MCS_API int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* ma
 MCS_API int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar);
 
 /* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over three
- * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 16 (env MCS_CHUNK_FRAMES). */
+ * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
 MCS_API int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames);
 
 /* Compact per-frame summary copied back by mcs_rig_process: n keypoints per camera, M rows, accepted landmarks. */

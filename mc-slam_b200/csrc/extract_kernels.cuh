@@ -95,34 +95,36 @@ __global__ void __launch_bounds__(256) resize_level_words_kernel(const __grid_co
     uint8_t* dst = S.pyr + (size_t)img * P.pyr_stride + D.plane_ofs;
     const int2 yt = __ldg(&ytab[D.ytab_ofs + dy]);
     const int sh = Sv.h, sw = Sv.w;
-    int sy0 = yt.x, sy1 = yt.x + 1;
-    sy0 = sy0 < 0 ? 0 : (sy0 < sh ? sy0 : sh - 1);
-    sy1 = sy1 < 0 ? 0 : (sy1 < sh ? sy1 : sh - 1);
+    const int sy0 = min(max(yt.x, 0), sh - 1), sy1 = min(max(yt.x + 1, 0), sh - 1);
     const int b0 = (short)(yt.y & 0xFFFF), b1 = yt.y >> 16;
-    const uint32_t* r0 = reinterpret_cast<const uint32_t*>(src + (size_t)sy0 * spitch);
-    const uint32_t* r1 = reinterpret_cast<const uint32_t*>(src + (size_t)sy1 * spitch);
-    int2 xt[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) xt[k] = __ldg(&xtab[D.xtab_ofs + min(dx0 + k, D.w - 1)]);
+    const uint32_t* r0 = reinterpret_cast<const uint32_t*>(src + (uint32_t)(sy0 * spitch));
+    const uint32_t* r1 = reinterpret_cast<const uint32_t*>(src + (uint32_t)(sy1 * spitch));
+    // 4 table entries {sx, a0 | a1 << 16} as two 128-bit loads (xtab_ofs is even and the table is padded past the row end)
+    const int4* xp = reinterpret_cast<const int4*>(xtab + D.xtab_ofs + dx0);
+    const int4 xa = __ldg(xp), xb = __ldg(xp + 1);
+    const int sx[4] = {xa.x, xa.z, xb.x, xb.z};
+    const uint32_t cf[4] = {(uint32_t)xa.y, (uint32_t)xa.w, (uint32_t)xb.y, (uint32_t)xb.w};
     const int lastw = ((sw + 3) >> 2) - 1;
-    const int wi = xt[0].x >> 2, wi1 = min(wi + 1, lastw), wi2 = min(wi + 2, lastw);
+    const int wi = sx[0] >> 2, wi1 = min(wi + 1, lastw), wi2 = min(wi + 2, lastw);
     const uint32_t u0 = __ldg(r0 + wi), u1 = __ldg(r0 + wi1), u2 = __ldg(r0 + wi2);
     const uint32_t v0 = __ldg(r1 + wi), v1 = __ldg(r1 + wi1), v2 = __ldg(r1 + wi2);
     uint32_t outw = 0;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        const int o = xt[k].x - 4 * wi;  // 0 .. 10 for scale <= 2; bytes o, o+1 (o+1 beyond the row end only ever meets coefficient 0)
-        const int wsel = o >> 2;         // word holding byte o
-        const int sft = (o & 3) * 8;
-        const uint32_t pu = __funnelshift_r(wsel == 0 ? u0 : (wsel == 1 ? u1 : u2), wsel == 0 ? u1 : u2, sft);
-        const uint32_t pv = __funnelshift_r(wsel == 0 ? v0 : (wsel == 1 ? v1 : v2), wsel == 0 ? v1 : v2, sft);
-        const int h0 = (int)__dp2a_lo((unsigned)xt[k].y, pu, 0u);
-        const int h1 = (int)__dp2a_lo((unsigned)xt[k].y, pv, 0u);
+        // bytes o, o+1 of the 12 loaded ones (o <= 10 for scale <= 2; beyond the row end o+1 only ever meets coefficient 0):
+        // one PRMT on the word pair that holds them.  Pixels past the row end (table padding) give garbage that is never stored.
+        const int o = min(max(sx[k] - 4 * wi, 0), 10);
+        const bool hi = o >= 4;
+        const uint32_t selv = (uint32_t)((o & 3) + (o >= 8 ? 4 : 0)) * 0x11u + 0x10u;
+        const uint32_t pu = __byte_perm(hi ? u1 : u0, hi ? u2 : u1, selv);
+        const uint32_t pv = __byte_perm(hi ? v1 : v0, hi ? v2 : v1, selv);
+        const int h0 = (int)__dp2a_lo(cf[k], pu, 0u);
+        const int h1 = (int)__dp2a_lo(cf[k], pv, 0u);
         int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
         v = min(max(v, 0), 255);
         outw |= (uint32_t)v << (8 * k);
     }
-    *reinterpret_cast<uint32_t*>(dst + (size_t)dy * D.pitch + dx0) = outw;  // pitch % 64 == 0: row padding absorbs the tail
+    *reinterpret_cast<uint32_t*>(dst + (uint32_t)(dy * D.pitch + dx0)) = outw;  // pitch % 64 == 0: row padding absorbs the tail
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -675,6 +677,145 @@ __global__ void __launch_bounds__(MCS_DESC_WARPS * 32) describe_kernel(const __g
         }
         kp.size = (float)Lv.scaled_patch;
         kp.angle = angle;
+        kp.response = (float)mcs_oct::cand_score(rec);
+        kp.octave = level;
+        kp.class_id = -1;
+        kps[slot] = kp;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K2+K5 fused (shipped mode, angle 0): the un-steered pattern only reads blurred pixels at offsets -13..12 around a keypoint, and
+// keypoints sit >= 19 px inside the level, so the blurred 26 x 26 patch depends on the 32 x 32 input patch alone (no border
+// handling).  One warp per keypoint stages that patch (pre-shifted so that patch column 0 is byte 0 of a shared row), runs the
+// same bit-exact separable 7-tap filter as blur_kernel (DP4A rows, DP2A columns on vertical pairs) and samples the 256 tests
+// from shared memory: the blurred pyramid is neither written nor read (blur_kernel remains for the steered mode and observers).
+// ------------------------------------------------------------------------------------------------------------
+#define MCS_DESCF_WARPS 8
+__global__ void __launch_bounds__(MCS_DESCF_WARPS * 32) describe_fused_kernel(const __grid_constant__ McsPlan P, ImageSet S,
+                                                                              const uint32_t* __restrict__ sel,
+                                                                              const int* __restrict__ sel_count,
+                                                                              KeypointPod* __restrict__ kps, uint8_t* __restrict__ desc,
+                                                                              int* __restrict__ kp_count) {
+    __shared__ uint32_t s_in[MCS_DESCF_WARPS][32][8];                   // input patch rows -16..15, columns -16..15
+    __shared__ __align__(16) uint32_t s_pair[MCS_DESCF_WARPS][16][28];  // row-filtered patch as vertical pairs (row 2p | row 2p+1 << 16)
+    __shared__ __align__(4) uint8_t s_bl[MCS_DESCF_WARPS][26][28];      // blurred patch rows/columns -13..12
+    const int img = blockIdx.y;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int k = blockIdx.x * MCS_DESCF_WARPS + warp;  // output slot
+    int level = -1, before = 0, total = 0;
+#pragma unroll 1
+    for (int l = 0; l < P.nlevels; l++) {
+        const int c = max(sel_count[img * P.nlevels + l], 0);
+        if (level < 0 && k < total + c) {
+            level = l;
+            before = total;
+        }
+        total += c;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) kp_count[img] = min(total, P.kp_cap);
+    if (level < 0 || k >= P.kp_cap) return;  // warp-uniform
+    const McsLevel& Lv = P.L[level];
+    const uint32_t rec = sel[(size_t)img * P.sel_stride + Lv.sel_ofs + (k - before)];
+    const int px = mcs_oct::cand_x(rec) + MCS_MIN_BORDER, py = mcs_oct::cand_y(rec) + MCS_MIN_BORDER;  // :883-884
+    int pitch;
+    const uint8_t* im = level_ptr(P, S, img, level, pitch);
+    // stage: shared word (r, c) = image bytes (px - 16 + 4c) .. +3 of row py - 16 + r
+    {
+        const int gb = px - 16, aw = gb >> 2, sh = (gb & 3) * 8;
+        const uint32_t* g0 = reinterpret_cast<const uint32_t*>(im + (size_t)(py - 16) * pitch) + aw;
+        const int pw = pitch >> 2;
+        uint32_t lo[8], hi[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int idx = lane + 32 * i, r = idx >> 3, c = idx & 7;
+            const uint32_t* g = g0 + r * pw + c;
+            lo[i] = __ldg(g);
+            hi[i] = __ldg(g + 1);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int idx = lane + 32 * i;
+            s_in[warp][idx >> 3][idx & 7] = __funnelshift_r(lo[i], hi[i], sh);
+        }
+    }
+    __syncwarp();
+    const uint32_t wA = (uint32_t)c_gauss7[0] | ((uint32_t)c_gauss7[1] << 8) | ((uint32_t)c_gauss7[2] << 16) | ((uint32_t)c_gauss7[3] << 24);
+    const uint32_t wB = (uint32_t)c_gauss7[4] | ((uint32_t)c_gauss7[5] << 8) | ((uint32_t)c_gauss7[6] << 16);
+    // rows: output column j (0..25, patch column j - 13) = taps on bytes j .. j+6; item = (row pair p, 4 columns g)
+    for (int i = lane; i < 16 * 7; i += 32) {
+        const int p = i / 7, g = i - p * 7;
+        uint32_t hv[2][4];
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+            const uint32_t* row = s_in[warp][2 * p + rr];
+            const uint32_t W0 = row[g], W1 = row[g + 1], W2 = g < 6 ? row[g + 2] : 0u;  // columns 26, 27 are padding
+            hv[rr][0] = __dp4a(W1, wB, __dp4a(W0, wA, 0u));
+            hv[rr][1] = __dp4a(__funnelshift_r(W1, W2, 8), wB, __dp4a(__funnelshift_r(W0, W1, 8), wA, 0u));
+            hv[rr][2] = __dp4a(__funnelshift_r(W1, W2, 16), wB, __dp4a(__funnelshift_r(W0, W1, 16), wA, 0u));
+            hv[rr][3] = __dp4a(__funnelshift_r(W1, W2, 24), wB, __dp4a(__funnelshift_r(W0, W1, 24), wA, 0u));
+        }
+        uint4 o;
+        o.x = hv[0][0] | (hv[1][0] << 16);
+        o.y = hv[0][1] | (hv[1][1] << 16);
+        o.z = hv[0][2] | (hv[1][2] << 16);
+        o.w = hv[0][3] | (hv[1][3] << 16);
+        *reinterpret_cast<uint4*>(&s_pair[warp][p][4 * g]) = o;
+    }
+    __syncwarp();
+    {
+        const uint32_t k0 = c_gauss7[0], k1 = c_gauss7[1], k2 = c_gauss7[2], k3 = c_gauss7[3], k4 = c_gauss7[4], k5 = c_gauss7[5], k6 = c_gauss7[6];
+        const uint32_t e0 = k0 | (k1 << 8), e1 = k2 | (k3 << 8), e2 = k4 | (k5 << 8), e3 = k6;       // even output row 2q
+        const uint32_t o0 = k0 << 8, o1 = k1 | (k2 << 8), o2 = k3 | (k4 << 8), o3 = k5 | (k6 << 8);  // odd output row 2q + 1
+        // columns: output row y (0..25, patch row y - 13) = taps on filtered rows y .. y+6; item = (output row pair q, 4 columns g)
+        for (int i = lane; i < 13 * 7; i += 32) {
+            const int q = i / 7, g = i - q * 7;
+            const uint4 a = *reinterpret_cast<const uint4*>(&s_pair[warp][q][4 * g]);
+            const uint4 b = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 1][4 * g]);
+            const uint4 c = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 2][4 * g]);
+            const uint4 d = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 3][4 * g]);
+            const uint32_t pa[4] = {a.x, a.y, a.z, a.w}, pb[4] = {b.x, b.y, b.z, b.w}, pc[4] = {c.x, c.y, c.z, c.w}, pd[4] = {d.x, d.y, d.z, d.w};
+            uint32_t oe = 0, oo = 0;
+#pragma unroll
+            for (int kk = 0; kk < 4; kk++) {
+                const uint32_t ve = __dp2a_lo(pd[kk], e3, __dp2a_lo(pc[kk], e2, __dp2a_lo(pb[kk], e1, __dp2a_lo(pa[kk], e0, 32768u))));
+                const uint32_t vo = __dp2a_lo(pd[kk], o3, __dp2a_lo(pc[kk], o2, __dp2a_lo(pb[kk], o1, __dp2a_lo(pa[kk], o0, 32768u))));
+                oe |= (ve >> 16) << (8 * kk);
+                oo |= (vo >> 16) << (8 * kk);
+            }
+            *reinterpret_cast<uint32_t*>(&s_bl[warp][2 * q][4 * g]) = oe;
+            *reinterpret_cast<uint32_t*>(&s_bl[warp][2 * q + 1][4 * g]) = oo;
+        }
+    }
+    __syncwarp();
+    // 16 points = 8 tests = 1 descriptor byte per lane; test t = bytes (x0, y0, x1, y1) of word t  (computeOrbDescriptor :106-145, a = 1, b = 0)
+    const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + lane * 2);
+    const uint4 pw1 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + lane * 2 + 1);
+    const uint32_t pw[8] = {pw0.x, pw0.y, pw0.z, pw0.w, pw1.x, pw1.y, pw1.z, pw1.w};
+    const uint8_t* bl = &s_bl[warp][13][13];
+    int val = 0;
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        const int x0 = (int)(signed char)(pw[t]), y0 = (int)(signed char)(pw[t] >> 8);
+        const int x1 = (int)(signed char)(pw[t] >> 16), y1 = (int)(signed char)(pw[t] >> 24);
+        val |= ((int)bl[y0 * 28 + x0] < (int)bl[y1 * 28 + x1]) << t;
+    }
+    int w4 = val & 0xFF;
+    w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 1) & 0xFF) << 8;
+    w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 2) & 0xFF) << 16;
+    w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 3) & 0xFF) << 24;
+    const size_t slot = (size_t)img * P.kp_cap + k;
+    if ((lane & 3) == 0) reinterpret_cast<uint32_t*>(desc + slot * 32)[lane >> 2] = (uint32_t)w4;
+    if (lane == 0) {
+        KeypointPod kp;
+        kp.x = (float)px;
+        kp.y = (float)py;
+        if (level != 0) {  // :1149-1151  pt *= scale (f32)
+            kp.x = __fmul_rn(kp.x, Lv.scale);
+            kp.y = __fmul_rn(kp.y, Lv.scale);
+        }
+        kp.size = (float)Lv.scaled_patch;
+        kp.angle = 0.0f;  // computeOrientation writes 0.0 (:475)
         kp.response = (float)mcs_oct::cand_score(rec);
         kp.octave = level;
         kp.class_id = -1;

@@ -43,7 +43,9 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
         qa = __ldg(qp);
         qb = __ldg(qp + 1);
     }
-    int d0 = 1 << 20, d1 = 1 << 20, i0 = -1;
+    // running top-2 as packed keys (distance << 16 | train index): the order of keys is knnMatch's order (distance, then lower
+    // train index first), and best / second-best update with three min/max instead of compare-and-select chains
+    uint32_t k0 = 0xFFFFFFFFu, k1 = 0xFFFFFFFFu;
     const uint4* tbase = reinterpret_cast<const uint4*>(desc + (size_t)cb * kp_cap * 32);
     for (int c0 = 0; c0 < nt; c0 += MCS_MATCH_CHUNK) {
         const int m = min(MCS_MATCH_CHUNK, nt - c0);
@@ -62,17 +64,16 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
                 const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 ^ x4));
                 const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 ^ s2));
                 const uint32_t t1 = c1 ^ c2 ^ c3, f1 = (c1 & c2) | (c3 & (c1 ^ c2));
-                const int d = __popc(s3) + __popc(x7) + 2 * __popc(t1) + 4 * __popc(f1);
-                if (d < d0) {  // strict '<': on ties the lower train index stays first, as knnMatch orders them
-                    d1 = d0;
-                    d0 = d;
-                    i0 = c0 + j;
-                } else if (d < d1) {
-                    d1 = d;
-                }
+                const uint32_t key = (uint32_t)(__popc(s3) + __popc(x7)) * 65536u + (uint32_t)__popc(t1) * 131072u +
+                                     (uint32_t)__popc(f1) * 262144u + (uint32_t)(c0 + j);
+                const uint32_t hi = max(key, k0);
+                k0 = min(key, k0);
+                k1 = min(k1, hi);
             }
         }
     }
+    const int d0 = nt >= 1 ? (int)(k0 >> 16) : (1 << 20), d1 = nt >= 2 ? (int)(k1 >> 16) : (1 << 20);
+    const int i0 = nt >= 1 ? (int)(k0 & 0xFFFFu) : -1;
     if (!active) return;
     // m[0].distance < neigh_ratio * m[1].distance  and not  m[0].distance > dist_thresh   (:1061-1063), f32 arithmetic.
     // With fewer than 2 train descriptors the reference reads m[1] out of range; here: no match.

@@ -175,8 +175,10 @@ bool build_plan(const OrbTables& T, int width, int height, int use_angle, McsPla
         L.sel_ofs = sel;
         sel += L.oct_cap;
         if (l > 0) {
+            if (xtab.size() & 1) xtab.push_back(make_int2(0, 0));  // 16-byte aligned rows of the table (128-bit loads)
             L.xtab_ofs = (int)xtab.size();
             build_resize_axis(P.L[l - 1].w, L.w, xtab, true);
+            for (int k = 0; k < 4; k++) xtab.push_back(xtab.back());  // padding read by the last thread of a row
             L.ytab_ofs = (int)ytab.size();
             build_resize_axis(P.L[l - 1].h, L.h, ytab, false);
         }
@@ -241,6 +243,7 @@ struct Engine {
     mcs::ImageSet last_set{};
     int last_n = 0;
     bool profiling = false;
+    bool blur_valid = false;  // d_blur holds the blurred pyramid of the last run (only the steered mode needs it on the path)
     cudaEvent_t ev[ST_COUNT + 1] = {};
     bool ev_rec[ST_COUNT + 1] = {};
     float stage_ms[ST_COUNT] = {};
@@ -392,12 +395,23 @@ struct Engine {
         mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
         launches++;
         mark(ST_BLUR);
-        mcs::blur_kernel<<<dim3(P.n_tiles, n), 256, 0, st>>>(P, set, blur);
-        launches++;
-        mark(ST_DESCRIBE);
-        mcs::describe_kernel<<<dim3((P.kp_cap + MCS_DESC_WARPS - 1) / MCS_DESC_WARPS, n), MCS_DESC_WARPS * 32, 0, st>>>(
-            P, set, blur, sel, sel_count, kps, desc, kp_count);
-        launches++;
+        if (P.use_angle) {
+            // steered mode: rotated pattern offsets reach +-18 px, so the whole level is blurred first
+            mcs::blur_kernel<<<dim3(P.n_tiles, n), 256, 0, st>>>(P, set, blur);
+            launches++;
+            mark(ST_DESCRIBE);
+            mcs::describe_kernel<<<dim3((P.kp_cap + MCS_DESC_WARPS - 1) / MCS_DESC_WARPS, n), MCS_DESC_WARPS * 32, 0, st>>>(
+                P, set, blur, sel, sel_count, kps, desc, kp_count);
+            launches++;
+            blur_valid = true;
+        } else {
+            // shipped mode (angle 0): blur only the 32 x 32 patch under every keypoint, inside the descriptor kernel
+            mark(ST_DESCRIBE);
+            mcs::describe_fused_kernel<<<dim3((P.kp_cap + MCS_DESCF_WARPS - 1) / MCS_DESCF_WARPS, n), MCS_DESCF_WARPS * 32, 0, st>>>(
+                P, set, sel, sel_count, kps, desc, kp_count);
+            launches++;
+            blur_valid = false;
+        }
         // every keypoint has pt.x >= 19, so a lapping area ending before 19 (the callers' {0,0}) selects nothing (:1153)
         const bool lap_active = lap && lap[1] >= lap[0] && lap[1] >= MCS_EDGE_THRESHOLD;
         if (lap_active) {
@@ -573,6 +587,13 @@ static int engine_download_level(Engine& E, int image_index, int level, int kind
     const uint8_t* src;
     int pitch;
     if (kind == 2) {
+        if (!E.blur_valid) {  // observer only: the shipped-mode path never materialises the blurred pyramid
+            CK(cudaStreamSynchronize(E.stream));
+            mcs::ImageSet set = E.last_set;
+            mcs::blur_kernel<<<dim3(E.plan.n_tiles, E.last_n), 256, 0, E.stream>>>(E.plan, set, E.d_blur);
+            CK(cudaStreamSynchronize(E.stream));
+            E.blur_valid = true;
+        }
         src = E.d_blur + (size_t)image_index * E.plan.pyr_stride + L.plane_ofs;
         pitch = L.pitch;
     } else if (level == 0) {
@@ -714,7 +735,7 @@ struct mcs_rig {
     Slot slots[NSLOT];
     cudaEvent_t ev_begin = nullptr;
     int tri_list_stride = 0, sm_count = 148;
-    int chunk_frames = 16;  // frames per pipelined chunk (0 = no chunking)
+    int chunk_frames = 64;  // frames per pipelined chunk (0 = no chunking)
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
     size_t masks_bytes = 0;
