@@ -53,7 +53,7 @@ def algorithmic_bytes(ncam=NCAM, w=W, h=H, nfeat=NFEAT):
         "fast": allpx + 4 * 10 * nfeat // 4,             # every level read once; candidate records (4 B, ~2.5 per kept feature)
         "octree": 4 * 10 * nfeat // 4 + 4 * nfeat,       # candidate records in, selected records out
         "blur": 2 * allpx,                               # every level read and written once
-        "describe": (32 + 28 + 4) * nfeat,               # selected record in, descriptor + keypoint out
+        "describe": (1024 + 32 + 28 + 4) * nfeat,        # 32x32 patch + selected record in, descriptor + keypoint out (blur fused)
     }
     frame = {k: v * ncam for k, v in per_cam.items()}
     frame["match"] = ncam * (ncam - 1) * nfeat * 32 + (ncam * (ncam - 1) // 2) * nfeat * 8
@@ -234,11 +234,13 @@ def run_gpu(args, rank, world, local):
         host_step()
     ms_e2e = timed(host_step, args.steps)
     clk = clocks.stop()
-    # per-stage device times (CUDA events between the stages on the rig's stream), same steps again with profiling on
+    # per-stage device times (CUDA events between the stages on the rig's stream) with profiling on: one unchunked launch
+    # sequence over `Fp` frames per step, i.e. exactly what one pipeline chunk launches (and what the ncu captures profile)
+    Fp = min(F, 64)
     rig.set_profiling(True)
     acc = dict.fromkeys(STAGES, 0.0)
     for _ in range(args.steps):
-        dev_step()
+        rig.process_device(d_images, Fp)
         for k, v in rig.stage_times().items():
             acc[k] += v
     rig.set_profiling(False)
@@ -246,7 +248,7 @@ def run_gpu(args, rank, world, local):
     kc, n_rows, n_acc = rig.counts(0)
     d2h = rig_d2h_bytes(rig, F)
     return dict(rig=rig, calib=calib, frames=frames, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches, clocks=clk, stage_ms=stage_ms,
-                counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, F=F, dist=dist)
+                counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, F=F, Fp=Fp, dist=dist)
 
 
 def rig_d2h_bytes(rig, F):
@@ -323,29 +325,37 @@ def main():
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured)"
     else:
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback"
-    sm = r["stage_ms"]
+    sm, Fp = r["stage_ms"], r["Fp"]
     kernels = {k: v for k, v in sm.items() if k not in ("upload", "download")}
     dom = max(kernels, key=kernels.get)
-    launches_per_step = {"pyramid": 7}.get(dom, 1)
-    achieved = stage_bytes[dom] * F / (sm[dom] / 1e3) / 1e9
+    launches_per_step = {"pyramid": 7, "triangulate": 3}.get(dom, 1)
+    achieved = stage_bytes[dom] * Fp / (sm[dom] / 1e3) / 1e9
+    # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of the same launch shape
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        t = json.load(open(tpath)).get(dom)
+        if t and t.get("frames_per_launch") == Fp:
+            traffic = t["dram_bytes_per_launch"]
     line = {
         "metric": "rig-frames/sec (ORB extract+intra-match+triangulate)", "value": value, "unit": "rig-frames/s", "n_gpus": world,
         "steps": steps, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": F, "distinct_scenes": args.distinct,
-                   "l2": "per-step working set (%.0f MB of images + pyramids + blurred pyramids per GPU) exceeds the 126 MB L2" %
-                         (F * NCAM * (W * H + 2 * 1.3e6) / 1e6),
+                   "chunk_frames": int(os.environ.get("MCS_CHUNK_FRAMES", "64")),
+                   "l2": "per-step working set (%.0f MB of images + pyramids per GPU) exceeds the 126 MB L2" % (F * NCAM * (W * H + 1.3e6) / 1e6),
                    "sharding": "by rig frame, no collective"},
         "e2e": {"value": e2e, "unit": "rig-frames/s", "h2d_bytes_per_step": int(F * NCAM * W * H), "d2h_bytes_per_step": int(r["d2h"]),
                 "ms_per_step": r["ms_e2e"] / steps},
         "gpu_launches": int(r["launches"]),
         "clocks": r["clocks"],
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": stage_bytes[dom] * F // launches_per_step,
+                     "traffic": traffic, "peak_source": peak_src, "frames_per_launch": Fp,
+                     "algorithmic_bytes_per_launch": stage_bytes[dom] * Fp // launches_per_step,
                      "launch_ms": sm[dom] / launches_per_step,
                      "path": {"bytes_per_rig_frame": total_bytes, "achieved": total_bytes * value / world / 1e9,
                               "frac": total_bytes * value / world / 1e9 / peak}},
-        "stage_ms_per_step": {k: round(v, 4) for k, v in sm.items()},
+        "stage_ms_per_launch_sequence": {"frames": Fp, **{k: round(v, 4) for k, v in sm.items()}},
         "counts_frame0": {"keypoints": r["counts"][0], "intramatch_rows": r["counts"][1], "landmarks": r["counts"][2]},
     }
     if world == 1 and not args.no_cpu:
