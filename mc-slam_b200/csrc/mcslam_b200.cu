@@ -731,7 +731,7 @@ struct mcs_rig {
         cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
         int *d_tri_lists = nullptr, *d_tri_counts = nullptr;
     };
-    static constexpr int NSLOT = 3;
+    static constexpr int NSLOT = 4;
     Slot slots[NSLOT];
     cudaEvent_t ev_begin = nullptr;
     int tri_list_stride = 0, sm_count = 148;
@@ -1018,8 +1018,10 @@ struct mcs_rig {
         const float* dm = d_masks_in;
         int rc;
         if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
-        const bool chunked = chunk_frames > 0 && n_frames > chunk_frames && !eng.profiling;
-        const int step = chunked ? chunk_frames : n_frames;
+        // host-buffer calls use half-size chunks: more copies in flight hide more of the PCIe time
+        const int cf = h_images ? std::max(1, chunk_frames / 2) : chunk_frames;
+        const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
+        const int step = chunked ? cf : n_frames;
         mcs::ImageSet set{};
         if (chunked) {
             CK(cudaEventRecord(ev_begin, eng.stream));
