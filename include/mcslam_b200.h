@@ -180,12 +180,17 @@ MCS_API int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* ma
 /* Same, inputs resident in device memory, nothing copied back (results are read with the getters). */
 MCS_API int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar);
 
-/* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over three
+/* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over four
  * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
 MCS_API int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames);
 
 /* Compact per-frame summary copied back by mcs_rig_process: n keypoints per camera, M rows, accepted landmarks. */
 MCS_API int mcs_rig_get_counts(mcs_rig* rig, int frame, int* kp_counts /*[num_cams]*/, int* n_rows, int* n_accepted);
+
+/* Observers for tests: pyramid level / blurred level of one camera image of the last batch (same kinds as
+ * mcs_extractor_download_level). */
+MCS_API int mcs_rig_download_level(mcs_rig* rig, int frame, int cam, int level, int kind, uint8_t* dst, int dst_stride);
+MCS_API int mcs_rig_level_size(const mcs_rig* rig, int level, int* width, int* height);
 
 /* Stream / timing plumbing for harnesses. */
 MCS_API void* mcs_rig_stream(mcs_rig* rig);                 /* cudaStream_t the rig launches on */
@@ -199,6 +204,30 @@ MCS_API int mcs_rig_set_profiling(mcs_rig* rig, int enable); /* record the per-s
  * second one, waits for it and returns the device time between the two in milliseconds. */
 MCS_API int mcs_rig_timer_start(mcs_rig* rig);
 MCS_API int mcs_rig_timer_stop(mcs_rig* rig, float* ms);
+
+/* ---- Inter-frame matcher primitive ---------------------------------------------------
+ * Replaces  Ptr<DescriptorMatcher> matcher = DescriptorMatcher::create("BruteForce-Hamming"); matcher->knnMatch(q, t, matches, 2);
+ * in FrontEnd::findMatchesMono (MCSlam/src/FrontEnd.cpp:3134-3135) and FrontEnd::findInterMatches (:3199-3201, :3373-3375):
+ * n_sets independent (query, train) problems per launch.  Result rows are int32 (trainIdx0, distance0, trainIdx1, distance1) per
+ * query in query order, -1 where the train set has fewer than 2 rows; ties are ordered by train index like OpenCV's.  The
+ * ratio / distance / mask / 3-D gates differ between the two call sites and stay with the caller (mcslam_adaptor.hpp). */
+typedef struct mcs_matcher mcs_matcher;
+MCS_API mcs_matcher* mcs_matcher_create(int device, int max_sets, int max_query_rows, int max_train_rows);
+MCS_API void mcs_matcher_destroy(mcs_matcher* m);
+/* Host buffers: q_desc = the sets' query descriptors concatenated [sum(q_count)][32], t_desc likewise; out_knn [sum(q_count)][4].
+ * Returns the number of query rows written.  At most 65535 train rows per set. */
+MCS_API int mcs_knn2(mcs_matcher* m, const uint8_t* q_desc, const int* q_count, const uint8_t* t_desc, const int* t_count, int n_sets,
+                     int32_t* out_knn);
+/* Same with descriptors and output resident in device memory; asynchronous on mcs_matcher_stream(). */
+MCS_API int mcs_knn2_device(mcs_matcher* m, const void* d_q_desc, const int* q_count, const void* d_t_desc, const int* t_count,
+                            int n_sets, void* d_out_knn);
+MCS_API void* mcs_matcher_stream(mcs_matcher* m);
+MCS_API int mcs_matcher_synchronize(mcs_matcher* m);
+MCS_API long long mcs_matcher_kernel_launches(const mcs_matcher* m);
+/* knnMatch(k = 2) between feature sets a rig handle already holds on the device (no descriptor traffic over PCIe): set s matches
+ * image q_image[s] = frame * num_cams + cam against image t_image[s], e.g. findMatchesMono for every consecutive frame pair of a
+ * batch.  out_knn: [n_sets][feature_capacity][4]; rows past the query image's keypoint count stay -1. */
+MCS_API int mcs_rig_knn2_images(mcs_rig* rig, const int* q_image, const int* t_image, int n_sets, int32_t* out_knn);
 
 /* Plain device-memory helpers so harnesses written without a CUDA binding can stage resident inputs. */
 MCS_API void* mcs_device_malloc(int device, size_t bytes);

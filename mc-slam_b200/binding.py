@@ -37,7 +37,8 @@ EXPORTS = [
     "mcs_rig_triangulate_device_masks", "mcs_rig_get_landmarks", "mcs_rig_triangulate_nview", "mcs_rig_triangulate_pair", "mcs_rig_process",
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
-    "mcs_host_free_pinned",
+    "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
+    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images",
 ]
 
 
@@ -100,6 +101,17 @@ def lib():
     L.mcs_rig_timer_stop.argtypes = [vp, vp]
     L.mcs_rig_download_level.argtypes = [vp, ci, ci, ci, ci, vp, ci]
     L.mcs_rig_level_size.argtypes = [vp, ci, vp, vp]
+    L.mcs_matcher_create.restype = vp
+    L.mcs_matcher_create.argtypes = [ci, ci, ci, ci]
+    L.mcs_matcher_destroy.argtypes = [vp]
+    L.mcs_knn2.argtypes = [vp, vp, vp, vp, vp, ci, vp]
+    L.mcs_knn2_device.argtypes = [vp, vp, vp, vp, vp, ci, vp]
+    L.mcs_matcher_stream.restype = vp
+    L.mcs_matcher_stream.argtypes = [vp]
+    L.mcs_matcher_synchronize.argtypes = [vp]
+    L.mcs_matcher_kernel_launches.restype = C.c_longlong
+    L.mcs_matcher_kernel_launches.argtypes = [vp]
+    L.mcs_rig_knn2_images.argtypes = [vp, vp, vp, ci, vp]
     L.mcs_device_malloc.restype = vp
     L.mcs_device_malloc.argtypes = [ci, C.c_size_t]
     L.mcs_device_free.argtypes = [ci, vp]
@@ -384,6 +396,15 @@ class RigFrames:
         names = ["upload", "pyramid", "fast", "octree", "blur", "describe", "match", "merge", "triangulate", "download"]
         return dict(zip(names, ms.tolist()))
 
+    def knn2_images(self, q_images, t_images):
+        """knnMatch(k=2) between resident feature sets (image index = frame * num_cams + cam): the findMatchesMono primitive
+        (FrontEnd.cpp:3134) without descriptor traffic.  int32 [n_sets, kp_cap, 4], rows past the query count are -1."""
+        qi = np.ascontiguousarray(q_images, np.int32).ravel()
+        ti = np.ascontiguousarray(t_images, np.int32).ravel()
+        out = np.empty((len(qi), self.kp_cap, 4), np.int32)
+        _check(lib().mcs_rig_knn2_images(self.hd, _p(qi), _p(ti), len(qi), _p(out)), "rig_knn2_images")
+        return out
+
     def level(self, frame, cam, level, kind=0):
         w, h = C.c_int(), C.c_int()
         _check(lib().mcs_rig_level_size(self.hd, level, C.byref(w), C.byref(h)), "rig_level_size")
@@ -391,6 +412,49 @@ class RigFrames:
         out = np.zeros((h.value + pad, w.value + pad), np.uint8)
         _check(lib().mcs_rig_download_level(self.hd, frame, cam, level, kind, _p(out), out.shape[1]), "rig_download_level")
         return out
+
+
+class Matcher:
+    """Batched DescriptorMatcher("BruteForce-Hamming").knnMatch(q, t, k=2) (FrontEnd.cpp:3134-3135, :3199-3201)."""
+
+    def __init__(self, max_sets=1, max_query_rows=8192, max_train_rows=8192, device=0):
+        self.device, self.max_sets = device, max_sets
+        self.hd = lib().mcs_matcher_create(device, max_sets, max_query_rows, max_train_rows)
+        if not self.hd:
+            raise McsError("mcs_matcher_create failed: " + lib().mcs_last_error().decode())
+
+    def close(self):
+        if getattr(self, "hd", None):
+            lib().mcs_matcher_destroy(self.hd)
+            self.hd = None
+
+    __del__ = close
+
+    def knn2(self, q_sets, t_sets):
+        """q_sets / t_sets: lists of uint8 [n_i, 32] arrays (one problem each).  Returns a list of int32 [nq_i, 4] arrays
+        (trainIdx0, dist0, trainIdx1, dist1)."""
+        qs = [np.ascontiguousarray(q, np.uint8).reshape(-1, 32) for q in q_sets]
+        ts = [np.ascontiguousarray(t, np.uint8).reshape(-1, 32) for t in t_sets]
+        qc = np.array([len(q) for q in qs], np.int32)
+        tc = np.array([len(t) for t in ts], np.int32)
+        q = np.concatenate(qs) if qs else np.zeros((0, 32), np.uint8)
+        t = np.concatenate(ts) if ts else np.zeros((0, 32), np.uint8)
+        out = np.empty((max(len(q), 1), 4), np.int32)
+        n = _check(lib().mcs_knn2(self.hd, _p(q), _p(qc), _p(t), _p(tc), len(qs), _p(out)), "knn2")
+        assert n == len(q)
+        return np.split(out[:n], np.cumsum(qc)[:-1])
+
+    def knn2_device(self, d_q, q_counts, d_t, t_counts, d_out):
+        qc = np.ascontiguousarray(q_counts, np.int32)
+        tc = np.ascontiguousarray(t_counts, np.int32)
+        return _check(lib().mcs_knn2_device(self.hd, C.c_void_p(d_q), _p(qc), C.c_void_p(d_t), _p(tc), len(qc), C.c_void_p(d_out)), "knn2_device")
+
+    def synchronize(self):
+        _check(lib().mcs_matcher_synchronize(self.hd), "matcher_synchronize")
+
+    @property
+    def kernel_launches(self):
+        return int(lib().mcs_matcher_kernel_launches(self.hd))
 
 
 def device_malloc(device, nbytes):
@@ -407,3 +471,9 @@ def device_free(device, p):
 def device_upload(device, dptr, arr):
     arr = np.ascontiguousarray(arr)
     _check(lib().mcs_device_upload(device, C.c_void_p(dptr), _p(arr), arr.nbytes), "device_upload")
+
+
+def device_download(device, arr, dptr):
+    """Copies arr.nbytes from device pointer dptr into the (contiguous) numpy array arr."""
+    assert arr.flags["C_CONTIGUOUS"]
+    _check(lib().mcs_device_download(device, _p(arr), C.c_void_p(dptr), arr.nbytes), "device_download")

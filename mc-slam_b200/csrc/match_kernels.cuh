@@ -23,6 +23,18 @@ struct PairList {
     unsigned char a[28], b[28];  // camera pairs i<j in the reference's loop order (:1110-1111)
 };
 
+// 256-bit Hamming distance in bits 16.. of a sort key.  POPC issues at a quarter of the LOP3 rate, so the 8 XOR words go through a
+// carry-save adder tree first (ones / twos / fours bit-planes): 4 POPC instead of 8.
+__device__ __forceinline__ uint32_t hamming_key(const uint4 qa, const uint4 qb, const uint4 ta, const uint4 tb) {
+    const uint32_t x0 = qa.x ^ ta.x, x1 = qa.y ^ ta.y, x2 = qa.z ^ ta.z, x3 = qa.w ^ ta.w;
+    const uint32_t x4 = qb.x ^ tb.x, x5 = qb.y ^ tb.y, x6 = qb.z ^ tb.z, x7 = qb.w ^ tb.w;
+    const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 ^ x1));
+    const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 ^ x4));
+    const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 ^ s2));
+    const uint32_t t1 = c1 ^ c2 ^ c3, f1 = (c1 & c2) | (c3 & (c1 ^ c2));
+    return (uint32_t)(__popc(s3) + __popc(x7)) * 65536u + (uint32_t)__popc(t1) * 131072u + (uint32_t)__popc(f1) * 262144u;
+}
+
 // match_train[(frame * n_pairs + pair) * kp_cap + q] = accepted train index of query q, or -1.
 // match_d0 (optional) gets the best distance for diagnostics/tests.
 __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cams, int kp_cap, PairList pairs, int frame0,
@@ -56,16 +68,7 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
 #pragma unroll 4
             for (int j = 0; j < m; j++) {
                 const uint4 ta = s_train[2 * j], tb = s_train[2 * j + 1];
-                // POPC issues at a quarter of the LOP3 rate, so the 8 XOR words go through a carry-save adder tree first
-                // (ones / twos / fours bit-planes): 4 POPC instead of 8.
-                const uint32_t x0 = qa.x ^ ta.x, x1 = qa.y ^ ta.y, x2 = qa.z ^ ta.z, x3 = qa.w ^ ta.w;
-                const uint32_t x4 = qb.x ^ tb.x, x5 = qb.y ^ tb.y, x6 = qb.z ^ tb.z, x7 = qb.w ^ tb.w;
-                const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 ^ x1));
-                const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 ^ x4));
-                const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 ^ s2));
-                const uint32_t t1 = c1 ^ c2 ^ c3, f1 = (c1 & c2) | (c3 & (c1 ^ c2));
-                const uint32_t key = (uint32_t)(__popc(s3) + __popc(x7)) * 65536u + (uint32_t)__popc(t1) * 131072u +
-                                     (uint32_t)__popc(f1) * 262144u + (uint32_t)(c0 + j);
+                const uint32_t key = hamming_key(qa, qb, ta, tb) + (uint32_t)(c0 + j);
                 const uint32_t hi = max(key, k0);
                 k0 = min(key, k0);
                 k1 = min(k1, hi);
@@ -82,6 +85,60 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
     match_train[o] = ok ? i0 : -1;
     if (match_d0) match_d0[o] = d0;
     if (match_d1) match_d1[o] = d1;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K6b  knn2: DescriptorMatcher("BruteForce-Hamming")->knnMatch(query, train, k = 2) as the inter-frame matchers call it
+// (/root/reference/MCSlam/src/FrontEnd.cpp:3134-3135 findMatchesMono, :3199-3201 findInterMatches), for many independent
+// (query, train) sets per launch.  Output per query row: (trainIdx0, dist0, trainIdx1, dist1), -1 where the train set is
+// shorter than k; ties keep the lower train index first like cv::batchDistance's sort.  The ratio / distance / 3-D gates
+// stay with the caller because the two reference call sites apply different ones.
+// ------------------------------------------------------------------------------------------------------------
+struct Knn2Set {
+    int q_ofs, nq, t_ofs, nt;  // row offsets into the query / train descriptor arrays; with `counts`: nq, nt index it
+    int out_ofs, pad0, pad1, pad2;
+};
+
+__global__ void __launch_bounds__(MCS_MATCH_NT) knn2_kernel(const uint8_t* __restrict__ qdesc, const uint8_t* __restrict__ tdesc,
+                                                            const Knn2Set* __restrict__ sets, const int* __restrict__ counts,
+                                                            int4* __restrict__ out) {
+    extern __shared__ __align__(16) uint4 s_train[];  // [MCS_MATCH_CHUNK][2]
+    const Knn2Set S = sets[blockIdx.y];
+    const int nq = counts ? counts[S.nq] : S.nq, nt = counts ? counts[S.nt] : S.nt;
+    const int q0i = blockIdx.x * MCS_MATCH_NT;
+    if (q0i >= nq) return;
+    const int q = q0i + threadIdx.x;
+    const bool active = q < nq;
+    uint4 qa = make_uint4(0, 0, 0, 0), qb = qa;
+    if (active) {
+        const uint4* qp = reinterpret_cast<const uint4*>(qdesc + ((size_t)S.q_ofs + q) * 32);
+        qa = __ldg(qp);
+        qb = __ldg(qp + 1);
+    }
+    uint32_t k0 = 0xFFFFFFFFu, k1 = 0xFFFFFFFFu;
+    const uint4* tbase = reinterpret_cast<const uint4*>(tdesc + (size_t)S.t_ofs * 32);
+    for (int c0 = 0; c0 < nt; c0 += MCS_MATCH_CHUNK) {
+        const int m = min(MCS_MATCH_CHUNK, nt - c0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < m * 2; t += MCS_MATCH_NT) s_train[t] = __ldg(tbase + (size_t)c0 * 2 + t);
+        __syncthreads();
+        if (active) {
+#pragma unroll 4
+            for (int j = 0; j < m; j++) {
+                const uint32_t key = hamming_key(qa, qb, s_train[2 * j], s_train[2 * j + 1]) + (uint32_t)(c0 + j);
+                const uint32_t hi = max(key, k0);
+                k0 = min(key, k0);
+                k1 = min(k1, hi);
+            }
+        }
+    }
+    if (!active) return;
+    int4 r;
+    r.x = nt >= 1 ? (int)(k0 & 0xFFFFu) : -1;
+    r.y = nt >= 1 ? (int)(k0 >> 16) : -1;
+    r.z = nt >= 2 ? (int)(k1 & 0xFFFFu) : -1;
+    r.w = nt >= 2 ? (int)(k1 >> 16) : -1;
+    out[(size_t)S.out_ofs + q] = r;
 }
 
 // ------------------------------------------------------------------------------------------------------------

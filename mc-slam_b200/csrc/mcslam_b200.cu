@@ -1338,3 +1338,140 @@ MCS_API int mcs_rig_level_size(const mcs_rig* rig, int level, int* width, int* h
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// Inter-frame matcher primitive: batched knnMatch(k = 2).
+// ------------------------------------------------------------------------------------------------------------
+struct mcs_matcher {
+    int device = 0, max_sets = 0, max_q = 0, max_t = 0;
+    cudaStream_t stream = nullptr;
+    uint8_t *d_q = nullptr, *d_t = nullptr;
+    mcs::Knn2Set *d_sets = nullptr, *h_sets = nullptr;
+    int4* d_out = nullptr;
+    long long launches = 0;
+    ~mcs_matcher() {
+        if (cudaSetDevice(device) != cudaSuccess) return;
+        if (stream) cudaStreamDestroy(stream);
+        cudaFree(d_q); cudaFree(d_t); cudaFree(d_sets); cudaFree(d_out);
+        if (h_sets) cudaFreeHost(h_sets);
+    }
+    int init() {
+        CK(cudaSetDevice(device));
+        CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        CK(cudaMalloc(&d_q, (size_t)std::max(max_q, 1) * 32));
+        CK(cudaMalloc(&d_t, (size_t)std::max(max_t, 1) * 32));
+        CK(cudaMalloc(&d_sets, (size_t)max_sets * sizeof(mcs::Knn2Set)));
+        CK(cudaMallocHost(&h_sets, (size_t)max_sets * sizeof(mcs::Knn2Set)));
+        CK(cudaMalloc(&d_out, (size_t)std::max(max_q, 1) * sizeof(int4)));
+        return 0;
+    }
+    // fills h_sets from the per-set counts; returns the largest query count or a negative error
+    int layout(const int* q_count, const int* t_count, int n_sets, int& tot_q, int& tot_t) {
+        if (n_sets < 1 || n_sets > max_sets || !q_count || !t_count) { set_err("knn2: bad n_sets"); return MCS_ERR_ARG; }
+        tot_q = tot_t = 0;
+        int max_nq = 0;
+        for (int i = 0; i < n_sets; i++) {
+            if (q_count[i] < 0 || t_count[i] < 0) { set_err("knn2: negative count"); return MCS_ERR_ARG; }
+            if (t_count[i] > 65535) { set_err("knn2: more than 65535 train descriptors in one set"); return MCS_ERR_CAPACITY; }
+            h_sets[i] = mcs::Knn2Set{tot_q, q_count[i], tot_t, t_count[i], tot_q, 0, 0, 0};
+            tot_q += q_count[i];
+            tot_t += t_count[i];
+            max_nq = std::max(max_nq, q_count[i]);
+        }
+        return max_nq;
+    }
+    int launch(const uint8_t* dq, const uint8_t* dt, const int* counts, int n_sets, int max_nq, int4* out) {
+        CK(cudaMemcpyAsync(d_sets, h_sets, (size_t)n_sets * sizeof(mcs::Knn2Set), cudaMemcpyHostToDevice, stream));
+        if (max_nq > 0) {
+            dim3 g((max_nq + MCS_MATCH_NT - 1) / MCS_MATCH_NT, n_sets);
+            mcs::knn2_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, stream>>>(dq, dt, d_sets, counts, out);
+            CK(cudaGetLastError());
+            launches++;
+        }
+        return 0;
+    }
+};
+
+extern "C" {
+
+mcs_matcher* mcs_matcher_create(int device, int max_sets, int max_query_rows, int max_train_rows) {
+    if (max_sets < 1 || max_query_rows < 0 || max_train_rows < 0) { set_err("mcs_matcher_create: bad sizes"); return nullptr; }
+    mcs_matcher* m = new mcs_matcher();
+    m->device = device; m->max_sets = max_sets; m->max_q = max_query_rows; m->max_t = max_train_rows;
+    if (m->init()) { delete m; return nullptr; }
+    return m;
+}
+void mcs_matcher_destroy(mcs_matcher* m) { delete m; }
+long long mcs_matcher_kernel_launches(const mcs_matcher* m) { return m ? m->launches : 0; }
+
+int mcs_knn2(mcs_matcher* m, const uint8_t* q_desc, const int* q_count, const uint8_t* t_desc, const int* t_count, int n_sets,
+             int32_t* out_knn) {
+    if (!m || !out_knn) return MCS_ERR_ARG;
+    CK(cudaSetDevice(m->device));
+    int tot_q, tot_t;
+    const int max_nq = m->layout(q_count, t_count, n_sets, tot_q, tot_t);
+    if (max_nq < 0) return max_nq;
+    if (tot_q > m->max_q || tot_t > m->max_t) { set_err("knn2: descriptor rows exceed the matcher's capacity"); return MCS_ERR_CAPACITY; }
+    if (tot_q == 0) return 0;
+    if ((!q_desc) || (tot_t > 0 && !t_desc)) return MCS_ERR_ARG;
+    CK(cudaMemcpyAsync(m->d_q, q_desc, (size_t)tot_q * 32, cudaMemcpyHostToDevice, m->stream));
+    if (tot_t) CK(cudaMemcpyAsync(m->d_t, t_desc, (size_t)tot_t * 32, cudaMemcpyHostToDevice, m->stream));
+    int rc = m->launch(m->d_q, m->d_t, nullptr, n_sets, max_nq, m->d_out);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out_knn, m->d_out, (size_t)tot_q * sizeof(int4), cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    return tot_q;
+}
+
+int mcs_knn2_device(mcs_matcher* m, const void* d_q_desc, const int* q_count, const void* d_t_desc, const int* t_count, int n_sets,
+                    void* d_out_knn) {
+    if (!m || !d_out_knn || !d_q_desc || !d_t_desc) return MCS_ERR_ARG;
+    CK(cudaSetDevice(m->device));
+    int tot_q, tot_t;
+    const int max_nq = m->layout(q_count, t_count, n_sets, tot_q, tot_t);
+    if (max_nq < 0) return max_nq;
+    int rc = m->launch((const uint8_t*)d_q_desc, (const uint8_t*)d_t_desc, nullptr, n_sets, max_nq, (int4*)d_out_knn);
+    if (rc) return rc;
+    return tot_q;
+}
+void* mcs_matcher_stream(mcs_matcher* m) { return m ? (void*)m->stream : nullptr; }
+int mcs_matcher_synchronize(mcs_matcher* m) {
+    if (!m) return MCS_ERR_ARG;
+    CK(cudaSetDevice(m->device));
+    CK(cudaStreamSynchronize(m->stream));
+    return 0;
+}
+
+// knnMatch(k = 2) between feature sets the rig already holds on the device: set s matches image q_image[s] (= frame * num_cams + cam)
+// against image t_image[s].  out_knn: [n_sets][feature_capacity][4]; rows >= the query image's keypoint count are left at -1.
+int mcs_rig_knn2_images(mcs_rig* rig, const int* q_image, const int* t_image, int n_sets, int32_t* out_knn) {
+    RIG_ENTER(rig);
+    if (!q_image || !t_image || !out_knn || n_sets < 1) return MCS_ERR_ARG;
+    const int n_img = rig->n_extracted * rig->C, cap = rig->kp_cap;
+    if (rig->n_extracted < 1) { set_err("knn2_images before extract"); return MCS_ERR_STATE; }
+    if (cap > 65535) return MCS_ERR_CAPACITY;
+    std::vector<mcs::Knn2Set> sets(n_sets);
+    for (int i = 0; i < n_sets; i++) {
+        if (q_image[i] < 0 || q_image[i] >= n_img || t_image[i] < 0 || t_image[i] >= n_img) { set_err("knn2_images: image index out of range"); return MCS_ERR_ARG; }
+        sets[i] = mcs::Knn2Set{q_image[i] * cap, q_image[i], t_image[i] * cap, t_image[i], i * cap, 0, 0, 0};
+    }
+    mcs::Knn2Set* d_sets = nullptr;
+    int4* d_out = nullptr;
+    const size_t out_bytes = (size_t)n_sets * cap * sizeof(int4);
+    cudaStream_t st = rig->eng.stream;
+    CK(cudaMallocAsync(&d_sets, sets.size() * sizeof(mcs::Knn2Set), st));
+    CK(cudaMallocAsync(&d_out, out_bytes, st));
+    CK(cudaMemcpyAsync(d_sets, sets.data(), sets.size() * sizeof(mcs::Knn2Set), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(d_out, 0xFF, out_bytes, st));
+    dim3 g((cap + MCS_MATCH_NT - 1) / MCS_MATCH_NT, n_sets);
+    mcs::knn2_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, st>>>(rig->eng.d_desc, rig->eng.d_desc, d_sets, rig->eng.d_kp_count, d_out);
+    CK(cudaGetLastError());
+    rig->eng.launches++;
+    CK(cudaMemcpyAsync(out_knn, d_out, out_bytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaFreeAsync(d_sets, st));
+    CK(cudaFreeAsync(d_out, st));
+    return 0;
+}
+
+}  // extern "C"

@@ -3,6 +3,7 @@
 //   ORBextractor       /root/reference/MCSlam/include/MCSlam/ORBextractor.h:44-112
 //   MultiCameraFrame   /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h (extract / intra-match / triangulate subset)
 //   IntraMatch         /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h:42-57
+//   InterFrameMatcher  FrontEnd::findMatchesMono / findInterMatches, /root/reference/MCSlam/src/FrontEnd.cpp:3114-3470
 // Without OpenCV headers the containers are PODs (mcs_keypoint, byte vectors).  Define MCS_WITH_OPENCV before including this
 // file (in a build that has OpenCV) to get the cv::InputArray / cv::KeyPoint / cv::Mat overloads with the reference's exact
 // signatures.  There is no CPU path: every method launches the sm_100a kernels and throws std::runtime_error when the library
@@ -11,6 +12,7 @@
 #define MCSLAM_ADAPTOR_HPP
 
 #include <array>
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <stdexcept>
@@ -150,7 +152,7 @@ class MultiCameraFrame {
 public:
     MultiCameraFrame(const std::vector<mcs_calib>& calib, int width, int height, int nfeatures, float scaleFactor, int nlevels,
                      int iniThFAST, int minThFAST, int device = 0, int max_frames = 1)
-        : num_cams_((int)calib.size()), w_(width), h_img_(height) {
+        : num_cams_((int)calib.size()), calib_(calib), w_(width), h_img_(height) {
         mcs_rig_config cfg{};
         cfg.num_cams = num_cams_; cfg.width = width; cfg.height = height; cfg.nfeatures = nfeatures; cfg.scale_factor = scaleFactor;
         cfg.nlevels = nlevels; cfg.ini_th_fast = iniThFAST; cfg.min_th_fast = minThFAST; cfg.max_frames = max_frames; cfg.device = device;
@@ -252,6 +254,37 @@ public:
         check(mcs_rig_triangulate_pair(h_, cam1, cam2, &kps_1[0][0], &kps_2[0][0], (int)kps_1.size(), &pts3D[0][0]), "mcs_rig_triangulate_pair");
     }
 
+    // triangulateIntraMatches(kps_1, kps_2) (:446-472): kps_1[i][ind] / kps_2[i][ind] hold the matched pixel pairs of camera i and
+    // camera j = i + 1 + ind; every pair is triangulated with the 2-view DLT above and moved into camera 0's frame
+    // (R_i^T, -R_i^T t_i converted to f32, cv::Affine3f product).  Fills pts3D_ in the reference's pair order.
+    void triangulateIntraMatches(const std::vector<std::vector<std::vector<std::array<float, 2>>>>& kps_1,
+                                 const std::vector<std::vector<std::vector<std::array<float, 2>>>>& kps_2) {
+        pts3D_.clear();
+        for (int i = 0; i < num_cams_ - 1; i++) {
+            int ind = 0;
+            for (int j = i + 1; j < num_cams_; j++, ind++) {
+                std::vector<std::array<float, 3>> pts;
+                triangulate(kps_1[i][ind], kps_2[i][ind], pts, i, j);
+                if (i != 0) {
+                    float R[9], t[3];
+                    const mcs_calib& c = calib_[i];
+                    for (int r = 0; r < 3; r++) {
+                        for (int k = 0; k < 3; k++) R[r * 3 + k] = (float)c.R[k * 3 + r];
+                        t[r] = (float)((-c.R[0 * 3 + r]) * c.t[0] + (-c.R[1 * 3 + r]) * c.t[1] + (-c.R[2 * 3 + r]) * c.t[2]);
+                    }
+                    for (auto& p : pts) {
+                        const float x = p[0], y = p[1], z = p[2];
+                        p[0] = R[0] * x + R[1] * y + R[2] * z + t[0];
+                        p[1] = R[3] * x + R[4] * y + R[5] * z + t[1];
+                        p[2] = R[6] * x + R[7] * y + R[8] * z + t[2];
+                    }
+                }
+                pts3D_.insert(pts3D_.end(), pts.begin(), pts.end());
+            }
+        }
+    }
+    std::vector<std::array<float, 3>> pts3D_;  // MultiCameraFrame.h pts3D_ (get3DPoints, :510-514)
+
     // Throughput form of FrontEnd::processFrame (FrontEnd.cpp:991-1028) for n_frames rig frames in one launch sequence.
     void process_frames(const uint8_t* images, const float* masks, int n_frames, bool old = false) {
         check(mcs_rig_process(h_, images, masks, n_frames, old ? 1 : 0), "mcs_rig_process");
@@ -267,9 +300,129 @@ private:
         m.matchIndexN.assign(row, row + num_cams_);
         for (int c = 0; c < 5 && c < num_cams_; c++) m.matchIndex[c] = row[c];
     }
+    std::vector<mcs_calib> calib_;
     mcs_rig* h_ = nullptr;
     int w_, h_img_, kp_cap_ = 0, row_cap_ = 0;
     const uint8_t* images_ = nullptr;
+};
+
+// cv::DMatch stand-in (queryIdx, trainIdx, distance); with MCS_WITH_OPENCV the methods below also fill std::vector<cv::DMatch>.
+struct DMatch {
+    int queryIdx = -1, trainIdx = -1;
+    float distance = 0.f;
+};
+
+// What FrontEnd::findInterMatches reads of a MultiCameraFrame (MultiCameraFrame.h:138-151): the frame's IntraMatch list
+// (triangulated rows first, mono features appended), the landmark ids and the number of triangulated rows.
+struct InterFrameView {
+    const std::vector<IntraMatch>* intraMatches = nullptr;
+    const std::vector<int>* lIds = nullptr;
+    int intramatch_size = 0;
+};
+
+// Inter-frame matching of FrontEnd (FrontEnd.cpp:3114-3470).  The brute-force knnMatch(k = 2) runs on the GPU (mcs_knn2); the
+// accept / reject rules that differ between the call sites and the order-dependent one-to-one bookkeeping stay on the host, in
+// the reference's arithmetic (float distances promoted to double against 0.7 * m[1].distance).
+class InterFrameMatcher {
+public:
+    explicit InterFrameMatcher(int device = 0, int max_rows = 16384) : max_rows_(max_rows) {
+        h_ = mcs_matcher_create(device, 1, max_rows, max_rows);
+        if (!h_) throw std::runtime_error(std::string("mcs_matcher_create: ") + mcs_last_error());
+    }
+    ~InterFrameMatcher() { mcs_matcher_destroy(h_); }
+    InterFrameMatcher(const InterFrameMatcher&) = delete;
+    InterFrameMatcher& operator=(const InterFrameMatcher&) = delete;
+
+    // matcher->knnMatch(descs1, descs2, matches, 2) (FrontEnd.cpp:3135): rows of (trainIdx0, dist0, trainIdx1, dist1)
+    const std::vector<int32_t>& knnMatch(const uint8_t* descs1, int n1, const uint8_t* descs2, int n2) {
+        knn_.assign((size_t)(n1 > 0 ? n1 : 1) * 4, -1);
+        if (n1 > 0) check(mcs_knn2(h_, descs1, &n1, descs2, &n2, 1, knn_.data()), "mcs_knn2");
+        return knn_;
+    }
+
+    // findMatchesMono(lf_prev, lf_cur, cam_ind, matches) (FrontEnd.cpp:3114-3154).  descs*: image_descriptors[cam_ind] rows,
+    // kps*_undist: image_kps_undist[cam_ind], segMask*: segMasks[cam_ind] as CV_32F planes of `width` columns (nullptr = all static).
+    void findMatchesMono(const uint8_t* descs1, const std::vector<mcs_keypoint>& kps1_undist, const float* segMask1, const uint8_t* descs2,
+                         const std::vector<mcs_keypoint>& kps2_undist, const float* segMask2, int width, std::vector<DMatch>& matches) {
+        matches.clear();
+        const int n1 = (int)kps1_undist.size(), n2 = (int)kps2_undist.size();
+        const std::vector<int32_t>& k = knnMatch(descs1, n1, descs2, n2);
+        for (int q = 0; q < n1; q++) {
+            const int32_t* m = &k[(size_t)q * 4];
+            if (m[2] < 0) continue;  // fewer than two train descriptors: the reference would index m[1] out of range
+            const float d0 = (float)m[1], d1 = (float)m[3];
+            if (d0 < 0.7 * d1) {
+                if (d0 > 50) continue;
+                const mcs_keypoint &p = kps1_undist[q], &c = kps2_undist[m[0]];
+                const float s1 = segMask1 ? segMask1[(size_t)(int)p.y * width + (int)p.x] : 0.f;
+                const float s2 = segMask2 ? segMask2[(size_t)(int)c.y * width + (int)c.x] : 0.f;
+                if (s1 < 0.7 && s2 < 0.7) matches.push_back(DMatch{q, m[0], d0});
+            }
+        }
+    }
+
+    // findInterMatches(lf_prev, lf_cur, matches_z_filtered, matches_mono_z_filtered, viz) (FrontEnd.cpp:3157-3343).  Like the
+    // reference only matches_z_filtered is cleared on entry.
+    void findInterMatches(const InterFrameView& prev, const InterFrameView& cur, std::vector<DMatch>& matches_z_filtered,
+                          std::vector<DMatch>& matches_mono_z_filtered) {
+        inter(prev, cur, matches_z_filtered, &matches_mono_z_filtered);
+    }
+    // findInterMatches(lf_prev, lf_cur, matches_z_filtered, viz) (FrontEnd.cpp:3344-3470)
+    void findInterMatches(const InterFrameView& prev, const InterFrameView& cur, std::vector<DMatch>& matches_z_filtered) {
+        inter(prev, cur, matches_z_filtered, nullptr);
+    }
+
+private:
+    void inter(const InterFrameView& prev, const InterFrameView& cur, std::vector<DMatch>& lf, std::vector<DMatch>* mono) {
+        const std::vector<IntraMatch>&a = *prev.intraMatches, &b = *cur.intraMatches;
+        const int n1 = (int)a.size(), n2 = (int)b.size();
+        d1_.resize((size_t)n1 * 32);
+        d2_.resize((size_t)n2 * 32);
+        for (int i = 0; i < n1; i++) std::memcpy(&d1_[(size_t)i * 32], a[i].matchDesc.data(), 32);
+        for (int i = 0; i < n2; i++) std::memcpy(&d2_[(size_t)i * 32], b[i].matchDesc.data(), 32);
+        const std::vector<int32_t>& k = knnMatch(d1_.data(), n1, d2_.data(), n2);
+        lf.clear();
+        std::vector<int> inds1, inds2, mono_inds1, mono_inds2;
+        for (int q = 0; q < n1; q++) {
+            const int32_t* m = &k[(size_t)q * 4];
+            if (m[0] < 0) continue;
+            const int t = m[0];
+            const float d0 = (float)m[1];
+            if ((*prev.lIds)[q] == -1) {  // :3212-3218: landmarks skip the ratio test
+                if (m[2] < 0) continue;
+                if (d0 > 0.7 * (float)m[3]) continue;
+            }
+            if (!a[q].mono && !b[t].mono) {  // :3221-3232
+                const double dx = a[q].point3D[0] - b[t].point3D[0], dy = a[q].point3D[1] - b[t].point3D[1],
+                             dz = a[q].point3D[2] - b[t].point3D[2];
+                const float distance = (float)std::sqrt(dx * dx + dy * dy + dz * dz);
+                if (!(distance <= 2.0)) continue;
+            }
+            int pos_lf = -1, pos_mono = -1;
+            if (!mono || t < cur.intramatch_size) pos_lf = find(inds2, t);
+            if (mono) pos_mono = find(mono_inds2, t);
+            const DMatch dm{q, t, d0};
+            if (pos_lf < 0 && pos_mono < 0) {
+                if (!mono || (q < prev.intramatch_size && t < cur.intramatch_size)) {
+                    inds2.push_back(t); inds1.push_back(q); lf.push_back(dm);
+                } else {
+                    mono_inds2.push_back(t); mono_inds1.push_back(q); mono->push_back(dm);
+                }
+            } else if (pos_mono < 0) {  // train feature already taken by an intra-match inter-match: keep the closer one
+                if (d0 < lf[pos_lf].distance) { inds1[pos_lf] = q; lf[pos_lf] = dm; }
+            } else {
+                if (d0 < (*mono)[pos_mono].distance) { mono_inds1[pos_mono] = q; (*mono)[pos_mono] = dm; }
+            }
+        }
+    }
+    static int find(const std::vector<int>& v, int x) {
+        for (size_t i = 0; i < v.size(); i++) if (v[i] == x) return (int)i;
+        return -1;
+    }
+    mcs_matcher* h_ = nullptr;
+    int max_rows_ = 0;
+    std::vector<int32_t> knn_;
+    std::vector<uint8_t> d1_, d2_;
 };
 
 }  // namespace mcs_b200

@@ -1,0 +1,94 @@
+"""Generates tests/golden/knn2_cv2.npz: cv2.BFMatcher(NORM_HAMMING).knnMatch(q, t, k=2) (OpenCV 4.13.0 here) on descriptor sets with
+many distance ties (duplicated and near-duplicated rows), the primitive behind FrontEnd::findMatchesMono / findInterMatches
+(FrontEnd.cpp:3134, :3200).  Run from the repo root:  python oracle/gen_golden_knn2.py"""
+import os
+
+import cv2
+import numpy as np
+
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+rng = np.random.default_rng(11)
+t = rng.integers(0, 256, (700, 32), dtype=np.uint8)
+t[100:140] = t[0:40]                      # exact duplicates: ties on (distance 0)
+t[300:340, :4] = t[200:240, :4]
+q = t[rng.integers(0, 700, 500)].copy()
+flip = rng.integers(0, 256, (500, 32), dtype=np.uint8) & rng.integers(0, 256, (500, 32), dtype=np.uint8) & rng.integers(0, 256, (500, 32), dtype=np.uint8)
+q[100:] ^= flip[100:]                     # first 100 queries are exact copies of train rows
+knn = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, k=2)
+out = np.array([[m[0].trainIdx, int(m[0].distance), m[1].trainIdx, int(m[1].distance)] for m in knn], np.int32)
+np.savez_compressed(os.path.join(OUT, "knn2_cv2.npz"), q=q, t=t, knn=out)
+print("cv2", cv2.__version__, out.shape, "ties:", int((out[:, 1] == out[:, 3]).sum()))
+
+
+# ---- inter-frame host logic on top of cv2's knnMatch: a second, independent restatement (python, cv2.DMatch / cv2.norm) of
+# FrontEnd::findMatchesMono (:3114-3154) and both FrontEnd::findInterMatches overloads (:3157-3343, :3344-3470).  The reference
+# itself cannot run here (needs GTSAM / DBoW2 / ROS), so these fixtures pin oracle/mcs_oracle.cpp against cv2 + this restatement.
+def py_find_matches_mono(d1, d2, xy1, xy2, m1, m2):
+    out = []
+    for m in cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(d1, d2, k=2):
+        if float(m[0].distance) < 0.7 * float(m[1].distance):
+            if m[0].distance > 50:
+                continue
+            p, c = xy1[m[0].queryIdx], xy2[m[0].trainIdx]
+            if float(m1[int(p[1]), int(p[0])]) < 0.7 and float(m2[int(c[1]), int(c[0])]) < 0.7:  # float -> double like C++ (numpy would compare in f32)
+                out.append((m[0].queryIdx, m[0].trainIdx, int(m[0].distance)))
+    return np.array(out, np.int32).reshape(-1, 3)
+
+
+def py_find_inter_matches(d1, d2, mono1, mono2, p1, p2, lids1, isz1, isz2, split):
+    inds1, inds2, lf, mi1, mi2, mo = [], [], [], [], [], []
+    for m in cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(d1, d2, k=2):
+        q, t = m[0].queryIdx, m[0].trainIdx
+        if lids1[q] == -1 and float(m[0].distance) > 0.7 * float(m[1].distance):
+            continue
+        if not mono1[q] and not mono2[t]:
+            if not (float(np.float32(cv2.norm(p1[q] - p2[t]))) <= 2.0):
+                continue
+        in_lf = (t in inds2) if (not split or t < isz2) else False
+        in_mo = (t in mi2) if split else False
+        rec = (q, t, int(m[0].distance))
+        if not in_lf and not in_mo:
+            if not split or (q < isz1 and t < isz2):
+                inds2.append(t); inds1.append(q); lf.append(rec)
+            else:
+                mi2.append(t); mi1.append(q); mo.append(rec)
+        elif not in_mo:
+            k = inds2.index(t)
+            if rec[2] < lf[k][2]:
+                inds1[k] = q; lf[k] = rec
+        else:
+            k = mi2.index(t)
+            if rec[2] < mo[k][2]:
+                mi1[k] = q; mo[k] = rec
+    return np.array(lf, np.int32).reshape(-1, 3), np.array(mo, np.int32).reshape(-1, 3)
+
+
+rng = np.random.default_rng(12)
+W, H = 720, 540
+n1, n2 = 600, 640
+d2 = rng.integers(0, 256, (n2, 32), dtype=np.uint8)
+src = rng.integers(0, n2, n1)
+noise = np.zeros((n1, 32), np.uint8)
+for k in range(n1):                        # 0..70 flipped bits: both sides of the distance-50 gate
+    bits = rng.choice(256, int(rng.integers(0, 70)), replace=False)
+    np.bitwise_or.at(noise[k], bits // 8, (1 << (bits % 8)).astype(np.uint8))
+d1 = d2[src] ^ noise
+d1[500:] = rng.integers(0, 256, (100, 32), dtype=np.uint8)
+xy1 = (rng.random((n1, 2)) * [W - 1, H - 1]).astype(np.float32)
+xy2 = (rng.random((n2, 2)) * [W - 1, H - 1]).astype(np.float32)
+blk = lambda: np.kron(np.round(rng.random((H // 12, W // 12)) * 0.9, 1), np.ones((12, 12))).astype(np.float32)  # 12x12-pixel blocks: the fixture stays small
+m1, m2 = blk(), blk()
+mono_out = py_find_matches_mono(d1, d2, xy1, xy2, m1, m2)
+
+isz1, isz2 = 350, 380                      # rows >= isz are mono features appended after the triangulated intra-matches
+mono1 = (np.arange(n1) >= isz1).astype(np.uint8)
+mono2 = (np.arange(n2) >= isz2).astype(np.uint8)
+p2 = rng.normal(0, 5, (n2, 3)) + [0, 0, 12]
+p1 = p2[src] + rng.normal(0, 0.9, (n1, 3))  # ~half inside the 2 m gate
+lids1 = np.where(rng.random(n1) < 0.3, rng.integers(0, 1000, n1), -1).astype(np.int32)
+lf_a, mo_a = py_find_inter_matches(d1, d2, mono1, mono2, p1, p2, lids1, isz1, isz2, True)
+lf_b, _ = py_find_inter_matches(d1, d2, mono1, mono2, p1, p2, lids1, isz1, isz2, False)
+np.savez_compressed(os.path.join(OUT, "inter_frame_cv2.npz"), d1=d1, d2=d2, xy1=xy1, xy2=xy2, m1=m1, m2=m2, mono_out=mono_out,
+                    mono1=mono1, mono2=mono2, p1=p1, p2=p2, lids1=lids1, isz=np.array([isz1, isz2]), lf_split=lf_a, mono_split=mo_a,
+                    lf_single=lf_b)
+print("findMatchesMono", len(mono_out), "findInterMatches split", len(lf_a), len(mo_a), "single", len(lf_b))

@@ -53,6 +53,9 @@ def lib():
         L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
         L.orc_hamming256.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_bf_match.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float] + [C.c_void_p] * 5
+        L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4
+        L.orc_find_matches_mono.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
+        L.orc_find_inter_matches.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_void_p] * 3
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_triangulate_pixels.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -186,6 +189,45 @@ def bf_match(q, t, dist_thresh=75.0, ratio=0.85):
     bi = np.zeros(max(nq, 1), np.int32)
     n = lib().orc_bf_match(_p(q), nq, _p(t), nt, dist_thresh, ratio, _p(i1), _p(i2), _p(bd), _p(sd), _p(bi))
     return i1[:n].copy(), i2[:n].copy(), bd[:nq], sd[:nq], bi[:nq]
+
+
+def knn2(q, t):
+    """knnMatch(q, t, k=2) (FrontEnd.cpp:3134, :3200): int32 [nq, 4] = (trainIdx0, dist0, trainIdx1, dist1), -1 where missing."""
+    q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+    t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+    out = [np.zeros(max(len(q), 1), np.int32) for _ in range(4)]
+    lib().orc_knn2(_p(q), len(q), _p(t), len(t), *[_p(o) for o in out])
+    return np.stack([o[:len(q)] for o in out], 1)
+
+
+def find_matches_mono(d1, d2, xy1, xy2, mask1=None, mask2=None, width=0):
+    """FrontEnd::findMatchesMono (FrontEnd.cpp:3114-3154): int32 [n, 3] = (queryIdx, trainIdx, distance)."""
+    d1 = np.ascontiguousarray(d1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(d2, np.uint8).reshape(-1, 32)
+    xy1 = np.ascontiguousarray(xy1, np.float32)
+    xy2 = np.ascontiguousarray(xy2, np.float32)
+    m1 = None if mask1 is None else np.ascontiguousarray(mask1, np.float32)
+    m2 = None if mask2 is None else np.ascontiguousarray(mask2, np.float32)
+    out = np.zeros((max(len(d1), 1), 3), np.int32)
+    n = lib().orc_find_matches_mono(_p(d1), len(d1), _p(d2), len(d2), _p(xy1), _p(xy2), _p(m1), _p(m2), width, _p(out))
+    return out[:n]
+
+
+def find_inter_matches(d1, d2, mono1, mono2, p1, p2, lids1, isz1, isz2, split_mono=True):
+    """FrontEnd::findInterMatches (FrontEnd.cpp:3157-3343 / :3344-3470): (matches_z_filtered, matches_mono_z_filtered) as int32 [n, 3]."""
+    d1 = np.ascontiguousarray(d1, np.uint8).reshape(-1, 32)
+    d2 = np.ascontiguousarray(d2, np.uint8).reshape(-1, 32)
+    mono1 = np.ascontiguousarray(mono1, np.uint8)
+    mono2 = np.ascontiguousarray(mono2, np.uint8)
+    p1 = np.ascontiguousarray(p1, np.float64)
+    p2 = np.ascontiguousarray(p2, np.float64)
+    lids1 = np.ascontiguousarray(lids1, np.int32)
+    lf = np.zeros((max(len(d1), 1), 3), np.int32)
+    mo = np.zeros((max(len(d1), 1), 3), np.int32)
+    nm = C.c_int(0)
+    n = lib().orc_find_inter_matches(_p(d1), len(d1), _p(d2), len(d2), _p(mono1), _p(mono2), _p(p1), _p(p2), _p(lids1), isz1, isz2,
+                                     int(split_mono), _p(lf), _p(mo), C.byref(nm))
+    return lf[:n], mo[:nm.value]
 
 
 def _ptr_array(arrs):

@@ -1,13 +1,100 @@
 // Host-side C++ adaptor smoke: mirrors how FrontEnd drives the reference classes (FrontEnd.cpp:991-1028).
 //   argv: <raw u8 images file [C][h][w]> C w h <out file>   -> writes counts, keypoints, descriptors, rows, landmarks as text
+//   argv: inter <dir> <out file>                              -> inter-frame matchers + pairwise triangulation (see run_inter)
 // Without a GPU the constructors throw (no CPU path): exit code 3.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
+#include <string>
 
 #include "../../mc-slam_b200/host/mcslam_adaptor.hpp"
 
+template <typename T>
+static std::vector<T> slurp(const std::string& path) {
+    std::ifstream f(path, std::ios::binary | std::ios::ate);
+    std::vector<T> v((size_t)f.tellg() / sizeof(T));
+    f.seekg(0);
+    f.read((char*)v.data(), v.size() * sizeof(T));
+    return v;
+}
+
+// argv: inter <dir> <out>   -- FrontEnd::findMatchesMono / findInterMatches (both overloads) and the pairwise
+// triangulateIntraMatches(kps_1, kps_2) through the adaptor, on arrays the python test wrote into <dir>.
+static int run_inter(const std::string& dir, const char* out_path) {
+    using namespace mcs_b200;
+    int n1, n2, w, isz1, isz2, C, npair;
+    FILE* meta = fopen((dir + "/meta.txt").c_str(), "r");
+    if (!meta || fscanf(meta, "%d %d %d %d %d %d %d", &n1, &n2, &w, &isz1, &isz2, &C, &npair) != 7) return 2;
+    fclose(meta);
+    auto d1 = slurp<uint8_t>(dir + "/d1.bin"), d2 = slurp<uint8_t>(dir + "/d2.bin");
+    auto xy1 = slurp<float>(dir + "/xy1.bin"), xy2 = slurp<float>(dir + "/xy2.bin");
+    auto m1 = slurp<float>(dir + "/m1.bin"), m2 = slurp<float>(dir + "/m2.bin");
+    auto mono1 = slurp<uint8_t>(dir + "/mono1.bin"), mono2 = slurp<uint8_t>(dir + "/mono2.bin");
+    auto p1 = slurp<double>(dir + "/p1.bin"), p2 = slurp<double>(dir + "/p2.bin");
+    auto lids = slurp<int>(dir + "/lids1.bin");
+    FILE* f = fopen(out_path, "w");
+    InterFrameMatcher im(0, 4096);
+    std::vector<mcs_keypoint> k1(n1), k2(n2);
+    for (int i = 0; i < n1; i++) { k1[i] = mcs_keypoint{}; k1[i].x = xy1[2 * i]; k1[i].y = xy1[2 * i + 1]; }
+    for (int i = 0; i < n2; i++) { k2[i] = mcs_keypoint{}; k2[i].x = xy2[2 * i]; k2[i].y = xy2[2 * i + 1]; }
+    std::vector<DMatch> mm;
+    im.findMatchesMono(d1.data(), k1, m1.data(), d2.data(), k2, m2.data(), w, mm);
+    for (auto& m : mm) fprintf(f, "mono %d %d %d\n", m.queryIdx, m.trainIdx, (int)m.distance);
+    std::vector<IntraMatch> a(n1), b(n2);
+    for (int i = 0; i < n1; i++) {
+        memcpy(a[i].matchDesc.data(), &d1[(size_t)i * 32], 32);
+        a[i].mono = mono1[i] != 0;
+        for (int k = 0; k < 3; k++) a[i].point3D[k] = p1[3 * i + k];
+    }
+    for (int i = 0; i < n2; i++) {
+        memcpy(b[i].matchDesc.data(), &d2[(size_t)i * 32], 32);
+        b[i].mono = mono2[i] != 0;
+        for (int k = 0; k < 3; k++) b[i].point3D[k] = p2[3 * i + k];
+    }
+    std::vector<int> none(n2, -1);
+    InterFrameView prev{&a, &lids, isz1}, cur{&b, &none, isz2};
+    std::vector<DMatch> lf, mo, single;
+    im.findInterMatches(prev, cur, lf, mo);
+    im.findInterMatches(prev, cur, single);
+    for (auto& m : lf) fprintf(f, "lf %d %d %d\n", m.queryIdx, m.trainIdx, (int)m.distance);
+    for (auto& m : mo) fprintf(f, "mo %d %d %d\n", m.queryIdx, m.trainIdx, (int)m.distance);
+    for (auto& m : single) fprintf(f, "single %d %d %d\n", m.queryIdx, m.trainIdx, (int)m.distance);
+    // empty train set: no rows, no crash (the reference would index m[0] of an empty vector)
+    std::vector<IntraMatch> nobody;
+    InterFrameView empty{&nobody, &none, 0};
+    im.findInterMatches(prev, empty, single);
+    fprintf(f, "empty %zu\n", single.size());
+
+    // pairwise triangulation wrapper: pairs.bin = for every camera pair (i < j) npair rows of (x1 y1 x2 y2) f32
+    std::vector<mcs_calib> calib(C);
+    std::ifstream(dir + "/calib.bin", std::ios::binary).read((char*)calib.data(), C * sizeof(mcs_calib));
+    auto pairs = slurp<float>(dir + "/pairs.bin");
+    MultiCameraFrame fr(calib, 320, 240, 300, 1.2f, 8, 20, 7);
+    std::vector<std::vector<std::vector<std::array<float, 2>>>> kp1(C - 1), kp2(C - 1);
+    size_t o = 0;
+    for (int i = 0; i < C - 1; i++)
+        for (int j = i + 1; j < C; j++) {
+            std::vector<std::array<float, 2>> u(npair), v(npair);
+            for (int k = 0; k < npair; k++, o += 4) { u[k] = {pairs[o], pairs[o + 1]}; v[k] = {pairs[o + 2], pairs[o + 3]}; }
+            kp1[i].push_back(u);
+            kp2[i].push_back(v);
+        }
+    fr.triangulateIntraMatches(kp1, kp2);
+    for (auto& p : fr.pts3D_) fprintf(f, "pt %.9g %.9g %.9g\n", p[0], p[1], p[2]);
+    fclose(f);
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc >= 4 && std::string(argv[1]) == "inter") {
+        try {
+            return run_inter(argv[2], argv[3]);
+        } catch (const std::exception& e) {
+            fprintf(stderr, "adaptor: %s\n", e.what());
+            return 3;
+        }
+    }
     if (argc < 6) return 2;
     const int C = atoi(argv[2]), w = atoi(argv[3]), h = atoi(argv[4]);
     std::vector<uint8_t> img((size_t)C * w * h);

@@ -1,0 +1,135 @@
+"""GPU parity for the inter-frame matcher primitive: batched knnMatch(k=2) through the C ABI (mcs_knn2,
+mcs_knn2_device, mcs_rig_knn2_images) and the C++ adaptor's findMatchesMono / findInterMatches, against the cv2 golden fixtures and
+the oracle.  Indices and distances bit-exact."""
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_knn2_golden(golden):
+    import mcslam_b200 as M
+    g = golden("knn2_cv2.npz")
+    m = M.Matcher(max_sets=1, max_query_rows=1024, max_train_rows=1024)
+    out = m.knn2([g["q"]], [g["t"]])[0]
+    assert np.array_equal(out, g["knn"])
+    assert m.kernel_launches == 1
+
+
+def test_knn2_ragged_sets_vs_oracle():
+    """Many sets in one launch: empty query set, empty / 1-row / 2-row train sets, a train set longer than the shared-memory chunk
+    (1024 rows), duplicates (ties), and the capacity errors."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    rng = np.random.default_rng(5)
+    sizes = [(300, 280), (0, 50), (40, 0), (17, 1), (33, 2), (700, 2600), (129, 1024), (128, 1025), (1, 1)]
+    qs = [rng.integers(0, 256, (a, 32), dtype=np.uint8) for a, _ in sizes]
+    ts = [rng.integers(0, 256, (b, 32), dtype=np.uint8) for _, b in sizes]
+    ts[0][100:140] = ts[0][0:40]
+    qs[0][:40] = ts[0][:40]
+    ts[5][2000:2050] = ts[5][10:60]
+    qs[5][:50] = ts[5][10:60]
+    m = M.Matcher(max_sets=len(sizes), max_query_rows=2048, max_train_rows=8192)
+    outs = m.knn2(qs, ts)
+    for (a, b), q, t, o in zip(sizes, qs, ts, outs):
+        assert o.shape == (a, 4)
+        assert np.array_equal(o, O.knn2(q, t)), (a, b)
+    with pytest.raises(M.McsError):
+        m.knn2([qs[5]] * 4, [ts[5]] * 4)  # 2800 query rows > 2048
+    with pytest.raises(M.McsError):
+        M.Matcher(max_sets=1, max_query_rows=8, max_train_rows=70000).knn2([qs[0][:8]], [np.zeros((65536, 32), np.uint8)])
+
+
+def test_knn2_device_entry():
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from mcslam_b200 import binding as B
+    rng = np.random.default_rng(6)
+    q = rng.integers(0, 256, (900, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (1500, 32), dtype=np.uint8)
+    dq, dt, do = B.device_malloc(0, q.nbytes), B.device_malloc(0, t.nbytes), B.device_malloc(0, 900 * 16)
+    B.device_upload(0, dq, q)
+    B.device_upload(0, dt, t)
+    m = M.Matcher(max_sets=2)
+    assert m.knn2_device(dq, [400, 500], dt, [700, 800], do) == 900
+    m.synchronize()
+    out = np.zeros((900, 4), np.int32)
+    B.device_download(0, out, do)
+    assert np.array_equal(out[:400], O.knn2(q[:400], t[:700])) and np.array_equal(out[400:], O.knn2(q[400:], t[700:]))
+    for p in (dq, dt, do):
+        B.device_free(0, p)
+
+
+def test_rig_knn2_images_consecutive_frames():
+    """findMatchesMono's knnMatch for every consecutive frame pair of a batch on the descriptors the rig already holds."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(3, 320, 240)
+    frames = np.stack([M.synth.make_rig_frame(calib, 320, 240, frame_index=40 + i, n_rects=6) for i in range(3)])
+    rig = M.RigFrames(calib, 320, 240, nfeatures=400, max_frames=3)
+    rig.process(frames)
+    qi = [f * 3 + c for f in range(2) for c in range(3)]
+    ti = [(f + 1) * 3 + c for f in range(2) for c in range(3)]
+    out = rig.knn2_images(qi, ti)
+    for s, (a, b) in enumerate(zip(qi, ti)):
+        _, da = rig.features(a // 3, a % 3)
+        _, db = rig.features(b // 3, b % 3)
+        assert len(da) > 50 and len(db) > 50
+        assert np.array_equal(out[s, :len(da)], O.knn2(da, db)), s
+        assert (out[s, len(da):] == -1).all()
+    with pytest.raises(M.McsError):
+        rig.knn2_images([0], [99])
+
+
+def test_cpp_adaptor_interframe(tmp_path, golden):
+    """mcs_b200::InterFrameMatcher::findMatchesMono / findInterMatches (both overloads) and the pairwise
+    MultiCameraFrame::triangulateIntraMatches(kps_1, kps_2) from a C++ program: matches equal the cv2 fixture bit for bit, 3-D points
+    equal the oracle's f32 2-view DLT (+ camera-0 transform) within 1e-3 relative (f32 SVD, same bar as triangulate())."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from test_host_side import _build_adaptor
+    exe = _build_adaptor(tmp_path)
+    g = golden("inter_frame_cv2.npz")
+    d = tmp_path / "inter"
+    d.mkdir()
+    for k in ("d1", "d2", "xy1", "xy2", "m1", "m2", "mono1", "mono2", "p1", "p2", "lids1"):
+        (d / (k + ".bin")).write_bytes(np.ascontiguousarray(g[k]).tobytes())
+    C, npair = 4, 25
+    calib = M.synth.make_rig(C, 320, 240)
+    (d / "calib.bin").write_bytes(np.ascontiguousarray(calib).tobytes())
+    rng = np.random.default_rng(9)
+    P = [np.asarray(c["K"]).reshape(3, 3) @ np.hstack([np.asarray(c["R"]).reshape(3, 3), np.asarray(c["t"]).reshape(3, 1)]) for c in calib]
+    pairs, expect = [], []
+    for i in range(C - 1):
+        for j in range(i + 1, C):
+            X = np.hstack([rng.uniform(-2, 2, (npair, 2)), rng.uniform(4, 15, (npair, 1)), np.ones((npair, 1))])
+            u = (P[i] @ X.T).T
+            v = (P[j] @ X.T).T
+            p1 = (u[:, :2] / u[:, 2:] + rng.normal(0, 0.2, (npair, 2))).astype(np.float32)
+            p2 = (v[:, :2] / v[:, 2:] + rng.normal(0, 0.2, (npair, 2))).astype(np.float32)
+            pairs.append(np.hstack([p1, p2]))
+            pts = O.triangulate_pair_f32(calib, i, j, p1, p2)
+            if i != 0:  # MultiCameraFrame.cpp:458-468
+                R = np.asarray(calib[i]["R"]).reshape(3, 3).T
+                t = -R @ np.asarray(calib[i]["t"])
+                pts = (pts @ R.astype(np.float32).T + t.astype(np.float32)).astype(np.float32)
+            expect.append(pts)
+    (d / "pairs.bin").write_bytes(np.concatenate(pairs).astype(np.float32).tobytes())
+    (d / "meta.txt").write_text("%d %d %d %d %d %d %d\n" % (len(g["d1"]), len(g["d2"]), g["m1"].shape[1], g["isz"][0], g["isz"][1], C, npair))
+    out = subprocess.run([exe, "inter", str(d), str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    lines = (tmp_path / "o.txt").read_text().splitlines()
+
+    def rows(tag):
+        return np.array([list(map(int, l.split()[1:])) for l in lines if l.startswith(tag + " ")], np.int32).reshape(-1, 3)
+
+    assert np.array_equal(rows("mono"), g["mono_out"])
+    assert np.array_equal(rows("lf"), g["lf_split"]) and np.array_equal(rows("mo"), g["mono_split"])
+    assert np.array_equal(rows("single"), g["lf_single"])
+    assert "empty 0" in lines
+    got = np.array([[float(x) for x in l.split()[1:]] for l in lines if l.startswith("pt ")], np.float32)
+    exp = np.concatenate(expect)
+    assert got.shape == exp.shape
+    assert np.allclose(got, exp, rtol=1e-3, atol=1e-3), np.abs(got - exp).max()

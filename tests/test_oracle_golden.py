@@ -104,3 +104,27 @@ def test_lapping_area(golden):
     assert mono == int((~st).sum()) and len(k) == len(k0)
     assert (k[:mono] == k0[~st]).all() and (k[mono:] == k0[st][::-1]).all()
     assert np.array_equal(d[:mono], d0[~st]) and np.array_equal(d[mono:], d0[st][::-1])
+
+
+def test_knn2_matches_cv2_golden(golden):
+    """oracle knn2 == cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) incl. tie order (64 tied rows in the fixture)."""
+    import oracle_lib as O
+    g = golden("knn2_cv2.npz")
+    assert np.array_equal(O.knn2(g["q"], g["t"]), g["knn"])
+    one = O.knn2(g["q"][:5], g["t"][:1])
+    assert (one[:, 0] == 0).all() and (one[:, 2:] == -1).all()
+    assert (O.knn2(g["q"][:5], g["t"][:0]) == -1).all() and O.knn2(g["q"][:0], g["t"]).shape == (0, 4)
+
+
+def test_inter_frame_host_logic_matches_cv2_restatement(golden):
+    """oracle findMatchesMono / findInterMatches (both overloads) == the independent python + cv2 restatement the fixture was
+    generated with (oracle/gen_golden_knn2.py)."""
+    import oracle_lib as O
+    g = golden("inter_frame_cv2.npz")
+    assert np.array_equal(O.find_matches_mono(g["d1"], g["d2"], g["xy1"], g["xy2"], g["m1"], g["m2"], g["m1"].shape[1]), g["mono_out"])
+    args = (g["d1"], g["d2"], g["mono1"], g["mono2"], g["p1"], g["p2"], g["lids1"], int(g["isz"][0]), int(g["isz"][1]))
+    lf, mo = O.find_inter_matches(*args, split_mono=True)
+    assert np.array_equal(lf, g["lf_split"]) and np.array_equal(mo, g["mono_split"]) and len(lf) > 50 and len(mo) > 50
+    lf, mo = O.find_inter_matches(*args, split_mono=False)
+    assert np.array_equal(lf, g["lf_single"]) and len(mo) == 0
+    assert len(set(lf[:, 1].tolist())) == len(lf), "train indices are unique after the one-to-one step"
