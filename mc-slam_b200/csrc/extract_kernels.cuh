@@ -270,8 +270,17 @@ __device__ __forceinline__ int fast_strength_pol(const uint8_t* c, int tp, int s
 //   flags [ih][G] u8           pass-1 result per group of 4 pixels: bit 2e = bright pre-test of pixel e, bit 2e+1 = dark
 //   queue u16                  one entry per (pixel, polarity) that passed: corner << 15 | dark << 14 | ly << 7 | lx
 //   surv  u32                  NMS survivors (packed candidates)
+// c_magic20[n] = ceil(2^20 / n): t / n == (t * c_magic20[n]) >> 20 for the small t, n of the cell loops (checked on the host for
+// every plan, build_cell_table)
+#define MCS_M20(n) (((1u << 20) + (n) - 1u) / (n))
+__constant__ uint32_t c_magic20[32] = {0,           MCS_M20(1),  MCS_M20(2),  MCS_M20(3),  MCS_M20(4),  MCS_M20(5),  MCS_M20(6),  MCS_M20(7),
+                                       MCS_M20(8),  MCS_M20(9),  MCS_M20(10), MCS_M20(11), MCS_M20(12), MCS_M20(13), MCS_M20(14), MCS_M20(15),
+                                       MCS_M20(16), MCS_M20(17), MCS_M20(18), MCS_M20(19), MCS_M20(20), MCS_M20(21), MCS_M20(22), MCS_M20(23),
+                                       MCS_M20(24), MCS_M20(25), MCS_M20(26), MCS_M20(27), MCS_M20(28), MCS_M20(29), MCS_M20(30), MCS_M20(31)};
+
 __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_constant__ McsPlan P, ImageSet S,
-                                                                 uint32_t* __restrict__ cand, int* __restrict__ cand_count) {
+                                                                 const uint4* __restrict__ cell_tab, uint32_t* __restrict__ cand,
+                                                                 int* __restrict__ cand_count) {
     extern __shared__ __align__(16) unsigned char s_fast[];
     __shared__ int s_wsum[MCS_FAST_NT / 32], s_nsurv;
     uint32_t* s_tile = reinterpret_cast<uint32_t*>(s_fast);
@@ -281,20 +290,15 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
     uint32_t* s_surv = reinterpret_cast<uint32_t*>(s_fast + P.fast_ofs_surv);
     constexpr int TPW = MCS_FAST_TPW, TP = TPW * 4, SP = MCS_FAST_SP;
     const int img = blockIdx.y;
-    int level = 0;
-#pragma unroll 1
-    for (int l = 1; l < P.nlevels; l++)
-        if ((int)blockIdx.x >= P.L[l].cell_base) level = l;
+    // host-built cell record (build_cell_table): level, sub-image origin and size, candidate coordinate offset; cells the
+    // reference skips (:809, :818) are not in the table
+    const uint4 ct = __ldg(cell_tab + blockIdx.x);
+    const int level = (int)ct.x;
     const McsLevel& Lv = P.L[level];
-    const int ci = blockIdx.x - Lv.cell_base;
-    const int i = ci / Lv.n_cols, j = ci - i * Lv.n_cols;
-    const int maxBX = Lv.w - MCS_MIN_BORDER, maxBY = Lv.h - MCS_MIN_BORDER;
-    const int iniX = MCS_MIN_BORDER + j * Lv.w_cell, iniY = MCS_MIN_BORDER + i * Lv.h_cell;
-    if (iniY >= maxBY - 3 || iniX >= maxBX - 6) return;  // :809, :818
-    const int maxX = min(iniX + Lv.w_cell + 6, maxBX), maxY = min(iniY + Lv.h_cell + 6, maxBY);
-    const int cw = maxX - iniX, ch = maxY - iniY;  // sub-image handed to cv::FAST
-    const int iw = cw - 6, ih = ch - 6;            // computed interior
-    if (iw <= 0 || ih <= 0) return;
+    const int iniX = (int)(ct.y & 0xFFFFu), iniY = (int)(ct.y >> 16);
+    const int cw = (int)(ct.z & 0xFFFFu), ch = (int)(ct.z >> 16);  // sub-image handed to cv::FAST
+    const int iw = cw - 6, ih = ch - 6;                            // computed interior
+    const int xoff = (int)(ct.w & 0xFFFFu), yoff = (int)(ct.w >> 16);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int pitch;
     const uint8_t* src = level_ptr(P, S, img, level, pitch);
@@ -302,7 +306,7 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
     // stage the sub-image: shared word c of row r = image bytes (iniX - 1 + 4c) .. +3, cut out of two aligned 32-bit loads
     {
         const int nws = G + 2, gb = iniX - 1, aw = gb >> 2, sh = (gb & 3) * 8;
-        const uint32_t mg = ((1u << 20) + nws - 1) / nws;  // t / nws == (t * mg) >> 20 (t < 76 * 21)
+        const uint32_t mg = c_magic20[nws];  // t / nws == (t * mg) >> 20 (t < 76 * 21)
         for (int t = threadIdx.x; t < nws * ch; t += MCS_FAST_NT) {
             const int r = (int)(((uint32_t)t * mg) >> 20), c = t - r * nws;
             const uint32_t* g = reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * pitch) + aw + c;
@@ -310,7 +314,7 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
         }
     }
     const int ngroups = G * ih;
-    const uint32_t mgG = ((1u << 20) + G - 1) / G;
+    const uint32_t mgG = c_magic20[G];
     uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
     int* cnt = cand_count + img * P.nlevels + level;
     // FAST(cell, iniThFAST); only if that finds nothing, FAST(cell, minThFAST)  (:825, :842-845)
@@ -428,7 +432,7 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
             if (sc > max(max(n0, n1), n2)) {
                 const int slot = atomicAdd(&s_nsurv, 1);
                 // keypoint in ROI coordinates: FAST x in the sub-image (lx + 3) shifted by j*wCell (:864-865)
-                if (slot < P.fast_maxsurv) s_surv[slot] = mcs_oct::pack_cand(lx + 3 + j * Lv.w_cell, ly + 3 + i * Lv.h_cell, sc);
+                if (slot < P.fast_maxsurv) s_surv[slot] = mcs_oct::pack_cand(lx + xoff, ly + yoff, sc);
             }
         }
         __syncthreads();

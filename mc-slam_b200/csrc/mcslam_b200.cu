@@ -210,6 +210,27 @@ bool build_plan(const OrbTables& T, int width, int height, int use_angle, McsPla
     return true;
 }
 
+
+// One record per FAST cell the reference actually runs (ComputeKeyPointsOctTree :804-821; cells with iniY >= maxBorderY - 3 or
+// iniX >= maxBorderX - 6 are skipped there and are not listed): x = level, y = iniX | iniY << 16, z = sub-image width | height << 16,
+// w = candidate coordinate offset (3 + j * wCell) | (3 + i * hCell) << 16.
+void build_cell_table(const McsPlan& P, std::vector<uint4>& tab) {
+    tab.clear();
+    for (int l = 0; l < P.nlevels; l++) {
+        const McsLevel& L = P.L[l];
+        const int maxBX = L.w - MCS_MIN_BORDER, maxBY = L.h - MCS_MIN_BORDER;
+        for (int i = 0; i < L.n_rows; i++)
+            for (int j = 0; j < L.n_cols; j++) {
+                const int iniX = MCS_MIN_BORDER + j * L.w_cell, iniY = MCS_MIN_BORDER + i * L.h_cell;
+                if (iniY >= maxBY - 3 || iniX >= maxBX - 6) continue;
+                const int cw = std::min(iniX + L.w_cell + 6, maxBX) - iniX, ch = std::min(iniY + L.h_cell + 6, maxBY) - iniY;
+                if (cw - 6 <= 0 || ch - 6 <= 0) continue;
+                tab.push_back(make_uint4((unsigned)l, (unsigned)iniX | ((unsigned)iniY << 16), (unsigned)cw | ((unsigned)ch << 16),
+                                         (unsigned)(3 + j * L.w_cell) | ((unsigned)(3 + i * L.h_cell) << 16)));
+            }
+    }
+}
+
 }  // namespace
 
 // =================================================================================================================
@@ -230,6 +251,8 @@ struct Engine {
     // device buffers
     uint8_t *d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
     int2 *d_xtab = nullptr, *d_ytab = nullptr;
+    uint4* d_cell_tab = nullptr;  // FAST cell records (build_cell_table)
+    int n_fast_cells = 0;
     uint32_t *d_cand = nullptr, *d_sel = nullptr;
     uint16_t* d_knode = nullptr;
     int *d_cand_count = nullptr, *d_sel_count = nullptr, *d_kp_count = nullptr, *d_mono = nullptr;
@@ -252,12 +275,12 @@ struct Engine {
     ~Engine() { release(); }
 
     void free_all() {
-        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cand); cudaFree(d_sel);
+        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_cand); cudaFree(d_sel);
         cudaFree(d_knode); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
         cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp);
         cudaFreeHost(h_kps); cudaFreeHost(h_desc); cudaFreeHost(h_kp_count); cudaFreeHost(h_mono); cudaFreeHost(h_sel_count);
         cudaFreeHost(h_cand_count);
-        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
+        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
         d_cand_count = d_sel_count = d_kp_count = d_mono = nullptr; d_kps = d_kps_tmp = nullptr; d_desc = d_desc_tmp = nullptr;
         h_kps = nullptr; h_desc = nullptr; h_kp_count = h_mono = h_sel_count = h_cand_count = nullptr;
     }
@@ -328,8 +351,13 @@ struct Engine {
         } else {
             CK(cudaStreamSynchronize(stream));
         }
-        cudaFree(d_xtab); cudaFree(d_ytab);
-        d_xtab = d_ytab = nullptr;
+        cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab);
+        d_xtab = d_ytab = nullptr; d_cell_tab = nullptr;
+        std::vector<uint4> cells;
+        build_cell_table(np, cells);
+        n_fast_cells = (int)cells.size();
+        CK(cudaMalloc(&d_cell_tab, std::max<size_t>(cells.size(), 1) * sizeof(uint4)));
+        if (!cells.empty()) CK(cudaMemcpy(d_cell_tab, cells.data(), cells.size() * sizeof(uint4), cudaMemcpyHostToDevice));
         CK(cudaMalloc(&d_xtab, xt.size() * sizeof(int2)));
         CK(cudaMalloc(&d_ytab, yt.size() * sizeof(int2)));
         CK(cudaMemcpy(d_xtab, xt.data(), xt.size() * sizeof(int2), cudaMemcpyHostToDevice));
@@ -387,8 +415,8 @@ struct Engine {
             launches++;
         }
         mark(ST_FAST);
-        if (P.n_cells > 0) {
-            mcs::fast_cells_kernel<<<dim3(P.n_cells, n), MCS_FAST_NT, P.fast_smem_bytes, st>>>(P, set, cand, cand_count);
+        if (n_fast_cells > 0) {
+            mcs::fast_cells_kernel<<<dim3(n_fast_cells, n), MCS_FAST_NT, P.fast_smem_bytes, st>>>(P, set, d_cell_tab, cand, cand_count);
             launches++;
         }
         mark(ST_OCTREE);
