@@ -127,6 +127,51 @@ __global__ void __launch_bounds__(256) resize_level_words_kernel(const __grid_co
     *reinterpret_cast<uint32_t*>(dst + (uint32_t)(dy * D.pitch + dx0)) = outw;  // pitch % 64 == 0: row padding absorbs the tail
 }
 
+// Third form of K1, used when the host could build the selector tables (build_resize_word_tables: scale <= 2 and non-negative
+// coefficients that sum to <= 2049, which also makes the 0..255 saturation a no-op).  Per output word the table holds the first
+// source word, the byte shift that aligns source pixel sx[0] to byte 0 of an 8-byte window, four PRMT selectors relative to that
+// window and the four coefficient pairs; per output row the two clamped source rows and the vertical coefficients.  No per-pixel
+// index arithmetic is left in the kernel and all launch constants arrive as scalar arguments.
+struct ResizeSelArgs {
+    const uint8_t* src;   // level l-1 of image 0
+    uint8_t* dst;         // level l of image 0
+    size_t src_stride, dst_stride;  // bytes between images
+    int spitch, dpitch;
+    int lastw;            // last valid 32-bit word of a source row
+    int dwords, dh;       // output words per row, output rows
+    const int4* xw;       // [dwords][2]: {wi, selectors, c0, c1}, {c2, c3, shift, 0}
+    const int4* yw;       // [dh]: {sy0, sy1, b0, b1}
+};
+
+__global__ void __launch_bounds__(256) resize_level_sel_kernel(const ResizeSelArgs A) {
+    const int g = blockIdx.x * 32 + threadIdx.x, dy = blockIdx.y * 8 + threadIdx.y;
+    if (g >= A.dwords || dy >= A.dh) return;
+    const int4 xa = __ldg(A.xw + 2 * g), xb = __ldg(A.xw + 2 * g + 1);
+    const int4 yt = __ldg(A.yw + dy);
+    const uint8_t* base = A.src + blockIdx.z * A.src_stride;
+    const uint32_t* r0 = reinterpret_cast<const uint32_t*>(base + (uint32_t)(yt.x * A.spitch));
+    const uint32_t* r1 = reinterpret_cast<const uint32_t*>(base + (uint32_t)(yt.y * A.spitch));
+    const int wi = xa.x, wi1 = min(wi + 1, A.lastw), wi2 = min(wi + 2, A.lastw);
+    const uint32_t u0 = __ldg(r0 + wi), u1 = __ldg(r0 + wi1), u2 = __ldg(r0 + wi2);
+    const uint32_t v0 = __ldg(r1 + wi), v1 = __ldg(r1 + wi1), v2 = __ldg(r1 + wi2);
+    const uint32_t sh = (uint32_t)xb.z;
+    const uint32_t ua = __funnelshift_r(u0, u1, sh), ub = __funnelshift_r(u1, u2, sh);
+    const uint32_t va = __funnelshift_r(v0, v1, sh), vb = __funnelshift_r(v1, v2, sh);
+    const uint32_t cf[4] = {(uint32_t)xa.z, (uint32_t)xa.w, (uint32_t)xb.x, (uint32_t)xb.y};
+    const uint32_t sel = (uint32_t)xa.y;
+    const int b0 = yt.z, b1 = yt.w;
+    uint32_t outw = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t pu = __byte_perm(ua, ub, sel >> (8 * k)), pv = __byte_perm(va, vb, sel >> (8 * k));
+        const int h0 = (int)__dp2a_lo(cf[k], pu, 0u);
+        const int h1 = (int)__dp2a_lo(cf[k], pv, 0u);
+        const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;  // in 0..255 by construction of the tables
+        outw |= (uint32_t)v << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(A.dst + blockIdx.z * A.dst_stride + (uint32_t)(dy * A.dpitch + 4 * g)) = outw;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // K2  cv::GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) on 8U: 8.8 fixed-point kernel {18,34,48,56,48,34,18}/256,
 // exact integer accumulation, one rounding (v + 32768) >> 16.  Tile 64x16 + 3 px halo staged in shared memory,

@@ -211,6 +211,37 @@ bool build_plan(const OrbTables& T, int width, int height, int use_angle, McsPla
 }
 
 
+// Selector tables of resize_level_sel_kernel for one level (from the cv::resize tables of build_resize_axis).  Returns false when
+// the level cannot use that kernel (4 output pixels spanning more than 7 source bytes, or coefficients outside the range that keeps
+// the result in 0..255 without saturation).
+bool build_resize_word_tables(const McsLevel& D, const McsLevel& Sv, const std::vector<int2>& xtab, const std::vector<int2>& ytab,
+                              std::vector<int4>& xw, std::vector<int4>& yw) {
+    auto coef_ok = [](int packed) {
+        const int a0 = (short)(packed & 0xFFFF), a1 = packed >> 16;
+        return a0 >= 0 && a1 >= 0 && a0 + a1 <= 2049;
+    };
+    const int dwords = (D.w + 3) / 4;
+    for (int g = 0; g < dwords; g++) {
+        const int2* e = &xtab[D.xtab_ofs + 4 * g];  // padded by 4 entries past the row end
+        const int sx0 = e[0].x;
+        uint32_t sel = 0;
+        for (int k = 0; k < 4; k++) {
+            const int o = e[k].x - sx0;
+            if (o < 0 || o > 6 || e[k].x < 0 || !coef_ok(e[k].y)) return false;
+            sel |= (uint32_t)(o | ((o + 1) << 4)) << (8 * k);
+        }
+        xw.push_back(make_int4(sx0 >> 2, (int)sel, e[0].y, e[1].y));
+        xw.push_back(make_int4(e[2].y, e[3].y, (sx0 & 3) * 8, 0));
+    }
+    for (int dy = 0; dy < D.h; dy++) {
+        const int2 y = ytab[D.ytab_ofs + dy];
+        if (!coef_ok(y.y)) return false;
+        const int sy0 = std::min(std::max(y.x, 0), Sv.h - 1), sy1 = std::min(std::max(y.x + 1, 0), Sv.h - 1);
+        yw.push_back(make_int4(sy0, sy1, (short)(y.y & 0xFFFF), y.y >> 16));
+    }
+    return true;
+}
+
 // One record per FAST cell the reference actually runs (ComputeKeyPointsOctTree :804-821; cells with iniY >= maxBorderY - 3 or
 // iniX >= maxBorderX - 6 are skipped there and are not listed): x = level, y = iniX | iniY << 16, z = sub-image width | height << 16,
 // w = candidate coordinate offset (3 + j * wCell) | (3 + i * hCell) << 16.
@@ -252,6 +283,9 @@ struct Engine {
     uint8_t *d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
     int2 *d_xtab = nullptr, *d_ytab = nullptr;
     uint4* d_cell_tab = nullptr;  // FAST cell records (build_cell_table)
+    int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
+    int rs_xw_ofs[MCS_PLAN_MAX_LEVELS] = {}, rs_yw_ofs[MCS_PLAN_MAX_LEVELS] = {};
+    bool rs_sel_ok = false;
     int n_fast_cells = 0;
     uint32_t *d_cand = nullptr, *d_sel = nullptr;
     uint16_t* d_knode = nullptr;
@@ -275,12 +309,12 @@ struct Engine {
     ~Engine() { release(); }
 
     void free_all() {
-        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_cand); cudaFree(d_sel);
+        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_rs_tab); cudaFree(d_cand); cudaFree(d_sel);
         cudaFree(d_knode); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
         cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp);
         cudaFreeHost(h_kps); cudaFreeHost(h_desc); cudaFreeHost(h_kp_count); cudaFreeHost(h_mono); cudaFreeHost(h_sel_count);
         cudaFreeHost(h_cand_count);
-        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
+        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_rs_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
         d_cand_count = d_sel_count = d_kp_count = d_mono = nullptr; d_kps = d_kps_tmp = nullptr; d_desc = d_desc_tmp = nullptr;
         h_kps = nullptr; h_desc = nullptr; h_kp_count = h_mono = h_sel_count = h_cand_count = nullptr;
     }
@@ -358,6 +392,24 @@ struct Engine {
         n_fast_cells = (int)cells.size();
         CK(cudaMalloc(&d_cell_tab, std::max<size_t>(cells.size(), 1) * sizeof(uint4)));
         if (!cells.empty()) CK(cudaMemcpy(d_cell_tab, cells.data(), cells.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+        {
+            std::vector<int4> rs;
+            rs_sel_ok = true;
+            for (int l = 1; l < np.nlevels && rs_sel_ok; l++) {
+                std::vector<int4> xw, yw;
+                rs_sel_ok = build_resize_word_tables(np.L[l], np.L[l - 1], xt, yt, xw, yw);
+                rs_xw_ofs[l] = (int)rs.size();
+                rs.insert(rs.end(), xw.begin(), xw.end());
+                rs_yw_ofs[l] = (int)rs.size();
+                rs.insert(rs.end(), yw.begin(), yw.end());
+            }
+            cudaFree(d_rs_tab);
+            d_rs_tab = nullptr;
+            if (rs_sel_ok && !rs.empty()) {
+                CK(cudaMalloc(&d_rs_tab, rs.size() * sizeof(int4)));
+                CK(cudaMemcpy(d_rs_tab, rs.data(), rs.size() * sizeof(int4), cudaMemcpyHostToDevice));
+            }
+        }
         CK(cudaMalloc(&d_xtab, xt.size() * sizeof(int2)));
         CK(cudaMalloc(&d_ytab, yt.size() * sizeof(int2)));
         CK(cudaMemcpy(d_xtab, xt.data(), xt.size() * sizeof(int2), cudaMemcpyHostToDevice));
@@ -410,7 +462,21 @@ struct Engine {
         CK(cudaMemsetAsync(cand_count, 0, (size_t)n * P.nlevels * sizeof(int), st));
         for (int l = 1; l < P.nlevels; l++) {
             dim3 b(32, 8), g((P.L[l].w + 127) / 128, (P.L[l].h + 7) / 8, n);
-            if (T.scale_factor_f <= 2.0f) mcs::resize_level_words_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
+            if (rs_sel_ok && d_rs_tab) {
+                mcs::ResizeSelArgs A;
+                A.src = l == 1 ? set.l0 : set.pyr + P.L[l - 1].plane_ofs;
+                A.src_stride = l == 1 ? set.l0_stride : (size_t)P.pyr_stride;
+                A.spitch = l == 1 ? set.l0_pitch : P.L[l - 1].pitch;
+                A.dst = set.pyr + P.L[l].plane_ofs;
+                A.dst_stride = (size_t)P.pyr_stride;
+                A.dpitch = P.L[l].pitch;
+                A.lastw = ((P.L[l - 1].w + 3) >> 2) - 1;
+                A.dwords = (P.L[l].w + 3) / 4;
+                A.dh = P.L[l].h;
+                A.xw = d_rs_tab + rs_xw_ofs[l];
+                A.yw = d_rs_tab + rs_yw_ofs[l];
+                mcs::resize_level_sel_kernel<<<g, b, 0, st>>>(A);
+            } else if (T.scale_factor_f <= 2.0f) mcs::resize_level_words_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
             else mcs::resize_level_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
             launches++;
         }
