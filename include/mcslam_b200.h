@@ -224,6 +224,16 @@ MCS_API int mcs_knn2_device(mcs_matcher* m, const void* d_q_desc, const int* q_c
 MCS_API void* mcs_matcher_stream(mcs_matcher* m);
 MCS_API int mcs_matcher_synchronize(mcs_matcher* m);
 MCS_API long long mcs_matcher_kernel_launches(const mcs_matcher* m);
+/* ORBextractor::getMatches_distRatio (MCSlam/src/ORBextractor.cpp:1228-1290) for n_groups candidate-list pairs in one launch: the
+ * per-node calls of MultiCameraFrame::BowMatching (MultiCameraFrame.cpp:946-1022) and FrontEnd::InterMatchingBow (FrontEnd.cpp:3791,
+ * :3905).  Group g matches the features a_idx[a_ofs[g] .. a_ofs[g+1]) of descA against b_idx[b_ofs[g] .. b_ofs[g+1]) of descB
+ * (CSR lists; the caller intersects the two DBoW2 FeatureVectors).  Accept: best <= th_low (TH_LOW = 75, ORBextractor.h:27) and
+ * best / second <= max_neighbor_ratio (0.85, :90) in double; a B feature claimed twice keeps the closer A feature.  match_a /
+ * match_b (capacity a_ofs[n_groups]) receive the groups' i_match_A / i_match_B concatenated in group order; group_count[g] (optional)
+ * the matches of group g; *book_k (optional) the BookK distance-evaluation count.  Returns the total number of matches. */
+MCS_API int mcs_match_subsets(mcs_matcher* m, const uint8_t* descA, int nA, const uint8_t* descB, int nB, int n_groups, const int* a_ofs,
+                              const uint32_t* a_idx, const int* b_ofs, const uint32_t* b_idx, int th_low, double max_neighbor_ratio,
+                              uint32_t* match_a, uint32_t* match_b, int* group_count, long long* book_k);
 /* knnMatch(k = 2) between feature sets a rig handle already holds on the device (no descriptor traffic over PCIe): set s matches
  * image q_image[s] = frame * num_cams + cam against image t_image[s], e.g. findMatchesMono for every consecutive frame pair of a
  * batch.  out_knn: [n_sets][feature_capacity][4]; rows past the query image's keypoint count stay -1. */

@@ -38,7 +38,7 @@ EXPORTS = [
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
-    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images",
+    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets",
 ]
 
 
@@ -112,6 +112,7 @@ def lib():
     L.mcs_matcher_kernel_launches.restype = C.c_longlong
     L.mcs_matcher_kernel_launches.argtypes = [vp]
     L.mcs_rig_knn2_images.argtypes = [vp, vp, vp, ci, vp]
+    L.mcs_match_subsets.argtypes = [vp, vp, ci, vp, ci, ci, vp, vp, vp, vp, ci, C.c_double, vp, vp, vp, vp]
     L.mcs_device_malloc.restype = vp
     L.mcs_device_malloc.argtypes = [ci, C.c_size_t]
     L.mcs_device_free.argtypes = [ci, vp]
@@ -443,6 +444,32 @@ class Matcher:
         n = _check(lib().mcs_knn2(self.hd, _p(q), _p(qc), _p(t), _p(tc), len(qs), _p(out)), "knn2")
         assert n == len(q)
         return np.split(out[:n], np.cumsum(qc)[:-1])
+
+    def match_subsets(self, A, B, groups_a, groups_b, th_low=75, max_ratio=0.85):
+        """getMatches_distRatio (ORBextractor.cpp:1228-1290) for the candidate-list pairs zip(groups_a, groups_b) in one launch.
+        Returns (i_match_A, i_match_B, per-group counts, BookK), matches concatenated in group order."""
+        A = np.ascontiguousarray(A, np.uint8).reshape(-1, 32)
+        B = np.ascontiguousarray(B, np.uint8).reshape(-1, 32)
+        ao = np.zeros(len(groups_a) + 1, np.int32)
+        bo = np.zeros(len(groups_b) + 1, np.int32)
+        ao[1:] = np.cumsum([len(g) for g in groups_a])
+        bo[1:] = np.cumsum([len(g) for g in groups_b])
+        ai = np.array([i for g in groups_a for i in g], np.uint32)
+        bi = np.array([i for g in groups_b for i in g], np.uint32)
+        ma = np.zeros(max(len(ai), 1), np.uint32)
+        mb = np.zeros(max(len(ai), 1), np.uint32)
+        gc = np.zeros(max(len(groups_a), 1), np.int32)
+        bk = C.c_longlong(0)
+        n = _check(lib().mcs_match_subsets(self.hd, _p(A), len(A), _p(B), len(B), len(groups_a), _p(ao), _p(ai), _p(bo), _p(bi), th_low,
+                                           max_ratio, _p(ma), _p(mb), _p(gc), C.byref(bk)), "match_subsets")
+        return ma[:n], mb[:n], gc[:len(groups_a)], bk.value
+
+    def bow_matching(self, A, B, fv_a, fv_b, th_low=75, max_ratio=0.85):
+        """Node walk of BowMatching / InterMatchingBow (MultiCameraFrame.cpp:946-1022, FrontEnd.cpp:3791-3965) over two feature
+        vectors {node id: [indices]}: nodes present in both, ascending.  Returns (indices_1, indices_2, words, BookK)."""
+        nodes = sorted(set(fv_a) & set(fv_b))
+        ma, mb, gc, bk = self.match_subsets(A, B, [fv_a[n] for n in nodes], [fv_b[n] for n in nodes], th_low, max_ratio)
+        return ma, mb, np.array([n for n, c in zip(nodes, gc) if c >= 1], np.uint32), bk
 
     def knn2_device(self, d_q, q_counts, d_t, t_counts, d_out):
         qc = np.ascontiguousarray(q_counts, np.int32)

@@ -142,6 +142,78 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) knn2_kernel(const uint8_t* __res
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K6c  ORBextractor::getMatches_distRatio (/root/reference/MCSlam/src/ORBextractor.cpp:1228-1290) for many candidate-list pairs
+// ("groups": the features of one vocabulary node in image A and in image B) per launch; one block per group.
+// Phase 1, thread per query of i_A: best / second-best candidate of i_B with strict '<' (first candidate wins ties, :1253-1262);
+// accepted when best <= th_low and (double)best / (double)second <= max_ratio (:1264-1265; second = 1e9 with one candidate).
+// Phase 2, warp 0, queries in list order: a B feature claimed twice keeps the closer A feature at the position of the first claim
+// (:1268-1284); the linear search of the reference runs 32 entries per step.
+// Outputs of group g start at a_ofs[g] (a group makes at most |i_A| matches); group_count / group_dups give the match count and
+// the number of duplicate-claim distance re-evaluations (BookK bookkeeping).
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
+           __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void __launch_bounds__(128) subset_match_kernel(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
+                                                           const int* __restrict__ a_ofs, const uint32_t* __restrict__ a_idx,
+                                                           const int* __restrict__ b_ofs, const uint32_t* __restrict__ b_idx, int th_low,
+                                                           double max_ratio, uint32_t* __restrict__ tmp_b, int* __restrict__ tmp_d,
+                                                           uint32_t* __restrict__ match_a, uint32_t* __restrict__ match_b,
+                                                           int* __restrict__ match_d, int* __restrict__ group_count,
+                                                           int* __restrict__ group_dups) {
+    const int g = blockIdx.x;
+    const int a0 = a_ofs[g], na = a_ofs[g + 1] - a0, b0 = b_ofs[g], nb = b_ofs[g + 1] - b0;
+    for (int i = threadIdx.x; i < na; i += blockDim.x) {
+        const uint4* qa = reinterpret_cast<const uint4*>(A + (size_t)a_idx[a0 + i] * 32);
+        const uint4 q0 = __ldg(qa), q1 = __ldg(qa + 1);
+        int best_j = -1, best1 = 1 << 30, best2 = 1 << 30;
+        for (int j = 0; j < nb; j++) {
+            const uint4* tb = reinterpret_cast<const uint4*>(B + (size_t)__ldg(b_idx + b0 + j) * 32);
+            const int d = hamming256(q0, q1, __ldg(tb), __ldg(tb + 1));
+            if (d < best1) { best_j = j; best2 = best1; best1 = d; }
+            else if (d < best2) best2 = d;
+        }
+        const double d2 = best2 == (1 << 30) ? 1e9 : (double)best2;
+        const bool ok = best_j >= 0 && best1 <= th_low && __ddiv_rn((double)best1, d2) <= max_ratio;
+        tmp_b[a0 + i] = ok ? b_idx[b0 + best_j] : 0xFFFFFFFFu;
+        tmp_d[a0 + i] = best1;
+    }
+    __syncthreads();
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x;
+    int n = 0, dups = 0;
+    for (int i = 0; i < na; i++) {
+        const uint32_t idxB = tmp_b[a0 + i];
+        if (idxB == 0xFFFFFFFFu) continue;  // warp-uniform
+        int pos = -1;
+        for (int k0 = 0; k0 < n && pos < 0; k0 += 32) {
+            const int k = k0 + lane;
+            const unsigned hit = __ballot_sync(0xFFFFFFFFu, k < n && match_b[a0 + k] == idxB);
+            if (hit) pos = k0 + __ffs(hit) - 1;
+        }
+        if (lane == 0) {
+            const int d1 = tmp_d[a0 + i];
+            if (pos < 0) {
+                match_b[a0 + n] = idxB;
+                match_a[a0 + n] = a_idx[a0 + i];
+                match_d[a0 + n] = d1;
+            } else if (d1 < match_d[a0 + pos]) {  // distance of the current holder to idxB == its own best distance
+                match_a[a0 + pos] = a_idx[a0 + i];
+                match_d[a0 + pos] = d1;
+            }
+        }
+        if (pos < 0) n++; else dups++;
+        __syncwarp();
+    }
+    if (lane == 0) {
+        group_count[g] = n;
+        group_dups[g] = dups;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K7  merge.  The reference mutates match_inv_idx in pair order, later pairs see earlier state (:1222-1266), so the
 // walk is sequential per frame: one block per frame, thread 0 walks, the block initialises.  match_inv_idx lives in
 // shared memory (u16, 0xFFFF = -1).

@@ -1443,10 +1443,13 @@ struct mcs_matcher {
     mcs::Knn2Set *d_sets = nullptr, *h_sets = nullptr;
     int4* d_out = nullptr;
     long long launches = 0;
+    // subset matcher workspace (grown on demand): CSR offsets, index lists, per-query scratch, outputs
+    int *d_sub_i32 = nullptr;
+    size_t sub_cap = 0;
     ~mcs_matcher() {
         if (cudaSetDevice(device) != cudaSuccess) return;
         if (stream) cudaStreamDestroy(stream);
-        cudaFree(d_q); cudaFree(d_t); cudaFree(d_sets); cudaFree(d_out);
+        cudaFree(d_q); cudaFree(d_t); cudaFree(d_sets); cudaFree(d_out); cudaFree(d_sub_i32);
         if (h_sets) cudaFreeHost(h_sets);
     }
     int init() {
@@ -1534,6 +1537,76 @@ int mcs_matcher_synchronize(mcs_matcher* m) {
     CK(cudaSetDevice(m->device));
     CK(cudaStreamSynchronize(m->stream));
     return 0;
+}
+
+// ORBextractor::getMatches_distRatio for n_groups candidate-list pairs (see K6c).  Host buffers; blocking.
+int mcs_match_subsets(mcs_matcher* m, const uint8_t* descA, int nA, const uint8_t* descB, int nB, int n_groups, const int* a_ofs,
+                      const uint32_t* a_idx, const int* b_ofs, const uint32_t* b_idx, int th_low, double max_neighbor_ratio,
+                      uint32_t* match_a, uint32_t* match_b, int* group_count, long long* book_k) {
+    if (!m || n_groups < 0 || nA < 0 || nB < 0) return MCS_ERR_ARG;
+    if (book_k) *book_k = 0;
+    if (n_groups == 0) return 0;
+    if (!a_ofs || !b_ofs || !match_a || !match_b) return MCS_ERR_ARG;
+    CK(cudaSetDevice(m->device));
+    const int ta = a_ofs[n_groups], tb = b_ofs[n_groups];
+    if (a_ofs[0] != 0 || b_ofs[0] != 0 || ta < 0 || tb < 0) { set_err("match_subsets: offsets must start at 0"); return MCS_ERR_ARG; }
+    for (int g = 0; g < n_groups; g++)
+        if (a_ofs[g + 1] < a_ofs[g] || b_ofs[g + 1] < b_ofs[g]) { set_err("match_subsets: offsets must not decrease"); return MCS_ERR_ARG; }
+    for (int i = 0; i < ta; i++) if (a_idx[i] >= (uint32_t)nA) { set_err("match_subsets: index into A out of range"); return MCS_ERR_ARG; }
+    for (int i = 0; i < tb; i++) if (b_idx[i] >= (uint32_t)nB) { set_err("match_subsets: index into B out of range"); return MCS_ERR_ARG; }
+    if (nA > m->max_q || nB > m->max_t) { set_err("match_subsets: descriptor rows exceed the matcher's capacity"); return MCS_ERR_CAPACITY; }
+    if (ta == 0) { if (group_count) memset(group_count, 0, n_groups * sizeof(int)); return 0; }
+    // workspace layout (int32 units): a_ofs | b_ofs | a_idx | b_idx | tmp_b | tmp_d | match_a | match_b | match_d | count | dups
+    const size_t G1 = (size_t)n_groups + 1;
+    const size_t need = 2 * G1 + (size_t)ta + tb + 5 * (size_t)ta + 2 * (size_t)n_groups;
+    if (need > m->sub_cap) {
+        cudaFree(m->d_sub_i32);
+        m->d_sub_i32 = nullptr;
+        m->sub_cap = 0;
+        CK(cudaMalloc(&m->d_sub_i32, need * 2 * sizeof(int)));
+        m->sub_cap = need * 2;
+    }
+    int* w = m->d_sub_i32;
+    int* d_aofs = w; w += G1;
+    int* d_bofs = w; w += G1;
+    uint32_t* d_aidx = (uint32_t*)w; w += ta;
+    uint32_t* d_bidx = (uint32_t*)w; w += tb;
+    uint32_t* d_tmpb = (uint32_t*)w; w += ta;
+    int* d_tmpd = w; w += ta;
+    uint32_t* d_ma = (uint32_t*)w; w += ta;
+    uint32_t* d_mb = (uint32_t*)w; w += ta;
+    int* d_md = w; w += ta;
+    int* d_cnt = w; w += n_groups;
+    int* d_dup = w;
+    cudaStream_t st = m->stream;
+    CK(cudaMemcpyAsync(m->d_q, descA, (size_t)nA * 32, cudaMemcpyHostToDevice, st));
+    if (nB) CK(cudaMemcpyAsync(m->d_t, descB, (size_t)nB * 32, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_aofs, a_ofs, G1 * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_bofs, b_ofs, G1 * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_aidx, a_idx, (size_t)ta * sizeof(int), cudaMemcpyHostToDevice, st));
+    if (tb) CK(cudaMemcpyAsync(d_bidx, b_idx, (size_t)tb * sizeof(int), cudaMemcpyHostToDevice, st));
+    mcs::subset_match_kernel<<<n_groups, 128, 0, st>>>(m->d_q, m->d_t, d_aofs, d_aidx, d_bofs, d_bidx, th_low, max_neighbor_ratio, d_tmpb,
+                                                        d_tmpd, d_ma, d_mb, d_md, d_cnt, d_dup);
+    CK(cudaGetLastError());
+    m->launches++;
+    std::vector<uint32_t> ha(ta), hb(ta);
+    std::vector<int> hc(2 * (size_t)n_groups);
+    CK(cudaMemcpyAsync(ha.data(), d_ma, (size_t)ta * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hb.data(), d_mb, (size_t)ta * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hc.data(), d_cnt, 2 * (size_t)n_groups * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    int n = 0;
+    long long book = 0;
+    for (int g = 0; g < n_groups; g++) {  // concatenate the groups' match lists in group order
+        const int c = hc[g];
+        memcpy(match_a + n, ha.data() + a_ofs[g], c * sizeof(uint32_t));
+        memcpy(match_b + n, hb.data() + a_ofs[g], c * sizeof(uint32_t));
+        if (group_count) group_count[g] = c;
+        n += c;
+        book += (long long)(a_ofs[g + 1] - a_ofs[g]) * (b_ofs[g + 1] - b_ofs[g]) + hc[n_groups + g];
+    }
+    if (book_k) *book_k = book;
+    return n;
 }
 
 // knnMatch(k = 2) between feature sets the rig already holds on the device: set s matches image q_image[s] (= frame * num_cams + cam)

@@ -3,6 +3,7 @@
 //   ORBextractor       /root/reference/MCSlam/include/MCSlam/ORBextractor.h:44-112
 //   MultiCameraFrame   /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h (extract / intra-match / triangulate subset)
 //   IntraMatch         /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h:42-57
+//   BowMatcher         ORBextractor::getMatches_distRatio (ORBextractor.cpp:1228-1290) + the BowMatching / InterMatchingBow node walk
 //   InterFrameMatcher  FrontEnd::findMatchesMono / findInterMatches, /root/reference/MCSlam/src/FrontEnd.cpp:3114-3470
 // Without OpenCV headers the containers are PODs (mcs_keypoint, byte vectors).  Define MCS_WITH_OPENCV before including this
 // file (in a build that has OpenCV) to get the cv::InputArray / cv::KeyPoint / cv::Mat overloads with the reference's exact
@@ -15,6 +16,8 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <map>
+#include <set>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -304,6 +307,84 @@ private:
     mcs_rig* h_ = nullptr;
     int w_, h_img_, kp_cap_ = 0, row_cap_ = 0;
     const uint8_t* images_ = nullptr;
+};
+
+// DBoW2::FeatureVector as the matchers read it: node id -> indices of the features that fell into that vocabulary node, ordered by
+// node id.  The vocabulary itself (DBoW2 transform, MultiCameraFrame.cpp:257) stays with the caller.
+typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
+
+// The BoW-guided matchers: ORBextractor::getMatches_distRatio (ORBextractor.cpp:1228-1290) and the node walk around it in
+// MultiCameraFrame::BowMatching (MultiCameraFrame.cpp:946-1022) and FrontEnd::InterMatchingBow (FrontEnd.cpp:3791-3840, :3905-3965).
+// All common nodes of the two feature vectors are matched in ONE kernel launch (mcs_match_subsets) instead of one call per node.
+class BowMatcher {
+public:
+    explicit BowMatcher(int device = 0, int max_rows = 16384) {
+        h_ = mcs_matcher_create(device, 1, max_rows, max_rows);
+        if (!h_) throw std::runtime_error(std::string("mcs_matcher_create: ") + mcs_last_error());
+    }
+    ~BowMatcher() { mcs_matcher_destroy(h_); }
+    BowMatcher(const BowMatcher&) = delete;
+    BowMatcher& operator=(const BowMatcher&) = delete;
+
+    double max_neighbor_ratio = 0.85;  // ORBextractor.h:90
+    int TH_LOW = 75;                   // ORBextractor.h:27
+
+    // getMatches_distRatio(A, i_A, B, i_B, i_match_A, i_match_B, BookK): A, B = descriptor rows (n x 32 bytes)
+    void getMatches_distRatio(const uint8_t* A, int nA, const std::vector<unsigned int>& i_A, const uint8_t* B, int nB,
+                              const std::vector<unsigned int>& i_B, std::vector<unsigned int>& i_match_A,
+                              std::vector<unsigned int>& i_match_B, int& BookK) {
+        const int a_ofs[2] = {0, (int)i_A.size()}, b_ofs[2] = {0, (int)i_B.size()};
+        i_match_A.assign(i_A.size(), 0);
+        i_match_B.assign(i_A.size(), 0);
+        long long book = 0;
+        const int n = mcs_match_subsets(h_, A, nA, B, nB, 1, a_ofs, i_A.data(), b_ofs, i_B.data(), TH_LOW, max_neighbor_ratio,
+                                        i_match_A.data(), i_match_B.data(), nullptr, &book);
+        check(n, "mcs_match_subsets");
+        i_match_A.resize(n);
+        i_match_B.resize(n);
+        BookK += (int)book;
+    }
+
+    // BowMatching / InterMatchingBow: walk both feature vectors in node order (the lower_bound walk of the reference visits exactly
+    // the node ids present in both), match every common node, concatenate in node order; `words` receives the nodes with >= 1 match.
+    void BowMatching(const FeatureVector& featVec1, const FeatureVector& featVec2, const uint8_t* descs1, int n1, const uint8_t* descs2,
+                     int n2, std::vector<unsigned int>& indices_1, std::vector<unsigned int>& indices_2,
+                     std::set<unsigned int>* words = nullptr) {
+        indices_1.clear();
+        indices_2.clear();
+        std::vector<int> a_ofs(1, 0), b_ofs(1, 0);
+        std::vector<unsigned int> a_idx, b_idx, nodes;
+        FeatureVector::const_iterator it1 = featVec1.begin(), it2 = featVec2.begin();
+        while (it1 != featVec1.end() && it2 != featVec2.end()) {
+            if (it1->first == it2->first) {
+                nodes.push_back(it1->first);
+                a_idx.insert(a_idx.end(), it1->second.begin(), it1->second.end());
+                b_idx.insert(b_idx.end(), it2->second.begin(), it2->second.end());
+                a_ofs.push_back((int)a_idx.size());
+                b_ofs.push_back((int)b_idx.size());
+                ++it1; ++it2;
+            } else if (it1->first < it2->first) {
+                it1 = featVec1.lower_bound(it2->first);
+            } else {
+                it2 = featVec2.lower_bound(it1->first);
+            }
+        }
+        if (nodes.empty()) return;
+        indices_1.assign(a_idx.size(), 0);
+        indices_2.assign(a_idx.size(), 0);
+        std::vector<int> counts(nodes.size(), 0);
+        const int n = mcs_match_subsets(h_, descs1, n1, descs2, n2, (int)nodes.size(), a_ofs.data(), a_idx.data(), b_ofs.data(), b_idx.data(),
+                                        TH_LOW, max_neighbor_ratio, indices_1.data(), indices_2.data(), counts.data(), nullptr);
+        check(n, "mcs_match_subsets");
+        indices_1.resize(n);
+        indices_2.resize(n);
+        if (words)
+            for (size_t g = 0; g < nodes.size(); g++)
+                if (counts[g] >= 1) words->insert(nodes[g]);
+    }
+
+private:
+    mcs_matcher* h_ = nullptr;
 };
 
 // cv::DMatch stand-in (queryIdx, trainIdx, distance); with MCS_WITH_OPENCV the methods below also fill std::vector<cv::DMatch>.

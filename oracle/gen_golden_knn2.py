@@ -92,3 +92,64 @@ np.savez_compressed(os.path.join(OUT, "inter_frame_cv2.npz"), d1=d1, d2=d2, xy1=
                     mono1=mono1, mono2=mono2, p1=p1, p2=p2, lids1=lids1, isz=np.array([isz1, isz2]), lf_split=lf_a, mono_split=mo_a,
                     lf_single=lf_b)
 print("findMatchesMono", len(mono_out), "findInterMatches split", len(lf_a), len(mo_a), "single", len(lf_b))
+
+
+# ---- BoW-guided subset matcher: ORBextractor::getMatches_distRatio (ORBextractor.cpp:1228-1290) + the node walk of BowMatching /
+# InterMatchingBow (MultiCameraFrame.cpp:946-1022, FrontEnd.cpp:3791-3965), restated in python over numpy popcounts.  The DBoW2
+# vocabulary is absent, so node ids are synthetic: matching features mostly share a node, with some scattered to other nodes.
+def py_dist(a, b):
+    return int(np.unpackbits(a ^ b).sum())
+
+
+def py_matches_dist_ratio(A, iA, B, iB, th_low=75, ratio=0.85):
+    ma, mb, book = [], [], 0
+    for ia in iA:
+        best_j, b1, b2 = -1, 1e9, 1e9
+        for j, ib in enumerate(iB):
+            d = float(py_dist(A[ia], B[ib])); book += 1
+            if d < b1:
+                best_j, b2, b1 = j, b1, d
+            elif d < b2:
+                b2 = d
+        if b1 <= th_low and b1 / b2 <= ratio:
+            idx_b = iB[best_j]
+            if idx_b not in mb:
+                mb.append(idx_b); ma.append(ia)
+            else:
+                k = mb.index(idx_b)
+                d = float(py_dist(A[ma[k]], B[idx_b])); book += 1
+                if b1 < d:
+                    ma[k] = ia
+    return ma, mb, book
+
+
+rng = np.random.default_rng(13)
+nB = 900
+B = rng.integers(0, 256, (nB, 32), dtype=np.uint8)
+srcA = rng.permutation(nB)[:800]
+A = B[srcA].copy()
+for k in range(len(A)):
+    bits = rng.choice(256, int(rng.integers(0, 90)), replace=False)
+    np.bitwise_xor.at(A[k], bits // 8, (1 << (bits % 8)).astype(np.uint8))
+A[700:] = A[rng.integers(0, 700, 100)]    # repeated A features: several queries claim the same B feature
+node_of_B = rng.integers(0, 60, nB) * 7 + 3
+node_of_A = node_of_B[srcA].copy()
+node_of_A[700:] = node_of_B[srcA[:700]][rng.integers(0, 700, 100)]
+scatter = rng.random(800) < 0.15
+node_of_A[scatter] = rng.integers(0, 70, int(scatter.sum())) * 7 + 3   # includes node ids that do not exist in B
+fvA, fvB = {}, {}
+for i, nd in enumerate(node_of_A):
+    fvA.setdefault(int(nd), []).append(i)
+for i, nd in enumerate(node_of_B):
+    fvB.setdefault(int(nd), []).append(i)
+i1, i2, words, book = [], [], [], 0
+for nd in sorted(set(fvA) & set(fvB)):     # the lower_bound walk visits exactly the common node ids in ascending order
+    a, b, k = py_matches_dist_ratio(A, fvA[nd], B, fvB[nd])
+    book += k
+    i1 += a; i2 += b
+    if a:
+        words.append(nd)
+np.savez_compressed(os.path.join(OUT, "bow_subsets.npz"), A=A, B=B, node_of_A=node_of_A.astype(np.int32), node_of_B=node_of_B.astype(np.int32),
+                    indices_1=np.array(i1, np.uint32), indices_2=np.array(i2, np.uint32), words=np.array(words, np.uint32),
+                    book_k=np.array([book], np.int64))
+print("bow subsets: nodes", len(fvA), len(fvB), "matches", len(i1), "words", len(words), "BookK", book)

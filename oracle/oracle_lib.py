@@ -56,6 +56,8 @@ def lib():
         L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orc_find_matches_mono.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
         L.orc_find_inter_matches.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_void_p] * 3
+        L.orc_matches_dist_ratio.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 3
+        L.orc_bow_matching.argtypes = [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 5
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_triangulate_pixels.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -228,6 +230,45 @@ def find_inter_matches(d1, d2, mono1, mono2, p1, p2, lids1, isz1, isz2, split_mo
     n = lib().orc_find_inter_matches(_p(d1), len(d1), _p(d2), len(d2), _p(mono1), _p(mono2), _p(p1), _p(p2), _p(lids1), isz1, isz2,
                                      int(split_mono), _p(lf), _p(mo), C.byref(nm))
     return lf[:n], mo[:nm.value]
+
+
+def feature_vector_csr(fv):
+    """{node id: [feature indices]} (a DBoW2::FeatureVector) -> (ascending node ids u32, CSR offsets i32, indices u32)."""
+    nodes = sorted(fv)
+    ofs = np.zeros(len(nodes) + 1, np.int32)
+    for k, nd in enumerate(nodes):
+        ofs[k + 1] = ofs[k] + len(fv[nd])
+    idx = np.array([i for nd in nodes for i in fv[nd]], np.uint32)
+    return np.array(nodes, np.uint32), ofs, idx
+
+
+def matches_dist_ratio(A, iA, B, iB, th_low=75, max_ratio=0.85):
+    """ORBextractor::getMatches_distRatio (ORBextractor.cpp:1228-1290): (i_match_A, i_match_B, BookK)."""
+    A = np.ascontiguousarray(A, np.uint8).reshape(-1, 32)
+    B = np.ascontiguousarray(B, np.uint8).reshape(-1, 32)
+    iA = np.ascontiguousarray(iA, np.uint32)
+    iB = np.ascontiguousarray(iB, np.uint32)
+    ma = np.zeros(max(len(iA), 1), np.uint32)
+    mb = np.zeros(max(len(iA), 1), np.uint32)
+    bk = C.c_longlong(0)
+    n = lib().orc_matches_dist_ratio(_p(A), _p(iA), len(iA), _p(B), _p(iB), len(iB), th_low, max_ratio, _p(ma), _p(mb), C.byref(bk))
+    return ma[:n], mb[:n], bk.value
+
+
+def bow_matching(A, B, fv_a, fv_b, th_low=75, max_ratio=0.85):
+    """BowMatching / InterMatchingBow node walk (MultiCameraFrame.cpp:946-1022, FrontEnd.cpp:3791-3965) over two feature vectors
+    given as {node id: [indices]}: (indices_1, indices_2, words, BookK)."""
+    A = np.ascontiguousarray(A, np.uint8).reshape(-1, 32)
+    B = np.ascontiguousarray(B, np.uint8).reshape(-1, 32)
+    na, oa, ia = feature_vector_csr(fv_a)
+    nb, ob, ib = feature_vector_csr(fv_b)
+    ma = np.zeros(max(len(ia), 1), np.uint32)
+    mb = np.zeros(max(len(ia), 1), np.uint32)
+    words = np.zeros(max(len(na), 1), np.uint32)
+    nw, bk = C.c_int(0), C.c_longlong(0)
+    n = lib().orc_bow_matching(_p(A), _p(B), _p(na), _p(oa), _p(ia), len(na), _p(nb), _p(ob), _p(ib), len(nb), th_low, max_ratio, _p(ma),
+                               _p(mb), _p(words), C.byref(nw), C.byref(bk))
+    return ma[:n], mb[:n], words[:nw.value], bk.value
 
 
 def _ptr_array(arrs):

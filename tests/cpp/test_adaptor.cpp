@@ -80,6 +80,27 @@ static int run_inter(const std::string& dir, const char* out_path) {
             kp1[i].push_back(u);
             kp2[i].push_back(v);
         }
+    {   // BoW-guided matcher: bow.bin = node id per feature (A then B), descriptors bowA.bin / bowB.bin
+        auto bA = slurp<uint8_t>(dir + "/bowA.bin"), bB = slurp<uint8_t>(dir + "/bowB.bin");
+        auto nodes = slurp<int>(dir + "/bow_nodes.bin");
+        const int nA = (int)bA.size() / 32, nB = (int)bB.size() / 32;
+        FeatureVector f1, f2;
+        for (int i = 0; i < nA; i++) f1[(unsigned)nodes[i]].push_back((unsigned)i);
+        for (int i = 0; i < nB; i++) f2[(unsigned)nodes[nA + i]].push_back((unsigned)i);
+        BowMatcher bm(0, 4096);
+        std::vector<unsigned int> i1, i2;
+        std::set<unsigned int> words;
+        bm.BowMatching(f1, f2, bA.data(), nA, bB.data(), nB, i1, i2, &words);
+        for (size_t k = 0; k < i1.size(); k++) fprintf(f, "bow %u %u\n", i1[k], i2[k]);
+        for (unsigned wd : words) fprintf(f, "word %u\n", wd);
+        int book = 0;
+        const unsigned first = f1.begin()->first;
+        if (f2.count(first)) {
+            bm.getMatches_distRatio(bA.data(), nA, f1[first], bB.data(), nB, f2[first], i1, i2, book);
+            for (size_t k = 0; k < i1.size(); k++) fprintf(f, "node0 %u %u\n", i1[k], i2[k]);
+            fprintf(f, "book %d\n", book);
+        }
+    }
     fr.triangulateIntraMatches(kp1, kp2);
     for (auto& p : fr.pts3D_) fprintf(f, "pt %.9g %.9g %.9g\n", p[0], p[1], p[2]);
     fclose(f);

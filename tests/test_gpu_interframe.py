@@ -83,6 +83,33 @@ def test_rig_knn2_images_consecutive_frames():
         rig.knn2_images([0], [99])
 
 
+def test_bow_subset_matcher(golden):
+    """mcs_match_subsets (getMatches_distRatio for all common vocabulary nodes in one launch) against the fixture and the oracle:
+    duplicate claims, nodes missing on one side, single-candidate and empty candidate lists, a 1500-query group."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from test_oracle_golden import _bow_fvs
+    g = golden("bow_subsets.npz")
+    fa, fb = _bow_fvs(g)
+    m = M.Matcher(max_sets=1, max_query_rows=4096, max_train_rows=4096)
+    a, b, w, k = m.bow_matching(g["A"], g["B"], fa, fb)
+    assert np.array_equal(a, g["indices_1"]) and np.array_equal(b, g["indices_2"]) and np.array_equal(w, g["words"]) and k == int(g["book_k"][0])
+    rng = np.random.default_rng(3)
+    A = rng.integers(0, 256, (1500, 32), dtype=np.uint8)
+    B = A[rng.integers(0, 1500, 1200)] ^ (rng.integers(0, 256, (1200, 32), dtype=np.uint8) & rng.integers(0, 256, (1200, 32), dtype=np.uint8)
+                                          & rng.integers(0, 256, (1200, 32), dtype=np.uint8) & rng.integers(0, 256, (1200, 32), dtype=np.uint8))
+    groups_a = [list(range(1500)), [5], [], [7, 8, 9], list(rng.integers(0, 1500, 40))]
+    groups_b = [list(range(1200)), [3], [1, 2], [], list(rng.integers(0, 1200, 64))]
+    ma, mb, gc, bk = m.match_subsets(A, B, groups_a, groups_b)
+    ea, eb, ec, ek = [], [], [], 0
+    for ga, gb in zip(groups_a, groups_b):
+        x, y, k2 = O.matches_dist_ratio(A, ga, B, gb)
+        ea += x.tolist(); eb += y.tolist(); ec.append(len(x)); ek += k2
+    assert ma.tolist() == ea and mb.tolist() == eb and gc.tolist() == ec and bk == ek and ec[0] > 300
+    with pytest.raises(M.McsError):
+        m.match_subsets(A, B, [[1500]], [[0]])
+
+
 def test_cpp_adaptor_interframe(tmp_path, golden):
     """mcs_b200::InterFrameMatcher::findMatchesMono / findInterMatches (both overloads) and the pairwise
     MultiCameraFrame::triangulateIntraMatches(kps_1, kps_2) from a C++ program: matches equal the cv2 fixture bit for bit, 3-D points
@@ -117,6 +144,10 @@ def test_cpp_adaptor_interframe(tmp_path, golden):
                 pts = (pts @ R.astype(np.float32).T + t.astype(np.float32)).astype(np.float32)
             expect.append(pts)
     (d / "pairs.bin").write_bytes(np.concatenate(pairs).astype(np.float32).tobytes())
+    gb = golden("bow_subsets.npz")
+    (d / "bowA.bin").write_bytes(np.ascontiguousarray(gb["A"]).tobytes())
+    (d / "bowB.bin").write_bytes(np.ascontiguousarray(gb["B"]).tobytes())
+    (d / "bow_nodes.bin").write_bytes(np.concatenate([gb["node_of_A"], gb["node_of_B"]]).astype(np.int32).tobytes())
     (d / "meta.txt").write_text("%d %d %d %d %d %d %d\n" % (len(g["d1"]), len(g["d2"]), g["m1"].shape[1], g["isz"][0], g["isz"][1], C, npair))
     out = subprocess.run([exe, "inter", str(d), str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr
@@ -129,6 +160,15 @@ def test_cpp_adaptor_interframe(tmp_path, golden):
     assert np.array_equal(rows("lf"), g["lf_split"]) and np.array_equal(rows("mo"), g["mono_split"])
     assert np.array_equal(rows("single"), g["lf_single"])
     assert "empty 0" in lines
+    bow = np.array([list(map(int, l.split()[1:])) for l in lines if l.startswith("bow ")], np.uint32).reshape(-1, 2)
+    assert np.array_equal(bow[:, 0], gb["indices_1"]) and np.array_equal(bow[:, 1], gb["indices_2"])
+    assert [int(l.split()[1]) for l in lines if l.startswith("word ")] == sorted(gb["words"].tolist())
+    from test_oracle_golden import _bow_fvs
+    fa, fb = _bow_fvs(gb)
+    n0 = min(fa)
+    ea, eb, ek = O.matches_dist_ratio(gb["A"], fa[n0], gb["B"], fb[n0])
+    node0 = np.array([list(map(int, l.split()[1:])) for l in lines if l.startswith("node0 ")], np.uint32).reshape(-1, 2)
+    assert node0[:, 0].tolist() == ea.tolist() and node0[:, 1].tolist() == eb.tolist() and ("book %d" % ek) in lines
     got = np.array([[float(x) for x in l.split()[1:]] for l in lines if l.startswith("pt ")], np.float32)
     exp = np.concatenate(expect)
     assert got.shape == exp.shape

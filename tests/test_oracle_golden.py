@@ -128,3 +128,28 @@ def test_inter_frame_host_logic_matches_cv2_restatement(golden):
     lf, mo = O.find_inter_matches(*args, split_mono=False)
     assert np.array_equal(lf, g["lf_single"]) and len(mo) == 0
     assert len(set(lf[:, 1].tolist())) == len(lf), "train indices are unique after the one-to-one step"
+
+
+def _bow_fvs(g):
+    fa, fb = {}, {}
+    for i, n in enumerate(g["node_of_A"]):
+        fa.setdefault(int(n), []).append(i)
+    for i, n in enumerate(g["node_of_B"]):
+        fb.setdefault(int(n), []).append(i)
+    return fa, fb
+
+
+def test_bow_subset_matcher_matches_python_restatement(golden):
+    """oracle getMatches_distRatio + BowMatching node walk == the numpy restatement the fixture was generated with
+    (oracle/gen_golden_knn2.py): repeated queries claim the same B feature, node ids missing on one side, BookK."""
+    import oracle_lib as O
+    g = golden("bow_subsets.npz")
+    fa, fb = _bow_fvs(g)
+    a, b, w, k = O.bow_matching(g["A"], g["B"], fa, fb)
+    assert np.array_equal(a, g["indices_1"]) and np.array_equal(b, g["indices_2"]) and np.array_equal(w, g["words"]) and k == int(g["book_k"][0])
+    assert len(set(fa) - set(fb)) > 0 and len(a) > 300
+    # single candidate in B: second-best stays 1e9, so the ratio test passes (ORBextractor.cpp:1247-1265)
+    ma, mb, bk = O.matches_dist_ratio(g["A"], [0, 1], g["A"], [0])
+    assert ma.tolist() == [0] and mb.tolist() == [0] and bk == 2
+    ma, mb, bk = O.matches_dist_ratio(g["A"], [0, 700], g["B"], [])
+    assert len(ma) == 0 and bk == 0
