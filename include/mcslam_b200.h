@@ -180,6 +180,16 @@ MCS_API int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* ma
 /* Same, inputs resident in device memory, nothing copied back (results are read with the getters). */
 MCS_API int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar);
 
+/* MultiCameraFrame::setData (MultiCameraFrame.cpp:95-152) fused in front of the path: images as the application holds them — CV_32F in
+ * [0, 1] (imread / 255, MCDataUtils/src/DatasetReader.cpp:699-711), `channels` = 1 or 3 (interleaved BGR), tightly packed
+ * [n_frames][num_cams][height][width][channels] — are multiplied by 255, converted to CV_8U (round half to even, saturate; :109-110)
+ * and reduced to gray (cvtColor BGR2GRAY on the 8-bit values, :112-116) on the device, then processed like mcs_rig_process /
+ * mcs_rig_process_device.  width * height must be a multiple of 4 and the buffer 16-byte aligned.  cv::undistort (RECTIFY,
+ * :123-136) is not applied. */
+MCS_API int mcs_rig_process_f32(mcs_rig* rig, const float* images, int channels, const float* masks, int n_frames, int old_epipolar);
+MCS_API int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int channels, const void* d_masks, int n_frames,
+                                       int old_epipolar);
+
 /* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over four
  * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
 MCS_API int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames);

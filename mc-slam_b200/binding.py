@@ -38,7 +38,7 @@ EXPORTS = [
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
-    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets",
+    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32",
 ]
 
 
@@ -112,6 +112,8 @@ def lib():
     L.mcs_matcher_kernel_launches.restype = C.c_longlong
     L.mcs_matcher_kernel_launches.argtypes = [vp]
     L.mcs_rig_knn2_images.argtypes = [vp, vp, vp, ci, vp]
+    L.mcs_rig_process_f32.argtypes = [vp, vp, ci, vp, ci, ci]
+    L.mcs_rig_process_device_f32.argtypes = [vp, vp, ci, vp, ci, ci]
     L.mcs_match_subsets.argtypes = [vp, vp, ci, vp, ci, ci, vp, vp, vp, vp, ci, C.c_double, vp, vp, vp, vp]
     L.mcs_device_malloc.restype = vp
     L.mcs_device_malloc.argtypes = [ci, C.c_size_t]
@@ -354,6 +356,21 @@ class RigFrames:
                 mp = _p(masks)
         _check(lib().mcs_rig_process(self.hd, ptr, mp, nf, int(old)), "mcs_rig_process")
         return nf
+
+    def process_f32(self, images, masks=None, old=False):
+        """setData + whole path on float32 images in [0, 1]: [n_frames, C, h, w] (gray) or [n_frames, C, h, w, 3] (BGR)."""
+        images = np.asarray(images)
+        assert images.dtype == np.float32 and images.flags["C_CONTIGUOUS"]
+        ch = 3 if (images.ndim == 5 and images.shape[-1] == 3) else 1
+        n = images.size // (self.C * self.h * self.w * ch)
+        if masks is not None:
+            masks = np.ascontiguousarray(masks, np.float32)
+        _check(lib().mcs_rig_process_f32(self.hd, _p(images), ch, _p(masks), n, int(old)), "rig_process_f32")
+        return n
+
+    def process_device_f32(self, d_images, channels, n_frames, d_masks=None, old=False):
+        _check(lib().mcs_rig_process_device_f32(self.hd, C.c_void_p(d_images), channels, C.c_void_p(d_masks) if d_masks else None, n_frames,
+                                                int(old)), "rig_process_device_f32")
 
     def process_device(self, d_images, n_frames, d_masks=None, old=False):
         _check(lib().mcs_rig_process_device(self.hd, C.c_void_p(d_images), C.c_void_p(d_masks) if d_masks else None, n_frames, int(old)),

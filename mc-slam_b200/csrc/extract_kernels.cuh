@@ -38,6 +38,39 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K0  MultiCameraFrame::setData input conversion (/root/reference/MCSlam/src/MultiCameraFrame.cpp:109-116): the app holds CV_32F
+// images in [0, 1] (imread / 255, MCDataUtils/src/DatasetReader.cpp:699-711).  multiply(img, 255) in f32, convertTo(CV_8U) =
+// saturate_cast<uchar>(cvRound(v)) (round half to even), and for 3 interleaved channels cvtColor(BGR2GRAY) on the 8-bit values:
+// (B * 3735 + G * 19235 + R * 9798 + 2^14) >> 15.  4 pixels per thread, 128-bit loads, one 32-bit store: HBM-bound.
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t f32_to_u8(float v) {
+    const int r = __float2int_rn(__fmul_rn(v, 255.0f));  // NaN -> 0 like saturate_cast of cvRound's INT_MIN
+    return (uint32_t)min(max(r, 0), 255);
+}
+
+template <int CH>
+__global__ void __launch_bounds__(256) stage_f32_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t n_quads) {
+    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_quads; q += (size_t)gridDim.x * blockDim.x) {
+        const float4* p = reinterpret_cast<const float4*>(src) + q * CH;
+        uint32_t o;
+        if (CH == 1) {
+            const float4 a = __ldcs(p);
+            o = f32_to_u8(a.x) | (f32_to_u8(a.y) << 8) | (f32_to_u8(a.z) << 16) | (f32_to_u8(a.w) << 24);
+        } else {
+            const float4 a = __ldcs(p), b = __ldcs(p + 1), c = __ldcs(p + 2);
+            const float v[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+            o = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t B = f32_to_u8(v[3 * k]), G = f32_to_u8(v[3 * k + 1]), R = f32_to_u8(v[3 * k + 2]);
+                o |= ((B * 3735u + G * 19235u + R * 9798u + (1u << 14)) >> 15) << (8 * k);
+            }
+        }
+        reinterpret_cast<uint32_t*>(dst)[q] = o;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K1  cv::resize(prev, cur, INTER_LINEAR) on 8U: 11-bit fixed-point coefficients, two-stage rounding.
 // xtab[dx] = {sx, a0 | a1 << 16}, ytab[dy] = {sy, b0 | b1 << 16} are built on the host exactly as OpenCV does.
 // One thread produces 4 horizontally adjacent pixels (one 32-bit store).

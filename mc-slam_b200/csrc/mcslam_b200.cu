@@ -282,6 +282,7 @@ struct Engine {
     // device buffers
     uint8_t *d_input = nullptr, *d_pyr = nullptr, *d_blur = nullptr;
     int2 *d_xtab = nullptr, *d_ytab = nullptr;
+    int sm_count_ = 148;
     uint4* d_cell_tab = nullptr;  // FAST cell records (build_cell_table)
     int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
     int rs_xw_ofs[MCS_PLAN_MAX_LEVELS] = {}, rs_yw_ofs[MCS_PLAN_MAX_LEVELS] = {};
@@ -532,6 +533,19 @@ struct Engine {
             for (int i = 0; i < n; i++)
                 CK(cudaMemcpy2DAsync(dst + (size_t)i * w * h, w, images + i * image_stride, stride, w, h, cudaMemcpyHostToDevice, st));
         }
+        return make_set(d_input, n, w, h, set, img0, st);
+    }
+    // setData conversion (K0): n tight f32 images (1 or 3 interleaved channels) in device memory -> tight u8 gray images at
+    // d_input[img0 ...], then the usual image set.  w * h must be a multiple of 4 (checked by the callers).
+    int stage_f32(const float* d_src, int channels, int n, int w, int h, mcs::ImageSet& set, int img0, cudaStream_t st) {
+        if (n < 1 || img0 + n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+        const size_t quads = (size_t)n * w * h / 4;
+        const int blocks = (int)std::min<size_t>((quads + 255) / 256, (size_t)sm_count_ * 16);
+        uint8_t* dst = d_input + (size_t)img0 * w * h;
+        if (channels == 1) mcs::stage_f32_kernel<1><<<blocks, 256, 0, st>>>(d_src, dst, quads);
+        else mcs::stage_f32_kernel<3><<<blocks, 256, 0, st>>>(d_src, dst, quads);
+        CK(cudaGetLastError());
+        launches++;
         return make_set(d_input, n, w, h, set, img0, st);
     }
     // device-resident tight images (d_images = image 0); re-pitched only when 32-bit row loads would be misaligned
@@ -824,6 +838,8 @@ struct mcs_rig {
         cudaStream_t st = nullptr, st2 = nullptr;
         cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
         int *d_tri_lists = nullptr, *d_tri_counts = nullptr;
+        float* d_f32 = nullptr;  // staging of one chunk of f32 input images (process_f32 with host buffers)
+        size_t f32_bytes = 0;
     };
     static constexpr int NSLOT = 4;
     Slot slots[NSLOT];
@@ -855,7 +871,7 @@ struct mcs_rig {
             if (S.st && k > 0) { cudaStreamSynchronize(S.st); cudaStreamDestroy(S.st); }
             if (S.st2) { cudaStreamSynchronize(S.st2); cudaStreamDestroy(S.st2); }
             if (S.ev_fork) { cudaEventDestroy(S.ev_fork); cudaEventDestroy(S.ev_join); cudaEventDestroy(S.ev_done); }
-            cudaFree(S.d_tri_lists); cudaFree(S.d_tri_counts);
+            cudaFree(S.d_tri_lists); cudaFree(S.d_tri_counts); cudaFree(S.d_f32);
         }
         if (ev_begin) cudaEventDestroy(ev_begin);
         cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
@@ -912,6 +928,7 @@ struct mcs_rig {
         CK(cudaMalloc(&d_row_count, F * sizeof(int)));
         tri_list_stride = (int)rw;
         CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, eng.device));
+        eng.sm_count_ = sm_count;
         if ((rc = set_tri_smem())) return rc;
         CK(cudaEventCreateWithFlags(&ev_begin, cudaEventDisableTiming));
         for (int k = 0; k < NSLOT; k++) {
@@ -1107,13 +1124,14 @@ struct mcs_rig {
     // merge, Jacobi) of one chunk hide behind the throughput-bound ones of its neighbours.  Everything is ordered against the
     // main stream (fork at ev_begin, join at ev_done), so timers and synchronisation on the main stream cover all of it.
     int process(const uint8_t* h_images, const uint8_t* d_images, const float* h_masks, const float* d_masks_in, int n_frames, int old,
-                bool download) {
+                bool download, const float* h_f32 = nullptr, const float* d_f32 = nullptr, int channels = 1) {
         const int w = cfg.width, h = cfg.height;
+        const size_t f32_frame = (size_t)C * w * h * channels;  // floats per rig frame
         const float* dm = d_masks_in;
         int rc;
         if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
         // host-buffer calls use half-size chunks: more copies in flight hide more of the PCIe time
-        const int cf = h_images ? std::max(1, chunk_frames / 2) : chunk_frames;
+        const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / 2) : chunk_frames;
         const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
         const int step = chunked ? cf : n_frames;
         mcs::ImageSet set{};
@@ -1125,7 +1143,21 @@ struct mcs_rig {
         for (int f0 = 0; f0 < n_frames; f0 += step, ci++) {
             const int nf = std::min(step, n_frames - f0), k = chunked ? ci % NSLOT : 0;
             cudaStream_t st = slots[k].st;
-            if (h_images) rc = eng.upload(h_images + (size_t)f0 * C * w * h, nf * C, w, h, w, (size_t)w * h, set, f0 * C, st);
+            if (h_f32) {
+                Slot& S = slots[k];
+                const size_t bytes = (size_t)nf * f32_frame * sizeof(float);
+                if (bytes > S.f32_bytes) {
+                    CK(cudaStreamSynchronize(st));
+                    cudaFree(S.d_f32);
+                    S.d_f32 = nullptr; S.f32_bytes = 0;
+                    CK(cudaMalloc(&S.d_f32, (size_t)step * f32_frame * sizeof(float)));
+                    S.f32_bytes = (size_t)step * f32_frame * sizeof(float);
+                }
+                eng.mark(ST_UPLOAD);
+                CK(cudaMemcpyAsync(S.d_f32, h_f32 + (size_t)f0 * f32_frame, bytes, cudaMemcpyHostToDevice, st));
+                rc = eng.stage_f32(S.d_f32, channels, nf * C, w, h, set, f0 * C, st);
+            } else if (d_f32) rc = eng.stage_f32(d_f32 + (size_t)f0 * f32_frame, channels, nf * C, w, h, set, f0 * C, st);
+            else if (h_images) rc = eng.upload(h_images + (size_t)f0 * C * w * h, nf * C, w, h, w, (size_t)w * h, set, f0 * C, st);
             else rc = eng.make_set(d_images, nf * C, w, h, set, f0 * C, st);
             if (rc) return rc;
             if ((rc = stage_extract(set, nf, f0, k))) return rc;
@@ -1350,6 +1382,29 @@ int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_mas
     if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
     rig->eng.begin_profile();
     return rig->process(nullptr, (const uint8_t*)d_images, nullptr, (const float*)d_masks, n_frames, old_epipolar ? 1 : 0, false);
+}
+static int check_f32_args(mcs_rig* rig, const void* images, int channels, int n_frames) {
+    if (!images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (channels != 1 && channels != 3) { set_err("f32 input: channels must be 1 (gray) or 3 (BGR)"); return MCS_ERR_ARG; }
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    if (((size_t)rig->cfg.width * rig->cfg.height) % 4 != 0) { set_err("f32 input: width * height must be a multiple of 4"); return MCS_ERR_ARG; }
+    if (((uintptr_t)images & 15) != 0) { set_err("f32 input: buffer must be 16-byte aligned"); return MCS_ERR_ARG; }
+    return 0;
+}
+int mcs_rig_process_f32(mcs_rig* rig, const float* images, int channels, const float* masks, int n_frames, int old_epipolar) {
+    RIG_ENTER(rig);
+    int rc = check_f32_args(rig, images, channels, n_frames);
+    if (rc) return rc;
+    rig->eng.begin_profile();
+    return rig->process(nullptr, nullptr, masks, nullptr, n_frames, old_epipolar ? 1 : 0, true, images, nullptr, channels);
+}
+int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int channels, const void* d_masks, int n_frames, int old_epipolar) {
+    RIG_ENTER(rig);
+    int rc = check_f32_args(rig, d_images, channels, n_frames);
+    if (rc) return rc;
+    rig->eng.begin_profile();
+    return rig->process(nullptr, nullptr, nullptr, (const float*)d_masks, n_frames, old_epipolar ? 1 : 0, false, nullptr, (const float*)d_images,
+                        channels);
 }
 int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames) {
     if (!rig || chunk_frames < 0) return MCS_ERR_ARG;

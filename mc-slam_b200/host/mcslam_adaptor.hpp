@@ -293,6 +293,12 @@ public:
         check(mcs_rig_process(h_, images, masks, n_frames, old ? 1 : 0), "mcs_rig_process");
     }
 
+    // setData (MultiCameraFrame.cpp:95-152) + processFrame for the application's native CV_32F [0, 1] images (1 or 3 BGR channels,
+    // [n_frames][num_cams][h][w][channels]): multiply by 255, convertTo(CV_8U), BGR2GRAY run on the device in front of the path.
+    void process_frames_f32(const float* images, int channels, const float* masks, int n_frames, bool old = false) {
+        check(mcs_rig_process_f32(h_, images, channels, masks, n_frames, old ? 1 : 0), "mcs_rig_process_f32");
+    }
+
     int num_cams_;
     std::vector<std::vector<mcs_keypoint>> image_kps, image_kps_undist;
     std::vector<std::vector<uint8_t>> image_descriptors;  // per camera n x 32 bytes

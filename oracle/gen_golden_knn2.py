@@ -153,3 +153,22 @@ np.savez_compressed(os.path.join(OUT, "bow_subsets.npz"), A=A, B=B, node_of_A=no
                     indices_1=np.array(i1, np.uint32), indices_2=np.array(i2, np.uint32), words=np.array(words, np.uint32),
                     book_k=np.array([book], np.int64))
 print("bow subsets: nodes", len(fvA), len(fvB), "matches", len(i1), "words", len(words), "BookK", book)
+
+
+# ---- setData input conversion through cv2 (MultiCameraFrame.cpp:107-116): multiply(img, 255); convertTo(CV_8U); cvtColor(BGR2GRAY)
+rng = np.random.default_rng(14)
+gray = rng.random((48, 64), dtype=np.float32)
+gray.ravel()[:16] = [0, 1, 0.5, 0.0019607844, 0.005882353, 1.2, -0.3, 0.998, 0.5019608, 0.49803922, 2.5 / 255, 3.5 / 255, 254.5 / 255, 255.5 / 255,
+                     1e-8, 0.9999999]
+bgr = rng.random((40, 52, 3), dtype=np.float32)
+bgr.reshape(-1)[:6] = [0.5, 1.5 / 255, 2.5 / 255, 1.0, 1.0, 1.0]
+
+
+def cv_set_data(img):
+    m = cv2.multiply(img, 255.0)
+    u8 = cv2.add(m, np.zeros_like(m), dtype=cv2.CV_8U)       # saturate_cast<uchar>(cvRound(.)) like Mat::convertTo
+    return cv2.cvtColor(u8, cv2.COLOR_BGR2GRAY) if u8.ndim == 3 else u8
+
+
+np.savez_compressed(os.path.join(OUT, "set_data_f32.npz"), gray=gray, gray_u8=cv_set_data(gray), bgr=bgr, bgr_u8=cv_set_data(bgr))
+print("setData fixture", cv_set_data(gray).ravel()[:16])

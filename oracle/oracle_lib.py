@@ -58,6 +58,7 @@ def lib():
         L.orc_find_inter_matches.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_void_p] * 3
         L.orc_matches_dist_ratio.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 3
         L.orc_bow_matching.argtypes = [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 5
+        L.orc_set_data_f32.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_triangulate_pixels.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -269,6 +270,16 @@ def bow_matching(A, B, fv_a, fv_b, th_low=75, max_ratio=0.85):
     n = lib().orc_bow_matching(_p(A), _p(B), _p(na), _p(oa), _p(ia), len(na), _p(nb), _p(ob), _p(ib), len(nb), th_low, max_ratio, _p(ma),
                                _p(mb), _p(words), C.byref(nw), C.byref(bk))
     return ma[:n], mb[:n], words[:nw.value], bk.value
+
+
+def set_data_f32(images):
+    """setData conversion (MultiCameraFrame.cpp:107-116): float32 [..., h, w] or [..., h, w, 3] (BGR) in [0, 1] -> uint8 gray."""
+    images = np.ascontiguousarray(images, np.float32)
+    ch = 3 if images.shape[-1] == 3 and images.ndim >= 3 else 1
+    shape = images.shape[:-1] if ch == 3 else images.shape
+    out = np.zeros(shape, np.uint8)
+    lib().orc_set_data_f32(_p(images), ch, out.size, _p(out))
+    return out
 
 
 def _ptr_array(arrs):

@@ -235,3 +235,57 @@ def test_chunked_pipeline_equals_single_chunk():
     same(ref, snapshot())
     B.device_free(0, d_img)
     B.device_free(0, d_msk)
+
+
+@pytest.mark.parametrize("channels", [1, 3])
+def test_process_f32_equals_set_data_then_u8_path(golden, channels):
+    """mcs_rig_process_f32 / mcs_rig_process_device_f32 (setData conversion fused in front, MultiCameraFrame.cpp:107-116): level 0 equals
+    the oracle's / cv2's converted image bit for bit, and every downstream result equals the u8 entry point fed with that image.
+    5 frames in chunks of 2 (ragged last chunk)."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from mcslam_b200 import binding as B
+    g = golden("set_data_f32.npz")
+    calib = M.synth.make_rig(3, 320, 240)
+    u8 = np.stack([M.synth.make_rig_frame(calib, 320, 240, frame_index=60 + i, n_rects=6) for i in range(5)])
+    rng = np.random.default_rng(21)
+    f32 = ((u8.astype(np.float32) + rng.uniform(-0.6, 0.6, u8.shape).astype(np.float32)) / np.float32(255.0)).astype(np.float32)
+    if channels == 3:
+        f32 = np.stack([f32 * np.float32(0.9), f32, np.clip(f32 * np.float32(1.1), 0, 1.05)], -1).astype(np.float32)
+    f32 = np.ascontiguousarray(f32)
+    want = O.set_data_f32(f32)
+    assert want.shape == u8.shape and (want != u8).any()
+    rig = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=5)
+    rig.set_chunk_frames(4)  # host path uses chunks of 2
+    rig.process(want)
+    ref = [([rig.features(f, c) for c in range(3)], rig.intra_matches(f), rig.landmarks(f)) for f in range(5)]
+
+    def check():
+        for f in range(5):
+            for c in range(3):
+                assert np.array_equal(rig.level(f, c, 0), want[f, c]), (f, c)
+                k, d = rig.features(f, c)
+                assert (k == ref[f][0][c][0]).all() and np.array_equal(d, ref[f][0][c][1])
+            assert np.array_equal(rig.intra_matches(f), ref[f][1])
+            lm = rig.landmarks(f)
+            for key in lm:
+                assert np.array_equal(lm[key], ref[f][2][key]), key
+
+    assert rig.process_f32(f32) == 5
+    check()
+    dptr = B.device_malloc(0, f32.nbytes)
+    B.device_upload(0, dptr, f32)
+    rig.process(u8)  # overwrite the handle's state with something else first
+    rig.process_device_f32(dptr, channels, 5)
+    rig.synchronize()
+    check()
+    B.device_free(0, dptr)
+    # the cv2 fixture straight through the kernel: a 1-camera "rig" of the fixture's size
+    img = g["gray"] if channels == 1 else g["bgr"]
+    h, w = img.shape[:2]
+    one = M.RigFrames(M.synth.make_rig(1, w, h), w, h, nfeatures=50, max_frames=1)
+    one.process_f32(np.ascontiguousarray(img[None, None]))
+    assert np.array_equal(one.level(0, 0, 0), g["gray_u8"] if channels == 1 else g["bgr_u8"])
+    with pytest.raises(M.McsError):
+        lib_rc = B.lib().mcs_rig_process_f32(one.hd, B._p(img), 2, None, 1, 0)
+        B._check(lib_rc, "process_f32")

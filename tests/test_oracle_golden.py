@@ -153,3 +153,10 @@ def test_bow_subset_matcher_matches_python_restatement(golden):
     assert ma.tolist() == [0] and mb.tolist() == [0] and bk == 2
     ma, mb, bk = O.matches_dist_ratio(g["A"], [0, 700], g["B"], [])
     assert len(ma) == 0 and bk == 0
+
+
+def test_set_data_f32_matches_cv2(golden):
+    """oracle setData conversion == cv2 multiply / convertTo(CV_8U) / cvtColor(BGR2GRAY) incl. .5 ties, out-of-range and tiny values."""
+    import oracle_lib as O
+    g = golden("set_data_f32.npz")
+    assert np.array_equal(O.set_data_f32(g["gray"]), g["gray_u8"]) and np.array_equal(O.set_data_f32(g["bgr"]), g["bgr_u8"])
