@@ -12,11 +12,13 @@
 #ifndef MCSLAM_ADAPTOR_HPP
 #define MCSLAM_ADAPTOR_HPP
 
+#include <algorithm>
 #include <array>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <map>
+#include <numeric>
 #include <set>
 #include <stdexcept>
 #include <string>
@@ -242,6 +244,62 @@ public:
                 mono_rows->push_back(m);
             }
         }
+    }
+
+    // The rest of FrontEnd::obtainLfFeatures around the triangulation block (FrontEnd.cpp:213-533, shipped branch: tiling and refview
+    // off, no vocabulary transform): intraMatches = accepted rows in row order, then the mono features — single-view rows (:371-384)
+    // followed by every keypoint no accepted row uses, camera-major (:487-505) — ordered by descending response with the reference's
+    // argsorte (utils.h:20-30: std::sort, unstable) and cut to total_feats - intramatch_size (:513-521).  lIds all -1.
+    struct LfFeatures {
+        std::vector<IntraMatch> intraMatches;
+        std::vector<int> lIds;
+        int intramatch_size = 0, mono_size = 0;
+    };
+    void obtainLfFeatures(const float* segMasks, LfFeatures& out, int total_feats = 3000) {
+        std::vector<IntraMatch> accepted, mono_keypoints;
+        triangulateIntraMatches(segMasks, accepted, &mono_keypoints);
+        std::vector<std::vector<char>> keypoint_mask(num_cams_);
+        for (int c = 0; c < num_cams_; c++) keypoint_mask[c].assign(image_kps_undist[c].size(), 1);
+        std::vector<float> responses;
+        for (const IntraMatch& m : accepted)
+            for (int c = 0; c < num_cams_; c++)
+                if (m.matchIndexN[c] >= 0) keypoint_mask[c][m.matchIndexN[c]] = 0;
+        for (IntraMatch& m : mono_keypoints) {
+            int c = 0;
+            while (m.matchIndexN[c] < 0) c++;
+            const int j = m.matchIndexN[c];
+            std::memcpy(m.matchDesc.data(), &image_descriptors[c][(size_t)j * 32], 32);
+            m.uv_ref[0] = image_kps_undist[c][j].x; m.uv_ref[1] = image_kps_undist[c][j].y;
+            m.mono = true;
+            responses.push_back(image_kps_undist[c][j].response);
+            keypoint_mask[c][j] = 0;
+        }
+        for (int c = 0; c < num_cams_; c++)
+            for (size_t j = 0; j < image_kps_undist[c].size(); j++) {
+                if (!keypoint_mask[c][j]) continue;
+                IntraMatch m;
+                m.matchIndexN.assign(num_cams_, -1);
+                m.matchIndexN[c] = (int)j;
+                if (c < 5) m.matchIndex[c] = (int)j;
+                std::memcpy(m.matchDesc.data(), &image_descriptors[c][j * 32], 32);
+                m.uv_ref[0] = image_kps_undist[c][j].x; m.uv_ref[1] = image_kps_undist[c][j].y;
+                m.n_rays = 1;
+                m.mono = true;
+                mono_keypoints.push_back(m);
+                responses.push_back(image_kps_undist[c][j].response);
+                keypoint_mask[c][j] = 0;
+            }
+        std::vector<int> sorted_kp_ind(responses.size());
+        std::iota(sorted_kp_ind.begin(), sorted_kp_ind.end(), 0);
+        std::sort(sorted_kp_ind.begin(), sorted_kp_ind.end(), [&responses](int i, int j) -> bool { return responses[i] > responses[j]; });
+        out.intraMatches = accepted;
+        out.intramatch_size = (int)accepted.size();
+        out.mono_size = 0;
+        for (size_t i = 0; i < sorted_kp_ind.size() && (int)i < total_feats - out.intramatch_size; i++) {
+            out.intraMatches.push_back(mono_keypoints[sorted_kp_ind[i]]);
+            out.mono_size++;
+        }
+        out.lIds.assign(out.intraMatches.size(), -1);
     }
 
     // triangulateIntraMatches(x, view_inds, pt) (:411-441): x = 2 x n pixel coordinates (row 0 = u, row 1 = v)

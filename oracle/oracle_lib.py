@@ -58,6 +58,7 @@ def lib():
         L.orc_find_inter_matches.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_void_p] * 3
         L.orc_matches_dist_ratio.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 3
         L.orc_bow_matching.argtypes = [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 5
+        L.orc_argsorte_desc.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.orc_set_data_f32.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
@@ -280,6 +281,43 @@ def set_data_f32(images):
     out = np.zeros(shape, np.uint8)
     lib().orc_set_data_f32(_p(images), ch, out.size, _p(out))
     return out
+
+
+def argsorte_desc(values):
+    values = np.ascontiguousarray(values, np.float32)
+    idx = np.zeros(max(len(values), 1), np.int32)
+    lib().orc_argsorte_desc(_p(values), len(values), _p(idx))
+    return idx[:len(values)]
+
+
+def obtain_lf_features(kps, tri, total_feats=3000):
+    """FrontEnd::obtainLfFeatures bookkeeping around the triangulation block (FrontEnd.cpp:213-533, the shipped branch: tiling and
+    refview off): accepted rows go to intraMatches in row order and consume their keypoints (:355-365); single-view rows (:371-384)
+    and then every keypoint still unused, camera-major (:487-505), become mono candidates; the candidates are ordered by descending
+    response with argsorte (:513) and the first total_feats - intramatch_size are appended (:515-521).
+    Returns (row indices of the accepted rows, [(cam, keypoint index)] of the appended mono features)."""
+    used = [np.zeros(len(k), bool) for k in kps]
+    accepted, mono, resp = [], [], []
+    for r in range(len(tri["rows"])):
+        row = tri["rows"][r]
+        if tri["status"][r] == 1:
+            accepted.append(r)
+            for c, j in enumerate(row):
+                if j >= 0:
+                    used[c][j] = True
+        elif tri["nviews"][r] == 1:
+            c = int(np.flatnonzero(row >= 0)[0])
+            mono.append((c, int(row[c])))
+            resp.append(kps[c][row[c]]["response"])
+            used[c][row[c]] = True
+    for c in range(len(kps)):
+        for j in range(len(kps[c])):
+            if not used[c][j]:
+                mono.append((c, j))
+                resp.append(kps[c][j]["response"])
+    order = argsorte_desc(resp)
+    take = max(0, total_feats - len(accepted))
+    return accepted, [mono[i] for i in order[:take]]
 
 
 def _ptr_array(arrs):

@@ -140,6 +140,15 @@ int main(int argc, char** argv) {
         fprintf(f, "rows %zu landmarks %zu\n", rows.size(), lms.size());
         for (auto& r : rows) fprintf(f, "row %d %d %d\n", r.matchIndexN[0], r.matchIndexN[1], r.matchIndexN[C - 1]);
         for (auto& m : lms) fprintf(f, "lm %d %.12g %.12g %.12g\n", m.n_rays, m.point3D[0], m.point3D[1], m.point3D[2]);
+        mcs_b200::MultiCameraFrame::LfFeatures lf;
+        fr.obtainLfFeatures(nullptr, lf, 700);  // small budget so that the response cut is exercised
+        fprintf(f, "lfsizes %d %d %zu\n", lf.intramatch_size, lf.mono_size, lf.lIds.size());
+        for (int i = lf.intramatch_size; i < (int)lf.intraMatches.size(); i++) {
+            const auto& m = lf.intraMatches[i];
+            int c = 0;
+            while (m.matchIndexN[c] < 0) c++;
+            fprintf(f, "lfmono %d %d %d %d\n", c, m.matchIndexN[c], (int)m.mono, m.matchDesc[0]);
+        }
         fclose(f);
         uint8_t empty = 0;
         if (ex(nullptr, 0, 0, 0, nullptr, k, d, lap) != -1) return 4;  // `if(_image.empty()) return -1;`

@@ -189,6 +189,13 @@ def test_cpp_adaptor_equals_oracle(tmp_path):
     got = np.array([[float(v) for v in l[2:5]] for l in lm])
     assert np.allclose(got, tri["xyz"][acc], rtol=1e-6, atol=1e-9)
     assert [int(l[1]) for l in lm] == tri["nviews"][acc].tolist()
+    # obtainLfFeatures bookkeeping: accepted rows, then mono features by descending response (unstable std::sort order), budget 700
+    accepted, mono = O.obtain_lf_features(K, tri, total_feats=700)
+    sizes = [l.split() for l in lines if l.startswith("lfsizes ")][0]
+    assert int(sizes[1]) == len(accepted) and int(sizes[2]) == len(mono) == 700 - len(accepted) and int(sizes[3]) == 700
+    got_mono = [tuple(map(int, l.split()[1:])) for l in lines if l.startswith("lfmono ")]
+    assert [(c, j) for c, j, _, _ in got_mono] == mono
+    assert all(m == 1 and d0 == D[c][j][0] for c, j, m, d0 in got_mono)
 
 
 def test_chunked_pipeline_equals_single_chunk():
