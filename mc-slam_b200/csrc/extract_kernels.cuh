@@ -634,6 +634,9 @@ __global__ void __launch_bounds__(MCS_OCT_NT) octree_kernel(const __grid_constan
 // 512 (x, y) pairs, see include/mcs_orb_pattern.inc.  Global (L1-cached), not __constant__: every lane reads a different
 // 32-byte slice, which the constant cache would serialise 32 ways.
 __device__ __align__(16) signed char g_pattern[1024];
+// test t of the un-steered pattern as byte offsets into a 28-byte-pitch blurred patch whose centre is (13, 13):
+// (y0 * 28 + x0 + 377) | (y1 * 28 + x1 + 377) << 16   (filled by the host next to g_pattern)
+__device__ __align__(16) uint32_t g_pattern_ofs28[256];
 
 struct KeypointPod {
     float x, y, size, angle, response;
@@ -785,15 +788,20 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32) describe_fused_kernel(co
     const int img = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int k = blockIdx.x * MCS_DESCF_WARPS + warp;  // output slot
-    int level = -1, before = 0, total = 0;
-#pragma unroll 1
-    for (int l = 0; l < P.nlevels; l++) {
-        const int c = max(sel_count[img * P.nlevels + l], 0);
-        if (level < 0 && k < total + c) {
-            level = l;
-            before = total;
+    // level of slot k: lane l holds level l's selected count, warp scan, first level whose running total exceeds k
+    int level, before, total;
+    {
+        const int c = lane < P.nlevels ? max(__ldg(&sel_count[img * P.nlevels + lane]), 0) : 0;
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
         }
-        total += c;
+        total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, lane < P.nlevels && k < incl);
+        level = m ? __ffs(m) - 1 : -1;
+        before = __shfl_sync(0xFFFFFFFFu, incl - c, max(level, 0));
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) kp_count[img] = min(total, P.kp_cap);
     if (level < 0 || k >= P.kp_cap) return;  // warp-uniform
@@ -870,18 +878,15 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32) describe_fused_kernel(co
         }
     }
     __syncwarp();
-    // 16 points = 8 tests = 1 descriptor byte per lane; test t = bytes (x0, y0, x1, y1) of word t  (computeOrbDescriptor :106-145, a = 1, b = 0)
-    const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + lane * 2);
-    const uint4 pw1 = __ldg(reinterpret_cast<const uint4*>(g_pattern) + lane * 2 + 1);
+    // 16 points = 8 tests = 1 descriptor byte per lane; test t compares the blurred patch at two precomputed byte offsets
+    // (computeOrbDescriptor :106-145 with a = 1, b = 0)
+    const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2);
+    const uint4 pw1 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2 + 1);
     const uint32_t pw[8] = {pw0.x, pw0.y, pw0.z, pw0.w, pw1.x, pw1.y, pw1.z, pw1.w};
-    const uint8_t* bl = &s_bl[warp][13][13];
+    const uint8_t* bl = &s_bl[warp][0][0];
     int val = 0;
 #pragma unroll
-    for (int t = 0; t < 8; t++) {
-        const int x0 = (int)(signed char)(pw[t]), y0 = (int)(signed char)(pw[t] >> 8);
-        const int x1 = (int)(signed char)(pw[t] >> 16), y1 = (int)(signed char)(pw[t] >> 24);
-        val |= ((int)bl[y0 * 28 + x0] < (int)bl[y1 * 28 + x1]) << t;
-    }
+    for (int t = 0; t < 8; t++) val |= ((int)bl[pw[t] & 0xFFFFu] < (int)bl[pw[t] >> 16]) << t;
     int w4 = val & 0xFF;
     w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 1) & 0xFF) << 8;
     w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 2) & 0xFF) << 16;

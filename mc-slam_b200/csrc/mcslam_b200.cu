@@ -344,6 +344,14 @@ struct Engine {
         gauss_kernel_fixed(7, 2.0, k7);
         CK(cudaMemcpyToSymbol(mcs::c_gauss7, k7, sizeof(k7)));
         CK(cudaMemcpyToSymbol(mcs::g_pattern, MCS_ORB_PATTERN_XY, 1024));
+        {
+            uint32_t ofs[256];
+            for (int t = 0; t < 256; t++) {
+                const signed char* q = MCS_ORB_PATTERN_XY + 4 * t;  // x0, y0, x1, y1
+                ofs[t] = (uint32_t)(q[1] * 28 + q[0] + 377) | ((uint32_t)(q[3] * 28 + q[2] + 377) << 16);
+            }
+            CK(cudaMemcpyToSymbol(mcs::g_pattern_ofs28, ofs, sizeof(ofs)));
+        }
         return replan(max_w, max_h);
     }
 
@@ -1139,9 +1147,14 @@ struct mcs_rig {
             CK(cudaEventRecord(ev_begin, eng.stream));
             for (int k = 1; k < NSLOT; k++) CK(cudaStreamWaitEvent(slots[k].st, ev_begin, 0));
         }
-        int ci = 0;
-        for (int f0 = 0; f0 < n_frames; f0 += step, ci++) {
-            const int nf = std::min(step, n_frames - f0), k = chunked ? ci % NSLOT : 0;
+        // Host-buffer calls ramp the chunk size up (step/4, step/2, step, ...): the kernels of the first chunk start after a quarter
+        // of the upload time, and that chunk's latency-bound kernels overlap the upload of the next ones.
+        int ci = 0, nf = 0;
+        const bool ramp = chunked && (h_images || h_f32) && step >= 8;
+        for (int f0 = 0; f0 < n_frames; f0 += nf, ci++) {
+            const int want = !ramp ? step : (ci == 0 ? step / 4 : (ci == 1 ? step / 2 : step));
+            nf = std::min(want, n_frames - f0);
+            const int k = chunked ? ci % NSLOT : 0;
             cudaStream_t st = slots[k].st;
             if (h_f32) {
                 Slot& S = slots[k];
