@@ -634,8 +634,9 @@ __global__ void __launch_bounds__(MCS_OCT_NT) octree_kernel(const __grid_constan
 // 512 (x, y) pairs, see include/mcs_orb_pattern.inc.  Global (L1-cached), not __constant__: every lane reads a different
 // 32-byte slice, which the constant cache would serialise 32 ways.
 __device__ __align__(16) signed char g_pattern[1024];
-// test t of the un-steered pattern as byte offsets into a 28-byte-pitch blurred patch whose centre is (13, 13):
-// (y0 * 28 + x0 + 377) | (y1 * 28 + x1 + 377) << 16   (filled by the host next to g_pattern)
+// un-steered pattern for describe_fused_kernel: word 8 * lane + slot = ofs0 | ofs1 << 10 | bit << 20 with ofs = y * 28 + x + 377, the
+// byte offset into a 28-byte-pitch blurred patch whose centre is (13, 13); bit = which of the lane's 8 tests the slot holds
+// (filled by the host next to g_pattern, slot order chosen against shared-memory bank conflicts)
 __device__ __align__(16) uint32_t g_pattern_ofs28[256];
 
 struct KeypointPod {
@@ -777,14 +778,17 @@ __global__ void __launch_bounds__(MCS_DESC_WARPS * 32) describe_kernel(const __g
 // from shared memory: the blurred pyramid is neither written nor read (blur_kernel remains for the steered mode and observers).
 // ------------------------------------------------------------------------------------------------------------
 #define MCS_DESCF_WARPS 8
-__global__ void __launch_bounds__(MCS_DESCF_WARPS * 32) describe_fused_kernel(const __grid_constant__ McsPlan P, ImageSet S,
+__global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 6) describe_fused_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                               const uint32_t* __restrict__ sel,
                                                                               const int* __restrict__ sel_count,
                                                                               KeypointPod* __restrict__ kps, uint8_t* __restrict__ desc,
                                                                               int* __restrict__ kp_count) {
-    __shared__ uint32_t s_in[MCS_DESCF_WARPS][32][8];                   // input patch rows -16..15, columns -16..15
+    // input patch rows -16..15, columns -16..15; row pitch 12 words so that the 4 row pairs x 8 word columns one H-pass step reads
+    // fall into 32 different banks.  The blurred patch (26 x 28 bytes, rows/columns -13..12) reuses the space: the input is dead
+    // once the H pass has finished.
+    __shared__ __align__(16) uint32_t s_in[MCS_DESCF_WARPS][32][12];
     __shared__ __align__(16) uint32_t s_pair[MCS_DESCF_WARPS][16][28];  // row-filtered patch as vertical pairs (row 2p | row 2p+1 << 16)
-    __shared__ __align__(4) uint8_t s_bl[MCS_DESCF_WARPS][26][28];      // blurred patch rows/columns -13..12
+    uint8_t* const s_blw = reinterpret_cast<uint8_t*>(&s_in[threadIdx.x >> 5][0][0]);
     const int img = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int k = blockIdx.x * MCS_DESCF_WARPS + warp;  // output slot
@@ -833,8 +837,9 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32) describe_fused_kernel(co
     const uint32_t wA = (uint32_t)c_gauss7[0] | ((uint32_t)c_gauss7[1] << 8) | ((uint32_t)c_gauss7[2] << 16) | ((uint32_t)c_gauss7[3] << 24);
     const uint32_t wB = (uint32_t)c_gauss7[4] | ((uint32_t)c_gauss7[5] << 8) | ((uint32_t)c_gauss7[6] << 16);
     // rows: output column j (0..25, patch column j - 13) = taps on bytes j .. j+6; item = (row pair p, 4 columns g)
-    for (int i = lane; i < 16 * 7; i += 32) {
-        const int p = i / 7, g = i - p * 7;
+    for (int pb = 0; pb < 16; pb += 4) {
+        const int p = pb + (lane >> 3), g = lane & 7;  // lane = (row pair, word column); column 7 idles
+        if (g == 7) continue;
         uint32_t hv[2][4];
 #pragma unroll
         for (int rr = 0; rr < 2; rr++) {
@@ -858,35 +863,41 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32) describe_fused_kernel(co
         const uint32_t e0 = k0 | (k1 << 8), e1 = k2 | (k3 << 8), e2 = k4 | (k5 << 8), e3 = k6;       // even output row 2q
         const uint32_t o0 = k0 << 8, o1 = k1 | (k2 << 8), o2 = k3 | (k4 << 8), o3 = k5 | (k6 << 8);  // odd output row 2q + 1
         // columns: output row y (0..25, patch row y - 13) = taps on filtered rows y .. y+6; item = (output row pair q, 4 columns g)
-        for (int i = lane; i < 13 * 7; i += 32) {
-            const int q = i / 7, g = i - q * 7;
-            const uint4 a = *reinterpret_cast<const uint4*>(&s_pair[warp][q][4 * g]);
-            const uint4 b = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 1][4 * g]);
-            const uint4 c = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 2][4 * g]);
-            const uint4 d = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 3][4 * g]);
-            const uint32_t pa[4] = {a.x, a.y, a.z, a.w}, pb[4] = {b.x, b.y, b.z, b.w}, pc[4] = {c.x, c.y, c.z, c.w}, pd[4] = {d.x, d.y, d.z, d.w};
-            uint32_t oe = 0, oo = 0;
+        // lane = (segment of output row pairs, 4 columns g): segments {0-3, 4-6, 7-9, 10-12} walk down with a 4-row-pair window in
+        // registers, so every filtered row pair is loaded once or twice instead of four times
+        const int seg = lane >> 3, g = lane & 7;
+        const int q0 = seg == 0 ? 0 : 1 + 3 * seg, q1 = 4 + 3 * seg;
+        if (g < 7) {
+            uint4 a = *reinterpret_cast<const uint4*>(&s_pair[warp][q0][4 * g]);
+            uint4 b = *reinterpret_cast<const uint4*>(&s_pair[warp][q0 + 1][4 * g]);
+            uint4 c = *reinterpret_cast<const uint4*>(&s_pair[warp][q0 + 2][4 * g]);
+            for (int q = q0; q < q1; q++) {
+                const uint4 d = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 3][4 * g]);
+                const uint32_t pa[4] = {a.x, a.y, a.z, a.w}, pb[4] = {b.x, b.y, b.z, b.w}, pc[4] = {c.x, c.y, c.z, c.w}, pd[4] = {d.x, d.y, d.z, d.w};
+                uint32_t oe = 0, oo = 0;
 #pragma unroll
-            for (int kk = 0; kk < 4; kk++) {
-                const uint32_t ve = __dp2a_lo(pd[kk], e3, __dp2a_lo(pc[kk], e2, __dp2a_lo(pb[kk], e1, __dp2a_lo(pa[kk], e0, 32768u))));
-                const uint32_t vo = __dp2a_lo(pd[kk], o3, __dp2a_lo(pc[kk], o2, __dp2a_lo(pb[kk], o1, __dp2a_lo(pa[kk], o0, 32768u))));
-                oe |= (ve >> 16) << (8 * kk);
-                oo |= (vo >> 16) << (8 * kk);
+                for (int kk = 0; kk < 4; kk++) {
+                    const uint32_t ve = __dp2a_lo(pd[kk], e3, __dp2a_lo(pc[kk], e2, __dp2a_lo(pb[kk], e1, __dp2a_lo(pa[kk], e0, 32768u))));
+                    const uint32_t vo = __dp2a_lo(pd[kk], o3, __dp2a_lo(pc[kk], o2, __dp2a_lo(pb[kk], o1, __dp2a_lo(pa[kk], o0, 32768u))));
+                    oe |= (ve >> 16) << (8 * kk);
+                    oo |= (vo >> 16) << (8 * kk);
+                }
+                *reinterpret_cast<uint32_t*>(s_blw + (2 * q) * 28 + 4 * g) = oe;
+                *reinterpret_cast<uint32_t*>(s_blw + (2 * q + 1) * 28 + 4 * g) = oo;
+                a = b; b = c; c = d;
             }
-            *reinterpret_cast<uint32_t*>(&s_bl[warp][2 * q][4 * g]) = oe;
-            *reinterpret_cast<uint32_t*>(&s_bl[warp][2 * q + 1][4 * g]) = oo;
         }
     }
     __syncwarp();
-    // 16 points = 8 tests = 1 descriptor byte per lane; test t compares the blurred patch at two precomputed byte offsets
-    // (computeOrbDescriptor :106-145 with a = 1, b = 0)
+    // 16 points = 8 tests = 1 descriptor byte per lane (computeOrbDescriptor :106-145 with a = 1, b = 0).  Slot s of lane i is one of
+    // the tests 8i .. 8i+7, in an order the host chose so that the 32 lanes of a slot hit few common banks; each word holds the two
+    // byte offsets into the blurred patch and the bit the result goes to.
     const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2);
     const uint4 pw1 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2 + 1);
     const uint32_t pw[8] = {pw0.x, pw0.y, pw0.z, pw0.w, pw1.x, pw1.y, pw1.z, pw1.w};
-    const uint8_t* bl = &s_bl[warp][0][0];
     int val = 0;
 #pragma unroll
-    for (int t = 0; t < 8; t++) val |= ((int)bl[pw[t] & 0xFFFFu] < (int)bl[pw[t] >> 16]) << t;
+    for (int t = 0; t < 8; t++) val |= ((int)s_blw[pw[t] & 0x3FFu] < (int)s_blw[(pw[t] >> 10) & 0x3FFu]) << (pw[t] >> 20);
     int w4 = val & 0xFF;
     w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 1) & 0xFF) << 8;
     w4 |= (__shfl_down_sync(0xFFFFFFFFu, val, 2) & 0xFF) << 16;

@@ -345,10 +345,36 @@ struct Engine {
         CK(cudaMemcpyToSymbol(mcs::c_gauss7, k7, sizeof(k7)));
         CK(cudaMemcpyToSymbol(mcs::g_pattern, MCS_ORB_PATTERN_XY, 1024));
         {
+            // slot order per lane: greedy over slots, each lane takes the remaining test whose two sample words add least to the fullest
+            // banks of the slot's two loads (same word = broadcast, no conflict)
             uint32_t ofs[256];
-            for (int t = 0; t < 256; t++) {
-                const signed char* q = MCS_ORB_PATTERN_XY + 4 * t;  // x0, y0, x1, y1
-                ofs[t] = (uint32_t)(q[1] * 28 + q[0] + 377) | ((uint32_t)(q[3] * 28 + q[2] + 377) << 16);
+            bool used[256] = {};
+            for (int slot = 0; slot < 8; slot++) {
+                int load[2][32] = {};
+                std::vector<int> words[2];
+                for (int lane = 0; lane < 32; lane++) {
+                    int best = -1, best_cost = 1 << 30;
+                    uint32_t best_o[2] = {0, 0};
+                    for (int b = 0; b < 8; b++) {
+                        const int t = lane * 8 + b;
+                        if (used[t]) continue;
+                        const signed char* q = MCS_ORB_PATTERN_XY + 4 * t;  // x0, y0, x1, y1
+                        const uint32_t o[2] = {(uint32_t)(q[1] * 28 + q[0] + 377), (uint32_t)(q[3] * 28 + q[2] + 377)};
+                        int cost = 0;
+                        for (int e = 0; e < 2; e++) {
+                            const int w = (int)(o[e] >> 2);
+                            const bool bcast = std::find(words[e].begin(), words[e].end(), w) != words[e].end();
+                            cost += bcast ? 0 : (load[e][w & 31] + 1) * (load[e][w & 31] + 1);
+                        }
+                        if (cost < best_cost) { best_cost = cost; best = b; best_o[0] = o[0]; best_o[1] = o[1]; }
+                    }
+                    used[lane * 8 + best] = true;
+                    for (int e = 0; e < 2; e++) {
+                        const int w = (int)(best_o[e] >> 2);
+                        if (std::find(words[e].begin(), words[e].end(), w) == words[e].end()) { words[e].push_back(w); load[e][w & 31]++; }
+                    }
+                    ofs[lane * 8 + slot] = best_o[0] | (best_o[1] << 10) | ((uint32_t)best << 20);
+                }
             }
             CK(cudaMemcpyToSymbol(mcs::g_pattern_ofs28, ofs, sizeof(ofs)));
         }
