@@ -754,21 +754,36 @@ __global__ void __launch_bounds__(128) tri_solve2_kernel(int num_cams, int kp_ca
     tri_solve_class<2, 128>(nullptr, blockIdx.x, gridDim.x, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride);
 }
 
-// One launch for every view count >= 3: blockIdx.y = view-count class (NV = num_cams - y), blockIdx.x = persistent block of that class,
-// so the long, latency-bound solves of the different classes overlap instead of queueing behind each other.
+// One launch for every view count >= 3.  The solves are long, latency-bound and need a whole shared-memory slice each, so the grid is
+// as many one-warp blocks as fit the SMs, and every block pulls tiles of 32 rows from one queue that runs over the view-count classes
+// from the largest systems down (they run longest): no block idles while another class still has work.
 __global__ void __launch_bounds__(MCS_TRI_NT) tri_solve_kernel(int num_cams, int kp_cap, int row_cap, const CalibDev* __restrict__ calib,
                                                                const KeypointPod* __restrict__ kps, const uint8_t* __restrict__ desc,
                                                                LandmarkOut out, const int* __restrict__ lists,
-                                                               const int* __restrict__ list_count, int list_stride) {
+                                                               const int* __restrict__ list_count, int list_stride,
+                                                               int* __restrict__ tile_counter) {
     extern __shared__ __align__(16) double s_tri[];
-    const int b = blockIdx.x, nb = gridDim.x;
-    switch (num_cams - (int)blockIdx.y) {  // largest systems first: they run longest
-        case 3: tri_solve_class<3>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
-        case 4: tri_solve_class<4>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
-        case 5: tri_solve_class<5>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
-        case 6: tri_solve_class<6>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
-        case 7: tri_solve_class<7>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
-        default: tri_solve_class<8>(s_tri, b, nb, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+    __shared__ int s_tile;
+    constexpr int ONE = 1 << 20;  // "grid size" that makes tri_solve_class handle exactly one tile
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = atomicAdd(tile_counter, 1);
+        __syncthreads();
+        int t = s_tile, nv = num_cams;
+        for (; nv >= 3; nv--) {
+            const int tiles = (list_count[nv] + MCS_TRI_NT - 1) / MCS_TRI_NT;
+            if (t < tiles) break;
+            t -= tiles;
+        }
+        if (nv < 3) return;
+        switch (nv) {
+            case 3: tri_solve_class<3>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 4: tri_solve_class<4>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 5: tri_solve_class<5>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 6: tri_solve_class<6>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 7: tri_solve_class<7>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            default: tri_solve_class<8>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        }
     }
 }
 

@@ -974,7 +974,7 @@ struct mcs_rig {
             CK(cudaEventCreateWithFlags(&S.ev_join, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&S.ev_done, cudaEventDisableTiming));
             CK(cudaMalloc(&S.d_tri_lists, (size_t)(MCS_MAX_CAMS + 1) * rw * sizeof(int)));
-            CK(cudaMalloc(&S.d_tri_counts, (MCS_MAX_CAMS + 1) * sizeof(int)));
+            CK(cudaMalloc(&S.d_tri_counts, (MCS_MAX_CAMS + 2) * sizeof(int)));  // per view count + the tile queue head
         }
         if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
         CK(cudaMalloc(&lm.rows, rw * C * sizeof(int)));
@@ -1061,7 +1061,7 @@ struct mcs_rig {
         const float* mask = d_mask_ptr ? d_mask_ptr + (size_t)f0 * C * cfg.width * cfg.height : nullptr;
         eng.mark(ST_TRIANG);
         CK(cudaMemsetAsync(out.n_accepted, 0, n_frames * sizeof(int), S.st));
-        CK(cudaMemsetAsync(S.d_tri_counts, 0, (MCS_MAX_CAMS + 1) * sizeof(int), S.st));
+        CK(cudaMemsetAsync(S.d_tri_counts, 0, (MCS_MAX_CAMS + 2) * sizeof(int), S.st));
         dim3 g((row_cap + 127) / 128, n_frames);
         mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, S.st>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows + (size_t)f0 * row_cap * C,
                                                                     d_row_count + f0, kps, mask, out, S.d_tri_lists, S.d_tri_counts, tri_list_stride);
@@ -1076,8 +1076,10 @@ struct mcs_rig {
             eng.launches++;
             CK(cudaEventRecord(S.ev_join, S.st2));
             if (C >= 3) {
-                mcs::tri_solve_kernel<<<dim3(sm_count * 2, C - 2), MCS_TRI_NT, tri_smem(C), S.st>>>(C, kp_cap, row_cap, d_calib, kps, desc, out,
-                                                                                                  S.d_tri_lists, S.d_tri_counts, tri_list_stride);
+                const int per_sm = std::max(1, std::min(16, (int)((227 * 1024) / (tri_smem(C) + 1024))));
+                mcs::tri_solve_kernel<<<sm_count * per_sm, MCS_TRI_NT, tri_smem(C), S.st>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
+                                                                                          S.d_tri_counts, tri_list_stride,
+                                                                                          S.d_tri_counts + MCS_MAX_CAMS + 1);
                 eng.launches++;
             }
             CK(cudaStreamWaitEvent(S.st, S.ev_join, 0));
