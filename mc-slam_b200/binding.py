@@ -43,7 +43,8 @@ EXPORTS = [
 
 
 def library_path():
-    return os.path.join(_HERE, "libmcslam_b200.so")
+    # MCS_LIB: another build of the same library (kernel tuning experiments, tools/exp/)
+    return os.environ.get("MCS_LIB") or os.path.join(_HERE, "libmcslam_b200.so")
 
 
 def lib():

@@ -309,7 +309,9 @@ __global__ void __launch_bounds__(256) blur_kernel(const __grid_constant__ McsPl
 // The arc minima use packed 16-bit lanes (d + 256 keeps both lanes positive) and 3-input min/max (VIMNMX3).
 // ring offsets of FAST 9/16 in OpenCV order: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
 // ------------------------------------------------------------------------------------------------------------
+#ifndef MCS_FAST_NT
 #define MCS_FAST_NT 128
+#endif
 #define MCS_FAST_TPW 21  // tile pitch in 32-bit words: sub-image <= 75 px + 1 + staging slack (compile-time so ring offsets are immediates)
 #define MCS_FAST_SP 72   // score tile pitch (bytes)
 
@@ -537,7 +539,9 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
 // ------------------------------------------------------------------------------------------------------------
 // K4  DistributeOctTree.  One block per (level, image); algorithm in octree_core.h, executed with a CUDA block context.
 // ------------------------------------------------------------------------------------------------------------
-#define MCS_OCT_NT 256
+#ifndef MCS_OCT_NT
+#define MCS_OCT_NT 128  // 128 beats 256 inside the chunked pipeline: more blocks per SM hide the barrier-heavy serial phases
+#endif
 
 struct CudaBlockCtx {
     __device__ __forceinline__ int nthreads() const { return blockDim.x; }
