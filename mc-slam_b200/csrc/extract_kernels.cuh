@@ -781,8 +781,10 @@ __global__ void __launch_bounds__(MCS_DESC_WARPS * 32) describe_kernel(const __g
 // same bit-exact separable 7-tap filter as blur_kernel (DP4A rows, DP2A columns on vertical pairs) and samples the 256 tests
 // from shared memory: the blurred pyramid is neither written nor read (blur_kernel remains for the steered mode and observers).
 // ------------------------------------------------------------------------------------------------------------
+#ifndef MCS_DESCF_WARPS
 #define MCS_DESCF_WARPS 8
-__global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 6) describe_fused_kernel(const __grid_constant__ McsPlan P, ImageSet S,
+#endif
+__global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 48 / MCS_DESCF_WARPS) describe_fused_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                               const uint32_t* __restrict__ sel,
                                                                               const int* __restrict__ sel_count,
                                                                               KeypointPod* __restrict__ kps, uint8_t* __restrict__ desc,

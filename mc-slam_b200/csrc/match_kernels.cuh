@@ -15,8 +15,13 @@
 
 namespace mcs {
 
+#ifndef MCS_MATCH_NT
 #define MCS_MATCH_NT 128
-#define MCS_MATCH_CHUNK 1024  // train descriptors staged in shared memory per pass (32 KB)
+#endif
+#ifndef MCS_MATCH_CHUNK
+#define MCS_MATCH_CHUNK 1024
+#endif
+// MCS_MATCH_CHUNK train descriptors are staged in shared memory per pass (1024 = 32 KB)
 
 struct PairList {
     int n_pairs;
@@ -214,110 +219,186 @@ __global__ void __launch_bounds__(128) subset_match_kernel(const uint8_t* __rest
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// K7  merge.  The reference mutates match_inv_idx in pair order, later pairs see earlier state (:1222-1266), so the
-// walk is sequential per frame: one block per frame, thread 0 walks, the block initialises.  match_inv_idx lives in
-// shared memory (u16, 0xFFFF = -1).
+// K7  merge: computeIntraMatches(matches, old) after the pair matcher (:1222-1266).  The reference walks the matches of the pairs
+// in order and mutates match_inv_idx / the row table as it goes, so later matches and later pairs see earlier state.  Pairs stay
+// sequential (one block per frame walks them), but inside one pair (i, j) the walk decomposes:
+//   * a match (fi, fj) reads a = inv_i[fi] and b = inv_j[fj].  inv_i[fi] is only ever written by fi's own match, so a is the
+//     pre-pair value.  inv_j[fj] is shared by the matches with the same fj ("group").
+//   * b == -1: the group's FIRST match in query order acts — a == -1: new row;  a != -1: R[a][j] = fj, inv_j[fj] = a (no check,
+//     :1260-1264; a row shared by several fi through stale inverse entries keeps the LAST writer in query order).  Every later
+//     match of the group then sees b != -1 with R[b][i] occupied and does nothing.
+//   * b != -1 (pre-pair): only matches with a == -1 can act, and only while R[b][i] == -1: the first in query order over all
+//     groups that share the row b takes the slot (:1238-1247).
+//   * new row ids are handed out in query order: block-wide exclusive scan of the "creates a row" flags.
+// Three block-wide passes per pair instead of a one-thread walk; bit-identical rows (same order, same ids).
+// Shared memory: match_inv_idx (u16, 0xFFFF = -1), per-train-feature group minimum, per-row first / last claimant, per-query
+// decision, and (when it fits) the row table itself.
 // Fmat: per pair the f64 fundamental matrix built on the host (:1126-1141); sigma2 = mvLevelSigma2.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) merge_kernel(int num_cams, int kp_cap, int row_cap, PairList pairs,
-                                                    const int* __restrict__ kp_count, const int* __restrict__ match_train,
-                                                    const KeypointPod* __restrict__ kps, int use_epipolar,
-                                                    const double* __restrict__ Fmat, const float* __restrict__ sigma2,
-                                                    int* __restrict__ rows, int* __restrict__ row_count, int rows_in_smem) {
-    // dynamic shared: [num_cams][kp_cap] u16 match_inv_idx | [kp_cap] u32 compacted matches (fi | fj << 16) | optional row table
-    extern __shared__ __align__(16) uint16_t s_inv[];
-    __shared__ int s_nm, s_M;
-    const int frame = blockIdx.x;
-    const int inv_elems = (num_cams * kp_cap + 1) & ~1;
-    uint32_t* s_list = reinterpret_cast<uint32_t*>(s_inv + inv_elems);
+#define MCS_MERGE_NT 256
+
+struct MergeSmem {
+    size_t inv, grp, rfirst, rlast, val, kind, rows, total;
+};
+__host__ __device__ inline MergeSmem merge_smem_layout(int num_cams, int kp_cap, int row_cap, bool rows_in_smem) {
+    MergeSmem L;
+    size_t o = 0;
+    auto take = [&o](size_t bytes) { const size_t at = o; o += (bytes + 15) & ~(size_t)15; return at; };
+    L.inv = take((size_t)num_cams * kp_cap * 2);
+    L.grp = take((size_t)kp_cap * 4);
+    L.rfirst = take((size_t)row_cap * 4);
+    L.rlast = take((size_t)row_cap * 4);
+    L.val = take((size_t)kp_cap * 2);
+    L.kind = take((size_t)kp_cap);
+    L.rows = take(rows_in_smem ? (size_t)row_cap * num_cams * 4 : 0);
+    L.total = o;
+    return L;
+}
+
+__device__ __forceinline__ bool epipolar_ok(const KeypointPod& p1, const KeypointPod& p2, const double* __restrict__ F,
+                                            const float* __restrict__ sigma2) {
+    // :1177-1205 — products in f64 (no FMA contraction), narrowed to f32 exactly where the reference does
+    float a = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[0]), __dmul_rn((double)p2.y, F[3])), F[6]);
+    float b = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[1]), __dmul_rn((double)p2.y, F[4])), F[7]);
+    float c = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[2]), __dmul_rn((double)p2.y, F[5])), F[8]);
+    float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+    den = den != 0.f ? (float)__ddiv_rn(1.0, __dsqrt_rn((double)den)) : 1.f;
+    a = __fmul_rn(a, den);
+    b = __fmul_rn(b, den);
+    c = __fmul_rn(c, den);
+    den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+    const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, p1.x), __fmul_rn(b, p1.y)), c);
+    if (den == 0.f) return false;
+    const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+    const float thr = (float)__dmul_rn(3.84, (double)sigma2[p1.octave]);
+    return dsqr < thr;
+}
+
+__global__ void __launch_bounds__(MCS_MERGE_NT) merge_kernel(int num_cams, int kp_cap, int row_cap, PairList pairs,
+                                                             const int* __restrict__ kp_count, const int* __restrict__ match_train,
+                                                             const KeypointPod* __restrict__ kps, int use_epipolar,
+                                                             const double* __restrict__ Fmat, const float* __restrict__ sigma2,
+                                                             int* __restrict__ rows, int* __restrict__ row_count, int rows_in_smem) {
+    enum { K_NONE = 0, K_VALID = 1, K_NEW = 2, K_ATT_A = 3, K_ATT_B = 4 };
+    constexpr int NT = MCS_MERGE_NT, BIG = 0x7FFFFFFF;
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    __shared__ int s_wsum[NT / 32];
+    const MergeSmem L = merge_smem_layout(num_cams, kp_cap, row_cap, rows_in_smem != 0);
+    uint16_t* s_inv = reinterpret_cast<uint16_t*>(s_raw + L.inv);
+    int* s_grp = reinterpret_cast<int*>(s_raw + L.grp);        // [fj] smallest query index of the valid matches onto fj
+    int* s_rfirst = reinterpret_cast<int*>(s_raw + L.rfirst);  // [row] smallest query index claiming the row's column i
+    int* s_rlast = reinterpret_cast<int*>(s_raw + L.rlast);    // [row] largest (query index + 1) writing the row's column j
+    uint16_t* s_val = reinterpret_cast<uint16_t*>(s_raw + L.val);  // [q] row the decision refers to
+    uint8_t* s_kind = s_raw + L.kind;                              // [q] decision of the current pair
+    const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int* G = rows + (size_t)frame * row_cap * num_cams;
-    int* R = rows_in_smem ? reinterpret_cast<int*>(s_list + kp_cap) : G;
-    for (int t = threadIdx.x; t < num_cams * kp_cap; t += blockDim.x) s_inv[t] = 0xFFFFu;
-    if (threadIdx.x == 0) s_M = 0;
-    const int lane = threadIdx.x & 31;
+    int* R = rows_in_smem ? reinterpret_cast<int*>(s_raw + L.rows) : G;
+    for (int t = tid; t < num_cams * kp_cap; t += NT) s_inv[t] = 0xFFFFu;
+    for (int t = tid; t < kp_cap; t += NT) { s_grp[t] = BIG; s_kind[t] = K_NONE; }
+    for (int t = tid; t < row_cap; t += NT) { s_rfirst[t] = BIG; s_rlast[t] = 0; }
+    // every thread owns the same contiguous range of query indices in all pairs (needed for the ordered scan)
+    const int IT = (kp_cap + NT - 1) / NT;
+    const int q_lo = tid * IT;
+    int M = 0;
+    __syncthreads();
     for (int p = 0; p < pairs.n_pairs; p++) {
         const int i = pairs.a[p], j = pairs.b[p];
         const int nq = kp_count[frame * num_cams + i];
+        const int q_hi = min(q_lo + IT, nq);
         const int* mt = match_train + ((size_t)frame * pairs.n_pairs + p) * kp_cap;
-        __syncthreads();
-        if (threadIdx.x == 0) s_nm = 0;
-        __syncthreads();
-        // order-preserving compaction of the accepted matches of this pair (query order, :1060-1076); one warp keeps it simple
-        if (threadIdx.x < 32) {
-            int base = 0;
-            for (int q0 = 0; q0 < nq; q0 += 32) {
-                const int q = q0 + lane;
-                const int fj = q < nq ? __ldg(&mt[q]) : -1;
-                const unsigned m = __ballot_sync(0xFFFFFFFFu, fj >= 0);
-                if (fj >= 0) s_list[base + __popc(m & ((1u << lane) - 1))] = (uint32_t)q | ((uint32_t)fj << 16);
-                base += __popc(m);
-            }
-            if (lane == 0) s_nm = base;
-        }
-        __syncthreads();
-        if (threadIdx.x != 0) continue;
-        // the reference mutates match_inv_idx while it walks: later matches (and later pairs) see earlier state => sequential
-        const int nm = s_nm;
-        int M = s_M;
-        const double* F = Fmat + p * 9;
         uint16_t* invi = s_inv + i * kp_cap;
         uint16_t* invj = s_inv + j * kp_cap;
-        for (int e = 0; e < nm; e++) {
-            const uint32_t pr = s_list[e];
-            const int fi = (int)(pr & 0xFFFFu), fj = (int)(pr >> 16);
-            if (use_epipolar) {
-                // :1177-1205 — products in f64 (no FMA contraction), narrowed to f32 exactly where the reference does
-                const KeypointPod p1 = kps[(size_t)(frame * num_cams + i) * kp_cap + fi];
-                const KeypointPod p2 = kps[(size_t)(frame * num_cams + j) * kp_cap + fj];
-                float a = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[0]), __dmul_rn((double)p2.y, F[3])), F[6]);
-                float b = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[1]), __dmul_rn((double)p2.y, F[4])), F[7]);
-                float c = (float)__dadd_rn(__dadd_rn(__dmul_rn((double)p2.x, F[2]), __dmul_rn((double)p2.y, F[5])), F[8]);
-                float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
-                den = den != 0.f ? (float)__ddiv_rn(1.0, __dsqrt_rn((double)den)) : 1.f;
-                a = __fmul_rn(a, den);
-                b = __fmul_rn(b, den);
-                c = __fmul_rn(c, den);
-                den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
-                const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, p1.x), __fmul_rn(b, p1.y)), c);
-                bool res;
-                if (den == 0.f) res = false;
-                else {
-                    const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
-                    const float thr = (float)__dmul_rn(3.84, (double)sigma2[p1.octave]);
-                    res = dsqr < thr;
+        const KeypointPod* ki = kps + (size_t)(frame * num_cams + i) * kp_cap;
+        const KeypointPod* kj = kps + (size_t)(frame * num_cams + j) * kp_cap;
+        // pass A: valid matches (epipolar gate when `old`), group minimum per train feature
+        for (int q = q_lo; q < q_hi; q++) {
+            const int fj = __ldg(&mt[q]);
+            bool ok = fj >= 0;
+            if (ok && use_epipolar) ok = epipolar_ok(ki[q], kj[fj], Fmat + p * 9, sigma2);
+            s_kind[q] = ok ? K_VALID : K_NONE;
+            if (ok) atomicMin(&s_grp[fj], q);
+        }
+        __syncthreads();
+        // pass B: decisions against the pre-pair state
+        for (int q = q_lo; q < q_hi; q++) {
+            if (s_kind[q] == K_NONE) continue;
+            const int fj = __ldg(&mt[q]);
+            const int a = invi[q], b = invj[fj];
+            int kind = K_VALID, val = 0;  // valid but without effect unless one of the cases below applies
+            if (b == 0xFFFF) {
+                if (s_grp[fj] == q) {
+                    if (a == 0xFFFF) kind = K_NEW;
+                    else { kind = K_ATT_A; val = a; atomicMax(&s_rlast[a], q + 1); }
                 }
-                if (!res) continue;
+            } else if (a == 0xFFFF && R[(size_t)b * num_cams + i] == -1) {
+                kind = K_ATT_B; val = b; atomicMin(&s_rfirst[b], q);
             }
-            const int mi = invi[fi] == 0xFFFFu ? -1 : (int)invi[fi];
-            const int mj = invj[fj] == 0xFFFFu ? -1 : (int)invj[fj];
-            if (mi == -1 && mj == -1) {
-                if (M < row_cap) {
-                    int* r = R + (size_t)M * num_cams;
+            s_kind[q] = (uint8_t)kind;
+            s_val[q] = (uint16_t)val;
+        }
+        // ordered ids of the new rows
+        int my_new = 0;
+        __syncthreads();
+        for (int q = q_lo; q < q_hi; q++) my_new += s_kind[q] == K_NEW;
+        int incl = my_new;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int base = M + incl - my_new, total_new = 0;
+#pragma unroll
+        for (int w = 0; w < NT / 32; w++) {
+            const int ws = s_wsum[w];
+            if (w < warp) base += ws;
+            total_new += ws;
+        }
+        // pass C: apply the decisions (they touch disjoint state)
+        for (int q = q_lo; q < q_hi; q++) {
+            const int kind = s_kind[q];
+            if (kind < K_NEW) continue;
+            const int fj = __ldg(&mt[q]);
+            if (kind == K_NEW) {
+                const int id = base++;
+                if (id < row_cap) {
+                    int* r = R + (size_t)id * num_cams;
                     for (int c = 0; c < num_cams; c++) r[c] = -1;
-                    r[i] = fi;
+                    r[i] = q;
                     r[j] = fj;
-                    invi[fi] = (uint16_t)M;
-                    invj[fj] = (uint16_t)M;
+                    invi[q] = (uint16_t)id;
+                    invj[fj] = (uint16_t)id;
                 }
-                M++;
-            } else if (mi == -1 && mj != -1) {
-                if (R[(size_t)mj * num_cams + i] == -1) {
-                    R[(size_t)mj * num_cams + i] = fi;
-                    invi[fi] = (uint16_t)mj;
+            } else if (kind == K_ATT_A) {
+                const int a = s_val[q];
+                invj[fj] = (uint16_t)a;
+                if (s_rlast[a] == q + 1) R[(size_t)a * num_cams + j] = fj;
+            } else {
+                const int b = s_val[q];
+                if (s_rfirst[b] == q) {
+                    R[(size_t)b * num_cams + i] = q;
+                    invi[q] = (uint16_t)b;
                 }
-            } else if (mi != -1 && mj == -1) {
-                R[(size_t)mi * num_cams + j] = fj;
-                invj[fj] = (uint16_t)mi;
             }
         }
-        s_M = M;
+        M += total_new;
+        __syncthreads();
+        // reset the claim tables for the next pair
+        for (int q = q_lo; q < q_hi; q++) {
+            const int kind = s_kind[q];
+            if (kind == K_NONE) continue;
+            s_grp[__ldg(&mt[q])] = BIG;
+            if (kind == K_ATT_A) s_rlast[s_val[q]] = 0;
+            else if (kind == K_ATT_B) s_rfirst[s_val[q]] = BIG;
+            s_kind[q] = K_NONE;
+        }
+        __syncthreads();
     }
-    __syncthreads();
-    const int M = s_M;
-    if (threadIdx.x == 0) row_count[frame] = M;
+    if (tid == 0) row_count[frame] = M;
     if (rows_in_smem) {
         const int n = min(M, row_cap) * num_cams;
-        for (int t = threadIdx.x; t < n; t += blockDim.x) G[t] = R[t];
+        for (int t = tid; t < n; t += NT) G[t] = R[t];
     }
 }
 

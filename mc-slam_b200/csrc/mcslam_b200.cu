@@ -994,12 +994,12 @@ struct mcs_rig {
         CK(cudaMallocHost(&h_accepted, rw));
         CK(cudaMallocHost(&h_xyz, rw * 3 * sizeof(double)));
         CK(cudaMallocHost(&h_uv, rw * 2 * sizeof(float)));
-        // match_inv_idx (u16) + compacted match list + (when it fits) the IntraMatch row table itself
-        merge_smem = (size_t)((C * kp_cap + 1) & ~1) * sizeof(uint16_t) + (size_t)kp_cap * sizeof(uint32_t);
-        if (kp_cap >= 65535) { set_err("too many features per camera for the merge kernel"); return MCS_ERR_ARG; }
+        // match_inv_idx (u16) + claim tables + (when it fits) the IntraMatch row table itself
+        if (kp_cap >= 65535 || row_cap >= 65535) { set_err("too many features per camera for the merge kernel"); return MCS_ERR_ARG; }
+        merge_smem = mcs::merge_smem_layout(C, kp_cap, row_cap, false).total;
         if (merge_smem > 200 * 1024) { set_err("too many features per frame for the merge kernel's shared table"); return MCS_ERR_ARG; }
-        merge_rows_smem = merge_smem + (size_t)row_cap * C * sizeof(int) <= 100 * 1024;
-        if (merge_rows_smem) merge_smem += (size_t)row_cap * C * sizeof(int);
+        merge_rows_smem = mcs::merge_smem_layout(C, kp_cap, row_cap, true).total <= 100 * 1024;
+        if (merge_rows_smem) merge_smem = mcs::merge_smem_layout(C, kp_cap, row_cap, true).total;
         CK(cudaFuncSetAttribute(mcs::merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(merge_smem, 1024)));
         return 0;
     }
@@ -1035,7 +1035,7 @@ struct mcs_rig {
             eng.launches++;
         }
         eng.mark(ST_MERGE);
-        mcs::merge_kernel<<<n_frames, 128, merge_smem, st>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
+        mcs::merge_kernel<<<n_frames, MCS_MERGE_NT, merge_smem, st>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
                                                              eng.d_kps + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
                                                              d_rows + (size_t)f0 * row_cap * C, d_row_count + f0, merge_rows_smem ? 1 : 0);
         eng.launches++;
