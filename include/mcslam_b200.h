@@ -134,6 +134,9 @@ MCS_API int mcs_rig_extract(mcs_rig* rig, const uint8_t* images, int n_frames);
 /* The same with images already resident in device memory (bench `value` leg); layout as above. */
 MCS_API int mcs_rig_extract_device(mcs_rig* rig, const void* d_images, int n_frames);
 
+/* Features computed elsewhere for the rig frames [0, n_frames) instead of stage A (image_kps / image_descriptors filled by another
+ * extractor): counts[n_frames * num_cams], then the cameras' keypoints and 32-byte descriptors back to back in image order. */
+MCS_API int mcs_rig_set_features(mcs_rig* rig, int n_frames, const int* counts, const mcs_keypoint* keypoints, const uint8_t* descriptors);
 /* image_kps[cam] / image_descriptors[cam] of frame `frame`.  Returns the keypoint count. */
 MCS_API int mcs_rig_get_features(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, uint8_t* descriptors, int capacity);
 

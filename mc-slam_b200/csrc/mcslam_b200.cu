@@ -1288,6 +1288,33 @@ int mcs_rig_get_features(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoin
     return n;
 }
 
+// Features computed elsewhere (another extractor, a test) for the rig frames [0, n_frames): replaces stage A for the stages that
+// follow.  counts[n_frames * num_cams]; keypoints / descriptors: the cameras' features back to back in image order.
+int mcs_rig_set_features(mcs_rig* rig, int n_frames, const int* counts, const mcs_keypoint* keypoints, const uint8_t* descriptors) {
+    RIG_ENTER(rig);
+    if (!counts || !keypoints || !descriptors || n_frames < 1) return MCS_ERR_ARG;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    const int n_img = n_frames * rig->C, cap = rig->kp_cap;
+    cudaStream_t st = rig->eng.stream;
+    size_t ofs = 0;
+    for (int i = 0; i < n_img; i++) {
+        const int n = counts[i];
+        if (n < 0 || n > cap) { set_err("set_features: more features than the handle's capacity"); return MCS_ERR_CAPACITY; }
+        if (n) {
+            CK(cudaMemcpyAsync(rig->eng.d_kps + (size_t)i * cap, keypoints + ofs, (size_t)n * sizeof(mcs_keypoint), cudaMemcpyHostToDevice, st));
+            CK(cudaMemcpyAsync(rig->eng.d_desc + (size_t)i * cap * 32, descriptors + ofs * 32, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+        }
+        ofs += n;
+    }
+    CK(cudaMemcpyAsync(rig->eng.d_kp_count, counts, (size_t)n_img * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    rig->n_extracted = n_frames;
+    rig->n_matched = rig->n_triangulated = 0;
+    rig->eng.last_n = n_img;
+    rig->invalidate();
+    return 0;
+}
+
 int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float dist_thresh, float neigh_ratio, uint32_t* indices_1,
                               uint32_t* indices_2, mcs_keypoint* kps1, mcs_keypoint* kps2, int capacity) {
     RIG_ENTER(rig);

@@ -296,3 +296,56 @@ def test_process_f32_equals_set_data_then_u8_path(golden, channels):
     with pytest.raises(M.McsError):
         lib_rc = B.lib().mcs_rig_process_f32(one.hd, B._p(img), 2, None, 1, 0)
         B._check(lib_rc, "process_f32")
+
+
+@pytest.mark.parametrize("old", [False, True])
+def test_merge_many_to_one_stress(old):
+    """IntraMatch merge on injected features (mcs_rig_set_features) built to make the order-dependent cases frequent: clusters of
+    near-duplicate descriptors, so that many queries of one camera pick the same train feature, rows get attached / overwritten by
+    later pairs, and inverse-index entries go stale.  6 frames x 5 cameras, ragged counts (incl. an empty camera); rows, landmarks
+    and counts bit-exact against the oracle's sequential walk."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    C, w, h, F = 5, 320, 240, 6
+    calib = M.synth.make_rig(C, w, h)
+    rig = M.RigFrames(calib, w, h, nfeatures=400, max_frames=F)
+    rng = np.random.default_rng(77 + int(old))
+    sigma2 = O.Extractor(400).sigma2
+    allK, allD, per_frame = [], [], []
+    for f in range(F):
+        n_centres = [12, 40, 150, 300, 60, 25][f]
+        centres = rng.integers(0, 256, (n_centres, 32), dtype=np.uint8)
+        K, D = [], []
+        for c in range(C):
+            n = int(rng.integers(150, rig.kp_cap - 10)) if not (f == 2 and c == 3) else 0
+            which = rng.integers(0, n_centres, n)
+            d = centres[which].copy()
+            for k in range(n):  # 0..24 flipped bits: within the distance gate, ratio test decided by the cluster structure
+                bits = rng.choice(256, int(rng.integers(0, 25)), replace=False)
+                np.bitwise_xor.at(d[k], bits // 8, (1 << (bits % 8)).astype(np.uint8))
+            k = np.zeros(n, M.KP_DTYPE)
+            k["x"] = rng.uniform(20, w - 20, n).astype(np.float32)
+            k["y"] = rng.uniform(20, h - 20, n).astype(np.float32)
+            k["size"] = 31
+            k["response"] = rng.integers(7, 200, n)
+            k["octave"] = rng.integers(0, 8, n)
+            k["class_id"] = -1
+            K.append(k)
+            D.append(d)
+        per_frame.append((K, D))
+        allK += K
+        allD += D
+    rig.set_features(allK, allD)
+    rig.compute_intra_matches(F, old=old)
+    rig.triangulate(F)
+    many_to_one = 0
+    for f, (K, D) in enumerate(per_frame):
+        rows, pc = O.intra_matches(D, K, calib, sigma2, use_epipolar=old)
+        got = rig.intra_matches(f)
+        assert got.shape == rows.shape and np.array_equal(got, rows), "frame %d" % f
+        tri = O.triangulate_rows(calib, K, D, rows)
+        lm = rig.landmarks(f)
+        assert np.array_equal(lm["status"], tri["status"]) and np.array_equal(lm["rep_cam"], tri["rep_cam"])
+        a, b = rig.brute_force_match(f, 0, 1)[:2]
+        many_to_one += len(b) - len(set(b.tolist()))
+    assert old or many_to_one > 50, "the fixture must contain many-to-one matches"
