@@ -245,14 +245,36 @@ __host__ __device__ inline MergeSmem merge_smem_layout(int num_cams, int kp_cap,
     size_t o = 0;
     auto take = [&o](size_t bytes) { const size_t at = o; o += (bytes + 15) & ~(size_t)15; return at; };
     L.inv = take((size_t)num_cams * kp_cap * 2);
-    L.grp = take((size_t)kp_cap * 4);
-    L.rfirst = take((size_t)row_cap * 4);
-    L.rlast = take((size_t)row_cap * 4);
+    L.grp = take((size_t)kp_cap * 2);
+    L.rfirst = take((size_t)row_cap * 2);
+    L.rlast = take((size_t)row_cap * 2);
     L.val = take((size_t)kp_cap * 2);
     L.kind = take((size_t)kp_cap);
     L.rows = take(rows_in_smem ? (size_t)row_cap * num_cams * 4 : 0);
     L.total = o;
     return L;
+}
+
+// 16-bit atomic min / max in shared memory (CAS on the containing word; the claim tables see little contention)
+__device__ __forceinline__ void atomic_min_u16(uint16_t* p, uint32_t v) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+    const int sh = (int)(reinterpret_cast<uintptr_t>(p) & 2) * 8;
+    uint32_t old = *w;
+    while (((old >> sh) & 0xFFFFu) > v) {
+        const uint32_t prev = atomicCAS(w, old, (old & ~(0xFFFFu << sh)) | (v << sh));
+        if (prev == old) break;
+        old = prev;
+    }
+}
+__device__ __forceinline__ void atomic_max_u16(uint16_t* p, uint32_t v) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+    const int sh = (int)(reinterpret_cast<uintptr_t>(p) & 2) * 8;
+    uint32_t old = *w;
+    while (((old >> sh) & 0xFFFFu) < v) {
+        const uint32_t prev = atomicCAS(w, old, (old & ~(0xFFFFu << sh)) | (v << sh));
+        if (prev == old) break;
+        old = prev;
+    }
 }
 
 __device__ __forceinline__ bool epipolar_ok(const KeypointPod& p1, const KeypointPod& p2, const double* __restrict__ F,
@@ -280,14 +302,14 @@ __global__ void __launch_bounds__(MCS_MERGE_NT) merge_kernel(int num_cams, int k
                                                              const double* __restrict__ Fmat, const float* __restrict__ sigma2,
                                                              int* __restrict__ rows, int* __restrict__ row_count, int rows_in_smem) {
     enum { K_NONE = 0, K_VALID = 1, K_NEW = 2, K_ATT_A = 3, K_ATT_B = 4 };
-    constexpr int NT = MCS_MERGE_NT, BIG = 0x7FFFFFFF;
+    constexpr int NT = MCS_MERGE_NT, BIG = 0xFFFF;
     extern __shared__ __align__(16) unsigned char s_raw[];
     __shared__ int s_wsum[NT / 32];
     const MergeSmem L = merge_smem_layout(num_cams, kp_cap, row_cap, rows_in_smem != 0);
     uint16_t* s_inv = reinterpret_cast<uint16_t*>(s_raw + L.inv);
-    int* s_grp = reinterpret_cast<int*>(s_raw + L.grp);        // [fj] smallest query index of the valid matches onto fj
-    int* s_rfirst = reinterpret_cast<int*>(s_raw + L.rfirst);  // [row] smallest query index claiming the row's column i
-    int* s_rlast = reinterpret_cast<int*>(s_raw + L.rlast);    // [row] largest (query index + 1) writing the row's column j
+    uint16_t* s_grp = reinterpret_cast<uint16_t*>(s_raw + L.grp);        // [fj] smallest query index of the valid matches onto fj
+    uint16_t* s_rfirst = reinterpret_cast<uint16_t*>(s_raw + L.rfirst);  // [row] smallest query index claiming the row's column i
+    uint16_t* s_rlast = reinterpret_cast<uint16_t*>(s_raw + L.rlast);    // [row] largest (query index + 1) writing the row's column j
     uint16_t* s_val = reinterpret_cast<uint16_t*>(s_raw + L.val);  // [q] row the decision refers to
     uint8_t* s_kind = s_raw + L.kind;                              // [q] decision of the current pair
     const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -316,7 +338,7 @@ __global__ void __launch_bounds__(MCS_MERGE_NT) merge_kernel(int num_cams, int k
             bool ok = fj >= 0;
             if (ok && use_epipolar) ok = epipolar_ok(ki[q], kj[fj], Fmat + p * 9, sigma2);
             s_kind[q] = ok ? K_VALID : K_NONE;
-            if (ok) atomicMin(&s_grp[fj], q);
+            if (ok) atomic_min_u16(&s_grp[fj], (uint32_t)q);
         }
         __syncthreads();
         // pass B: decisions against the pre-pair state
@@ -328,10 +350,10 @@ __global__ void __launch_bounds__(MCS_MERGE_NT) merge_kernel(int num_cams, int k
             if (b == 0xFFFF) {
                 if (s_grp[fj] == q) {
                     if (a == 0xFFFF) kind = K_NEW;
-                    else { kind = K_ATT_A; val = a; atomicMax(&s_rlast[a], q + 1); }
+                    else { kind = K_ATT_A; val = a; atomic_max_u16(&s_rlast[a], (uint32_t)(q + 1)); }
                 }
             } else if (a == 0xFFFF && R[(size_t)b * num_cams + i] == -1) {
-                kind = K_ATT_B; val = b; atomicMin(&s_rfirst[b], q);
+                kind = K_ATT_B; val = b; atomic_min_u16(&s_rfirst[b], (uint32_t)q);
             }
             s_kind[q] = (uint8_t)kind;
             s_val[q] = (uint16_t)val;

@@ -349,3 +349,33 @@ def test_merge_many_to_one_stress(old):
         a, b = rig.brute_force_match(f, 0, 1)[:2]
         many_to_one += len(b) - len(set(b.tolist()))
     assert old or many_to_one > 50, "the fixture must contain many-to-one matches"
+
+
+def test_merge_config4_capacity():
+    """SURVEY config 4 (8 cameras, 1920 x 1200, 4000 features per camera): the handle must come up (the merge kernel's shared tables
+    are sized by camera count x feature capacity) and merge 8 x ~4000 injected features exactly like the oracle."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    C, w, h = 8, 1920, 1200
+    calib = M.synth.make_rig(C, w, h, spacing=0.1)
+    rig = M.RigFrames(calib, w, h, nfeatures=4000, max_frames=1)
+    assert rig.kp_cap >= 4000
+    rng = np.random.default_rng(5)
+    centres = rng.integers(0, 256, (3000, 32), dtype=np.uint8)
+    K, D = [], []
+    for c in range(C):
+        n = rig.kp_cap - int(rng.integers(0, 200))
+        d = centres[rng.integers(0, len(centres), n)].copy()
+        flips = rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        d ^= flips  # ~16 flipped bits
+        k = np.zeros(n, M.KP_DTYPE)
+        k["x"] = rng.uniform(20, w - 20, n).astype(np.float32)
+        k["y"] = rng.uniform(20, h - 20, n).astype(np.float32)
+        k["size"], k["class_id"] = 31, -1
+        K.append(k)
+        D.append(d)
+    rig.set_features(K, D)
+    rig.compute_intra_matches(1)
+    rows, pc = O.intra_matches(D, K, calib, O.Extractor(4000).sigma2)
+    got = rig.intra_matches(0)
+    assert len(rows) > 4000 and got.shape == rows.shape and np.array_equal(got, rows)
