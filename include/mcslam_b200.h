@@ -193,6 +193,13 @@ MCS_API int mcs_rig_process_f32(mcs_rig* rig, const float* images, int channels,
 MCS_API int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int channels, const void* d_masks, int n_frames,
                                        int old_epipolar);
 
+/* RECTIFY branch of MultiCameraFrame::setData (MultiCameraFrame.cpp:123-136; CamArrayConfig::RECTIFY defaults to true): when enabled,
+ * every image entering the handle (all extract / process entry points) goes through cv::undistort(img, K, dist_coeffs) with
+ * dist = (k1, k2, p1, p2, k3) of mcs_calib, and every mask through the same maps (float weights), on the device.  Keypoints are then in
+ * undistorted coordinates (image_kps_undist = image_kps, :241-243).  Off by default (the u8 entry points expect what setData hands
+ * to the extractor). */
+MCS_API int mcs_rig_set_undistort(mcs_rig* rig, int enable);
+
 /* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over four
  * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
 MCS_API int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames);

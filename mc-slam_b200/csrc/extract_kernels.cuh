@@ -71,6 +71,53 @@ __global__ void __launch_bounds__(256) stage_f32_kernel(const float* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K0b  cv::undistort of setData's RECTIFY branch (/root/reference/MCSlam/src/MultiCameraFrame.cpp:123-136) as a gather: the host
+// builds cv::initUndistortRectifyMap's CV_16SC2 fixed-point maps once per camera (map.x = sx | sy << 16 as int16, map.y = fy * 32 + fx,
+// 5-bit fractions); remap(INTER_LINEAR, BORDER_CONSTANT 0) is 4 taps with the integer weights (32 - fy)(32 - fx) * 32 ... (the
+// entries of OpenCV's 15-bit table are exactly these products) and (v + 2^14) >> 15.  4 output pixels per thread; the result goes
+// straight into the pyramid's level-0 plane.  The f32 variant (segmentation masks, :131-134) uses the float weights in OpenCV's order.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) undistort_u8_kernel(const uint8_t* __restrict__ src, size_t src_stride, uint8_t* __restrict__ dst,
+                                                           size_t dst_stride, int dpitch, const uint2* __restrict__ maps, int num_cams,
+                                                           int img0, int w, int h) {
+    const int g = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;  // g = group of 4 pixels
+    if (4 * g >= w || y >= h) return;
+    const int img = blockIdx.z;
+    const uint8_t* S = src + (size_t)img * src_stride;
+    const uint2* M = maps + (size_t)((img0 + img) % num_cams) * w * h + (size_t)y * w + 4 * g;
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        if (4 * g + k >= w) break;
+        const uint2 m = __ldg(M + k);
+        const int sx = (short)(m.x & 0xFFFFu), sy = (short)(m.x >> 16), fx = (int)(m.y & 31u), fy = (int)(m.y >> 5);
+        const bool x0 = sx >= 0 && sx < w, x1 = sx + 1 >= 0 && sx + 1 < w, y0 = sy >= 0 && sy < h, y1 = sy + 1 >= 0 && sy + 1 < h;
+        const uint8_t* r0 = S + (size_t)sy * w + sx;
+        const int p00 = (x0 && y0) ? r0[0] : 0, p01 = (x1 && y0) ? r0[1] : 0, p10 = (x0 && y1) ? r0[w] : 0, p11 = (x1 && y1) ? r0[w + 1] : 0;
+        const int v = p00 * ((32 - fy) * (32 - fx) * 32) + p01 * ((32 - fy) * fx * 32) + p10 * (fy * (32 - fx) * 32) + p11 * (fy * fx * 32);
+        out |= (uint32_t)((v + (1 << 14)) >> 15) << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(dst + (size_t)img * dst_stride + (size_t)y * dpitch + 4 * g) = out;  // dpitch % 64 == 0
+}
+
+__global__ void __launch_bounds__(256) undistort_f32_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                                            const uint2* __restrict__ maps, int num_cams, int w, int h) {
+    const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    if (x >= w || y >= h) return;
+    const int img = blockIdx.z;
+    const float* S = src + (size_t)img * w * h;
+    const uint2 m = __ldg(maps + (size_t)(img % num_cams) * w * h + (size_t)y * w + x);
+    const int sx = (short)(m.x & 0xFFFFu), sy = (short)(m.x >> 16);
+    const float fx = __fmul_rn((float)(m.y & 31u), 1.f / 32), fy = __fmul_rn((float)(m.y >> 5), 1.f / 32);
+    const bool x0 = sx >= 0 && sx < w, x1 = sx + 1 >= 0 && sx + 1 < w, y0 = sy >= 0 && sy < h, y1 = sy + 1 >= 0 && sy + 1 < h;
+    const float* r0 = S + (size_t)sy * w + sx;
+    const float p00 = (x0 && y0) ? r0[0] : 0.f, p01 = (x1 && y0) ? r0[1] : 0.f, p10 = (x0 && y1) ? r0[w] : 0.f, p11 = (x1 && y1) ? r0[w + 1] : 0.f;
+    const float w00 = __fmul_rn(1.f - fy, 1.f - fx), w01 = __fmul_rn(1.f - fy, fx), w10 = __fmul_rn(fy, 1.f - fx), w11 = __fmul_rn(fy, fx);
+    dst[(size_t)img * w * h + (size_t)y * w + x] =
+        __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p00, w00), __fmul_rn(p01, w01)), __fmul_rn(p10, w10)), __fmul_rn(p11, w11));
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K1  cv::resize(prev, cur, INTER_LINEAR) on 8U: 11-bit fixed-point coefficients, two-stage rounding.
 // xtab[dx] = {sx, a0 | a1 << 16}, ytab[dy] = {sy, b0 | b1 << 16} are built on the host exactly as OpenCV does.
 // One thread produces 4 horizontally adjacent pixels (one 32-bit store).

@@ -242,6 +242,41 @@ bool build_resize_word_tables(const McsLevel& D, const McsLevel& Sv, const std::
     return true;
 }
 
+// cv::initUndistortRectifyMap(K, dist, I, K', CV_16SC2) as cv::undistort runs it per stripe of max(1, 4096 / cols) rows with
+// K'.cy = cy - y0 (OpenCV imgproc undistort): f64 arithmetic in OpenCV's operation order (3x3 inverse by cofactors, _x / _y / _w
+// accumulated along the row), coordinates * 32 rounded half to even.  out[i] = {sx | sy << 16 (int16 each), fy * 32 + fx}.
+void build_undistort_map(const mcs_calib& c, int w, int h, uint2* out) {
+    const double k1 = c.dist[0], k2 = c.dist[1], p1 = c.dist[2], p2 = c.dist[3], k3 = c.dist[4];
+    const double fx = c.K[0], fy = c.K[4], u0 = c.K[2], v0 = c.K[5];
+    const int stripe0 = std::min(std::max(1, (1 << 12) / std::max(w, 1)), h);
+    for (int y0 = 0; y0 < h; y0 += stripe0) {
+        const int ss = std::min(stripe0, h - y0);
+        double A[9];
+        for (int i = 0; i < 9; i++) A[i] = c.K[i];
+        A[5] = v0 - y0;
+        const double det = A[0] * (A[4] * A[8] - A[5] * A[7]) - A[1] * (A[3] * A[8] - A[5] * A[6]) + A[2] * (A[3] * A[7] - A[4] * A[6]);
+        const double d = 1. / det;
+        const double ir[9] = {(A[4] * A[8] - A[5] * A[7]) * d, (A[2] * A[7] - A[1] * A[8]) * d, (A[1] * A[5] - A[2] * A[4]) * d,
+                              (A[5] * A[6] - A[3] * A[8]) * d, (A[0] * A[8] - A[2] * A[6]) * d, (A[2] * A[3] - A[0] * A[5]) * d,
+                              (A[3] * A[7] - A[4] * A[6]) * d, (A[1] * A[6] - A[0] * A[7]) * d, (A[0] * A[4] - A[1] * A[3]) * d};
+        for (int i = 0; i < ss; i++) {
+            double _x = i * ir[1] + ir[2], _y = i * ir[4] + ir[5], _w = i * ir[7] + ir[8];
+            for (int j = 0; j < w; j++, _x += ir[0], _y += ir[3], _w += ir[6]) {
+                const double iw = 1. / _w, x = _x * iw, y = _y * iw;
+                const double x2 = x * x, y2 = y * y, r2 = x2 + y2, _2xy = 2 * x * y;
+                const double kr = (1 + ((k3 * r2 + k2) * r2 + k1) * r2) / (1 + ((0 * r2 + 0) * r2 + 0) * r2);
+                const double xd = x * kr + p1 * _2xy + p2 * (r2 + 2 * x2);
+                const double yd = y * kr + p1 * (r2 + 2 * y2) + p2 * _2xy;
+                const double u = fx * xd + u0, v = fy * yd + v0;
+                auto sat = [](double t) { return t < -2147483648.0 ? (long)INT32_MIN : (t > 2147483647.0 ? (long)INT32_MAX : std::lrint(t)); };
+                const long iu = sat(u * 32), iv = sat(v * 32);
+                out[(size_t)(y0 + i) * w + j] =
+                    make_uint2((uint32_t)(uint16_t)(short)(iu >> 5) | ((uint32_t)(uint16_t)(short)(iv >> 5) << 16), (uint32_t)((iv & 31) * 32 + (iu & 31)));
+            }
+        }
+    }
+}
+
 // One record per FAST cell the reference actually runs (ComputeKeyPointsOctTree :804-821; cells with iniY >= maxBorderY - 3 or
 // iniX >= maxBorderX - 6 are skipped there and are not listed): x = level, y = iniX | iniY << 16, z = sub-image width | height << 16,
 // w = candidate coordinate offset (3 + j * wCell) | (3 + i * hCell) << 16.
@@ -582,6 +617,21 @@ struct Engine {
         launches++;
         return make_set(d_input, n, w, h, set, img0, st);
     }
+    // RECTIFY branch of setData: n tight images starting at image img0 of d_images are undistorted (K0b) into the pyramid's level-0
+    // planes, which become the image set's level 0.
+    int make_set_undistorted(const uint8_t* d_images, int n, int w, int h, const uint2* maps, int num_cams, mcs::ImageSet& set, int img0,
+                             cudaStream_t st) {
+        if (n < 1 || img0 + n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
+        dim3 b(32, 8), g((w + 127) / 128, (h + 7) / 8, n);
+        mcs::undistort_u8_kernel<<<g, b, 0, st>>>(d_images + (size_t)img0 * w * h, (size_t)w * h,
+                                                  d_pyr + (size_t)img0 * plan.pyr_stride + plan.L[0].plane_ofs, plan.pyr_stride, plan.L[0].pitch,
+                                                  maps, num_cams, img0, w, h);
+        CK(cudaGetLastError());
+        launches++;
+        set.pyr = d_pyr;
+        set.l0 = d_pyr + plan.L[0].plane_ofs; set.l0_pitch = plan.L[0].pitch; set.l0_stride = plan.pyr_stride;
+        return 0;
+    }
     // device-resident tight images (d_images = image 0); re-pitched only when 32-bit row loads would be misaligned
     int make_set(const uint8_t* d_images, int n, int w, int h, mcs::ImageSet& set, int img0 = 0, cudaStream_t st = nullptr) {
         if (!st) st = stream;
@@ -883,6 +933,12 @@ struct mcs_rig {
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
     size_t masks_bytes = 0;
+    // RECTIFY (setData :123-136): per-camera undistortion maps and the buffer the undistorted masks go to
+    uint2* d_und_maps = nullptr;
+    float* d_masks_und = nullptr;
+    size_t masks_und_bytes = 0;
+    bool undistort_on = false;
+    std::vector<mcs_calib> calib_host;
     // pinned host mirrors
     int *h_rows = nullptr, *h_row_count = nullptr, *h_lm_rows = nullptr, *h_n_views = nullptr, *h_rep = nullptr, *h_n_acc = nullptr,
         *h_match_tmp = nullptr;
@@ -910,7 +966,7 @@ struct mcs_rig {
         if (ev_begin) cudaEventDestroy(ev_begin);
         cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
         cudaFree(d_row_count); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
-        cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks);
+        cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks); cudaFree(d_und_maps); cudaFree(d_masks_und);
         cudaFreeHost(h_rows); cudaFreeHost(h_row_count); cudaFreeHost(h_lm_rows); cudaFreeHost(h_n_views); cudaFreeHost(h_rep);
         cudaFreeHost(h_n_acc); cudaFreeHost(h_match_tmp); cudaFreeHost(h_accepted); cudaFreeHost(h_xyz); cudaFreeHost(h_uv);
     }
@@ -918,6 +974,7 @@ struct mcs_rig {
     int init(const mcs_rig_config* c, const mcs_calib* cal) {
         cfg = *c;
         C = c->num_cams; F = c->max_frames;
+        calib_host.assign(cal, cal + std::max(C, 0));
         if (C < 1 || C > MCS_MAX_CAMS || F < 1) { set_err("num_cams must be in [1,8], max_frames >= 1"); return MCS_ERR_ARG; }
         int rc = eng.init(c->nfeatures, c->scale_factor, c->nlevels, c->ini_th_fast, c->min_th_fast, c->device, c->width, c->height, C * F);
         if (rc) return rc;
@@ -1108,6 +1165,42 @@ struct mcs_rig {
         CK(cudaMemcpyAsync(h_rep + o, lm.rep_cam + o, rw * sizeof(int), cudaMemcpyDeviceToHost, st));
         return 0;
     }
+    // RECTIFY: the segmentation masks are undistorted with the same maps (MultiCameraFrame.cpp:131-134); *dm is replaced
+    int undistort_masks(const float** dm, int n_frames) {
+        if (!undistort_on || !*dm) return 0;
+        const int w = cfg.width, h = cfg.height;
+        const size_t need = (size_t)n_frames * C * w * h * sizeof(float);
+        if (need > masks_und_bytes) {
+            CK(cudaStreamSynchronize(eng.stream));
+            cudaFree(d_masks_und);
+            d_masks_und = nullptr; masks_und_bytes = 0;
+            CK(cudaMalloc(&d_masks_und, (size_t)F * C * w * h * sizeof(float)));
+            masks_und_bytes = (size_t)F * C * w * h * sizeof(float);
+        }
+        dim3 b(32, 8), g((w + 31) / 32, (h + 7) / 8, n_frames * C);
+        mcs::undistort_f32_kernel<<<g, b, 0, eng.stream>>>(*dm, d_masks_und, d_und_maps, C, w, h);
+        CK(cudaGetLastError());
+        eng.launches++;
+        *dm = d_masks_und;
+        return 0;
+    }
+    // image set of the tight device images [img0, img0 + n) of `d_images` (image 0 = base), undistorted first when RECTIFY is on
+    int make_set(const uint8_t* d_images, int n, mcs::ImageSet& set, int img0, cudaStream_t st) {
+        if (undistort_on) return eng.make_set_undistorted(d_images, n, cfg.width, cfg.height, d_und_maps, C, set, img0, st);
+        return eng.make_set(d_images, n, cfg.width, cfg.height, set, img0, st);
+    }
+    int set_undistort(bool on) {
+        if (on && !d_und_maps) {
+            const size_t px = (size_t)cfg.width * cfg.height;
+            std::vector<uint2> maps(px * C);
+            for (int c = 0; c < C; c++) build_undistort_map(calib_host[c], cfg.width, cfg.height, maps.data() + px * c);
+            CK(cudaMalloc(&d_und_maps, maps.size() * sizeof(uint2)));
+            CK(cudaMemcpy(d_und_maps, maps.data(), maps.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+        }
+        undistort_on = on;
+        invalidate();
+        return 0;
+    }
     int upload_masks(const float* masks, int n_frames, const float** out) {
         *out = nullptr;
         if (!masks) return 0;
@@ -1166,6 +1259,7 @@ struct mcs_rig {
         const float* dm = d_masks_in;
         int rc;
         if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
+        if ((rc = undistort_masks(&dm, n_frames))) return rc;
         // host-buffer calls use half-size chunks: more copies in flight hide more of the PCIe time
         const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / 2) : chunk_frames;
         const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
@@ -1199,7 +1293,9 @@ struct mcs_rig {
                 rc = eng.stage_f32(S.d_f32, channels, nf * C, w, h, set, f0 * C, st);
             } else if (d_f32) rc = eng.stage_f32(d_f32 + (size_t)f0 * f32_frame, channels, nf * C, w, h, set, f0 * C, st);
             else if (h_images) rc = eng.upload(h_images + (size_t)f0 * C * w * h, nf * C, w, h, w, (size_t)w * h, set, f0 * C, st);
-            else rc = eng.make_set(d_images, nf * C, w, h, set, f0 * C, st);
+            else rc = make_set(d_images, nf * C, set, f0 * C, st);
+            if (!rc && undistort_on && (h_f32 || d_f32 || h_images))  // staged tight in d_input: undistort from there
+                rc = eng.make_set_undistorted(eng.d_input, nf * C, w, h, d_und_maps, C, set, f0 * C, st);
             if (rc) return rc;
             if ((rc = stage_extract(set, nf, f0, k))) return rc;
             // computeIntraMatches(matches_map, old): BruteForceMatch(i, j, 75, 0.85, ...) (MultiCameraFrame.cpp:1118)
@@ -1262,6 +1358,7 @@ int mcs_rig_extract(mcs_rig* rig, const uint8_t* images, int n_frames) {
     mcs::ImageSet set;
     const int w = rig->cfg.width, h = rig->cfg.height;
     int rc = rig->eng.upload(images, n_frames * rig->C, w, h, w, (size_t)w * h, set);
+    if (!rc && rig->undistort_on) rc = rig->eng.make_set_undistorted(rig->eng.d_input, n_frames * rig->C, w, h, rig->d_und_maps, rig->C, set, 0, rig->eng.stream);
     if (rc) return rc;
     return rig->stage_extract(set, n_frames);
 }
@@ -1271,7 +1368,7 @@ int mcs_rig_extract_device(mcs_rig* rig, const void* d_images, int n_frames) {
     if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
     rig->eng.begin_profile();
     mcs::ImageSet set;
-    int rc = rig->eng.make_set((const uint8_t*)d_images, n_frames * rig->C, rig->cfg.width, rig->cfg.height, set);
+    int rc = rig->make_set((const uint8_t*)d_images, n_frames * rig->C, set, 0, rig->eng.stream);
     if (rc) return rc;
     return rig->stage_extract(set, n_frames);
 }
@@ -1371,12 +1468,16 @@ int mcs_rig_triangulate(mcs_rig* rig, int n_frames, const float* masks) {
     RIG_ENTER(rig);
     const float* dm = nullptr;
     int rc = rig->upload_masks(masks, n_frames, &dm);
+    if (!rc) rc = rig->undistort_masks(&dm, n_frames);
     if (rc) return rc;
     return rig->stage_triangulate(n_frames, dm);
 }
 int mcs_rig_triangulate_device_masks(mcs_rig* rig, int n_frames, const void* d_masks) {
     RIG_ENTER(rig);
-    return rig->stage_triangulate(n_frames, (const float*)d_masks);
+    const float* dm = (const float*)d_masks;
+    int rc = rig->undistort_masks(&dm, n_frames);
+    if (rc) return rc;
+    return rig->stage_triangulate(n_frames, dm);
 }
 int mcs_rig_get_landmarks(mcs_rig* rig, int frame, mcs_landmarks* out, int capacity) {
     RIG_ENTER(rig);
@@ -1473,6 +1574,10 @@ int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int channels,
     rig->eng.begin_profile();
     return rig->process(nullptr, nullptr, nullptr, (const float*)d_masks, n_frames, old_epipolar ? 1 : 0, false, nullptr, (const float*)d_images,
                         channels);
+}
+int mcs_rig_set_undistort(mcs_rig* rig, int enable) {
+    RIG_ENTER(rig);
+    return rig->set_undistort(enable != 0);
 }
 int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames) {
     if (!rig || chunk_frames < 0) return MCS_ERR_ARG;

@@ -351,6 +351,10 @@ public:
         check(mcs_rig_process(h_, images, masks, n_frames, old ? 1 : 0), "mcs_rig_process");
     }
 
+    // camconfig_.RECTIFY (MultiCameraFrame.cpp:123-136, :241-243): cv::undistort of every image and segmentation mask entering the
+    // handle with the calibration's distortion coefficients; keypoints are then already undistorted (image_kps_undist = image_kps).
+    void setRectify(bool on) { check(mcs_rig_set_undistort(h_, on ? 1 : 0), "mcs_rig_set_undistort"); }
+
     // setData (MultiCameraFrame.cpp:95-152) + processFrame for the application's native CV_32F [0, 1] images (1 or 3 BGR channels,
     // [n_frames][num_cams][h][w][channels]): multiply by 255, convertTo(CV_8U), BGR2GRAY run on the device in front of the path.
     void process_frames_f32(const float* images, int channels, const float* masks, int n_frames, bool old = false) {

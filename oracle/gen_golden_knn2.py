@@ -172,3 +172,19 @@ def cv_set_data(img):
 
 np.savez_compressed(os.path.join(OUT, "set_data_f32.npz"), gray=gray, gray_u8=cv_set_data(gray), bgr=bgr, bgr_u8=cv_set_data(bgr))
 print("setData fixture", cv_set_data(gray).ravel()[:16])
+
+
+# ---- cv2.undistort (RECTIFY branch of setData, MultiCameraFrame.cpp:123-136) with two of the shipped calibrations' coefficient
+# sets scaled to a 320 x 240 image: strong barrel (nuance cam0) and a pincushion-like set that samples outside the source image.
+rng = np.random.default_rng(15)
+uw, uh = 320, 240
+uimg = cv2.GaussianBlur(rng.integers(0, 256, (uh, uw), dtype=np.uint8), (0, 0), 1.2)
+umask = np.kron(np.round(rng.random((uh // 8, uw // 8)), 1), np.ones((8, 8))).astype(np.float32)
+K1 = np.array([[203.8, 0, 163.2], [0, 203.2, 110.4], [0, 0, 1]], np.float64)
+d1 = np.array([-0.376399267634092, 0.2684942610034098, 0.001628309011323219, 0.0014062772667959773, 0.0])
+K2 = np.array([[311.2, 0, 157.8], [0, 311.0, 120.4], [0, 0, 1]], np.float64)
+d2 = np.array([0.12, 0.05, -0.0023147852033182366, 0.001098765060765587, -0.01])
+np.savez_compressed(os.path.join(OUT, "undistort_cv2.npz"), img=uimg, mask=umask, K1=K1, d1=d1, K2=K2, d2=d2,
+                    img_u1=cv2.undistort(uimg, K1, d1), img_u2=cv2.undistort(uimg, K2, d2),
+                    mask_u1=cv2.undistort(umask, K1, d1), mask_u2=cv2.undistort(umask, K2, d2))
+print("undistort fixture written")

@@ -59,6 +59,8 @@ def lib():
         L.orc_matches_dist_ratio.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 3
         L.orc_bow_matching.argtypes = [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 5
         L.orc_argsorte_desc.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_undistort_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_undistort_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_set_data_f32.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
@@ -318,6 +320,22 @@ def obtain_lf_features(kps, tri, total_feats=3000):
     order = argsorte_desc(resp)
     take = max(0, total_feats - len(accepted))
     return accepted, [mono[i] for i in order[:take]]
+
+
+def undistort(img, K, dist):
+    """cv::undistort(img, K, dist) as setData applies it for RECTIFY rigs (MultiCameraFrame.cpp:123-136); uint8 or float32 [h, w]."""
+    K = np.ascontiguousarray(K, np.float64).reshape(9)
+    d5 = np.zeros(5, np.float64)
+    d5[:len(np.ravel(dist))] = np.ravel(dist)[:5]
+    img = np.ascontiguousarray(img)
+    out = np.zeros_like(img)
+    h, w = img.shape
+    if img.dtype == np.uint8:
+        lib().orc_undistort_u8(_p(img), w, h, _p(K), _p(d5), _p(out))
+    else:
+        assert img.dtype == np.float32
+        lib().orc_undistort_f32(_p(img), w, h, _p(K), _p(d5), _p(out))
+    return out
 
 
 def _ptr_array(arrs):

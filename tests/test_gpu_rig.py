@@ -379,3 +379,71 @@ def test_merge_config4_capacity():
     rows, pc = O.intra_matches(D, K, calib, O.Extractor(4000).sigma2)
     got = rig.intra_matches(0)
     assert len(rows) > 4000 and got.shape == rows.shape and np.array_equal(got, rows)
+
+
+def test_undistort_rectify_branch(golden):
+    """mcs_rig_set_undistort (RECTIFY branch of setData, MultiCameraFrame.cpp:123-136): level 0 equals cv2.undistort (fixture) / the
+    oracle bit for bit, masks are undistorted with the same maps, and everything downstream equals the plain path fed with the
+    undistorted images and masks.  Host u8, host f32 and device entry points; 5 frames in chunks of 2."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from mcslam_b200 import binding as B
+    g = golden("undistort_cv2.npz")
+    for k in ("1", "2"):  # the cv2 fixture straight through the kernel: 1-camera rig
+        cal = M.synth.make_rig(1, 320, 240).copy()
+        cal["K"][0] = g["K" + k].reshape(9)
+        cal["dist"][0] = g["d" + k]
+        one = M.RigFrames(cal, 320, 240, nfeatures=100, max_frames=1)
+        one.set_undistort(True)
+        one.process(g["img"][None, None], masks=g["mask"][None, None])
+        assert np.array_equal(one.level(0, 0, 0), g["img_u" + k]), k
+    C, w, h, F = 3, 320, 240, 5
+    calib = M.synth.make_rig(C, w, h).copy()
+    dists = [[-0.28, 0.11, 0.0012, -0.0007, 0.0], [0.1, 0.04, -0.002, 0.001, -0.01], [0, 0, 0, 0, 0]]
+    for c in range(C):
+        calib["dist"][c] = dists[c]
+    frames = np.stack([M.synth.make_rig_frame(calib, w, h, frame_index=80 + i, n_rects=6) for i in range(F)])
+    masks = np.stack([M.synth.make_masks(C, w, h, frame_index=i) for i in range(F)])
+    und = np.stack([[O.undistort(frames[f, c], calib["K"][c], calib["dist"][c]) for c in range(C)] for f in range(F)])
+    und_m = np.stack([[O.undistort(masks[f, c], calib["K"][c], calib["dist"][c]) for c in range(C)] for f in range(F)])
+    assert np.array_equal(und[:, 2], frames[:, 2]), "zero distortion is the identity"
+    assert (und[:, 0] != frames[:, 0]).mean() > 0.3
+    rig = M.RigFrames(calib, w, h, nfeatures=300, max_frames=F)
+    rig.set_chunk_frames(4)
+    rig.process(und, masks=und_m)  # plain path on pre-undistorted inputs = the expectation
+    ref = [([rig.features(f, c) for c in range(C)], rig.intra_matches(f), rig.landmarks(f)) for f in range(F)]
+
+    def check():
+        for f in range(F):
+            for c in range(C):
+                assert np.array_equal(rig.level(f, c, 0), und[f, c]), (f, c)
+                k, d = rig.features(f, c)
+                assert (k == ref[f][0][c][0]).all() and np.array_equal(d, ref[f][0][c][1])
+            assert np.array_equal(rig.intra_matches(f), ref[f][1])
+            lm = rig.landmarks(f)
+            for key in lm:
+                assert np.array_equal(lm[key], ref[f][2][key]), key
+
+    rig.set_undistort(True)
+    rig.process(frames, masks=masks)
+    check()
+    rig.process(und)  # scramble the state
+    rig.set_undistort(True)
+    f32 = np.ascontiguousarray(frames.astype(np.float32) / np.float32(255.0))
+    rig.process_f32(f32, masks=masks)
+    check()
+    dptr, dm = B.device_malloc(0, frames.nbytes), B.device_malloc(0, masks.nbytes)
+    B.device_upload(0, dptr, frames)
+    B.device_upload(0, dm, masks)
+    rig.process_device(dptr, F, d_masks=dm)
+    rig.synchronize()
+    check()
+    rig.extract(frames)           # stage-wise entry points
+    rig.compute_intra_matches(F)
+    rig.triangulate(F, masks=masks)
+    check()
+    B.device_free(0, dptr)
+    B.device_free(0, dm)
+    rig.set_undistort(False)
+    rig.process(frames, masks=masks)
+    assert np.array_equal(rig.level(0, 0, 0), frames[0, 0])

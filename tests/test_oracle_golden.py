@@ -160,3 +160,14 @@ def test_set_data_f32_matches_cv2(golden):
     import oracle_lib as O
     g = golden("set_data_f32.npz")
     assert np.array_equal(O.set_data_f32(g["gray"]), g["gray_u8"]) and np.array_equal(O.set_data_f32(g["bgr"]), g["bgr_u8"])
+
+
+def test_undistort_matches_cv2(golden):
+    """oracle cv::undistort restatement (stripe-wise fixed-point maps + bilinear remap, BORDER_CONSTANT) == cv2.undistort bit for bit,
+    on u8 images and f32 masks, for a strong barrel calibration and one that samples outside the source image (k3 != 0)."""
+    import oracle_lib as O
+    g = golden("undistort_cv2.npz")
+    for k in ("1", "2"):
+        assert np.array_equal(O.undistort(g["img"], g["K" + k], g["d" + k]), g["img_u" + k])
+        assert np.array_equal(O.undistort(g["mask"], g["K" + k], g["d" + k]), g["mask_u" + k])
+    assert (g["img_u2"] == 0).sum() > 100, "the second calibration must exercise the constant border"
