@@ -200,6 +200,15 @@ MCS_API int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int c
  * to the extractor). */
 MCS_API int mcs_rig_set_undistort(mcs_rig* rig, int enable);
 
+/* RECTIFY = false branch of extractFeatureSingle (MultiCameraFrame.cpp:244-245): image_kps_undist = UndistortKeyPoints (:300-347) =
+ * cv::undistortPoints(image_kps, K, dist, noArray(), K) with K and dist narrowed to f32; cameras whose first coefficient reads as 0
+ * through the reference's `.at<float>(0)` on the CV_64F matrix (:302, i.e. the low 32 bits of the double are zero) are copied.  When
+ * enabled the undistorted keypoints feed what the reference feeds with image_kps_undist: the keypoints BruteForceMatch returns and the
+ * epipolar gate of computeIntraMatches(matches, old); triangulation keeps using image_kps (FrontEnd.cpp:265, :292-298). */
+MCS_API int mcs_rig_set_undistort_keypoints(mcs_rig* rig, int enable);
+/* image_kps_undist[cam] of frame `frame` (a copy of image_kps while the option above is off).  Returns the keypoint count. */
+MCS_API int mcs_rig_get_keypoints_undist(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, int capacity);
+
 /* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over four
  * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
 MCS_API int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames);

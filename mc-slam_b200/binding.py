@@ -38,7 +38,7 @@ EXPORTS = [
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
-    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort",
+    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist",
 ]
 
 
@@ -115,6 +115,8 @@ def lib():
     L.mcs_rig_knn2_images.argtypes = [vp, vp, vp, ci, vp]
     L.mcs_rig_set_features.argtypes = [vp, ci, vp, vp, vp]
     L.mcs_rig_set_undistort.argtypes = [vp, ci]
+    L.mcs_rig_set_undistort_keypoints.argtypes = [vp, ci]
+    L.mcs_rig_get_keypoints_undist.argtypes = [vp, ci, ci, vp, ci]
     L.mcs_rig_process_f32.argtypes = [vp, vp, ci, vp, ci, ci]
     L.mcs_rig_process_device_f32.argtypes = [vp, vp, ci, vp, ci, ci]
     L.mcs_match_subsets.argtypes = [vp, vp, ci, vp, ci, ci, vp, vp, vp, vp, ci, C.c_double, vp, vp, vp, vp]
@@ -287,6 +289,15 @@ class RigFrames:
     def set_undistort(self, on):
         """RECTIFY branch of setData: cv::undistort of images and masks with the calibration's distortion coefficients."""
         _check(lib().mcs_rig_set_undistort(self.hd, int(on)), "rig_set_undistort")
+
+    def set_undistort_keypoints(self, on):
+        """RECTIFY = false: image_kps_undist = cv::undistortPoints(image_kps) (UndistortKeyPoints, MultiCameraFrame.cpp:300-347)."""
+        _check(lib().mcs_rig_set_undistort_keypoints(self.hd, int(on)), "rig_set_undistort_keypoints")
+
+    def keypoints_undist(self, frame, cam):
+        k = np.zeros(self.kp_cap, KP_DTYPE)
+        n = _check(lib().mcs_rig_get_keypoints_undist(self.hd, frame, cam, _p(k), self.kp_cap), "rig_get_keypoints_undist")
+        return k[:n].copy()
 
     def set_features(self, kps, descs):
         """Features from elsewhere instead of stage A: kps / descs = per image (frame-major, camera-minor) KP_DTYPE / uint8 [n, 32]."""

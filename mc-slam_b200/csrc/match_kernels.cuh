@@ -219,6 +219,46 @@ __global__ void __launch_bounds__(128) subset_match_kernel(const uint8_t* __rest
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// MultiCameraFrame::UndistortKeyPoints (:300-347, the RECTIFY = false branch of extractFeatureSingle): image_kps_undist =
+// cv::undistortPoints(image_kps, K32, dist32, noArray(), K32) with K and the coefficients narrowed to f32 first (:318-322).  OpenCV's
+// undistortPoints: f64, 5 fixed-point iterations of the inverse radial-tangential model, re-projection through K, narrowed to f32.
+// A camera is copied unchanged when `dist_coeffs_[cam].at<float>(0) == 0.0` (:302) — the reference reads the first f64 coefficient
+// through a float pointer, i.e. it tests the LOW 32 bits of the double; `copy_cam` carries that decision from the host.
+// ------------------------------------------------------------------------------------------------------------
+struct UndistPtsCam {
+    double fx, fy, cx, cy;  // (double)(float)K
+    double k[5];            // (double)(float)dist: k1 k2 p1 p2 k3
+    int copy_cam, pad;
+};
+
+__global__ void __launch_bounds__(128) undistort_points_kernel(const KeypointPod* __restrict__ in, KeypointPod* __restrict__ out,
+                                                               const int* __restrict__ kp_count, int kp_cap,
+                                                               const UndistPtsCam* __restrict__ cams, int num_cams, int img0) {
+    const int img = blockIdx.y, q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= kp_count[img]) return;
+    const UndistPtsCam c = cams[(img0 + img) % num_cams];
+    KeypointPod p = in[(size_t)img * kp_cap + q];
+    if (!c.copy_cam) {
+        const double ifx = 1. / c.fx, ify = 1. / c.fy;
+        double x = ((double)p.x - c.cx) * ifx, y = ((double)p.y - c.cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int it = 0; it < 5; it++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((0 * r2 + 0) * r2 + 0) * r2) / (1 + ((c.k[4] * r2 + c.k[1]) * r2 + c.k[0]) * r2);
+            if (icdist < 0) { x = x0; y = y0; break; }
+            const double dX = 2 * c.k[2] * x * y + c.k[3] * (r2 + 2 * x * x) + 0 * r2 + 0 * r2 * r2;
+            const double dY = c.k[2] * (r2 + 2 * y * y) + 2 * c.k[3] * x * y + 0 * r2 + 0 * r2 * r2;
+            x = (x0 - dX) * icdist;
+            y = (y0 - dY) * icdist;
+        }
+        const double xx = c.fx * x + 0 * y + c.cx, yy = 0 * x + c.fy * y + c.cy, ww = 1. / (0 * x + 0 * y + 1.0);
+        p.x = (float)(xx * ww);
+        p.y = (float)(yy * ww);
+    }
+    out[(size_t)img * kp_cap + q] = p;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K7  merge: computeIntraMatches(matches, old) after the pair matcher (:1222-1266).  The reference walks the matches of the pairs
 // in order and mutates match_inv_idx / the row table as it goes, so later matches and later pairs see earlier state.  Pairs stay
 // sequential (one block per frame walks them), but inside one pair (i, j) the walk decomposes:

@@ -938,6 +938,11 @@ struct mcs_rig {
     float* d_masks_und = nullptr;
     size_t masks_und_bytes = 0;
     bool undistort_on = false;
+    // RECTIFY = false with distorted lenses: image_kps_undist on the device (UndistortKeyPoints, MultiCameraFrame.cpp:300-347)
+    bool undist_pts_on = false;
+    mcs::KeypointPod *d_kps_undist = nullptr, *h_kps_undist = nullptr;
+    mcs::UndistPtsCam* d_undist_cams = nullptr;
+    bool kps_undist_host = false;
     std::vector<mcs_calib> calib_host;
     // pinned host mirrors
     int *h_rows = nullptr, *h_row_count = nullptr, *h_lm_rows = nullptr, *h_n_views = nullptr, *h_rep = nullptr, *h_n_acc = nullptr,
@@ -966,7 +971,7 @@ struct mcs_rig {
         if (ev_begin) cudaEventDestroy(ev_begin);
         cudaFree(d_calib); cudaFree(d_F); cudaFree(d_sigma2); cudaFree(d_match_train); cudaFree(d_match_tmp); cudaFree(d_rows);
         cudaFree(d_row_count); cudaFree(lm.rows); cudaFree(lm.accepted); cudaFree(lm.n_views); cudaFree(lm.xyz); cudaFree(lm.uv_ref);
-        cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks); cudaFree(d_und_maps); cudaFree(d_masks_und);
+        cudaFree(lm.rep_cam); cudaFree(lm.n_accepted); cudaFree(d_masks); cudaFree(d_und_maps); cudaFree(d_masks_und); cudaFree(d_kps_undist); cudaFree(d_undist_cams); cudaFreeHost(h_kps_undist);
         cudaFreeHost(h_rows); cudaFreeHost(h_row_count); cudaFreeHost(h_lm_rows); cudaFreeHost(h_n_views); cudaFreeHost(h_rep);
         cudaFreeHost(h_n_acc); cudaFreeHost(h_match_tmp); cudaFreeHost(h_accepted); cudaFreeHost(h_xyz); cudaFreeHost(h_uv);
     }
@@ -1066,7 +1071,7 @@ struct mcs_rig {
         CK(cudaFuncSetAttribute(mcs::tri_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem(MCS_MAX_CAMS)));
         return 0;
     }
-    void invalidate() { feat_host = rows_host = lm_host = false; }
+    void invalidate() { feat_host = rows_host = lm_host = kps_undist_host = false; }
 
     // The three stages for frames [f0, f0 + nf) of the workspace on slot `k` (0 = main stream).  Every kernel indexes frames
     // relative to the pointers it is given, so a chunk is the same launch with offset pointers.
@@ -1077,6 +1082,51 @@ struct mcs_rig {
         n_extracted = f0 == 0 ? n_frames : std::max(n_extracted, f0 + n_frames);
         if (f0 == 0) n_matched = n_triangulated = 0;
         invalidate();
+        return undistort_keypoints(n_frames, f0, slots[k].st);
+    }
+    // image_kps_undist of the frames [f0, f0 + n_frames)
+    int undistort_keypoints(int n_frames, int f0, cudaStream_t st) {
+        if (!undist_pts_on) return 0;
+        dim3 g((kp_cap + 127) / 128, n_frames * C);
+        mcs::undistort_points_kernel<<<g, 128, 0, st>>>(eng.d_kps + (size_t)f0 * C * kp_cap, d_kps_undist + (size_t)f0 * C * kp_cap,
+                                                        eng.d_kp_count + (size_t)f0 * C, kp_cap, d_undist_cams, C, f0 * C);
+        CK(cudaGetLastError());
+        eng.launches++;
+        kps_undist_host = false;
+        return 0;
+    }
+    const mcs::KeypointPod* kps_undist_dev() const { return undist_pts_on ? d_kps_undist : eng.d_kps; }
+    int set_undistort_keypoints(bool on) {
+        if (on && !d_kps_undist) {
+            std::vector<mcs::UndistPtsCam> cams(C);
+            for (int c = 0; c < C; c++) {
+                const mcs_calib& k = calib_host[c];
+                mcs::UndistPtsCam u{};
+                u.fx = (double)(float)k.K[0]; u.fy = (double)(float)k.K[4]; u.cx = (double)(float)k.K[2]; u.cy = (double)(float)k.K[5];
+                for (int i = 0; i < 5; i++) u.k[i] = (double)(float)k.dist[i];
+                uint64_t bits;
+                memcpy(&bits, &k.dist[0], 8);
+                float lo;
+                const uint32_t lo_bits = (uint32_t)bits;  // `.at<float>(0)` of a CV_64F matrix (:302)
+                memcpy(&lo, &lo_bits, 4);
+                u.copy_cam = lo == 0.0f ? 1 : 0;
+                cams[c] = u;
+            }
+            CK(cudaMalloc(&d_undist_cams, sizeof(mcs::UndistPtsCam) * C));
+            CK(cudaMemcpy(d_undist_cams, cams.data(), sizeof(mcs::UndistPtsCam) * C, cudaMemcpyHostToDevice));
+            CK(cudaMalloc(&d_kps_undist, (size_t)F * C * kp_cap * sizeof(mcs::KeypointPod)));
+            CK(cudaMallocHost(&h_kps_undist, (size_t)F * C * kp_cap * sizeof(mcs::KeypointPod)));
+        }
+        undist_pts_on = on;
+        kps_undist_host = false;
+        return 0;
+    }
+    int ensure_kps_undist() {
+        if (!undist_pts_on || kps_undist_host) return 0;
+        if (n_extracted < 1) { set_err("no extracted frames"); return MCS_ERR_STATE; }
+        CK(cudaMemcpyAsync(h_kps_undist, d_kps_undist, (size_t)n_extracted * C * kp_cap * sizeof(mcs::KeypointPod), cudaMemcpyDeviceToHost, eng.stream));
+        CK(cudaStreamSynchronize(eng.stream));
+        kps_undist_host = true;
         return 0;
     }
     int stage_match(int n_frames, int old, float dist_thresh, float ratio, int f0 = 0, int k = 0) {
@@ -1093,7 +1143,7 @@ struct mcs_rig {
         }
         eng.mark(ST_MERGE);
         mcs::merge_kernel<<<n_frames, MCS_MERGE_NT, merge_smem, st>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
-                                                             eng.d_kps + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
+                                                             kps_undist_dev() + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
                                                              d_rows + (size_t)f0 * row_cap * C, d_row_count + f0, merge_rows_smem ? 1 : 0);
         eng.launches++;
         eng.mark(ST_TRIANG);
@@ -1409,7 +1459,7 @@ int mcs_rig_set_features(mcs_rig* rig, int n_frames, const int* counts, const mc
     rig->n_matched = rig->n_triangulated = 0;
     rig->eng.last_n = n_img;
     rig->invalidate();
-    return 0;
+    return rig->undistort_keypoints(n_frames, 0, st);
 }
 
 int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float dist_thresh, float neigh_ratio, uint32_t* indices_1,
@@ -1431,7 +1481,9 @@ int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float
     CK(cudaMemcpyAsync(rig->h_match_tmp, rig->d_match_tmp, (size_t)cap * 3 * sizeof(int), cudaMemcpyDeviceToHost, rig->eng.stream));
     CK(cudaStreamSynchronize(rig->eng.stream));
     int rc = rig->ensure_features();
+    if (!rc) rc = rig->ensure_kps_undist();
     if (rc) return rc;
+    const mcs::KeypointPod* hk = rig->undist_pts_on ? rig->h_kps_undist : rig->eng.h_kps;
     const int ia = frame * rig->C + cam1, ib = frame * rig->C + cam2;
     const int nq = rig->eng.h_kp_count[ia];
     int n = 0;
@@ -1442,8 +1494,8 @@ int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float
         if (indices_1) indices_1[n] = (uint32_t)q;
         if (indices_2) indices_2[n] = (uint32_t)t;
         // kps come from image_kps_undist; with zero distortion that is a copy of image_kps (MultiCameraFrame.cpp:302-305)
-        if (kps1) memcpy(&kps1[n], rig->eng.h_kps + (size_t)ia * cap + q, sizeof(mcs_keypoint));
-        if (kps2) memcpy(&kps2[n], rig->eng.h_kps + (size_t)ib * cap + t, sizeof(mcs_keypoint));
+        if (kps1) memcpy(&kps1[n], hk + (size_t)ia * cap + q, sizeof(mcs_keypoint));
+        if (kps2) memcpy(&kps2[n], hk + (size_t)ib * cap + t, sizeof(mcs_keypoint));
         n++;
     }
     return n;
@@ -1578,6 +1630,22 @@ int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int channels,
 int mcs_rig_set_undistort(mcs_rig* rig, int enable) {
     RIG_ENTER(rig);
     return rig->set_undistort(enable != 0);
+}
+int mcs_rig_set_undistort_keypoints(mcs_rig* rig, int enable) {
+    RIG_ENTER(rig);
+    return rig->set_undistort_keypoints(enable != 0);
+}
+int mcs_rig_get_keypoints_undist(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, int capacity) {
+    RIG_ENTER(rig);
+    if (frame < 0 || frame >= rig->n_extracted || cam < 0 || cam >= rig->C || !keypoints) return MCS_ERR_ARG;
+    int rc = rig->ensure_features();
+    if (!rc) rc = rig->ensure_kps_undist();
+    if (rc) return rc;
+    const int img = frame * rig->C + cam, n = rig->eng.h_kp_count[img];
+    if (n > capacity) { set_err("keypoint capacity too small"); return MCS_ERR_CAPACITY; }
+    const mcs::KeypointPod* hk = rig->undist_pts_on ? rig->h_kps_undist : rig->eng.h_kps;
+    memcpy(keypoints, hk + (size_t)img * rig->kp_cap, (size_t)n * sizeof(mcs_keypoint));
+    return n;
 }
 int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames) {
     if (!rig || chunk_frames < 0) return MCS_ERR_ARG;

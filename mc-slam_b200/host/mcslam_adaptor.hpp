@@ -186,7 +186,8 @@ public:
             check(n, "mcs_rig_get_features");
             image_kps[c].resize(n);
             image_descriptors[c].resize((size_t)n * 32);
-            image_kps_undist[c] = image_kps[c];
+            image_kps_undist[c].resize(n);  // UndistortKeyPoints (:300-347) when setUndistortKeypoints(true), else the copy of :241-243 / :302-305
+            if (n) check(mcs_rig_get_keypoints_undist(h_, 0, c, image_kps_undist[c].data(), n), "mcs_rig_get_keypoints_undist");
         }
     }
     void extractFeatures() { extractFeaturesParallel(); }  // :266-298, same results without the thread fan-out
@@ -354,6 +355,8 @@ public:
     // camconfig_.RECTIFY (MultiCameraFrame.cpp:123-136, :241-243): cv::undistort of every image and segmentation mask entering the
     // handle with the calibration's distortion coefficients; keypoints are then already undistorted (image_kps_undist = image_kps).
     void setRectify(bool on) { check(mcs_rig_set_undistort(h_, on ? 1 : 0), "mcs_rig_set_undistort"); }
+    // RECTIFY = false with distorted lenses: image_kps_undist = cv::undistortPoints(image_kps) (UndistortKeyPoints, :300-347)
+    void setUndistortKeypoints(bool on) { check(mcs_rig_set_undistort_keypoints(h_, on ? 1 : 0), "mcs_rig_set_undistort_keypoints"); }
 
     // setData (MultiCameraFrame.cpp:95-152) + processFrame for the application's native CV_32F [0, 1] images (1 or 3 BGR channels,
     // [n_frames][num_cams][h][w][channels]): multiply by 255, convertTo(CV_8U), BGR2GRAY run on the device in front of the path.

@@ -188,3 +188,14 @@ np.savez_compressed(os.path.join(OUT, "undistort_cv2.npz"), img=uimg, mask=umask
                     img_u1=cv2.undistort(uimg, K1, d1), img_u2=cv2.undistort(uimg, K2, d2),
                     mask_u1=cv2.undistort(umask, K1, d1), mask_u2=cv2.undistort(umask, K2, d2))
 print("undistort fixture written")
+
+
+# ---- cv2.undistortPoints as UndistortKeyPoints calls it (MultiCameraFrame.cpp:318-334): K and dist narrowed to f32, P = K
+rng = np.random.default_rng(16)
+upts = (rng.random((1500, 2)) * [uw, uh]).astype(np.float32)
+und_pts = {}
+for name, Kx, dx in (("1", K1, d1), ("2", K2, d2)):
+    K32, d32 = Kx.astype(np.float32), dx.astype(np.float32).reshape(1, -1)
+    und_pts[name] = cv2.undistortPoints(upts.reshape(-1, 1, 2).copy(), K32, d32, None, K32).reshape(-1, 2)
+np.savez_compressed(os.path.join(OUT, "undistort_points_cv2.npz"), pts=upts, K1=K1, d1=d1, K2=K2, d2=d2, out1=und_pts["1"], out2=und_pts["2"])
+print("undistortPoints fixture written")

@@ -61,6 +61,7 @@ def lib():
         L.orc_argsorte_desc.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.orc_undistort_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_undistort_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_set_data_f32.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
@@ -335,6 +336,17 @@ def undistort(img, K, dist):
     else:
         assert img.dtype == np.float32
         lib().orc_undistort_f32(_p(img), w, h, _p(K), _p(d5), _p(out))
+    return out
+
+
+def undistort_keypoints(kps, K, dist):
+    """UndistortKeyPoints (MultiCameraFrame.cpp:300-347): KP_DTYPE array with pt replaced by cv::undistortPoints(pt, K32, dist32, P=K32)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    K = np.ascontiguousarray(K, np.float64).reshape(9)
+    d5 = np.zeros(5, np.float64)
+    d5[:len(np.ravel(dist))] = np.ravel(dist)[:5]
+    out = np.zeros_like(kps)
+    lib().orc_undistort_keypoints(_p(kps), len(kps), _p(K), _p(d5), _p(out))
     return out
 
 

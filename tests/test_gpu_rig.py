@@ -447,3 +447,55 @@ def test_undistort_rectify_branch(golden):
     rig.set_undistort(False)
     rig.process(frames, masks=masks)
     assert np.array_equal(rig.level(0, 0, 0), frames[0, 0])
+
+
+@pytest.mark.parametrize("old", [False, True])
+def test_undistort_keypoints_branch(golden, old):
+    """mcs_rig_set_undistort_keypoints (RECTIFY = false, UndistortKeyPoints MultiCameraFrame.cpp:300-347): image_kps_undist equals
+    cv2.undistortPoints (fixture, through set_features) / the oracle bit for bit; BruteForceMatch returns the undistorted keypoints,
+    the `old` epipolar gate runs on them, triangulation keeps the distorted ones."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    g = golden("undistort_points_cv2.npz")
+    for k in ("1", "2"):
+        cal = M.synth.make_rig(1, 320, 240).copy()
+        cal["K"][0], cal["dist"][0] = g["K" + k].reshape(9), g["d" + k]
+        one = M.RigFrames(cal, 320, 240, nfeatures=2000, max_frames=1)
+        one.set_undistort_keypoints(True)
+        n = min(len(g["pts"]), one.kp_cap)
+        kp = np.zeros(n, M.KP_DTYPE)
+        kp["x"], kp["y"] = g["pts"][:n, 0], g["pts"][:n, 1]
+        one.set_features([kp], [np.zeros((n, 32), np.uint8)])
+        u = one.keypoints_undist(0, 0)
+        assert np.array_equal(u["x"], g["out" + k][:n, 0]) and np.array_equal(u["y"], g["out" + k][:n, 1])
+    C, w, h = 3, 320, 240
+    calib = M.synth.make_rig(C, w, h).copy()
+    dists = [[-0.28, 0.11, 0.0012, -0.0007, 0.0], [0.5, 0.04, -0.002, 0.001, 0.0], [0.05, -0.01, 0.001, 0.0005, 0.002]]
+    for c in range(C):
+        calib["dist"][c] = dists[c]
+    frames = np.stack([M.synth.make_rig_frame(calib, w, h, frame_index=90 + i, n_rects=6) for i in range(2)])
+    rig = M.RigFrames(calib, w, h, nfeatures=300, max_frames=2)
+    rig.set_undistort_keypoints(True)
+    rig.process(frames, old=old)
+    ex = O.Extractor(300)
+    for f in range(2):
+        K, D = [], []
+        for c in range(C):
+            _, k, d = O.Extractor(300)(frames[f, c])
+            K.append(k)
+            D.append(d)
+        KU = [O.undistort_keypoints(K[c], calib["K"][c], calib["dist"][c]) for c in range(C)]
+        assert np.array_equal(KU[1], K[1]), "0.5 reads as zero through the reference's float access: copied"
+        assert (KU[0]["x"] != K[0]["x"]).any()
+        for c in range(C):
+            k, _ = rig.features(f, c)
+            assert (k == K[c]).all() and (rig.keypoints_undist(f, c) == KU[c]).all()
+        rows, _ = O.intra_matches(D, KU, calib, ex.sigma2, use_epipolar=old)
+        assert np.array_equal(rig.intra_matches(f), rows)
+        tri = O.triangulate_rows(calib, K, D, rows)
+        lm = rig.landmarks(f)
+        assert np.array_equal(lm["status"], tri["status"])
+        ok = tri["nviews"] >= 2
+        assert np.allclose(lm["xyz"][ok], tri["xyz"][ok], rtol=1e-6, atol=1e-9)
+        i1, i2, k1, k2 = rig.brute_force_match(f, 0, 2)
+        assert len(i1) > 5 and (k1 == KU[0][i1]).all() and (k2 == KU[2][i2]).all()

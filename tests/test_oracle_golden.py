@@ -171,3 +171,17 @@ def test_undistort_matches_cv2(golden):
         assert np.array_equal(O.undistort(g["img"], g["K" + k], g["d" + k]), g["img_u" + k])
         assert np.array_equal(O.undistort(g["mask"], g["K" + k], g["d" + k]), g["mask_u" + k])
     assert (g["img_u2"] == 0).sum() > 100, "the second calibration must exercise the constant border"
+
+
+def test_undistort_keypoints_matches_cv2(golden):
+    """oracle UndistortKeyPoints == cv2.undistortPoints(pts, K32, dist32, P=K32) bit for bit; the reference's float read of the f64
+    coefficient (MultiCameraFrame.cpp:302) makes 0.5 count as 'no distortion'."""
+    import oracle_lib as O
+    g = golden("undistort_points_cv2.npz")
+    kp = np.zeros(len(g["pts"]), O.KP_DTYPE)
+    kp["x"], kp["y"] = g["pts"][:, 0], g["pts"][:, 1]
+    for k in ("1", "2"):
+        o = O.undistort_keypoints(kp, g["K" + k], g["d" + k])
+        assert np.array_equal(o["x"], g["out" + k][:, 0]) and np.array_equal(o["y"], g["out" + k][:, 1])
+    assert np.array_equal(O.undistort_keypoints(kp, g["K1"], [0.5, 0.1, 0, 0, 0]), kp)
+    assert np.array_equal(O.undistort_keypoints(kp, g["K1"], [0, 0.1, 0, 0, 0]), kp)
