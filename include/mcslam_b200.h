@@ -268,6 +268,26 @@ MCS_API int mcs_match_subsets(mcs_matcher* m, const uint8_t* descA, int nA, cons
  * batch.  out_knn: [n_sets][feature_capacity][4]; rows past the query image's keypoint count stay -1. */
 MCS_API int mcs_rig_knn2_images(mcs_rig* rig, const int* q_image, const int* t_image, int n_sets, int32_t* out_knn);
 
+/* ---- DBoW2 vocabulary transform ---------------------------------------------------------------------------------
+ * DBoW2 (ORB-SLAM2 fork with loadFromTextFile) is an external, un-vendored dependency of the reference; the front-end calls
+ * orb_vocabulary->loadFromTextFile(voc_file) (MCSlam/include/MCSlam/FrontEnd.h:137-138) and orb_vocabulary->transform(vec_desc, bowVec,
+ * featVec, 4) (MCSlam/src/MultiCameraFrame.cpp:257, MCSlam/src/FrontEnd.cpp:533).  TemplatedVocabulary::transform per feature: descend
+ * from the root to the Hamming-nearest child (first child wins ties) down to a leaf; word id and weight are the leaf's, node id the
+ * node passed at level L - levelsup.  A feature enters the FeatureVector under its node id when its weight is > 0. */
+typedef struct mcs_vocab mcs_vocab;
+/* Text format: first line "k L scoring weighting", then one line per node 1..n: "parent is_leaf d0 ... d31 weight". */
+MCS_API mcs_vocab* mcs_vocab_load_text(const char* path, int device);
+/* The same from arrays (node i + 1 of the file = entry i). */
+MCS_API mcs_vocab* mcs_vocab_create(int device, int k, int L, int scoring, int weighting, int n_nodes, const int* parent, const int* is_leaf,
+                                    const uint8_t* descriptors /*[n_nodes][32]*/, const double* weights);
+MCS_API void mcs_vocab_destroy(mcs_vocab* v);
+MCS_API int mcs_vocab_info(const mcs_vocab* v, int* k, int* L, int* n_nodes /* incl. root */, int* n_words);
+MCS_API int mcs_vocab_transform(mcs_vocab* v, const uint8_t* descriptors, int n, int levelsup, int32_t* word_id, int32_t* node_id,
+                                double* weight /* may be NULL */);
+/* For every image of the last batch of a rig handle, on the resident descriptors: outputs [n_frames * num_cams][feature_capacity]
+ * (-1 / 0 past an image's keypoint count). */
+MCS_API int mcs_rig_vocab_transform(mcs_rig* rig, mcs_vocab* v, int levelsup, int32_t* word_id, int32_t* node_id, double* weight);
+
 /* Plain device-memory helpers so harnesses written without a CUDA binding can stage resident inputs. */
 MCS_API void* mcs_device_malloc(int device, size_t bytes);
 MCS_API void mcs_device_free(int device, void* p);

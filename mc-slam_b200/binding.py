@@ -38,7 +38,8 @@ EXPORTS = [
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
-    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist",
+    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
+    "mcs_vocab_transform", "mcs_rig_vocab_transform",
 ]
 
 
@@ -115,6 +116,14 @@ def lib():
     L.mcs_rig_knn2_images.argtypes = [vp, vp, vp, ci, vp]
     L.mcs_rig_set_features.argtypes = [vp, ci, vp, vp, vp]
     L.mcs_rig_set_undistort.argtypes = [vp, ci]
+    L.mcs_vocab_load_text.restype = vp
+    L.mcs_vocab_load_text.argtypes = [C.c_char_p, ci]
+    L.mcs_vocab_create.restype = vp
+    L.mcs_vocab_create.argtypes = [ci, ci, ci, ci, ci, ci, vp, vp, vp, vp]
+    L.mcs_vocab_destroy.argtypes = [vp]
+    L.mcs_vocab_info.argtypes = [vp, vp, vp, vp, vp]
+    L.mcs_vocab_transform.argtypes = [vp, vp, ci, ci, vp, vp, vp]
+    L.mcs_rig_vocab_transform.argtypes = [vp, vp, ci, vp, vp, vp]
     L.mcs_rig_set_undistort_keypoints.argtypes = [vp, ci]
     L.mcs_rig_get_keypoints_undist.argtypes = [vp, ci, ci, vp, ci]
     L.mcs_rig_process_f32.argtypes = [vp, vp, ci, vp, ci, ci]
@@ -524,6 +533,47 @@ class Matcher:
     @property
     def kernel_launches(self):
         return int(lib().mcs_matcher_kernel_launches(self.hd))
+
+
+class Vocabulary:
+    """DBoW2 vocabulary (loadFromTextFile format, FrontEnd.h:137-138) and its transform (MultiCameraFrame.cpp:257)."""
+
+    def __init__(self, path=None, device=0, k=10, L=None, parent=None, is_leaf=None, node_desc=None, weight=None):
+        if path is not None:
+            self.hd = lib().mcs_vocab_load_text(str(path).encode(), device)
+        else:
+            parent = np.ascontiguousarray(parent, np.int32)
+            is_leaf = np.ascontiguousarray(is_leaf, np.int32)
+            node_desc = np.ascontiguousarray(node_desc, np.uint8).reshape(-1, 32)
+            weight = np.ascontiguousarray(weight, np.float64)
+            self.hd = lib().mcs_vocab_create(device, k, L, 0, 0, len(parent), _p(parent), _p(is_leaf), _p(node_desc), _p(weight))
+        if not self.hd:
+            raise McsError("vocabulary: " + lib().mcs_last_error().decode())
+        v = [C.c_int() for _ in range(4)]
+        _check(lib().mcs_vocab_info(self.hd, *[C.byref(x) for x in v]), "vocab_info")
+        self.k, self.L, self.n_nodes, self.n_words = [x.value for x in v]
+
+    def close(self):
+        if getattr(self, "hd", None):
+            lib().mcs_vocab_destroy(self.hd)
+            self.hd = None
+
+    __del__ = close
+
+    def transform(self, feats, levelsup=4):
+        feats = np.ascontiguousarray(feats, np.uint8).reshape(-1, 32)
+        n = len(feats)
+        wid, nid, w = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        _check(lib().mcs_vocab_transform(self.hd, _p(feats), n, levelsup, _p(wid), _p(nid), _p(w)), "vocab_transform")
+        return wid[:n], nid[:n], w[:n]
+
+    def transform_rig(self, rig, levelsup=4):
+        """Every image of the rig's last batch on the resident descriptors: arrays [n_images, kp_cap]."""
+        n_img = rig.C * rig.F
+        shape = (n_img, rig.kp_cap)
+        wid, nid, w = np.full(shape, -1, np.int32), np.full(shape, -1, np.int32), np.zeros(shape, np.float64)
+        _check(lib().mcs_rig_vocab_transform(rig.hd, self.hd, levelsup, _p(wid), _p(nid), _p(w)), "rig_vocab_transform")
+        return wid, nid, w
 
 
 def device_malloc(device, nbytes):

@@ -259,6 +259,49 @@ __global__ void __launch_bounds__(128) undistort_points_kernel(const KeypointPod
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// DBoW2 vocabulary transform (external dependency of the reference, not vendored: DBoW2 as forked for ORB-SLAM2 with
+// loadFromTextFile; called as orb_vocabulary->transform(vec_desc, bowVec, featVec, 4) at MultiCameraFrame.cpp:257 and
+// FrontEnd.cpp:533).  TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup): from the root, at every level move
+// to the child whose descriptor is nearest in Hamming distance (first child wins ties, strict '<'), remember the node reached at
+// level L - levelsup, stop at a leaf; word id / weight are the leaf's.  One thread per feature; children are stored contiguously.
+// ------------------------------------------------------------------------------------------------------------
+struct VocabNode {
+    int child_begin, child_count;  // children are nodes [child_begin, child_begin + child_count) of the reordered table
+    int word_id;                   // >= 0 for leaves
+    int orig_id;                   // node id in the file's numbering (what FeatureVector keys use)
+};
+
+__global__ void __launch_bounds__(128) vocab_transform_kernel(const VocabNode* __restrict__ nodes, const uint4* __restrict__ node_desc,
+                                                              const double* __restrict__ node_weight, int L, int levelsup,
+                                                              const uint8_t* __restrict__ desc, const int* __restrict__ counts, int stride,
+                                                              int* __restrict__ word_id, int* __restrict__ node_id,
+                                                              double* __restrict__ weight) {
+    const int set = blockIdx.y, q = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = counts ? counts[set] : stride;
+    if (q >= n) return;
+    const size_t o = (size_t)set * stride + q;
+    const uint4* f = reinterpret_cast<const uint4*>(desc + o * 32);
+    const uint4 f0 = __ldg(f), f1 = __ldg(f + 1);
+    const int nid_level = L - levelsup;
+    int cur = 0, level = 0, nid = 0;
+    do {
+        level++;
+        const VocabNode nd = nodes[cur];
+        int best = nd.child_begin, best_d = 1 << 30;
+        for (int c = 0; c < nd.child_count; c++) {
+            const int id = nd.child_begin + c;
+            const int d = hamming256(f0, f1, __ldg(node_desc + 2 * id), __ldg(node_desc + 2 * id + 1));
+            if (d < best_d) { best_d = d; best = id; }
+        }
+        cur = best;
+        if (level == nid_level) nid = nodes[cur].orig_id;
+    } while (nodes[cur].child_count > 0);
+    word_id[o] = nodes[cur].word_id;
+    node_id[o] = nid_level <= 0 ? 0 : nid;
+    weight[o] = node_weight[cur];
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K7  merge: computeIntraMatches(matches, old) after the pair matcher (:1222-1266).  The reference walks the matches of the pairs
 // in order and mutates match_inv_idx / the row table as it goes, so later matches and later pairs see earlier state.  Pairs stay
 // sequential (one block per frame walks them), but inside one pair (i, j) the walk decomposes:

@@ -1938,3 +1938,178 @@ int mcs_rig_knn2_images(mcs_rig* rig, const int* q_image, const int* t_image, in
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// DBoW2 vocabulary (text format of the ORB-SLAM2 fork's loadFromTextFile, FrontEnd.h:138) + transform.
+// ------------------------------------------------------------------------------------------------------------
+struct mcs_vocab {
+    int device = 0, k = 0, L = 0, scoring = 0, weighting = 0, n_nodes = 0, n_words = 0;
+    cudaStream_t stream = nullptr;
+    mcs::VocabNode* d_nodes = nullptr;
+    uint4* d_desc = nullptr;
+    double* d_weight = nullptr;
+    // workspace of mcs_vocab_transform
+    uint8_t* d_in = nullptr;
+    int *d_word = nullptr, *d_node = nullptr;
+    double* d_w = nullptr;
+    size_t cap = 0;
+    ~mcs_vocab() {
+        if (cudaSetDevice(device) != cudaSuccess) return;
+        if (stream) cudaStreamDestroy(stream);
+        cudaFree(d_nodes); cudaFree(d_desc); cudaFree(d_weight); cudaFree(d_in); cudaFree(d_word); cudaFree(d_node); cudaFree(d_w);
+    }
+    // parent[n], is_leaf[n], desc[n][32], weight[n] for the nodes 1..n of the file (node 0 is the root)
+    int build(int n, const int* parent, const int* is_leaf, const uint8_t* desc, const double* weight) {
+        n_nodes = n + 1;
+        std::vector<std::vector<int>> children(n_nodes);
+        std::vector<int> word(n_nodes, -1);
+        n_words = 0;
+        for (int i = 1; i <= n; i++) {
+            const int p = parent[i - 1];
+            if (p < 0 || p >= i) { set_err("vocabulary: parent id must precede the node"); return MCS_ERR_ARG; }
+            children[p].push_back(i);  // file order = DBoW2's children order
+            if (is_leaf[i - 1] > 0) word[i] = n_words++;
+        }
+        // breadth-first renumbering so that every node's children are contiguous
+        std::vector<int> order(1, 0), new_id(n_nodes, -1);
+        new_id[0] = 0;
+        for (size_t h = 0; h < order.size(); h++)
+            for (int c : children[order[h]]) { new_id[c] = (int)order.size(); order.push_back(c); }
+        if ((int)order.size() != n_nodes) { set_err("vocabulary: unreachable nodes"); return MCS_ERR_ARG; }
+        std::vector<mcs::VocabNode> nodes(n_nodes);
+        std::vector<uint8_t> nd((size_t)n_nodes * 32, 0);
+        std::vector<double> nw(n_nodes, 0.0);
+        for (int t = 0; t < n_nodes; t++) {
+            const int o = order[t];
+            nodes[t].child_count = (int)children[o].size();
+            nodes[t].child_begin = nodes[t].child_count ? new_id[children[o][0]] : 0;
+            nodes[t].word_id = word[o];
+            nodes[t].orig_id = o;
+            if (o > 0) { memcpy(&nd[(size_t)t * 32], desc + (size_t)(o - 1) * 32, 32); nw[t] = weight[o - 1]; }
+            if (nodes[t].child_count == 0 && word[o] < 0 && n > 0) { set_err("vocabulary: inner node without children"); return MCS_ERR_ARG; }
+        }
+        CK(cudaSetDevice(device));
+        CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        CK(cudaMalloc(&d_nodes, nodes.size() * sizeof(mcs::VocabNode)));
+        CK(cudaMalloc(&d_desc, nd.size()));
+        CK(cudaMalloc(&d_weight, nw.size() * sizeof(double)));
+        CK(cudaMemcpy(d_nodes, nodes.data(), nodes.size() * sizeof(mcs::VocabNode), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_desc, nd.data(), nd.size(), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_weight, nw.data(), nw.size() * sizeof(double), cudaMemcpyHostToDevice));
+        return 0;
+    }
+};
+
+extern "C" {
+
+mcs_vocab* mcs_vocab_create(int device, int k, int L, int scoring, int weighting, int n_nodes, const int* parent, const int* is_leaf,
+                            const uint8_t* descriptors, const double* weights) {
+    if (n_nodes < 1 || !parent || !is_leaf || !descriptors || !weights || L < 1) { set_err("mcs_vocab_create: bad arguments"); return nullptr; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { set_err("no CUDA device: this library has no CPU path"); return nullptr; }
+    mcs_vocab* v = new mcs_vocab();
+    v->device = device; v->k = k; v->L = L; v->scoring = scoring; v->weighting = weighting;
+    if (v->build(n_nodes, parent, is_leaf, descriptors, weights)) { delete v; return nullptr; }
+    return v;
+}
+
+// loadFromTextFile: "k L scoring weighting", then one line per node: parent is_leaf d0 .. d31 weight
+mcs_vocab* mcs_vocab_load_text(const char* path, int device) {
+    FILE* f = path ? fopen(path, "r") : nullptr;
+    if (!f) { set_err("mcs_vocab_load_text: cannot open file"); return nullptr; }
+    int k = 0, L = 0, n1 = 0, n2 = 0;
+    if (fscanf(f, "%d %d %d %d", &k, &L, &n1, &n2) != 4 || k < 0 || k > 20 || L < 1 || L > 10 || n1 < 0 || n1 > 5 || n2 < 0 || n2 > 3) {
+        fclose(f);
+        set_err("mcs_vocab_load_text: vocabulary header out of range");
+        return nullptr;
+    }
+    std::vector<int> parent, leaf;
+    std::vector<uint8_t> desc;
+    std::vector<double> weight;
+    for (;;) {
+        int pid, il;
+        if (fscanf(f, "%d %d", &pid, &il) != 2) break;
+        uint8_t d[32];
+        bool ok = true;
+        for (int i = 0; i < 32 && ok; i++) {
+            int b;
+            ok = fscanf(f, "%d", &b) == 1;
+            d[i] = (uint8_t)b;
+        }
+        double w;
+        if (!ok || fscanf(f, "%lf", &w) != 1) { fclose(f); set_err("mcs_vocab_load_text: truncated node line"); return nullptr; }
+        parent.push_back(pid); leaf.push_back(il); weight.push_back(w);
+        desc.insert(desc.end(), d, d + 32);
+    }
+    fclose(f);
+    return mcs_vocab_create(device, k, L, n1, n2, (int)parent.size(), parent.data(), leaf.data(), desc.data(), weight.data());
+}
+void mcs_vocab_destroy(mcs_vocab* v) { delete v; }
+int mcs_vocab_info(const mcs_vocab* v, int* k, int* L, int* n_nodes, int* n_words) {
+    if (!v) return MCS_ERR_ARG;
+    if (k) *k = v->k;
+    if (L) *L = v->L;
+    if (n_nodes) *n_nodes = v->n_nodes;
+    if (n_words) *n_words = v->n_words;
+    return 0;
+}
+
+// TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup) for n descriptors (host buffers)
+int mcs_vocab_transform(mcs_vocab* v, const uint8_t* descriptors, int n, int levelsup, int32_t* word_id, int32_t* node_id, double* weight) {
+    if (!v || n < 0 || (n && (!descriptors || !word_id || !node_id))) return MCS_ERR_ARG;
+    if (n == 0) return 0;
+    CK(cudaSetDevice(v->device));
+    if ((size_t)n > v->cap) {
+        cudaFree(v->d_in); cudaFree(v->d_word); cudaFree(v->d_node); cudaFree(v->d_w);
+        v->d_in = nullptr; v->d_word = v->d_node = nullptr; v->d_w = nullptr; v->cap = 0;
+        const size_t c = (size_t)n * 2;
+        CK(cudaMalloc(&v->d_in, c * 32));
+        CK(cudaMalloc(&v->d_word, c * sizeof(int)));
+        CK(cudaMalloc(&v->d_node, c * sizeof(int)));
+        CK(cudaMalloc(&v->d_w, c * sizeof(double)));
+        v->cap = c;
+    }
+    cudaStream_t st = v->stream;
+    CK(cudaMemcpyAsync(v->d_in, descriptors, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+    mcs::vocab_transform_kernel<<<dim3((n + 127) / 128, 1), 128, 0, st>>>(v->d_nodes, v->d_desc, v->d_weight, v->L, levelsup, v->d_in, nullptr, n,
+                                                                         v->d_word, v->d_node, v->d_w);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(word_id, v->d_word, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(node_id, v->d_node, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (weight) CK(cudaMemcpyAsync(weight, v->d_w, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return n;
+}
+
+// The same for every image a rig handle holds (descriptors stay on the device): outputs [n_images][feature_capacity]
+int mcs_rig_vocab_transform(mcs_rig* rig, mcs_vocab* v, int levelsup, int32_t* word_id, int32_t* node_id, double* weight) {
+    RIG_ENTER(rig);
+    if (!v || !word_id || !node_id) return MCS_ERR_ARG;
+    if (rig->n_extracted < 1) { set_err("vocab transform before extract"); return MCS_ERR_STATE; }
+    if (v->device != rig->eng.device) { set_err("vocabulary lives on another device"); return MCS_ERR_ARG; }
+    const int n_img = rig->n_extracted * rig->C, cap = rig->kp_cap;
+    const size_t tot = (size_t)n_img * cap;
+    int *d_word = nullptr, *d_node = nullptr;
+    double* d_w = nullptr;
+    cudaStream_t st = rig->eng.stream;
+    CK(cudaMallocAsync(&d_word, tot * sizeof(int), st));
+    CK(cudaMallocAsync(&d_node, tot * sizeof(int), st));
+    CK(cudaMallocAsync(&d_w, tot * sizeof(double), st));
+    CK(cudaMemsetAsync(d_word, 0xFF, tot * sizeof(int), st));
+    CK(cudaMemsetAsync(d_node, 0xFF, tot * sizeof(int), st));
+    CK(cudaMemsetAsync(d_w, 0, tot * sizeof(double), st));
+    mcs::vocab_transform_kernel<<<dim3((cap + 127) / 128, n_img), 128, 0, st>>>(v->d_nodes, v->d_desc, v->d_weight, v->L, levelsup, rig->eng.d_desc,
+                                                                               rig->eng.d_kp_count, cap, d_word, d_node, d_w);
+    CK(cudaGetLastError());
+    rig->eng.launches++;
+    CK(cudaMemcpyAsync(word_id, d_word, tot * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(node_id, d_node, tot * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (weight) CK(cudaMemcpyAsync(weight, d_w, tot * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaFreeAsync(d_word, st));
+    CK(cudaFreeAsync(d_node, st));
+    CK(cudaFreeAsync(d_w, st));
+    return 0;
+}
+
+}  // extern "C"

@@ -3,6 +3,7 @@
 //   ORBextractor       /root/reference/MCSlam/include/MCSlam/ORBextractor.h:44-112
 //   MultiCameraFrame   /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h (extract / intra-match / triangulate subset)
 //   IntraMatch         /root/reference/MCSlam/include/MCSlam/MultiCameraFrame.h:42-57
+//   ORBVocabulary      DBoW2 vocabulary: loadFromTextFile (FrontEnd.h:137-138), transform(features, bowVec, featVec, 4) (MultiCameraFrame.cpp:257)
 //   BowMatcher         ORBextractor::getMatches_distRatio (ORBextractor.cpp:1228-1290) + the BowMatching / InterMatchingBow node walk
 //   InterFrameMatcher  FrontEnd::findMatchesMono / findInterMatches, /root/reference/MCSlam/src/FrontEnd.cpp:3114-3470
 // Without OpenCV headers the containers are PODs (mcs_keypoint, byte vectors).  Define MCS_WITH_OPENCV before including this
@@ -383,6 +384,42 @@ private:
 // DBoW2::FeatureVector as the matchers read it: node id -> indices of the features that fell into that vocabulary node, ordered by
 // node id.  The vocabulary itself (DBoW2 transform, MultiCameraFrame.cpp:257) stays with the caller.
 typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
+
+// DBoW2::TemplatedVocabulary as the front-end uses it (MCSlam/include/MCSlam/ORBVocabulary.h; DBoW2 itself is an external, un-vendored
+// dependency): loadFromTextFile (FrontEnd.h:137-138) and transform(features, bowVec, featVec, levelsup) (MultiCameraFrame.cpp:257,
+// FrontEnd.cpp:533).  The tree descent runs on the GPU for all features of a call; word ids / weights are returned alongside the
+// FeatureVector for callers that build a BowVector.
+class ORBVocabulary {
+public:
+    explicit ORBVocabulary(int device = 0) : device_(device) {}
+    ~ORBVocabulary() { mcs_vocab_destroy(h_); }
+    ORBVocabulary(const ORBVocabulary&) = delete;
+    ORBVocabulary& operator=(const ORBVocabulary&) = delete;
+    bool loadFromTextFile(const std::string& filename) {
+        mcs_vocab_destroy(h_);
+        h_ = mcs_vocab_load_text(filename.c_str(), device_);
+        return h_ != nullptr;
+    }
+    // features: n x 32 bytes.  featVec: node id (at level L - levelsup) -> feature indices in ascending order, features whose word has
+    // weight 0 left out (DBoW2: `if(w > 0)`).
+    void transform(const uint8_t* features, int n, FeatureVector& featVec, int levelsup, std::vector<int>* word_ids = nullptr,
+                   std::vector<double>* weights = nullptr) const {
+        if (!h_) throw std::runtime_error("ORBVocabulary::transform: no vocabulary loaded");
+        std::vector<int32_t> wid(n > 0 ? n : 1), nid(n > 0 ? n : 1);
+        std::vector<double> w(n > 0 ? n : 1);
+        check(mcs_vocab_transform(h_, features, n, levelsup, wid.data(), nid.data(), w.data()), "mcs_vocab_transform");
+        featVec.clear();
+        for (int i = 0; i < n; i++)
+            if (w[i] > 0) featVec[(unsigned int)nid[i]].push_back((unsigned int)i);
+        if (word_ids) word_ids->assign(wid.begin(), wid.begin() + n);
+        if (weights) weights->assign(w.begin(), w.begin() + n);
+    }
+    mcs_vocab* handle() const { return h_; }
+
+private:
+    mcs_vocab* h_ = nullptr;
+    int device_ = 0;
+};
 
 // The BoW-guided matchers: ORBextractor::getMatches_distRatio (ORBextractor.cpp:1228-1290) and the node walk around it in
 // MultiCameraFrame::BowMatching (MultiCameraFrame.cpp:946-1022) and FrontEnd::InterMatchingBow (FrontEnd.cpp:3791-3840, :3905-3965).

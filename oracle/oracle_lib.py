@@ -62,6 +62,7 @@ def lib():
         L.orc_undistort_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_undistort_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_vocab_transform.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_int] + [C.c_void_p] * 3
         L.orc_set_data_f32.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
@@ -348,6 +349,29 @@ def undistort_keypoints(kps, K, dist):
     out = np.zeros_like(kps)
     lib().orc_undistort_keypoints(_p(kps), len(kps), _p(K), _p(d5), _p(out))
     return out
+
+
+def vocab_transform(L, parent, is_leaf, node_desc, weight, feats, levelsup=4):
+    """DBoW2 transform per feature on a vocabulary in loadFromTextFile layout: (word_id, node_id, weight) arrays."""
+    parent = np.ascontiguousarray(parent, np.int32)
+    is_leaf = np.ascontiguousarray(is_leaf, np.int32)
+    node_desc = np.ascontiguousarray(node_desc, np.uint8).reshape(-1, 32)
+    weight = np.ascontiguousarray(weight, np.float64)
+    feats = np.ascontiguousarray(feats, np.uint8).reshape(-1, 32)
+    n = len(feats)
+    wid, nid, w = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+    lib().orc_vocab_transform(L, len(parent), _p(parent), _p(is_leaf), _p(node_desc), _p(weight), _p(feats), n, levelsup, _p(wid), _p(nid), _p(w))
+    return wid[:n], nid[:n], w[:n]
+
+
+def feature_vector(node_id, weight):
+    """FeatureVector of DBoW2's transform(features, bowVec, featVec, levelsup): {node id: [feature indices]}, features of weight 0
+    (stopped words) left out."""
+    fv = {}
+    for i, (n, w) in enumerate(zip(node_id, weight)):
+        if w > 0:
+            fv.setdefault(int(n), []).append(i)
+    return fv
 
 
 def _ptr_array(arrs):

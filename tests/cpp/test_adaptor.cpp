@@ -101,6 +101,19 @@ static int run_inter(const std::string& dir, const char* out_path) {
             fprintf(f, "book %d\n", book);
         }
     }
+    {   // vocabulary: voc.txt in <dir>, transform of the bowA descriptors at levelsup 2
+        ORBVocabulary voc;
+        if (voc.loadFromTextFile(dir + "/voc.txt")) {
+            auto bA = slurp<uint8_t>(dir + "/bowA.bin");
+            FeatureVector fv;
+            voc.transform(bA.data(), (int)bA.size() / 32, fv, 2);
+            for (auto& kv : fv) {
+                fprintf(f, "fv %u", kv.first);
+                for (unsigned i : kv.second) fprintf(f, " %u", i);
+                fprintf(f, "\n");
+            }
+        }
+    }
     fr.triangulateIntraMatches(kp1, kp2);
     for (auto& p : fr.pts3D_) fprintf(f, "pt %.9g %.9g %.9g\n", p[0], p[1], p[2]);
     fclose(f);

@@ -148,6 +148,12 @@ def test_cpp_adaptor_interframe(tmp_path, golden):
     (d / "bowA.bin").write_bytes(np.ascontiguousarray(gb["A"]).tobytes())
     (d / "bowB.bin").write_bytes(np.ascontiguousarray(gb["B"]).tobytes())
     (d / "bow_nodes.bin").write_bytes(np.concatenate([gb["node_of_A"], gb["node_of_B"]]).astype(np.int32).tobytes())
+    vrng = np.random.default_rng(32)
+    vp, vl, vd, vw = _random_vocabulary(vrng, 5, 3)
+    with open(d / "voc.txt", "w") as f:
+        f.write("5 3 0 0\n")
+        for p_, l_, d_, w_ in zip(vp, vl, vd, vw):
+            f.write("%d %d %s %.17g\n" % (p_, l_, " ".join(str(int(b)) for b in d_), w_))
     (d / "meta.txt").write_text("%d %d %d %d %d %d %d\n" % (len(g["d1"]), len(g["d2"]), g["m1"].shape[1], g["isz"][0], g["isz"][1], C, npair))
     out = subprocess.run([exe, "inter", str(d), str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr
@@ -169,7 +175,80 @@ def test_cpp_adaptor_interframe(tmp_path, golden):
     ea, eb, ek = O.matches_dist_ratio(gb["A"], fa[n0], gb["B"], fb[n0])
     node0 = np.array([list(map(int, l.split()[1:])) for l in lines if l.startswith("node0 ")], np.uint32).reshape(-1, 2)
     assert node0[:, 0].tolist() == ea.tolist() and node0[:, 1].tolist() == eb.tolist() and ("book %d" % ek) in lines
+    _, vnid, vwt = O.vocab_transform(3, vp, vl, vd, vw, gb["A"], 2)
+    efv = O.feature_vector(vnid, vwt)
+    gfv = {int(l.split()[1]): list(map(int, l.split()[2:])) for l in lines if l.startswith("fv ")}
+    assert gfv == efv and len(gfv) >= 3
     got = np.array([[float(x) for x in l.split()[1:]] for l in lines if l.startswith("pt ")], np.float32)
     exp = np.concatenate(expect)
     assert got.shape == exp.shape
     assert np.allclose(got, exp, rtol=1e-3, atol=1e-3), np.abs(got - exp).max()
+
+
+def _random_vocabulary(rng, k, L, p_early_leaf=0.15):
+    """A vocabulary in loadFromTextFile layout: nodes in breadth-first file order, children with near-duplicate descriptors (ties),
+    some early leaves, some zero weights."""
+    parent, leaf, desc, weight = [], [], [], []
+    frontier = [(0, 0, rng.integers(0, 256, 32, dtype=np.uint8))]
+    while frontier:
+        nxt = []
+        for pid, depth, centre in frontier:
+            for c in range(k):
+                d = centre ^ (rng.integers(0, 256, 32, dtype=np.uint8) & rng.integers(0, 256, 32, dtype=np.uint8))
+                if c in (3, 4):
+                    d = desc[-1].copy()  # duplicate of the previous sibling: distance ties
+                nid = len(parent) + 1
+                is_leaf = depth + 1 == L or (depth + 1 >= 2 and rng.random() < p_early_leaf)
+                parent.append(pid); leaf.append(int(is_leaf)); desc.append(d)
+                weight.append(0.0 if (is_leaf and rng.random() < 0.1) else float(rng.uniform(0.1, 9.0)))
+                if not is_leaf:
+                    nxt.append((nid, depth + 1, d))
+        frontier = nxt
+    return np.array(parent, np.int32), np.array(leaf, np.int32), np.array(desc, np.uint8), np.array(weight, np.float64)
+
+
+def test_vocabulary_transform(tmp_path):
+    """DBoW2 transform (word id, node id at level L - levelsup, weight) through mcs_vocab_load_text / mcs_vocab_transform /
+    mcs_rig_vocab_transform against the oracle, and the FeatureVector-driven BowMatching on top of it."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    rng = np.random.default_rng(31)
+    k, L = 6, 4
+    parent, leaf, desc, weight = _random_vocabulary(rng, k, L)
+    path = tmp_path / "voc.txt"
+    with open(path, "w") as f:
+        f.write("%d %d 0 0\n" % (k, L))
+        for p, l, d, w in zip(parent, leaf, desc, weight):
+            f.write("%d %d %s %.17g\n" % (p, l, " ".join(str(int(b)) for b in d), w))
+    voc = M.Vocabulary(path)
+    assert (voc.k, voc.L, voc.n_nodes, voc.n_words) == (k, L, len(parent) + 1, int(leaf.sum()))
+    feats = desc[rng.integers(0, len(desc), 3000)] ^ (rng.integers(0, 256, (3000, 32), dtype=np.uint8) & rng.integers(0, 256, (3000, 32), dtype=np.uint8)
+                                                     & rng.integers(0, 256, (3000, 32), dtype=np.uint8))
+    for levelsup in (0, 2, 4, 6):
+        got = voc.transform(feats, levelsup)
+        exp = O.vocab_transform(L, parent, leaf, desc, weight, feats, levelsup)
+        for a, b in zip(got, exp):
+            assert np.array_equal(a, b), levelsup
+    assert (exp[2] == 0).any() and len(set(got[1].tolist())) == 1  # stopped words exist; levelsup >= L collapses to the root
+    voc2 = M.Vocabulary(k=k, L=L, parent=parent, is_leaf=leaf, node_desc=desc, weight=weight)
+    assert all(np.array_equal(a, b) for a, b in zip(voc2.transform(feats, 2), O.vocab_transform(L, parent, leaf, desc, weight, feats, 2)))
+    # on a rig's resident descriptors, then BowMatching between two cameras through the FeatureVectors
+    calib = M.synth.make_rig(3, 320, 240)
+    rig = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=1)
+    rig.process(M.synth.make_rig_frame(calib, 320, 240, frame_index=3, n_rects=6)[None])
+    wid, nid, w = voc.transform_rig(rig, 2)
+    fvs, D = [], []
+    for c in range(3):
+        _, d = rig.features(0, c)
+        e = O.vocab_transform(L, parent, leaf, desc, weight, d, 2)
+        n = len(d)
+        assert np.array_equal(wid[c, :n], e[0]) and np.array_equal(nid[c, :n], e[1]) and np.array_equal(w[c, :n], e[2])
+        assert (wid[c, n:] == -1).all()
+        fvs.append(O.feature_vector(nid[c, :n], w[c, :n]))
+        D.append(d)
+    m = M.Matcher(max_sets=1, max_query_rows=1024, max_train_rows=1024)
+    a, b, words, bk = m.bow_matching(D[0], D[1], fvs[0], fvs[1])
+    ea, eb, ew, ek = O.bow_matching(D[0], D[1], fvs[0], fvs[1])
+    assert np.array_equal(a, ea) and np.array_equal(b, eb) and np.array_equal(words, ew) and bk == ek
+    with pytest.raises(M.McsError):
+        M.Vocabulary(tmp_path / "missing.txt")
