@@ -263,6 +263,14 @@ MCS_API long long mcs_matcher_kernel_launches(const mcs_matcher* m);
 MCS_API int mcs_match_subsets(mcs_matcher* m, const uint8_t* descA, int nA, const uint8_t* descB, int nB, int n_groups, const int* a_ofs,
                               const uint32_t* a_idx, const int* b_ofs, const uint32_t* b_idx, int th_low, double max_neighbor_ratio,
                               uint32_t* match_a, uint32_t* match_b, int* group_count, long long* book_k);
+/* Inner loop of the BoW-guided MultiCameraFrame::computeIntraMatches(matches, words_) (MultiCameraFrame.cpp:716-751), for the
+ * resident features of rig frame `frame`: group g = one vocabulary node seen by cameras cam_a[g] < cam_b[g] with the node's feature
+ * lists a_idx[a_ofs[g]..) / b_idx[b_ofs[g]..).  Per cam_a feature: position of the best cam_b feature inside the group's list (or -1),
+ * best and second-best Hamming distance (1000000000 = the reference's 1e9) over the cam_b features whose undistorted keypoint is
+ * less than y_gate (50, :731) rows away.  The row bookkeeping (:752-816) runs on the host (mcslam_adaptor.hpp). */
+MCS_API int mcs_rig_bow_best2(mcs_rig* rig, int frame, int n_groups, const int* cam_a, const int* cam_b, const int* a_ofs,
+                              const uint32_t* a_idx, const int* b_ofs, const uint32_t* b_idx, float y_gate, int32_t* best_j, int32_t* d1,
+                              int32_t* d2);
 /* knnMatch(k = 2) between feature sets a rig handle already holds on the device (no descriptor traffic over PCIe): set s matches
  * image q_image[s] = frame * num_cams + cam against image t_image[s], e.g. findMatchesMono for every consecutive frame pair of a
  * batch.  out_knn: [n_sets][feature_capacity][4]; rows past the query image's keypoint count stay -1. */

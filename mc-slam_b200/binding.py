@@ -39,7 +39,7 @@ EXPORTS = [
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
     "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
-    "mcs_vocab_transform", "mcs_rig_vocab_transform",
+    "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2",
 ]
 
 
@@ -124,6 +124,7 @@ def lib():
     L.mcs_vocab_info.argtypes = [vp, vp, vp, vp, vp]
     L.mcs_vocab_transform.argtypes = [vp, vp, ci, ci, vp, vp, vp]
     L.mcs_rig_vocab_transform.argtypes = [vp, vp, ci, vp, vp, vp]
+    L.mcs_rig_bow_best2.argtypes = [vp, ci, ci, vp, vp, vp, vp, vp, vp, cf, vp, vp, vp]
     L.mcs_rig_set_undistort_keypoints.argtypes = [vp, ci]
     L.mcs_rig_get_keypoints_undist.argtypes = [vp, ci, ci, vp, ci]
     L.mcs_rig_process_f32.argtypes = [vp, vp, ci, vp, ci, ci]
@@ -456,6 +457,24 @@ class RigFrames:
         out = np.empty((len(qi), self.kp_cap, 4), np.int32)
         _check(lib().mcs_rig_knn2_images(self.hd, _p(qi), _p(ti), len(qi), _p(out)), "rig_knn2_images")
         return out
+
+    def bow_best2(self, frame, groups, y_gate=50.0):
+        """Inner loop of the BoW-guided computeIntraMatches(matches, words_) (MultiCameraFrame.cpp:716-751) on frame `frame`'s resident
+        features.  groups: [(cam_a, cam_b, a_feature_indices, b_feature_indices)].  Returns per group (best_j, d1, d2) int32 arrays
+        (best_j = position in the group's b list or -1; 1000000000 = no candidate)."""
+        ca = np.array([g[0] for g in groups], np.int32)
+        cb = np.array([g[1] for g in groups], np.int32)
+        ao = np.zeros(len(groups) + 1, np.int32)
+        bo = np.zeros(len(groups) + 1, np.int32)
+        for k, g in enumerate(groups):
+            ao[k + 1] = ao[k] + len(g[2])
+            bo[k + 1] = bo[k] + len(g[3])
+        ai = np.ascontiguousarray(np.concatenate([np.asarray(g[2], np.uint32) for g in groups]) if groups else np.zeros(0, np.uint32), np.uint32)
+        bi = np.ascontiguousarray(np.concatenate([np.asarray(g[3], np.uint32) for g in groups]) if groups else np.zeros(0, np.uint32), np.uint32)
+        bj, d1, d2 = (np.empty(max(int(ao[-1]), 1), np.int32) for _ in range(3))
+        _check(lib().mcs_rig_bow_best2(self.hd, frame, len(groups), _p(ca), _p(cb), _p(ao), _p(ai), _p(bo), _p(bi), y_gate, _p(bj), _p(d1), _p(d2)),
+               "rig_bow_best2")
+        return [(bj[ao[k]:ao[k + 1]].copy(), d1[ao[k]:ao[k + 1]].copy(), d2[ao[k]:ao[k + 1]].copy()) for k in range(len(groups))]
 
     def level(self, frame, cam, level, kind=0):
         w, h = C.c_int(), C.c_int()

@@ -302,6 +302,41 @@ __global__ void __launch_bounds__(128) vocab_transform_kernel(const VocabNode* _
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K6d  inner loop of the BoW-guided computeIntraMatches(matches, words_) (/root/reference/MCSlam/src/MultiCameraFrame.cpp:716-751):
+// for a vocabulary node seen by cameras cam1 < cam2, per cam1 feature of the node the best / second-best cam2 feature of the node
+// whose undistorted keypoint lies within y_gate rows (|dy| >= 50 skipped, :731), strict '<' so the first candidate wins.  The
+// order-dependent row bookkeeping (:752-816) stays on the host; one block per (node, camera pair) group, raw results out.
+// best_j: position inside the group's cam2 list or -1; d1 / d2: distances, 1000000000 standing for the reference's 1e9.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) bow_best2_kernel(const uint8_t* __restrict__ desc, const KeypointPod* __restrict__ kps_undist, int kp_cap,
+                                                       const int* __restrict__ img_a, const int* __restrict__ img_b,
+                                                       const int* __restrict__ a_ofs, const uint32_t* __restrict__ a_idx,
+                                                       const int* __restrict__ b_ofs, const uint32_t* __restrict__ b_idx, float y_gate,
+                                                       int* __restrict__ best_j, int* __restrict__ d1, int* __restrict__ d2) {
+    const int g = blockIdx.x;
+    const int a0 = a_ofs[g], na = a_ofs[g + 1] - a0, b0 = b_ofs[g], nb = b_ofs[g + 1] - b0;
+    const size_t ia = (size_t)img_a[g] * kp_cap, ib = (size_t)img_b[g] * kp_cap;
+    for (int i = threadIdx.x; i < na; i += blockDim.x) {
+        const uint32_t fa = a_idx[a0 + i];
+        const uint4* qa = reinterpret_cast<const uint4*>(desc + (ia + fa) * 32);
+        const uint4 q0 = __ldg(qa), q1 = __ldg(qa + 1);
+        const float ya = kps_undist[ia + fa].y;
+        int bj = -1, best1 = 1000000000, best2 = 1000000000;
+        for (int j = 0; j < nb; j++) {
+            const uint32_t fb = __ldg(b_idx + b0 + j);
+            if (fabsf(__fsub_rn(ya, kps_undist[ib + fb].y)) >= y_gate) continue;
+            const uint4* tb = reinterpret_cast<const uint4*>(desc + (ib + fb) * 32);
+            const int d = hamming256(q0, q1, __ldg(tb), __ldg(tb + 1));
+            if (d < best1) { bj = j; best2 = best1; best1 = d; }
+            else if (d < best2) best2 = d;
+        }
+        best_j[a0 + i] = bj;
+        d1[a0 + i] = best1;
+        d2[a0 + i] = best2;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K7  merge: computeIntraMatches(matches, old) after the pair matcher (:1222-1266).  The reference walks the matches of the pairs
 // in order and mutates match_inv_idx / the row table as it goes, so later matches and later pairs see earlier state.  Pairs stay
 // sequential (one block per frame walks them), but inside one pair (i, j) the walk decomposes:

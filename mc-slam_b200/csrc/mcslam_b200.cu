@@ -1905,6 +1905,53 @@ int mcs_match_subsets(mcs_matcher* m, const uint8_t* descA, int nA, const uint8_
     return n;
 }
 
+// Inner loop of the BoW-guided computeIntraMatches(matches, words_) for n_groups (node, cam1, cam2) groups of frame `frame` (see K6d)
+int mcs_rig_bow_best2(mcs_rig* rig, int frame, int n_groups, const int* cam_a, const int* cam_b, const int* a_ofs, const uint32_t* a_idx,
+                      const int* b_ofs, const uint32_t* b_idx, float y_gate, int32_t* best_j, int32_t* d1, int32_t* d2) {
+    RIG_ENTER(rig);
+    if (frame < 0 || frame >= rig->n_extracted || n_groups < 0) return MCS_ERR_ARG;
+    if (n_groups == 0) return 0;
+    if (!cam_a || !cam_b || !a_ofs || !b_ofs || !best_j || !d1 || !d2) return MCS_ERR_ARG;
+    int rc = rig->ensure_features();
+    if (rc) return rc;
+    const int ta = a_ofs[n_groups], tb = b_ofs[n_groups];
+    std::vector<int> img(2 * (size_t)n_groups);
+    for (int g = 0; g < n_groups; g++) {
+        if (cam_a[g] < 0 || cam_a[g] >= rig->C || cam_b[g] < 0 || cam_b[g] >= rig->C || a_ofs[g + 1] < a_ofs[g] || b_ofs[g + 1] < b_ofs[g]) {
+            set_err("bow_best2: bad group");
+            return MCS_ERR_ARG;
+        }
+        img[g] = frame * rig->C + cam_a[g];
+        img[n_groups + g] = frame * rig->C + cam_b[g];
+        const int na = rig->eng.h_kp_count[img[g]], nb = rig->eng.h_kp_count[img[n_groups + g]];
+        for (int i = a_ofs[g]; i < a_ofs[g + 1]; i++) if ((int)a_idx[i] >= na) { set_err("bow_best2: feature index out of range"); return MCS_ERR_ARG; }
+        for (int i = b_ofs[g]; i < b_ofs[g + 1]; i++) if ((int)b_idx[i] >= nb) { set_err("bow_best2: feature index out of range"); return MCS_ERR_ARG; }
+    }
+    if (ta == 0) return 0;
+    cudaStream_t st = rig->eng.stream;
+    const size_t G1 = (size_t)n_groups + 1, words = 2 * (size_t)n_groups + 2 * G1 + ta + tb + 3 * (size_t)ta;
+    int* w = nullptr;
+    CK(cudaMallocAsync(&w, words * sizeof(int), st));
+    int *d_img = w, *d_aofs = d_img + 2 * n_groups, *d_bofs = d_aofs + G1;
+    uint32_t *d_aidx = (uint32_t*)(d_bofs + G1), *d_bidx = d_aidx + ta;
+    int *d_bj = (int*)(d_bidx + tb), *d_d1 = d_bj + ta, *d_d2 = d_d1 + ta;
+    CK(cudaMemcpyAsync(d_img, img.data(), img.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_aofs, a_ofs, G1 * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_bofs, b_ofs, G1 * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_aidx, a_idx, (size_t)ta * sizeof(int), cudaMemcpyHostToDevice, st));
+    if (tb) CK(cudaMemcpyAsync(d_bidx, b_idx, (size_t)tb * sizeof(int), cudaMemcpyHostToDevice, st));
+    mcs::bow_best2_kernel<<<n_groups, 64, 0, st>>>(rig->eng.d_desc, rig->kps_undist_dev(), rig->kp_cap, d_img, d_img + n_groups, d_aofs, d_aidx,
+                                                   d_bofs, d_bidx, y_gate, d_bj, d_d1, d_d2);
+    CK(cudaGetLastError());
+    rig->eng.launches++;
+    CK(cudaMemcpyAsync(best_j, d_bj, (size_t)ta * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d1, d_d1, (size_t)ta * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d2, d_d2, (size_t)ta * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaFreeAsync(w, st));
+    return ta;
+}
+
 // knnMatch(k = 2) between feature sets the rig already holds on the device: set s matches image q_image[s] (= frame * num_cams + cam)
 // against image t_image[s].  out_knn: [n_sets][feature_capacity][4]; rows >= the query image's keypoint count are left at -1.
 int mcs_rig_knn2_images(mcs_rig* rig, const int* q_image, const int* t_image, int n_sets, int32_t* out_knn) {

@@ -152,6 +152,10 @@ struct IntraMatch {
     double point3D[3] = {0, 0, 0};
 };
 
+// DBoW2::FeatureVector as the matchers read it: node id -> indices of the features that fell into that vocabulary node, ordered by
+// node id.  ORBVocabulary::transform (below) builds it on the GPU.
+typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
+
 // The extract / intra-match / triangulate entry points of MultiCameraFrame for ONE rig frame (the class also batches frames
 // through process_frames for throughput).  Image data: num_cams CV_8UC1 planes of the same size, tightly packed.
 class MultiCameraFrame {
@@ -211,6 +215,145 @@ public:
         check(M, "mcs_rig_get_intra_matches");
         matches.assign(M, IntraMatch());
         for (int r = 0; r < M; r++) fill_row(matches[r], &rows[(size_t)r * num_cams_]);
+    }
+
+    // computeIntraMatches(matches, words_) (:586-943) — the BoW-guided intra-rig matcher FrontEnd runs by default (FrontEnd.cpp:1009),
+    // over BoW_feats[cam] (the FeatureVectors of :257).  The walk over the vocabulary nodes depends on node ids only, so it is done
+    // twice: once to list every (node, cam1 < cam2) group, whose best / second-best search (:716-751) then runs on the GPU in ONE
+    // launch over the features the rig handle already holds, and once more to replay the reference's order-dependent row bookkeeping
+    // (:752-816) on those tables.  Reference quirks kept: the last node of every FeatureVector is never visited (:627), words_ gets one
+    // entry per successful cam1 feature even when its row was merged into an older one, stolen features leave rows with n_rays == 1.
+    std::vector<FeatureVector> BoW_feats;
+    void computeIntraMatches(std::vector<IntraMatch>& matches, std::vector<unsigned int>& words_, int TH_LOW = 75,
+                             double max_neighbor_ratio = 0.85) {
+        if ((int)BoW_feats.size() != num_cams_) throw std::invalid_argument("computeIntraMatches: BoW_feats must hold one FeatureVector per camera");
+        typedef FeatureVector::const_iterator It;
+        std::vector<It> begin(num_cams_), last(num_cams_);
+        for (int c = 0; c < num_cams_; c++) {
+            if (BoW_feats[c].empty()) return;
+            begin[c] = BoW_feats[c].begin();
+            last[c] = std::prev(BoW_feats[c].end());
+        }
+        struct Step { unsigned int node; std::vector<int> cams; std::vector<const std::vector<unsigned int>*> feats; int group0; };
+        std::vector<Step> steps;
+        std::vector<int> cam_a, cam_b, a_ofs(1, 0), b_ofs(1, 0);
+        std::vector<uint32_t> a_idx, b_idx;
+        {
+            std::vector<It> it = begin;
+            auto done = [&]() {
+                bool res = true;
+                for (int c = 0; c < num_cams_; c++) res = res && it[c]->first >= last[c]->first;
+                return res;
+            };
+            while (!done()) {
+                long lo = (long)INT32_MAX - 1;
+                Step st;
+                for (int c = 0; c < num_cams_; c++) {
+                    const long w = it[c] == last[c] ? (long)INT32_MAX : (long)it[c]->first;
+                    if (w < lo) { lo = w; st.cams.assign(1, c); }
+                    else if (w == lo) st.cams.push_back(c);
+                }
+                st.node = (unsigned int)lo;
+                for (int c : st.cams) st.feats.push_back(&it[c]->second);
+                st.group0 = (int)cam_a.size();
+                const int S = (int)st.cams.size();
+                if (S >= 2) {
+                    for (int i = 0; i + 1 < S; i++)
+                        for (int j = i + 1; j < S; j++) {
+                            cam_a.push_back(st.cams[i]); cam_b.push_back(st.cams[j]);
+                            a_idx.insert(a_idx.end(), st.feats[i]->begin(), st.feats[i]->end());
+                            b_idx.insert(b_idx.end(), st.feats[j]->begin(), st.feats[j]->end());
+                            a_ofs.push_back((int)a_idx.size()); b_ofs.push_back((int)b_idx.size());
+                        }
+                    steps.push_back(st);
+                }
+                for (int c : st.cams) ++it[c];
+            }
+        }
+        std::vector<int32_t> best_j(a_idx.size()), d1(a_idx.size()), d2(a_idx.size());
+        check(mcs_rig_bow_best2(h_, 0, (int)cam_a.size(), cam_a.data(), cam_b.data(), a_ofs.data(), a_idx.data(), b_ofs.data(), b_idx.data(),
+                                50.f, best_j.data(), d1.data(), d2.data()), "mcs_rig_bow_best2");
+        auto popcount256 = [&](int camx, int fx, int camy, int fy) {
+            const uint8_t *x = &image_descriptors[camx][(size_t)fx * 32], *y = &image_descriptors[camy][(size_t)fy * 32];
+            int d = 0;
+            for (int k = 0; k < 32; k++) d += __builtin_popcount((unsigned)(x[k] ^ y[k]));
+            return d;
+        };
+        matches.reserve(10000);
+        std::vector<std::vector<int>> rows;  // rows[r][cam], mirrored into `matches` at the end
+        std::vector<int> rays;
+        int cur = 0;  // intraMatchInd
+        for (const Step& st : steps) {
+            const int S = (int)st.cams.size();
+            std::vector<std::vector<int>> flags(S);
+            for (int i = 0; i < S; i++) flags[i].assign(st.feats[i]->size(), -1);
+            int g = st.group0;
+            for (int i = 0; i + 1 < S; g += S - 1 - i, i++) {
+                const int cam1 = st.cams[i];
+                const std::vector<unsigned int>& f1 = *st.feats[i];
+                for (size_t c1 = 0; c1 < f1.size(); c1++) {
+                    if (flags[i][c1] != -1) continue;
+                    bool found = false, updateOnce = true;
+                    rows.emplace_back(num_cams_, -1);
+                    rows.back()[cam1] = (int)f1[c1];
+                    rays.push_back(1);
+                    flags[i][c1] = cur;
+                    for (int j = i + 1; j < S; j++) {
+                        const int cam2 = st.cams[j], gg = g + (j - i - 1);
+                        const std::vector<unsigned int>& f2 = *st.feats[j];
+                        const int bj = best_j[a_ofs[gg] + c1];
+                        const double b1 = d1[a_ofs[gg] + c1] >= 1000000000 ? 1e9 : (double)d1[a_ofs[gg] + c1];
+                        const double b2 = d2[a_ofs[gg] + c1] >= 1000000000 ? 1e9 : (double)d2[a_ofs[gg] + c1];
+                        if (!(b1 <= TH_LOW && b1 / b2 <= max_neighbor_ratio)) continue;
+                        const int owner = flags[j][bj];
+                        if (owner == cur) continue;
+                        if (owner == -1) {
+                            rows[cur][cam2] = (int)f2[bj]; rays[cur]++;
+                            flags[j][bj] = cur;
+                            found = true;
+                            continue;
+                        }
+                        const int old_cam1 = rows[owner][cam1];
+                        if (old_cam1 == -1) {  // the owning row has no cam1 feature yet: fold this row into it, once per cam1 feature (:762-795)
+                            if (!updateOnce) continue;
+                            updateOnce = false;
+                            bool disjoint = true;
+                            int inc = 0;
+                            for (int t = 0; t < num_cams_ && disjoint; t++)
+                                if (rows[cur][t] != -1) { if (rows[owner][t] != -1) disjoint = false; else inc++; }
+                            if (disjoint) {
+                                for (int t = 0; t < num_cams_; t++) if (rows[cur][t] != -1) rows[owner][t] = rows[cur][t];
+                                rays[owner] += inc;
+                                flags[i][c1] = owner;
+                                cur = owner;
+                                found = true;
+                                rows.pop_back(); rays.pop_back();
+                            }
+                            continue;
+                        }
+                        if (b1 < (double)popcount256(cam1, old_cam1, cam2, (int)f2[bj])) {  // closer than the current owner: steal (:797-806)
+                            rows[owner][cam2] = -1; rays[owner]--;
+                            rows[cur][cam2] = (int)f2[bj]; rays[cur]++;
+                            flags[j][bj] = cur;
+                            found = true;
+                        }
+                    }
+                    if (found) {
+                        words_.push_back(st.node);
+                        cur = (int)rows.size();
+                    } else {
+                        rows.pop_back(); rays.pop_back();
+                        flags[i][c1] = -1;
+                    }
+                }
+            }
+        }
+        for (size_t r = 0; r < rows.size(); r++) {
+            IntraMatch m;
+            fill_row(m, rows[r].data());
+            m.n_rays = rays[r];
+            matches.push_back(m);
+        }
     }
 
     // Triangulation block of FrontEnd::obtainLfFeatures (FrontEnd.cpp:249-370): mask filter (masks: [num_cams][h][w] f32 or null),
@@ -380,10 +523,6 @@ private:
     int w_, h_img_, kp_cap_ = 0, row_cap_ = 0;
     const uint8_t* images_ = nullptr;
 };
-
-// DBoW2::FeatureVector as the matchers read it: node id -> indices of the features that fell into that vocabulary node, ordered by
-// node id.  The vocabulary itself (DBoW2 transform, MultiCameraFrame.cpp:257) stays with the caller.
-typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
 
 // DBoW2::TemplatedVocabulary as the front-end uses it (MCSlam/include/MCSlam/ORBVocabulary.h; DBoW2 itself is an external, un-vendored
 // dependency): loadFromTextFile (FrontEnd.h:137-138) and transform(features, bowVec, featVec, levelsup) (MultiCameraFrame.cpp:257,

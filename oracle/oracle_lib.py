@@ -63,6 +63,7 @@ def lib():
         L.orc_undistort_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_vocab_transform.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_int] + [C.c_void_p] * 3
+        L.orc_intra_matches_bow.argtypes = [C.c_int] + [C.c_void_p] * 6 + [C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_set_data_f32.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         L.orc_intra_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                         C.c_float, C.c_void_p, C.c_int, C.c_void_p]
@@ -372,6 +373,24 @@ def feature_vector(node_id, weight):
         if w > 0:
             fv.setdefault(int(n), []).append(i)
     return fv
+
+
+def intra_matches_bow(descs, kps_undist, fvs, th_low=75, ratio=0.85):
+    """computeIntraMatches(matches, words_) (MultiCameraFrame.cpp:586-943) over per-camera feature vectors {node id: [indices]}.
+    Returns (rows [M, num_cams] int32, n_rays [M], words [n])."""
+    nc = len(descs)
+    descs = [np.ascontiguousarray(d, np.uint8).reshape(-1, 32) for d in descs]
+    kps = [np.ascontiguousarray(k, KP_DTYPE) for k in kps_undist]
+    csr = [feature_vector_csr(fv) for fv in fvs]
+    nn = np.array([len(c[0]) for c in csr], np.int32)
+    cap = int(sum(len(d) for d in descs)) + 1
+    rows = np.full((cap, nc), -1, np.int32)
+    nr = np.zeros(cap, np.int32)
+    words = np.zeros(cap, np.uint32)
+    nw = C.c_int(0)
+    M = lib().orc_intra_matches_bow(nc, _ptr_array(descs), _ptr_array(kps), _p(nn), _ptr_array([c[0] for c in csr]), _ptr_array([c[1] for c in csr]),
+                                    _ptr_array([c[2] for c in csr]), th_low, ratio, _p(rows), _p(nr), cap, _p(words), C.byref(nw))
+    return rows[:M].copy(), nr[:M].copy(), words[:nw.value].copy()
 
 
 def _ptr_array(arrs):

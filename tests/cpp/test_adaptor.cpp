@@ -162,6 +162,23 @@ int main(int argc, char** argv) {
             while (m.matchIndexN[c] < 0) c++;
             fprintf(f, "lfmono %d %d %d %d\n", c, m.matchIndexN[c], (int)m.mono, m.matchDesc[0]);
         }
+        {   // BoW-guided computeIntraMatches(matches, words_): vocabulary in <images>.voc.txt, FeatureVectors at levelsup argv[6]
+            mcs_b200::ORBVocabulary voc;
+            if (argc >= 7 && voc.loadFromTextFile(std::string(argv[1]) + ".voc.txt")) {
+                fr.BoW_feats.assign(C, mcs_b200::FeatureVector());
+                for (int c = 0; c < C; c++)
+                    voc.transform(fr.image_descriptors[c].data(), (int)fr.image_descriptors[c].size() / 32, fr.BoW_feats[c], atoi(argv[6]));
+                std::vector<mcs_b200::IntraMatch> bm;
+                std::vector<unsigned int> words;
+                fr.computeIntraMatches(bm, words);
+                for (auto& r : bm) {
+                    fprintf(f, "bowrow %d", r.n_rays);
+                    for (int c = 0; c < C; c++) fprintf(f, " %d", r.matchIndexN[c]);
+                    fprintf(f, "\n");
+                }
+                for (unsigned w : words) fprintf(f, "bowword %u\n", w);
+            }
+        }
         fclose(f);
         uint8_t empty = 0;
         if (ex(nullptr, 0, 0, 0, nullptr, k, d, lap) != -1) return 4;  // `if(_image.empty()) return -1;`

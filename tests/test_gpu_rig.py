@@ -499,3 +499,88 @@ def test_undistort_keypoints_branch(golden, old):
         assert np.allclose(lm["xyz"][ok], tri["xyz"][ok], rtol=1e-6, atol=1e-9)
         i1, i2, k1, k2 = rig.brute_force_match(f, 0, 2)
         assert len(i1) > 5 and (k1 == KU[0][i1]).all() and (k2 == KU[2][i2]).all()
+
+
+def _write_vocabulary(path, k, L, seed, seeds_desc=None):
+    from test_gpu_interframe import _random_vocabulary
+    rng = np.random.default_rng(seed)
+    parent, leaf, desc, weight = _random_vocabulary(rng, k, L)
+    if seeds_desc is not None:  # centre the first-level nodes on real descriptors so that the features spread over the tree
+        desc[:k] = seeds_desc[:k]
+    with open(path, "w") as f:
+        f.write("%d %d 0 0\n" % (k, L))
+        for p, l, d, w in zip(parent, leaf, desc, weight):
+            f.write("%d %d %s %.17g\n" % (p, l, " ".join(str(int(b)) for b in d), w))
+    return parent, leaf, desc, weight
+
+
+def test_bow_best2_equals_bruteforce():
+    """mcs_rig_bow_best2 (the per-node best / second-best search of the BoW-guided computeIntraMatches, MultiCameraFrame.cpp:716-751)
+    against a numpy restatement on a rig's resident features: ragged groups, an empty cam2 list, the 50-row gate."""
+    import mcslam_b200 as M
+    calib = M.synth.make_rig(3, 320, 240)
+    rig = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=2)
+    rig.process(np.stack([M.synth.make_rig_frame(calib, 320, 240, frame_index=i, n_rects=6) for i in (3, 4)]))
+    rng = np.random.default_rng(5)
+    for frame in (0, 1):
+        feats = [rig.features(frame, c) for c in range(3)]
+        kpu = [rig.keypoints_undist(frame, c) for c in range(3)]
+        groups = []
+        for g in range(40):
+            a, b = sorted(rng.choice(3, 2, replace=False).tolist())
+            na, nb = int(rng.integers(1, 70)), int(rng.integers(0, 40)) if g != 7 else 0
+            groups.append((a, b, rng.choice(len(feats[a][0]), min(na, len(feats[a][0])), replace=False).astype(np.uint32),
+                           rng.choice(len(feats[b][0]), min(nb, len(feats[b][0])), replace=False).astype(np.uint32)))
+        got = rig.bow_best2(frame, groups)
+        n_gated = 0
+        for (a, b, ia, ib), (bj, d1, d2) in zip(groups, got):
+            Da, Db = feats[a][1][ia], feats[b][1][ib]
+            dist = np.unpackbits(Da[:, None, :] ^ Db[None, :, :], axis=2).sum(2).astype(np.int64) if len(ib) else np.zeros((len(ia), 0), np.int64)
+            ok = np.abs(kpu[a]["y"][ia][:, None] - kpu[b]["y"][ib][None, :]) < np.float32(50)
+            n_gated += int((~ok).sum())
+            dist = np.where(ok, dist, 10 ** 9)
+            for i in range(len(ia)):
+                row = dist[i]
+                if len(row) == 0 or row.min() >= 10 ** 9:
+                    assert bj[i] == -1 and d1[i] == 10 ** 9 and d2[i] == 10 ** 9
+                    continue
+                j = int(np.argmin(row))  # first minimum, as the strict '<' of :735
+                rest = np.delete(row, j)
+                assert (bj[i], d1[i]) == (j, row[j]) and d2[i] == (rest.min() if len(rest) else 10 ** 9)
+        assert n_gated > 0
+    assert rig.bow_best2(0, []) == []
+    with pytest.raises(M.McsError):
+        rig.bow_best2(0, [(0, 1, np.array([100000], np.uint32), np.array([0], np.uint32))])
+
+
+@pytest.mark.parametrize("levelsup", [1, 2])
+def test_cpp_adaptor_bow_intra_matches(tmp_path, levelsup):
+    """MultiCameraFrame::computeIntraMatches(matches, words_) — the BoW-guided intra-rig matcher FrontEnd runs by default
+    (MultiCameraFrame.cpp:586-943) — through the C++ adaptor (vocabulary transform and per-node searches on the GPU, the row bookkeeping
+    on the host) against the oracle's restatement: rows, n_rays and words_ identical."""
+    import subprocess
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from test_host_side import _build_adaptor
+    exe = _build_adaptor(tmp_path)
+    calib = M.synth.make_rig(4, 320, 240)
+    frame = M.synth.make_rig_frame(calib, 320, 240, frame_index=9, n_rects=7)
+    K, D, _, _, _ = _oracle_frame(O, frame, calib, 400)
+    (tmp_path / "im.bin").write_bytes(frame.tobytes())
+    (tmp_path / "im.bin.calib").write_bytes(np.ascontiguousarray(calib).tobytes())
+    k, L = 6, 3
+    pick = np.random.default_rng(2).choice(len(D[0]), k, replace=False)
+    parent, leaf, desc, weight = _write_vocabulary(tmp_path / "im.bin.voc.txt", k, L, 77, D[0][pick])
+    out = subprocess.run([exe, str(tmp_path / "im.bin"), "4", "320", "240", str(tmp_path / "o.txt"), str(levelsup)], capture_output=True,
+                         text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    lines = (tmp_path / "o.txt").read_text().splitlines()
+    fvs = []
+    for c in range(4):
+        _, nid, w = O.vocab_transform(L, parent, leaf, desc, weight, D[c], levelsup)
+        fvs.append(O.feature_vector(nid, w))
+    rows, n_rays, words = O.intra_matches_bow(D, K, fvs)
+    got = np.array([list(map(int, l.split()[1:])) for l in lines if l.startswith("bowrow ")], np.int32).reshape(-1, 5)
+    assert len(rows) > 30 and (n_rays >= 3).any()
+    assert np.array_equal(got[:, 1:], rows) and np.array_equal(got[:, 0], n_rays)
+    assert [int(l.split()[1]) for l in lines if l.startswith("bowword ")] == words.tolist()

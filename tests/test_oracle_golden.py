@@ -185,3 +185,118 @@ def test_undistort_keypoints_matches_cv2(golden):
         assert np.array_equal(o["x"], g["out" + k][:, 0]) and np.array_equal(o["y"], g["out" + k][:, 1])
     assert np.array_equal(O.undistort_keypoints(kp, g["K1"], [0.5, 0.1, 0, 0, 0]), kp)
     assert np.array_equal(O.undistort_keypoints(kp, g["K1"], [0, 0.1, 0, 0, 0]), kp)
+
+
+def _bow_intra_py(D, Y, fvs, th_low=75, ratio=0.85):
+    """Second, loop-level restatement of computeIntraMatches(matches, words_) (MultiCameraFrame.cpp:586-943) in Python, written from the
+    reference listing independently of oracle/mcs_oracle.cpp; small inputs only."""
+    nc = len(D)
+    if any(len(fv) == 0 for fv in fvs):
+        return [], [], []
+    nodes = [sorted(fv) for fv in fvs]
+    it = [0] * nc
+    end = [len(n) - 1 for n in nodes]
+    matches, rays, words = [], [], []
+    cur = 0
+    pop = lambda a, b: int(np.unpackbits(a ^ b).sum())
+    while not all(nodes[c][it[c]] >= nodes[c][end[c]] for c in range(nc)):
+        wid = [2 ** 31 - 1 if it[c] == end[c] else nodes[c][it[c]] for c in range(nc)]
+        lo = min(min(wid), 2 ** 31 - 2)
+        sel = [c for c in range(nc) if wid[c] == lo] if lo < 2 ** 31 - 2 else []
+        feats = [fvs[c][nodes[c][it[c]]] for c in sel]
+        flags = [[-1] * len(f) for f in feats]
+        if len(sel) >= 2:
+            for i in range(len(sel) - 1):
+                c1 = sel[i]
+                for a, fa in enumerate(feats[i]):
+                    if flags[i][a] != -1:
+                        continue
+                    found, once = False, True
+                    matches.append([-1] * nc); rays.append(1)
+                    matches[-1][c1] = fa
+                    flags[i][a] = cur
+                    for j in range(i + 1, len(sel)):
+                        c2 = sel[j]
+                        bj, b1, b2 = -1, 1e9, 1e9
+                        for b, fb in enumerate(feats[j]):
+                            if abs(np.float32(Y[c1][fa]) - np.float32(Y[c2][fb])) >= 50:
+                                continue
+                            d = pop(D[c1][fa], D[c2][fb])
+                            if d < b1:
+                                bj, b2, b1 = b, b1, d
+                            elif d < b2:
+                                b2 = d
+                        if not (b1 <= th_low and b1 / b2 <= ratio):
+                            continue
+                        own = flags[j][bj]
+                        if own == cur:
+                            continue
+                        if own == -1:
+                            matches[cur][c2] = feats[j][bj]; rays[cur] += 1; flags[j][bj] = cur; found = True
+                            continue
+                        old = matches[own][c1]
+                        if old == -1:
+                            if not once:
+                                continue
+                            once = False
+                            mine = [t for t in range(nc) if matches[cur][t] != -1]
+                            if all(matches[own][t] == -1 for t in mine):
+                                for t in mine:
+                                    matches[own][t] = matches[cur][t]
+                                rays[own] += len(mine)
+                                flags[i][a] = own
+                                cur = own
+                                found = True
+                                matches.pop(); rays.pop()
+                            continue
+                        if b1 < pop(D[c1][old], D[c2][feats[j][bj]]):
+                            matches[own][c2] = -1; rays[own] -= 1
+                            matches[cur][c2] = feats[j][bj]; rays[cur] += 1; flags[j][bj] = cur; found = True
+                    if found:
+                        words.append(nodes[sel[0]][it[sel[0]]])
+                        cur = len(matches)
+                    else:
+                        matches.pop(); rays.pop()
+                        flags[i][a] = -1
+        for c in sel:
+            it[c] += 1
+        if not sel:
+            break
+    return matches, rays, words
+
+
+def test_bow_intra_matches_oracle():
+    """oracle intra_matches_bow: hand-checked cases (a three-view row; the never-visited last node; the |dy| >= 50 gate) and agreement
+    with the Python restatement on clustered random descriptors, 2 to 5 cameras."""
+    import oracle_lib as O
+    kp = lambda ys: np.array([(0, y, 31, -1, 0, 0, -1) for y in ys], O.KP_DTYPE)
+    d = np.zeros((2, 32), np.uint8)
+    d[1] = 255
+    fv = [{5: [0], 9: [1]}] * 3
+    rows, nr, words = O.intra_matches_bow([d] * 3, [kp([10, 10])] * 3, fv)
+    assert rows.tolist() == [[0, 0, 0]] and nr.tolist() == [3] and words.tolist() == [5]  # node 9 is the last node: never visited
+    rows, nr, words = O.intra_matches_bow([d] * 3, [kp([10, 10]), kp([70, 10]), kp([20, 10])], fv)
+    assert rows.tolist() == [[0, -1, 0]] and nr.tolist() == [2]  # camera 1's feature is 60 rows away from camera 0's
+    assert len(O.intra_matches_bow([d] * 3, [kp([10, 10])] * 3, [{5: [0], 9: [1]}, {}, {5: [0]}])[0]) == 0  # an empty FeatureVector: early return
+    rng = np.random.default_rng(123)
+    for nc in (2, 3, 4, 5):
+        centres = rng.integers(0, 256, (40, 32), dtype=np.uint8)
+        D, K, fvs = [], [], []
+        for c in range(nc):
+            n = int(rng.integers(60, 110))
+            src = rng.integers(0, 40, n)
+            noise = rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8) \
+                & rng.integers(0, 256, (n, 32), dtype=np.uint8)
+            D.append(centres[src] ^ noise)
+            K.append(kp((src * 7 % 200 + rng.integers(0, 30, n)).astype(np.float32)))
+            fv = {}
+            for i, s in enumerate(src):
+                if rng.random() < 0.9:
+                    fv.setdefault(int(s // 4) * 3 + 1, []).append(i)
+            fvs.append(fv)
+        rows, nr, words = O.intra_matches_bow(D, K, fvs)
+        er, en, ew = _bow_intra_py(D, [k["y"] for k in K], fvs)
+        assert len(rows) > 10
+        assert rows.tolist() == er and nr.tolist() == en and words.tolist() == ew
+        if nc >= 3:
+            assert len(words) > len(rows) or (nr == 1).any() or (nr >= 3).any()
