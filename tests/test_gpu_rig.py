@@ -584,3 +584,18 @@ def test_cpp_adaptor_bow_intra_matches(tmp_path, levelsup):
     assert len(rows) > 30 and (n_rays >= 3).any()
     assert np.array_equal(got[:, 1:], rows) and np.array_equal(got[:, 0], n_rays)
     assert [int(l.split()[1]) for l in lines if l.startswith("bowword ")] == words.tolist()
+
+
+def test_config4_full_size_rig_frame():
+    """SURVEY config 4 at its full size — 8 cameras, 1920 x 1200, nfeatures = 4000, 28 pairs — one rig frame through extract, match, merge
+    and triangulation against the oracle (maximum sizes: 5200 FAST cells per camera, ~4000 x 4000 Hamming per pair, IntraMatch width 8)."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    C, w, h = 8, 1920, 1200
+    calib = M.synth.make_rig(C, w, h, spacing=0.1)
+    frame = M.synth.make_rig_frame(calib, w, h, frame_index=3, n_rects=10)
+    rig = M.RigFrames(calib, w, h, nfeatures=4000, max_frames=1)
+    rig.process(frame[None])
+    K, D, rows, pc, tri = _oracle_frame(O, frame, calib, 4000)
+    assert min(len(k) for k in K) > 3000 and len(rows) > 3000
+    _check_frame(rig, 0, K, D, rows, tri, C)
