@@ -19,6 +19,7 @@
 #include <cstdint>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <numeric>
 #include <set>
 #include <stdexcept>
@@ -156,6 +157,9 @@ struct IntraMatch {
 // node id.  ORBVocabulary::transform (below) builds it on the GPU.
 typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
 
+class BowMatcher;
+struct DMatch;
+
 // The extract / intra-match / triangulate entry points of MultiCameraFrame for ONE rig frame (the class also batches frames
 // through process_frames for throughput).  Image data: num_cams CV_8UC1 planes of the same size, tightly packed.
 class MultiCameraFrame {
@@ -170,7 +174,7 @@ public:
         if (!h_) throw std::runtime_error(std::string("mcs_rig_create: ") + mcs_last_error());
         kp_cap_ = mcs_rig_feature_capacity(h_);
         row_cap_ = mcs_rig_row_capacity(h_);
-        image_kps.resize(num_cams_); image_kps_undist.resize(num_cams_); image_descriptors.resize(num_cams_);
+        image_kps.resize(num_cams_); image_kps_undist.resize(num_cams_); image_descriptors.resize(num_cams_); BoW_feats.resize(num_cams_);
     }
     ~MultiCameraFrame() { mcs_rig_destroy(h_); }
     MultiCameraFrame(const MultiCameraFrame&) = delete;
@@ -356,6 +360,19 @@ public:
         }
     }
 
+    // BowMatching(cam1_ind, cam2_ind, indices_1, indices_2, kps1, kps2, words) (:946-1022): the per-node ratio-test matcher between two
+    // cameras' FeatureVectors (BoW_feats); like the reference it clears the index lists but APPENDS to kps1 / kps2.
+    inline void BowMatching(int cam1_ind, int cam2_ind, std::vector<unsigned int>& indices_1, std::vector<unsigned int>& indices_2,
+                            std::vector<mcs_keypoint>& kps1, std::vector<mcs_keypoint>& kps2, std::set<unsigned int>& words);
+    // computeIntraMatches_chained(matches, old) (:1290-1355): BowMatching between neighbouring cameras (j-1, j), |dy| < 50 gate on the
+    // undistorted keypoints, rows chained through the shared camera.  n_rays is left at its default, as in the reference.
+    inline void computeIntraMatches_chained(std::vector<IntraMatch>& matches, bool old);
+    // computeIntraMatches(matches, kps_1, kps_2) (:1365-1466): per camera pair (i < j) the BowMatching matches as DMatch(i_idx, j_idx, 0)
+    // with the (distorted) image_kps points.  x/y pairs in kps_1 / kps_2.
+    inline void computeIntraMatches(std::vector<std::vector<std::vector<DMatch>>>& matches,
+                                    std::vector<std::vector<std::vector<std::array<float, 2>>>>& kps_1,
+                                    std::vector<std::vector<std::vector<std::array<float, 2>>>>& kps_2);
+
     // Triangulation block of FrontEnd::obtainLfFeatures (FrontEnd.cpp:249-370): mask filter (masks: [num_cams][h][w] f32 or null),
     // N-view DLT, depth gate.  Returns the accepted rows in order (what the reference pushes to currentFrame->intraMatches);
     // single-view rows (mono candidates, :371-384) are returned in `mono_rows`.
@@ -518,6 +535,7 @@ private:
         m.matchIndexN.assign(row, row + num_cams_);
         for (int c = 0; c < 5 && c < num_cams_; c++) m.matchIndex[c] = row[c];
     }
+    std::shared_ptr<BowMatcher> bow_;  // created on first use by the BoW pair matchers
     std::vector<mcs_calib> calib_;
     mcs_rig* h_ = nullptr;
     int w_, h_img_, kp_cap_ = 0, row_cap_ = 0;
@@ -639,6 +657,78 @@ struct DMatch {
     int queryIdx = -1, trainIdx = -1;
     float distance = 0.f;
 };
+
+inline void MultiCameraFrame::BowMatching(int cam1_ind, int cam2_ind, std::vector<unsigned int>& indices_1, std::vector<unsigned int>& indices_2,
+                                          std::vector<mcs_keypoint>& kps1, std::vector<mcs_keypoint>& kps2, std::set<unsigned int>& words) {
+    if (!bow_) bow_ = std::make_shared<BowMatcher>();
+    bow_->BowMatching(BoW_feats.at(cam1_ind), BoW_feats.at(cam2_ind), image_descriptors[cam1_ind].data(),
+                      (int)image_descriptors[cam1_ind].size() / 32, image_descriptors[cam2_ind].data(),
+                      (int)image_descriptors[cam2_ind].size() / 32, indices_1, indices_2, &words);
+    for (size_t m = 0; m < indices_1.size(); m++) {
+        kps1.push_back(image_kps_undist[cam1_ind][indices_1[m]]);
+        kps2.push_back(image_kps_undist[cam2_ind][indices_2[m]]);
+    }
+}
+
+inline void MultiCameraFrame::computeIntraMatches_chained(std::vector<IntraMatch>& matches, bool /*old*/) {
+    matches.reserve(10000);
+    std::vector<std::vector<int>> inv(num_cams_);
+    for (int c = 0; c < num_cams_; c++) inv[c].assign(image_kps[c].size(), -1);
+    std::set<unsigned int> wordIds;
+    for (int j = 1; j < num_cams_; j++) {
+        const int i = j - 1;
+        std::vector<unsigned int> indices1, indices2;
+        std::vector<mcs_keypoint> kp1, kp2;
+        BowMatching(i, j, indices1, indices2, kp1, kp2, wordIds);
+        for (size_t k = 0; k < indices1.size(); k++) {
+            const int fi = (int)indices1[k], fj = (int)indices2[k];
+            const int row_i = inv[i][fi], row_j = inv[j][fj];
+            if (std::fabs(image_kps_undist[i][fi].y - image_kps_undist[j][fj].y) >= 50) continue;
+            if (row_i == -1 && row_j == -1) {
+                IntraMatch m;
+                m.matchIndexN.assign(num_cams_, -1);
+                m.matchIndexN[i] = fi; m.matchIndexN[j] = fj;
+                if (i < 5) m.matchIndex[i] = fi;
+                if (j < 5) m.matchIndex[j] = fj;
+                inv[i][fi] = inv[j][fj] = (int)matches.size();
+                matches.push_back(m);
+            } else if (row_j == -1) {  // :1340-1343 — as in the reference, row_i may be -1 here only if row_j is set, so row_i is valid
+                matches[row_i].matchIndexN[j] = fj;
+                if (j < 5) matches[row_i].matchIndex[j] = fj;
+                inv[j][fj] = row_i;
+            }
+        }
+    }
+}
+
+inline void MultiCameraFrame::computeIntraMatches(std::vector<std::vector<std::vector<DMatch>>>& matches,
+                                                  std::vector<std::vector<std::vector<std::array<float, 2>>>>& kps_1,
+                                                  std::vector<std::vector<std::vector<std::array<float, 2>>>>& kps_2) {
+    if ((int)BoW_feats.size() != num_cams_) throw std::invalid_argument("computeIntraMatches: BoW_feats must hold one FeatureVector per camera");
+    kps_1.clear();
+    kps_2.clear();
+    std::set<unsigned int> unused;
+    for (int i = 0; i + 1 < num_cams_; i++) {
+        matches.emplace_back();
+        kps_1.emplace_back();
+        kps_2.emplace_back();
+        for (int j = i + 1; j < num_cams_; j++) {
+            std::vector<unsigned int> i_ind, j_ind;
+            std::vector<mcs_keypoint> ku1, ku2;
+            BowMatching(i, j, i_ind, j_ind, ku1, ku2, unused);
+            std::vector<DMatch> m_vec(i_ind.size());
+            std::vector<std::array<float, 2>> p1(i_ind.size()), p2(i_ind.size());
+            for (size_t k = 0; k < i_ind.size(); k++) {
+                m_vec[k].queryIdx = (int)i_ind[k]; m_vec[k].trainIdx = (int)j_ind[k]; m_vec[k].distance = 0.f;
+                p1[k] = {image_kps[i][i_ind[k]].x, image_kps[i][i_ind[k]].y};
+                p2[k] = {image_kps[j][j_ind[k]].x, image_kps[j][j_ind[k]].y};
+            }
+            matches.back().push_back(m_vec);
+            kps_1.back().push_back(p1);
+            kps_2.back().push_back(p2);
+        }
+    }
+}
 
 // What FrontEnd::findInterMatches reads of a MultiCameraFrame (MultiCameraFrame.h:138-151): the frame's IntraMatch list
 // (triangulated rows first, mono features appended), the landmark ids and the number of triangulated rows.

@@ -393,6 +393,41 @@ def intra_matches_bow(descs, kps_undist, fvs, th_low=75, ratio=0.85):
     return rows[:M].copy(), nr[:M].copy(), words[:nw.value].copy()
 
 
+def intra_matches_chained(descs, kps_undist, fvs):
+    """computeIntraMatches_chained (MultiCameraFrame.cpp:1290-1355): BowMatching between cameras (j-1, j), |dy| < 50 on the undistorted
+    keypoints, rows chained through the shared camera.  int32 [M, num_cams]."""
+    nc = len(descs)
+    inv = [np.full(len(d), -1, np.int64) for d in descs]
+    rows = []
+    for j in range(1, nc):
+        i = j - 1
+        i1, i2, _, _ = bow_matching(descs[i], descs[j], fvs[i], fvs[j])
+        for fi, fj in zip(i1.tolist(), i2.tolist()):
+            ri, rj = inv[i][fi], inv[j][fj]
+            if abs(np.float32(kps_undist[i]["y"][fi]) - np.float32(kps_undist[j]["y"][fj])) >= 50:
+                continue
+            if ri == -1 and rj == -1:
+                r = [-1] * nc
+                r[i], r[j] = fi, fj
+                inv[i][fi] = inv[j][fj] = len(rows)
+                rows.append(r)
+            elif rj == -1:
+                rows[ri][j] = fj
+                inv[j][fj] = ri
+    return np.array(rows, np.int32).reshape(-1, nc)
+
+
+def intra_matches_dmatch(descs, kps, fvs):
+    """computeIntraMatches(matches, kps_1, kps_2) (MultiCameraFrame.cpp:1365-1466): {(i, j): (queryIdx, trainIdx, pts_i, pts_j)} per
+    camera pair i < j, points taken from the distorted image_kps."""
+    out = {}
+    for i in range(len(descs) - 1):
+        for j in range(i + 1, len(descs)):
+            i1, i2, _, _ = bow_matching(descs[i], descs[j], fvs[i], fvs[j])
+            out[(i, j)] = (i1, i2, np.stack([kps[i]["x"][i1], kps[i]["y"][i1]], 1), np.stack([kps[j]["x"][i2], kps[j]["y"][i2]], 1))
+    return out
+
+
 def _ptr_array(arrs):
     return (C.c_void_p * len(arrs))(*[a.ctypes.data if a is not None else None for a in arrs])
 

@@ -177,6 +177,21 @@ int main(int argc, char** argv) {
                     fprintf(f, "\n");
                 }
                 for (unsigned w : words) fprintf(f, "bowword %u\n", w);
+                std::vector<mcs_b200::IntraMatch> chained;
+                fr.computeIntraMatches_chained(chained, false);
+                for (auto& r : chained) {
+                    fprintf(f, "chainrow");
+                    for (int c = 0; c < C; c++) fprintf(f, " %d", r.matchIndexN[c]);
+                    fprintf(f, "\n");
+                }
+                std::vector<std::vector<std::vector<mcs_b200::DMatch>>> dm;
+                std::vector<std::vector<std::vector<std::array<float, 2>>>> k1, k2;
+                fr.computeIntraMatches(dm, k1, k2);
+                for (size_t i = 0; i < dm.size(); i++)
+                    for (size_t j = 0; j < dm[i].size(); j++)
+                        for (size_t k = 0; k < dm[i][j].size(); k++)
+                            fprintf(f, "dm %zu %zu %d %d %.9g %.9g %.9g %.9g\n", i, i + 1 + j, dm[i][j][k].queryIdx, dm[i][j][k].trainIdx,
+                                    k1[i][j][k][0], k1[i][j][k][1], k2[i][j][k][0], k2[i][j][k][1]);
             }
         }
         fclose(f);

@@ -584,6 +584,21 @@ def test_cpp_adaptor_bow_intra_matches(tmp_path, levelsup):
     assert len(rows) > 30 and (n_rays >= 3).any()
     assert np.array_equal(got[:, 1:], rows) and np.array_equal(got[:, 0], n_rays)
     assert [int(l.split()[1]) for l in lines if l.startswith("bowword ")] == words.tolist()
+    # the pairwise BoW variants on the same FeatureVectors: computeIntraMatches_chained (:1290-1355) and the DMatch overload (:1365-1466)
+    chained = np.array([list(map(int, l.split()[1:])) for l in lines if l.startswith("chainrow ")], np.int32).reshape(-1, 4)
+    exp_chain = O.intra_matches_chained(D, K, fvs)
+    assert len(exp_chain) > 20 and np.array_equal(chained, exp_chain)
+    dm = {}
+    for l in lines:
+        if l.startswith("dm "):
+            t = l.split()
+            dm.setdefault((int(t[1]), int(t[2])), []).append([float(v) for v in t[3:]])
+    exp_dm = O.intra_matches_dmatch(D, K, fvs)
+    assert sum(len(v[0]) for v in exp_dm.values()) > 60
+    for pair, (i1, i2, p1, p2) in exp_dm.items():
+        got_p = np.array(dm.get(pair, []), np.float64).reshape(-1, 6)
+        assert got_p[:, 0].tolist() == i1.tolist() and got_p[:, 1].tolist() == i2.tolist(), pair
+        assert np.array_equal(got_p[:, 2:4].astype(np.float32), p1) and np.array_equal(got_p[:, 4:6].astype(np.float32), p2)
 
 
 def test_config4_full_size_rig_frame():
