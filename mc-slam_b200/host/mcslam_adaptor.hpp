@@ -17,6 +17,8 @@
 #include <array>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -156,6 +158,142 @@ struct IntraMatch {
 // DBoW2::FeatureVector as the matchers read it: node id -> indices of the features that fell into that vocabulary node, ordered by
 // node id.  ORBVocabulary::transform (below) builds it on the GPU.
 typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
+
+// Kalibr camchain calibration file as the data readers parse it (MCDataUtils/src/RosDataReader.cpp:258-380, DatasetReader.cpp:169-268):
+// top-level nodes in file order, stopping at the first whose name does not contain "cam" (RosDataReader.cpp:266); per camera
+// `distortion_coeffs` (radtan: copied in order; otherwise equidistant-style k1 k2 -> slots 0, 1 and the third value -> slot 4, :293-304),
+// `resolution` (must be the same for all cameras), `intrinsics` fx fy cx cy, `rostopic`, and `T_cn_cnm1` (rows 0-2 -> R | t; absent ->
+// identity).  With camchain = true the transforms are composed towards camera 0: R_i = R * R_{i-1}, t_i = R * t_{i-1} + t (:343-350).
+// The file is OpenCV-FileStorage YAML; the subset Kalibr writes (block maps, flow sequences, `- [..]` rows, # comments) is parsed here.
+struct CamArrayConfig {
+    std::vector<mcs_calib> calib;          // K_mats_, R_mats_, t_vecs_, dist_coeffs_ per camera
+    std::vector<mcs_calib> calib_kalibr;   // the un-chained R_mats_kalibr / t_vecs_kalibr
+    std::vector<std::string> cam_topics;
+    int width = 0, height = 0;
+    int num_cams() const { return (int)calib.size(); }
+};
+
+inline CamArrayConfig read_kalibr_data(const std::string& path, bool radtan = true, bool camchain = true) {
+    FILE* fp = std::fopen(path.c_str(), "r");
+    if (!fp) throw std::runtime_error("read_kalibr_data: cannot open " + path);
+    struct Node { std::string name; std::map<std::string, std::string> scalars; std::map<std::string, std::vector<double>> lists; };
+    std::vector<Node> nodes;
+    std::string pending_key;  // key whose value is a block sequence on the following lines
+    int depth2_indent = -1;
+    auto strip = [](std::string v) {
+        size_t a = v.find_first_not_of(" \t\r\n"), b = v.find_last_not_of(" \t\r\n");
+        return a == std::string::npos ? std::string() : v.substr(a, b - a + 1);
+    };
+    auto numbers = [&](const std::string& v, std::vector<double>& out) {
+        const char* p = v.c_str();
+        while (*p) {
+            if ((*p >= '0' && *p <= '9') || *p == '-' || *p == '+' || *p == '.') {
+                char* e = nullptr;
+                const double d = std::strtod(p, &e);
+                if (e == p) { p++; continue; }
+                out.push_back(d);
+                p = e;
+            } else p++;
+        }
+    };
+    char buf[4096];
+    while (std::fgets(buf, sizeof buf, fp)) {
+        std::string line(buf);
+        for (size_t i = 0; i < line.size(); i++)  // comments: '#' at line start or after whitespace
+            if (line[i] == '#' && (i == 0 || line[i - 1] == ' ' || line[i - 1] == '\t')) { line.resize(i); break; }
+        if (strip(line).empty() || line[0] == '%' || line.compare(0, 3, "---") == 0) continue;
+        const int indent = (int)line.find_first_not_of(" \t");
+        const std::string body = strip(line);
+        if (indent == 0) {
+            const size_t c = body.find(':');
+            if (c == std::string::npos) continue;
+            Node n;
+            n.name = strip(body.substr(0, c));
+            nodes.push_back(n);
+            pending_key.clear();
+            depth2_indent = -1;
+            continue;
+        }
+        if (nodes.empty()) continue;
+        Node& n = nodes.back();
+        if (body[0] == '-') {  // a row of the pending block sequence
+            if (!pending_key.empty()) numbers(body.substr(1), n.lists[pending_key]);
+            continue;
+        }
+        if (depth2_indent < 0) depth2_indent = indent;
+        if (indent > depth2_indent) continue;  // deeper maps (imu / gps blocks) are not camera data
+        const size_t c = body.find(':');
+        if (c == std::string::npos) continue;
+        const std::string key = strip(body.substr(0, c));
+        std::string val = strip(body.substr(c + 1));
+        pending_key.clear();
+        if (val.empty()) { pending_key = key; n.lists[key]; continue; }
+        if (val[0] == '[') {
+            while (val.find(']') == std::string::npos && std::fgets(buf, sizeof buf, fp)) val += buf;  // flow sequence over several lines
+            numbers(val, n.lists[key]);
+        } else {
+            if (val.size() >= 2 && (val[0] == '"' || val[0] == '\'')) val = val.substr(1, val.size() - 2);
+            n.scalars[key] = val;
+        }
+    }
+    std::fclose(fp);
+    CamArrayConfig cfg;
+    for (const Node& n : nodes) {
+        if (n.name.find("cam") == std::string::npos) break;
+        mcs_calib c;
+        std::memset(&c, 0, sizeof c);
+        const int i = (int)cfg.calib.size();
+        auto need = [&](const char* key, size_t count) -> const std::vector<double>& {
+            auto it = n.lists.find(key);
+            if (it == n.lists.end() || it->second.size() < count) throw std::runtime_error("read_kalibr_data: " + n.name + " lacks " + key);
+            return it->second;
+        };
+        const std::vector<double>& dc = need("distortion_coeffs", radtan ? 0 : 3);
+        if (radtan) {
+            for (size_t j = 0; j < dc.size() && j < 5; j++) c.dist[j] = dc[j];
+        } else {
+            c.dist[0] = dc[0]; c.dist[1] = dc[1]; c.dist[4] = dc[2];
+        }
+        const std::vector<double>& res = need("resolution", 2);
+        if (i > 0) {
+            if ((int)res[0] != cfg.width || (int)res[1] != cfg.height) throw std::runtime_error("Resolution of all images is not the same!");
+        } else {
+            cfg.width = (int)res[0]; cfg.height = (int)res[1];
+        }
+        const std::vector<double>& in = need("intrinsics", 4);
+        c.K[0] = in[0]; c.K[4] = in[1]; c.K[2] = in[2]; c.K[5] = in[3]; c.K[8] = 1.0;
+        auto tn = n.lists.find("T_cn_cnm1");
+        if (tn == n.lists.end() || tn->second.empty()) {
+            c.R[0] = c.R[4] = c.R[8] = 1.0;
+        } else {
+            if (tn->second.size() < 12) throw std::runtime_error("read_kalibr_data: " + n.name + " has a short T_cn_cnm1");
+            for (int r = 0; r < 3; r++) {
+                for (int k = 0; k < 3; k++) c.R[r * 3 + k] = tn->second[r * 4 + k];
+                c.t[r] = tn->second[r * 4 + 3];
+            }
+        }
+        cfg.calib_kalibr.push_back(c);
+        if (camchain && i > 0) {
+            const mcs_calib& p = cfg.calib[i - 1];
+            mcs_calib o = c;
+            for (int r = 0; r < 3; r++) {
+                for (int k = 0; k < 3; k++) {
+                    double acc = 0;
+                    for (int m = 0; m < 3; m++) acc += c.R[r * 3 + m] * p.R[m * 3 + k];
+                    o.R[r * 3 + k] = acc;
+                }
+                double acc = 0;
+                for (int m = 0; m < 3; m++) acc += c.R[r * 3 + m] * p.t[m];
+                o.t[r] = acc + c.t[r];
+            }
+            c = o;
+        }
+        cfg.calib.push_back(c);
+        auto topic = n.scalars.find("rostopic");
+        cfg.cam_topics.push_back(topic == n.scalars.end() ? std::string() : topic->second);
+    }
+    return cfg;
+}
 
 class BowMatcher;
 struct DMatch;

@@ -129,6 +129,28 @@ int main(int argc, char** argv) {
             return 3;
         }
     }
+    if (argc >= 6 && std::string(argv[1]) == "calib") {  // calib <yaml> <radtan 0|1> <camchain 0|1> <out>: the Kalibr camchain reader
+        try {
+            mcs_b200::CamArrayConfig cfg = mcs_b200::read_kalibr_data(argv[2], atoi(argv[3]) != 0, atoi(argv[4]) != 0);
+            FILE* f = fopen(argv[5], "w");
+            fprintf(f, "size %d %d %d\n", cfg.num_cams(), cfg.width, cfg.height);
+            for (int c = 0; c < cfg.num_cams(); c++) {
+                fprintf(f, "topic %s\n", cfg.cam_topics[c].c_str());
+                const double* v = (const double*)&cfg.calib[c];
+                fprintf(f, "cam");
+                for (int k = 0; k < 26; k++) fprintf(f, " %.17g", v[k]);
+                fprintf(f, "\nraw");
+                v = (const double*)&cfg.calib_kalibr[c];
+                for (int k = 0; k < 26; k++) fprintf(f, " %.17g", v[k]);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+            return 0;
+        } catch (const std::exception& e) {
+            fprintf(stderr, "adaptor: %s\n", e.what());
+            return 3;
+        }
+    }
     if (argc < 6) return 2;
     const int C = atoi(argv[2]), w = atoi(argv[3]), h = atoi(argv[4]);
     std::vector<uint8_t> img((size_t)C * w * h);

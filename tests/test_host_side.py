@@ -100,3 +100,110 @@ def test_cpp_adaptor_compiles_and_fails_loudly_without_gpu(tmp_path):
     (tmp_path / "im.bin.calib").write_bytes(bytes(26 * 8))
     out = subprocess.run([exe, str(img), "1", "16", "16", str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=120)
     assert out.returncode == 3 and "no CUDA device" in out.stderr
+
+
+_CAMCHAIN = """%YAML:1.0
+cam0:
+  cam_overlaps: [1, 2]
+  camera_model: pinhole
+  distortion_coeffs: [-0.3763, 0.2684, 0.0016283, 0.0014]   # k1 k2 p1 p2
+  distortion_model: radtan
+  intrinsics: [1844.36, 1844.33, 598.72, 485.86]
+  resolution: [1224, 1024]
+  rostopic: /camera_array/cam0/image_raw
+  # a comment line
+cam1:
+  T_cn_cnm1:
+    - [0.99997941, -0.00226848, -0.00600149, -0.66233802]
+    - [0.00225066, 0.99999304, -0.00297441, -0.00501759]
+    - [0.00600820, 0.00296084, 0.99997756, 0.01280345]
+    - [0.0, 0.0, 0.0, 1.0]
+  cam_overlaps: [0, 2]
+  camera_model: pinhole
+  distortion_coeffs: [-0.3587, 0.2540, 0.0030,
+                      -0.00076]
+  distortion_model: radtan
+  intrinsics: [1827.67, 1827.60, 622.98, 492.40]
+  resolution: [1224, 1024]
+  rostopic: /camera_array/cam2/image_raw
+
+cam2:
+  T_cn_cnm1:
+    - [0.99997123, -0.00580741, -0.00487955, -0.66276135]
+    - [0.00577088, 0.99995546, -0.00746730, -0.00717784]
+    - [0.00492270, 0.00743893, 0.99996021, -1.0680037e-02]
+    - [0.0, 0.0, 0.0, 1.0]
+  camera_model: pinhole
+  distortion_coeffs: [-0.3590, 0.1732, 0.0015, -0.00076, 0.01]
+  distortion_model: radtan
+  intrinsics: [1838.76, 1839.26, 632.04, 487.11]
+  resolution: [1224, 1024]
+  rostopic: /camera_array/cam4/image_raw
+
+imu:
+  rostopic: /imu/imu_uncompensated
+  acc_noise: 0.001119    # accelerometer measurement noise standard deviation.
+  Tbc:
+    - [-8.58e-04,  6.61e-03,  9.99e-01,  8.20e-02]
+    - [ 9.99e-01,  3.15e-03,  8.37e-04, -6.57e-01]
+    - [0.,          0.,          0.,          1.        ]
+cam9:
+  intrinsics: [1, 2, 3, 4]
+"""
+
+
+def _camchain_expect(text, radtan, camchain):
+    import yaml
+    doc = yaml.safe_load(text.split("\n", 1)[1])
+    out, raw = [], []
+    for name, f in doc.items():
+        if "cam" not in name:
+            break  # RosDataReader.cpp:266
+        dc = f["distortion_coeffs"]
+        dist = np.zeros(5)
+        if radtan:
+            dist[:len(dc)] = dc
+        else:
+            dist[0], dist[1], dist[4] = dc[0], dc[1], dc[2]
+        K = np.zeros((3, 3))
+        K[0, 0], K[1, 1], K[0, 2], K[1, 2], K[2, 2] = *f["intrinsics"], 1.0
+        R, t = np.eye(3), np.zeros(3)
+        if "T_cn_cnm1" in f:
+            T = np.array(f["T_cn_cnm1"], np.float64)
+            R, t = T[:3, :3].copy(), T[:3, 3].copy()
+        raw.append(np.concatenate([K.ravel(), R.ravel(), t, dist]))
+        if camchain and out:
+            Rp, tp = out[-1][9:18].reshape(3, 3), out[-1][18:21]
+            R, t = R @ Rp, R @ tp + t
+        out.append(np.concatenate([K.ravel(), R.ravel(), t, dist]))
+    return np.array(out), np.array(raw), [f.get("rostopic", "") for n, f in doc.items()][:len(out)]
+
+
+@pytest.mark.parametrize("radtan,camchain", [(1, 1), (0, 1), (1, 0)])
+def test_kalibr_camchain_reader(tmp_path, radtan, camchain):
+    """mcs_b200::read_kalibr_data (the Kalibr camchain format of MCDataUtils/src/RosDataReader.cpp:258-380 / DatasetReader.cpp:169-268)
+    against PyYAML + numpy on a file with comments, a flow list over two lines, 4- and 5-entry distortion lists and an imu block that
+    ends the camera list; plus the reference's own calibration files when they are present."""
+    exe = _build_adaptor(tmp_path)
+    files = [("synthetic", _CAMCHAIN)]
+    for rel in ("MCApps/params/nuance_calib/nuance.yaml", "MCApps/params/zed_calib/calib_zed.yaml"):
+        path = os.path.join("/root/reference", rel)
+        if os.path.exists(path):
+            files.append((rel, open(path).read()))
+    for name, text in files:
+        (tmp_path / "c.yaml").write_text(text)
+        out = subprocess.run([exe, "calib", str(tmp_path / "c.yaml"), str(radtan), str(camchain), str(tmp_path / "c.txt")],
+                             capture_output=True, text=True, timeout=60)
+        assert out.returncode == 0, (name, out.stderr)
+        lines = (tmp_path / "c.txt").read_text().splitlines()
+        exp, raw, topics = _camchain_expect(text, radtan, camchain)
+        head = lines[0].split()
+        assert int(head[1]) == len(exp) >= 2 and (int(head[2]), int(head[3])) in ((1224, 1024), (640, 360)), name
+        got = np.array([[float(v) for v in l.split()[1:]] for l in lines if l.startswith("cam ")])
+        got_raw = np.array([[float(v) for v in l.split()[1:]] for l in lines if l.startswith("raw ")])
+        assert np.array_equal(got_raw, raw), name  # parsed values bit-exact
+        assert np.allclose(got, exp, rtol=0, atol=1e-15) and np.array_equal(got[:, :9], exp[:, :9]) and np.array_equal(got[:, 21:], exp[:, 21:]), name
+        assert [l.split(" ", 1)[1] for l in lines if l.startswith("topic ")] == topics, name
+    (tmp_path / "bad.yaml").write_text(_CAMCHAIN.replace("resolution: [1224, 1024]\n  rostopic: /camera_array/cam2", "resolution: [640, 480]\n  rostopic: /camera_array/cam2"))
+    out = subprocess.run([exe, "calib", str(tmp_path / "bad.yaml"), "1", "1", str(tmp_path / "c.txt")], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "Resolution of all images is not the same" in out.stderr
