@@ -190,6 +190,8 @@ def run_gpu(args, rank, world, local):
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # one process per GPU: keep this rank's host thread and its pinned staging buffers on the GPU's own NUMA node
+    cpus_bound = 0 if os.environ.get("MCS_NO_AFFINITY") else M.lib().mcs_bind_host_thread(local)
     F = args.frames
     calib, frames = make_workload(F, args.distinct, rank)
     rig = M.RigFrames(calib, W, H, nfeatures=NFEAT, max_frames=F, device=local)
@@ -248,7 +250,7 @@ def run_gpu(args, rank, world, local):
     host_step()  # leave the results of a full (chunked, host-buffer) step in the handle for the parity block
     kc, n_rows, n_acc = rig.counts(0)
     d2h = rig_d2h_bytes(rig, F)
-    return dict(rig=rig, calib=calib, frames=frames, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches, clocks=clk, stage_ms=stage_ms,
+    return dict(rig=rig, calib=calib, frames=frames, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches, clocks=clk, stage_ms=stage_ms, cpus_bound=cpus_bound,
                 counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, F=F, Fp=Fp, dist=dist)
 
 
@@ -353,7 +355,7 @@ def main():
         "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": F, "distinct_scenes": args.distinct,
                    "chunk_frames": int(os.environ.get("MCS_CHUNK_FRAMES", "64")),
                    "l2": "per-step working set (%.0f MB of images + pyramids per GPU) exceeds the 126 MB L2" % (F * NCAM * (W * H + 1.3e6) / 1e6),
-                   "sharding": "by rig frame, no collective"},
+                   "sharding": "by rig frame, no collective", "host_cpus_bound_to_gpu_numa_node": int(r["cpus_bound"])},
         "e2e": {"value": e2e, "unit": "rig-frames/s", "h2d_bytes_per_step": int(F * NCAM * W * H), "d2h_bytes_per_step": int(r["d2h"]),
                 "ms_per_step": r["ms_e2e"] / steps},
         "gpu_launches": int(r["launches"]),

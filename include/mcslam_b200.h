@@ -56,6 +56,9 @@ typedef struct mcs_calib {
 
 MCS_API const char* mcs_last_error(void); /* thread-local, never NULL */
 MCS_API int mcs_device_count(void);
+/* Pin the calling host thread to the CPUs local to GPU `device` (NUMA node of its PCIe root); call before creating handles and pinned
+ * buffers in a one-process-per-GPU host.  Returns the CPU count of the set, 0 if the topology is not exposed, < 0 on a bad device. */
+MCS_API int mcs_bind_host_thread(int device);
 MCS_API const char* mcs_version(void);
 
 /* ------------------------------------------------------------------------------------------------------------------

@@ -29,7 +29,7 @@ class _Landmarks(C.Structure):
 
 
 EXPORTS = [
-    "mcs_last_error", "mcs_device_count", "mcs_version", "mcs_extractor_create", "mcs_extractor_destroy", "mcs_extractor_set_orientation",
+    "mcs_last_error", "mcs_device_count", "mcs_bind_host_thread", "mcs_version", "mcs_extractor_create", "mcs_extractor_destroy", "mcs_extractor_set_orientation",
     "mcs_extractor_capacity", "mcs_extract", "mcs_extract_batch", "mcs_extractor_get_tables", "mcs_extractor_level_size",
     "mcs_extractor_download_level", "mcs_extractor_download_candidates", "mcs_rig_create", "mcs_rig_destroy", "mcs_rig_feature_capacity",
     "mcs_rig_row_capacity", "mcs_rig_set_orientation", "mcs_rig_extract", "mcs_rig_extract_device", "mcs_rig_get_features",

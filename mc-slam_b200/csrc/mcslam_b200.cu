@@ -1,5 +1,6 @@
 // mcslam_b200.cu — host engine + C ABI (include/mcslam_b200.h) over the sm_100a kernels in extract_kernels.cuh and
 // match_kernels.cuh.  No CPU fallback: every stage is a kernel launch; creation fails without a CUDA device.
+#include <sched.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -693,6 +694,34 @@ const char* mcs_version(void) { return "mcslam_b200 0.1 (sm_100a)"; }
 int mcs_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+// Pin the calling host thread to the CPUs next to GPU `device` (its PCIe root's NUMA node, /sys/bus/pci/devices/<bdf>/local_cpulist):
+// pinned staging buffers allocated afterwards are first-touched on that node, so the H2D / D2H copies of a multi-GPU host do not
+// cross the socket interconnect.  Returns the number of CPUs in the set, 0 when the topology is not exposed (nothing changed).
+int mcs_bind_host_thread(int device) {
+    char bdf[32] = {0};
+    if (cudaDeviceGetPCIBusId(bdf, sizeof bdf, device) != cudaSuccess) { set_err("mcs_bind_host_thread: bad device"); return MCS_ERR_ARG; }
+    for (char* c = bdf; *c; c++) *c = (char)tolower(*c);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bdf + "/local_cpulist";
+    FILE* f = fopen(path.c_str(), "r");
+    if (!f) return 0;
+    char line[4096] = {0};
+    const bool got = fgets(line, sizeof line, f) != nullptr;
+    fclose(f);
+    if (!got) return 0;
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    int n = 0;
+    for (char* p = line; *p;) {  // "0-31,64-95"
+        if (*p < '0' || *p > '9') { p++; continue; }
+        const long a = strtol(p, &p, 10);
+        long b = a;
+        if (*p == '-') b = strtol(p + 1, &p, 10);
+        for (long c = a; c <= b && c < CPU_SETSIZE; c++) { CPU_SET((int)c, &set); n++; }
+    }
+    if (n == 0 || sched_setaffinity(0, sizeof set, &set) != 0) return 0;
     return n;
 }
 
