@@ -584,6 +584,228 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K3s  per-cell FAST on STRIPS of cells.  One block = up to 5 horizontally adjacent cells of one cell row.  The computed
+// interiors of neighbouring cells tile the level without overlap (cell j computes columns [iniX_j + 3, iniX_j + wCell + 3)), so the
+// corner score of a pixel is the same whichever cell it is computed for; what is per cell is (a) the NMS rule "neighbours outside
+// the cell's interior score 0" and (b) the iniTh -> minTh retry of a cell that returned nothing (:842-845).  The strip kernel
+// therefore stages one tile for the whole strip (16-byte copies at the image's own alignment, no shifting), runs the pre-test and
+// the arc strength once per pixel, and applies (a) with a cell-boundary mask in the NMS and (b) by re-scanning only the cells that
+// stayed empty.  Against one block per cell this removes the 3 px halo columns between cells from the staging, most of the
+// per-block prologue and every block-wide scan:
+//   * each warp compacts the (pixel, polarity) entries of its own 32 pixel groups into a private stack in shared memory and
+//     evaluates them 32 at a time as soon as 32 are pending (dense warps, no block barrier, no flag array);
+//   * corners go to a block list through one shared atomic per warp batch; the NMS walks that list and appends survivors to the
+//     level's candidate list with one global atomic per warp batch (the list is unordered; the octree kernel orders it).
+// Tile x coordinates are image x - (iniX & ~15); the score tile uses the same coordinates with one zero row above and below.
+// ------------------------------------------------------------------------------------------------------------
+#define MCS_FS_NT 256
+#define MCS_FS_TP 208  // tile and score pitch in bytes: 15 (alignment) + 187 (interior) + 6 (halo)
+#define MCS_FS_WQ 288  // entries per warp stack: < 32 pending + 32 groups x 8
+#define MCS_FS_MAXW 187
+
+struct FastStripCtx {
+    const uint8_t* tile;
+    uint8_t* score;
+    uint16_t* wq;
+    uint16_t* corner;
+    int* ncorner;
+    int ih, lane;
+};
+
+// one batch of the warp's stack: arc strength (= cv::FAST's score), corner <=> strength >= th
+__device__ __forceinline__ void fs_eval(const FastStripCtx& X, bool active, int e, int th) {
+    constexpr int TP = MCS_FS_TP;
+    bool corner = false;
+    if (active) {
+        const int ly = (e >> 8) & 0x7F, tx = e & 0xFF;
+        const int sc = fast_strength_pol(X.tile + (ly + 3) * TP + tx, TP, (e & 0x8000) ? -1 : 1);
+        corner = sc >= th && sc > 0;
+        if (corner) X.score[(ly + 1) * TP + tx] = (uint8_t)min(sc, 255);
+    }
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, corner);
+    if (m) {
+        int base = 0;
+        if (X.lane == 0) base = atomicAdd(X.ncorner, __popc(m));
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (corner) X.corner[base + __popc(m & ((1u << X.lane) - 1u))] = (uint16_t)(e & 0x7FFF);
+    }
+}
+
+// pre-test + strength of the interior columns [xa, xb) (tile coordinates) of all ih rows at threshold th
+__device__ __forceinline__ void fs_scan(const FastStripCtx& X, int th, int xa, int xb, uint32_t mg, int warp) {
+    constexpr int TPW = MCS_FS_TP / 4;
+    const int ga = xa >> 2, nG = ((xb - 1) >> 2) - ga + 1;
+    const int ngroups = nG * X.ih;
+    const uint32_t K1 = (uint32_t)(0x8000 - th - 1) * 0x00010001u;  // bit 15 of (a + K1 - b) per lane  <=>  a - b > th
+    int pending = 0;
+    for (int gb = warp * 32; gb < ngroups; gb += MCS_FS_NT) {
+        const int gi = gb + X.lane;
+        uint32_t f = 0, ebase = 0;
+        if (gi < ngroups) {
+            const int ly = (int)(((uint32_t)gi * mg) >> 20), g = ga + gi - ly * nG;
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(X.tile) + (ly + 3) * TPW + g;
+            const uint32_t W0 = row[-1], W1 = row[0], W2 = row[1];
+            const uint32_t Up = row[-3 * TPW], Dn = row[3 * TPW];
+            const uint32_t Lf = __funnelshift_r(W0, W1, 8), Rt = __funnelshift_r(W1, W2, 24);
+            const uint32_t A0 = row[-1 - 2 * TPW], A1 = row[-2 * TPW], A2 = row[1 - 2 * TPW];
+            const uint32_t B0 = row[-1 + 2 * TPW], B1 = row[2 * TPW], B2 = row[1 + 2 * TPW];
+            const uint32_t UL = __funnelshift_r(A0, A1, 16), UR = __funnelshift_r(A1, A2, 16);
+            const uint32_t DL = __funnelshift_r(B0, B1, 16), DR = __funnelshift_r(B1, B2, 16);
+#pragma unroll
+            for (int hpair = 0; hpair < 2; hpair++) {
+                const uint32_t sel = hpair ? 0x4342u : 0x4140u;
+                const uint32_t c2 = __byte_perm(W1, 0, sel), u2 = __byte_perm(Up, 0, sel), d2 = __byte_perm(Dn, 0, sel);
+                const uint32_t l2 = __byte_perm(Lf, 0, sel), r2 = __byte_perm(Rt, 0, sel);
+                const uint32_t ul = __byte_perm(UL, 0, sel), dr = __byte_perm(DR, 0, sel);
+                const uint32_t ur = __byte_perm(UR, 0, sel), dl = __byte_perm(DL, 0, sel);
+                // the four opposite pairs (0,8) (4,12) (2,10) (6,14): a 9-arc holds at least one pixel of each
+                const uint32_t bmin = __vimin3_u16x2(__vminu2(__vmaxu2(u2, d2), __vmaxu2(l2, r2)), __vmaxu2(ul, dr), __vmaxu2(ur, dl));
+                const uint32_t dmax = __vimax3_u16x2(__vmaxu2(__vminu2(u2, d2), __vminu2(l2, r2)), __vminu2(ul, dr), __vminu2(ur, dl));
+                const uint32_t Bf = bmin + K1 - c2, Df = c2 + K1 - dmax;
+                const uint32_t t2 = ((Bf >> 15) & 0x00010001u) | ((Df >> 14) & 0x00020002u);
+                f |= ((t2 | (t2 >> 14)) & 0xFu) << (4 * hpair);
+            }
+            // pixel e of the group is inside [xa, xb)  <=>  lo <= e < hi
+            const int lo = max(xa - 4 * g, 0), hi = min(xb - 4 * g, 4);
+            f &= ((1u << (2 * hi)) - 1u) & ~((1u << (2 * lo)) - 1u);
+            ebase = (uint32_t)((ly << 8) | (4 * g));
+        }
+        const int cnt = __popc(f);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (X.lane >= o) incl += v;
+        }
+        const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (total == 0) continue;  // warp-uniform
+        int pos = pending + incl - cnt;
+        if (f) {
+#pragma unroll
+            for (int b = 0; b < 8; b++) {  // predicated stores
+                if (f & (1u << b)) {
+                    X.wq[pos] = (uint16_t)(((b & 1) << 15) | (ebase + (b >> 1)));
+                    pos++;
+                }
+            }
+        }
+        pending += total;
+        __syncwarp();
+        while (pending >= 32) {
+            pending -= 32;
+            fs_eval(X, true, X.wq[pending + X.lane], th);
+            __syncwarp();
+        }
+    }
+    if (pending > 0) {
+        const bool act = X.lane < pending;
+        fs_eval(X, act, act ? X.wq[X.lane] : 0, th);
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_constant__ McsPlan P, ImageSet S,
+                                                                    const uint4* __restrict__ strip_tab, uint32_t* __restrict__ cand,
+                                                                    int* __restrict__ cand_count) {
+    extern __shared__ __align__(16) unsigned char s_fs[];
+    __shared__ int s_ncorner, s_cellcnt[8];
+    constexpr int TP = MCS_FS_TP;
+    const int img = blockIdx.y;
+    // host-built strip record (build_strip_table)
+    const uint4 ra = __ldg(strip_tab + 2 * blockIdx.x), rb = __ldg(strip_tab + 2 * blockIdx.x + 1);
+    const int level = (int)(ra.x & 0xFFu), ncells = (int)((ra.x >> 8) & 0xFFu), wcell = (int)(ra.x >> 16);
+    const int iniX = (int)(ra.y & 0xFFFFu), iniY = (int)(ra.y >> 16);
+    const int wint = (int)(ra.z & 0xFFFFu), ih = (int)(ra.z >> 16);  // computed interior of the strip
+    const int xoff = (int)(ra.w & 0xFFFFu), yoff = (int)(ra.w >> 16);
+    const uint32_t mg_groups = rb.x, mg_quads = rb.y, mg_cell = rb.z;
+    const McsLevel& Lv = P.L[level];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int pitch;
+    const uint8_t* src = level_ptr(P, S, img, level, pitch);
+    const int ox = iniX & ~15;         // image x of tile byte 0
+    const int x0 = iniX + 3 - ox;      // tile x of interior column 0 (3..18)
+    const int ch = ih + 6;
+    uint8_t* s_tile = s_fs;
+    uint8_t* s_score = s_fs + P.fs_ofs_score;
+    FastStripCtx X;
+    X.tile = s_tile;
+    X.score = s_score;
+    X.wq = reinterpret_cast<uint16_t*>(s_fs + P.fs_ofs_wq) + warp * MCS_FS_WQ;
+    X.corner = reinterpret_cast<uint16_t*>(s_fs + P.fs_ofs_corner);
+    X.ncorner = &s_ncorner;
+    X.ih = ih;
+    X.lane = lane;
+    {   // stage the sub-image rows [iniY, iniY + ch) as 16-byte copies (rows are 16-byte aligned: make_set), zero the score tile
+        const int nq = (x0 + wint + 3 + 15) >> 4;
+        const uint8_t* g0 = src + (size_t)iniY * pitch + ox;
+        for (int t = threadIdx.x; t < nq * ch; t += MCS_FS_NT) {
+            const int r = (int)(((uint32_t)t * mg_quads) >> 20), c = t - r * nq;
+            *reinterpret_cast<uint4*>(s_tile + r * TP + c * 16) = __ldg(reinterpret_cast<const uint4*>(g0 + (size_t)r * pitch) + c);
+        }
+        for (int t = threadIdx.x; t < (ih + 2) * (TP / 16); t += MCS_FS_NT) reinterpret_cast<uint4*>(s_score)[t] = make_uint4(0, 0, 0, 0);
+        if (threadIdx.x < 8) s_cellcnt[threadIdx.x] = 0;
+        if (threadIdx.x == 0) s_ncorner = 0;
+    }
+    __syncthreads();
+    uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
+    int* cnt = cand_count + img * P.nlevels + level;
+    // strict-'>' 8-neighbour NMS over the corner list; a neighbour in another cell of the strip scores 0 for this pixel
+    auto nms = [&]() {
+        const int nc = s_ncorner;
+        for (int q0 = 0; q0 < nc; q0 += MCS_FS_NT) {
+            const int q = q0 + threadIdx.x;
+            bool surv = false;
+            uint32_t rec = 0;
+            if (q < nc) {
+                const int e = X.corner[q];
+                const int ly = (e >> 8) & 0x7F, tx = e & 0xFF;
+                const uint8_t* qp = &s_score[(ly + 1) * TP + tx];
+                const int sc = qp[0];
+                const int xi = tx - x0;
+                const int ci = (int)(((uint32_t)xi * mg_cell) >> 20), xc = xi - ci * wcell;
+                int n = max((int)qp[-TP], (int)qp[TP]);
+                if (xc != 0) n = max(n, max(max((int)qp[-TP - 1], (int)qp[-1]), (int)qp[TP - 1]));
+                if (xc != wcell - 1) n = max(n, max(max((int)qp[-TP + 1], (int)qp[1]), (int)qp[TP + 1]));
+                surv = sc > n;
+                if (surv) {
+                    atomicAdd(&s_cellcnt[ci], 1);
+                    // keypoint in ROI coordinates: FAST x in the cell's sub-image shifted by j * wCell (:864-865)
+                    rec = mcs_oct::pack_cand(xi + xoff, ly + yoff, sc);
+                }
+            }
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, surv);
+            if (m) {
+                int p0 = 0;
+                if (lane == 0) p0 = atomicAdd(cnt, __popc(m));
+                p0 = __shfl_sync(0xFFFFFFFFu, p0, 0) + __popc(m & ((1u << lane) - 1u));
+                if (surv && p0 < Lv.cand_cap) out[p0] = rec;
+            }
+        }
+    };
+    // FAST(cell, iniThFAST) for every cell of the strip
+    fs_scan(X, P.ini_th, x0, x0 + wint, mg_groups, warp);
+    __syncthreads();
+    nms();
+    if (P.min_th >= P.ini_th) return;  // the retry could only find a subset of nothing
+    __syncthreads();
+    // only for the cells that returned nothing: FAST(cell, minThFAST)  (:842-845)
+    unsigned failed = 0;
+    for (int c = 0; c < ncells; c++)
+        if (s_cellcnt[c] == 0) failed |= 1u << c;
+    if (!failed) return;  // block-uniform
+    if (threadIdx.x == 0) s_ncorner = 0;
+    __syncthreads();
+    for (int c = 0; c < ncells; c++) {
+        if (!(failed & (1u << c))) continue;
+        const int xa = x0 + c * wcell, xb = min(xa + wcell, x0 + wint);
+        const int nG = ((xb - 1) >> 2) - (xa >> 2) + 1;  // <= 19
+        fs_scan(X, P.min_th, xa, xb, c_magic20[nG], warp);
+    }
+    __syncthreads();
+    nms();
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K4  DistributeOctTree.  One block per (level, image); algorithm in octree_core.h, executed with a CUDA block context.
 // ------------------------------------------------------------------------------------------------------------
 #ifndef MCS_OCT_NT

@@ -298,6 +298,64 @@ void build_cell_table(const McsPlan& P, std::vector<uint4>& tab) {
     }
 }
 
+// Strips of the FAST cell grid for fast_strips_kernel: up to 187 interior columns (<= 5 cells) of one cell row, the same cells
+// build_cell_table lists (skip rules of :809, :818).  Two uint4 per strip:
+//   a.x = level | cells << 8 | wCell << 16, a.y = iniX | iniY << 16 (first cell), a.z = interior width | height << 16,
+//   a.w = candidate coordinate offset (3 + j0 * wCell) | (3 + i * hCell) << 16
+//   b.x / b.y / b.z = ceil(2^20 / n) for n = pixel groups per row, 16-byte words per tile row, wCell (index divisions in the kernel;
+//   exact for the operand ranges of one strip, verified here).
+// Also sizes the kernel's shared memory (tile rows, score rows, corner list) for the largest strip of the plan.
+bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
+    tab.clear();
+    int chm = 7, area = 1;
+    auto magic = [](int n, int tmax) -> uint32_t {
+        const uint32_t m = ((1u << 20) + n - 1) / n;
+        for (int t = 0; t <= tmax; t++)
+            if ((int)(((uint64_t)t * m) >> 20) != t / n || (uint64_t)t * m >= (1ull << 32)) return 0;
+        return m;
+    };
+    for (int l = 0; l < P.nlevels; l++) {
+        const McsLevel& L = P.L[l];
+        const int maxBX = L.w - MCS_MIN_BORDER, maxBY = L.h - MCS_MIN_BORDER;
+        if (L.n_cols < 1) continue;
+        int live_cols = 0;  // cells of a row the reference runs
+        for (int j = 0; j < L.n_cols; j++)
+            if (MCS_MIN_BORDER + j * L.w_cell < maxBX - 6) live_cols = j + 1;
+        if (live_cols < 1) continue;
+        const int kmax = std::max(1, MCS_FS_MAXW / L.w_cell);
+        const int nstrips = (live_cols + kmax - 1) / kmax;
+        for (int i = 0; i < L.n_rows; i++) {
+            const int iniY = MCS_MIN_BORDER + i * L.h_cell;
+            if (iniY >= maxBY - 3) continue;
+            const int ch = std::min(iniY + L.h_cell + 6, maxBY) - iniY;
+            if (ch - 6 <= 0) continue;
+            for (int s = 0; s < nstrips; s++) {
+                const int j0 = (int)((long long)s * live_cols / nstrips), j1 = (int)((long long)(s + 1) * live_cols / nstrips);
+                const int iniX = MCS_MIN_BORDER + j0 * L.w_cell;
+                const int endX = std::min(MCS_MIN_BORDER + (j1 - 1) * L.w_cell + L.w_cell + 6, maxBX);
+                const int wint = endX - iniX - 6, ih = ch - 6;
+                if (wint < 1 || wint > MCS_FS_MAXW || j1 - j0 > 8) { set_err("internal: FAST strip geometry"); return false; }
+                const int x0 = (iniX & 15) + 3;
+                const int nG = ((x0 + wint - 1) >> 2) - (x0 >> 2) + 1, nq = (x0 + wint + 3 + 15) >> 4;
+                const uint32_t m1 = magic(nG, nG * ih), m2 = magic(nq, nq * ch), m3 = magic(L.w_cell, 255);
+                if (!m1 || !m2 || !m3) { set_err("internal: FAST strip index division"); return false; }
+                tab.push_back(make_uint4((unsigned)l | ((unsigned)(j1 - j0) << 8) | ((unsigned)L.w_cell << 16), (unsigned)iniX | ((unsigned)iniY << 16),
+                                         (unsigned)wint | ((unsigned)ih << 16),
+                                         (unsigned)(3 + j0 * L.w_cell) | ((unsigned)(3 + i * L.h_cell) << 16)));
+                tab.push_back(make_uint4(m1, m2, m3, 0));
+                chm = std::max(chm, ch);
+                area = std::max(area, wint * ih);
+            }
+        }
+    }
+    int o = align_up(MCS_FS_TP * chm + 16, 16);
+    P.fs_ofs_score = o; o += align_up(MCS_FS_TP * (chm - 6 + 2), 16);
+    P.fs_ofs_wq = o; o += (MCS_FS_NT / 32) * MCS_FS_WQ * 2;
+    P.fs_ofs_corner = o; o += align_up(area * 2, 16);
+    P.fs_smem_bytes = o;
+    return true;
+}
+
 }  // namespace
 
 // =================================================================================================================
@@ -320,6 +378,9 @@ struct Engine {
     int2 *d_xtab = nullptr, *d_ytab = nullptr;
     int sm_count_ = 148;
     uint4* d_cell_tab = nullptr;  // FAST cell records (build_cell_table)
+    uint4* d_strip_tab = nullptr;  // FAST strip records (build_strip_table)
+    int n_fast_strips = 0;
+    bool fast_per_cell = false;  // MCS_FAST_CELLS=1: the one-block-per-cell kernel (A/B runs)
     int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
     int rs_xw_ofs[MCS_PLAN_MAX_LEVELS] = {}, rs_yw_ofs[MCS_PLAN_MAX_LEVELS] = {};
     bool rs_sel_ok = false;
@@ -346,12 +407,12 @@ struct Engine {
     ~Engine() { release(); }
 
     void free_all() {
-        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_rs_tab); cudaFree(d_cand); cudaFree(d_sel);
+        cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_strip_tab); cudaFree(d_rs_tab); cudaFree(d_cand); cudaFree(d_sel);
         cudaFree(d_knode); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
         cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp);
         cudaFreeHost(h_kps); cudaFreeHost(h_desc); cudaFreeHost(h_kp_count); cudaFreeHost(h_mono); cudaFreeHost(h_sel_count);
         cudaFreeHost(h_cand_count);
-        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_rs_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
+        d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_strip_tab = nullptr; d_rs_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
         d_cand_count = d_sel_count = d_kp_count = d_mono = nullptr; d_kps = d_kps_tmp = nullptr; d_desc = d_desc_tmp = nullptr;
         h_kps = nullptr; h_desc = nullptr; h_kp_count = h_mono = h_sel_count = h_cand_count = nullptr;
     }
@@ -458,6 +519,14 @@ struct Engine {
         }
         cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab);
         d_xtab = d_ytab = nullptr; d_cell_tab = nullptr;
+        cudaFree(d_strip_tab);
+        d_strip_tab = nullptr;
+        std::vector<uint4> strips;
+        if (!build_strip_table(np, strips)) return MCS_ERR_ARG;
+        n_fast_strips = (int)strips.size() / 2;
+        CK(cudaMalloc(&d_strip_tab, std::max<size_t>(strips.size(), 1) * sizeof(uint4)));
+        if (!strips.empty()) CK(cudaMemcpy(d_strip_tab, strips.data(), strips.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+        if (const char* e = getenv("MCS_FAST_CELLS")) fast_per_cell = atoi(e) != 0;
         std::vector<uint4> cells;
         build_cell_table(np, cells);
         n_fast_cells = (int)cells.size();
@@ -491,6 +560,8 @@ struct Engine {
         if (oct_smem > 200 * 1024) { set_err("features per level exceed the octree kernel's shared-memory table"); return MCS_ERR_ARG; }
         if (plan.fast_smem_bytes > 200 * 1024) { set_err("internal: FAST cell too large for shared memory"); return MCS_ERR_ARG; }
         CK(cudaFuncSetAttribute(mcs::fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.fast_smem_bytes, 1024)));
+        if (plan.fs_smem_bytes > 200 * 1024) { set_err("internal: FAST strip too large for shared memory"); return MCS_ERR_ARG; }
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.fs_smem_bytes, 1024)));
         CK(cudaFuncSetAttribute(mcs::octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
         last_n = 0;
         return 0;
@@ -552,8 +623,11 @@ struct Engine {
             launches++;
         }
         mark(ST_FAST);
-        if (n_fast_cells > 0) {
+        if (fast_per_cell && n_fast_cells > 0) {
             mcs::fast_cells_kernel<<<dim3(n_fast_cells, n), MCS_FAST_NT, P.fast_smem_bytes, st>>>(P, set, d_cell_tab, cand, cand_count);
+            launches++;
+        } else if (n_fast_strips > 0) {
+            mcs::fast_strips_kernel<<<dim3(n_fast_strips, n), MCS_FS_NT, P.fs_smem_bytes, st>>>(P, set, d_strip_tab, cand, cand_count);
             launches++;
         }
         mark(ST_OCTREE);
@@ -633,11 +707,11 @@ struct Engine {
         set.l0 = d_pyr + plan.L[0].plane_ofs; set.l0_pitch = plan.L[0].pitch; set.l0_stride = plan.pyr_stride;
         return 0;
     }
-    // device-resident tight images (d_images = image 0); re-pitched only when 32-bit row loads would be misaligned
+    // device-resident tight images (d_images = image 0); re-pitched only when 128-bit row loads would be misaligned
     int make_set(const uint8_t* d_images, int n, int w, int h, mcs::ImageSet& set, int img0 = 0, cudaStream_t st = nullptr) {
         if (!st) st = stream;
         set.pyr = d_pyr;
-        if ((w & 3) == 0 && ((uintptr_t)d_images & 15) == 0) {
+        if ((w & 15) == 0 && ((uintptr_t)d_images & 15) == 0) {  // rows start 16-byte aligned (FAST tile staging)
             set.l0 = d_images; set.l0_pitch = w; set.l0_stride = (size_t)w * h;
         } else {
             for (int i = img0; i < img0 + n; i++)

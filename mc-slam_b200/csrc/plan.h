@@ -53,6 +53,8 @@ struct McsPlan {
     int fast_sp;        // score tile pitch
     int fast_ofs_score, fast_ofs_flags, fast_ofs_queue, fast_ofs_surv, fast_smem_bytes;
     int fast_maxsurv;   // survivor capacity (records)
+    // strip FAST kernel (fast_strips_kernel): score tile, per-warp entry stacks, corner list (bytes)
+    int fs_ofs_score, fs_ofs_wq, fs_ofs_corner, fs_smem_bytes;
     int umax[16];       // circular patch row half-widths for IC_Angle (ORBextractor.cpp:452-467)
     McsLevel L[MCS_PLAN_MAX_LEVELS];
 };

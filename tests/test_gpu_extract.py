@@ -79,6 +79,43 @@ def test_noise_worst_case_720():
     assert mono == m2 and (kps == k2).all() and np.array_equal(desc, d2)
 
 
+@pytest.mark.parametrize("w,h,seed", [(720, 540, 3), (500, 375, 4), (417, 312, 5)])
+def test_threshold_fallback_mixed_cells(w, h, seed):
+    """Cells without a corner at iniThFAST are re-run at minThFAST (ORBextractor.cpp:842-845) one by one.  Bands of strong texture,
+    weak texture (strengths between the two thresholds) and flat grey of widths unrelated to the cell grid put retried and
+    non-retried cells next to each other inside one strip of the FAST kernel, and corners of equal score next to each other."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    rng = np.random.default_rng(seed)
+    img = np.full((h, w), 128, np.uint8)
+    x = 0
+    while x < w:
+        bw = int(rng.integers(9, 90))
+        kind = int(rng.integers(0, 4))
+        if kind == 0:
+            band = rng.integers(0, 256, (h, bw))
+        elif kind == 1:
+            band = 128 + rng.integers(-9, 10, (h, bw))       # weak: most strengths below 20
+        elif kind == 2:
+            band = 128 + 12 * rng.integers(0, 2, (h, bw))    # two grey values: many equal scores
+        else:
+            band = np.full((h, bw), 128)
+        y = 0
+        while y < h:  # flat rows cut the bands so that cell rows differ too
+            bh = int(rng.integers(20, 120))
+            if rng.integers(0, 3) == 0:
+                band[y:y + bh] = 128
+            y += bh
+        img[:, x:x + bw] = band[:, :max(0, min(bw, w - x))]
+        x += bw
+    ex = M.Extractor(1500, max_width=w, max_height=h)
+    mono, kps, desc = ex(img)
+    orc = O.Extractor(1500)
+    m2, k2, d2 = orc(img)
+    _compare_stages(ex, orc, img)
+    assert mono == m2 and len(kps) == len(k2) and (kps == k2).all() and np.array_equal(desc, d2)
+
+
 def test_batch_equals_single_and_resize_of_handle():
     import mcslam_b200 as M
     import oracle_lib as O
