@@ -307,7 +307,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames", type=int, default=256, help="rig frames per step per GPU (one batched launch sequence)")
+    ap.add_argument("--frames", type=int, default=512, help="rig frames per step per GPU (one batched launch sequence)")
     ap.add_argument("--distinct", type=int, default=4, help="ray-cast scenes per rank; the batch is filled with shifted copies")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline sample length")
     ap.add_argument("--cpu-step-seconds", type=float, default=6.0, help="--impl reference: seconds of CPU work per step")

@@ -218,38 +218,71 @@ struct ResizeSelArgs {
     size_t src_stride, dst_stride;  // bytes between images
     int spitch, dpitch;
     int lastw;            // last valid 32-bit word of a source row
+    int sh;               // source rows
     int dwords, dh;       // output words per row, output rows
     const int4* xw;       // [dwords][2]: {wi, selectors, c0, c1}, {c2, c3, shift, 0}
     const int4* yw;       // [dh]: {sy0, sy1, b0, b1}
 };
 
+// Each thread produces MCS_RS_ROWS consecutive output rows of its 4-pixel word.  Those rows read a contiguous band of at most NR
+// source rows (<= 6 for the 1.2 pyramid, host-checked per level): the thread loads the band once (all loads in flight together, one
+// 64-bit row pointer each, words at +0 / +4 / +8), runs the horizontal pass once per source row and parks the four sums as one
+// 16-byte shared-memory slot per (row, thread), because the output rows pick their two source rows by a run-time index
+// (ytab) that registers cannot be indexed with.  The vertical pass is two LDS.128, eight IMAD.HI and a pack per output row.
+// First version (one output row per thread): fmaheavy pipe 71 % busy (DP2A + IMAD.HI + IMAD.WIDE address math + IMAD.MOV copies),
+// 28 instructions per pixel; this one runs the horizontal pass on ~1.4 instead of 2 source rows per output row and sets the column
+// tables up once per 16 pixels.  CLAMP: level 0 may alias a caller's tight buffer, where the two words after the last word of a row
+// must not be touched for the last row of the allocation; the library's own planes are padded.
+#define MCS_RS_ROWS 4
+template <int NR, bool CLAMP>
 __global__ void __launch_bounds__(256) resize_level_sel_kernel(const ResizeSelArgs A) {
-    const int g = blockIdx.x * 32 + threadIdx.x, dy = blockIdx.y * 8 + threadIdx.y;
-    if (g >= A.dwords || dy >= A.dh) return;
+    __shared__ uint4 s_h[NR][256];
+    const int g = blockIdx.x * 32 + threadIdx.x, dy0 = (blockIdx.y * 8 + threadIdx.y) * MCS_RS_ROWS;
+    if (g >= A.dwords || dy0 >= A.dh) return;
+    const int tid = threadIdx.y * 32 + threadIdx.x;
     const int4 xa = __ldg(A.xw + 2 * g), xb = __ldg(A.xw + 2 * g + 1);
-    const int4 yt = __ldg(A.yw + dy);
-    const uint8_t* base = A.src + blockIdx.z * A.src_stride;
-    const uint32_t* r0 = reinterpret_cast<const uint32_t*>(base + (uint32_t)(yt.x * A.spitch));
-    const uint32_t* r1 = reinterpret_cast<const uint32_t*>(base + (uint32_t)(yt.y * A.spitch));
-    const int wi = xa.x, wi1 = min(wi + 1, A.lastw), wi2 = min(wi + 2, A.lastw);
-    const uint32_t u0 = __ldg(r0 + wi), u1 = __ldg(r0 + wi1), u2 = __ldg(r0 + wi2);
-    const uint32_t v0 = __ldg(r1 + wi), v1 = __ldg(r1 + wi1), v2 = __ldg(r1 + wi2);
-    const uint32_t sh = (uint32_t)xb.z;
-    const uint32_t ua = __funnelshift_r(u0, u1, sh), ub = __funnelshift_r(u1, u2, sh);
-    const uint32_t va = __funnelshift_r(v0, v1, sh), vb = __funnelshift_r(v1, v2, sh);
-    const uint32_t cf[4] = {(uint32_t)xa.z, (uint32_t)xa.w, (uint32_t)xb.x, (uint32_t)xb.y};
-    const uint32_t sel = (uint32_t)xa.y;
-    const int b0 = yt.z, b1 = yt.w;
-    uint32_t outw = 0;
+    int4 yt[MCS_RS_ROWS];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint32_t pu = __byte_perm(ua, ub, sel >> (8 * k)), pv = __byte_perm(va, vb, sel >> (8 * k));
-        const int h0 = (int)__dp2a_lo(cf[k], pu, 0u);
-        const int h1 = (int)__dp2a_lo(cf[k], pv, 0u);
-        const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;  // in 0..255 by construction of the tables
-        outw |= (uint32_t)v << (8 * k);
+    for (int r = 0; r < MCS_RS_ROWS; r++) yt[r] = __ldg(A.yw + min(dy0 + r, A.dh - 1));  // {sy0, sy1, b0, b1}, rows clamped on the host
+    const int wi = xa.x;
+    const uint8_t* col = A.src + blockIdx.z * A.src_stride + 4 * wi;
+    const int o1 = CLAMP ? 4 * (min(wi + 1, A.lastw) - wi) : 4, o2 = CLAMP ? 4 * (min(wi + 2, A.lastw) - wi) : 8;
+    const int smin = yt[0].x;
+    uint32_t u[NR][3];
+#pragma unroll
+    for (int i = 0; i < NR; i++) {
+        const uint8_t* rp = col + (uint32_t)(min(smin + i, A.sh - 1) * A.spitch);
+        u[i][0] = __ldg(reinterpret_cast<const uint32_t*>(rp));
+        u[i][1] = __ldg(reinterpret_cast<const uint32_t*>(rp + o1));
+        u[i][2] = __ldg(reinterpret_cast<const uint32_t*>(rp + o2));
     }
-    *reinterpret_cast<uint32_t*>(A.dst + blockIdx.z * A.dst_stride + (uint32_t)(dy * A.dpitch + 4 * g)) = outw;
+    const uint32_t sh = (uint32_t)xb.z;
+    const uint32_t cf[4] = {(uint32_t)xa.z, (uint32_t)xa.w, (uint32_t)xb.x, (uint32_t)xb.y};
+    const uint32_t sl[4] = {(uint32_t)xa.y, (uint32_t)xa.y >> 8, (uint32_t)xa.y >> 16, (uint32_t)xa.y >> 24};
+    // horizontal pass: (sum of two taps) >> 4, as cv::resize stores it between its passes
+#pragma unroll
+    for (int i = 0; i < NR; i++) {
+        const uint32_t ua = __funnelshift_r(u[i][0], u[i][1], sh), ub = __funnelshift_r(u[i][1], u[i][2], sh);
+        uint4 hv;
+        hv.x = __dp2a_lo(cf[0], __byte_perm(ua, ub, sl[0]), 0u) >> 4;
+        hv.y = __dp2a_lo(cf[1], __byte_perm(ua, ub, sl[1]), 0u) >> 4;
+        hv.z = __dp2a_lo(cf[2], __byte_perm(ua, ub, sl[2]), 0u) >> 4;
+        hv.w = __dp2a_lo(cf[3], __byte_perm(ua, ub, sl[3]), 0u) >> 4;
+        s_h[i][tid] = hv;
+    }
+    uint8_t* drow = A.dst + blockIdx.z * A.dst_stride + (uint32_t)(dy0 * A.dpitch + 4 * g);
+#pragma unroll
+    for (int r = 0; r < MCS_RS_ROWS; r++) {
+        if (dy0 + r >= A.dh) break;
+        const uint4 h0 = s_h[yt[r].x - smin][tid], h1 = s_h[yt[r].y - smin][tid];  // own slots only: no barrier
+        // (b * h) >> 16 as the high half of (b << 16) * h: coefficients and sums are non-negative (build_resize_word_tables)
+        const uint32_t b0 = (uint32_t)yt[r].z << 16, b1 = (uint32_t)yt[r].w << 16;
+        const uint32_t v0 = (__umulhi(b0, h0.x) + __umulhi(b1, h1.x) + 2u) >> 2;  // in 0..255 by construction of the tables
+        const uint32_t v1 = (__umulhi(b0, h0.y) + __umulhi(b1, h1.y) + 2u) >> 2;
+        const uint32_t v2 = (__umulhi(b0, h0.z) + __umulhi(b1, h1.z) + 2u) >> 2;
+        const uint32_t v3 = (__umulhi(b0, h0.w) + __umulhi(b1, h1.w) + 2u) >> 2;
+        *reinterpret_cast<uint32_t*>(drow + (uint32_t)(r * A.dpitch)) = __byte_perm(__byte_perm(v0, v1, 0x0040), __byte_perm(v2, v3, 0x0040), 0x5410);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -603,6 +636,22 @@ __global__ void __launch_bounds__(MCS_FAST_NT) fast_cells_kernel(const __grid_co
 #define MCS_FS_WQ 288  // entries per warp stack: < 32 pending + 32 groups x 8
 #define MCS_FS_MAXW 187
 
+// Plain atomics as PTX: the callers are already warp-aggregated (one lane per batch), so nvcc's automatic same-address aggregation
+// (VOTE / FLO / POPC / SHFL around every atomicAdd, 6.7 % of the kernel's instructions in the first ncu capture) is pure overhead.
+__device__ __forceinline__ int fs_atom_add_shared(int* p, int v) {
+    int old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void fs_red_add_shared(int* p, int v) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int fs_atom_add_global(int* p, int v) {
+    int old;
+    asm volatile("atom.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+
 struct FastStripCtx {
     const uint8_t* tile;
     uint8_t* score;
@@ -625,7 +674,7 @@ __device__ __forceinline__ void fs_eval(const FastStripCtx& X, bool active, int 
     const unsigned m = __ballot_sync(0xFFFFFFFFu, corner);
     if (m) {
         int base = 0;
-        if (X.lane == 0) base = atomicAdd(X.ncorner, __popc(m));
+        if (X.lane == 0) base = fs_atom_add_shared(X.ncorner, __popc(m));
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
         if (corner) X.corner[base + __popc(m & ((1u << X.lane) - 1u))] = (uint16_t)(e & 0x7FFF);
     }
@@ -682,11 +731,21 @@ __device__ __forceinline__ void fs_scan(const FastStripCtx& X, int th, int xa, i
         int pos = pending + incl - cnt;
         if (f) {
 #pragma unroll
-            for (int b = 0; b < 8; b++) {  // predicated stores
-                if (f & (1u << b)) {
-                    X.wq[pos] = (uint16_t)(((b & 1) << 15) | (ebase + (b >> 1)));
+            for (int e = 0; e < 4; e++) {  // predicated stores; one entry per pixel, bit 15 = dark
+                const uint32_t fb = (f >> (2 * e)) & 3u;
+                if (fb) {
+                    X.wq[pos] = (uint16_t)(((fb & 2u) << 14) | (ebase + e));
                     pos++;
                 }
+            }
+            const uint32_t both = f & (f >> 1) & 0x55u;  // rare: both pre-tests passed, the dark entry went in; add the bright one
+            if (both) {
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    if (both & (1u << (2 * e))) {
+                        X.wq[pos] = (uint16_t)(ebase + e);
+                        pos++;
+                    }
             }
         }
         pending += total;
@@ -768,7 +827,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
                 if (xc != wcell - 1) n = max(n, max(max((int)qp[-TP + 1], (int)qp[1]), (int)qp[TP + 1]));
                 surv = sc > n;
                 if (surv) {
-                    atomicAdd(&s_cellcnt[ci], 1);
+                    fs_red_add_shared(&s_cellcnt[ci], 1);
                     // keypoint in ROI coordinates: FAST x in the cell's sub-image shifted by j * wCell (:864-865)
                     rec = mcs_oct::pack_cand(xi + xoff, ly + yoff, sc);
                 }
@@ -776,7 +835,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
             const unsigned m = __ballot_sync(0xFFFFFFFFu, surv);
             if (m) {
                 int p0 = 0;
-                if (lane == 0) p0 = atomicAdd(cnt, __popc(m));
+                if (lane == 0) p0 = fs_atom_add_global(cnt, __popc(m));
                 p0 = __shfl_sync(0xFFFFFFFFu, p0, 0) + __popc(m & ((1u << lane) - 1u));
                 if (surv && p0 < Lv.cand_cap) out[p0] = rec;
             }

@@ -379,9 +379,17 @@ struct Engine {
     int sm_count_ = 148;
     uint4* d_cell_tab = nullptr;  // FAST cell records (build_cell_table)
     uint4* d_strip_tab = nullptr;  // FAST strip records (build_strip_table)
+    // optional high-priority side stream for the latency-bound kernels of a launch sequence (octree; merge and triangulation in
+    // mcs_rig): their few long-lived blocks are placed ahead of the queued blocks of the issue-bound kernels of other chunks
+    struct HiLane {
+        cudaStream_t st = nullptr;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+    };
+    int fs_smem_launch = 0;        // dynamic shared memory of the strip kernel (>= plan.fs_smem_bytes; MCS_FS_BLOCKS pads it)
     int n_fast_strips = 0;
     bool fast_per_cell = false;  // MCS_FAST_CELLS=1: the one-block-per-cell kernel (A/B runs)
     int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
+    int rs_nr[MCS_PLAN_MAX_LEVELS] = {};  // source rows one group of MCS_RS_ROWS output rows spans (resize_level_sel_kernel<NR>)
     int rs_xw_ofs[MCS_PLAN_MAX_LEVELS] = {}, rs_yw_ofs[MCS_PLAN_MAX_LEVELS] = {};
     bool rs_sel_ok = false;
     int n_fast_cells = 0;
@@ -538,6 +546,14 @@ struct Engine {
             for (int l = 1; l < np.nlevels && rs_sel_ok; l++) {
                 std::vector<int4> xw, yw;
                 rs_sel_ok = build_resize_word_tables(np.L[l], np.L[l - 1], xt, yt, xw, yw);
+                rs_nr[l] = 0;
+                for (size_t r0 = 0; rs_sel_ok && r0 < yw.size(); r0 += MCS_RS_ROWS) {
+                    const size_t r1 = std::min(yw.size(), r0 + MCS_RS_ROWS) - 1;
+                    rs_nr[l] = std::max(rs_nr[l], yw[r1].y - yw[r0].x + 1);
+                    for (size_t r = r0; r < r1; r++)
+                        if (yw[r + 1].x < yw[r].x || yw[r].y < yw[r].x) rs_sel_ok = false;  // rows must not go backwards
+                }
+                if (rs_nr[l] > 8) rs_sel_ok = false;
                 rs_xw_ofs[l] = (int)rs.size();
                 rs.insert(rs.end(), xw.begin(), xw.end());
                 rs_yw_ofs[l] = (int)rs.size();
@@ -561,7 +577,12 @@ struct Engine {
         if (plan.fast_smem_bytes > 200 * 1024) { set_err("internal: FAST cell too large for shared memory"); return MCS_ERR_ARG; }
         CK(cudaFuncSetAttribute(mcs::fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.fast_smem_bytes, 1024)));
         if (plan.fs_smem_bytes > 200 * 1024) { set_err("internal: FAST strip too large for shared memory"); return MCS_ERR_ARG; }
-        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.fs_smem_bytes, 1024)));
+        fs_smem_launch = plan.fs_smem_bytes;
+        if (const char* e = getenv("MCS_FS_BLOCKS")) {  // tuning: cap the strip kernel's resident blocks per SM through its shared memory
+            const int nb = atoi(e);
+            if (nb >= 1 && nb <= 8) fs_smem_launch = std::max(fs_smem_launch, std::min(200 * 1024, (227 * 1024) / nb - 1024 - 64));
+        }
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
         CK(cudaFuncSetAttribute(mcs::octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
         last_n = 0;
         return 0;
@@ -584,7 +605,7 @@ struct Engine {
 
     // Stage A on images [img0, img0 + n) of the workspace, already described by `set0` (the set of image 0), on stream `st`
     // (0 = the handle's main stream).  Leaves keypoints/descriptors/counts on the device.
-    int run(const mcs::ImageSet& set0, int n, const int lap[2], int img0 = 0, cudaStream_t st = nullptr) {
+    int run(const mcs::ImageSet& set0, int n, const int lap[2], int img0 = 0, cudaStream_t st = nullptr, const HiLane* hi = nullptr) {
         if (n < 1 || img0 < 0 || img0 + n > max_images) { set_err("n_images exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
         if (!st) st = stream;
         last_set = set0; last_n = img0 == 0 ? n : std::max(last_n, img0 + n);
@@ -605,6 +626,7 @@ struct Engine {
         for (int l = 1; l < P.nlevels; l++) {
             dim3 b(32, 8), g((P.L[l].w + 127) / 128, (P.L[l].h + 7) / 8, n);
             if (rs_sel_ok && d_rs_tab) {
+                g.y = (P.L[l].h + 8 * MCS_RS_ROWS - 1) / (8 * MCS_RS_ROWS);
                 mcs::ResizeSelArgs A;
                 A.src = l == 1 ? set.l0 : set.pyr + P.L[l - 1].plane_ofs;
                 A.src_stride = l == 1 ? set.l0_stride : (size_t)P.pyr_stride;
@@ -613,11 +635,22 @@ struct Engine {
                 A.dst_stride = (size_t)P.pyr_stride;
                 A.dpitch = P.L[l].pitch;
                 A.lastw = ((P.L[l - 1].w + 3) >> 2) - 1;
+                A.sh = P.L[l - 1].h;
                 A.dwords = (P.L[l].w + 3) / 4;
                 A.dh = P.L[l].h;
                 A.xw = d_rs_tab + rs_xw_ofs[l];
                 A.yw = d_rs_tab + rs_yw_ofs[l];
-                mcs::resize_level_sel_kernel<<<g, b, 0, st>>>(A);
+                // level 0 aliasing a caller's buffer is the only source plane without readable padding behind its last row
+                const uint8_t* l0b = set0.l0;
+                const bool padded = l > 1 || (l0b >= d_pyr && l0b < d_pyr + (size_t)max_images * P.pyr_stride) ||
+                                    (l0b >= d_input && l0b < d_input + (size_t)max_images * in_bytes);
+                if (rs_nr[l] <= 6) {
+                    if (padded) mcs::resize_level_sel_kernel<6, false><<<g, b, 0, st>>>(A);
+                    else mcs::resize_level_sel_kernel<6, true><<<g, b, 0, st>>>(A);
+                } else {
+                    if (padded) mcs::resize_level_sel_kernel<8, false><<<g, b, 0, st>>>(A);
+                    else mcs::resize_level_sel_kernel<8, true><<<g, b, 0, st>>>(A);
+                }
             } else if (T.scale_factor_f <= 2.0f) mcs::resize_level_words_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
             else mcs::resize_level_kernel<<<g, b, 0, st>>>(P, set, l, d_xtab, d_ytab);
             launches++;
@@ -627,11 +660,19 @@ struct Engine {
             mcs::fast_cells_kernel<<<dim3(n_fast_cells, n), MCS_FAST_NT, P.fast_smem_bytes, st>>>(P, set, d_cell_tab, cand, cand_count);
             launches++;
         } else if (n_fast_strips > 0) {
-            mcs::fast_strips_kernel<<<dim3(n_fast_strips, n), MCS_FS_NT, P.fs_smem_bytes, st>>>(P, set, d_strip_tab, cand, cand_count);
+            mcs::fast_strips_kernel<<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, d_strip_tab, cand, cand_count);
             launches++;
         }
         mark(ST_OCTREE);
-        mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
+        if (hi) {
+            CK(cudaEventRecord(hi->e0, st));
+            CK(cudaStreamWaitEvent(hi->st, hi->e0, 0));
+            mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, hi->st>>>(P, cand, cand_count, knode, sel, sel_count);
+            CK(cudaEventRecord(hi->e1, hi->st));
+            CK(cudaStreamWaitEvent(st, hi->e1, 0));
+        } else {
+            mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
+        }
         launches++;
         mark(ST_BLUR);
         if (P.use_angle) {
@@ -1026,6 +1067,7 @@ struct mcs_rig {
         cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
         int *d_tri_lists = nullptr, *d_tri_counts = nullptr;
         float* d_f32 = nullptr;  // staging of one chunk of f32 input images (process_f32 with host buffers)
+        Engine::HiLane hi;       // high-priority side stream (use_hi)
         size_t f32_bytes = 0;
     };
     static constexpr int NSLOT = 4;
@@ -1033,6 +1075,7 @@ struct mcs_rig {
     cudaEvent_t ev_begin = nullptr;
     int tri_list_stride = 0, sm_count = 148;
     int chunk_frames = 64;  // frames per pipelined chunk (0 = no chunking)
+    bool use_hi = false;    // MCS_HIPRIO=1: octree, merge and triangulation on the slots' high-priority side streams
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
     size_t masks_bytes = 0;
@@ -1069,6 +1112,7 @@ struct mcs_rig {
             if (S.st && k > 0) { cudaStreamSynchronize(S.st); cudaStreamDestroy(S.st); }
             if (S.st2) { cudaStreamSynchronize(S.st2); cudaStreamDestroy(S.st2); }
             if (S.ev_fork) { cudaEventDestroy(S.ev_fork); cudaEventDestroy(S.ev_join); cudaEventDestroy(S.ev_done); }
+            if (S.hi.st) { cudaStreamSynchronize(S.hi.st); cudaStreamDestroy(S.hi.st); cudaEventDestroy(S.hi.e0); cudaEventDestroy(S.hi.e1); }
             cudaFree(S.d_tri_lists); cudaFree(S.d_tri_counts); cudaFree(S.d_f32);
         }
         if (ev_begin) cudaEventDestroy(ev_begin);
@@ -1142,6 +1186,16 @@ struct mcs_rig {
             CK(cudaMalloc(&S.d_tri_counts, (MCS_MAX_CAMS + 2) * sizeof(int)));  // per view count + the tile queue head
         }
         if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
+        if (const char* e = getenv("MCS_HIPRIO")) use_hi = atoi(e) != 0;
+        if (use_hi) {
+            int lo = 0, hi = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            for (int k = 0; k < NSLOT; k++) {
+                CK(cudaStreamCreateWithPriority(&slots[k].hi.st, cudaStreamNonBlocking, hi));
+                CK(cudaEventCreateWithFlags(&slots[k].hi.e0, cudaEventDisableTiming));
+                CK(cudaEventCreateWithFlags(&slots[k].hi.e1, cudaEventDisableTiming));
+            }
+        }
         CK(cudaMalloc(&lm.rows, rw * C * sizeof(int)));
         CK(cudaMalloc(&lm.accepted, rw));
         CK(cudaMalloc(&lm.n_views, rw * sizeof(int)));
@@ -1180,7 +1234,7 @@ struct mcs_rig {
     // relative to the pointers it is given, so a chunk is the same launch with offset pointers.
     int stage_extract(const mcs::ImageSet& set, int n_frames, int f0 = 0, int k = 0) {
         static const int lap[2] = {0, 0};  // vLapping = {0,0} (MultiCameraFrame.cpp:235, :274)
-        int rc = eng.run(set, n_frames * C, lap, f0 * C, slots[k].st);
+        int rc = eng.run(set, n_frames * C, lap, f0 * C, slots[k].st, use_hi ? &slots[k].hi : nullptr);
         if (rc) return rc;
         n_extracted = f0 == 0 ? n_frames : std::max(n_extracted, f0 + n_frames);
         if (f0 == 0) n_matched = n_triangulated = 0;
@@ -1245,10 +1299,20 @@ struct mcs_rig {
             eng.launches++;
         }
         eng.mark(ST_MERGE);
-        mcs::merge_kernel<<<n_frames, MCS_MERGE_NT, merge_smem, st>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
+        cudaStream_t ml = st;
+        if (use_hi) {
+            CK(cudaEventRecord(slots[k].hi.e0, st));
+            CK(cudaStreamWaitEvent(slots[k].hi.st, slots[k].hi.e0, 0));
+            ml = slots[k].hi.st;
+        }
+        mcs::merge_kernel<<<n_frames, MCS_MERGE_NT, merge_smem, ml>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
                                                              kps_undist_dev() + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
                                                              d_rows + (size_t)f0 * row_cap * C, d_row_count + f0, merge_rows_smem ? 1 : 0);
         eng.launches++;
+        if (use_hi) {
+            CK(cudaEventRecord(slots[k].hi.e1, ml));
+            CK(cudaStreamWaitEvent(st, slots[k].hi.e1, 0));
+        }
         eng.mark(ST_TRIANG);
         CK(cudaGetLastError());
         n_matched = f0 == 0 ? n_frames : std::max(n_matched, f0 + n_frames);
@@ -1270,16 +1334,22 @@ struct mcs_rig {
         const uint8_t* desc = eng.d_desc + (size_t)f0 * C * kp_cap * 32;
         const float* mask = d_mask_ptr ? d_mask_ptr + (size_t)f0 * C * cfg.width * cfg.height : nullptr;
         eng.mark(ST_TRIANG);
-        CK(cudaMemsetAsync(out.n_accepted, 0, n_frames * sizeof(int), S.st));
-        CK(cudaMemsetAsync(S.d_tri_counts, 0, (MCS_MAX_CAMS + 2) * sizeof(int), S.st));
+        cudaStream_t tl = S.st;  // the stream the triangulation kernels run on
+        if (use_hi) {
+            CK(cudaEventRecord(S.hi.e0, S.st));
+            CK(cudaStreamWaitEvent(S.hi.st, S.hi.e0, 0));
+            tl = S.hi.st;
+        }
+        CK(cudaMemsetAsync(out.n_accepted, 0, n_frames * sizeof(int), tl));
+        CK(cudaMemsetAsync(S.d_tri_counts, 0, (MCS_MAX_CAMS + 2) * sizeof(int), tl));
         dim3 g((row_cap + 127) / 128, n_frames);
-        mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, S.st>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows + (size_t)f0 * row_cap * C,
+        mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, tl>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows + (size_t)f0 * row_cap * C,
                                                                     d_row_count + f0, kps, mask, out, S.d_tri_lists, S.d_tri_counts, tri_list_stride);
         eng.launches++;
         // 2-view rows on a forked stream, every larger view count in one launch (blockIdx.y = class) on the slot's stream;
         // persistent grid-stride blocks because the list lengths live on the device
         if (C >= 2) {
-            CK(cudaEventRecord(S.ev_fork, S.st));
+            CK(cudaEventRecord(S.ev_fork, tl));
             CK(cudaStreamWaitEvent(S.st2, S.ev_fork, 0));
             const int nb2 = std::max(1, std::min(sm_count * 8, (n_frames * row_cap + 127) / 128));
             mcs::tri_solve2_kernel<<<nb2, 128, 0, S.st2>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists, S.d_tri_counts, tri_list_stride);
@@ -1287,12 +1357,16 @@ struct mcs_rig {
             CK(cudaEventRecord(S.ev_join, S.st2));
             if (C >= 3) {
                 const int per_sm = std::max(1, std::min(16, (int)((227 * 1024) / (tri_smem(C) + 1024))));
-                mcs::tri_solve_kernel<<<sm_count * per_sm, MCS_TRI_NT, tri_smem(C), S.st>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
+                mcs::tri_solve_kernel<<<sm_count * per_sm, MCS_TRI_NT, tri_smem(C), tl>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
                                                                                           S.d_tri_counts, tri_list_stride,
                                                                                           S.d_tri_counts + MCS_MAX_CAMS + 1);
                 eng.launches++;
             }
-            CK(cudaStreamWaitEvent(S.st, S.ev_join, 0));
+            CK(cudaStreamWaitEvent(tl, S.ev_join, 0));
+        }
+        if (use_hi) {
+            CK(cudaEventRecord(S.hi.e1, tl));
+            CK(cudaStreamWaitEvent(S.st, S.hi.e1, 0));
         }
         eng.mark(ST_DOWNLOAD);
         CK(cudaGetLastError());
