@@ -1075,6 +1075,8 @@ struct mcs_rig {
     cudaEvent_t ev_begin = nullptr;
     int tri_list_stride = 0, sm_count = 148;
     int chunk_frames = 64;  // frames per pipelined chunk (0 = no chunking)
+    int tri_per_sm = 3;     // resident tri_solve blocks per SM (MCS_TRI_PER_SM; 0 = as many as shared memory holds): 3 measured best — the
+                            // one-warp blocks hold 44 KB of shared memory each for the length of a Jacobi chain, which other chunks' kernels need
     bool use_hi = false;    // MCS_HIPRIO=1: octree, merge and triangulation on the slots' high-priority side streams
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
@@ -1187,6 +1189,7 @@ struct mcs_rig {
         }
         if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
         if (const char* e = getenv("MCS_HIPRIO")) use_hi = atoi(e) != 0;
+        if (const char* e = getenv("MCS_TRI_PER_SM")) tri_per_sm = std::max(0, atoi(e));
         if (use_hi) {
             int lo = 0, hi = 0;
             CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -1356,7 +1359,7 @@ struct mcs_rig {
             eng.launches++;
             CK(cudaEventRecord(S.ev_join, S.st2));
             if (C >= 3) {
-                const int per_sm = std::max(1, std::min(16, (int)((227 * 1024) / (tri_smem(C) + 1024))));
+                const int per_sm = std::max(1, std::min(tri_per_sm > 0 ? tri_per_sm : 16, (int)((227 * 1024) / (tri_smem(C) + 1024))));
                 mcs::tri_solve_kernel<<<sm_count * per_sm, MCS_TRI_NT, tri_smem(C), tl>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
                                                                                           S.d_tri_counts, tri_list_stride,
                                                                                           S.d_tri_counts + MCS_MAX_CAMS + 1);
