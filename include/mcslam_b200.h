@@ -95,6 +95,14 @@ MCS_API int mcs_extract_batch(mcs_extractor* ex, const uint8_t* images, int n_im
 
 /* GetLevels / GetScaleFactor(s) / GetInverseScaleFactors / GetScaleSigmaSquares / GetInverseScaleSigmaSquares
  * (ORBextractor.h:61-81) and mnFeaturesPerLevel.  Each array has nlevels entries; NULL pointers are skipped. */
+/* Host-only inspection of the FAST work decomposition of one configuration (the cell grid of ComputeKeyPointsOctTree,
+ * ORBextractor.cpp:780-821, and the strips of cells one block of the FAST kernel processes).  Needs no device.  cells: capacity x 4
+ * words {level, iniX | iniY << 16, width | height << 16 of the sub-image handed to cv::FAST, candidate offset}; strips: capacity x 8
+ * words (a.x = level | cells << 8 | wCell << 16, a.y = iniX | iniY << 16, a.z = interior width | height << 16, a.w = offset,
+ * b = index-division constants).  Either array may be NULL. */
+MCS_API int mcs_plan_fast_tables(int width, int height, int nfeatures, float scale_factor, int nlevels, uint32_t* cells, int* n_cells,
+                                 uint32_t* strips, int* n_strips, int* strip_smem_bytes, int capacity);
+
 MCS_API int mcs_extractor_get_tables(const mcs_extractor* ex, int* nlevels, float* scale_factors, float* inv_scale_factors,
                                      float* level_sigma2, float* inv_level_sigma2, int* features_per_level);
 

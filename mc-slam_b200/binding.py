@@ -39,7 +39,7 @@ EXPORTS = [
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
     "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
-    "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2",
+    "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2", "mcs_plan_fast_tables",
 ]
 
 
@@ -615,3 +615,17 @@ def device_download(device, arr, dptr):
     """Copies arr.nbytes from device pointer dptr into the (contiguous) numpy array arr."""
     assert arr.flags["C_CONTIGUOUS"]
     _check(lib().mcs_device_download(device, _p(arr), C.c_void_p(dptr), arr.nbytes), "device_download")
+
+
+def plan_fast_tables(width, height, nfeatures=1000, scale_factor=1.2, nlevels=8, capacity=65536):
+    """Host-only (no GPU): the FAST cell table and strip table of one configuration -> (cells [n, 4] u32, strips [n, 8] u32, smem bytes)."""
+    L = lib()
+    L.mcs_plan_fast_tables.restype = C.c_int
+    L.mcs_plan_fast_tables.argtypes = [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.c_void_p,
+                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int]
+    cells = np.zeros((capacity, 4), np.uint32)
+    strips = np.zeros((capacity, 8), np.uint32)
+    nc, ns, sm = C.c_int(), C.c_int(), C.c_int()
+    _check(L.mcs_plan_fast_tables(width, height, nfeatures, scale_factor, nlevels, cells.ctypes.data, C.byref(nc), strips.ctypes.data,
+                                  C.byref(ns), C.byref(sm), capacity), "mcs_plan_fast_tables")
+    return cells[:nc.value].copy(), strips[:ns.value].copy(), sm.value

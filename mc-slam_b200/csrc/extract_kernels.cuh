@@ -870,6 +870,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
 #ifndef MCS_OCT_NT
 #define MCS_OCT_NT 128  // 128 beats 256 inside the chunked pipeline: more blocks per SM hide the barrier-heavy serial phases
 #endif
+#define MCS_OCT_NT_MAX 512  // the block size is a launch parameter (Engine::oct_nt): large quotas (config 4) use wider blocks
 
 struct CudaBlockCtx {
     __device__ __forceinline__ int nthreads() const { return blockDim.x; }
@@ -928,7 +929,7 @@ struct CudaBlockCtx {
 };
 
 // sel[img][sel_ofs(level) + k] = k-th retained candidate of the level in final list order; sel_count[img][level] = how many.
-__global__ void __launch_bounds__(MCS_OCT_NT) octree_kernel(const __grid_constant__ McsPlan P, const uint32_t* __restrict__ cand,
+__global__ void __maxnreg__(48) octree_kernel(const __grid_constant__ McsPlan P, const uint32_t* __restrict__ cand,
                                                             const int* __restrict__ cand_count, uint16_t* __restrict__ knode,
                                                             uint32_t* __restrict__ sel, int* __restrict__ sel_count) {
     extern __shared__ __align__(16) unsigned char s_oct[];

@@ -389,6 +389,7 @@ struct Engine {
     int n_fast_strips = 0;
     bool fast_per_cell = false;  // MCS_FAST_CELLS=1: the one-block-per-cell kernel (A/B runs)
     int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
+    int oct_nt = MCS_OCT_NT;  // octree block size (MCS_OCT_THREADS overrides)
     int rs_nr[MCS_PLAN_MAX_LEVELS] = {};  // source rows one group of MCS_RS_ROWS output rows spans (resize_level_sel_kernel<NR>)
     int rs_xw_ofs[MCS_PLAN_MAX_LEVELS] = {}, rs_yw_ofs[MCS_PLAN_MAX_LEVELS] = {};
     bool rs_sel_ok = false;
@@ -535,6 +536,10 @@ struct Engine {
         CK(cudaMalloc(&d_strip_tab, std::max<size_t>(strips.size(), 1) * sizeof(uint4)));
         if (!strips.empty()) CK(cudaMemcpy(d_strip_tab, strips.data(), strips.size() * sizeof(uint4), cudaMemcpyHostToDevice));
         if (const char* e = getenv("MCS_FAST_CELLS")) fast_per_cell = atoi(e) != 0;
+        if (const char* e = getenv("MCS_OCT_THREADS")) {
+            const int v = atoi(e);
+            if (v >= 32 && v <= MCS_OCT_NT_MAX && v % 32 == 0) oct_nt = v;
+        }
         std::vector<uint4> cells;
         build_cell_table(np, cells);
         n_fast_cells = (int)cells.size();
@@ -667,11 +672,11 @@ struct Engine {
         if (hi) {
             CK(cudaEventRecord(hi->e0, st));
             CK(cudaStreamWaitEvent(hi->st, hi->e0, 0));
-            mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, hi->st>>>(P, cand, cand_count, knode, sel, sel_count);
+            mcs::octree_kernel<<<dim3(P.nlevels, n), oct_nt, oct_smem, hi->st>>>(P, cand, cand_count, knode, sel, sel_count);
             CK(cudaEventRecord(hi->e1, hi->st));
             CK(cudaStreamWaitEvent(st, hi->e1, 0));
         } else {
-            mcs::octree_kernel<<<dim3(P.nlevels, n), MCS_OCT_NT, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
+            mcs::octree_kernel<<<dim3(P.nlevels, n), oct_nt, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
         }
         launches++;
         mark(ST_BLUR);
@@ -806,6 +811,30 @@ extern "C" {
 
 const char* mcs_last_error(void) { return g_err.c_str(); }
 const char* mcs_version(void) { return "mcslam_b200 0.1 (sm_100a)"; }
+// Host-only: the FAST work decomposition of one extractor configuration (no device needed).  cells[i] = {level, iniX | iniY << 16,
+// sub-image width | height << 16, offset}; strips[i] = the two uint4 of build_strip_table.  Returns 0, or a negative error code.
+int mcs_plan_fast_tables(int width, int height, int nfeatures, float scale_factor, int nlevels, uint32_t* cells, int* n_cells,
+                         uint32_t* strips, int* n_strips, int* strip_smem_bytes, int capacity) {
+    if (width < 1 || height < 1 || nfeatures < 1 || nlevels < 1 || nlevels > MCS_PLAN_MAX_LEVELS || !(scale_factor > 1.f) || !n_cells || !n_strips) {
+        set_err("mcs_plan_fast_tables: bad arguments");
+        return MCS_ERR_ARG;
+    }
+    OrbTables T;
+    T.build(nfeatures, scale_factor, nlevels, 20, 7);
+    McsPlan P;
+    std::vector<int2> xt, yt;
+    if (!build_plan(T, width, height, 0, P, xt, yt)) return MCS_ERR_ARG;
+    std::vector<uint4> ct, st;
+    build_cell_table(P, ct);
+    if (!build_strip_table(P, st)) return MCS_ERR_ARG;
+    *n_cells = (int)ct.size();
+    *n_strips = (int)st.size() / 2;
+    if (strip_smem_bytes) *strip_smem_bytes = P.fs_smem_bytes;
+    if ((int)ct.size() > capacity || (int)st.size() / 2 > capacity) { set_err("mcs_plan_fast_tables: capacity"); return MCS_ERR_CAPACITY; }
+    if (cells) memcpy(cells, ct.data(), ct.size() * sizeof(uint4));
+    if (strips) memcpy(strips, st.data(), st.size() * sizeof(uint4));
+    return 0;
+}
 int mcs_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;

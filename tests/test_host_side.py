@@ -207,3 +207,42 @@ def test_kalibr_camchain_reader(tmp_path, radtan, camchain):
     (tmp_path / "bad.yaml").write_text(_CAMCHAIN.replace("resolution: [1224, 1024]\n  rostopic: /camera_array/cam2", "resolution: [640, 480]\n  rostopic: /camera_array/cam2"))
     out = subprocess.run([exe, "calib", str(tmp_path / "bad.yaml"), "1", "1", str(tmp_path / "c.txt")], capture_output=True, text=True, timeout=60)
     assert out.returncode == 3 and "Resolution of all images is not the same" in out.stderr
+
+
+@pytest.mark.parametrize("w,h", [(720, 540), (1920, 1200), (333, 251), (203, 157), (640, 480), (1224, 1024), (752, 480), (97, 83), (4096, 70)])
+def test_fast_strips_cover_the_cell_grid_exactly(w, h):
+    """Host logic of the strip FAST kernel (no GPU): every cell the reference runs (ComputeKeyPointsOctTree, ORBextractor.cpp:804-821) lies in
+    exactly one strip, a strip's interior is the union of its cells' interiors, and the geometry fits the kernel's compile-time tile."""
+    from mcslam_b200 import binding as B
+    cells, strips, smem = B.plan_fast_tables(w, h, 1000)
+    assert smem <= 200 * 1024
+    covered = {}
+    for s in strips:
+        level, ncells, wcell = int(s[0] & 0xFF), int((s[0] >> 8) & 0xFF), int(s[0] >> 16)
+        inix, iniy = int(s[1] & 0xFFFF), int(s[1] >> 16)
+        wint, ih = int(s[2] & 0xFFFF), int(s[2] >> 16)
+        xoff, yoff = int(s[3] & 0xFFFF), int(s[3] >> 16)
+        assert 1 <= ncells <= 8 and 1 <= wint <= 187 and ih >= 1
+        assert (inix & 15) + 3 + wint + 3 <= 208          # tile pitch of the kernel
+        assert (ncells - 1) * wcell < wint <= ncells * wcell
+        for c in range(ncells):
+            key = (level, inix + c * wcell, iniy)
+            assert key not in covered
+            covered[key] = (min(wcell, wint - c * wcell), ih, xoff + c * wcell, yoff)
+        # index divisions of the kernel: pixel groups per row and 16-byte words per row
+        x0 = (inix & 15) + 3
+        ng = ((x0 + wint - 1) >> 2) - (x0 >> 2) + 1
+        nq = (x0 + wint + 3 + 15) >> 4
+        for t in range(ng * ih):
+            assert (t * int(s[4])) >> 20 == t // ng
+        for t in range(nq * (ih + 6)):
+            assert (t * int(s[5])) >> 20 == t // nq
+        for t in range(wint):
+            assert (t * int(s[6])) >> 20 == t // wcell
+    assert len(covered) == len(cells)
+    for c in cells:
+        key = (int(c[0]), int(c[1] & 0xFFFF), int(c[1] >> 16))
+        cw, ch = int(c[2] & 0xFFFF), int(c[2] >> 16)
+        assert key in covered, key
+        iw, ih, xo, yo = covered[key]
+        assert (iw, ih) == (cw - 6, ch - 6) and (xo, yo) == (int(c[3] & 0xFFFF), int(c[3] >> 16))
