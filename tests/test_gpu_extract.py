@@ -116,6 +116,21 @@ def test_threshold_fallback_mixed_cells(w, h, seed):
     assert mono == m2 and len(kps) == len(k2) and (kps == k2).all() and np.array_equal(desc, d2)
 
 
+@pytest.mark.parametrize("w,h", [(97, 83), (131, 64), (70, 400), (1000, 71), (752, 480), (1226, 370)])
+def test_odd_sizes_single_cell_levels(w, h):
+    """Sizes whose upper levels shrink to one cell row / column (cells up to 69 px wide), levels too small for any cell, widths that are
+    not a multiple of 16 (re-pitched level 0) and one long strip row: noise images against the oracle, stage by stage."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    img = M.synth.noise_image(w, h, 7 * w + h)
+    ex = M.Extractor(300, max_width=w, max_height=h)
+    mono, kps, desc = ex(img)
+    orc = O.Extractor(300)
+    m2, k2, d2 = orc(img)
+    _compare_stages(ex, orc, img)
+    assert mono == m2 and len(kps) == len(k2) and (kps == k2).all() and np.array_equal(desc, d2)
+
+
 def test_batch_equals_single_and_resize_of_handle():
     import mcslam_b200 as M
     import oracle_lib as O
