@@ -643,8 +643,8 @@ __device__ __forceinline__ int fs_atom_add_shared(int* p, int v) {
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     return old;
 }
-__device__ __forceinline__ void fs_red_add_shared(int* p, int v) {
-    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+__device__ __forceinline__ void fs_red_or_shared(unsigned* p, unsigned v) {
+    asm volatile("red.shared.or.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 }
 __device__ __forceinline__ int fs_atom_add_global(int* p, int v) {
     int old;
@@ -767,7 +767,8 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
                                                                     const uint4* __restrict__ strip_tab, uint32_t* __restrict__ cand,
                                                                     int* __restrict__ cand_count) {
     extern __shared__ __align__(16) unsigned char s_fs[];
-    __shared__ int s_ncorner, s_cellcnt[8];
+    __shared__ int s_ncorner;
+    __shared__ unsigned s_cellmask;  // bit c: cell c of the strip has a keypoint
     constexpr int TP = MCS_FS_TP;
     const int img = blockIdx.y;
     // host-built strip record (build_strip_table)
@@ -802,8 +803,10 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
             *reinterpret_cast<uint4*>(s_tile + r * TP + c * 16) = __ldg(reinterpret_cast<const uint4*>(g0 + (size_t)r * pitch) + c);
         }
         for (int t = threadIdx.x; t < (ih + 2) * (TP / 16); t += MCS_FS_NT) reinterpret_cast<uint4*>(s_score)[t] = make_uint4(0, 0, 0, 0);
-        if (threadIdx.x < 8) s_cellcnt[threadIdx.x] = 0;
-        if (threadIdx.x == 0) s_ncorner = 0;
+        if (threadIdx.x == 0) {
+            s_ncorner = 0;
+            s_cellmask = 0;
+        }
     }
     __syncthreads();
     uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
@@ -827,7 +830,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
                 if (xc != wcell - 1) n = max(n, max(max((int)qp[-TP + 1], (int)qp[1]), (int)qp[TP + 1]));
                 surv = sc > n;
                 if (surv) {
-                    fs_red_add_shared(&s_cellcnt[ci], 1);
+                    fs_red_or_shared(&s_cellmask, 1u << ci);
                     // keypoint in ROI coordinates: FAST x in the cell's sub-image shifted by j * wCell (:864-865)
                     rec = mcs_oct::pack_cand(xi + xoff, ly + yoff, sc);
                 }
@@ -848,9 +851,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_
     if (P.min_th >= P.ini_th) return;  // the retry could only find a subset of nothing
     __syncthreads();
     // only for the cells that returned nothing: FAST(cell, minThFAST)  (:842-845)
-    unsigned failed = 0;
-    for (int c = 0; c < ncells; c++)
-        if (s_cellcnt[c] == 0) failed |= 1u << c;
+    const unsigned failed = ~s_cellmask & ((1u << ncells) - 1u);
     if (!failed) return;  // block-uniform
     if (threadIdx.x == 0) s_ncorner = 0;
     __syncthreads();
