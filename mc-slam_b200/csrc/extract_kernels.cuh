@@ -763,7 +763,10 @@ __device__ __forceinline__ void fs_scan(const FastStripCtx& X, int th, int xa, i
     }
 }
 
-__global__ void __launch_bounds__(MCS_FS_NT, 6) fast_strips_kernel(const __grid_constant__ McsPlan P, ImageSet S,
+#ifndef MCS_FS_MINB
+#define MCS_FS_MINB 6
+#endif
+__global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                     const uint4* __restrict__ strip_tab, uint32_t* __restrict__ cand,
                                                                     int* __restrict__ cand_count) {
     extern __shared__ __align__(16) unsigned char s_fs[];
