@@ -1210,7 +1210,10 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 48 / MCS_DESCF_WARPS) de
             uint4 a = *reinterpret_cast<const uint4*>(&s_pair[warp][q0][4 * g]);
             uint4 b = *reinterpret_cast<const uint4*>(&s_pair[warp][q0 + 1][4 * g]);
             uint4 c = *reinterpret_cast<const uint4*>(&s_pair[warp][q0 + 2][4 * g]);
-            for (int q = q0; q < q1; q++) {
+#pragma unroll
+            for (int it = 0; it < 4; it++) {  // 3 or 4 row pairs per segment; unrolled so that the window rotates by renaming
+                const int q = q0 + it;
+                if (q >= q1) break;
                 const uint4 d = *reinterpret_cast<const uint4*>(&s_pair[warp][q + 3][4 * g]);
                 const uint32_t pa[4] = {a.x, a.y, a.z, a.w}, pb[4] = {b.x, b.y, b.z, b.w}, pc[4] = {c.x, c.y, c.z, c.w}, pd[4] = {d.x, d.y, d.z, d.w};
                 uint32_t oe = 0, oo = 0;

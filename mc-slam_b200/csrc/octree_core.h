@@ -121,8 +121,13 @@ MCS_HD Geo child_geo(const Geo& g, int q) {
 }
 
 // rank of a candidate in the reference's vToDistributeKeys order
-MCS_HD unsigned cand_rank(const Params& P, int x, int y) {
-    int j = (x - 3) / P.w_cell, i = (y - 3) / P.h_cell;
+// The two cell divisions as multiplications: t / n == (t * ceil(2^20 / n)) >> 20 for t * n < 2^20 (coordinates < 4096, cells <= 69 px).
+struct RankDiv {
+    unsigned mw, mh;
+    MCS_HD explicit RankDiv(const Params& P) : mw(((1u << 20) + P.w_cell - 1) / P.w_cell), mh(((1u << 20) + P.h_cell - 1) / P.h_cell) {}
+};
+MCS_HD unsigned cand_rank(const Params& P, const RankDiv& D, int x, int y) {
+    const int j = (int)(((unsigned)(x - 3) * D.mw) >> 20), i = (int)(((unsigned)(y - 3) * D.mh) >> 20);
     return ((unsigned)(i * P.n_cols + j) << 14) | ((unsigned)(y - 3 - i * P.h_cell) << 7) | (unsigned)(x - 3 - j * P.w_cell);
 }
 
@@ -133,6 +138,7 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
     const int NT = ctx.nthreads();
     int* V = S.vars;
     if (n_keys <= 0) return 0;
+    const RankDiv rdiv(P);
 
     // ---- roots (:558-582) --------------------------------------------------------------------------------------
     ctx.par([&] {
@@ -337,14 +343,14 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
         for (int k = ctx.tid(); k < n_keys; k += NT) {
             const uint32_t c = cand[k];
             const int nd = knode[k];
-            if ((unsigned)cand_score(c) == S.best[nd]) ctx.atomic_min(&S.bestrank[nd], cand_rank(P, cand_x(c), cand_y(c)));
+            if ((unsigned)cand_score(c) == S.best[nd]) ctx.atomic_min(&S.bestrank[nd], cand_rank(P, rdiv, cand_x(c), cand_y(c)));
         }
     });
     ctx.par([&] {
         for (int k = ctx.tid(); k < n_keys; k += NT) {
             const uint32_t c = cand[k];
             const int nd = knode[k];
-            if ((unsigned)cand_score(c) == S.best[nd] && cand_rank(P, cand_x(c), cand_y(c)) == S.bestrank[nd]) out[nd] = c;
+            if ((unsigned)cand_score(c) == S.best[nd] && cand_rank(P, rdiv, cand_x(c), cand_y(c)) == S.bestrank[nd]) out[nd] = c;
         }
     });
     return n_out;
