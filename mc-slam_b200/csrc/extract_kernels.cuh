@@ -889,14 +889,21 @@ struct CudaBlockCtx {
         if (threadIdx.x == 0) f();
         __syncthreads();
     }
-    __device__ __forceinline__ void atomic_add(int* p, int v) { atomicAdd(p, v); }
-    __device__ __forceinline__ void atomic_max(unsigned* p, unsigned v) { atomicMax(p, v); }
-    __device__ __forceinline__ void atomic_min(unsigned* p, unsigned v) { atomicMin(p, v); }
+    // every target lives in the block's shared memory (mcs_oct::Shared); plain PTX reductions skip nvcc's same-address aggregation wrapper
+    __device__ __forceinline__ void atomic_add(int* p, int v) {
+        asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    }
+    __device__ __forceinline__ void atomic_max(unsigned* p, unsigned v) {
+        asm volatile("red.shared.max.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    }
+    __device__ __forceinline__ void atomic_min(unsigned* p, unsigned v) {
+        asm volatile("red.shared.min.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    }
     // in-place exclusive scan of a[0..n) in shared memory; collective; returns the total
     __device__ int exclusive_scan(int* a, int n) {
         __shared__ int s_ws[34];
         const int NT = blockDim.x, t = threadIdx.x, lane = t & 31, w = t >> 5, nwarps = NT >> 5;
-        const int per = (n + NT - 1) / NT;
+        const int per = (n + NT - 1) >> (31 - __clz(NT));  // block sizes are powers of two
         const int beg = min(t * per, n), end = min(beg + per, n);
         int sum = 0;
         for (int i = beg; i < end; i++) sum += a[i];
