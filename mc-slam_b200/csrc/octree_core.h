@@ -231,13 +231,19 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
                 c[0] = c[1] = c[2] = c[3] = 0;
             }
         });
+        // four keys per step with all their loads issued first: the passes over the keys are bound by the latency of the
+        // knode[] / cand[] reads (global memory), not by arithmetic
         ctx.par([&] {
-            for (int k = ctx.tid(); k < n_keys; k += NT) {
-                const int nd = knode[k];
-                if (S.flag[nd]) {
-                    const uint32_t c = cand[k];
-                    ctx.atomic_add(&S.cc[nd * 4 + quadrant(geo[nd], cand_x(c), cand_y(c))], 1);
+            for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+                int nd[4];
+                uint32_t c[4];
+                for (int u = 0; u < 4; u++) {
+                    const int k = k0 + u * NT;
+                    nd[u] = k < n_keys ? (int)knode[k] : -1;
+                    c[u] = k < n_keys ? cand[k] : 0u;
                 }
+                for (int u = 0; u < 4; u++)
+                    if (nd[u] >= 0 && S.flag[nd[u]]) ctx.atomic_add(&S.cc[nd[u] * 4 + quadrant(geo[nd[u]], cand_x(c[u]), cand_y(c[u]))], 1);
             }
         });
         // per processed node: number of non-empty children m, expandable children e
@@ -307,14 +313,19 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
             }
         });
         ctx.par([&] {
-            for (int k = ctx.tid(); k < n_keys; k += NT) {
-                const int nd = knode[k];
-                int q = 0;
-                if (S.flag[nd]) {
-                    const uint32_t c = cand[k];
-                    q = quadrant(geo[nd], cand_x(c), cand_y(c));
+            for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+                int nd[4];
+                uint32_t c[4];
+                for (int u = 0; u < 4; u++) {
+                    const int k = k0 + u * NT;
+                    nd[u] = k < n_keys ? (int)knode[k] : -1;
+                    c[u] = k < n_keys ? cand[k] : 0u;
                 }
-                knode[k] = S.map[nd * 4 + q];
+                for (int u = 0; u < 4; u++) {
+                    if (nd[u] < 0) continue;
+                    const int q = S.flag[nd[u]] ? quadrant(geo[nd[u]], cand_x(c[u]), cand_y(c[u])) : 0;
+                    knode[k0 + u * NT] = S.map[nd[u] * 4 + q];
+                }
             }
             if (ctx.tid() == 0) {
                 V[V_CUR] = nxt;
