@@ -148,11 +148,16 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
         }
     });
     ctx.par([&] {
-        for (int k = ctx.tid(); k < n_keys; k += NT) {
-            int r = (int)((float)cand_x(cand[k]) / P.hX);
-            r = r < 0 ? 0 : (r >= P.n_ini ? P.n_ini - 1 : r);
-            knode[k] = (uint16_t)r;
-            ctx.atomic_add(&S.cnt[1][r], 1);
+        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+            uint32_t c[4];
+            for (int u = 0; u < 4; u++) c[u] = k0 + u * NT < n_keys ? cand[k0 + u * NT] : 0u;
+            for (int u = 0; u < 4; u++) {
+                if (k0 + u * NT >= n_keys) break;
+                int r = (int)((float)cand_x(c[u]) / P.hX);
+                r = r < 0 ? 0 : (r >= P.n_ini ? P.n_ini - 1 : r);
+                knode[k0 + u * NT] = (uint16_t)r;
+                ctx.atomic_add(&S.cnt[1][r], 1);
+            }
         }
     });
     ctx.serial([&] {
@@ -348,20 +353,44 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
         }
     });
     ctx.par([&] {
-        for (int k = ctx.tid(); k < n_keys; k += NT) ctx.atomic_max(&S.best[knode[k]], (unsigned)cand_score(cand[k]));
-    });
-    ctx.par([&] {
-        for (int k = ctx.tid(); k < n_keys; k += NT) {
-            const uint32_t c = cand[k];
-            const int nd = knode[k];
-            if ((unsigned)cand_score(c) == S.best[nd]) ctx.atomic_min(&S.bestrank[nd], cand_rank(P, rdiv, cand_x(c), cand_y(c)));
+        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+            int nd[4];
+            uint32_t c[4];
+            for (int u = 0; u < 4; u++) {
+                const int k = k0 + u * NT;
+                nd[u] = k < n_keys ? (int)knode[k] : -1;
+                c[u] = k < n_keys ? cand[k] : 0u;
+            }
+            for (int u = 0; u < 4; u++)
+                if (nd[u] >= 0) ctx.atomic_max(&S.best[nd[u]], (unsigned)cand_score(c[u]));
         }
     });
     ctx.par([&] {
-        for (int k = ctx.tid(); k < n_keys; k += NT) {
-            const uint32_t c = cand[k];
-            const int nd = knode[k];
-            if ((unsigned)cand_score(c) == S.best[nd] && cand_rank(P, rdiv, cand_x(c), cand_y(c)) == S.bestrank[nd]) out[nd] = c;
+        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+            int nd[4];
+            uint32_t c[4];
+            for (int u = 0; u < 4; u++) {
+                const int k = k0 + u * NT;
+                nd[u] = k < n_keys ? (int)knode[k] : -1;
+                c[u] = k < n_keys ? cand[k] : 0u;
+            }
+            for (int u = 0; u < 4; u++)
+                if (nd[u] >= 0 && (unsigned)cand_score(c[u]) == S.best[nd[u]])
+                    ctx.atomic_min(&S.bestrank[nd[u]], cand_rank(P, rdiv, cand_x(c[u]), cand_y(c[u])));
+        }
+    });
+    ctx.par([&] {
+        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+            int nd[4];
+            uint32_t c[4];
+            for (int u = 0; u < 4; u++) {
+                const int k = k0 + u * NT;
+                nd[u] = k < n_keys ? (int)knode[k] : -1;
+                c[u] = k < n_keys ? cand[k] : 0u;
+            }
+            for (int u = 0; u < 4; u++)
+                if (nd[u] >= 0 && (unsigned)cand_score(c[u]) == S.best[nd[u]] && cand_rank(P, rdiv, cand_x(c[u]), cand_y(c[u])) == S.bestrank[nd[u]])
+                    out[nd[u]] = c[u];
         }
     });
     return n_out;
