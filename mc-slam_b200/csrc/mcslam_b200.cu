@@ -1102,11 +1102,15 @@ struct mcs_rig {
         Engine::HiLane hi;       // high-priority side stream (use_hi)
         size_t f32_bytes = 0;
     };
-    static constexpr int NSLOT = 4;
+#ifndef MCS_NSLOT
+#define MCS_NSLOT 6
+#endif
+    static constexpr int NSLOT = MCS_NSLOT;
     Slot slots[NSLOT];
     cudaEvent_t ev_begin = nullptr;
     int tri_list_stride = 0, sm_count = 148;
     int chunk_frames = 64;  // frames per pipelined chunk (0 = no chunking)
+    int host_chunk_div = 4; // host-buffer calls use chunks of chunk_frames / host_chunk_div (MCS_HOST_CHUNK_DIV): 6 slots x quarter chunks measured best
     int tri_per_sm = 3;     // resident tri_solve blocks per SM (MCS_TRI_PER_SM; 0 = as many as shared memory holds): 3 measured best — the
                             // one-warp blocks hold 44 KB of shared memory each for the length of a Jacobi chain, which other chunks' kernels need
     bool use_hi = false;    // MCS_HIPRIO=1: octree, merge and triangulation on the slots' high-priority side streams
@@ -1221,6 +1225,7 @@ struct mcs_rig {
         }
         if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
         if (const char* e = getenv("MCS_HIPRIO")) use_hi = atoi(e) != 0;
+        if (const char* e = getenv("MCS_HOST_CHUNK_DIV")) host_chunk_div = std::max(1, std::min(16, atoi(e)));
         if (const char* e = getenv("MCS_TRI_PER_SM")) tri_per_sm = std::max(0, atoi(e));
         if (use_hi) {
             int lo = 0, hi = 0;
@@ -1523,7 +1528,7 @@ struct mcs_rig {
         if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
         if ((rc = undistort_masks(&dm, n_frames))) return rc;
         // host-buffer calls use half-size chunks: more copies in flight hide more of the PCIe time
-        const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / 2) : chunk_frames;
+        const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / host_chunk_div) : chunk_frames;
         const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
         const int step = chunked ? cf : n_frames;
         mcs::ImageSet set{};
