@@ -1113,7 +1113,7 @@ struct mcs_rig {
     int host_chunk_div = 4; // host-buffer calls use chunks of chunk_frames / host_chunk_div (MCS_HOST_CHUNK_DIV): 6 slots x quarter chunks measured best
     int tri_per_sm = 3;     // resident tri_solve blocks per SM (MCS_TRI_PER_SM; 0 = as many as shared memory holds): 3 measured best — the
                             // one-warp blocks hold 44 KB of shared memory each for the length of a Jacobi chain, which other chunks' kernels need
-    bool use_hi = false;    // MCS_HIPRIO=1: octree, merge and triangulation on the slots' high-priority side streams
+    bool use_hi = true;     // octree, merge and triangulation on the slots' high-priority side streams (MCS_HIPRIO=0 switches it off): +0.7 %
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
     size_t masks_bytes = 0;
