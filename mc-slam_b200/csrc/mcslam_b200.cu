@@ -1527,7 +1527,7 @@ struct mcs_rig {
         int rc;
         if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
         if ((rc = undistort_masks(&dm, n_frames))) return rc;
-        // host-buffer calls use half-size chunks: more copies in flight hide more of the PCIe time
+        // host-buffer calls use smaller chunks (chunk_frames / host_chunk_div): more copies in flight hide more of the PCIe time
         const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / host_chunk_div) : chunk_frames;
         const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
         const int step = chunked ? cf : n_frames;
