@@ -246,3 +246,17 @@ def test_fast_strips_cover_the_cell_grid_exactly(w, h):
         assert key in covered, key
         iw, ih, xo, yo = covered[key]
         assert (iw, ih) == (cw - 6, ch - 6) and (xo, yo) == (int(c[3] & 0xFFFF), int(c[3] >> 16))
+
+
+def test_algorithmic_bytes_model_matches_survey_8d():
+    """bench.py's roofline numerator is SURVEY.md 8(d)'s two-pass pixel model: level sizes from the reference constructor's f32
+    arithmetic, 13,185,090 B per rig frame for config 1/2, 14,245,090 for config 3 (with the mask lookups), 124,259,632 for config 4."""
+    import bench
+    sizes = bench.level_sizes(720, 540)
+    assert sizes == [(720, 540), (600, 450), (500, 375), (417, 312), (347, 260), (289, 217), (241, 181), (201, 151)]
+    assert sum(a * b for a, b in sizes) == 1203309
+    assert sum(a * b for a, b in bench.level_sizes(1920, 1200)) == 7131727
+    total, stages = bench.algorithmic_bytes()
+    assert total == 13185090 and stages["match"] == 720000 and stages["triangulate"] == 132000
+    assert bench.algorithmic_bytes(5, 720, 540, 2000)[0] + 4 * 5 * 2000 == 14245090
+    assert bench.algorithmic_bytes(8, 1920, 1200, 4000)[0] == 124259632
