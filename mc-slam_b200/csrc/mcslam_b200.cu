@@ -1164,8 +1164,8 @@ struct mcs_rig {
     int init(const mcs_rig_config* c, const mcs_calib* cal) {
         cfg = *c;
         C = c->num_cams; F = c->max_frames;
-        calib_host.assign(cal, cal + std::max(C, 0));
-        if (C < 1 || C > MCS_MAX_CAMS || F < 1) { set_err("num_cams must be in [1,8], max_frames >= 1"); return MCS_ERR_ARG; }
+        if (C < 1 || C > MCS_MAX_CAMS || F < 1 || !cal) { set_err("num_cams must be in [1,8], max_frames >= 1, calibration non-null"); return MCS_ERR_ARG; }
+        calib_host.assign(cal, cal + C);
         int rc = eng.init(c->nfeatures, c->scale_factor, c->nlevels, c->ini_th_fast, c->min_th_fast, c->device, c->width, c->height, C * F);
         if (rc) return rc;
         kp_cap = eng.plan.kp_cap;
@@ -1435,6 +1435,7 @@ struct mcs_rig {
     // RECTIFY: the segmentation masks are undistorted with the same maps (MultiCameraFrame.cpp:131-134); *dm is replaced
     int undistort_masks(const float** dm, int n_frames) {
         if (!undistort_on || !*dm) return 0;
+        if (n_frames < 1 || n_frames > F) { set_err("n_frames exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
         const int w = cfg.width, h = cfg.height;
         const size_t need = (size_t)n_frames * C * w * h * sizeof(float);
         if (need > masks_und_bytes) {
@@ -1471,6 +1472,7 @@ struct mcs_rig {
     int upload_masks(const float* masks, int n_frames, const float** out) {
         *out = nullptr;
         if (!masks) return 0;
+        if (n_frames < 1 || n_frames > F) { set_err("n_frames exceeds the handle's capacity"); return MCS_ERR_CAPACITY; }
         const size_t need = (size_t)n_frames * C * cfg.width * cfg.height * sizeof(float);
         if (need > masks_bytes) {
             CK(cudaStreamSynchronize(eng.stream));
@@ -1735,6 +1737,7 @@ int mcs_rig_get_intra_matches(mcs_rig* rig, int frame, int32_t* rows, int capaci
 
 int mcs_rig_triangulate(mcs_rig* rig, int n_frames, const float* masks) {
     RIG_ENTER(rig);
+    if (n_frames < 1 || n_frames > rig->F || n_frames > rig->n_matched) { set_err("triangulate: n_frames out of range (1 .. frames intra-matched)"); return n_frames > rig->F ? MCS_ERR_CAPACITY : MCS_ERR_STATE; }
     const float* dm = nullptr;
     int rc = rig->upload_masks(masks, n_frames, &dm);
     if (!rc) rc = rig->undistort_masks(&dm, n_frames);
@@ -1743,6 +1746,7 @@ int mcs_rig_triangulate(mcs_rig* rig, int n_frames, const float* masks) {
 }
 int mcs_rig_triangulate_device_masks(mcs_rig* rig, int n_frames, const void* d_masks) {
     RIG_ENTER(rig);
+    if (n_frames < 1 || n_frames > rig->F || n_frames > rig->n_matched) { set_err("triangulate: n_frames out of range (1 .. frames intra-matched)"); return n_frames > rig->F ? MCS_ERR_CAPACITY : MCS_ERR_STATE; }
     const float* dm = (const float*)d_masks;
     int rc = rig->undistort_masks(&dm, n_frames);
     if (rc) return rc;
@@ -1956,12 +1960,17 @@ struct mcs_matcher {
     mcs::Knn2Set *d_sets = nullptr, *h_sets = nullptr;
     int4* d_out = nullptr;
     long long launches = 0;
+    // h_sets is one pinned staging buffer read by an asynchronous H2D copy: ev_sets marks the end of the last copy out of it, and
+    // layout() waits for that copy (not for the kernel behind it) before it overwrites the table for the next call
+    cudaEvent_t ev_sets = nullptr;
+    bool sets_in_flight = false;
     // subset matcher workspace (grown on demand): CSR offsets, index lists, per-query scratch, outputs
     int *d_sub_i32 = nullptr;
     size_t sub_cap = 0;
     ~mcs_matcher() {
         if (cudaSetDevice(device) != cudaSuccess) return;
-        if (stream) cudaStreamDestroy(stream);
+        if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
+        if (ev_sets) cudaEventDestroy(ev_sets);
         cudaFree(d_q); cudaFree(d_t); cudaFree(d_sets); cudaFree(d_out); cudaFree(d_sub_i32);
         if (h_sets) cudaFreeHost(h_sets);
     }
@@ -1973,6 +1982,7 @@ struct mcs_matcher {
         CK(cudaMalloc(&d_sets, (size_t)max_sets * sizeof(mcs::Knn2Set)));
         CK(cudaMallocHost(&h_sets, (size_t)max_sets * sizeof(mcs::Knn2Set)));
         CK(cudaMalloc(&d_out, (size_t)std::max(max_q, 1) * sizeof(int4)));
+        CK(cudaEventCreateWithFlags(&ev_sets, cudaEventDisableTiming));
         return 0;
     }
     // fills h_sets from the per-set counts; returns the largest query count or a negative error
@@ -1980,6 +1990,10 @@ struct mcs_matcher {
         if (n_sets < 1 || n_sets > max_sets || !q_count || !t_count) { set_err("knn2: bad n_sets"); return MCS_ERR_ARG; }
         tot_q = tot_t = 0;
         int max_nq = 0;
+        if (sets_in_flight) {  // the previous call's copy of the set table may still be reading h_sets
+            CK(cudaEventSynchronize(ev_sets));
+            sets_in_flight = false;
+        }
         for (int i = 0; i < n_sets; i++) {
             if (q_count[i] < 0 || t_count[i] < 0) { set_err("knn2: negative count"); return MCS_ERR_ARG; }
             if (t_count[i] > 65535) { set_err("knn2: more than 65535 train descriptors in one set"); return MCS_ERR_CAPACITY; }
@@ -1992,6 +2006,8 @@ struct mcs_matcher {
     }
     int launch(const uint8_t* dq, const uint8_t* dt, const int* counts, int n_sets, int max_nq, int4* out) {
         CK(cudaMemcpyAsync(d_sets, h_sets, (size_t)n_sets * sizeof(mcs::Knn2Set), cudaMemcpyHostToDevice, stream));
+        CK(cudaEventRecord(ev_sets, stream));
+        sets_in_flight = true;
         if (max_nq > 0) {
             dim3 g((max_nq + MCS_MATCH_NT - 1) / MCS_MATCH_NT, n_sets);
             mcs::knn2_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, stream>>>(dq, dt, d_sets, counts, out);

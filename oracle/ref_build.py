@@ -15,6 +15,7 @@ it is expected to hold, so a different reference checkout fails loudly instead o
 On the GPU box /root/reference does not exist: the prebuilt oracle/_ref/libmcsref.so travels with the snapshot.
 """
 import os
+import shutil
 import subprocess
 import sys
 
@@ -90,7 +91,10 @@ def build(force=False, verbose=False):
         "-L", HERE, "-loracle", "-Wl,-rpath,$ORIGIN/.."]
     if verbose:
         print(" ".join(cmd))
-    subprocess.check_call(cmd)
+    try:
+        subprocess.check_call(cmd)
+    finally:
+        shutil.rmtree(GEN, ignore_errors=True)  # the extracted reference text is needed for the compile only
     return SO
 
 

@@ -62,6 +62,37 @@ def test_knn2_device_entry():
         B.device_free(0, p)
 
 
+def test_knn2_device_back_to_back_different_layouts():
+    """mcs_knn2_device is asynchronous and stages its set table through one pinned buffer: a second call with a different layout,
+    queued while the first may still be running, must not disturb the first (h_sets reuse)."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    from mcslam_b200 import binding as B
+    rng = np.random.default_rng(16)
+    q = rng.integers(0, 256, (4000, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (6000, 32), dtype=np.uint8)
+    dq, dt = B.device_malloc(0, q.nbytes), B.device_malloc(0, t.nbytes)
+    B.device_upload(0, dq, q)
+    B.device_upload(0, dt, t)
+    layouts = [([1000, 3000], [2000, 4000]), ([4000], [6000]), ([100, 200, 300, 3400], [3000, 1000, 1000, 1000]), ([2500, 1500], [100, 5900])]
+    m = M.Matcher(max_sets=4)
+    outs = [B.device_malloc(0, 4000 * 16) for _ in layouts]
+    for rep in range(3):
+        for (qc, tc), do in zip(layouts, outs):
+            assert m.knn2_device(dq, qc, dt, tc, do) == 4000
+        m.synchronize()
+        for (qc, tc), do in zip(layouts, outs):
+            out = np.zeros((4000, 4), np.int32)
+            B.device_download(0, out, do)
+            qo = to = 0
+            for a, b in zip(qc, tc):
+                assert np.array_equal(out[qo:qo + a], O.knn2(q[qo:qo + a], t[to:to + b])), (rep, qc, tc)
+                qo += a
+                to += b
+    for p_ in [dq, dt] + outs:
+        B.device_free(0, p_)
+
+
 def test_rig_knn2_images_consecutive_frames():
     """findMatchesMono's knnMatch for every consecutive frame pair of a batch on the descriptors the rig already holds."""
     import mcslam_b200 as M
