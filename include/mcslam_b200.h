@@ -261,6 +261,20 @@ MCS_API int mcs_knn2(mcs_matcher* m, const uint8_t* q_desc, const int* q_count, 
 /* Same with descriptors and output resident in device memory; asynchronous on mcs_matcher_stream(). */
 MCS_API int mcs_knn2_device(mcs_matcher* m, const void* d_q_desc, const int* q_count, const void* d_t_desc, const int* t_count,
                             int n_sets, void* d_out_knn);
+/* mcs_knn2_device with NO allocation anywhere: no handle, no cudaMalloc / cudaFree / pinned memory, no host-to-device copy.  It has
+ * no counterpart in the reference; it was added for callers that cannot allocate (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The kernel's scratch - the per-set offset table - is a
+ * file-scope __device__ array of MCS_KNN2_STATIC_MAX_SETS entries (8 KB, held by every GPU that loads the library until exit) that a
+ * one-block kernel fills on the device from the counts.  Inputs and outputs are the caller's device buffers as for mcs_knn2_device;
+ * `stream` is a cudaStream_t (NULL = the default stream); the call is asynchronous on it.  Limits: n_sets <= MCS_KNN2_STATIC_MAX_SETS,
+ * <= 65535 train rows per set, <= MCS_KNN2_STATIC_MAX_ROWS query rows and train rows per call; beyond them MCS_ERR_CAPACITY with a
+ * text in mcs_last_error().  All calls on one GPU share the one table, which keeps the last call's contents (entries [0, n_sets)
+ * are rewritten by each call; nothing has to start at zero): calls that may OVERLAP on the GPU (different streams, no ordering
+ * between them) race on it - issue them on one stream or order them with events.  Returns the number of query rows. */
+#define MCS_KNN2_STATIC_MAX_SETS 256
+#define MCS_KNN2_STATIC_MAX_ROWS (1 << 24)
+MCS_API int mcs_knn2_device_static(int device, void* stream, const void* d_q_desc, const int* q_count, const void* d_t_desc,
+                                   const int* t_count, int n_sets, void* d_out_knn);
 MCS_API void* mcs_matcher_stream(mcs_matcher* m);
 MCS_API int mcs_matcher_synchronize(mcs_matcher* m);
 MCS_API long long mcs_matcher_kernel_launches(const mcs_matcher* m);

@@ -38,7 +38,7 @@ EXPORTS = [
     "mcs_rig_process_device", "mcs_rig_get_counts", "mcs_rig_stream", "mcs_rig_synchronize", "mcs_rig_kernel_launches", "mcs_rig_stage_times",
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
-    "mcs_knn2_device", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
+    "mcs_knn2_device", "mcs_knn2_device_static", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
     "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2", "mcs_plan_fast_tables",
 ]
 
@@ -108,6 +108,7 @@ def lib():
     L.mcs_matcher_destroy.argtypes = [vp]
     L.mcs_knn2.argtypes = [vp, vp, vp, vp, vp, ci, vp]
     L.mcs_knn2_device.argtypes = [vp, vp, vp, vp, vp, ci, vp]
+    L.mcs_knn2_device_static.argtypes = [ci, vp, vp, vp, vp, vp, ci, vp]
     L.mcs_matcher_stream.restype = vp
     L.mcs_matcher_stream.argtypes = [vp]
     L.mcs_matcher_synchronize.argtypes = [vp]
@@ -593,6 +594,14 @@ class Vocabulary:
         wid, nid, w = np.full(shape, -1, np.int32), np.full(shape, -1, np.int32), np.zeros(shape, np.float64)
         _check(lib().mcs_rig_vocab_transform(rig.hd, self.hd, levelsup, _p(wid), _p(nid), _p(w)), "rig_vocab_transform")
         return wid, nid, w
+
+
+def knn2_device_static(device, d_q, q_counts, d_t, t_counts, d_out, stream=None):
+    """mcs_knn2_device_static: the knn2 kernel with its set table in a static __device__ array; allocates nothing."""
+    qc = np.ascontiguousarray(q_counts, np.int32)
+    tc = np.ascontiguousarray(t_counts, np.int32)
+    return _check(lib().mcs_knn2_device_static(device, C.c_void_p(stream), C.c_void_p(d_q), _p(qc), C.c_void_p(d_t), _p(tc), len(qc),
+                                               C.c_void_p(d_out)), "knn2_device_static")
 
 
 def device_malloc(device, nbytes):

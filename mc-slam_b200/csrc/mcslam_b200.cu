@@ -2060,6 +2060,92 @@ int mcs_knn2_device(mcs_matcher* m, const void* d_q_desc, const int* q_count, co
     if (rc) return rc;
     return tot_q;
 }
+// ------------------------------------------------------------------------------------------------------------
+// mcs_knn2_device_static: knnMatch(k = 2) on device-resident sets WITHOUT any allocation (
+// no counterpart in the reference).  The set table that knn2_kernel reads is the kernel's scratch: here it lives in a file-scope
+// __device__ array instead of a cudaMalloc'ed buffer, and a one-block kernel builds it on the device from the counts (passed by value
+// as a kernel argument), so the call needs no handle, no workspace, no host-to-device copy.  Every GPU that loads the library holds
+// the 8 KB array until exit.  In host code `g_knn2_static_sets` is only a stand-in for the symbol: its device address is taken once
+// per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+// ------------------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+static __device__ __align__(256) mcs::Knn2Set g_knn2_static_sets[MCS_KNN2_STATIC_MAX_SETS];
+
+struct Knn2StaticCounts {  // by-value kernel argument: 2 KB
+    int q[MCS_KNN2_STATIC_MAX_SETS], t[MCS_KNN2_STATIC_MAX_SETS];
+};
+
+// entries [0, n_sets) are rewritten by every call (nothing in the scratch has to start at zero); one thread: n_sets <= 256
+__global__ void knn2_static_layout_kernel(const __grid_constant__ Knn2StaticCounts c, int n_sets, mcs::Knn2Set* __restrict__ sets) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int tq = 0, tt = 0;
+    for (int i = 0; i < n_sets; i++) {
+        sets[i] = mcs::Knn2Set{tq, c.q[i], tt, c.t[i], tq, 0, 0, 0};
+        tq += c.q[i];
+        tt += c.t[i];
+    }
+}
+
+constexpr int kMaxDevices = 64;
+std::mutex g_knn2_static_mu;
+mcs::Knn2Set* g_knn2_static_ptr[kMaxDevices] = {};
+
+// device address of the scratch array on `device` (which must be current); looked up once per device
+int knn2_static_scratch(int device, mcs::Knn2Set** out) {
+    std::lock_guard<std::mutex> lk(g_knn2_static_mu);
+    if (!g_knn2_static_ptr[device]) {
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_knn2_static_sets));
+        if (!p) { set_err("knn2_device_static: cudaGetSymbolAddress returned null"); return MCS_ERR_CUDA; }
+        g_knn2_static_ptr[device] = (mcs::Knn2Set*)p;
+    }
+    *out = g_knn2_static_ptr[device];
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int mcs_knn2_device_static(int device, void* stream, const void* d_q_desc, const int* q_count, const void* d_t_desc, const int* t_count,
+                           int n_sets, void* d_out_knn) {
+    if (!d_q_desc || !d_t_desc || !d_out_knn || !q_count || !t_count) { set_err("knn2_device_static: null argument"); return MCS_ERR_ARG; }
+    if (n_sets < 1 || n_sets > MCS_KNN2_STATIC_MAX_SETS) {
+        set_err("knn2_device_static: n_sets must be in [1, " + std::to_string(MCS_KNN2_STATIC_MAX_SETS) + "] (size of the static set table)");
+        return MCS_ERR_CAPACITY;
+    }
+    if (device < 0 || device >= kMaxDevices) { set_err("knn2_device_static: device ordinal out of range"); return MCS_ERR_ARG; }
+    Knn2StaticCounts c;
+    long long tot_q = 0, tot_t = 0;
+    int max_nq = 0;
+    for (int i = 0; i < n_sets; i++) {
+        if (q_count[i] < 0 || t_count[i] < 0) { set_err("knn2_device_static: negative count"); return MCS_ERR_ARG; }
+        if (t_count[i] > 65535) { set_err("knn2_device_static: more than 65535 train descriptors in one set"); return MCS_ERR_CAPACITY; }
+        c.q[i] = q_count[i];
+        c.t[i] = t_count[i];
+        tot_q += q_count[i];
+        tot_t += t_count[i];
+        max_nq = std::max(max_nq, q_count[i]);
+    }
+    if (tot_q > MCS_KNN2_STATIC_MAX_ROWS || tot_t > MCS_KNN2_STATIC_MAX_ROWS) {
+        set_err("knn2_device_static: more than " + std::to_string(MCS_KNN2_STATIC_MAX_ROWS) + " query or train rows in one call");
+        return MCS_ERR_CAPACITY;
+    }
+    CK(cudaSetDevice(device));
+    mcs::Knn2Set* d_sets = nullptr;
+    int rc = knn2_static_scratch(device, &d_sets);
+    if (rc) return rc;
+    if (max_nq == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    knn2_static_layout_kernel<<<1, 32, 0, st>>>(c, n_sets, d_sets);
+    dim3 g((max_nq + MCS_MATCH_NT - 1) / MCS_MATCH_NT, n_sets);
+    mcs::knn2_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, st>>>((const uint8_t*)d_q_desc, (const uint8_t*)d_t_desc, d_sets, nullptr,
+                                                                    (int4*)d_out_knn);
+    CK(cudaGetLastError());
+    return (int)tot_q;
+}
+
 void* mcs_matcher_stream(mcs_matcher* m) { return m ? (void*)m->stream : nullptr; }
 int mcs_matcher_synchronize(mcs_matcher* m) {
     if (!m) return MCS_ERR_ARG;
