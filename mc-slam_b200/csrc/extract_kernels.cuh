@@ -659,6 +659,7 @@ struct FastStripCtx {
     uint16_t* corner;
     int* ncorner;
     int ih, lane;
+    int cap;  // entries the corner list holds; the count keeps running past it
 };
 
 // one batch of the warp's stack: arc strength (= cv::FAST's score), corner <=> strength >= th
@@ -676,7 +677,8 @@ __device__ __forceinline__ void fs_eval(const FastStripCtx& X, bool active, int 
         int base = 0;
         if (X.lane == 0) base = fs_atom_add_shared(X.ncorner, __popc(m));
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (corner) X.corner[base + __popc(m & ((1u << X.lane) - 1u))] = (uint16_t)(e & 0x7FFF);
+        const int at = base + __popc(m & ((1u << X.lane) - 1u));
+        if (corner && at < X.cap) X.corner[at] = (uint16_t)(e & 0x7FFF);
     }
 }
 
@@ -763,15 +765,49 @@ __device__ __forceinline__ void fs_scan(const FastStripCtx& X, int th, int xa, i
     }
 }
 
+#define MCS_FT_CORNERS 2048
+struct FastTmaMaps {
+    CUtensorMap map[MCS_PLAN_MAX_LEVELS];
+    int box_rows[MCS_PLAN_MAX_LEVELS];
+};
+
+__device__ __forceinline__ uint32_t ft_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// Bounded: a tile that never arrives (a bad tensor map) traps the kernel instead of hanging the device.
+__device__ __forceinline__ void ft_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (int spin = 0; spin < (1 << 22); spin++) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+    }
+    __trap();
+}
+
 #ifndef MCS_FS_MINB
 #define MCS_FS_MINB 6
 #endif
+// TMA = true (the default): the tile comes as ONE cp.async.bulk.tensor.3d issued by thread 0 onto an mbarrier (box 208 x box_rows[level]
+// of the level's (x, y, image) tensor map; rows of the box below the image arrive as zeros) instead of the per-thread LDG.128 + STS.128
+// loop with its index division; the score tile is cleared while the tile is in flight.  img0 = image index of blockIdx.y = 0 in the
+// tensor maps (which are encoded on image 0 of the workspace).
+template <bool TMA>
 __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(const __grid_constant__ McsPlan P, ImageSet S,
+                                                                    const __grid_constant__ FastTmaMaps M, int img0,
                                                                     const uint4* __restrict__ strip_tab, uint32_t* __restrict__ cand,
                                                                     int* __restrict__ cand_count) {
-    extern __shared__ __align__(16) unsigned char s_fs[];
-    __shared__ int s_ncorner;
-    __shared__ unsigned s_cellmask;  // bit c: cell c of the strip has a keypoint
+    // no static shared memory: the dynamic block then starts at the (1 KB aligned) base of the CTA's window, which makes the tile a valid
+    // TMA destination (128-byte aligned) without a run-time fix-up
+    extern __shared__ __align__(128) unsigned char s_fs[];
+    uint64_t& s_bar = *reinterpret_cast<uint64_t*>(s_fs + P.fs_ofs_ctl);
+    int& s_ncorner = *reinterpret_cast<int*>(s_fs + P.fs_ofs_ctl + 8);
+    unsigned& s_cellmask = *reinterpret_cast<unsigned*>(s_fs + P.fs_ofs_ctl + 12);  // bit c: cell c of the strip has a keypoint
     constexpr int TP = MCS_FS_TP;
     const int img = blockIdx.y;
     // host-built strip record (build_strip_table)
@@ -783,8 +819,6 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
     const uint32_t mg_groups = rb.x, mg_quads = rb.y, mg_cell = rb.z;
     const McsLevel& Lv = P.L[level];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int pitch;
-    const uint8_t* src = level_ptr(P, S, img, level, pitch);
     const int ox = iniX & ~15;         // image x of tile byte 0
     const int x0 = iniX + 3 - ox;      // tile x of interior column 0 (3..18)
     const int ch = ih + 6;
@@ -798,7 +832,26 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
     X.ncorner = &s_ncorner;
     X.ih = ih;
     X.lane = lane;
-    {   // stage the sub-image rows [iniY, iniY + ch) as 16-byte copies (rows are 16-byte aligned: make_set), zero the score tile
+    X.cap = 0x7FFFFFFF;  // the list is sized for every pixel of the largest strip
+    if constexpr (TMA) {
+        if (threadIdx.x == 0) {
+            const uint32_t bar = ft_smem_u32(&s_bar);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TP * M.box_rows[level]) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+                             ft_smem_u32(s_tile)),
+                         "l"(reinterpret_cast<uint64_t>(&M.map[level])), "r"(bar), "r"(ox), "r"(iniY), "r"(img0 + img)
+                         : "memory");
+            s_ncorner = 0;
+            s_cellmask = 0;
+        }
+        for (int t = threadIdx.x; t < (ih + 2) * (TP / 16); t += MCS_FS_NT) reinterpret_cast<uint4*>(s_score)[t] = make_uint4(0, 0, 0, 0);
+        __syncthreads();  // the barrier is initialised, the score tile is zero
+        ft_mbar_wait(ft_smem_u32(&s_bar), 0);
+    } else {   // stage the sub-image rows [iniY, iniY + ch) as 16-byte copies (rows are 16-byte aligned: make_set), zero the score tile
+        int pitch;
+        const uint8_t* src = level_ptr(P, S, img, level, pitch);
         const int nq = (x0 + wint + 3 + 15) >> 4;
         const uint8_t* g0 = src + (size_t)iniY * pitch + ox;
         for (int t = threadIdx.x; t < nq * ch; t += MCS_FS_NT) {
@@ -810,8 +863,8 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
             s_ncorner = 0;
             s_cellmask = 0;
         }
+        __syncthreads();
     }
-    __syncthreads();
     uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
     int* cnt = cand_count + img * P.nlevels + level;
     // strict-'>' 8-neighbour NMS over the corner list; a neighbour in another cell of the strip scores 0 for this pixel
@@ -866,6 +919,179 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
     }
     __syncthreads();
     nms();
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K3c  FAST strips, persistent blocks with TMA tile staging (the default).  Same arithmetic and the same strip records as
+// fast_strips_kernel; what changes is how a block gets its pixels and how long it lives:
+//   * every (level) plane is described by a 3-D tensor map (x, y, image) with a 208 x box_rows[level] box; ONE elected thread
+//     issues cp.async.bulk.tensor.3d for a whole strip tile onto an mbarrier — no per-thread LDG.128 + STS.128 staging loop, no index
+//     division, out-of-image rows of the box arrive as zeros;
+//   * a block takes work items (strip, image) — blockIdx.x first, then from a global counter (a fixed stride gives a block only
+//     the strips of one residue class and measured 30 % slower than the plain kernel) — with two tile buffers: the tile of item
+//     k + 1 is in flight while item k is scanned, so the load latency every short-lived block of fast_strips_kernel paid is hidden;
+//   * the score tile is zeroed once per block; after each NMS only the bytes written for corners are cleared again.  The corner
+//     list has a fixed capacity (MCS_FT_CORNERS); a strip with more corners than that (dense noise) runs its NMS as a scan of the
+//     score tile instead — same survivors, the candidate list is unordered anyway.
+// ------------------------------------------------------------------------------------------------------------
+#ifndef MCS_FT_MINB
+#define MCS_FT_MINB 6
+#endif
+__global__ void __launch_bounds__(MCS_FS_NT, MCS_FT_MINB) fast_strips_tma_kernel(const __grid_constant__ McsPlan P, const __grid_constant__ FastTmaMaps M,
+                                                                        const uint4* __restrict__ strip_tab, int n_strips, int n_items, int img0,
+                                                                        uint32_t* __restrict__ cand, int* __restrict__ cand_count,
+                                                                        int* __restrict__ work_ctr) {
+    // no static shared memory in this kernel: the dynamic block then starts at the (1 KB aligned) base of the CTA's window, so the TMA
+    // destinations are 128-byte aligned without a run-time fix-up and every address below is base + a constant-bank offset
+    extern __shared__ __align__(128) unsigned char s_ft[];
+    constexpr int TP = MCS_FS_TP;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* s_score = s_ft + P.ft_ofs_score;
+    const int score_quads = P.ft_score_bytes >> 4;
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_ft + P.ft_ofs_ctl);         // [2] tile-arrived barriers
+    int* s_ctl = reinterpret_cast<int*>(s_ft + P.ft_ofs_ctl + 16);
+    int& s_ncorner = s_ctl[0];
+    int* s_item = s_ctl + 2;              // [2][2] (work item, image) whose tile is in (or on its way to) buffer 0 / 1; item >= n_items: none left
+    unsigned* s_cellmask3 = reinterpret_cast<unsigned*>(s_ctl + 6);  // [3] bit c: cell c of the strip has a keypoint; item k uses word k % 3 (loop head)
+    FastStripCtx X;
+    X.score = s_score;
+    X.wq = reinterpret_cast<uint16_t*>(s_ft + P.ft_ofs_wq) + warp * MCS_FS_WQ;
+    X.corner = reinterpret_cast<uint16_t*>(s_ft + P.ft_ofs_corner);
+    X.ncorner = &s_ncorner;
+    X.lane = lane;
+    X.cap = MCS_FT_CORNERS;
+    // one elected thread: tile of work item `w` -> buffer `b`
+    auto issue = [&](int w, int b) {
+        const int img = w / n_strips, s = w - img * n_strips;
+        s_item[2 * b] = w;
+        s_item[2 * b + 1] = img;
+        const uint4 ra = __ldg(strip_tab + 2 * s);
+        const int level = (int)(ra.x & 0xFFu), iniX = (int)(ra.y & 0xFFFFu), iniY = (int)(ra.y >> 16);
+        const uint32_t bar = ft_smem_u32(&s_bar[b]), dst = ft_smem_u32(s_ft + b * P.ft_tile_bytes);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TP * M.box_rows[level]) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+                     "l"(reinterpret_cast<uint64_t>(&M.map[level])), "r"(bar), "r"(iniX & ~15), "r"(iniY), "r"(img0 + img)
+                     : "memory");
+    };
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ft_smem_u32(&s_bar[0])), "r"(1) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ft_smem_u32(&s_bar[1])), "r"(1) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        s_ncorner = 0;
+        s_cellmask3[0] = 0;
+        if ((int)blockIdx.x < n_items) issue(blockIdx.x, 0);
+        else s_item[0] = n_items;
+    }
+    for (int t = threadIdx.x; t < score_quads; t += MCS_FS_NT) reinterpret_cast<uint4*>(s_score)[t] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    int k3 = 0;
+    for (int k = 0;; k++, k3 = k3 == 2 ? 0 : k3 + 1) {
+        const int b = k & 1;
+        const int2 wi = *reinterpret_cast<const int2*>(s_item + 2 * b);  // written by thread 0 at the head of item k - 1 (or before the first barrier); barriers since
+        const int w = wi.x;
+        if (w >= n_items) break;
+        if (threadIdx.x == 0) {
+            // The mask word of item k + 1 is cleared here, not at the end of item k: thread 0 may reach this point while other
+            // warps still read the word of item k - 1 (the `failed` test below has no barrier after it), hence three words.
+            s_cellmask3[k3 == 2 ? 0 : k3 + 1] = 0;
+            const int wn = (int)gridDim.x + fs_atom_add_global(work_ctr, 1);
+            if (wn < n_items) issue(wn, b ^ 1);  // tile buffer b ^ 1 was last read before the barrier that ended item k - 1
+            else s_item[2 * (b ^ 1)] = n_items;
+        }
+        unsigned* s_cellmask = &s_cellmask3[k3];
+        const int img = wi.y, s = w - img * n_strips;
+        const uint4 ra = __ldg(strip_tab + 2 * s), rb = __ldg(strip_tab + 2 * s + 1);
+        const int level = (int)(ra.x & 0xFFu), ncells = (int)((ra.x >> 8) & 0xFFu), wcell = (int)(ra.x >> 16);
+        const int iniX = (int)(ra.y & 0xFFFFu);
+        const int wint = (int)(ra.z & 0xFFFFu), ih = (int)(ra.z >> 16);
+        const int xoff = (int)(ra.w & 0xFFFFu), yoff = (int)(ra.w >> 16);
+        const uint32_t mg_groups = rb.x, mg_cell = rb.z;
+        const McsLevel& Lv = P.L[level];
+        const int x0 = (iniX & 15) + 3;
+        X.tile = s_ft + b * P.ft_tile_bytes;
+        X.ih = ih;
+        uint32_t* out = cand + (size_t)img * P.cand_stride + Lv.cand_ofs;
+        int* cnt = cand_count + img * P.nlevels + level;
+        // NMS of one pixel (tile coordinates) whose score is sc > 0; a neighbour in another cell of the strip scores 0 for it
+        auto nms_pixel = [&](int ly, int tx, int sc, uint32_t& rec) -> bool {
+            const uint8_t* qp = &s_score[(ly + 1) * TP + tx];
+            const int xi = tx - x0;
+            const int ci = (int)(((uint32_t)xi * mg_cell) >> 20), xc = xi - ci * wcell;
+            int n = max((int)qp[-TP], (int)qp[TP]);
+            if (xc != 0) n = max(n, max(max((int)qp[-TP - 1], (int)qp[-1]), (int)qp[TP - 1]));
+            if (xc != wcell - 1) n = max(n, max(max((int)qp[-TP + 1], (int)qp[1]), (int)qp[TP + 1]));
+            if (sc <= n) return false;
+            fs_red_or_shared(s_cellmask, 1u << ci);
+            rec = mcs_oct::pack_cand(xi + xoff, ly + yoff, sc);  // ROI coordinates: FAST x in the cell's sub-image shifted by j * wCell (:864-865)
+            return true;
+        };
+        auto append = [&](bool surv, uint32_t rec) {
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, surv);
+            if (m) {
+                int p0 = 0;
+                if (lane == 0) p0 = fs_atom_add_global(cnt, __popc(m));
+                p0 = __shfl_sync(0xFFFFFFFFu, p0, 0) + __popc(m & ((1u << lane) - 1u));
+                if (surv && p0 < Lv.cand_cap) out[p0] = rec;
+            }
+        };
+        // strict-'>' 8-neighbour NMS, then the score bytes and the corner count go back to zero for the next scan
+        auto nms_and_clear = [&]() {
+            const int nc = s_ncorner;
+            if (nc <= MCS_FT_CORNERS) {
+                for (int q0 = 0; q0 < nc; q0 += MCS_FS_NT) {
+                    const int q = q0 + threadIdx.x;
+                    bool surv = false;
+                    uint32_t rec = 0;
+                    if (q < nc) {
+                        const int e = X.corner[q];
+                        const int ly = (e >> 8) & 0x7F, tx = e & 0xFF;
+                        surv = nms_pixel(ly, tx, s_score[(ly + 1) * TP + tx], rec);
+                    }
+                    append(surv, rec);
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) s_ncorner = 0;
+                for (int q = threadIdx.x; q < nc; q += MCS_FS_NT) {
+                    const int e = X.corner[q];
+                    s_score[(((e >> 8) & 0x7F) + 1) * TP + (e & 0xFF)] = 0;
+                }
+            } else {  // more corners than the list holds: walk the score tile itself
+                const int npix = ih * wint;
+                for (int p0 = 0; p0 < npix; p0 += MCS_FS_NT) {
+                    const int p = p0 + threadIdx.x;
+                    bool surv = false;
+                    uint32_t rec = 0;
+                    if (p < npix) {
+                        const int ly = p / wint, tx = x0 + p - ly * wint;
+                        const int sc = s_score[(ly + 1) * TP + tx];
+                        if (sc > 0) surv = nms_pixel(ly, tx, sc, rec);
+                    }
+                    append(surv, rec);
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) s_ncorner = 0;
+                for (int t = threadIdx.x; t < score_quads; t += MCS_FS_NT) reinterpret_cast<uint4*>(s_score)[t] = make_uint4(0, 0, 0, 0);
+            }
+        };
+        ft_mbar_wait(ft_smem_u32(&s_bar[b]), (uint32_t)(k >> 1) & 1u);
+        // FAST(cell, iniThFAST) for every cell of the strip
+        fs_scan(X, P.ini_th, x0, x0 + wint, mg_groups, warp);
+        __syncthreads();
+        nms_and_clear();
+        __syncthreads();  // tile buffer b is free, the score tile is zero again
+        const unsigned failed = ~*s_cellmask & ((1u << ncells) - 1u);
+        if (P.min_th < P.ini_th && failed) {  // block-uniform.  Only for the cells that returned nothing: FAST(cell, minThFAST)  (:842-845)
+            for (int c = 0; c < ncells; c++) {
+                if (!(failed & (1u << c))) continue;
+                const int xa = x0 + c * wcell, xb = min(xa + wcell, x0 + wint);
+                const int nG = ((xb - 1) >> 2) - (xa >> 2) + 1;  // <= 19
+                fs_scan(X, P.min_th, xa, xb, c_magic20[nG], warp);
+            }
+            __syncthreads();
+            nms_and_clear();
+            __syncthreads();
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------

@@ -1,6 +1,7 @@
 // mcslam_b200.cu — host engine + C ABI (include/mcslam_b200.h) over the sm_100a kernels in extract_kernels.cuh and
 // match_kernels.cuh.  No CPU fallback: every stage is a kernel launch; creation fails without a CUDA device.
 #include <sched.h>
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -308,6 +309,7 @@ void build_cell_table(const McsPlan& P, std::vector<uint4>& tab) {
 bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
     tab.clear();
     int chm = 7, area = 1;
+    for (int& r : P.ft_box_rows) r = 0;
     auto magic = [](int n, int tmax) -> uint32_t {
         const uint32_t m = ((1u << 20) + n - 1) / n;
         for (int t = 0; t <= tmax; t++)
@@ -345,6 +347,7 @@ bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
                 tab.push_back(make_uint4(m1, m2, m3, 0));
                 chm = std::max(chm, ch);
                 area = std::max(area, wint * ih);
+                P.ft_box_rows[l] = std::max(P.ft_box_rows[l], ch);
             }
         }
     }
@@ -352,7 +355,16 @@ bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
     P.fs_ofs_score = o; o += align_up(MCS_FS_TP * (chm - 6 + 2), 16);
     P.fs_ofs_wq = o; o += (MCS_FS_NT / 32) * MCS_FS_WQ * 2;
     P.fs_ofs_corner = o; o += align_up(area * 2, 16);
+    P.fs_ofs_ctl = o; o += 16;  // mbarrier, corner count, cell mask
     P.fs_smem_bytes = o;
+    // the persistent TMA kernel: [tile 0][tile 1][score][entry stacks][corner list], tiles 128-byte aligned (TMA destination)
+    P.ft_tile_bytes = align_up(MCS_FS_TP * chm, 128);
+    o = 2 * P.ft_tile_bytes;
+    P.ft_ofs_score = o; P.ft_score_bytes = align_up(MCS_FS_TP * (chm - 6 + 2), 16); o += P.ft_score_bytes;
+    P.ft_ofs_wq = o; o += (MCS_FS_NT / 32) * MCS_FS_WQ * 2;
+    P.ft_ofs_corner = o; o += MCS_FT_CORNERS * 2;
+    P.ft_ofs_ctl = o; o += 64;  // two mbarriers, corner count, work items, cell masks
+    P.ft_smem_bytes = o;
     return true;
 }
 
@@ -387,6 +399,16 @@ struct Engine {
     };
     int fs_smem_launch = 0;        // dynamic shared memory of the strip kernel (>= plan.fs_smem_bytes; MCS_FS_BLOCKS pads it)
     int n_fast_strips = 0;
+    // MCS_FAST_TMA: 1 (default) = fast_strips_kernel<true>, the tile arrives by TMA; 0 = fast_strips_kernel<false>, per-thread staging loop;
+    // 2 = fast_strips_tma_kernel, persistent blocks with two tile buffers (measured slower, kept for A/B runs: profiles/README.md)
+    int fast_tma = 1;
+    mcs::FastTmaMaps ft_maps{};     // one 3-D tensor map (x, y, image) per level; level 0 follows the image set of the call
+    const uint8_t* ft_l0_base = nullptr;
+    int ft_l0_pitch = 0;
+    size_t ft_l0_stride = 0;
+    int ft_blocks_per_sm = MCS_FT_MINB;
+    int ft_grid_mult = 1;           // MCS_FT_GRID_MULT: blocks per resident slot (large = one item per block, tuning only)
+    int* d_ft_ctr = nullptr;        // work counters of the persistent kernel, one per first image of a launch
     bool fast_per_cell = false;  // MCS_FAST_CELLS=1: the one-block-per-cell kernel (A/B runs)
     int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
     int oct_nt = MCS_OCT_NT;  // octree block size (MCS_OCT_THREADS overrides)
@@ -417,12 +439,12 @@ struct Engine {
 
     void free_all() {
         cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_strip_tab); cudaFree(d_rs_tab); cudaFree(d_cand); cudaFree(d_sel);
-        cudaFree(d_knode); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
+        cudaFree(d_knode); cudaFree(d_ft_ctr); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
         cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp);
         cudaFreeHost(h_kps); cudaFreeHost(h_desc); cudaFreeHost(h_kp_count); cudaFreeHost(h_mono); cudaFreeHost(h_sel_count);
         cudaFreeHost(h_cand_count);
         d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_strip_tab = nullptr; d_rs_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
-        d_cand_count = d_sel_count = d_kp_count = d_mono = nullptr; d_kps = d_kps_tmp = nullptr; d_desc = d_desc_tmp = nullptr;
+        d_ft_ctr = nullptr; d_cand_count = d_sel_count = d_kp_count = d_mono = nullptr; d_kps = d_kps_tmp = nullptr; d_desc = d_desc_tmp = nullptr;
         h_kps = nullptr; h_desc = nullptr; h_kp_count = h_mono = h_sel_count = h_cand_count = nullptr;
     }
     void release() {
@@ -508,6 +530,7 @@ struct Engine {
             CK(cudaMalloc(&d_knode, n * np.cand_stride * sizeof(uint16_t)));
             CK(cudaMalloc(&d_sel, n * np.sel_stride * sizeof(uint32_t)));
             CK(cudaMalloc(&d_cand_count, n * MCS_PLAN_MAX_LEVELS * sizeof(int)));
+            CK(cudaMalloc(&d_ft_ctr, n * sizeof(int)));
             CK(cudaMalloc(&d_sel_count, n * MCS_PLAN_MAX_LEVELS * sizeof(int)));
             CK(cudaMalloc(&d_kp_count, n * sizeof(int)));
             CK(cudaMalloc(&d_mono, n * sizeof(int)));
@@ -590,9 +613,65 @@ struct Engine {
             const int nb = atoi(e);
             if (nb >= 1 && nb <= 8) fs_smem_launch = std::max(fs_smem_launch, std::min(200 * 1024, (227 * 1024) / nb - 1024 - 64));
         }
-        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        if (const char* e = getenv("MCS_FAST_TMA")) fast_tma = std::min(std::max(atoi(e), 0), 2);
+        if (plan.ft_smem_bytes > 200 * 1024 && fast_tma == 2) fast_tma = 1;
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        if (fast_tma) {
+            CK(cudaFuncSetAttribute(mcs::fast_strips_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.ft_smem_bytes, 1024)));
+            int nb = 0;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, mcs::fast_strips_tma_kernel, MCS_FS_NT, plan.ft_smem_bytes));
+            ft_blocks_per_sm = std::max(nb, 1);
+            if (const char* e = getenv("MCS_FT_BLOCKS")) {
+                const int v = atoi(e);
+                if (v >= 1 && v <= ft_blocks_per_sm) ft_blocks_per_sm = v;
+            }
+            if (const char* e = getenv("MCS_FT_GRID_MULT")) ft_grid_mult = std::max(1, atoi(e));
+            ft_l0_base = nullptr;
+            for (int l = 1; l < plan.nlevels; l++) {
+                if (plan.ft_box_rows[l] < 1) continue;
+                int rc = encode_fast_map(l, d_pyr + plan.L[l].plane_ofs, plan.L[l].pitch, (size_t)plan.pyr_stride);
+                if (rc) return rc;
+            }
+        }
         CK(cudaFuncSetAttribute(mcs::octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
         last_n = 0;
+        return 0;
+    }
+
+    // tensor map of level l for fast_strips_tma_kernel: u8 [max_images][h][w] with the given row pitch and image stride, box 208 x
+    // box_rows x 1, no swizzle, out-of-bounds elements read as zero
+    int encode_fast_map(int l, const uint8_t* base, int pitch, size_t image_stride) {
+        typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                     const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        static EncodeFn enc = nullptr;
+        if (!enc) {
+            void* fp = nullptr;
+            cudaDriverEntryPointQueryResult qr;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess || !fp) {
+                set_err("cuTensorMapEncodeTiled is not available from this driver");
+                return MCS_ERR_CUDA;
+            }
+            enc = (EncodeFn)fp;
+        }
+        if (((uintptr_t)base & 15) || (pitch & 15) || (image_stride & 15)) { set_err("internal: FAST tensor map alignment"); return MCS_ERR_ARG; }
+        const cuuint64_t dims[3] = {(cuuint64_t)plan.L[l].w, (cuuint64_t)plan.L[l].h, (cuuint64_t)max_images};
+        const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)image_stride};
+        const cuuint32_t box[3] = {MCS_FS_TP, (cuuint32_t)plan.ft_box_rows[l], 1};
+        const cuuint32_t es[3] = {1, 1, 1};
+        const CUresult r = enc(&ft_maps.map[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides, box, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { set_err("cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")"); return MCS_ERR_CUDA; }
+        ft_maps.box_rows[l] = plan.ft_box_rows[l];
+        return 0;
+    }
+
+    // level 0 follows the image set of the call (a caller's device buffer, d_input or the re-pitched plane in d_pyr)
+    int encode_level0_map(const mcs::ImageSet& set0) {
+        if (plan.ft_box_rows[0] < 1 || (set0.l0 == ft_l0_base && set0.l0_pitch == ft_l0_pitch && set0.l0_stride == ft_l0_stride)) return 0;
+        int rc = encode_fast_map(0, set0.l0, set0.l0_pitch, set0.l0_stride);
+        if (rc) return rc;
+        ft_l0_base = set0.l0; ft_l0_pitch = set0.l0_pitch; ft_l0_stride = set0.l0_stride;
         return 0;
     }
 
@@ -667,8 +746,23 @@ struct Engine {
         if (fast_per_cell && n_fast_cells > 0) {
             mcs::fast_cells_kernel<<<dim3(n_fast_cells, n), MCS_FAST_NT, P.fast_smem_bytes, st>>>(P, set, d_cell_tab, cand, cand_count);
             launches++;
+        } else if (n_fast_strips > 0 && fast_tma == 2) {
+            int rc = encode_level0_map(set0);
+            if (rc) return rc;
+            const long long items = (long long)n_fast_strips * n;
+            const int grid = (int)std::min<long long>(items, (long long)sm_count_ * ft_blocks_per_sm * ft_grid_mult);
+            CK(cudaMemsetAsync(d_ft_ctr + img0, 0, sizeof(int), st));  // launches in flight together start at different images
+            // tensor maps are encoded on image 0 of the workspace; cand / cand_count are already offset to image img0
+            mcs::fast_strips_tma_kernel<<<grid, MCS_FS_NT, P.ft_smem_bytes, st>>>(P, ft_maps, d_strip_tab, n_fast_strips, (int)items, img0, cand, cand_count,
+                                                                                   d_ft_ctr + img0);
+            launches++;
+        } else if (n_fast_strips > 0 && fast_tma == 1) {
+            int rc = encode_level0_map(set0);
+            if (rc) return rc;
+            mcs::fast_strips_kernel<true><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
+            launches++;
         } else if (n_fast_strips > 0) {
-            mcs::fast_strips_kernel<<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, d_strip_tab, cand, cand_count);
+            mcs::fast_strips_kernel<false><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
             launches++;
         }
         mark(ST_OCTREE);

@@ -54,7 +54,10 @@ struct McsPlan {
     int fast_ofs_score, fast_ofs_flags, fast_ofs_queue, fast_ofs_surv, fast_smem_bytes;
     int fast_maxsurv;   // survivor capacity (records)
     // strip FAST kernel (fast_strips_kernel): score tile, per-warp entry stacks, corner list (bytes)
-    int fs_ofs_score, fs_ofs_wq, fs_ofs_corner, fs_smem_bytes;
+    int fs_ofs_score, fs_ofs_wq, fs_ofs_corner, fs_ofs_ctl, fs_smem_bytes;
+    // persistent TMA strip kernel (fast_strips_tma_kernel): two tile buffers, score tile, per-warp entry stacks, capped corner list
+    int ft_tile_bytes, ft_ofs_score, ft_score_bytes, ft_ofs_wq, ft_ofs_corner, ft_ofs_ctl, ft_smem_bytes;
+    int ft_box_rows[MCS_PLAN_MAX_LEVELS];  // TMA box height per level = tallest strip tile of the level
     int umax[16];       // circular patch row half-widths for IC_Angle (ORBextractor.cpp:452-467)
     McsLevel L[MCS_PLAN_MAX_LEVELS];
 };

@@ -144,6 +144,8 @@ struct KeyPoint {  // field order and defaults of cv::KeyPoint (28 bytes)
     KeyPoint() : pt(0, 0), size(0), angle(-1), response(0), octave(0), class_id(-1) {}
     KeyPoint(float x, float y, float size_, float angle_ = -1, float response_ = 0, int octave_ = 0, int class_id_ = -1)
         : pt(x, y), size(size_), angle(angle_), response(response_), octave(octave_), class_id(class_id_) {}
+    KeyPoint(Point2f pt_, float size_, float angle_ = -1, float response_ = 0, int octave_ = 0, int class_id_ = -1)
+        : pt(pt_), size(size_), angle(angle_), response(response_), octave(octave_), class_id(class_id_) {}
 };
 static_assert(sizeof(KeyPoint) == 28, "KeyPoint layout");
 
@@ -467,6 +469,12 @@ std::ostream& operator<<(std::ostream& o, const Mat& m);
 // cv::invert(DECOMP_LU): closed forms up to 3x3 (as OpenCV), Gauss-Jordan with partial pivoting above; zero matrix if singular.
 MatExpr shim_invert(const Mat& a);
 inline MatExpr Mat::inv() const { return shim_invert(*this); }
+inline double norm(const Mat& a) {  // NORM_L2 over all elements, accumulated in double in element order
+    double s = 0;
+    for (int i = 0; i < a.rows; i++)
+        for (int j = 0; j < a.cols; j++) s += a.getd(i, j) * a.getd(i, j);
+    return std::sqrt(s);
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 struct SVD {

@@ -176,7 +176,7 @@ def test_lapping_area_gpu(golden):
 
 def test_orientation_flag_mode(golden):
     """IC_Angle + steered BRIEF (dead code in the shipped reference, ORBextractor.cpp:475): checked against the oracle's
-    restatement.  Angles within 0.5 degree (fastAtan2 accuracy); descriptor bit mismatches are reported, few allowed."""
+    restatement.  Angles (same fastAtan2 polynomial, same operation order) and descriptor bits are bit-exact."""
     import mcslam_b200 as M
     import oracle_lib as O
     g = golden("single_256x192.npz")
@@ -191,10 +191,10 @@ def test_orientation_flag_mode(golden):
         assert (k[f] == k2[f]).all(), f
     dang = np.abs(k["angle"] - k2["angle"])
     dang = np.minimum(dang, 360 - dang)
-    assert dang.max() <= 0.5, dang.max()
     nbits = int(np.unpackbits(d ^ d2).sum())
     print("orientation mode: max angle diff %.3g deg, mismatched descriptor bits %d of %d" % (dang.max(), nbits, d.size * 8))
-    assert nbits <= 0.001 * d.size * 8
+    assert np.array_equal(k["angle"], k2["angle"]), dang.max()
+    assert nbits == 0
     ex.set_orientation(False)
     mono, k, d = ex(g["image"])
     assert (k == g["kps"]).all() and np.array_equal(d, g["desc"])

@@ -88,6 +88,58 @@ def _build_adaptor(tmp_path):
     return exe
 
 
+CV_API_FLAGS = ["-O2", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "oracle", "ref_shim"),
+                "-I" + os.path.join(ROOT, "tests", "cpp", "stub_eigen")]
+
+
+def _build_cv_api(tmp_path):
+    """tests/cpp/test_cv_api.cpp against the OpenCV stand-in of oracle/ref_shim (test infrastructure) and tests/cpp/stub_eigen."""
+    import __graft_entry__ as G
+    so = G.build()
+    exe = str(tmp_path / "t_cv_api")
+    subprocess.check_call(["g++"] + CV_API_FLAGS + ["-o", exe, os.path.join(ROOT, "tests", "cpp", "test_cv_api.cpp"), so, "-Wl,-rpath," + os.path.dirname(so)])
+    return exe
+
+
+def test_cv_api_compiles_and_fails_loudly_without_gpu(tmp_path):
+    """The cv::/Eigen-typed layer (mc-slam_b200/host/mcslam_cv.hpp, MCS_WITH_OPENCV branch of the adaptor included) compiles warning-free
+    against OpenCV-shaped headers and links; without a CUDA device its constructors throw."""
+    import mcslam_b200 as M
+    exe = _build_cv_api(tmp_path)
+    if M.lib().mcs_device_count() > 0:
+        pytest.skip("a GPU is present")
+    img = tmp_path / "im.bin"
+    img.write_bytes(bytes(16 * 16))
+    (tmp_path / "im.bin.calib").write_bytes(bytes(26 * 8))
+    out = subprocess.run([exe, str(img), "1", "16", "16", str(tmp_path / "o.txt")], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 3 and "no CUDA device" in out.stderr
+
+
+# (include file, reference file, first line, last line, text the first line holds, text the last line holds)
+_CALL_SITES = [
+    ("ref_mcf_extractFeatureSingle_body.inc", "MCSlam/src/MultiCameraFrame.cpp", 231, 261, "", "BoW_vecs[cam_ind] = bowVec;"),
+    ("ref_frontend_descs_from_intramatches.inc", "MCSlam/src/FrontEnd.cpp", 3165, 3183, "Mat descs1 = Mat(lf_prev->intraMatches.size()", "}"),
+    ("ref_frontend_point3d_diff.inc", "MCSlam/src/FrontEnd.cpp", 3224, 3225, "cv::Mat  dif= lf_prev->intraMatches[m[0].queryIdx].point3D", "float distance = cv::norm(dif);"),
+]
+
+
+def test_cv_api_compiles_reference_call_sites(tmp_path):
+    """Front-end lines that USE the frame — extractFeatureSingle's body (ORBextractor::operator() on cv containers, descs.row(j)), the
+    descriptor matrix built from intraMatches[].matchDesc / uv_ref, the point3D difference — are cut from the reference by line range (not
+    copied into the repository) and compiled verbatim against the typed layer."""
+    ref = os.environ.get("MCS_REFERENCE_ROOT", "/root/reference")
+    if not os.path.isfile(os.path.join(ref, "MCSlam", "src", "FrontEnd.cpp")):
+        pytest.skip("reference checkout not present (GPU box)")
+    for inc, rel, a, b, head, tail in _CALL_SITES:
+        with open(os.path.join(ref, rel), encoding="utf-8", errors="replace") as f:
+            lines = f.readlines()
+        chunk = lines[a - 1:b]
+        assert head in "".join(chunk[:2]) and chunk[-1].strip() == tail, (inc, chunk[0], chunk[-1])
+        (tmp_path / inc).write_text("".join(chunk))
+    subprocess.check_call(["g++"] + [f for f in CV_API_FLAGS if f != "-Werror"] + ["-w", "-DMCS_REFERENCE_SNIPPETS", "-I" + str(tmp_path), "-fsyntax-only",
+                                                                                  os.path.join(ROOT, "tests", "cpp", "test_cv_api.cpp")])
+
+
 def test_cpp_adaptor_compiles_and_fails_loudly_without_gpu(tmp_path):
     """The C++17 host adaptor (reference method signatures over the C ABI) builds with g++ alone; with no CUDA device its
     constructors throw — there is no CPU path behind it."""
