@@ -3,15 +3,18 @@
 
 Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0.  For N > 1 it is launched
 under torchrun (one rank per GPU); frames are sharded by rig frame, no collective on the data path (weak scaling: every
-rank processes its own batch of `--frames` rig frames per step).
+rank processes its own batch of `--frames` rig frames per step, generated from its own scene seeds).
 
   value     : rig-frames/s, inputs resident in HBM, results left on the device (mcs_rig_process_device)
-  e2e       : rig-frames/s through the host-buffer C-ABI call (mcs_rig_process): pinned H2D of the images and D2H of
+  e2e       : rig-frames/s through the host-buffer C-ABI call (mcs_rig_process): pinned H2D of the images (and masks) and D2H of
               keypoints / descriptors / IntraMatch rows / landmarks inside the timed region
-  roofline  : dominant stage, algorithmic bytes (DESIGN.md "Algorithmic bytes") / its CUDA-event time, vs MEASURED_PEAKS.json
-  cpu_baseline : oracle/liboracle.so (CPU restatement of the reference path, kind "port") on a bounded sample, rank 0, N = 1
-`--impl reference` times that CPU path alone with all host threads (the reference itself needs OpenCV C++/Eigen/DBoW2 and
-cannot be compiled here).
+  roofline  : dominant stage, algorithmic bytes (DESIGN.md "Algorithmic bytes") / its CUDA-event time, vs MEASURED_PEAKS.json;
+              roofline.issue = warp instructions (profiles/issue.json, from the committed ncu captures) against the SMs' issue rate
+  latency   : N = 1 only: per-call latency of batches of 1 / 8 / 64 rig frames (stream path, CUDA-graph replay, host buffers)
+  cpu_baseline : the reference's own code compiled here (oracle/_ref, kind "reference") when it is present and the rig has <= 5
+              cameras, else the CPU restatement oracle/liboracle.so (kind "port"); bounded sample, rank 0, N = 1
+`--impl reference` times that CPU path alone with all host threads.  `--config 2|3|4|noise` selects the BASELINE.json configuration
+(default 2, the one the metric is quoted on; `noise` = config 2 on uniform-noise images, the FAST / octree worst case).
 """
 import argparse
 import json
@@ -29,6 +32,15 @@ import numpy as np  # noqa: E402
 
 WORKLOAD = "config2: 5-camera 720x540 rig, ORB(1000 features, 8 levels, 1.2, FAST 20/7) extract + 10-pair Hamming intra-match + N-view triangulation"
 W, H, NCAM, NFEAT = 720, 540, 5, 1000
+CONFIGS = {
+    "2": dict(w=720, h=540, ncam=5, nfeat=1000, masks=False, frames=512, distinct=4, noise=False, workload=WORKLOAD),
+    "3": dict(w=720, h=540, ncam=5, nfeat=2000, masks=True, frames=256, distinct=2, noise=False,
+              workload="config3: 5-camera 720x540 rig, 2000 features per camera, semantic masks applied in the triangulation kernel"),
+    "4": dict(w=1920, h=1200, ncam=8, nfeat=4000, masks=False, frames=32, distinct=1, noise=False,
+              workload="config4: 8-camera 1920x1200 rig, 4000 features per camera, 8 levels (28 camera pairs)"),
+    "noise": dict(w=720, h=540, ncam=5, nfeat=1000, masks=False, frames=256, distinct=4, noise=True,
+                  workload="config2 geometry on uniform-noise images (worst case for FAST candidates and the octree)"),
+}
 STAGES = ["upload", "pyramid", "fast", "octree", "blur", "describe", "match", "merge", "triangulate", "download"]
 
 
@@ -110,34 +122,85 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def make_workload(n_frames, distinct, rank):
-    """[n_frames, NCAM, H, W] u8.  `distinct` frames come from the synthetic scene generator (seed = 1234 + frame index,
-    SURVEY.md 8d); the rest of the batch are those frames cyclically shifted by 8k columns (all cameras alike, so the
+def make_workload(n_frames, distinct, rank, cfg=None):
+    """[n_frames, ncam, h, w] u8 (+ f32 masks for config 3).  `distinct` frames come from the synthetic scene generator (seed = 1234 +
+    frame index); the rest of the batch are those frames cyclically shifted by 8k columns (all cameras alike, so the
     cross-camera geometry is kept) — distinct pixel data per frame without minutes of ray casting."""
     import mcslam_b200 as M
-    calib = M.synth.make_rig(NCAM, W, H)
-    base = [M.synth.make_rig_frame(calib, W, H, frame_index=rank * distinct + i) for i in range(distinct)]
-    frames = np.empty((n_frames, NCAM, H, W), np.uint8)
+    cfg = cfg or CONFIGS["2"]
+    w, h, ncam = cfg["w"], cfg["h"], cfg["ncam"]
+    calib = M.synth.make_rig(ncam, w, h)
+    if cfg["noise"]:
+        base = [np.stack([M.synth.noise_image(w, h, 977 * (rank * distinct + i) + c) for c in range(ncam)]) for i in range(distinct)]
+    else:
+        base = [M.synth.make_rig_frame(calib, w, h, frame_index=rank * distinct + i) for i in range(distinct)]
+    frames = np.empty((n_frames, ncam, h, w), np.uint8)
     for f in range(n_frames):
         frames[f] = np.roll(base[f % distinct], 8 * (f // distinct), axis=2)
-    return calib, frames
+    masks = None
+    if cfg["masks"]:
+        mb = [M.synth.make_masks(ncam, w, h, frame_index=rank * distinct + i) for i in range(distinct)]
+        masks = np.empty((n_frames, ncam, h, w), np.float32)
+        for f in range(n_frames):
+            masks[f] = np.roll(mb[f % distinct], 8 * (f // distinct), axis=2)
+    return calib, frames, masks
 
 
-def cpu_sample(calib, frames, seconds, threads_per_frame, pool_threads):
-    """Times the CPU oracle (oracle/liboracle.so: C++ restatement of ORBextractor + BruteForceMatch + merge + DLT) on as many
-    frames of the workload as fit in ~`seconds`.  threads_per_frame = 5 mirrors the reference's thread-per-camera fan-out
-    (MultiCameraFrame.cpp:212-227); pool_threads frames run concurrently."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import oracle_lib as O
+class CpuArm:
+    """The CPU implementation of the path for one configuration: oracle/_ref (the reference's own ORBextractor.cpp and MultiCameraFrame /
+    FrontEnd method bodies compiled here; IntraMatch holds 5 cameras) when present, else the restatement oracle/liboracle.so."""
+
+    def __init__(self, cfg, calib, want=1):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_lib as O
+        self.cfg, self.calib, self.O = cfg, calib, O
+        self.kind = "port"
+        self.R = None
+        try:
+            import ref_lib as R
+            if R.available() and cfg["ncam"] <= 5 and not os.environ.get("MCS_BENCH_CPU_PORT"):
+                self.R, self.kind = R, "reference"
+        except Exception:
+            pass
+        self.workers = [self._make() for _ in range(want)]
+
+    def _make(self):
+        c = self.cfg
+        if self.R is not None:
+            return self.R.Rig(self.calib, c["w"], c["h"], nfeatures=c["nfeat"])
+        return [self.O.Extractor(c["nfeat"]) for _ in range(c["ncam"])]
+
+    def run(self, i, images, do_match=True, do_triangulate=True):
+        """One rig frame on worker i, one thread per camera for the extraction as the reference does (MultiCameraFrame.cpp:212-227)."""
+        wk = self.workers[i]
+        if self.R is not None:
+            return wk.process(images, do_match, do_triangulate)
+        return self.O.process_rig(wk, images, self.calib, threads=self.cfg["ncam"], do_match=do_match, do_triangulate=do_triangulate)
+
+    def stage_ms(self, frames, n=3):
+        """Per-stage time of one rig frame (the reference logs the same three, FrontEnd.cpp:992-1014): extraction alone, then with the
+        intra-match, then with the triangulation; differences of medians."""
+        t = []
+        for flags in ((False, False), (True, False), (True, True)):
+            dt = []
+            for k in range(n):
+                t0 = time.perf_counter()
+                self.run(0, frames[k % len(frames)], *flags)
+                dt.append(time.perf_counter() - t0)
+            t.append(1e3 * float(np.median(dt)))
+        return {"extract": round(t[0], 2), "intra_match": round(t[1] - t[0], 2), "triangulate": round(t[2] - t[1], 2)}
+
+
+def cpu_sample(arm, frames, seconds, pool_threads):
+    """Times the CPU arm on as many frames of the workload as fit in ~`seconds`; pool_threads rig frames run concurrently, each with the
+    reference's thread-per-camera fan-out."""
     from concurrent.futures import ThreadPoolExecutor
-    exs = [[O.Extractor(NFEAT) for _ in range(NCAM)] for _ in range(pool_threads)]
-    O.process_rig(exs[0], frames[0], calib, threads=threads_per_frame)  # warm-up (page-in, allocations)
+    arm.run(0, frames[0])  # warm-up (page-in, allocations)
     done = 0
     t0 = time.perf_counter()
     with ThreadPoolExecutor(pool_threads) as tp:
         while True:
-            list(tp.map(lambda i: O.process_rig(exs[i], frames[(done + i) % len(frames)], calib, threads=threads_per_frame),
-                        range(pool_threads)))
+            list(tp.map(lambda i: arm.run(i, frames[(done + i) % len(frames)]), range(pool_threads)))
             done += pool_threads
             if time.perf_counter() - t0 >= seconds:
                 break
@@ -145,27 +208,29 @@ def cpu_sample(calib, frames, seconds, threads_per_frame, pool_threads):
     return done / dt, done, dt
 
 
-def run_reference(args, rank):
-    """--impl reference: the CPU path on the box's host cores (oracle port; the reference cannot be compiled here)."""
+def run_reference(args, rank, cfg):
+    """--impl reference: the CPU path on the box's host cores — the reference's own compiled code (oracle/_ref) where it exists."""
     if rank != 0:
         return
     ncores = os.cpu_count() or 1
-    pool = max(1, ncores // NCAM)
-    calib, frames = make_workload(max(pool, 2), 2, 0)
+    ncam = cfg["ncam"]
+    pool = max(1, ncores // ncam)
+    calib, frames, _ = make_workload(max(pool, 2), min(2, cfg["distinct"]), 0, cfg)
+    arm = CpuArm(cfg, calib, pool)
     per_step = []
-    for s in range(args.warmup + args.steps):
-        fps, n, dt = cpu_sample(calib, frames, args.cpu_step_seconds, NCAM, pool)
-        if s >= args.warmup:
+    for s_ in range(args.warmup + args.steps):
+        fps, n, dt = cpu_sample(arm, frames, args.cpu_step_seconds, pool)
+        if s_ >= args.warmup:
             per_step.append((fps, n, dt))
     fps = float(np.mean([p[0] for p in per_step]))
-    total, _ = algorithmic_bytes()
     line = {
         "impl": "reference", "metric": "rig-frames/sec (ORB extract+intra-match+triangulate)", "value": fps, "unit": "rig-frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * float(np.mean([p[2] for p in per_step])),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": int(np.mean([p[1] for p in per_step])), "note": "CPU only; bounded sample per step"},
-        "cpu_baseline": {"value": fps, "unit": "rig-frames/s", "cores": min(ncores, pool * NCAM), "kind": "port",
-                         "sample": "%d concurrent rig frames x %d camera threads, ~%.0f s per step" % (pool, NCAM, args.cpu_step_seconds)},
+        "config": {"workload": cfg["workload"], "frames_per_step": int(np.mean([p[1] for p in per_step])), "note": "CPU only; bounded sample per step"},
+        "cpu_baseline": {"value": fps, "unit": "rig-frames/s", "cores": min(ncores, pool * ncam), "kind": arm.kind,
+                         "sample": "%d concurrent rig frames x %d camera threads, ~%.0f s per step" % (pool, ncam, args.cpu_step_seconds),
+                         "stage_ms_one_frame": arm.stage_ms(frames)},
         "e2e": {"value": fps, "unit": "rig-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -179,7 +244,7 @@ def dist_setup(args):
     return rank, world, local
 
 
-def run_gpu(args, rank, world, local):
+def run_gpu(args, rank, world, local, cfg):
     import mcslam_b200 as M
     from mcslam_b200 import binding as B
     if M.lib().mcs_device_count() < 1:
@@ -193,13 +258,23 @@ def run_gpu(args, rank, world, local):
     # one process per GPU: keep this rank's host thread and its pinned staging buffers on the GPU's own NUMA node
     cpus_bound = 0 if os.environ.get("MCS_NO_AFFINITY") else M.lib().mcs_bind_host_thread(local)
     F = args.frames
-    calib, frames = make_workload(F, args.distinct, rank)
-    rig = M.RigFrames(calib, W, H, nfeatures=NFEAT, max_frames=F, device=local)
+    w, h, ncam, nfeat = cfg["w"], cfg["h"], cfg["ncam"], cfg["nfeat"]
+    calib, frames, masks = make_workload(F, args.distinct, rank, cfg)
+    rig = M.RigFrames(calib, w, h, nfeatures=nfeat, max_frames=F, device=local)
     # pinned host staging (the e2e leg copies from here every step) + a resident device copy (the `value` leg)
     pin = B.pinned_empty(frames.shape, np.uint8)
     pin.arr[...] = frames
     d_images = B.device_malloc(local, frames.nbytes)
     B.device_upload(local, d_images, frames)
+    pin_m = pin_u8 = None
+    d_masks = None
+    if masks is not None:
+        pin_m = B.pinned_empty(masks.shape, np.float32)
+        pin_m.arr[...] = masks
+        pin_u8 = B.pinned_empty(masks.shape, np.uint8)
+        pin_u8.arr[...] = np.where(masks.astype(np.float64) < 0.7, 0, 255)
+        d_masks = B.device_malloc(local, masks.nbytes)
+        B.device_upload(local, d_masks, masks)
 
     def barrier():
         rig.synchronize()
@@ -223,8 +298,8 @@ def run_gpu(args, rank, world, local):
         barrier()
         return max_over_ranks(ms)
 
-    dev_step = lambda: rig.process_device(d_images, F)            # noqa: E731
-    host_step = lambda: rig.process(pin.arr)                      # noqa: E731
+    dev_step = lambda: rig.process_device(d_images, F, d_masks)                            # noqa: E731
+    host_step = lambda: rig.process(pin.arr, masks=None if pin_m is None else pin_m.arr)   # noqa: E731
     for _ in range(max(args.warmup, 3)):
         dev_step()
     rig.synchronize()
@@ -235,23 +310,71 @@ def run_gpu(args, rank, world, local):
     for _ in range(max(args.warmup, 3)):
         host_step()
     ms_e2e = timed(host_step, args.steps)
+    ms_e2e_u8 = None
+    if pin_u8 is not None:  # the same call with the mask decision as one byte per pixel (mcs_rig_process_masks_u8)
+        u8_step = lambda: rig.process_masks_u8(pin.arr, pin_u8.arr)                        # noqa: E731
+        for _ in range(max(args.warmup, 3)):
+            u8_step()
+        ms_e2e_u8 = timed(u8_step, args.steps)
     clk = clocks.stop()
     # per-stage device times (CUDA events between the stages on the rig's stream) with profiling on: one unchunked launch
     # sequence over `Fp` frames per step, i.e. exactly what one pipeline chunk launches (and what the ncu captures profile)
-    Fp = min(F, 64)
+    Fp = min(F, 64 if cfg["ncam"] * cfg["w"] * cfg["h"] < 8e6 else 8)
     rig.set_profiling(True)
     acc = dict.fromkeys(STAGES, 0.0)
     for _ in range(args.steps):
-        rig.process_device(d_images, Fp)
+        rig.process_device(d_images, Fp, d_masks)
         for k, v in rig.stage_times().items():
             acc[k] += v
     rig.set_profiling(False)
     stage_ms = {k: v / args.steps for k, v in acc.items()}
+    latency = None
+    if world == 1 and not args.no_latency:
+        latency = latency_sweep(rig, d_images, d_masks, pin, pin_m, F, args.latency_iters)
     host_step()  # leave the results of a full (chunked, host-buffer) step in the handle for the parity block
     kc, n_rows, n_acc = rig.counts(0)
     d2h = rig_d2h_bytes(rig, F)
-    return dict(rig=rig, calib=calib, frames=frames, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches, clocks=clk, stage_ms=stage_ms, cpus_bound=cpus_bound,
-                counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, F=F, Fp=Fp, dist=dist)
+    h2d = frames.nbytes + (masks.nbytes if masks is not None else 0)
+    return dict(rig=rig, calib=calib, frames=frames, masks=masks, ms_dev=ms_dev, ms_e2e=ms_e2e, ms_e2e_u8=ms_e2e_u8, launches=launches, clocks=clk,
+                stage_ms=stage_ms, cpus_bound=cpus_bound, counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, h2d=h2d, F=F, Fp=Fp, dist=dist, latency=latency)
+
+
+def latency_sweep(rig, d_images, d_masks, pin, pin_m, F, iters):
+    """SURVEY.md 8(d) config 5 / FrontEnd::processFrame is called once per rig frame: host-observed latency (call -> results complete on
+    the device, resp. in host memory) of batches of 1, 8 and 64 rig frames.  `device`: mcs_rig_process_device on the streams;
+    `device_graph`: the same call replayed from a CUDA graph (mcs_rig_set_graph); `host`: mcs_rig_process from pinned buffers with the
+    results copied back."""
+    out = {}
+    for b in (1, 8, 64):
+        if b > F:
+            continue
+        n = max(20, iters // (1 if b < 64 else 4))
+        row = {}
+        for name in ("device", "device_graph", "host"):
+            rig.set_graph(name == "device_graph")
+            if name == "host":
+                fn = lambda: rig.process(pin.arr[:b], masks=None if pin_m is None else pin_m.arr[:b])  # noqa: E731
+            else:
+                fn = lambda: (rig.process_device(d_images, b, d_masks), rig.synchronize())              # noqa: E731
+            try:
+                for _ in range(5):
+                    fn()
+            except RuntimeError as e:  # a mode that cannot run is reported, it does not void the line
+                row[name] = {"error": str(e)[:200]}
+                continue
+            t = []
+            for _ in range(n):
+                t0 = time.perf_counter()
+                fn()
+                t.append(1e3 * (time.perf_counter() - t0))
+            t = np.sort(np.array(t))
+            row[name] = {"p50_ms": round(float(np.median(t)), 4), "p99_ms": round(float(t[min(len(t) - 1, int(0.99 * len(t)))]), 4),
+                         "rig_frames_per_s": round(b / (float(np.median(t)) / 1e3), 1)}
+        rig.set_graph(False)
+        out["batch_%d" % b] = row
+    out["iters"] = iters
+    out["clock"] = "host perf_counter around the call + stream synchronize"
+    return out
 
 
 def rig_d2h_bytes(rig, F):
@@ -263,12 +386,12 @@ def rig_d2h_bytes(rig, F):
     return feats + rows + lms
 
 
-def parity_report(rig, calib, frames):
+def parity_report(rig, calib, frames, masks, nfeat):
     """Mismatch counts against the CPU oracle (keypoints, descriptor bits, IntraMatch rows, 3-D points) for rig frames taken from
     the first, a middle and the last pipeline chunk of the last timed step."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_lib as O
-    ex = O.Extractor(NFEAT)
+    ex = O.Extractor(nfeat)
     F = len(frames)
     picks = sorted({0, F // 2 + 1 if F > 2 else 0, F - 1})
     bad_kp = bad_bits = bad_rows = bad_status = 0
@@ -290,7 +413,7 @@ def parity_report(rig, calib, frames):
             bad_rows += abs(len(got) - len(rows)) + 1
             continue
         bad_rows += int((got != rows).any(axis=1).sum())
-        tri = O.triangulate_rows(calib, K, D, rows)
+        tri = O.triangulate_rows(calib, K, D, rows, masks=None if masks is None else masks[f])
         lm = rig.landmarks(f)
         bad_status += int((lm["status"] != tri["status"]).sum())
         ok = tri["nviews"] >= 2
@@ -301,18 +424,48 @@ def parity_report(rig, calib, frames):
             "mismatched_depth_gate": bad_status, "xyz_max_rel_err": max_rel, "xyz_tolerance": 1e-6}
 
 
+def issue_roofline(stage_ms, Fp, amortised_ms_per_seq, clocks, dom):
+    """Instruction-issue roofline: warp instructions per launch sequence of `frames_per_sequence` rig frames, per kernel, from the committed
+    ncu captures (profiles/issue.json, written by tools/issue_table.py from profiles/*_raw.csv: smsp__inst_executed.sum), against
+    SMs x 4 schedulers x SM clock.  The path is integer work on bytes: this, not HBM, is the roofline that binds it."""
+    path = os.path.join(ROOT, "profiles", "issue.json")
+    if not os.path.exists(path):
+        return None
+    t = json.load(open(path))
+    if t.get("frames_per_sequence") != Fp:
+        return None
+    mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or t.get("sm_mhz_fallback", 1965.0)
+    peak = t.get("sms", 148) * 4 * mhz * 1e6  # warp instructions per second
+    total = sum(k["warp_insts"] for k in t["kernels"].values())
+    out = {"unit": "warp-inst/s", "peak": peak, "sm_mhz": mhz, "sms": t.get("sms", 148), "frames_per_sequence": Fp,
+           "warp_insts_per_sequence": total, "per_kernel": {k: v["warp_insts"] for k, v in t["kernels"].items()},
+           "path": {"achieved": total / (amortised_ms_per_seq / 1e3), "frac": total / (amortised_ms_per_seq / 1e3) / peak,
+                    "ms_at_full_issue_rate": 1e3 * total / peak},
+           "source": "profiles/issue.json"}
+    if dom in t["kernels"] and stage_ms.get(dom):
+        wi = t["kernels"][dom]["warp_insts"]
+        out["kernel"] = {"name": dom, "warp_insts": wi, "achieved": wi / (stage_ms[dom] / 1e3), "frac": wi / (stage_ms[dom] / 1e3) / peak}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames", type=int, default=512, help="rig frames per step per GPU (one batched launch sequence)")
-    ap.add_argument("--distinct", type=int, default=4, help="ray-cast scenes per rank; the batch is filled with shifted copies")
+    ap.add_argument("--config", default="2", choices=sorted(CONFIGS), help="BASELINE.json configuration (default 2: the headline metric)")
+    ap.add_argument("--frames", type=int, default=0, help="rig frames per step per GPU (default: 512 for config 2)")
+    ap.add_argument("--distinct", type=int, default=0, help="ray-cast scenes per rank; the batch is filled with shifted copies")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline sample length")
     ap.add_argument("--cpu-step-seconds", type=float, default=6.0, help="--impl reference: seconds of CPU work per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the oracle parity check and the CPU baseline (profiling runs)")
+    ap.add_argument("--no-latency", action="store_true", help="skip the batch 1 / 8 / 64 latency sweep")
+    ap.add_argument("--latency-iters", type=int, default=200)
     args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    args.frames = args.frames or cfg["frames"]
+    args.distinct = args.distinct or cfg["distinct"]
     rank, world, local = dist_setup(args)
     if args.gpus > 1 and world == 1 and "RANK" not in os.environ:
         # launched bare with --gpus N: re-launch under torchrun, one rank per GPU
@@ -320,11 +473,14 @@ def main():
                "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, rank, cfg)
         return
-    r = run_gpu(args, rank, world, local)
+    r = run_gpu(args, rank, world, local, cfg)
     F, steps = r["F"], args.steps
-    total_bytes, stage_bytes = algorithmic_bytes()
+    w, h, ncam, nfeat = cfg["w"], cfg["h"], cfg["ncam"], cfg["nfeat"]
+    total_bytes, stage_bytes = algorithmic_bytes(ncam, w, h, nfeat)
+    if cfg["masks"]:
+        total_bytes += 4 * ncam * nfeat  # one mask lookup per keypoint
     value = world * F * steps / (r["ms_dev"] / 1e3)
     e2e = world * F * steps / (r["ms_e2e"] / 1e3)
     if rank != 0:
@@ -344,19 +500,22 @@ def main():
     # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of the same launch shape
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and args.config == "2":
         t = json.load(open(tpath)).get(dom)
         if t and t.get("frames_per_launch") == Fp:
             traffic = t["dram_bytes_per_launch"]
+    amortised = r["ms_dev"] / steps / (F / Fp)  # device time per Fp rig frames inside the chunked pipeline
+    issue_bound = ("pyramid", "fast", "describe", "match")
     line = {
         "metric": "rig-frames/sec (ORB extract+intra-match+triangulate)", "value": value, "unit": "rig-frames/s", "n_gpus": world,
         "steps": steps, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": F, "distinct_scenes": args.distinct,
+        "config": {"workload": cfg["workload"], "frames_per_step_per_gpu": F, "distinct_scenes": args.distinct,
                    "chunk_frames": int(os.environ.get("MCS_CHUNK_FRAMES", "64")),
-                   "l2": "per-step working set (%.0f MB of images + pyramids per GPU) exceeds the 126 MB L2" % (F * NCAM * (W * H + 1.3e6) / 1e6),
-                   "sharding": "by rig frame, no collective", "host_cpus_bound_to_gpu_numa_node": int(r["cpus_bound"])},
-        "e2e": {"value": e2e, "unit": "rig-frames/s", "h2d_bytes_per_step": int(F * NCAM * W * H), "d2h_bytes_per_step": int(r["d2h"]),
+                   "l2": "per-step working set (%.0f MB of images + pyramids per GPU) exceeds the 126 MB L2" % (F * ncam * (w * h * 2.67) / 1e6),
+                   "sharding": "by rig frame (every rank its own frame stream), no collective",
+                   "host_cpus_bound_to_gpu_numa_node": int(r["cpus_bound"])},
+        "e2e": {"value": e2e, "unit": "rig-frames/s", "h2d_bytes_per_step": int(r["h2d"]), "d2h_bytes_per_step": int(r["d2h"]),
                 "ms_per_step": r["ms_e2e"] / steps},
         "gpu_launches": int(r["launches"]),
         "clocks": r["clocks"],
@@ -367,15 +526,31 @@ def main():
                      "path": {"bytes_per_rig_frame": total_bytes, "achieved": total_bytes * value / world / 1e9,
                               "frac": total_bytes * value / world / 1e9 / peak}},
         "stage_ms_per_launch_sequence": {"frames": Fp, **{k: round(v, 4) for k, v in sm.items()}},
+        # how much of the latency-bound kernels (octree, merge, triangulation) the chunk pipeline hides: the amortised device time per
+        # launch sequence next to the sum of the issue-bound kernels alone
+        "overlap": {"frames": Fp, "amortised_ms": round(amortised, 4), "issue_bound_sum_ms": round(sum(sm[k] for k in issue_bound), 4),
+                    "all_kernels_sum_ms": round(sum(kernels.values()), 4)},
         "counts_frame0": {"keypoints": r["counts"][0], "intramatch_rows": r["counts"][1], "landmarks": r["counts"][2]},
     }
+    if r["ms_e2e_u8"] is not None:
+        line["e2e"]["masks_u8"] = {"value": world * F * steps / (r["ms_e2e_u8"] / 1e3), "ms_per_step": r["ms_e2e_u8"] / steps,
+                                   "h2d_bytes_per_step": int(r["frames"].nbytes + r["masks"].size)}
+    if args.config == "2":
+        iss = issue_roofline(sm, Fp, amortised, r["clocks"], dom)
+        if iss:
+            line["roofline"]["issue"] = iss
+    if r["latency"]:
+        line["latency"] = r["latency"]
     if world == 1 and not args.no_cpu:
-        line["parity"] = parity_report(r["rig"], r["calib"], r["frames"])
+        line["parity"] = parity_report(r["rig"], r["calib"], r["frames"], r["masks"], nfeat)
         ncores = os.cpu_count() or 1
-        fps, n, dt = cpu_sample(r["calib"], r["frames"], args.cpu_seconds, NCAM, 1)
-        line["cpu_baseline"] = {"value": fps, "unit": "rig-frames/s", "cores": min(NCAM, ncores), "kind": "port",
+        arm = CpuArm(cfg, r["calib"], 1)
+        fps, n, dt = cpu_sample(arm, r["frames"], args.cpu_seconds, 1)
+        line["cpu_baseline"] = {"value": fps, "unit": "rig-frames/s", "cores": min(ncam, ncores), "kind": arm.kind,
                                 "sample": "%d rig frames of the workload in %.1f s, reference threading (1 thread per camera)" % (n, dt),
-                                "host_cores": ncores}
+                                "host_cores": ncores, "stage_ms_one_frame": arm.stage_ms(r["frames"])}
+        if r["latency"] and "batch_1" in r["latency"]:
+            line["latency"]["cpu_ms_per_rig_frame"] = round(1e3 / fps, 2)
     print(json.dumps(line), flush=True)
     if r["dist"] is not None:
         r["dist"].destroy_process_group()

@@ -194,6 +194,21 @@ MCS_API int mcs_rig_process(mcs_rig* rig, const uint8_t* images, const float* ma
 /* Same, inputs resident in device memory, nothing copied back (results are read with the getters). */
 MCS_API int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_masks, int n_frames, int old_epipolar);
 
+/* The same two calls with the segmentation decision already taken: masks_u8 holds one byte per pixel, 0 where the reference's
+ * `segMasks[i].at<float>(p.y, p.x) < 0.7` (FrontEnd.cpp:266) is true (static scene, the view is kept) and non-zero where it is false
+ * (dynamic object, the view is dropped).  [n_frames][num_cams][height][width]; a quarter of the f32 masks' PCIe traffic for the same
+ * results.  Not available together with mcs_rig_set_undistort (a decision cannot be interpolated; pass the f32 masks there). */
+MCS_API int mcs_rig_process_masks_u8(mcs_rig* rig, const uint8_t* images, const uint8_t* masks_u8, int n_frames, int old_epipolar);
+MCS_API int mcs_rig_process_device_masks_u8(mcs_rig* rig, const void* d_images, const void* d_masks_u8, int n_frames, int old_epipolar);
+
+/* Latency mode for the per-frame call of FrontEnd::processFrame (FrontEnd.cpp:991-1028).  When enabled, an unchunked
+ * mcs_rig_process_device / mcs_rig_process_device_masks_u8 call (n_frames <= chunk_frames, no RECTIFY) is captured into a CUDA graph the
+ * first time it is seen with a given (image pointer, mask pointer, n_frames, old_epipolar) and replayed with one cudaGraphLaunch
+ * afterwards; results are identical to the stream path.  Up to 16 shapes are cached per handle.  mcs_rig_graph_replays counts the
+ * replays (tests). */
+MCS_API int mcs_rig_set_graph(mcs_rig* rig, int enable);
+MCS_API long long mcs_rig_graph_replays(const mcs_rig* rig);
+
 /* MultiCameraFrame::setData (MultiCameraFrame.cpp:95-152) fused in front of the path: images as the application holds them — CV_32F in
  * [0, 1] (imread / 255, MCDataUtils/src/DatasetReader.cpp:699-711), `channels` = 1 or 3 (interleaved BGR), tightly packed
  * [n_frames][num_cams][height][width][channels] — are multiplied by 255, converted to CV_8U (round half to even, saturate; :109-110)
@@ -220,8 +235,9 @@ MCS_API int mcs_rig_set_undistort_keypoints(mcs_rig* rig, int enable);
 /* image_kps_undist[cam] of frame `frame` (a copy of image_kps while the option above is off).  Returns the keypoint count. */
 MCS_API int mcs_rig_get_keypoints_undist(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, int capacity);
 
-/* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over four
- * CUDA streams (upload, kernels and download of neighbouring chunks overlap).  0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
+/* mcs_rig_process / mcs_rig_process_device cut batches larger than `chunk_frames` rig frames into chunks that rotate over six
+ * CUDA streams (upload, kernels and download of neighbouring chunks overlap; host-buffer calls use chunks of a quarter of that).
+ * 0 = one chunk; default 64 (env MCS_CHUNK_FRAMES). */
 MCS_API int mcs_rig_set_chunk_frames(mcs_rig* rig, int chunk_frames);
 
 /* Compact per-frame summary copied back by mcs_rig_process: n keypoints per camera, M rows, accepted landmarks. */

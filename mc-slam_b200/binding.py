@@ -39,7 +39,8 @@ EXPORTS = [
     "mcs_rig_set_profiling", "mcs_rig_timer_start", "mcs_rig_timer_stop", "mcs_rig_set_chunk_frames", "mcs_device_malloc", "mcs_device_free", "mcs_device_upload", "mcs_device_download", "mcs_host_alloc_pinned",
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
     "mcs_knn2_device", "mcs_knn2_device_static", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
-    "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2", "mcs_plan_fast_tables",
+    "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2", "mcs_plan_fast_tables", "mcs_rig_process_masks_u8",
+    "mcs_rig_process_device_masks_u8", "mcs_rig_set_graph", "mcs_rig_graph_replays",
 ]
 
 
@@ -100,6 +101,11 @@ def lib():
     L.mcs_rig_set_profiling.argtypes = [vp, ci]
     L.mcs_rig_timer_start.argtypes = [vp]
     L.mcs_rig_set_chunk_frames.argtypes = [vp, ci]
+    L.mcs_rig_process_masks_u8.argtypes = [vp, vp, vp, ci, ci]
+    L.mcs_rig_process_device_masks_u8.argtypes = [vp, vp, vp, ci, ci]
+    L.mcs_rig_set_graph.argtypes = [vp, ci]
+    L.mcs_rig_graph_replays.argtypes = [vp]
+    L.mcs_rig_graph_replays.restype = C.c_longlong
     L.mcs_rig_timer_stop.argtypes = [vp, vp]
     L.mcs_rig_download_level.argtypes = [vp, ci, ci, ci, ci, vp, ci]
     L.mcs_rig_level_size.argtypes = [vp, ci, vp, vp]
@@ -411,6 +417,25 @@ class RigFrames:
     def process_device(self, d_images, n_frames, d_masks=None, old=False):
         _check(lib().mcs_rig_process_device(self.hd, C.c_void_p(d_images), C.c_void_p(d_masks) if d_masks else None, n_frames, int(old)),
                "mcs_rig_process_device")
+
+    def process_masks_u8(self, images, masks_u8, old=False):
+        """Host buffers; masks_u8 [n_frames, C, h, w] uint8: 0 = static pixel (the reference's mask < 0.7), non-zero = dynamic."""
+        images = np.ascontiguousarray(images, np.uint8)
+        masks_u8 = np.ascontiguousarray(masks_u8, np.uint8)
+        assert masks_u8.shape == images.shape
+        _check(lib().mcs_rig_process_masks_u8(self.hd, _p(images), _p(masks_u8), images.shape[0], int(old)), "mcs_rig_process_masks_u8")
+
+    def process_device_masks_u8(self, d_images, n_frames, d_masks_u8, old=False):
+        _check(lib().mcs_rig_process_device_masks_u8(self.hd, C.c_void_p(d_images), C.c_void_p(d_masks_u8), n_frames, int(old)),
+               "mcs_rig_process_device_masks_u8")
+
+    def set_graph(self, on):
+        """Latency mode: unchunked device-resident calls are captured into a CUDA graph once and replayed."""
+        _check(lib().mcs_rig_set_graph(self.hd, int(on)), "mcs_rig_set_graph")
+
+    @property
+    def graph_replays(self):
+        return lib().mcs_rig_graph_replays(self.hd)
 
     def counts(self, frame):
         kc = np.zeros(self.C, np.int32)

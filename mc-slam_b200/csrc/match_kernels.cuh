@@ -755,7 +755,7 @@ struct LandmarkOut {
 template <int MAXC>
 __global__ void __launch_bounds__(128) tri_classify_kernel(int num_cams, int kp_cap, int row_cap, int width, int height,
                                                            const int* __restrict__ rows_in, const int* __restrict__ row_count,
-                                                           const KeypointPod* __restrict__ kps, const float* __restrict__ masks,
+                                                           const KeypointPod* __restrict__ kps, const float* __restrict__ masks, int mask_u8,
                                                            LandmarkOut out, int* __restrict__ lists, int* __restrict__ list_count,
                                                            int list_stride) {
     const int frame = blockIdx.y;
@@ -774,7 +774,9 @@ __global__ void __launch_bounds__(128) tri_classify_kernel(int num_cams, int kp_
                 int my = (int)p.y, mx = (int)p.x;  // Mat::at<float>(float, float): truncation
                 my = min(max(my, 0), height - 1);
                 mx = min(max(mx, 0), width - 1);
-                keep = (double)masks[((size_t)(frame * num_cams + c) * height + my) * width + mx] < 0.7;  // :266
+                const size_t at = ((size_t)(frame * num_cams + c) * height + my) * width + mx;
+                // :266 on the f32 mask; the u8 form carries the caller's decision: 0 = static pixel (mask < 0.7), else dynamic
+                keep = mask_u8 ? reinterpret_cast<const uint8_t*>(masks)[at] == 0 : (double)masks[at] < 0.7;
             }
             if (keep) {
                 if (nv == 0) first = c;

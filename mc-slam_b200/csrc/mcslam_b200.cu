@@ -1233,11 +1233,35 @@ struct mcs_rig {
     size_t merge_smem = 0;
     bool merge_rows_smem = false;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
+    // Latency mode (mcs_rig_set_graph): the whole launch sequence of an unchunked device-resident call — memsets, every kernel, the
+    // forks to the side streams and their joins — captured once per (image pointer, mask pointer, frame count, epipolar flag) into a
+    // CUDA graph and replayed with one cudaGraphLaunch.  FrontEnd::processFrame (FrontEnd.cpp:991-1028) runs once per rig frame, so
+    // a serving loop calls with the same buffers every time.
+    struct GraphEntry {
+        const void* d_images = nullptr;
+        const void* d_masks = nullptr;
+        int n_frames = 0, old = 0;
+        cudaGraphExec_t exec = nullptr;
+        long long launches = 0;        // kernels in the graph
+        mcs::ImageSet last_set{};
+        int last_n = 0;
+        bool blur_valid = false;
+    };
+    std::vector<GraphEntry> graphs;
+    bool use_graph = false;
+    long long graph_replays = 0;
+
+    void drop_graphs() {
+        for (GraphEntry& g : graphs)
+            if (g.exec) cudaGraphExecDestroy(g.exec);
+        graphs.clear();
+    }
 
     ~mcs_rig() {
         if (!eng.stream) return;
         cudaSetDevice(eng.device);
         cudaStreamSynchronize(eng.stream);
+        drop_graphs();
         if (t0) { cudaEventDestroy(t0); cudaEventDestroy(t1); }
         for (int k = 0; k < NSLOT; k++) {
             Slot& S = slots[k];
@@ -1460,13 +1484,18 @@ struct mcs_rig {
         o.rows += r * C; o.accepted += r; o.n_views += r; o.xyz += r * 3; o.uv_ref += r * 2; o.rep_cam += r; o.n_accepted += f0;
         return o;
     }
-    int stage_triangulate(int n_frames, const float* d_mask_ptr, int f0 = 0, int k = 0) {
+    // d_mask_ptr: masks of frame 0 of the workspace (f32, or u8 decisions when mask_u8), or null
+    int stage_triangulate(int n_frames, const float* d_mask_ptr, int f0 = 0, int k = 0, bool mask_u8 = false) {
         if (n_frames < 1 || f0 + n_frames > n_matched) { set_err("triangulate before intra-match"); return MCS_ERR_STATE; }
         Slot& S = slots[k];
         const mcs::LandmarkOut out = lm_at(f0);
         const mcs::KeypointPod* kps = eng.d_kps + (size_t)f0 * C * kp_cap;
         const uint8_t* desc = eng.d_desc + (size_t)f0 * C * kp_cap * 32;
-        const float* mask = d_mask_ptr ? d_mask_ptr + (size_t)f0 * C * cfg.width * cfg.height : nullptr;
+        const float* mask = nullptr;
+        if (d_mask_ptr) {
+            const size_t ofs = (size_t)f0 * C * cfg.width * cfg.height;
+            mask = mask_u8 ? reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(d_mask_ptr) + ofs) : d_mask_ptr + ofs;
+        }
         eng.mark(ST_TRIANG);
         cudaStream_t tl = S.st;  // the stream the triangulation kernels run on
         if (use_hi) {
@@ -1478,7 +1507,8 @@ struct mcs_rig {
         CK(cudaMemsetAsync(S.d_tri_counts, 0, (MCS_MAX_CAMS + 2) * sizeof(int), tl));
         dim3 g((row_cap + 127) / 128, n_frames);
         mcs::tri_classify_kernel<MCS_MAX_CAMS><<<g, 128, 0, tl>>>(C, kp_cap, row_cap, cfg.width, cfg.height, d_rows + (size_t)f0 * row_cap * C,
-                                                                    d_row_count + f0, kps, mask, out, S.d_tri_lists, S.d_tri_counts, tri_list_stride);
+                                                                    d_row_count + f0, kps, mask, mask_u8 ? 1 : 0, out, S.d_tri_lists, S.d_tri_counts,
+                                                                    tri_list_stride);
         eng.launches++;
         // 2-view rows on a forked stream, every larger view count in one launch (blockIdx.y = class) on the slot's stream;
         // persistent grid-stride blocks because the list lengths live on the device
@@ -1615,19 +1645,79 @@ struct mcs_rig {
     // upload of one chunk, the kernels of another and the download of a third overlap, and the latency-bound kernels (octree,
     // merge, Jacobi) of one chunk hide behind the throughput-bound ones of its neighbours.  Everything is ordered against the
     // main stream (fork at ev_begin, join at ev_done), so timers and synchronisation on the main stream cover all of it.
+    // Masks: f32 segmentation masks (the reference's segMasks) or, with mask_u8, one byte per pixel holding the caller's decision
+    // (0 = static, keep; non-zero = dynamic, i.e. mask >= 0.7) — a quarter of the PCIe traffic for the same 1-bit answer.  Host masks
+    // are uploaded (and, with RECTIFY, undistorted) chunk by chunk on the chunk's own stream, like the images.
     int process(const uint8_t* h_images, const uint8_t* d_images, const float* h_masks, const float* d_masks_in, int n_frames, int old,
-                bool download, const float* h_f32 = nullptr, const float* d_f32 = nullptr, int channels = 1) {
+                bool download, const float* h_f32 = nullptr, const float* d_f32 = nullptr, int channels = 1, bool mask_u8 = false) {
         const int w = cfg.width, h = cfg.height;
         const size_t f32_frame = (size_t)C * w * h * channels;  // floats per rig frame
+        const size_t mask_frame = (size_t)C * w * h * (mask_u8 ? 1 : sizeof(float));  // mask bytes per rig frame
         const float* dm = d_masks_in;
         int rc;
-        if (h_masks && (rc = upload_masks(h_masks, n_frames, &dm))) return rc;
-        if ((rc = undistort_masks(&dm, n_frames))) return rc;
+        if (mask_u8 && undistort_on && (h_masks || d_masks_in)) { set_err("u8 mask decisions cannot be undistorted: pass f32 masks with RECTIFY"); return MCS_ERR_ARG; }
+        if (h_masks) {  // device staging for the host masks (sized for f32, the larger form)
+            const size_t need = (size_t)F * C * w * h * sizeof(float);
+            if (need > masks_bytes) {
+                CK(cudaStreamSynchronize(eng.stream));
+                cudaFree(d_masks);
+                d_masks = nullptr; masks_bytes = 0;
+                CK(cudaMalloc(&d_masks, need));
+                masks_bytes = need;
+            }
+            dm = d_masks;
+        }
+        if (undistort_on && dm) {
+            const size_t need = (size_t)F * C * w * h * sizeof(float);
+            if (need > masks_und_bytes) {
+                CK(cudaStreamSynchronize(eng.stream));
+                cudaFree(d_masks_und);
+                d_masks_und = nullptr; masks_und_bytes = 0;
+                CK(cudaMalloc(&d_masks_und, need));
+                masks_und_bytes = need;
+            }
+        }
         // host-buffer calls use smaller chunks (chunk_frames / host_chunk_div): more copies in flight hide more of the PCIe time
         const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / host_chunk_div) : chunk_frames;
         const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
         const int step = chunked ? cf : n_frames;
         mcs::ImageSet set{};
+        // latency mode: replay (or capture, the first time) the launch sequence of this exact call
+        const bool graphable = use_graph && d_images && !h_masks && !undistort_on && !chunked && !eng.profiling && !download;
+        GraphEntry* ge = nullptr;
+        long long launches_before = 0;
+        if (graphable) {
+            for (GraphEntry& g : graphs)
+                if (g.d_images == d_images && g.d_masks == dm && g.n_frames == n_frames && g.old == (old | (mask_u8 ? 2 : 0))) ge = &g;
+            if (ge) {
+                CK(cudaGraphLaunch(ge->exec, eng.stream));
+                eng.launches += ge->launches;
+                eng.last_set = ge->last_set; eng.last_n = ge->last_n; eng.blur_valid = ge->blur_valid;
+                n_extracted = n_matched = n_triangulated = n_frames;
+                invalidate();
+                graph_replays++;
+                return 0;
+            }
+            if (graphs.size() >= 16) drop_graphs();  // a caller that keeps changing buffers gets no benefit; bound the cache
+            launches_before = eng.launches;
+            CK(cudaStreamBeginCapture(eng.stream, cudaStreamCaptureModeThreadLocal));
+        }
+        auto end_capture = [&](int rc_in) -> int {  // always leaves capture mode; instantiates and launches on success
+            cudaGraph_t graph = nullptr;
+            const cudaError_t e = cudaStreamEndCapture(eng.stream, &graph);
+            if (rc_in) { if (graph) cudaGraphDestroy(graph); return rc_in; }
+            if (e != cudaSuccess || !graph) { set_err(std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e)); cudaGetLastError(); return MCS_ERR_CUDA; }
+            GraphEntry g;
+            g.d_images = d_images; g.d_masks = dm; g.n_frames = n_frames; g.old = old | (mask_u8 ? 2 : 0);
+            const cudaError_t ei = cudaGraphInstantiate(&g.exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ei != cudaSuccess) { set_err(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ei)); cudaGetLastError(); return MCS_ERR_CUDA; }
+            g.launches = eng.launches - launches_before;
+            g.last_set = eng.last_set; g.last_n = eng.last_n; g.blur_valid = eng.blur_valid;
+            graphs.push_back(g);
+            CK(cudaGraphLaunch(g.exec, eng.stream));
+            return 0;
+        };
         if (chunked) {
             CK(cudaEventRecord(ev_begin, eng.stream));
             for (int k = 1; k < NSLOT; k++) CK(cudaStreamWaitEvent(slots[k].st, ev_begin, 0));
@@ -1659,11 +1749,23 @@ struct mcs_rig {
             else rc = make_set(d_images, nf * C, set, f0 * C, st);
             if (!rc && undistort_on && (h_f32 || d_f32 || h_images))  // staged tight in d_input: undistort from there
                 rc = eng.make_set_undistorted(eng.d_input, nf * C, w, h, d_und_maps, C, set, f0 * C, st);
-            if (rc) return rc;
-            if ((rc = stage_extract(set, nf, f0, k))) return rc;
+            const float* dmk = dm;  // masks of frame 0 as this chunk's triangulation reads them
+            if (!rc && h_masks)
+                CK(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(d_masks) + (size_t)f0 * mask_frame, reinterpret_cast<const uint8_t*>(h_masks) + (size_t)f0 * mask_frame,
+                                   (size_t)nf * mask_frame, cudaMemcpyHostToDevice, st));
+            if (!rc && undistort_on && dm) {  // RECTIFY: the masks go through the same maps (MultiCameraFrame.cpp:131-134)
+                const size_t ofs = (size_t)f0 * C * w * h;
+                dim3 b(32, 8), g((w + 31) / 32, (h + 7) / 8, nf * C);
+                mcs::undistort_f32_kernel<<<g, b, 0, st>>>(dm + ofs, d_masks_und + ofs, d_und_maps, C, w, h);
+                eng.launches++;
+                dmk = d_masks_und;
+            }
+            if (!rc) rc = stage_extract(set, nf, f0, k);
             // computeIntraMatches(matches_map, old): BruteForceMatch(i, j, 75, 0.85, ...) (MultiCameraFrame.cpp:1118)
-            if ((rc = stage_match(nf, old, 75.f, 0.85f, f0, k))) return rc;
-            if ((rc = stage_triangulate(nf, dm, f0, k))) return rc;
+            if (!rc) rc = stage_match(nf, old, 75.f, 0.85f, f0, k);
+            if (!rc) rc = stage_triangulate(nf, dmk, f0, k, mask_u8);
+            if (graphable) return end_capture(rc);  // one unchunked pass; nothing is downloaded in this mode
+            if (rc) return rc;
             if (download) {
                 if ((rc = eng.download_features_async(f0 * C, nf * C, st))) return rc;
                 if ((rc = download_rows_async(f0, nf, st))) return rc;
@@ -1705,6 +1807,8 @@ int mcs_rig_feature_capacity(const mcs_rig* rig) { return rig ? rig->kp_cap : MC
 int mcs_rig_row_capacity(const mcs_rig* rig) { return rig ? rig->row_cap : MCS_ERR_ARG; }
 int mcs_rig_set_orientation(mcs_rig* rig, int enable) {
     if (!rig) return MCS_ERR_ARG;
+    cudaStreamSynchronize(rig->eng.stream);
+    rig->drop_graphs();
     rig->eng.use_angle = enable ? 1 : 0;
     return rig->eng.replan(rig->cfg.width, rig->cfg.height);
 }
@@ -1919,6 +2023,30 @@ int mcs_rig_process_device(mcs_rig* rig, const void* d_images, const void* d_mas
     rig->eng.begin_profile();
     return rig->process(nullptr, (const uint8_t*)d_images, nullptr, (const float*)d_masks, n_frames, old_epipolar ? 1 : 0, false);
 }
+int mcs_rig_process_masks_u8(mcs_rig* rig, const uint8_t* images, const uint8_t* masks_u8, int n_frames, int old_epipolar) {
+    RIG_ENTER(rig);
+    if (!images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    rig->eng.begin_profile();
+    return rig->process(images, nullptr, reinterpret_cast<const float*>(masks_u8), nullptr, n_frames, old_epipolar ? 1 : 0, true, nullptr, nullptr, 1, true);
+}
+int mcs_rig_process_device_masks_u8(mcs_rig* rig, const void* d_images, const void* d_masks_u8, int n_frames, int old_epipolar) {
+    RIG_ENTER(rig);
+    if (!d_images || n_frames < 1) return MCS_ERR_EMPTY;
+    if (n_frames > rig->F) { set_err("n_frames exceeds max_frames"); return MCS_ERR_CAPACITY; }
+    rig->eng.begin_profile();
+    return rig->process(nullptr, (const uint8_t*)d_images, nullptr, (const float*)d_masks_u8, n_frames, old_epipolar ? 1 : 0, false, nullptr, nullptr, 1, true);
+}
+int mcs_rig_set_graph(mcs_rig* rig, int enable) {
+    RIG_ENTER(rig);
+    rig->use_graph = enable != 0;
+    if (!rig->use_graph) {
+        CK(cudaStreamSynchronize(rig->eng.stream));
+        rig->drop_graphs();
+    }
+    return 0;
+}
+long long mcs_rig_graph_replays(const mcs_rig* rig) { return rig ? rig->graph_replays : 0; }
 static int check_f32_args(mcs_rig* rig, const void* images, int channels, int n_frames) {
     if (!images || n_frames < 1) return MCS_ERR_EMPTY;
     if (channels != 1 && channels != 3) { set_err("f32 input: channels must be 1 (gray) or 3 (BGR)"); return MCS_ERR_ARG; }
@@ -1944,10 +2072,14 @@ int mcs_rig_process_device_f32(mcs_rig* rig, const void* d_images, int channels,
 }
 int mcs_rig_set_undistort(mcs_rig* rig, int enable) {
     RIG_ENTER(rig);
+    cudaStreamSynchronize(rig->eng.stream);
+    rig->drop_graphs();
     return rig->set_undistort(enable != 0);
 }
 int mcs_rig_set_undistort_keypoints(mcs_rig* rig, int enable) {
     RIG_ENTER(rig);
+    cudaStreamSynchronize(rig->eng.stream);
+    rig->drop_graphs();
     return rig->set_undistort_keypoints(enable != 0);
 }
 int mcs_rig_get_keypoints_undist(mcs_rig* rig, int frame, int cam, mcs_keypoint* keypoints, int capacity) {

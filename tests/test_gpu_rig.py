@@ -273,6 +273,83 @@ def test_cv_api_equals_oracle(tmp_path):
     assert rel.max() < 1e-3
 
 
+def test_masks_u8_and_graph_latency_mode():
+    """(1) mcs_rig_process_masks_u8 / mcs_rig_process_device_masks_u8: the caller's 1-byte decision (0 = mask < 0.7) gives the rows, mask
+    decisions and points of the f32 masks (FrontEnd.cpp:266).  (2) mcs_rig_set_graph: the CUDA-graph replay of an unchunked
+    device-resident call equals the stream path, frame counts 1 and 3, with and without masks; changing the input pixels between
+    replays changes the results accordingly (the graph holds pointers, not data)."""
+    import mcslam_b200 as M
+    from mcslam_b200 import binding as B
+    calib = M.synth.make_rig(3, 320, 240)
+    frames = np.stack([M.synth.make_rig_frame(calib, 320, 240, frame_index=30 + i, n_rects=5) for i in range(3)])
+    masks = np.stack([M.synth.make_masks(3, 320, 240, frame_index=i) for i in range(3)])
+    masks[0, 0, :8, :8] = 0.7  # exactly 0.7f passes `< 0.7` under the float -> double promotion
+    mu8 = np.where(masks.astype(np.float64) < 0.7, 0, 255).astype(np.uint8)
+    rig = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=3)
+
+    def snapshot(n):
+        out = []
+        for f in range(n):
+            feats = [rig.features(f, c) for c in range(3)]
+            out.append((feats, rig.intra_matches(f), rig.landmarks(f), rig.counts(f)))
+        return out
+
+    def same(a, b):
+        assert len(a) == len(b)
+        for (fa, ra, la, ca), (fb, rb, lb, cb) in zip(a, b):
+            for (ka, da), (kb, db) in zip(fa, fb):
+                assert (ka == kb).all() and np.array_equal(da, db)
+            assert np.array_equal(ra, rb)
+            for k in la:
+                assert np.array_equal(la[k], lb[k]), k
+            assert (ca[0] == cb[0]).all() and ca[1:] == cb[1:]
+
+    rig.process(frames, masks=masks)
+    ref_m = snapshot(3)
+    assert sum(int((r[2]["nviews"] < (r[2]["rows"] >= 0).sum(1)).sum() + (r[1] != r[2]["rows"]).any(1).sum()) for r in ref_m) > 0, "masks must drop views"
+    rig.process_masks_u8(frames, mu8)
+    same(ref_m, snapshot(3))
+    d_img = B.device_malloc(0, frames.nbytes)
+    B.device_upload(0, d_img, frames)
+    d_mu8 = B.device_malloc(0, mu8.nbytes)
+    B.device_upload(0, d_mu8, mu8)
+    rig.process_device_masks_u8(d_img, 3, d_mu8)
+    same(ref_m, snapshot(3))
+    rig.process(frames)
+    ref_plain = snapshot(3)
+    # graph mode
+    rig.set_graph(True)
+    for n, dm, ref in ((3, None, ref_plain), (1, None, ref_plain[:1]), (3, d_mu8, ref_m)):
+        r0 = rig.graph_replays
+        for it in range(3):  # capture, replay, replay
+            if dm is None:
+                rig.process_device(d_img, n)
+            else:
+                rig.process_device_masks_u8(d_img, n, dm)
+            same(ref, snapshot(n))
+        assert rig.graph_replays == r0 + 2
+    # new pixels behind the same pointer: the replay computes the new frames
+    frames2 = np.roll(frames, 16, axis=3)
+    rig.set_graph(False)
+    B.device_upload(0, d_img, frames2)
+    rig.process_device(d_img, 3)
+    ref2 = snapshot(3)
+    assert any(not np.array_equal(a[1], b[1]) for a, b in zip(ref2, ref_plain))
+    rig.set_graph(True)
+    B.device_upload(0, d_img, frames)
+    rig.process_device(d_img, 3)   # capture on the old pixels
+    B.device_upload(0, d_img, frames2)
+    r0 = rig.graph_replays
+    rig.process_device(d_img, 3)   # replay on the new ones
+    assert rig.graph_replays == r0 + 1
+    same(ref2, snapshot(3))
+    rig.set_graph(False)
+    rig.process_device(d_img, 3)
+    same(ref2, snapshot(3))
+    B.device_free(0, d_img)
+    B.device_free(0, d_mu8)
+
+
 def test_chunked_pipeline_equals_single_chunk():
     """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
     -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""
