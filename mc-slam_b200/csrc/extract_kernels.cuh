@@ -775,6 +775,7 @@ __device__ __forceinline__ uint32_t ft_smem_u32(const void* p) { return (uint32_
 // Bounded: a tile that never arrives (a bad tensor map) traps the kernel instead of hanging the device.
 __device__ __forceinline__ void ft_mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
+#pragma unroll 1
     for (int spin = 0; spin < (1 << 22); spin++) {
         asm volatile(
             "{\n"
