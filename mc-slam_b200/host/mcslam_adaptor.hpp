@@ -295,6 +295,106 @@ inline CamArrayConfig read_kalibr_data(const std::string& path, bool radtan = tr
     return cfg;
 }
 
+// FrontEnd::compute_overlap (FrontEnd.cpp:43-198): per camera the 40 x 30 px grid cells whose centre, unprojected at depth dmin = 1 and
+// moved into another camera (T_ji = T_j0 * T_i0^-1), projects inside that camera's image (x in (10, width), y in (10, height)).  Outputs
+// what the reference keeps: overlap_masks[c] = CV_8U image, 50 x (number of other cameras that see the cell) over the cell's pixels
+// (rows / columns beyond the last whole cell stay 0), and non_overlap_fraction[c] = cells of camera c nobody else sees / the same count
+// summed over the cameras (float; the reference divides by zero when every cell is seen).  Calibration-only set-up work that runs once
+// per rig (a few thousand 3 x 4 products), so it is host code; the shipped front-end branch reads the masks only when `tiling` is on
+// (FrontEnd.cpp:493).  The epipolar-line part of the loop and the imshow block compute nothing that is kept.
+struct OverlapInfo {
+    std::vector<std::vector<uint8_t>> overlap_masks;  // [num_cams][height * width]
+    std::vector<float> non_overlap_fraction;          // [num_cams]
+};
+inline OverlapInfo compute_overlap(const std::vector<mcs_calib>& calib, int width, int height) {
+    const int cell_size_x = 40, cell_size_y = 30;
+    const int grid_rows = height / cell_size_y, grid_cols = width / cell_size_x;
+    const int C = (int)calib.size();
+    OverlapInfo out;
+    int total_non_overlap_cells = 0;
+    auto T4 = [](const mcs_calib& c, double T[16]) {
+        for (int r = 0; r < 3; r++) {
+            for (int k = 0; k < 3; k++) T[r * 4 + k] = c.R[r * 3 + k];
+            T[r * 4 + 3] = c.t[r];
+        }
+        T[12] = T[13] = T[14] = 0; T[15] = 1;
+    };
+    auto inv4 = [](const double A[16], double X[16]) {  // Gauss-Jordan with partial pivoting (cv::Mat::inv(), DECOMP_LU)
+        double a[4][8];
+        for (int r = 0; r < 4; r++)
+            for (int k = 0; k < 4; k++) { a[r][k] = A[r * 4 + k]; a[r][4 + k] = r == k ? 1.0 : 0.0; }
+        for (int i = 0; i < 4; i++) {
+            int p = i;
+            for (int r = i + 1; r < 4; r++)
+                if (std::fabs(a[r][i]) > std::fabs(a[p][i])) p = r;
+            if (p != i) for (int k = 0; k < 8; k++) std::swap(a[i][k], a[p][k]);
+            const double d = 1.0 / a[i][i];
+            for (int k = 0; k < 8; k++) a[i][k] *= d;
+            for (int r = 0; r < 4; r++) {
+                if (r == i) continue;
+                const double f = a[r][i];
+                for (int k = 0; k < 8; k++) a[r][k] -= f * a[i][k];
+            }
+        }
+        for (int r = 0; r < 4; r++)
+            for (int k = 0; k < 4; k++) X[r * 4 + k] = a[r][4 + k];
+    };
+    for (int c1 = 0; c1 < C; c1++) {
+        std::vector<double> overlap_grid2((size_t)grid_rows * grid_cols, 0.0);
+        for (int c2 = 0; c2 < C; c2++) {
+            if (c1 == c2) continue;
+            double Ti[16], Tj[16], Tinv[16], Tji[16];
+            T4(calib[c1], Ti);
+            T4(calib[c2], Tj);
+            inv4(Ti, Tinv);
+            for (int r = 0; r < 4; r++)
+                for (int k = 0; k < 4; k++) {
+                    double s = 0;
+                    for (int q = 0; q < 4; q++) s += Tj[r * 4 + q] * Tinv[q * 4 + k];
+                    Tji[r * 4 + k] = s;
+                }
+            const double dmin = 1.0;
+            const double* K1 = calib[c1].K;
+            const double* K2 = calib[c2].K;
+            for (int i = 0; i < grid_cols; i++)
+                for (int j = 0; j < grid_rows; j++) {
+                    const double gx = cell_size_x * i + (cell_size_x / 2.0), gy = cell_size_y * j + (cell_size_y / 2.0);
+                    const double p[4] = {(gx - K1[2]) / K1[0] * dmin, (gy - K1[5]) / K1[4] * dmin, dmin, 1.0};
+                    double q[3], pr[3];
+                    for (int r = 0; r < 3; r++) {
+                        double s = 0;
+                        for (int k = 0; k < 4; k++) s += Tji[r * 4 + k] * p[k];
+                        q[r] = s;
+                    }
+                    for (int r = 0; r < 3; r++) {
+                        double s = 0;
+                        for (int k = 0; k < 3; k++) s += K2[r * 3 + k] * q[k];
+                        pr[r] = s;
+                    }
+                    const double ex = pr[0] / pr[2], ey = pr[1] / pr[2];
+                    if (ex > 10 && ex < width && ey < height && ey > 10) overlap_grid2[(size_t)j * grid_cols + i] += 1;
+                }
+        }
+        int nz = 0;
+        for (double v : overlap_grid2) nz += v != 0;
+        const float no_overlap_cells = (float)(grid_rows * grid_cols - nz);
+        out.non_overlap_fraction.push_back(no_overlap_cells);
+        total_non_overlap_cells += (int)no_overlap_cells;
+        std::vector<uint8_t> mask((size_t)width * height, 0);
+        for (int j = 0; j < grid_rows; j++)
+            for (int i = 0; i < grid_cols; i++) {
+                const double v = overlap_grid2[(size_t)j * grid_cols + i] * 50;  // overlap_grid * 50, convertTo(CV_8U)
+                const uint8_t b = (uint8_t)std::min(255.0, std::max(0.0, std::nearbyint(v)));
+                if (!b) continue;
+                for (int y = cell_size_y * j; y < cell_size_y * (j + 1); y++)
+                    std::memset(&mask[(size_t)y * width + cell_size_x * i], b, cell_size_x);
+            }
+        out.overlap_masks.push_back(std::move(mask));
+    }
+    for (int i = 0; i < C; i++) out.non_overlap_fraction[i] = out.non_overlap_fraction[i] / total_non_overlap_cells;
+    return out;
+}
+
 class BowMatcher;
 struct DMatch;
 

@@ -151,6 +151,17 @@ int main(int argc, char** argv) {
             return 3;
         }
     }
+    if (argc >= 7 && std::string(argv[1]) == "overlap") {  // overlap <calib bin> C w h <out>: FrontEnd::compute_overlap (host, no GPU)
+        const int C = atoi(argv[3]), w = atoi(argv[4]), h = atoi(argv[5]);
+        std::vector<mcs_calib> calib(C);
+        std::ifstream(argv[2], std::ios::binary).read((char*)calib.data(), C * sizeof(mcs_calib));
+        const mcs_b200::OverlapInfo o = mcs_b200::compute_overlap(calib, w, h);
+        FILE* f = fopen(argv[6], "wb");
+        for (int c = 0; c < C; c++) fwrite(o.overlap_masks[c].data(), 1, o.overlap_masks[c].size(), f);
+        fwrite(o.non_overlap_fraction.data(), sizeof(float), C, f);
+        fclose(f);
+        return 0;
+    }
     if (argc < 6) return 2;
     const int C = atoi(argv[2]), w = atoi(argv[3]), h = atoi(argv[4]);
     std::vector<uint8_t> img((size_t)C * w * h);

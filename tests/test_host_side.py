@@ -154,6 +154,49 @@ def test_cpp_adaptor_compiles_and_fails_loudly_without_gpu(tmp_path):
     assert out.returncode == 3 and "no CUDA device" in out.stderr
 
 
+def test_compute_overlap_matches_numpy_restatement(tmp_path):
+    """mcs_b200::compute_overlap (FrontEnd::compute_overlap, FrontEnd.cpp:43-198: per-camera grid-overlap masks and the no-overlap
+    fractions; calibration-only host work) against a numpy restatement of the reference loop on two synthetic rigs."""
+    import mcslam_b200 as M
+    exe = _build_adaptor(tmp_path)
+    for ncam, w, h, spacing, deg in ((5, 720, 540, 0.165, 1.0), (3, 330, 250, 0.9, 8.0)):
+        calib = M.synth.make_rig(ncam, w, h, spacing=spacing, perturb_deg=deg)
+        (tmp_path / "c.bin").write_bytes(np.ascontiguousarray(calib).tobytes())
+        out = subprocess.run([exe, "overlap", str(tmp_path / "c.bin"), str(ncam), str(w), str(h), str(tmp_path / "o.bin")], capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr
+        raw = (tmp_path / "o.bin").read_bytes()
+        masks = np.frombuffer(raw[:ncam * w * h], np.uint8).reshape(ncam, h, w)
+        frac = np.frombuffer(raw[ncam * w * h:], np.float32)
+        rows, cols = h // 30, w // 40
+        want_masks, no_cells = [], []
+        for c1 in range(ncam):
+            grid2 = np.zeros((rows, cols))
+            Ti = np.eye(4); Ti[:3, :3] = calib[c1]["R"].reshape(3, 3); Ti[:3, 3] = calib[c1]["t"]
+            K1 = calib[c1]["K"].reshape(3, 3)
+            for c2 in range(ncam):
+                if c2 == c1:
+                    continue
+                Tj = np.eye(4); Tj[:3, :3] = calib[c2]["R"].reshape(3, 3); Tj[:3, 3] = calib[c2]["t"]
+                Tji = Tj @ np.linalg.inv(Ti)
+                K2 = calib[c2]["K"].reshape(3, 3)
+                for i in range(cols):
+                    for j in range(rows):
+                        gx, gy = 40 * i + 20.0, 30 * j + 15.0
+                        p = np.array([(gx - K1[0, 2]) / K1[0, 0], (gy - K1[1, 2]) / K1[1, 1], 1.0, 1.0])
+                        pr = K2 @ (Tji[:3] @ p)
+                        ex, ey = pr[0] / pr[2], pr[1] / pr[2]
+                        if 10 < ex < w and 10 < ey < h:
+                            grid2[j, i] += 1
+            m = np.zeros((h, w), np.uint8)
+            m[:rows * 30, :cols * 40] = np.kron(np.clip(grid2 * 50, 0, 255).astype(np.uint8), np.ones((30, 40), np.uint8))
+            want_masks.append(m)
+            no_cells.append(np.float32(rows * cols - np.count_nonzero(grid2)))
+        assert np.array_equal(masks, np.stack(want_masks))
+        total = int(sum(int(v) for v in no_cells))
+        assert total > 0 and len(set(masks.ravel())) > 1
+        assert np.array_equal(frac, np.array([v / np.float32(total) for v in no_cells], np.float32))
+
+
 _CAMCHAIN = """%YAML:1.0
 cam0:
   cam_overlaps: [1, 2]
