@@ -122,28 +122,33 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def make_workload(n_frames, distinct, rank, cfg=None):
-    """[n_frames, ncam, h, w] u8 (+ f32 masks for config 3).  `distinct` frames come from the synthetic scene generator (seed = 1234 +
-    frame index); the rest of the batch are those frames cyclically shifted by 8k columns (all cameras alike, so the
-    cross-camera geometry is kept) — distinct pixel data per frame without minutes of ray casting."""
+def make_workload(n_frames, distinct, rank, cfg=None, world=1):
+    """This rank's share of ONE stream of world * n_frames rig frames: [n_frames, ncam, h, w] u8 (+ f32 masks for config 3) and the
+    global frame index of every local frame.  Rig frame g of the stream belongs to rank g mod world (mcslam_b200.sharding).
+    Frame g shows scene g mod (distinct * world) — rendered by the synthetic scene generator, seed = 1234 + scene —
+    cyclically shifted by 8 * (g div (distinct * world)) columns (all cameras alike, so the cross-camera geometry is kept): distinct
+    pixel data per frame without minutes of ray casting; every rank renders `distinct` scenes of its own."""
     import mcslam_b200 as M
+    from mcslam_b200 import sharding as S
     cfg = cfg or CONFIGS["2"]
     w, h, ncam = cfg["w"], cfg["h"], cfg["ncam"]
     calib = M.synth.make_rig(ncam, w, h)
-    if cfg["noise"]:
-        base = [np.stack([M.synth.noise_image(w, h, 977 * (rank * distinct + i) + c) for c in range(ncam)]) for i in range(distinct)]
-    else:
-        base = [M.synth.make_rig_frame(calib, w, h, frame_index=rank * distinct + i) for i in range(distinct)]
+    mine = S.frames_for_rank(world * n_frames, rank, world)
+    period = distinct * world
+    scenes, mscenes = {}, {}
     frames = np.empty((n_frames, ncam, h, w), np.uint8)
-    for f in range(n_frames):
-        frames[f] = np.roll(base[f % distinct], 8 * (f // distinct), axis=2)
-    masks = None
-    if cfg["masks"]:
-        mb = [M.synth.make_masks(ncam, w, h, frame_index=rank * distinct + i) for i in range(distinct)]
-        masks = np.empty((n_frames, ncam, h, w), np.float32)
-        for f in range(n_frames):
-            masks[f] = np.roll(mb[f % distinct], 8 * (f // distinct), axis=2)
-    return calib, frames, masks
+    masks = np.empty((n_frames, ncam, h, w), np.float32) if cfg["masks"] else None
+    for j, g in enumerate(mine):
+        sc = g % period
+        if sc not in scenes:
+            scenes[sc] = (np.stack([M.synth.noise_image(w, h, 977 * sc + c) for c in range(ncam)]) if cfg["noise"]
+                          else M.synth.make_rig_frame(calib, w, h, frame_index=sc))
+            if masks is not None:
+                mscenes[sc] = M.synth.make_masks(ncam, w, h, frame_index=sc)
+        frames[j] = np.roll(scenes[sc], 8 * (g // period), axis=2)
+        if masks is not None:
+            masks[j] = np.roll(mscenes[sc], 8 * (g // period), axis=2)
+    return calib, frames, masks, mine
 
 
 class CpuArm:
@@ -215,7 +220,7 @@ def run_reference(args, rank, cfg):
     ncores = os.cpu_count() or 1
     ncam = cfg["ncam"]
     pool = max(1, ncores // ncam)
-    calib, frames, _ = make_workload(max(pool, 2), min(2, cfg["distinct"]), 0, cfg)
+    calib, frames, _, _ = make_workload(max(pool, 2), min(2, cfg["distinct"]), 0, cfg)
     arm = CpuArm(cfg, calib, pool)
     per_step = []
     for s_ in range(args.warmup + args.steps):
@@ -259,7 +264,7 @@ def run_gpu(args, rank, world, local, cfg):
     cpus_bound = 0 if os.environ.get("MCS_NO_AFFINITY") else M.lib().mcs_bind_host_thread(local)
     F = args.frames
     w, h, ncam, nfeat = cfg["w"], cfg["h"], cfg["ncam"], cfg["nfeat"]
-    calib, frames, masks = make_workload(F, args.distinct, rank, cfg)
+    calib, frames, masks, mine = make_workload(F, args.distinct, rank, cfg, world)
     rig = M.RigFrames(calib, w, h, nfeatures=nfeat, max_frames=F, device=local)
     # pinned host staging (the e2e leg copies from here every step) + a resident device copy (the `value` leg)
     pin = B.pinned_empty(frames.shape, np.uint8)
@@ -333,10 +338,26 @@ def run_gpu(args, rank, world, local, cfg):
         latency = latency_sweep(rig, d_images, d_masks, pin, pin_m, F, args.latency_iters)
     host_step()  # leave the results of a full (chunked, host-buffer) step in the handle for the parity block
     kc, n_rows, n_acc = rig.counts(0)
+    # what a multi-GPU front-end hands on: per-frame counts gathered to rank 0 and ordered by global frame index (the features themselves
+    # stay with the rank that owns the frame); after the timed region
+    gathered = None
+    try:
+        from mcslam_b200 import sharding as S
+        local = {}
+        for j, g in enumerate(mine):
+            c = rig.counts(j)
+            local[g] = (int(c[0].sum()), int(c[1]), int(c[2]))
+        allf = S.gather_by_frame(local, world * F, dist)
+        if allf is not None:
+            gathered = {"frames": len(allf), "keypoints": sum(a[0] for a in allf), "intramatch_rows": sum(a[1] for a in allf),
+                        "landmarks": sum(a[2] for a in allf), "order": "global frame index, frame g from rank g mod n_gpus"}
+    except Exception as e:  # reported, does not void the timing
+        gathered = {"error": str(e)[:200]}
     d2h = rig_d2h_bytes(rig, F)
     h2d = frames.nbytes + (masks.nbytes if masks is not None else 0)
     return dict(rig=rig, calib=calib, frames=frames, masks=masks, ms_dev=ms_dev, ms_e2e=ms_e2e, ms_e2e_u8=ms_e2e_u8, launches=launches, clocks=clk,
-                stage_ms=stage_ms, cpus_bound=cpus_bound, counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, h2d=h2d, F=F, Fp=Fp, dist=dist, latency=latency)
+                stage_ms=stage_ms, cpus_bound=cpus_bound, counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, h2d=h2d, F=F, Fp=Fp, dist=dist, latency=latency,
+                gathered=gathered)
 
 
 def latency_sweep(rig, d_images, d_masks, pin, pin_m, F, iters):
@@ -513,7 +534,7 @@ def main():
         "config": {"workload": cfg["workload"], "frames_per_step_per_gpu": F, "distinct_scenes": args.distinct,
                    "chunk_frames": int(os.environ.get("MCS_CHUNK_FRAMES", "64")),
                    "l2": "per-step working set (%.0f MB of images + pyramids per GPU) exceeds the 126 MB L2" % (F * ncam * (w * h * 2.67) / 1e6),
-                   "sharding": "by rig frame (every rank its own frame stream), no collective",
+                   "sharding": "one stream of n_gpus x frames_per_step_per_gpu rig frames, frame g on rank g mod n_gpus, no collective on the data path",
                    "host_cpus_bound_to_gpu_numa_node": int(r["cpus_bound"])},
         "e2e": {"value": e2e, "unit": "rig-frames/s", "h2d_bytes_per_step": int(r["h2d"]), "d2h_bytes_per_step": int(r["d2h"]),
                 "ms_per_step": r["ms_e2e"] / steps},
@@ -531,6 +552,7 @@ def main():
         "overlap": {"frames": Fp, "amortised_ms": round(amortised, 4), "issue_bound_sum_ms": round(sum(sm[k] for k in issue_bound), 4),
                     "all_kernels_sum_ms": round(sum(kernels.values()), 4)},
         "counts_frame0": {"keypoints": r["counts"][0], "intramatch_rows": r["counts"][1], "landmarks": r["counts"][2]},
+        "gathered_counts": r["gathered"],
     }
     if r["ms_e2e_u8"] is not None:
         line["e2e"]["masks_u8"] = {"value": world * F * steps / (r["ms_e2e_u8"] / 1e3), "ms_per_step": r["ms_e2e_u8"] / steps,

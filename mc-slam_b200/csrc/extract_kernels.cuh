@@ -765,6 +765,108 @@ __device__ __forceinline__ void fs_scan(const FastStripCtx& X, int th, int xa, i
     }
 }
 
+// The 4-pair necessary test on the four pixels of one tile word (bits 2e / 2e + 1 of the result: bright / dark pre-test of pixel e).
+// c, up, dn: the words at rows 0, -3, +3; lf, rt: the pixels at x - 3, x + 3; ul .. dr: the diagonal ring pixels (+-2, +-2).
+__device__ __forceinline__ uint32_t fs_pretest_word(uint32_t c, uint32_t up, uint32_t dn, uint32_t lf, uint32_t rt, uint32_t ul, uint32_t ur, uint32_t dl,
+                                                    uint32_t dr, uint32_t K1) {
+    uint32_t f = 0;
+#pragma unroll
+    for (int hpair = 0; hpair < 2; hpair++) {
+        const uint32_t sel = hpair ? 0x4342u : 0x4140u;
+        const uint32_t c2 = __byte_perm(c, 0, sel), u2 = __byte_perm(up, 0, sel), d2 = __byte_perm(dn, 0, sel);
+        const uint32_t l2 = __byte_perm(lf, 0, sel), r2 = __byte_perm(rt, 0, sel);
+        const uint32_t a2 = __byte_perm(ul, 0, sel), b2 = __byte_perm(dr, 0, sel);
+        const uint32_t e2 = __byte_perm(ur, 0, sel), g2 = __byte_perm(dl, 0, sel);
+        // the four opposite pairs (0,8) (4,12) (2,10) (6,14): a 9-arc holds at least one pixel of each
+        const uint32_t bmin = __vimin3_u16x2(__vminu2(__vmaxu2(u2, d2), __vmaxu2(l2, r2)), __vmaxu2(a2, b2), __vmaxu2(e2, g2));
+        const uint32_t dmax = __vimax3_u16x2(__vmaxu2(__vminu2(u2, d2), __vminu2(l2, r2)), __vminu2(a2, b2), __vminu2(e2, g2));
+        const uint32_t Bf = bmin + K1 - c2, Df = c2 + K1 - dmax;
+        const uint32_t t2 = ((Bf >> 15) & 0x00010001u) | ((Df >> 14) & 0x00020002u);
+        f |= ((t2 | (t2 >> 14)) & 0xFu) << (4 * hpair);
+    }
+    return f;
+}
+
+#define MCS_FS_WQ8 544  // entries per warp stack of fs_scan8: < 32 pending + 32 units x 16
+
+// fs_scan with EIGHT pixels (two adjacent tile words) per thread and step: the two words share 6 of their 22 loads and 2 of their 8
+// funnel shifts, and the index arithmetic, the [xa, xb) mask and the warp scan of the compaction are paid once per 8 pixels.
+// mu = ceil(2^20 / units per row), units per row = ceil(words / 2).
+__device__ __forceinline__ void fs_scan8(const FastStripCtx& X, int th, int xa, int xb, uint32_t mu, int warp) {
+    constexpr int TPW = MCS_FS_TP / 4;
+    const int ga = xa >> 2, nG = ((xb - 1) >> 2) - ga + 1, nU = (nG + 1) >> 1;
+    const int nunits = nU * X.ih;
+    const uint32_t K1 = (uint32_t)(0x8000 - th - 1) * 0x00010001u;  // bit 15 of (a + K1 - b) per lane  <=>  a - b > th
+    int pending = 0;
+    for (int ub = warp * 32; ub < nunits; ub += MCS_FS_NT) {
+        const int ui = ub + X.lane;
+        uint32_t f = 0, ebase = 0;
+        if (ui < nunits) {
+            const int ly = (int)(((uint32_t)ui * mu) >> 20), g = ga + 2 * (ui - ly * nU);
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(X.tile) + (ly + 3) * TPW + g;
+            const uint32_t W1 = row[0], W2 = row[1];
+            const uint32_t A1 = row[-2 * TPW], A2 = row[1 - 2 * TPW], B1 = row[2 * TPW], B2 = row[1 + 2 * TPW];
+            const uint32_t UR1 = __funnelshift_r(A1, A2, 16), DR1 = __funnelshift_r(B1, B2, 16);  // = UL / DL of the second word
+            {
+                const uint32_t W0 = row[-1], A0 = row[-1 - 2 * TPW], B0 = row[-1 + 2 * TPW];
+                f = fs_pretest_word(W1, row[-3 * TPW], row[3 * TPW], __funnelshift_r(W0, W1, 8), __funnelshift_r(W1, W2, 24),
+                                    __funnelshift_r(A0, A1, 16), UR1, __funnelshift_r(B0, B1, 16), DR1, K1);
+            }
+            {
+                const uint32_t W3 = row[2], A3 = row[2 - 2 * TPW], B3 = row[2 + 2 * TPW];
+                f |= fs_pretest_word(W2, row[1 - 3 * TPW], row[1 + 3 * TPW], __funnelshift_r(W1, W2, 8), __funnelshift_r(W2, W3, 24), UR1,
+                                     __funnelshift_r(A2, A3, 16), DR1, __funnelshift_r(B2, B3, 16), K1)
+                     << 8;
+            }
+            // pixel e of the unit is inside [xa, xb)  <=>  lo <= e < hi
+            const int lo = max(xa - 4 * g, 0), hi = min(xb - 4 * g, 8);
+            f &= ((1u << (2 * hi)) - 1u) & ~((1u << (2 * lo)) - 1u);
+            ebase = (uint32_t)((ly << 8) | (4 * g));
+        }
+        const int cnt = __popc(f);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (X.lane >= o) incl += v;
+        }
+        const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (total == 0) continue;  // warp-uniform
+        int pos = pending + incl - cnt;
+        if (f) {
+#pragma unroll
+            for (int e = 0; e < 8; e++) {  // predicated stores; one entry per pixel, bit 15 = dark
+                const uint32_t fb = (f >> (2 * e)) & 3u;
+                if (fb) {
+                    X.wq[pos] = (uint16_t)(((fb & 2u) << 14) | (ebase + e));
+                    pos++;
+                }
+            }
+            const uint32_t both = f & (f >> 1) & 0x5555u;  // rare: both pre-tests passed, the dark entry went in; add the bright one
+            if (both) {
+#pragma unroll
+                for (int e = 0; e < 8; e++)
+                    if (both & (1u << (2 * e))) {
+                        X.wq[pos] = (uint16_t)(ebase + e);
+                        pos++;
+                    }
+            }
+        }
+        pending += total;
+        __syncwarp();
+        while (pending >= 32) {
+            pending -= 32;
+            fs_eval(X, true, X.wq[pending + X.lane], th);
+            __syncwarp();
+        }
+    }
+    if (pending > 0) {
+        const bool act = X.lane < pending;
+        fs_eval(X, act, act ? X.wq[X.lane] : 0, th);
+        __syncwarp();
+    }
+}
+
 #define MCS_FT_CORNERS 2048
 struct FastTmaMaps {
     CUtensorMap map[MCS_PLAN_MAX_LEVELS];
@@ -798,7 +900,8 @@ __device__ __forceinline__ void ft_mbar_wait(uint32_t bar, uint32_t parity) {
 // of the level's (x, y, image) tensor map; rows of the box below the image arrive as zeros) instead of the per-thread LDG.128 + STS.128
 // loop with its index division; the score tile is cleared while the tile is in flight.  img0 = image index of blockIdx.y = 0 in the
 // tensor maps (which are encoded on image 0 of the workspace).
-template <bool TMA>
+// PX8: the pre-test handles eight pixels per thread and step (fs_scan8) instead of four.
+template <bool TMA, bool PX8>
 __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                     const __grid_constant__ FastTmaMaps M, int img0,
                                                                     const uint4* __restrict__ strip_tab, uint32_t* __restrict__ cand,
@@ -817,7 +920,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
     const int iniX = (int)(ra.y & 0xFFFFu), iniY = (int)(ra.y >> 16);
     const int wint = (int)(ra.z & 0xFFFFu), ih = (int)(ra.z >> 16);  // computed interior of the strip
     const int xoff = (int)(ra.w & 0xFFFFu), yoff = (int)(ra.w >> 16);
-    const uint32_t mg_groups = rb.x, mg_quads = rb.y, mg_cell = rb.z;
+    const uint32_t mg_groups = PX8 ? rb.w : rb.x, mg_quads = rb.y, mg_cell = rb.z;
     const McsLevel& Lv = P.L[level];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ox = iniX & ~15;         // image x of tile byte 0
@@ -828,7 +931,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
     FastStripCtx X;
     X.tile = s_tile;
     X.score = s_score;
-    X.wq = reinterpret_cast<uint16_t*>(s_fs + P.fs_ofs_wq) + warp * MCS_FS_WQ;
+    X.wq = reinterpret_cast<uint16_t*>(s_fs + P.fs_ofs_wq) + warp * (PX8 ? MCS_FS_WQ8 : MCS_FS_WQ);
     X.corner = reinterpret_cast<uint16_t*>(s_fs + P.fs_ofs_corner);
     X.ncorner = &s_ncorner;
     X.ih = ih;
@@ -902,7 +1005,8 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
         }
     };
     // FAST(cell, iniThFAST) for every cell of the strip
-    fs_scan(X, P.ini_th, x0, x0 + wint, mg_groups, warp);
+    if constexpr (PX8) fs_scan8(X, P.ini_th, x0, x0 + wint, mg_groups, warp);
+    else fs_scan(X, P.ini_th, x0, x0 + wint, mg_groups, warp);
     __syncthreads();
     nms();
     if (P.min_th >= P.ini_th) return;  // the retry could only find a subset of nothing
@@ -916,7 +1020,8 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
         if (!(failed & (1u << c))) continue;
         const int xa = x0 + c * wcell, xb = min(xa + wcell, x0 + wint);
         const int nG = ((xb - 1) >> 2) - (xa >> 2) + 1;  // <= 19
-        fs_scan(X, P.min_th, xa, xb, c_magic20[nG], warp);
+        if constexpr (PX8) fs_scan8(X, P.min_th, xa, xb, c_magic20[(nG + 1) >> 1], warp);
+        else fs_scan(X, P.min_th, xa, xb, c_magic20[nG], warp);
     }
     __syncthreads();
     nms();

@@ -339,12 +339,13 @@ bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
                 if (wint < 1 || wint > MCS_FS_MAXW || j1 - j0 > 8) { set_err("internal: FAST strip geometry"); return false; }
                 const int x0 = (iniX & 15) + 3;
                 const int nG = ((x0 + wint - 1) >> 2) - (x0 >> 2) + 1, nq = (x0 + wint + 3 + 15) >> 4;
-                const uint32_t m1 = magic(nG, nG * ih), m2 = magic(nq, nq * ch), m3 = magic(L.w_cell, 255);
-                if (!m1 || !m2 || !m3) { set_err("internal: FAST strip index division"); return false; }
+                const int nU = (nG + 1) >> 1;  // pre-test units of two words (fs_scan8)
+                const uint32_t m1 = magic(nG, nG * ih), m2 = magic(nq, nq * ch), m3 = magic(L.w_cell, 255), m4 = magic(nU, nU * ih);
+                if (!m1 || !m2 || !m3 || !m4) { set_err("internal: FAST strip index division"); return false; }
                 tab.push_back(make_uint4((unsigned)l | ((unsigned)(j1 - j0) << 8) | ((unsigned)L.w_cell << 16), (unsigned)iniX | ((unsigned)iniY << 16),
                                          (unsigned)wint | ((unsigned)ih << 16),
                                          (unsigned)(3 + j0 * L.w_cell) | ((unsigned)(3 + i * L.h_cell) << 16)));
-                tab.push_back(make_uint4(m1, m2, m3, 0));
+                tab.push_back(make_uint4(m1, m2, m3, m4));
                 chm = std::max(chm, ch);
                 area = std::max(area, wint * ih);
                 P.ft_box_rows[l] = std::max(P.ft_box_rows[l], ch);
@@ -353,7 +354,7 @@ bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
     }
     int o = align_up(MCS_FS_TP * chm + 16, 16);
     P.fs_ofs_score = o; o += align_up(MCS_FS_TP * (chm - 6 + 2), 16);
-    P.fs_ofs_wq = o; o += (MCS_FS_NT / 32) * MCS_FS_WQ * 2;
+    P.fs_ofs_wq = o; o += (MCS_FS_NT / 32) * MCS_FS_WQ8 * 2;
     P.fs_ofs_corner = o; o += align_up(area * 2, 16);
     P.fs_ofs_ctl = o; o += 16;  // mbarrier, corner count, cell mask
     P.fs_smem_bytes = o;
@@ -402,6 +403,7 @@ struct Engine {
     // MCS_FAST_TMA: 1 (default) = fast_strips_kernel<true>, the tile arrives by TMA; 0 = fast_strips_kernel<false>, per-thread staging loop;
     // 2 = fast_strips_tma_kernel, persistent blocks with two tile buffers (measured slower, kept for A/B runs: profiles/README.md)
     int fast_tma = 1;
+    bool fast_px8 = true;           // MCS_FAST_PX8=0: four pixels per thread in the pre-test (fs_scan) instead of eight (fs_scan8)
     mcs::FastTmaMaps ft_maps{};     // one 3-D tensor map (x, y, image) per level; level 0 follows the image set of the call
     const uint8_t* ft_l0_base = nullptr;
     int ft_l0_pitch = 0;
@@ -613,10 +615,12 @@ struct Engine {
             const int nb = atoi(e);
             if (nb >= 1 && nb <= 8) fs_smem_launch = std::max(fs_smem_launch, std::min(200 * 1024, (227 * 1024) / nb - 1024 - 64));
         }
-        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
         if (const char* e = getenv("MCS_FAST_TMA")) fast_tma = std::min(std::max(atoi(e), 0), 2);
         if (plan.ft_smem_bytes > 200 * 1024 && fast_tma == 2) fast_tma = 1;
-        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        CK(cudaFuncSetAttribute(mcs::fast_strips_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(fs_smem_launch, 1024)));
+        if (const char* e = getenv("MCS_FAST_PX8")) fast_px8 = atoi(e) != 0;
         if (fast_tma) {
             CK(cudaFuncSetAttribute(mcs::fast_strips_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.ft_smem_bytes, 1024)));
             int nb = 0;
@@ -759,10 +763,11 @@ struct Engine {
         } else if (n_fast_strips > 0 && fast_tma == 1) {
             int rc = encode_level0_map(set0);
             if (rc) return rc;
-            mcs::fast_strips_kernel<true><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
+            if (fast_px8) mcs::fast_strips_kernel<true, true><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
+            else mcs::fast_strips_kernel<true, false><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
             launches++;
         } else if (n_fast_strips > 0) {
-            mcs::fast_strips_kernel<false><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
+            mcs::fast_strips_kernel<false, false><<<dim3(n_fast_strips, n), MCS_FS_NT, fs_smem_launch, st>>>(P, set, ft_maps, img0, d_strip_tab, cand, cand_count);
             launches++;
         }
         mark(ST_OCTREE);

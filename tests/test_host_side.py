@@ -334,6 +334,9 @@ def test_fast_strips_cover_the_cell_grid_exactly(w, h):
             assert (t * int(s[5])) >> 20 == t // nq
         for t in range(wint):
             assert (t * int(s[6])) >> 20 == t // wcell
+        nu = (ng + 1) >> 1  # units of two words (fs_scan8)
+        for t in range(nu * ih):
+            assert (t * int(s[7])) >> 20 == t // nu
     assert len(covered) == len(cells)
     for c in cells:
         key = (int(c[0]), int(c[1] & 0xFFFF), int(c[1] >> 16))
@@ -355,6 +358,24 @@ def test_algorithmic_bytes_model_matches_survey_8d():
     assert total == 13185090 and stages["match"] == 720000 and stages["triangulate"] == 132000
     assert bench.algorithmic_bytes(5, 720, 540, 2000)[0] + 4 * 5 * 2000 == 14245090
     assert bench.algorithmic_bytes(8, 1920, 1200, 4000)[0] == 124259632
+
+
+def test_issue_table_is_regenerated_from_the_committed_launch_list():
+    """profiles/issue.json (bench.py's roofline.issue numerators) is exactly what tools/issue_table.py makes of the committed ncu launch
+    list it names; the table covers every stage of the path and its total is the 2.5 G warp instructions per 64 rig frames DESIGN.md quotes."""
+    import importlib.util
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("issue_table", os.path.join(root, "tools", "issue_table.py"))
+    it = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(it)
+    have = json.load(open(os.path.join(root, "profiles", "issue.json")))
+    made = it.build(os.path.join(root, have["source"]))
+    assert made == have
+    assert set(have["kernels"]) == {"pyramid", "fast", "octree", "describe", "match", "merge", "triangulate"}
+    assert have["frames_per_sequence"] == 64 and have["kernels"]["pyramid"]["launches_per_sequence"] == 7
+    total = sum(k["warp_insts"] for k in have["kernels"].values())
+    assert 2.0e9 < total < 3.0e9
 
 
 def test_bench_reference_arm_contract():
