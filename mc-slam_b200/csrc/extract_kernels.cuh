@@ -791,10 +791,14 @@ __device__ __forceinline__ uint32_t fs_pretest_word(uint32_t c, uint32_t up, uin
 
 // fs_scan with EIGHT pixels (two adjacent tile words) per thread and step: the two words share 6 of their 22 loads and 2 of their 8
 // funnel shifts, and the index arithmetic, the [xa, xb) mask and the warp scan of the compaction are paid once per 8 pixels.
-// mu = ceil(2^20 / units per row), units per row = ceil(words / 2).
+// Units start at an even word, so the five word pairs of a unit are 64-bit loads (a warp's 32 units read 64 consecutive words in two
+// wavefronts, as 32-bit loads of stride 2 they would conflict two-way).  mu = ceil(2^20 / units per row); units per row =
+// ceil(words from the even word at or before xa to the word of xb - 1, / 2) — fs_units_per_row, also used by the host for the strip record.
+__host__ __device__ __forceinline__ int fs_units_per_row(int xa, int xb) { return ((((xb - 1) >> 2) - ((xa >> 2) & ~1) + 1) + 1) >> 1; }
+
 __device__ __forceinline__ void fs_scan8(const FastStripCtx& X, int th, int xa, int xb, uint32_t mu, int warp) {
     constexpr int TPW = MCS_FS_TP / 4;
-    const int ga = xa >> 2, nG = ((xb - 1) >> 2) - ga + 1, nU = (nG + 1) >> 1;
+    const int ga = (xa >> 2) & ~1, nU = fs_units_per_row(xa, xb);
     const int nunits = nU * X.ih;
     const uint32_t K1 = (uint32_t)(0x8000 - th - 1) * 0x00010001u;  // bit 15 of (a + K1 - b) per lane  <=>  a - b > th
     int pending = 0;
@@ -803,19 +807,20 @@ __device__ __forceinline__ void fs_scan8(const FastStripCtx& X, int th, int xa, 
         uint32_t f = 0, ebase = 0;
         if (ui < nunits) {
             const int ly = (int)(((uint32_t)ui * mu) >> 20), g = ga + 2 * (ui - ly * nU);
-            const uint32_t* row = reinterpret_cast<const uint32_t*>(X.tile) + (ly + 3) * TPW + g;
-            const uint32_t W1 = row[0], W2 = row[1];
-            const uint32_t A1 = row[-2 * TPW], A2 = row[1 - 2 * TPW], B1 = row[2 * TPW], B2 = row[1 + 2 * TPW];
-            const uint32_t UR1 = __funnelshift_r(A1, A2, 16), DR1 = __funnelshift_r(B1, B2, 16);  // = UL / DL of the second word
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(X.tile) + (ly + 3) * TPW + g;  // 8-byte aligned: TPW and g are even
+            const uint2 W = *reinterpret_cast<const uint2*>(row), A = *reinterpret_cast<const uint2*>(row - 2 * TPW),
+                        B = *reinterpret_cast<const uint2*>(row + 2 * TPW), U = *reinterpret_cast<const uint2*>(row - 3 * TPW),
+                        D = *reinterpret_cast<const uint2*>(row + 3 * TPW);
+            const uint32_t UR1 = __funnelshift_r(A.x, A.y, 16), DR1 = __funnelshift_r(B.x, B.y, 16);  // = UL / DL of the second word
             {
                 const uint32_t W0 = row[-1], A0 = row[-1 - 2 * TPW], B0 = row[-1 + 2 * TPW];
-                f = fs_pretest_word(W1, row[-3 * TPW], row[3 * TPW], __funnelshift_r(W0, W1, 8), __funnelshift_r(W1, W2, 24),
-                                    __funnelshift_r(A0, A1, 16), UR1, __funnelshift_r(B0, B1, 16), DR1, K1);
+                f = fs_pretest_word(W.x, U.x, D.x, __funnelshift_r(W0, W.x, 8), __funnelshift_r(W.x, W.y, 24), __funnelshift_r(A0, A.x, 16), UR1,
+                                    __funnelshift_r(B0, B.x, 16), DR1, K1);
             }
             {
                 const uint32_t W3 = row[2], A3 = row[2 - 2 * TPW], B3 = row[2 + 2 * TPW];
-                f |= fs_pretest_word(W2, row[1 - 3 * TPW], row[1 + 3 * TPW], __funnelshift_r(W1, W2, 8), __funnelshift_r(W2, W3, 24), UR1,
-                                     __funnelshift_r(A2, A3, 16), DR1, __funnelshift_r(B2, B3, 16), K1)
+                f |= fs_pretest_word(W.y, U.y, D.y, __funnelshift_r(W.x, W.y, 8), __funnelshift_r(W.y, W3, 24), UR1, __funnelshift_r(A.y, A3, 16), DR1,
+                                     __funnelshift_r(B.y, B3, 16), K1)
                      << 8;
             }
             // pixel e of the unit is inside [xa, xb)  <=>  lo <= e < hi
@@ -1020,7 +1025,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
         if (!(failed & (1u << c))) continue;
         const int xa = x0 + c * wcell, xb = min(xa + wcell, x0 + wint);
         const int nG = ((xb - 1) >> 2) - (xa >> 2) + 1;  // <= 19
-        if constexpr (PX8) fs_scan8(X, P.min_th, xa, xb, c_magic20[(nG + 1) >> 1], warp);
+        if constexpr (PX8) fs_scan8(X, P.min_th, xa, xb, c_magic20[fs_units_per_row(xa, xb)], warp);
         else fs_scan(X, P.min_th, xa, xb, c_magic20[nG], warp);
     }
     __syncthreads();

@@ -339,7 +339,7 @@ bool build_strip_table(McsPlan& P, std::vector<uint4>& tab) {
                 if (wint < 1 || wint > MCS_FS_MAXW || j1 - j0 > 8) { set_err("internal: FAST strip geometry"); return false; }
                 const int x0 = (iniX & 15) + 3;
                 const int nG = ((x0 + wint - 1) >> 2) - (x0 >> 2) + 1, nq = (x0 + wint + 3 + 15) >> 4;
-                const int nU = (nG + 1) >> 1;  // pre-test units of two words (fs_scan8)
+                const int nU = mcs::fs_units_per_row(x0, x0 + wint);  // pre-test units of two words from an even word (fs_scan8)
                 const uint32_t m1 = magic(nG, nG * ih), m2 = magic(nq, nq * ch), m3 = magic(L.w_cell, 255), m4 = magic(nU, nU * ih);
                 if (!m1 || !m2 || !m3 || !m4) { set_err("internal: FAST strip index division"); return false; }
                 tab.push_back(make_uint4((unsigned)l | ((unsigned)(j1 - j0) << 8) | ((unsigned)L.w_cell << 16), (unsigned)iniX | ((unsigned)iniY << 16),

@@ -334,7 +334,7 @@ def test_fast_strips_cover_the_cell_grid_exactly(w, h):
             assert (t * int(s[5])) >> 20 == t // nq
         for t in range(wint):
             assert (t * int(s[6])) >> 20 == t // wcell
-        nu = (ng + 1) >> 1  # units of two words (fs_scan8)
+        nu = ((((x0 + wint - 1) >> 2) - ((x0 >> 2) & ~1) + 1) + 1) >> 1  # units of two words from an even word (fs_scan8)
         for t in range(nu * ih):
             assert (t * int(s[7])) >> 20 == t // nu
     assert len(covered) == len(cells)
