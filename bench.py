@@ -196,6 +196,59 @@ class CpuArm:
         return {"extract": round(t[0], 2), "intra_match": round(t[1] - t[0], 2), "triangulate": round(t[2] - t[1], 2)}
 
 
+def cv2_primitives_ms(frames, nfeat, n=2):
+    """Sanity figure SURVEY.md 8(d) asks for where cv2 exists: the OpenCV primitives the reference's extractor and matcher spend their
+    time in, called through cv2 on the bench's own images with the reference's call shapes — per camera 7 x resize + copyMakeBorder,
+    FAST(20) per 35 px cell with the minTh retry on empty cells, 8 x GaussianBlur(7x7, 2); per rig frame BFMatcher(HAMMING).knnMatch(k=2)
+    for every camera pair on random descriptors of the configured count.  No octree, no descriptor sampling, no merge, no SVD: a lower
+    bound of an OpenCV-backed reference, not a replacement for the timed arm.  OpenCV's own threads.  None when cv2 is absent."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    ncam = frames.shape[1]
+    fast_i = cv2.FastFeatureDetector_create(20, True)
+    fast_m = cv2.FastFeatureDetector_create(7, True)
+    rng = np.random.default_rng(0)
+    descs = [rng.integers(0, 256, (nfeat, 32), dtype=np.uint8) for _ in range(ncam)]
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING)
+    t_ext, t_match = [], []
+    for k in range(n):
+        t0 = time.perf_counter()
+        for c in range(ncam):
+            img = frames[k % len(frames), c]
+            level = img
+            for l, (lw, lh) in enumerate(level_sizes(img.shape[1], img.shape[0])):
+                if l:
+                    level = cv2.resize(level, (lw, lh), interpolation=cv2.INTER_LINEAR)
+                cv2.copyMakeBorder(level, 19, 19, 19, 19, cv2.BORDER_REFLECT_101)
+                W = 35
+                wd, ht = lw - 32, lh - 32
+                ncol, nrow = max(wd // W, 1), max(ht // W, 1)
+                wc, hc = -(-wd // ncol), -(-ht // nrow)
+                for i in range(nrow):
+                    y0 = 16 + i * hc
+                    if y0 >= lh - 16 - 3:
+                        continue
+                    y1 = min(y0 + hc + 6, lh - 16)
+                    for j in range(ncol):
+                        x0 = 16 + j * wc
+                        if x0 >= lw - 16 - 6:
+                            continue
+                        cell = level[y0:y1, x0:min(x0 + wc + 6, lw - 16)]
+                        if not fast_i.detect(cell):
+                            fast_m.detect(cell)
+                cv2.GaussianBlur(level, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        t1 = time.perf_counter()
+        for i in range(ncam - 1):
+            for j in range(i + 1, ncam):
+                bf.knnMatch(descs[i], descs[j], k=2)
+        t2 = time.perf_counter()
+        t_ext.append(1e3 * (t1 - t0)); t_match.append(1e3 * (t2 - t1))
+    return {"extract_primitives_ms": round(float(np.median(t_ext)), 2), "knn_match_ms": round(float(np.median(t_match)), 2),
+            "cv2": cv2.__version__, "cv2_threads": int(cv2.getNumThreads()), "note": "primitives only, sequential over the cameras; a lower bound"}
+
+
 def cpu_sample(arm, frames, seconds, pool_threads):
     """Times the CPU arm on as many frames of the workload as fit in ~`seconds`; pool_threads rig frames run concurrently, each with the
     reference's thread-per-camera fan-out."""
@@ -570,7 +623,8 @@ def main():
         fps, n, dt = cpu_sample(arm, r["frames"], args.cpu_seconds, 1)
         line["cpu_baseline"] = {"value": fps, "unit": "rig-frames/s", "cores": min(ncam, ncores), "kind": arm.kind,
                                 "sample": "%d rig frames of the workload in %.1f s, reference threading (1 thread per camera)" % (n, dt),
-                                "host_cores": ncores, "stage_ms_one_frame": arm.stage_ms(r["frames"])}
+                                "host_cores": ncores, "stage_ms_one_frame": arm.stage_ms(r["frames"]),
+                                "cv2_primitives_one_frame": cv2_primitives_ms(r["frames"], nfeat)}
         if r["latency"] and "batch_1" in r["latency"]:
             line["latency"]["cpu_ms_per_rig_frame"] = round(1e3 / fps, 2)
     print(json.dumps(line), flush=True)
