@@ -414,6 +414,7 @@ struct Engine {
     bool fast_per_cell = false;  // MCS_FAST_CELLS=1: the one-block-per-cell kernel (A/B runs)
     int4* d_rs_tab = nullptr;     // resize_level_sel_kernel tables, all levels
     int oct_nt = MCS_OCT_NT;  // octree block size (MCS_OCT_THREADS overrides)
+    bool oct_nt_forced = false;
     int rs_nr[MCS_PLAN_MAX_LEVELS] = {};  // source rows one group of MCS_RS_ROWS output rows spans (resize_level_sel_kernel<NR>)
     int rs_xw_ofs[MCS_PLAN_MAX_LEVELS] = {}, rs_yw_ofs[MCS_PLAN_MAX_LEVELS] = {};
     bool rs_sel_ok = false;
@@ -566,7 +567,7 @@ struct Engine {
         oct_nt = T.nfeatures > 3000 ? 512 : (T.nfeatures > 1500 ? 256 : MCS_OCT_NT);
         if (const char* e = getenv("MCS_OCT_THREADS")) {
             const int v = atoi(e);
-            if (v >= 32 && v <= MCS_OCT_NT_MAX && v % 32 == 0) oct_nt = v;
+            if (v >= 32 && v <= MCS_OCT_NT_MAX && v % 32 == 0) { oct_nt = v; oct_nt_forced = true; }
         }
         std::vector<uint4> cells;
         build_cell_table(np, cells);
@@ -771,6 +772,15 @@ struct Engine {
             launches++;
         }
         mark(ST_OCTREE);
+        // Few images (the per-frame latency mode): the launch cannot fill the SMs with blocks, so each block gets more threads and
+        // its per-round passes over the candidates take fewer steps (one rig frame 0.49 -> 0.45 ms, eight 0.80 -> 0.76 ms); large
+        // batches keep the narrow blocks, which interleave better with the other chunks' kernels.
+        int oct_nt = this->oct_nt;
+        if (!oct_nt_forced) {
+            const int blocks = P.nlevels * n;
+            if (blocks * 2 <= sm_count_) oct_nt = std::max(oct_nt, 512);
+            else if (blocks <= 4 * sm_count_) oct_nt = std::max(oct_nt, 256);
+        }
         if (hi) {
             CK(cudaEventRecord(hi->e0, st));
             CK(cudaStreamWaitEvent(hi->st, hi->e0, 0));
