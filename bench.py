@@ -391,6 +391,7 @@ def run_gpu(args, rank, world, local, cfg):
         latency = latency_sweep(rig, d_images, d_masks, pin, pin_m, F, args.latency_iters)
     host_step()  # leave the results of a full (chunked, host-buffer) step in the handle for the parity block
     kc, n_rows, n_acc = rig.counts(0)
+    d2h = int(rig.last_d2h_bytes)  # counted by the library from the copies of that step (rows / landmarks sized by counts)
     # what a multi-GPU front-end hands on: per-frame counts gathered to rank 0 and ordered by global frame index (the features themselves
     # stay with the rank that owns the frame); after the timed region
     gathered = None
@@ -406,7 +407,6 @@ def run_gpu(args, rank, world, local, cfg):
                         "landmarks": sum(a[2] for a in allf), "order": "global frame index, frame g from rank g mod n_gpus"}
     except Exception as e:  # reported, does not void the timing
         gathered = {"error": str(e)[:200]}
-    d2h = rig_d2h_bytes(rig, F)
     h2d = frames.nbytes + (masks.nbytes if masks is not None else 0)
     return dict(rig=rig, calib=calib, frames=frames, masks=masks, ms_dev=ms_dev, ms_e2e=ms_e2e, ms_e2e_u8=ms_e2e_u8, launches=launches, clocks=clk,
                 stage_ms=stage_ms, cpus_bound=cpus_bound, counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, h2d=h2d, F=F, Fp=Fp, dist=dist, latency=latency,
@@ -458,15 +458,6 @@ def latency_sweep(rig, d_images, d_masks, pin, pin_m, F, iters):
     out["iters"] = iters
     out["clock"] = "host perf_counter around the call + stream synchronize"
     return out
-
-
-def rig_d2h_bytes(rig, F):
-    """Bytes mcs_rig_process copies back per call (counted from the copies in mcslam_b200.cu download_features/ensure_*)."""
-    C_, cap, rc = rig.C, rig.kp_cap, rig.row_cap
-    feats = F * C_ * (cap * (28 + 32) + 4 + 4 + 2 * 4 * rig.nlevels)
-    rows = F * (4 + rc * C_ * 4)
-    lms = F * (4 + 4) + F * rc * (C_ * 4 + 1 + 4 + 24 + 8 + 4)
-    return feats + rows + lms
 
 
 def parity_report(rig, calib, frames, masks, nfeat):
@@ -564,6 +555,7 @@ def main():
     total_bytes, stage_bytes = algorithmic_bytes(ncam, w, h, nfeat)
     if cfg["masks"]:
         total_bytes += 4 * ncam * nfeat  # one mask lookup per keypoint
+    io_bytes = ncam * w * h + 60 * ncam * nfeat + (ncam * (ncam - 1) // 2) * nfeat * 8 + stage_bytes["triangulate"]
     value = world * F * steps / (r["ms_dev"] / 1e3)
     e2e = world * F * steps / (r["ms_e2e"] / 1e3)
     if rank != 0:
@@ -607,7 +599,10 @@ def main():
                      "algorithmic_bytes_per_launch": stage_bytes[dom] * Fp // launches_per_step,
                      "launch_ms": sm[dom] / launches_per_step,
                      "path": {"bytes_per_rig_frame": total_bytes, "achieved": total_bytes * value / world / 1e9,
-                              "frac": total_bytes * value / world / 1e9 / peak}},
+                              "frac": total_bytes * value / world / 1e9 / peak,
+                              # SURVEY.md 8(d) "also report": the inputs-and-outputs-only lower bound (source pixels + keypoints +
+                              # descriptors + pair matches + points), so nobody mistakes the two-pass model for a minimum
+                              "io_only_bytes_per_rig_frame": io_bytes, "io_only_frac": io_bytes * value / world / 1e9 / peak}},
         "stage_ms_per_launch_sequence": {"frames": Fp, **{k: round(v, 4) for k, v in sm.items()}},
         # how much of the latency-bound kernels (octree, merge, triangulation) the chunk pipeline hides: the amortised device time per
         # launch sequence next to the sum of the issue-bound kernels alone

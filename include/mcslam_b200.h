@@ -208,6 +208,10 @@ MCS_API int mcs_rig_process_device_masks_u8(mcs_rig* rig, const void* d_images, 
  * replays (tests). */
 MCS_API int mcs_rig_set_graph(mcs_rig* rig, int enable);
 MCS_API long long mcs_rig_graph_replays(const mcs_rig* rig);
+/* Bytes the last host-buffer process call (mcs_rig_process, _masks_u8, _f32) copied back to the host: keypoints and descriptors by
+ * capacity, IntraMatch rows and landmark arrays by the row count of the fullest frame of the previous call + 25 % (whole slabs on the
+ * first call; frames that outgrow the estimate are completed by a second copy).  For harnesses that account PCIe traffic. */
+MCS_API long long mcs_rig_last_d2h_bytes(const mcs_rig* rig);
 
 /* MultiCameraFrame::setData (MultiCameraFrame.cpp:95-152) fused in front of the path: images as the application holds them — CV_32F in
  * [0, 1] (imread / 255, MCDataUtils/src/DatasetReader.cpp:699-711), `channels` = 1 or 3 (interleaved BGR), tightly packed

@@ -40,7 +40,7 @@ EXPORTS = [
     "mcs_host_free_pinned", "mcs_rig_download_level", "mcs_rig_level_size", "mcs_matcher_create", "mcs_matcher_destroy", "mcs_knn2",
     "mcs_knn2_device", "mcs_knn2_device_static", "mcs_matcher_stream", "mcs_matcher_synchronize", "mcs_matcher_kernel_launches", "mcs_rig_knn2_images", "mcs_match_subsets", "mcs_rig_process_f32", "mcs_rig_process_device_f32", "mcs_rig_set_features", "mcs_rig_set_undistort", "mcs_rig_set_undistort_keypoints", "mcs_rig_get_keypoints_undist", "mcs_vocab_load_text", "mcs_vocab_create", "mcs_vocab_destroy", "mcs_vocab_info",
     "mcs_vocab_transform", "mcs_rig_vocab_transform", "mcs_rig_bow_best2", "mcs_plan_fast_tables", "mcs_rig_process_masks_u8",
-    "mcs_rig_process_device_masks_u8", "mcs_rig_set_graph", "mcs_rig_graph_replays",
+    "mcs_rig_process_device_masks_u8", "mcs_rig_set_graph", "mcs_rig_graph_replays", "mcs_rig_last_d2h_bytes",
 ]
 
 
@@ -106,6 +106,8 @@ def lib():
     L.mcs_rig_set_graph.argtypes = [vp, ci]
     L.mcs_rig_graph_replays.argtypes = [vp]
     L.mcs_rig_graph_replays.restype = C.c_longlong
+    L.mcs_rig_last_d2h_bytes.argtypes = [vp]
+    L.mcs_rig_last_d2h_bytes.restype = C.c_longlong
     L.mcs_rig_timer_stop.argtypes = [vp, vp]
     L.mcs_rig_download_level.argtypes = [vp, ci, ci, ci, ci, vp, ci]
     L.mcs_rig_level_size.argtypes = [vp, ci, vp, vp]
@@ -436,6 +438,11 @@ class RigFrames:
     @property
     def graph_replays(self):
         return lib().mcs_rig_graph_replays(self.hd)
+
+    @property
+    def last_d2h_bytes(self):
+        """Bytes the last host-buffer process call copied back (counted from the copies it queued)."""
+        return lib().mcs_rig_last_d2h_bytes(self.hd)
 
     def counts(self, frame):
         kc = np.zeros(self.C, np.int32)

@@ -1553,22 +1553,61 @@ struct mcs_rig {
         lm_host = false;
         return 0;
     }
-    int download_rows_async(int f0, int nf, cudaStream_t st) {
-        CK(cudaMemcpyAsync(h_row_count + f0, d_row_count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_rows + (size_t)f0 * row_cap * C, d_rows + (size_t)f0 * row_cap * C, (size_t)nf * row_cap * C * sizeof(int),
-                           cudaMemcpyDeviceToHost, st));
+    // Result downloads are sized by counts, not capacities: the row tables hold up to row_cap = (num_cams * kp_cap + 1) / 2 rows per frame,
+    // a frame fills well under half of that.  The copies are queued before the counts are known on the host, so each array goes down as
+    // ONE strided copy per chunk (cudaMemcpy2DAsync: nf frames x the first `rows` rows of each frame's slab) with rows = rows_est, an
+    // estimate kept from the previous call (largest row count seen + 25 % + 64; the full capacity until a call has finished).  A frame
+    // that exceeds the estimate gets its remaining rows with a second, synchronous copy after the counts have arrived (top_up_rows).
+    long long d2h_bytes = 0;  // bytes queued for download by the last process call (bench.py's e2e accounting)
+    int rows_est = 0;         // 0 = not known yet: copy whole slabs
+    int rows_sent = 0;        // rows per frame the last process call downloaded
+    template <typename T>
+    int copy_rows_2d(T* h, const T* d, size_t per_row, int f0, int nf, int rows, cudaStream_t st) {
+        const size_t pitch = (size_t)row_cap * per_row * sizeof(T), o = (size_t)f0 * row_cap * per_row;
+        CK(cudaMemcpy2DAsync(h + o, pitch, d + o, pitch, (size_t)rows * per_row * sizeof(T), nf, cudaMemcpyDeviceToHost, st));
+        d2h_bytes += (long long)rows * per_row * sizeof(T) * nf;
         return 0;
     }
-    int download_landmarks_async(int f0, int nf, cudaStream_t st) {
-        const size_t o = (size_t)f0 * row_cap, rw = (size_t)nf * row_cap;
+    int download_rows_async(int f0, int nf, cudaStream_t st, int rows = -1) {
+        if (rows < 0) rows = row_cap;
+        CK(cudaMemcpyAsync(h_row_count + f0, d_row_count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
+        d2h_bytes += nf * sizeof(int);
+        return copy_rows_2d(h_rows, d_rows, C, f0, nf, rows, st);
+    }
+    int download_landmarks_async(int f0, int nf, cudaStream_t st, int rows = -1) {
+        if (rows < 0) rows = row_cap;
+        int rc;
         CK(cudaMemcpyAsync(h_row_count + f0, d_row_count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(h_n_acc + f0, lm.n_accepted + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_lm_rows + o * C, lm.rows + o * C, rw * C * sizeof(int), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_accepted + o, lm.accepted + o, rw, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_n_views + o, lm.n_views + o, rw * sizeof(int), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_xyz + o * 3, lm.xyz + o * 3, rw * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_uv + o * 2, lm.uv_ref + o * 2, rw * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_rep + o, lm.rep_cam + o, rw * sizeof(int), cudaMemcpyDeviceToHost, st));
+        d2h_bytes += 2 * nf * sizeof(int);
+        if ((rc = copy_rows_2d(h_lm_rows, lm.rows, C, f0, nf, rows, st))) return rc;
+        if ((rc = copy_rows_2d(h_accepted, lm.accepted, 1, f0, nf, rows, st))) return rc;
+        if ((rc = copy_rows_2d(h_n_views, lm.n_views, 1, f0, nf, rows, st))) return rc;
+        if ((rc = copy_rows_2d(h_xyz, lm.xyz, 3, f0, nf, rows, st))) return rc;
+        if ((rc = copy_rows_2d(h_uv, lm.uv_ref, 2, f0, nf, rows, st))) return rc;
+        return copy_rows_2d(h_rep, lm.rep_cam, 1, f0, nf, rows, st);
+    }
+    // after the counts are on the host: fetch what a too-small estimate left behind, then re-estimate for the next call
+    int top_up_rows(int n_frames) {
+        int max_rows = 0;
+        for (int f = 0; f < n_frames; f++) max_rows = std::max(max_rows, std::min(h_row_count[f], row_cap));
+        if (max_rows > rows_sent) {
+            for (int f = 0; f < n_frames; f++) {
+                const int M = std::min(h_row_count[f], row_cap);
+                if (M <= rows_sent) continue;
+                const size_t o = (size_t)f * row_cap + rows_sent, n = (size_t)(M - rows_sent);
+                CK(cudaMemcpyAsync(h_rows + o * C, d_rows + o * C, n * C * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+                CK(cudaMemcpyAsync(h_lm_rows + o * C, lm.rows + o * C, n * C * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+                CK(cudaMemcpyAsync(h_accepted + o, lm.accepted + o, n, cudaMemcpyDeviceToHost, eng.stream));
+                CK(cudaMemcpyAsync(h_n_views + o, lm.n_views + o, n * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+                CK(cudaMemcpyAsync(h_xyz + o * 3, lm.xyz + o * 3, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, eng.stream));
+                CK(cudaMemcpyAsync(h_uv + o * 2, lm.uv_ref + o * 2, n * 2 * sizeof(float), cudaMemcpyDeviceToHost, eng.stream));
+                CK(cudaMemcpyAsync(h_rep + o, lm.rep_cam + o, n * sizeof(int), cudaMemcpyDeviceToHost, eng.stream));
+                d2h_bytes += (long long)n * (2 * C * 4 + 1 + 4 + 24 + 8 + 4);
+            }
+            CK(cudaStreamSynchronize(eng.stream));
+        }
+        rows_est = std::min(row_cap, max_rows + max_rows / 4 + 64);
         return 0;
     }
     // RECTIFY: the segmentation masks are undistorted with the same maps (MultiCameraFrame.cpp:131-134); *dm is replaced
@@ -1696,6 +1735,10 @@ struct mcs_rig {
         const int cf = (h_images || h_f32) ? std::max(1, chunk_frames / host_chunk_div) : chunk_frames;
         const bool chunked = chunk_frames > 0 && n_frames > cf && !eng.profiling;
         const int step = chunked ? cf : n_frames;
+        if (download) {
+            d2h_bytes = 0;
+            rows_sent = rows_est > 0 ? rows_est : row_cap;
+        }
         mcs::ImageSet set{};
         // latency mode: replay (or capture, the first time) the launch sequence of this exact call
         const bool graphable = use_graph && d_images && !h_masks && !undistort_on && !chunked && !eng.profiling && !download;
@@ -1783,8 +1826,9 @@ struct mcs_rig {
             if (rc) return rc;
             if (download) {
                 if ((rc = eng.download_features_async(f0 * C, nf * C, st))) return rc;
-                if ((rc = download_rows_async(f0, nf, st))) return rc;
-                if ((rc = download_landmarks_async(f0, nf, st))) return rc;
+                d2h_bytes += (long long)nf * C * (8 + 8 * eng.plan.nlevels + (long long)kp_cap * (sizeof(mcs::KeypointPod) + 32));
+                if ((rc = download_rows_async(f0, nf, st, rows_sent))) return rc;
+                if ((rc = download_landmarks_async(f0, nf, st, rows_sent))) return rc;
             }
         }
         if (chunked) {
@@ -1800,6 +1844,7 @@ struct mcs_rig {
             if ((rc = eng.check_counts(n_frames * C))) return rc;
             feat_host = true;
             if ((rc = check_rows())) return rc;
+            if ((rc = top_up_rows(n_frames))) return rc;
             lm_host = true;
         }
         return 0;
@@ -2062,6 +2107,7 @@ int mcs_rig_set_graph(mcs_rig* rig, int enable) {
     return 0;
 }
 long long mcs_rig_graph_replays(const mcs_rig* rig) { return rig ? rig->graph_replays : 0; }
+long long mcs_rig_last_d2h_bytes(const mcs_rig* rig) { return rig ? rig->d2h_bytes : 0; }
 static int check_f32_args(mcs_rig* rig, const void* images, int channels, int n_frames) {
     if (!images || n_frames < 1) return MCS_ERR_EMPTY;
     if (channels != 1 && channels != 3) { set_err("f32 input: channels must be 1 (gray) or 3 (BGR)"); return MCS_ERR_ARG; }

@@ -350,6 +350,52 @@ def test_masks_u8_and_graph_latency_mode():
     B.device_free(0, d_mu8)
 
 
+def test_row_download_estimate_and_top_up():
+    """mcs_rig_process sizes the downloads of the IntraMatch rows and landmark arrays by the previous call's fullest frame (+ 25 % + 64)
+    instead of the table capacity.  A call on nearly flat frames (a handful of rows) followed by a call on textured frames (hundreds)
+    must fetch the missing rows afterwards; the results equal those of a fresh handle, and the byte count shrinks once the estimate is
+    in place."""
+    import mcslam_b200 as M
+    calib = M.synth.make_rig(3, 320, 240)
+    rich = np.stack([M.synth.make_rig_frame(calib, 320, 240, frame_index=40 + i, n_rects=6) for i in range(3)])
+    rng = np.random.default_rng(3)
+    flat = np.full_like(rich, 120)
+    flat[:, :, 60:120, 80:160] = rng.integers(0, 256, (3, 3, 60, 80), dtype=np.uint8)  # a little texture: few matches
+
+    def snapshot(rig):
+        return [([rig.features(f, c) for c in range(3)], rig.intra_matches(f), rig.landmarks(f), rig.counts(f)) for f in range(3)]
+
+    def same(a, b):
+        for (fa, ra, la, ca), (fb, rb, lb, cb) in zip(a, b):
+            for (ka, da), (kb, db) in zip(fa, fb):
+                assert (ka == kb).all() and np.array_equal(da, db)
+            assert np.array_equal(ra, rb)
+            for k in la:
+                assert np.array_equal(la[k], lb[k]), k
+            assert (ca[0] == cb[0]).all() and ca[1:] == cb[1:]
+
+    fresh = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=3)
+    fresh.process(rich)
+    want_rich = snapshot(fresh)
+    full_bytes = fresh.last_d2h_bytes
+    rows_rich = max(len(r[1]) for r in want_rich)
+    fresh2 = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=3)
+    fresh2.process(flat)
+    want_flat = snapshot(fresh2)
+    rows_flat = max(len(r[1]) for r in want_flat)
+    assert rows_rich > rows_flat + rows_flat // 4 + 64, (rows_rich, rows_flat)  # the rich frames outgrow the estimate left by the flat ones
+    rig = M.RigFrames(calib, 320, 240, nfeatures=300, max_frames=3)
+    rig.process(flat)
+    same(want_flat, snapshot(rig))
+    rig.process(rich)            # estimate from the flat call is too small: top-up path
+    same(want_rich, snapshot(rig))
+    rig.process(rich)            # estimate now fits: trimmed copies only
+    same(want_rich, snapshot(rig))
+    assert rig.last_d2h_bytes < full_bytes
+    rig.process(flat)
+    same(want_flat, snapshot(rig))
+
+
 def test_chunked_pipeline_equals_single_chunk():
     """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
     -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""
