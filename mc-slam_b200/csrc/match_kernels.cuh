@@ -93,6 +93,127 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K6x  EXPERIMENT, not the default path (MCS_MATCH_IMMA=1): the same BruteForceMatch with the distances from the integer tensor path.
+// north_star asks for XOR + __popc and no tensor cores in the matcher, so hamming_match_kernel above stays the product path; this kernel
+// exists to MEASURE what an exact integer formulation would buy (profiles/README.md, round 2).
+//   popc(q ^ t) = popc(q) + popc(t) - 2 * <q, t>   with the bits of q and t as 0 / 1 bytes, and <q, t> from
+//   mma.sync.m16n8k32.s32.u8.u8.s32 (IMMA.16832.U8.U8 on sm_100a; the b1 xor.popc form is emulated by ptxas with 8 of these plus masking).
+// One warp = 16 queries; their 256 bits live expanded in 32 A-fragment registers for the whole kernel.  The block expands MCS_IMMA_TC
+// train descriptors at a time into shared memory in B-fragment order (256 B per descriptor, conflict-free 64-bit loads) together with
+// the word K_t = popc(t) << 16 | train index, so that  key = K_t + (popc(q) << 16) - (dot << 17)  is the packed (distance, index) key
+// of hamming_match_kernel: same top-2 by min / max, same tie order, same accept rule => identical outputs.  Any fixed permutation of
+// the 256 bit positions cancels in the dot product; the one used here: k-step s = descriptor word s, thread-in-group t = byte t of
+// that word, low nibble in the k = 0..15 half, high nibble in the k = 16..31 half.
+// ------------------------------------------------------------------------------------------------------------
+#define MCS_IMMA_TC 128   // train descriptors per shared-memory pass
+#define MCS_IMMA_NT 256   // 8 warps x 16 queries
+
+__device__ __forceinline__ uint32_t bits4_to_bytes(uint32_t n) { return ((n & 0xFu) * 0x00204081u) & 0x01010101u; }
+
+__global__ void __launch_bounds__(MCS_IMMA_NT) hamming_match_imma_kernel(int num_cams, int kp_cap, PairList pairs, int frame0,
+                                                                         const uint8_t* __restrict__ desc, const int* __restrict__ kp_count,
+                                                                         float dist_thresh, float ratio, int* __restrict__ match_train,
+                                                                         int* __restrict__ match_d0, int* __restrict__ match_d1) {
+    __shared__ __align__(16) uint32_t s_b[MCS_IMMA_TC / 8][8][8][4][2];  // [tile][k-step][column][thread-in-group][low, high nibble]
+    __shared__ uint32_t s_k[MCS_IMMA_TC];                                // popc(t) << 16 | train index
+    const int frame = frame0 + blockIdx.z, pair = blockIdx.y;
+    const int ca = frame * num_cams + pairs.a[pair], cb = frame * num_cams + pairs.b[pair];
+    const int nq = kp_count[ca], nt = kp_count[cb];
+    const int q0i = blockIdx.x * (MCS_IMMA_NT / 2);
+    if (q0i >= nq) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int qa = q0i + warp * 16 + g, qb = qa + 8;  // the two query rows of this thread's fragments
+    uint32_t a[8][4];
+    uint32_t rq0 = 0, rq1 = 0;  // popc(q) << 16
+    {
+        uint32_t w0[8], w1[8];
+#pragma unroll
+        for (int s4 = 0; s4 < 2; s4++) {
+            uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
+            if (qa < nq) v0 = __ldg(reinterpret_cast<const uint4*>(desc + ((size_t)ca * kp_cap + qa) * 32) + s4);
+            if (qb < nq) v1 = __ldg(reinterpret_cast<const uint4*>(desc + ((size_t)ca * kp_cap + qb) * 32) + s4);
+            w0[4 * s4] = v0.x; w0[4 * s4 + 1] = v0.y; w0[4 * s4 + 2] = v0.z; w0[4 * s4 + 3] = v0.w;
+            w1[4 * s4] = v1.x; w1[4 * s4 + 1] = v1.y; w1[4 * s4 + 2] = v1.z; w1[4 * s4 + 3] = v1.w;
+        }
+#pragma unroll
+        for (int s = 0; s < 8; s++) {
+            rq0 += (uint32_t)__popc(w0[s]) << 16;
+            rq1 += (uint32_t)__popc(w1[s]) << 16;
+            const uint32_t b0 = w0[s] >> (8 * t), b1 = w1[s] >> (8 * t);
+            a[s][0] = bits4_to_bytes(b0);
+            a[s][1] = bits4_to_bytes(b1);
+            a[s][2] = bits4_to_bytes(b0 >> 4);
+            a[s][3] = bits4_to_bytes(b1 >> 4);
+        }
+    }
+    uint32_t k00 = 0xFFFFFFFFu, k01 = 0xFFFFFFFFu, k10 = 0xFFFFFFFFu, k11 = 0xFFFFFFFFu;  // top-2 keys of row qa / row qb (this thread's columns)
+    const uint32_t* tbase = reinterpret_cast<const uint32_t*>(desc + (size_t)cb * kp_cap * 32);
+    for (int c0 = 0; c0 < nt; c0 += MCS_IMMA_TC) {
+        __syncthreads();
+        for (int j = threadIdx.x; j < MCS_IMMA_TC; j += MCS_IMMA_NT) s_k[j] = 0x3FFF0000u;  // past the end: never among the best two
+        __syncthreads();
+        // expand: item = (train j, word s); 8 expanded words = [t][low, high]
+        for (int it = threadIdx.x; it < MCS_IMMA_TC * 8; it += MCS_IMMA_NT) {
+            const int s = it / MCS_IMMA_TC, j = it - s * MCS_IMMA_TC;  // train fastest: the 128-bit stores of a quarter-warp conflict 2-way at most
+            uint32_t w = 0;
+            const bool live = c0 + j < nt;
+            if (live) w = __ldg(tbase + (size_t)(c0 + j) * 8 + s);
+            uint4 lo, hi;  // t = 0, 1 | t = 2, 3
+            lo.x = bits4_to_bytes(w); lo.y = bits4_to_bytes(w >> 4); lo.z = bits4_to_bytes(w >> 8); lo.w = bits4_to_bytes(w >> 12);
+            hi.x = bits4_to_bytes(w >> 16); hi.y = bits4_to_bytes(w >> 20); hi.z = bits4_to_bytes(w >> 24); hi.w = bits4_to_bytes(w >> 28);
+            uint4* dst = reinterpret_cast<uint4*>(&s_b[j >> 3][s][j & 7][0][0]);
+            dst[0] = lo;
+            dst[1] = hi;
+            if (live) atomicAdd(&s_k[j], ((uint32_t)__popc(w) << 16) + (s == 0 ? (uint32_t)(c0 + j) - 0x3FFF0000u : 0u));
+        }
+        __syncthreads();
+        const int ntile = (min(MCS_IMMA_TC, nt - c0) + 7) >> 3;
+        for (int tile = 0; tile < ntile; tile++) {
+            int d0 = 0, d1 = 0, d2 = 0, d3 = 0;
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                const uint2 b = *reinterpret_cast<const uint2*>(&s_b[tile][s][g][t][0]);
+                asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+r"(d0), "+r"(d1), "+r"(d2), "+r"(d3)
+                             : "r"(a[s][0]), "r"(a[s][1]), "r"(a[s][2]), "r"(a[s][3]), "r"(b.x), "r"(b.y));
+            }
+            // d0: (row qa, column 2t), d1: (qa, 2t + 1), d2: (qb, 2t), d3: (qb, 2t + 1)
+            const uint2 kt = *reinterpret_cast<const uint2*>(&s_k[tile * 8 + 2 * t]);
+            uint32_t key, hi;
+            key = kt.x + rq0 - ((uint32_t)d0 << 17); hi = max(key, k00); k00 = min(key, k00); k01 = min(k01, hi);
+            key = kt.y + rq0 - ((uint32_t)d1 << 17); hi = max(key, k00); k00 = min(key, k00); k01 = min(k01, hi);
+            key = kt.x + rq1 - ((uint32_t)d2 << 17); hi = max(key, k10); k10 = min(key, k10); k11 = min(k11, hi);
+            key = kt.y + rq1 - ((uint32_t)d3 << 17); hi = max(key, k10); k10 = min(key, k10); k11 = min(k11, hi);
+        }
+    }
+    // merge the four column groups of a row: top-2 of the union of two top-2 lists
+#pragma unroll
+    for (int o = 1; o <= 2; o <<= 1) {
+        uint32_t b0 = __shfl_xor_sync(0xFFFFFFFFu, k00, o), b1 = __shfl_xor_sync(0xFFFFFFFFu, k01, o);
+        k01 = min(max(k00, b0), min(k01, b1));
+        k00 = min(k00, b0);
+        b0 = __shfl_xor_sync(0xFFFFFFFFu, k10, o);
+        b1 = __shfl_xor_sync(0xFFFFFFFFu, k11, o);
+        k11 = min(max(k10, b0), min(k11, b1));
+        k10 = min(k10, b0);
+    }
+    if (t != 0) return;
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        const int q = r ? qb : qa;
+        if (q >= nq) continue;
+        const uint32_t k0 = r ? k10 : k00, k1 = r ? k11 : k01;
+        const int e0 = nt >= 1 ? (int)(k0 >> 16) : (1 << 20), e1 = nt >= 2 ? (int)(k1 >> 16) : (1 << 20);
+        const int i0 = nt >= 1 ? (int)(k0 & 0xFFFFu) : -1;
+        const bool ok = nt >= 2 && ((float)e0 < __fmul_rn(ratio, (float)e1)) && !((float)e0 > dist_thresh);
+        const size_t o = ((size_t)blockIdx.z * pairs.n_pairs + pair) * kp_cap + q;
+        match_train[o] = ok ? i0 : -1;
+        if (match_d0) match_d0[o] = e0;
+        if (match_d1) match_d1[o] = e1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K6b  knn2: DescriptorMatcher("BruteForce-Hamming")->knnMatch(query, train, k = 2) as the inter-frame matchers call it
 // (/root/reference/MCSlam/src/FrontEnd.cpp:3134-3135 findMatchesMono, :3199-3201 findInterMatches), for many independent
 // (query, train) sets per launch.  Output per query row: (trainIdx0, dist0, trainIdx1, dist1), -1 where the train set is

@@ -1222,6 +1222,7 @@ struct mcs_rig {
     int host_chunk_div = 4; // host-buffer calls use chunks of chunk_frames / host_chunk_div (MCS_HOST_CHUNK_DIV): 6 slots x quarter chunks measured best
     int tri_per_sm = 3;     // resident tri_solve blocks per SM (MCS_TRI_PER_SM; 0 = as many as shared memory holds): 3 measured best — the
                             // one-warp blocks hold 44 KB of shared memory each for the length of a Jacobi chain, which other chunks' kernels need
+    bool match_imma = false; // MCS_MATCH_IMMA=1: experiment, the pair matcher on the u8 integer MMA (hamming_match_imma_kernel); not the product path
     bool use_hi = true;     // octree, merge and triangulation on the slots' high-priority side streams (MCS_HIPRIO=0 switches it off): +0.7 %
     mcs::LandmarkOut lm{};
     float* d_masks = nullptr;
@@ -1358,6 +1359,7 @@ struct mcs_rig {
         }
         if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
         if (const char* e = getenv("MCS_HIPRIO")) use_hi = atoi(e) != 0;
+        if (const char* e = getenv("MCS_MATCH_IMMA")) match_imma = atoi(e) != 0;
         if (const char* e = getenv("MCS_HOST_CHUNK_DIV")) host_chunk_div = std::max(1, std::min(16, atoi(e)));
         if (const char* e = getenv("MCS_TRI_PER_SM")) tri_per_sm = std::max(0, atoi(e));
         if (use_hi) {
@@ -1467,6 +1469,11 @@ struct mcs_rig {
         eng.mark(ST_MATCH);
         if (pairs.n_pairs > 0) {
             dim3 g((kp_cap + MCS_MATCH_NT - 1) / MCS_MATCH_NT, pairs.n_pairs, n_frames);
+            if (match_imma) {  // experiment (MCS_MATCH_IMMA=1): distances from the u8 integer MMA, same outputs
+                dim3 gi((kp_cap + MCS_IMMA_NT / 2 - 1) / (MCS_IMMA_NT / 2), pairs.n_pairs, n_frames);
+                mcs::hamming_match_imma_kernel<<<gi, MCS_IMMA_NT, 0, st>>>(C, kp_cap, pairs, f0, eng.d_desc, eng.d_kp_count, dist_thresh, ratio,
+                                                                           match_train, nullptr, nullptr);
+            } else
             mcs::hamming_match_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, st>>>(C, kp_cap, pairs, f0, eng.d_desc, eng.d_kp_count, dist_thresh,
                                                                                     ratio, match_train, nullptr, nullptr);
             eng.launches++;
@@ -1950,6 +1957,12 @@ int mcs_rig_brute_force_match(mcs_rig* rig, int frame, int cam1, int cam2, float
     const int cap = rig->kp_cap;
     dim3 g((cap + MCS_MATCH_NT - 1) / MCS_MATCH_NT, 1, 1);
     CK(cudaMemsetAsync(rig->d_match_tmp, 0xFF, (size_t)cap * 3 * sizeof(int), rig->eng.stream));
+    if (rig->match_imma) {  // experiment (MCS_MATCH_IMMA=1)
+        dim3 gi((cap + MCS_IMMA_NT / 2 - 1) / (MCS_IMMA_NT / 2), 1, 1);
+        mcs::hamming_match_imma_kernel<<<gi, MCS_IMMA_NT, 0, rig->eng.stream>>>(rig->C, cap, one, frame, rig->eng.d_desc, rig->eng.d_kp_count, dist_thresh,
+                                                                                neigh_ratio, rig->d_match_tmp, rig->d_match_tmp + cap,
+                                                                                rig->d_match_tmp + 2 * cap);
+    } else
     mcs::hamming_match_kernel<<<g, MCS_MATCH_NT, MCS_MATCH_CHUNK * 32, rig->eng.stream>>>(rig->C, cap, one, frame, rig->eng.d_desc,
                                                                                           rig->eng.d_kp_count, dist_thresh, neigh_ratio,
                                                                                           rig->d_match_tmp, rig->d_match_tmp + cap,

@@ -396,6 +396,43 @@ def test_row_download_estimate_and_top_up():
     same(want_flat, snapshot(rig))
 
 
+def test_imma_matcher_experiment_equals_product_matcher(monkeypatch):
+    """MCS_MATCH_IMMA=1 (an experiment, not the product path: north_star keeps the matcher on XOR + popc) computes the pair distances as
+    popc(q) + popc(t) - 2 <q, t> with the 0 / 1-byte dot product on the u8 integer MMA.  Same packed keys, same top-2, same accept rule:
+    rows, landmarks and every pair's match list equal those of hamming_match_kernel, on ragged feature counts (cameras with 1, 0 and
+    many features included through a nearly flat image) and with the epipolar gate."""
+    import mcslam_b200 as M
+    calib = M.synth.make_rig(4, 320, 240)
+    frames = np.stack([M.synth.make_rig_frame(calib, 320, 240, frame_index=50 + i, n_rects=6) for i in range(2)])
+    frames[1, 2] = 127          # a camera without features
+    frames[1, 3] = 127
+    frames[1, 3, 100:108, 100:108] = 255   # ... and one with a handful
+
+    def run(old):
+        rig = M.RigFrames(calib, 320, 240, nfeatures=400, max_frames=2)
+        rig.process(frames, old=old)
+        out = []
+        for f in range(2):
+            pairs = [rig.brute_force_match(f, i, j) for i in range(4) for j in range(i + 1, 4)]
+            out.append((rig.intra_matches(f), rig.landmarks(f), pairs, rig.counts(f)))
+        return out
+
+    for old in (False, True):
+        monkeypatch.delenv("MCS_MATCH_IMMA", raising=False)
+        ref = run(old)
+        monkeypatch.setenv("MCS_MATCH_IMMA", "1")
+        got = run(old)
+        monkeypatch.delenv("MCS_MATCH_IMMA")
+        assert sum(len(r[0]) for r in ref) > 100
+        for (ra, la, pa, ca), (rb, lb, pb, cb) in zip(ref, got):
+            assert np.array_equal(ra, rb)
+            for k in la:
+                assert np.array_equal(la[k], lb[k]), k
+            for x, y in zip(pa, pb):
+                assert all(np.array_equal(u, v) for u, v in zip(x, y))
+            assert (ca[0] == cb[0]).all() and ca[1:] == cb[1:]
+
+
 def test_chunked_pipeline_equals_single_chunk():
     """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
     -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""
