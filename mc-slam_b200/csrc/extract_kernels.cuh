@@ -1461,6 +1461,9 @@ __global__ void __launch_bounds__(MCS_DESC_WARPS * 32) describe_kernel(const __g
 #ifndef MCS_DESCF_WARPS
 #define MCS_DESCF_WARPS 8
 #endif
+#ifndef MCS_DESCF_KPW
+#define MCS_DESCF_KPW 4  // keypoints per warp
+#endif
 __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 48 / MCS_DESCF_WARPS) describe_fused_kernel(const __grid_constant__ McsPlan P, ImageSet S,
                                                                               const uint32_t* __restrict__ sel,
                                                                               const int* __restrict__ sel_count,
@@ -1474,24 +1477,29 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 48 / MCS_DESCF_WARPS) de
     uint8_t* const s_blw = reinterpret_cast<uint8_t*>(&s_in[threadIdx.x >> 5][0][0]);
     const int img = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int k = blockIdx.x * MCS_DESCF_WARPS + warp;  // output slot
-    // level of slot k: lane l holds level l's selected count, warp scan, first level whose running total exceeds k
-    int level, before, total;
-    {
-        const int c = lane < P.nlevels ? max(__ldg(&sel_count[img * P.nlevels + lane]), 0) : 0;
-        int incl = c;
+    // lane l holds level l's selected count and the running total up to it: loaded and scanned once per warp, then every one of the
+    // warp's MCS_DESCF_KPW keypoints finds its level with one ballot (the load + scan used to be paid per keypoint: 6 % of the
+    // instructions and 30 % of the stall samples of the one-keypoint-per-warp form)
+    const int cnt_l = lane < P.nlevels ? max(__ldg(&sel_count[img * P.nlevels + lane]), 0) : 0;
+    int incl = cnt_l;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-            if (lane >= o) incl += v;
-        }
-        total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-        const unsigned m = __ballot_sync(0xFFFFFFFFu, lane < P.nlevels && k < incl);
-        level = m ? __ffs(m) - 1 : -1;
-        before = __shfl_sync(0xFFFFFFFFu, incl - c, max(level, 0));
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) kp_count[img] = min(total, P.kp_cap);
-    if (level < 0 || k >= P.kp_cap) return;  // warp-uniform
+    {
+        const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (blockIdx.x == 0 && threadIdx.x == 0) kp_count[img] = min(total, P.kp_cap);
+    }
+    const int excl = incl - cnt_l;
+#pragma unroll 1
+    for (int it = 0; it < MCS_DESCF_KPW; it++) {
+    const int k = (blockIdx.x * MCS_DESCF_KPW + it) * MCS_DESCF_WARPS + warp;  // output slot: the block's warps take consecutive slots
+    const unsigned lm = __ballot_sync(0xFFFFFFFFu, lane < P.nlevels && k < incl);  // first level whose running total exceeds k
+    if (k >= P.kp_cap || lm == 0) break;  // past the last keypoint; warp-uniform, and slots only grow with `it`
+    const int level = __ffs(lm) - 1;
+    const int before = __shfl_sync(0xFFFFFFFFu, excl, level);
+    __syncwarp();  // the previous keypoint's descriptor reads of s_blw are done
     const McsLevel& Lv = P.L[level];
     const uint32_t rec = sel[(size_t)img * P.sel_stride + Lv.sel_ofs + (k - before)];
     const int px = mcs_oct::cand_x(rec) + MCS_MIN_BORDER, py = mcs_oct::cand_y(rec) + MCS_MIN_BORDER;  // :883-884
@@ -1578,7 +1586,7 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 48 / MCS_DESCF_WARPS) de
     // 16 points = 8 tests = 1 descriptor byte per lane (computeOrbDescriptor :106-145 with a = 1, b = 0).  Slot s of lane i is one of
     // the tests 8i .. 8i+7, in an order the host chose so that the 32 lanes of a slot hit few common banks; each word holds the two
     // byte offsets into the blurred patch and the bit the result goes to.
-    const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2);
+    const uint4 pw0 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2);  // (L1-resident; kept out of the loop-carried registers)
     const uint4 pw1 = __ldg(reinterpret_cast<const uint4*>(g_pattern_ofs28) + lane * 2 + 1);
     const uint32_t pw[8] = {pw0.x, pw0.y, pw0.z, pw0.w, pw1.x, pw1.y, pw1.z, pw1.w};
     int val = 0;
@@ -1605,6 +1613,7 @@ __global__ void __launch_bounds__(MCS_DESCF_WARPS * 32, 48 / MCS_DESCF_WARPS) de
         kp.class_id = -1;
         kps[slot] = kp;
     }
+    }  // keypoints of this warp
 }
 
 // operator() :1153-1162 with a non-trivial vLappingArea: keypoints with lap0 <= pt.x <= lap1 go to the BACK (filled

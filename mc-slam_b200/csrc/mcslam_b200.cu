@@ -804,7 +804,7 @@ struct Engine {
         } else {
             // shipped mode (angle 0): blur only the 32 x 32 patch under every keypoint, inside the descriptor kernel
             mark(ST_DESCRIBE);
-            mcs::describe_fused_kernel<<<dim3((P.kp_cap + MCS_DESCF_WARPS - 1) / MCS_DESCF_WARPS, n), MCS_DESCF_WARPS * 32, 0, st>>>(
+            mcs::describe_fused_kernel<<<dim3((P.kp_cap + MCS_DESCF_WARPS * MCS_DESCF_KPW - 1) / (MCS_DESCF_WARPS * MCS_DESCF_KPW), n), MCS_DESCF_WARPS * 32, 0, st>>>(
                 P, set, sel, sel_count, kps, desc, kp_count);
             launches++;
             blur_valid = false;
