@@ -295,6 +295,11 @@ def run_reference(args, rank, cfg):
     print(json.dumps(line), flush=True)
 
 
+def note(rank, msg):
+    """Progress line on stderr (stdout carries only the JSON line): which phase a rank is in when a run is cut short."""
+    print("[bench rank %d] %s" % (rank, msg), file=sys.stderr, flush=True)
+
+
 def dist_setup(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -317,7 +322,9 @@ def run_gpu(args, rank, world, local, cfg):
     cpus_bound = 0 if os.environ.get("MCS_NO_AFFINITY") else M.lib().mcs_bind_host_thread(local)
     F = args.frames
     w, h, ncam, nfeat = cfg["w"], cfg["h"], cfg["ncam"], cfg["nfeat"]
+    note(rank, "rendering the workload")
     calib, frames, masks, mine = make_workload(F, args.distinct, rank, cfg, world)
+    note(rank, "workload ready, creating the rig handle")
     rig = M.RigFrames(calib, w, h, nfeatures=nfeat, max_frames=F, device=local)
     # pinned host staging (the e2e leg copies from here every step) + a resident device copy (the `value` leg)
     pin = B.pinned_empty(frames.shape, np.uint8)
@@ -358,13 +365,16 @@ def run_gpu(args, rank, world, local, cfg):
 
     dev_step = lambda: rig.process_device(d_images, F, d_masks)                            # noqa: E731
     host_step = lambda: rig.process(pin.arr, masks=None if pin_m is None else pin_m.arr)   # noqa: E731
+    note(rank, "warm-up")
     for _ in range(max(args.warmup, 3)):
         dev_step()
     rig.synchronize()
+    note(rank, "timing the device-resident leg")
     launches0 = rig.kernel_launches
     clocks = ClockSampler(local)
     ms_dev = timed(dev_step, args.steps)
     launches = rig.kernel_launches - launches0
+    note(rank, "timing the host-buffer leg")
     for _ in range(max(args.warmup, 3)):
         host_step()
     ms_e2e = timed(host_step, args.steps)
@@ -395,6 +405,7 @@ def run_gpu(args, rank, world, local, cfg):
     # what a multi-GPU front-end hands on: per-frame counts gathered to rank 0 and ordered by global frame index (the features themselves
     # stay with the rank that owns the frame); after the timed region
     gathered = None
+    note(rank, "gathering the per-frame counts")
     try:
         from mcslam_b200 import sharding as S
         local = {}
@@ -407,6 +418,7 @@ def run_gpu(args, rank, world, local, cfg):
                         "landmarks": sum(a[2] for a in allf), "order": "global frame index, frame g from rank g mod n_gpus"}
     except Exception as e:  # reported, does not void the timing
         gathered = {"error": str(e)[:200]}
+    note(rank, "done")
     h2d = frames.nbytes + (masks.nbytes if masks is not None else 0)
     return dict(rig=rig, calib=calib, frames=frames, masks=masks, ms_dev=ms_dev, ms_e2e=ms_e2e, ms_e2e_u8=ms_e2e_u8, launches=launches, clocks=clk,
                 stage_ms=stage_ms, cpus_bound=cpus_bound, counts=(kc.tolist(), n_rows, n_acc), d2h=d2h, h2d=h2d, F=F, Fp=Fp, dist=dist, latency=latency,

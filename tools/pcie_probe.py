@@ -21,9 +21,12 @@ import torch.distributed as dist
 
 FRAMES, CHUNK, NSLOT = 512, 16, 6
 UP_PER_FRAME = 5 * 720 * 540
-# the 15 result copies of one chunk, bytes per rig frame (kp_cap 1004, row_cap 2510, 5 cameras, 8 levels): download_features_async,
-# download_rows_async, download_landmarks_async in mc-slam_b200/csrc/mcslam_b200.cu
-DOWN_PER_FRAME = [20, 20, 160, 160, 5 * 1004 * 28, 5 * 1004 * 32, 4, 2510 * 20, 4, 4, 2510 * 20, 2510, 2510 * 4, 2510 * 24, 2510 * 8, 2510 * 4]
+# the 16 result copies of one chunk, bytes per rig frame (kp_cap 1004, 5 cameras, 8 levels): download_features_async,
+# download_rows_async, download_landmarks_async in mc-slam_b200/csrc/mcslam_b200.cu.  ROWS = rows per frame the row / landmark copies
+# carry: the library sends the previous call's fullest frame + 25 % + 64 (about 1500 on the bench workload; MCS_PROBE_ROWS=2510 is the
+# table capacity, the round-1 pattern the first committed probe run used)
+ROWS = int(os.environ.get("MCS_PROBE_ROWS", "1500"))
+DOWN_PER_FRAME = [20, 20, 160, 160, 5 * 1004 * 28, 5 * 1004 * 32, 4, ROWS * 20, 4, 4, ROWS * 20, ROWS, ROWS * 4, ROWS * 24, ROWS * 8, ROWS * 4]
 
 
 def main():
@@ -85,7 +88,7 @@ def main():
     steps = 10
     up = FRAMES * UP_PER_FRAME
     down = FRAMES * sum(DOWN_PER_FRAME)
-    out = {"ranks": world, "frames_per_step": FRAMES, "chunk_frames": CHUNK, "streams": NSLOT, "h2d_bytes_per_step": up, "d2h_bytes_per_step": down}
+    out = {"ranks": world, "rows_per_frame_sent": ROWS, "frames_per_step": FRAMES, "chunk_frames": CHUNK, "streams": NSLOT, "h2d_bytes_per_step": up, "d2h_bytes_per_step": down}
     ms = timed(steps, h2d=True, d2h=False)
     out["h2d_chunks"] = {"ms_per_step": round(ms, 3), "aggregate_GBps": round(world * up / ms / 1e6, 1), "copy_bound_rig_frames_per_s": round(world * FRAMES / ms * 1e3)}
     ms = timed(steps, h2d=True, d2h=True)
