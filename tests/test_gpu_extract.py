@@ -79,6 +79,40 @@ def test_noise_worst_case_720():
     assert mono == m2 and (kps == k2).all() and np.array_equal(desc, d2)
 
 
+FUZZ = [  # w, h, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST
+    (411, 233, 300, 1.5, 5, 20, 7),
+    (640, 480, 800, 2.0, 4, 30, 10),
+    (257, 190, 200, 1.1, 10, 15, 5),
+    (512, 384, 600, 1.3, 6, 40, 40),
+    (300, 300, 150, 1.2, 3, 10, 3),
+    (720, 540, 2000, 1.2, 8, 12, 4),
+    (1000, 160, 400, 1.25, 4, 25, 9),   # every level keeps at least one 35 px cell row: below that the reference divides by zero
+]
+
+
+@pytest.mark.parametrize("w,h,nf,sf,nl,ini,mn", FUZZ)
+def test_constructor_parameter_sweep(w, h, nf, sf, nl, ini, mn):
+    """ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST) away from the 1000 / 1.2 / 8 / 20 / 7 every other test uses:
+    other scale factors (resize tables, level sizes, quotas), level counts, thresholds (equal thresholds switch the retry off), a wide
+    flat image (several octree roots), many features at low thresholds — a textured synthetic view blended with noise, stage by stage
+    against the oracle."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(2, w, h)
+    base = M.synth.make_rig_frame(calib, w, h, frame_index=w + h, n_rects=7)[1].astype(np.int32)
+    noise = M.synth.noise_image(w, h, 3 * w + nf).astype(np.int32)
+    img = np.clip((3 * base + noise) // 4, 0, 255).astype(np.uint8)
+    ex = M.Extractor(nf, scale_factor=sf, nlevels=nl, ini_th=ini, min_th=mn, max_width=w, max_height=h)
+    orc = O.Extractor(nf, sf, nl, ini, mn)
+    mono, kps, desc = ex(img)
+    m2, k2, d2 = orc(img)
+    t = ex.tables()
+    assert (t["quota"] == orc.quota).all() and (t["scale"] == orc.scale).all() and (t["sigma2"] == orc.sigma2).all()
+    _compare_stages(ex, orc, img, nlevels=nl)
+    assert mono == m2 and len(kps) == len(k2) and (kps == k2).all() and np.array_equal(desc, d2)
+    assert len(kps) > nf // 4
+
+
 @pytest.mark.parametrize("w,h,seed", [(720, 540, 3), (500, 375, 4), (417, 312, 5)])
 def test_threshold_fallback_mixed_cells(w, h, seed):
     """Cells without a corner at iniThFAST are re-run at minThFAST (ORBextractor.cpp:842-845) one by one.  Bands of strong texture,

@@ -35,6 +35,29 @@ def test_ref_extractor_matches_golden_and_oracle(golden, name, nf):
     assert m1 == m2 and 0 < m1 < len(k1) and (k1 == k2).all() and np.array_equal(d1, d2)
 
 
+SWEEP = [(411, 233, 300, 1.5, 5, 20, 7), (640, 480, 800, 2.0, 4, 30, 10), (257, 190, 200, 1.1, 10, 15, 5), (512, 384, 600, 1.3, 6, 40, 40),
+         (300, 300, 150, 1.2, 3, 10, 3), (720, 540, 2000, 1.2, 8, 12, 4), (1000, 160, 400, 1.25, 4, 25, 9)]
+
+
+@pytest.mark.parametrize("w,h,nf,sf,nl,ini,mn", SWEEP)
+def test_ref_extractor_equals_oracle_over_constructor_parameters(w, h, nf, sf, nl, ini, mn):
+    """The same ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST) sweep the GPU test runs
+    (tests/test_gpu_extract.py::test_constructor_parameter_sweep): the reference's compiled code and the restatement agree on tables,
+    pyramid levels, keypoints and descriptors."""
+    import mcslam_b200 as M
+    calib = M.synth.make_rig(2, w, h)
+    base = M.synth.make_rig_frame(calib, w, h, frame_index=w + h, n_rects=7)[1].astype(np.int32)
+    noise = M.synth.noise_image(w, h, 3 * w + nf).astype(np.int32)
+    img = np.clip((3 * base + noise) // 4, 0, 255).astype(np.uint8)
+    e, o = R.Extractor(nf, sf, nl, ini, mn), O.Extractor(nf, sf, nl, ini, mn)
+    mono, kps, desc = e(img)[:3]
+    mo, ko, do = o(img)
+    assert np.array_equal(e.quota, o.quota) and np.array_equal(e.scale, o.scale) and np.array_equal(e.sigma2, o.sigma2)
+    for l in range(nl):
+        assert np.array_equal(e.level(l), o.level(l)), l
+    assert mono == mo and len(kps) == len(ko) and (kps == ko).all() and np.array_equal(desc, do)
+
+
 @pytest.mark.parametrize("w,h,nf,seed", [(203, 157, 400, 1), (97, 83, 150, 2), (333, 130, 700, 3), (200, 260, 500, 4), (640, 480, 1000, 5)])
 def test_ref_extractor_equals_oracle_on_odd_sizes(w, h, nf, seed):
     """Single-cell levels, levels too small for a cell (nCols = 0), wide images with 3 octree roots, mild portrait, noise worst
