@@ -433,6 +433,23 @@ def test_imma_matcher_experiment_equals_product_matcher(monkeypatch):
             assert (ca[0] == cb[0]).all() and ca[1:] == cb[1:]
 
 
+@pytest.mark.parametrize("ncam,w,h,nf,old,with_masks", [(2, 320, 240, 400, False, True), (6, 256, 192, 250, True, False), (7, 200, 160, 150, False, True)])
+def test_rig_camera_count_sweep(ncam, w, h, nf, old, with_masks):
+    """Rigs of 2, 6 and 7 cameras (1, 15 and 21 camera pairs; the reference's IntraMatch holds 5, the row table here is [M][num_cams]):
+    features, rows, mask / depth-gate decisions and points of a two-frame batch against the oracle."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(ncam, w, h, spacing=0.12)
+    frames = np.stack([M.synth.make_rig_frame(calib, w, h, frame_index=70 + ncam + i, n_rects=6) for i in range(2)])
+    masks = np.stack([M.synth.make_masks(ncam, w, h, frame_index=9 + i) for i in range(2)]) if with_masks else None
+    rig = M.RigFrames(calib, w, h, nfeatures=nf, max_frames=2)
+    rig.process(frames, masks=masks, old=old)
+    for f in range(2):
+        K, D, rows, pc, tri = _oracle_frame(O, frames[f], calib, nf, masks=None if masks is None else masks[f], old=old)
+        assert len(rows) > 30
+        _check_frame(rig, f, K, D, rows, tri, ncam)
+
+
 def test_chunked_pipeline_equals_single_chunk():
     """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
     -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""
