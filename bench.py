@@ -182,18 +182,19 @@ class CpuArm:
             return wk.process(images, do_match, do_triangulate)
         return self.O.process_rig(wk, images, self.calib, threads=self.cfg["ncam"], do_match=do_match, do_triangulate=do_triangulate)
 
-    def stage_ms(self, frames, n=3):
+    def stage_ms(self, frames, n=6):
         """Per-stage time of one rig frame (the reference logs the same three, FrontEnd.cpp:992-1014): extraction alone, then with the
-        intra-match, then with the triangulation; differences of medians."""
+        intra-match, then with the triangulation, on the same frame; differences of the fastest of n runs each (the stages are cumulative
+        calls, so a difference of noisy medians could come out negative), floored at zero."""
         t = []
         for flags in ((False, False), (True, False), (True, True)):
             dt = []
             for k in range(n):
                 t0 = time.perf_counter()
-                self.run(0, frames[k % len(frames)], *flags)
+                self.run(0, frames[0], *flags)
                 dt.append(time.perf_counter() - t0)
-            t.append(1e3 * float(np.median(dt)))
-        return {"extract": round(t[0], 2), "intra_match": round(t[1] - t[0], 2), "triangulate": round(t[2] - t[1], 2)}
+            t.append(1e3 * float(min(dt)))
+        return {"extract": round(t[0], 2), "intra_match": round(max(t[1] - t[0], 0.0), 2), "triangulate": round(max(t[2] - t[1], 0.0), 2)}
 
 
 def cv2_primitives_ms(frames, nfeat, n=2):
