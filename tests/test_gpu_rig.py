@@ -450,6 +450,36 @@ def test_rig_camera_count_sweep(ncam, w, h, nf, old, with_masks):
         _check_frame(rig, f, K, D, rows, tri, ncam)
 
 
+def test_repeatability_stress():
+    """compute-sanitizer is not available on this pool, so races are hunted by repetition: a batch of 48 rig frames that holds the same
+    three frames 16 times over, processed three times (device-resident, six-stream chunk pipeline with chunks of 8).  Every copy of a
+    frame, in every pass, must produce identical features, rows and landmarks — a race in any kernel shows up as a difference."""
+    import mcslam_b200 as M
+    from mcslam_b200 import binding as B
+    calib = M.synth.make_rig(5, 720, 540)
+    base = np.stack([M.synth.make_rig_frame(calib, 720, 540, frame_index=90 + i) for i in range(3)])
+    frames = np.concatenate([base] * 16)
+    rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=48)
+    rig.set_chunk_frames(8)
+    d_img = B.device_malloc(0, frames.nbytes)
+    B.device_upload(0, d_img, frames)
+    ref = None
+    for rep in range(3):
+        rig.process_device(d_img, 48)
+        for f in range(48):
+            got = ([rig.features(f, c) for c in range(5)], rig.intra_matches(f), rig.landmarks(f))
+            if ref is None or len(ref) < 3:
+                ref = (ref or []) + [got]
+                continue
+            want = ref[f % 3]
+            for (ka, da), (kb, db) in zip(got[0], want[0]):
+                assert (ka == kb).all() and np.array_equal(da, db), (rep, f)
+            assert np.array_equal(got[1], want[1]), (rep, f)
+            for k in got[2]:
+                assert np.array_equal(got[2][k], want[2][k]), (rep, f, k)
+    B.device_free(0, d_img)
+
+
 def test_chunked_pipeline_equals_single_chunk():
     """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
     -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""
