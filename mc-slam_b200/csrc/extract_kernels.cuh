@@ -1033,7 +1033,10 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FS_MINB) fast_strips_kernel(con
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// K3c  FAST strips, persistent blocks with TMA tile staging (the default).  Same arithmetic and the same strip records as
+// K3c  FAST strips, persistent blocks with two TMA tile buffers.  NOT the default (MCS_FAST_TMA=2): measured 1.33-1.36 ms per 64 frames
+// against 1.16 ms for fast_strips_kernel<true, true> — the loop-carried state at the 40-register cap makes ptxas re-materialise values
+// inside the scan loops, and prefetching the next tile buys nothing because five other resident blocks already hide the load
+// (profiles/README.md, round 2).  Kept for A/B runs.  Same arithmetic (4-pixel pre-test) and the same strip records as
 // fast_strips_kernel; what changes is how a block gets its pixels and how long it lives:
 //   * every (level) plane is described by a 3-D tensor map (x, y, image) with a 208 x box_rows[level] box; ONE elected thread
 //     issues cp.async.bulk.tensor.3d for a whole strip tile onto an mbarrier — no per-thread LDG.128 + STS.128 staging loop, no index
