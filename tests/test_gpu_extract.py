@@ -79,6 +79,29 @@ def test_noise_worst_case_720():
     assert mono == m2 and (kps == k2).all() and np.array_equal(desc, d2)
 
 
+def test_one_handle_many_image_sizes():
+    """ORBextractor::operator() takes whatever image size it is given (the reference rebuilds mvImagePyramid per call): one handle fed
+    320x240, then a larger 640x480 (the workspace grows, plan and tensor maps are rebuilt), a width that is not a multiple of 16
+    (level 0 re-pitched), and 320x240 again — each call against the oracle, the first and last identical."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    ex = M.Extractor(500, max_width=320, max_height=240)
+    orc = O.Extractor(500)
+    first = None
+    for w, h, seed in ((320, 240, 1), (640, 480, 2), (411, 300, 3), (320, 240, 1)):
+        calib = M.synth.make_rig(2, w, h)
+        img = M.synth.make_rig_frame(calib, w, h, frame_index=seed, n_rects=6)[0]
+        mono, kps, desc = ex(img)
+        m2, k2, d2 = orc(img)
+        _compare_stages(ex, orc, img)
+        assert mono == m2 and len(kps) == len(k2) and (kps == k2).all() and np.array_equal(desc, d2), (w, h)
+        if (w, h, seed) == (320, 240, 1):
+            if first is None:
+                first = (kps.copy(), desc.copy())
+            else:
+                assert (kps == first[0]).all() and np.array_equal(desc, first[1])
+
+
 FUZZ = [  # w, h, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST
     (411, 233, 300, 1.5, 5, 20, 7),
     (640, 480, 800, 2.0, 4, 30, 10),
