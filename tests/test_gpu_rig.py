@@ -480,6 +480,23 @@ def test_repeatability_stress():
     B.device_free(0, d_img)
 
 
+def test_nview_dlt_matches_cv2_svd_fixture(golden):
+    """mcs_rig_triangulate_nview (MultiCameraFrame::triangulateIntraMatches(x, view_inds, pt), :411-441) on the fixture of
+    oracle/gen_golden_dlt.py: X from cv2.SVDecomp of the same design matrices, 200 noisy points over 2..5 views, 1e-9 relative."""
+    import mcslam_b200 as M
+    g = golden("dlt_cv2.npz")
+    rig = M.RigFrames(g["calib"], 720, 540, nfeatures=100, max_frames=1)
+    worst = 0.0
+    for v, xs, ys, want in zip(g["views"], g["xs"], g["ys"], g["xyz"]):
+        n = int((v >= 0).sum())
+        got = rig.triangulate_nview(v[:n].tolist(), [xs[:n].tolist()], [ys[:n].tolist()])[0]
+        worst = max(worst, float(np.abs(got - want).max() / np.abs(want).max()))
+    assert worst < 1e-9, worst
+    got = rig.triangulate_pair(0, 4, g["pair_p1"], g["pair_p2"])  # :481-507 against cv2.SVDecomp on the f32 system
+    rel = np.abs(got - g["pair_xyz"]).max(1) / np.abs(g["pair_xyz"]).max(1)
+    assert rel.max() < 1e-5, rel.max()
+
+
 def test_chunked_pipeline_equals_single_chunk():
     """mcs_rig_process cuts a batch into chunks over three streams; results must not depend on the chunking (7 frames, chunks of 2
     -> 4 chunks incl. a ragged last one, vs one chunk), on the host-buffer and the device-resident path."""

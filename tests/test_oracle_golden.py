@@ -75,6 +75,21 @@ def test_known_answer_triangulation():
     assert np.allclose(got32[0], [0, 0, 6], atol=2e-2)
 
 
+def test_nview_dlt_matches_cv2_svd(golden):
+    """N-view DLT (MultiCameraFrame.cpp:411-441) against OpenCV's own SVD: 200 noisy points over 2..5 views from oracle/gen_golden_dlt.py
+    (cv2.SVDecomp of the (3n) x (4+n) design).  1e-10 relative; the product's bar is 1e-6."""
+    g = golden("dlt_cv2.npz")
+    worst = 0.0
+    for v, xs, ys, want in zip(g["views"], g["xs"], g["ys"], g["xyz"]):
+        n = int((v >= 0).sum())
+        got = O.triangulate_pixels(g["calib"], v[:n].tolist(), xs[:n].tolist(), ys[:n].tolist())
+        worst = max(worst, float(np.abs(got - want).max() / np.abs(want).max()))
+    assert worst < 1e-10, worst
+    got = O.triangulate_pair_f32(g["calib"], 0, 4, g["pair_p1"], g["pair_p2"])  # MultiCameraFrame::triangulate (:481-507), f32 SVD
+    rel = np.abs(got - g["pair_xyz"]).max(1) / np.abs(g["pair_xyz"]).max(1)
+    assert rel.max() < 1e-5, rel.max()
+
+
 def test_edge_cases():
     e = O.Extractor(100)
     mono, k, d = e(np.zeros((0, 0), np.uint8).reshape(0, 0)) if False else (-1, [], [])
