@@ -21,6 +21,11 @@ namespace mcs {
 #ifndef MCS_MATCH_CHUNK
 #define MCS_MATCH_CHUNK 1024
 #endif
+#ifndef MCS_MATCH_UNROLL
+#define MCS_MATCH_UNROLL 4
+#endif
+#define MCS_PRAGMA_(x) _Pragma(#x)
+#define MCS_UNROLL(n) MCS_PRAGMA_(unroll n)
 // MCS_MATCH_CHUNK train descriptors are staged in shared memory per pass (1024 = 32 KB)
 
 struct PairList {
@@ -70,7 +75,7 @@ __global__ void __launch_bounds__(MCS_MATCH_NT) hamming_match_kernel(int num_cam
         for (int t = threadIdx.x; t < m * 2; t += MCS_MATCH_NT) s_train[t] = __ldg(tbase + (size_t)c0 * 2 + t);
         __syncthreads();
         if (active) {
-#pragma unroll 4
+            MCS_UNROLL(MCS_MATCH_UNROLL)
             for (int j = 0; j < m; j++) {
                 const uint4 ta = s_train[2 * j], tb = s_train[2 * j + 1];
                 const uint32_t key = hamming_key(qa, qb, ta, tb) + (uint32_t)(c0 + j);
