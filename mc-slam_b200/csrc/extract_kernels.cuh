@@ -1216,6 +1216,10 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FT_MINB) fast_strips_tma_kernel
 #endif
 #define MCS_OCT_NT_MAX 512  // the block size is a launch parameter (Engine::oct_nt): large quotas (config 4) use wider blocks
 
+// GTAB = false: the node tables live in the block's shared memory (every configuration the reference ships).  GTAB = true: a level
+// quota too large for that (one pyramid level holding ~2,600+ features) puts them in a per-block slice of global memory instead;
+// the same algorithm, generic atomics, __syncthreads() orders the block's global accesses.
+template <bool GTAB = false>
 struct CudaBlockCtx {
     __device__ __forceinline__ int nthreads() const { return blockDim.x; }
     __device__ __forceinline__ int tid() const { return threadIdx.x; }
@@ -1229,17 +1233,20 @@ struct CudaBlockCtx {
         if (threadIdx.x == 0) f();
         __syncthreads();
     }
-    // every target lives in the block's shared memory (mcs_oct::Shared); plain PTX reductions skip nvcc's same-address aggregation wrapper
+    // shared-memory tables (mcs_oct::Shared): plain PTX reductions skip nvcc's same-address aggregation wrapper
     __device__ __forceinline__ void atomic_add(int* p, int v) {
-        asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+        if (GTAB) atomicAdd(p, v);
+        else asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     }
     __device__ __forceinline__ void atomic_max(unsigned* p, unsigned v) {
-        asm volatile("red.shared.max.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+        if (GTAB) atomicMax(p, v);
+        else asm volatile("red.shared.max.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     }
     __device__ __forceinline__ void atomic_min(unsigned* p, unsigned v) {
-        asm volatile("red.shared.min.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+        if (GTAB) atomicMin(p, v);
+        else asm volatile("red.shared.min.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     }
-    // in-place exclusive scan of a[0..n) in shared memory; collective; returns the total
+    // in-place exclusive scan of a[0..n) (in the tables' memory); collective; returns the total
     __device__ int exclusive_scan(int* a, int n) {
         __shared__ int s_ws[34];
         const int NT = blockDim.x, t = threadIdx.x, lane = t & 31, w = t >> 5, nwarps = NT >> 5;
@@ -1280,9 +1287,11 @@ struct CudaBlockCtx {
 };
 
 // sel[img][sel_ofs(level) + k] = k-th retained candidate of the level in final list order; sel_count[img][level] = how many.
+template <bool GTAB>
 __global__ void __maxnreg__(48) octree_kernel(const __grid_constant__ McsPlan P, const uint32_t* __restrict__ cand,
                                                             const int* __restrict__ cand_count, uint16_t* __restrict__ knode,
-                                                            uint32_t* __restrict__ sel, int* __restrict__ sel_count) {
+                                                            uint32_t* __restrict__ sel, int* __restrict__ sel_count,
+                                                            unsigned char* __restrict__ g_tab, size_t g_tab_stride) {
     extern __shared__ __align__(16) unsigned char s_oct[];
     const int level = blockIdx.x, img = blockIdx.y;
     const McsLevel& Lv = P.L[level];
@@ -1301,8 +1310,8 @@ __global__ void __maxnreg__(48) octree_kernel(const __grid_constant__ McsPlan P,
         op.n_cols = Lv.n_cols;
         op.cap = Lv.oct_cap;
         mcs_oct::Shared sh;
-        sh.carve(s_oct, op.cap);
-        CudaBlockCtx ctx;
+        sh.carve(GTAB ? g_tab + ((size_t)img * P.nlevels + level) * g_tab_stride : s_oct, op.cap);
+        CudaBlockCtx<GTAB> ctx;
         const size_t kofs = (size_t)img * P.cand_stride + Lv.cand_ofs;
         n_out = mcs_oct::distribute(ctx, op, sh, cand + kofs, n_keys, knode + kofs, sel + (size_t)img * P.sel_stride + Lv.sel_ofs);
     }
@@ -1640,7 +1649,7 @@ __global__ void __launch_bounds__(256) lapping_permute_kernel(const __grid_const
     }
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
-    CudaBlockCtx ctx;
+    CudaBlockCtx<false> ctx;
     for (int base = 0; base < n; base += 1024) {
         const int m = min(1024, n - base);
         for (int i = threadIdx.x; i < m; i += blockDim.x) {

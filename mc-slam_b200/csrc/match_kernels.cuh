@@ -480,6 +480,7 @@ __global__ void __launch_bounds__(64) bow_best2_kernel(const uint8_t* __restrict
 // Fmat: per pair the f64 fundamental matrix built on the host (:1126-1141); sigma2 = mvLevelSigma2.
 // ------------------------------------------------------------------------------------------------------------
 #define MCS_MERGE_NT 256
+#define MCS_MERGE_NT_WIDE 1024
 
 struct MergeSmem {
     size_t inv, grp, rfirst, rlast, val, kind, rows, total;
@@ -540,13 +541,16 @@ __device__ __forceinline__ bool epipolar_ok(const KeypointPod& p1, const Keypoin
     return dsqr < thr;
 }
 
-__global__ void __launch_bounds__(MCS_MERGE_NT) merge_kernel(int num_cams, int kp_cap, int row_cap, PairList pairs,
-                                                             const int* __restrict__ kp_count, const int* __restrict__ match_train,
-                                                             const KeypointPod* __restrict__ kps, int use_epipolar,
-                                                             const double* __restrict__ Fmat, const float* __restrict__ sigma2,
-                                                             int* __restrict__ rows, int* __restrict__ row_count, int rows_in_smem) {
+// NT = MCS_MERGE_NT inside the chunked pipeline (one block per frame, many frames per launch); MCS_MERGE_NT_WIDE for launches of a
+// few frames, where the block's latency is the stage's: one query per thread instead of four shortens every pass of every pair.
+template <int NT>
+__global__ void __launch_bounds__(NT) merge_kernel(int num_cams, int kp_cap, int row_cap, PairList pairs,
+                                                   const int* __restrict__ kp_count, const int* __restrict__ match_train,
+                                                   const KeypointPod* __restrict__ kps, int use_epipolar,
+                                                   const double* __restrict__ Fmat, const float* __restrict__ sigma2,
+                                                   int* __restrict__ rows, int* __restrict__ row_count, int rows_in_smem) {
     enum { K_NONE = 0, K_VALID = 1, K_NEW = 2, K_ATT_A = 3, K_ATT_B = 4 };
-    constexpr int NT = MCS_MERGE_NT, BIG = 0xFFFF;
+    constexpr int BIG = 0xFFFF;
     extern __shared__ __align__(16) unsigned char s_raw[];
     __shared__ int s_wsum[NT / 32];
     const MergeSmem L = merge_smem_layout(num_cams, kp_cap, row_cap, rows_in_smem != 0);

@@ -421,6 +421,9 @@ struct Engine {
     int n_fast_cells = 0;
     uint32_t *d_cand = nullptr, *d_sel = nullptr;
     uint16_t* d_knode = nullptr;
+    unsigned char* d_oct_tab = nullptr;  // octree node tables in global memory, only when a level's tables exceed shared memory
+    size_t oct_tab_bytes = 0;
+    bool oct_gtab = false;
     int *d_cand_count = nullptr, *d_sel_count = nullptr, *d_kp_count = nullptr, *d_mono = nullptr;
     mcs::KeypointPod *d_kps = nullptr, *d_kps_tmp = nullptr;
     uint8_t *d_desc = nullptr, *d_desc_tmp = nullptr;
@@ -443,7 +446,8 @@ struct Engine {
     void free_all() {
         cudaFree(d_input); cudaFree(d_pyr); cudaFree(d_blur); cudaFree(d_xtab); cudaFree(d_ytab); cudaFree(d_cell_tab); cudaFree(d_strip_tab); cudaFree(d_rs_tab); cudaFree(d_cand); cudaFree(d_sel);
         cudaFree(d_knode); cudaFree(d_ft_ctr); cudaFree(d_cand_count); cudaFree(d_sel_count); cudaFree(d_kp_count); cudaFree(d_mono); cudaFree(d_kps);
-        cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp);
+        cudaFree(d_kps_tmp); cudaFree(d_desc); cudaFree(d_desc_tmp); cudaFree(d_oct_tab);
+        d_oct_tab = nullptr; oct_tab_bytes = 0;
         cudaFreeHost(h_kps); cudaFreeHost(h_desc); cudaFreeHost(h_kp_count); cudaFreeHost(h_mono); cudaFreeHost(h_sel_count);
         cudaFreeHost(h_cand_count);
         d_input = d_pyr = d_blur = nullptr; d_xtab = d_ytab = nullptr; d_cell_tab = nullptr; d_strip_tab = nullptr; d_rs_tab = nullptr; d_cand = d_sel = nullptr; d_knode = nullptr;
@@ -510,6 +514,15 @@ struct Engine {
             CK(cudaMemcpyToSymbol(mcs::g_pattern_ofs28, ofs, sizeof(ofs)));
         }
         return replan(max_w, max_h);
+    }
+
+    void launch_octree(const McsPlan& P, int n, int img0, int nt, cudaStream_t s, const uint32_t* cand, const int* cand_count, uint16_t* knode,
+                       uint32_t* sel, int* sel_count) {
+        if (oct_gtab)
+            mcs::octree_kernel<true><<<dim3(P.nlevels, n), nt, 0, s>>>(P, cand, cand_count, knode, sel, sel_count,
+                                                                     d_oct_tab + (size_t)img0 * P.nlevels * oct_smem, oct_smem);
+        else
+            mcs::octree_kernel<false><<<dim3(P.nlevels, n), nt, oct_smem, s>>>(P, cand, cand_count, knode, sel, sel_count, nullptr, 0);
     }
 
     // (re)build the plan for an image size; reallocates when the size grows
@@ -607,7 +620,21 @@ struct Engine {
         plan = np;
         planned_w = w; planned_h = h;
         oct_smem = mcs_oct::Shared::bytes(plan.oct_cap_max);
-        if (oct_smem > 200 * 1024) { set_err("features per level exceed the octree kernel's shared-memory table"); return MCS_ERR_ARG; }
+        // node tables of a level that do not fit a block's shared memory (a single level with ~2,600+ features: nlevels 1 or 2 with
+        // thousands of features) go to a per-block slice of global memory, octree_kernel<true>
+        oct_gtab = oct_smem > 200 * 1024;
+        if (oct_gtab) {
+            const size_t need = (size_t)max_images * plan.nlevels * oct_smem;
+            if (need > ((size_t)8 << 30)) { set_err("features per level x images too large for the octree workspace"); return MCS_ERR_ARG; }
+            if (need > oct_tab_bytes) {
+                CK(cudaStreamSynchronize(stream));
+                cudaFree(d_oct_tab);
+                d_oct_tab = nullptr;
+                oct_tab_bytes = 0;
+                CK(cudaMalloc(&d_oct_tab, need));
+                oct_tab_bytes = need;
+            }
+        }
         if (plan.fast_smem_bytes > 200 * 1024) { set_err("internal: FAST cell too large for shared memory"); return MCS_ERR_ARG; }
         CK(cudaFuncSetAttribute(mcs::fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(plan.fast_smem_bytes, 1024)));
         if (plan.fs_smem_bytes > 200 * 1024) { set_err("internal: FAST strip too large for shared memory"); return MCS_ERR_ARG; }
@@ -639,7 +666,7 @@ struct Engine {
                 if (rc) return rc;
             }
         }
-        CK(cudaFuncSetAttribute(mcs::octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
+        if (!oct_gtab) CK(cudaFuncSetAttribute(mcs::octree_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(oct_smem, 1024)));
         last_n = 0;
         return 0;
     }
@@ -784,11 +811,11 @@ struct Engine {
         if (hi) {
             CK(cudaEventRecord(hi->e0, st));
             CK(cudaStreamWaitEvent(hi->st, hi->e0, 0));
-            mcs::octree_kernel<<<dim3(P.nlevels, n), oct_nt, oct_smem, hi->st>>>(P, cand, cand_count, knode, sel, sel_count);
+            launch_octree(P, n, img0, oct_nt, hi->st, cand, cand_count, knode, sel, sel_count);
             CK(cudaEventRecord(hi->e1, hi->st));
             CK(cudaStreamWaitEvent(st, hi->e1, 0));
         } else {
-            mcs::octree_kernel<<<dim3(P.nlevels, n), oct_nt, oct_smem, st>>>(P, cand, cand_count, knode, sel, sel_count);
+            launch_octree(P, n, img0, oct_nt, st, cand, cand_count, knode, sel, sel_count);
         }
         launches++;
         mark(ST_BLUR);
@@ -1247,6 +1274,7 @@ struct mcs_rig {
     int n_extracted = 0, n_matched = 0, n_triangulated = 0;
     bool feat_host = false, rows_host = false, lm_host = false;
     size_t merge_smem = 0;
+    int merge_wide = -1;  // MCS_MERGE_WIDE: -1 by launch size, 0 / 1 forced
     bool merge_rows_smem = false;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     // Latency mode (mcs_rig_set_graph): the whole launch sequence of an unchunked device-resident call — memsets, every kernel, the
@@ -1360,6 +1388,7 @@ struct mcs_rig {
         if (const char* e = getenv("MCS_CHUNK_FRAMES")) chunk_frames = atoi(e);
         if (const char* e = getenv("MCS_HIPRIO")) use_hi = atoi(e) != 0;
         if (const char* e = getenv("MCS_MATCH_IMMA")) match_imma = atoi(e) != 0;
+        if (const char* e = getenv("MCS_MERGE_WIDE")) merge_wide = atoi(e);
         if (const char* e = getenv("MCS_HOST_CHUNK_DIV")) host_chunk_div = std::max(1, std::min(16, atoi(e)));
         if (const char* e = getenv("MCS_TRI_PER_SM")) tri_per_sm = std::max(0, atoi(e));
         if (use_hi) {
@@ -1394,7 +1423,8 @@ struct mcs_rig {
         if (merge_smem > 200 * 1024) { set_err("too many features per frame for the merge kernel's shared table"); return MCS_ERR_ARG; }
         merge_rows_smem = mcs::merge_smem_layout(C, kp_cap, row_cap, true).total <= 100 * 1024;
         if (merge_rows_smem) merge_smem = mcs::merge_smem_layout(C, kp_cap, row_cap, true).total;
-        CK(cudaFuncSetAttribute(mcs::merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(merge_smem, 1024)));
+        CK(cudaFuncSetAttribute(mcs::merge_kernel<MCS_MERGE_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(merge_smem, 1024)));
+        CK(cudaFuncSetAttribute(mcs::merge_kernel<MCS_MERGE_NT_WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(merge_smem, 1024)));
         return 0;
     }
 
@@ -1485,9 +1515,12 @@ struct mcs_rig {
             CK(cudaStreamWaitEvent(slots[k].hi.st, slots[k].hi.e0, 0));
             ml = slots[k].hi.st;
         }
-        mcs::merge_kernel<<<n_frames, MCS_MERGE_NT, merge_smem, ml>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
-                                                             kps_undist_dev() + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
-                                                             d_rows + (size_t)f0 * row_cap * C, d_row_count + f0, merge_rows_smem ? 1 : 0);
+        // a launch of few frames cannot fill the SMs: wide blocks (one query per thread) shorten its latency instead
+        const bool wide = merge_wide < 0 ? n_frames * 4 <= sm_count : merge_wide != 0;
+        const auto mk = wide ? &mcs::merge_kernel<MCS_MERGE_NT_WIDE> : &mcs::merge_kernel<MCS_MERGE_NT>;
+        mk<<<n_frames, wide ? MCS_MERGE_NT_WIDE : MCS_MERGE_NT, merge_smem, ml>>>(C, kp_cap, row_cap, pairs, eng.d_kp_count + (size_t)f0 * C, match_train,
+                                                                              kps_undist_dev() + (size_t)f0 * C * kp_cap, old, d_F, d_sigma2,
+                                                                              d_rows + (size_t)f0 * row_cap * C, d_row_count + f0, merge_rows_smem ? 1 : 0);
         eng.launches++;
         if (use_hi) {
             CK(cudaEventRecord(slots[k].hi.e1, ml));

@@ -110,6 +110,8 @@ FUZZ = [  # w, h, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST
     (300, 300, 150, 1.2, 3, 10, 3),
     (720, 540, 2000, 1.2, 8, 12, 4),
     (1000, 160, 400, 1.25, 4, 25, 9),   # every level keeps at least one 35 px cell row: below that the reference divides by zero
+    (640, 480, 2900, 1.2, 1, 12, 4),    # one level holds every feature: its octree tables exceed shared memory (octree_kernel<true>)
+    (500, 400, 4500, 2.0, 2, 10, 5),    # level 0 quota 3000: same
 ]
 
 

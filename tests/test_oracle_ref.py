@@ -36,7 +36,8 @@ def test_ref_extractor_matches_golden_and_oracle(golden, name, nf):
 
 
 SWEEP = [(411, 233, 300, 1.5, 5, 20, 7), (640, 480, 800, 2.0, 4, 30, 10), (257, 190, 200, 1.1, 10, 15, 5), (512, 384, 600, 1.3, 6, 40, 40),
-         (300, 300, 150, 1.2, 3, 10, 3), (720, 540, 2000, 1.2, 8, 12, 4), (1000, 160, 400, 1.25, 4, 25, 9)]
+         (300, 300, 150, 1.2, 3, 10, 3), (720, 540, 2000, 1.2, 8, 12, 4), (1000, 160, 400, 1.25, 4, 25, 9),
+         (640, 480, 2900, 1.2, 1, 12, 4), (500, 400, 4500, 2.0, 2, 10, 5)]
 
 
 @pytest.mark.parametrize("w,h,nf,sf,nl,ini,mn", SWEEP)
