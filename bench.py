@@ -458,11 +458,11 @@ def latency_sweep(rig, d_images, d_masks, pin, pin_m, F, iters):
             row[name] = {"p50_ms": round(float(np.median(t)), 4), "p99_ms": round(float(t[min(len(t) - 1, int(0.99 * len(t)))]), 4),
                          "rig_frames_per_s": round(b / (float(np.median(t)) / 1e3), 1)}
         rig.set_graph(False)
-        if b == 1:  # where one rig frame's time goes: CUDA events between the stages of one unchunked call
+        if b <= 8:  # where a small call's time goes: CUDA events between the stages of one unchunked call
             rig.set_profiling(True)
             acc = dict.fromkeys(STAGES, 0.0)
             for _ in range(20):
-                rig.process_device(d_images, 1, d_masks)
+                rig.process_device(d_images, b, d_masks)
                 for k, v in rig.stage_times().items():
                     acc[k] += v / 20
             rig.set_profiling(False)

@@ -932,7 +932,9 @@ __global__ void __launch_bounds__(128) tri_classify_kernel(int num_cams, int kp_
 template <int NV>
 __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double* z) {
     constexpr int M = 3 * NV, N = 4 + NV, T = MCS_TRI_NT;
+#ifdef MCS_TRI_ROT_REF
     const double eps = 2.220446049250313e-16;
+#endif
     // only rows 0..3 of V are ever read (z = V[0..3][best]) and a rotation updates every row independently, so V is kept as 4 x N
 #pragma unroll 1
     for (int i = 0; i < 4 * N; i++) sV[i * T] = 0;
@@ -958,11 +960,31 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
                     b += yk[k] * yk[k];
                     g += xk[k] * yk[k];
                 }
+                // The rotation of null_vector() — skip when |g| <= eps sqrt(a b); zeta = (b - a) / 2g, t = sign(zeta) / (|zeta| +
+                // sqrt(1 + zeta^2)), c = 1 / sqrt(1 + t^2) — in a form with a shorter dependent chain (this kernel is latency-bound and
+                // three square roots and three divisions in a row were most of it): the fraction for t extended by |2g|, the test
+                // squared, c by rsqrt — one square root, one division, one reciprocal square root.  The same rotation to a few ulp.
+                // Stopping rule 8 eps instead of eps: at eps the test sits inside the rounding noise of g itself (15 products), so
+                // now and then a row keeps "rotating" by less than an ulp until the 60-sweep cap — which row is a matter of
+                // rounding luck (the literal form has such rows too), and one such row holds its warp, and with it a small launch,
+                // for 10x the normal time (measured: one row of the bench's frame 6, triangulation stage of an 8-frame call
+                // 0.18 -> 0.35 ms).  At 8 eps every row of the workload stops after 5-7 sweeps.  Points move by <= 4e-13 relative
+                // against the oracle, which keeps the literal rule (tests: 1e-6; MCS_TRI_ROT_REF builds the literal form).
+#ifdef MCS_TRI_ROT_REF
                 if (fabs(g) <= eps * sqrt(a * b) || g == 0) continue;
                 changed = true;
                 const double zeta = (b - a) / (2 * g);
                 const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1 + zeta * zeta));
                 const double c = 1.0 / sqrt(1 + t * t), sn = c * t;
+#else
+                constexpr double tol2 = (8 * 2.220446049250313e-16) * (8 * 2.220446049250313e-16);
+                if (g * g <= tol2 * (a * b) || g == 0) continue;
+                changed = true;
+                const double d = b - a, h = 2 * g;
+                const double tt = fabs(h) / (fabs(d) + sqrt(d * d + h * h));
+                const double t = (d != 0 && (d < 0) != (h < 0)) ? -tt : tt;
+                const double c = rsqrt(1 + t * t), sn = c * t;
+#endif
 #pragma unroll
                 for (int k = 0; k < M; k++) {
                     sA[(k * N + p) * T] = c * xk[k] - sn * yk[k];

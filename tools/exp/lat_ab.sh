@@ -12,6 +12,7 @@ try:
     L = d["latency"]
     print("$name", {b: {m: L[b][m].get("p50_ms") for m in L[b] if m != "stage_ms"} for b in L if b.startswith("batch")}, d["stage_ms_per_launch_sequence"]["octree"])
     print("   batch-1 stages", L["batch_1"].get("stage_ms"))
+    print("   batch-8 stages", L["batch_8"].get("stage_ms"))
 except Exception as e:
     print("$name", "no line", e)
 PY
