@@ -433,6 +433,25 @@ def test_imma_matcher_experiment_equals_product_matcher(monkeypatch):
             assert (ca[0] == cb[0]).all() and ca[1:] == cb[1:]
 
 
+@pytest.mark.parametrize("old", [False, True])
+def test_merge_block_width_variants(monkeypatch, old):
+    """merge_kernel<256> (the chunked pipeline's launches of many frames) and merge_kernel<1024> (launches of few frames, one query per
+    thread) are picked by launch size; MCS_MERGE_WIDE forces either.  Both against the oracle's computeIntraMatches on a 5-camera frame
+    with ~1000 features per camera (every thread of the wide block owns a query; the narrow one walks four per thread)."""
+    import mcslam_b200 as M
+    import oracle_lib as O
+    calib = M.synth.make_rig(5, 720, 540)
+    frames = np.stack([M.synth.make_rig_frame(calib, 720, 540, frame_index=31)])
+    K, D, rows, pc, tri = _oracle_frame(O, frames[0], calib, 1000, old=old)
+    assert len(rows) > 500
+    for wide in ("0", "1"):
+        monkeypatch.setenv("MCS_MERGE_WIDE", wide)
+        rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=1)
+        rig.process(frames, old=old)
+        _check_frame(rig, 0, K, D, rows, tri, 5)
+    monkeypatch.delenv("MCS_MERGE_WIDE")
+
+
 @pytest.mark.parametrize("ncam,w,h,nf,old,with_masks", [(2, 320, 240, 400, False, True), (6, 256, 192, 250, True, False), (7, 200, 160, 150, False, True)])
 def test_rig_camera_count_sweep(ncam, w, h, nf, old, with_masks):
     """Rigs of 2, 6 and 7 cameras (1, 15 and 21 camera pairs; the reference's IntraMatch holds 5, the row table here is [M][num_cams]):
