@@ -954,11 +954,19 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
                     xk[k] = sA[(k * N + p) * T];
                     yk[k] = sA[(k * N + q) * T];
                 }
+                // summation order of tri_solve4_kernel (four lanes per row: matrix rows k = j, j + 4, ... summed per lane j, then
+                // (s0 + s1) + (s2 + s3)), so that the two kernels give bit-identical points and a call's size does not show in them
+                {
+                    double pa[4] = {0, 0, 0, 0}, pb[4] = {0, 0, 0, 0}, pg[4] = {0, 0, 0, 0};
 #pragma unroll
-                for (int k = 0; k < M; k++) {
-                    a += xk[k] * xk[k];
-                    b += yk[k] * yk[k];
-                    g += xk[k] * yk[k];
+                    for (int k = 0; k < M; k++) {
+                        pa[k & 3] += xk[k] * xk[k];
+                        pb[k & 3] += yk[k] * yk[k];
+                        pg[k & 3] += xk[k] * yk[k];
+                    }
+                    a = (pa[0] + pa[1]) + (pa[2] + pa[3]);
+                    b = (pb[0] + pb[1]) + (pb[2] + pb[3]);
+                    g = (pg[0] + pg[1]) + (pg[2] + pg[3]);
                 }
                 // The rotation of null_vector() — skip when |g| <= eps sqrt(a b); zeta = (b - a) / 2g, t = sign(zeta) / (|zeta| +
                 // sqrt(1 + zeta^2)), c = 1 / sqrt(1 + t^2) — in a form with a shorter dependent chain (this kernel is latency-bound and
@@ -1004,12 +1012,13 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
     double bestn = -1;
 #pragma unroll 1
     for (int j = 0; j < N; j++) {
-        double sq = 0;
+        double ps[4] = {0, 0, 0, 0};
 #pragma unroll
         for (int k = 0; k < M; k++) {
             const double v = sA[(k * N + j) * T];
-            sq += v * v;
+            ps[k & 3] += v * v;
         }
+        const double sq = (ps[0] + ps[1]) + (ps[2] + ps[3]);
         if (bestn < 0 || sq < bestn) {
             bestn = sq;
             best = j;
@@ -1159,6 +1168,235 @@ __global__ void __launch_bounds__(MCS_TRI_NT) tri_solve_kernel(int num_cams, int
             case 7: tri_solve_class<7>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
             default: tri_solve_class<8>(s_tri, t, ONE, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
         }
+    }
+}
+
+// ---- four lanes per row ---------------------------------------------------------------------------------------------------
+// The solve of one row is a chain of 6-7 sweeps x 21-36 dependent rotations, and with one row per thread every rotation walks the
+// 3NV matrix rows in sequence (dot products, then the update).  Here four adjacent lanes share a row: lane j of the group owns matrix
+// rows k = j, j + 4, ... (and row j of the 4 x N block of V), the three dot products are partial sums closed by two xor-shuffles (fp
+// addition commutes, so the four lanes hold bit-identical sums and take identical decisions), the scalar part is computed
+// redundantly.  A tile is 8 rows per warp; layout [column][k][row of the tile]: the 32 lanes of a load touch 32 consecutive doubles.
+// Control flow is warp-uniform (a converged or empty row only re-tests its pairs: |g| stays under the threshold, nothing changes),
+// so every shuffle runs with the full mask.  Pair order and stopping rule as in null_vector_smem; the summation order inside a dot
+// product differs (four partial sums), i.e. points move in the last bits only.
+#define MCS_TRI4_ROWS 8
+template <int NV>
+__device__ __forceinline__ void null_vector_smem4(double* sA, double* sV, int r, int j, double* z) {
+    constexpr int M = 3 * NV, N = 4 + NV, MI = (M + 3) / 4, MP = MI * 4, R = MCS_TRI4_ROWS;
+    constexpr double tol2 = (8 * 2.220446049250313e-16) * (8 * 2.220446049250313e-16);
+    double* a0 = sA + j * R + r;  // element (col, 4 i + j) at a0[(col * MP + 4 i) * R]
+    double* v0 = sV + j * R + r;  // V[j][col] at v0[col * 4 * R]
+#pragma unroll 1
+    for (int sweep = 0; sweep < 60; sweep++) {
+        bool changed = false;
+#pragma unroll 1
+        for (int p = 0; p < N - 1; p++) {
+#pragma unroll 1
+            for (int q = p + 1; q < N; q++) {
+                double xk[MI], yk[MI];
+                double a = 0, b = 0, g = 0;
+#pragma unroll
+                for (int i = 0; i < MI; i++) {
+                    xk[i] = a0[(p * MP + 4 * i) * R];
+                    yk[i] = a0[(q * MP + 4 * i) * R];
+                }
+#pragma unroll
+                for (int i = 0; i < MI; i++) {
+                    a += xk[i] * xk[i];
+                    b += yk[i] * yk[i];
+                    g += xk[i] * yk[i];
+                }
+#pragma unroll
+                for (int o = 1; o < 4; o <<= 1) {
+                    a += __shfl_xor_sync(0xFFFFFFFFu, a, o);
+                    b += __shfl_xor_sync(0xFFFFFFFFu, b, o);
+                    g += __shfl_xor_sync(0xFFFFFFFFu, g, o);
+                }
+                if (g * g <= tol2 * (a * b) || g == 0) continue;
+                changed = true;
+                const double d = b - a, h = 2 * g;
+                const double tt = fabs(h) / (fabs(d) + sqrt(d * d + h * h));
+                const double t = (d != 0 && (d < 0) != (h < 0)) ? -tt : tt;
+                const double c = rsqrt(1 + t * t), sn = c * t;
+#pragma unroll
+                for (int i = 0; i < MI; i++) {
+                    a0[(p * MP + 4 * i) * R] = c * xk[i] - sn * yk[i];
+                    a0[(q * MP + 4 * i) * R] = sn * xk[i] + c * yk[i];
+                }
+                const double x = v0[p * 4 * R], y = v0[q * 4 * R];
+                v0[p * 4 * R] = c * x - sn * y;
+                v0[q * 4 * R] = sn * x + c * y;
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, changed)) break;
+    }
+    int best = 0;
+    double bestn = -1;
+#pragma unroll 1
+    for (int col = 0; col < N; col++) {
+        double sq = 0;
+#pragma unroll
+        for (int i = 0; i < MI; i++) {
+            const double v = a0[(col * MP + 4 * i) * R];
+            sq += v * v;
+        }
+        sq += __shfl_xor_sync(0xFFFFFFFFu, sq, 1);
+        sq += __shfl_xor_sync(0xFFFFFFFFu, sq, 2);
+        if (bestn < 0 || sq < bestn) {
+            bestn = sq;
+            best = col;
+        }
+    }
+    const double mine = v0[best * 4 * R];  // V[j][best]
+    const int lane0 = (threadIdx.x & 31) & ~3;
+#pragma unroll
+    for (int k = 0; k < 4; k++) z[k] = __shfl_sync(0xFFFFFFFFu, mine, lane0 + k);
+}
+
+// one tile (8 rows) of view-count class NV; the whole warp calls it
+template <int NV>
+__device__ __forceinline__ void tri_solve_tile4(double* s_tri, int tile, int num_cams, int kp_cap, int row_cap, const CalibDev* __restrict__ calib,
+                                                const KeypointPod* __restrict__ kps, const uint8_t* __restrict__ desc, const LandmarkOut& out,
+                                                const int* __restrict__ lists, const int* __restrict__ list_count, int list_stride) {
+    constexpr int M = 3 * NV, N = 4 + NV, MI = (M + 3) / 4, MP = MI * 4, R = MCS_TRI4_ROWS;
+    const int lane = threadIdx.x & 31, r = lane >> 2, j = lane & 3;
+    const int count = list_count[NV];
+    const int e = tile * R + r;
+    const bool valid = e < count;
+    const size_t ro = valid ? (size_t)lists[(size_t)NV * list_stride + e] : 0;
+    const int frame = (int)(ro / row_cap);
+    int views[NV], feats[NV];
+    double xs[NV], ys[NV];
+#pragma unroll
+    for (int k = 0; k < NV; k++) { views[k] = 0; feats[k] = 0; xs[k] = 0; ys[k] = 0; }
+    if (valid) {
+        int n = 0;
+        for (int c = 0; c < num_cams; c++) {
+            const int f = out.rows[ro * num_cams + c];
+            if (f != -1 && n < NV) {
+                views[n] = c;
+                feats[n] = f;
+                n++;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NV; k++) {
+            const int c = views[k];
+            const KeypointPod p = kps[(size_t)(frame * num_cams + c) * kp_cap + feats[k]];
+            xs[k] = ((double)p.x - calib[c].K[2]) / calib[c].K[0];  // :292-298
+            ys[k] = ((double)p.y - calib[c].K[5]) / calib[c].K[4];
+        }
+    }
+    double* sA = s_tri;
+    double* sV = s_tri + N * MP * R;
+    double* a0 = sA + j * R + r;
+    double* v0 = sV + j * R + r;
+#pragma unroll 1
+    for (int i = 0; i < N * MI; i++) a0[i * 4 * R] = 0;  // own elements: (col, 4 i' + j) for all col, i'
+#pragma unroll 1
+    for (int col = 0; col < N; col++) v0[col * 4 * R] = col == j ? 1.0 : 0.0;
+    __syncwarp();
+    if (valid && j == 0) {
+        double* sr = sA + r;  // element (col, k) of this row at sr[(col * MP + k) * R]
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            const double* Pm = calib[views[i]].Rt;
+#pragma unroll
+            for (int jj = 0; jj < 3; jj++)
+#pragma unroll
+                for (int ii = 0; ii < 4; ii++) sr[(ii * MP + 3 * i + jj) * R] = -Pm[jj * 4 + ii];
+            sr[((4 + i) * MP + 3 * i + 0) * R] = xs[i];
+            sr[((4 + i) * MP + 3 * i + 1) * R] = ys[i];
+            sr[((4 + i) * MP + 3 * i + 2) * R] = 1.0;
+        }
+    }
+    __syncwarp();
+    double z[4];
+    null_vector_smem4<NV>(sA, sV, r, j, z);
+    __syncwarp();
+    if (!valid || j != 0) return;
+    double X[3];
+    X[0] = z[0] / z[3];
+    X[1] = z[1] / z[3];
+    X[2] = z[2] / z[3];
+    // representative descriptor: least median Hamming distance, first wins (MultiCameraFrame.cpp:530-567)
+    int bestMedian = 0x7FFFFFFF, bestIdx = 0;
+#pragma unroll
+    for (int a = 0; a < NV; a++) {
+        int dd[NV];
+#pragma unroll
+        for (int b = 0; b < NV; b++)
+            dd[b] = a == b ? 0
+                           : hamming256(desc + ((size_t)(frame * num_cams + views[a]) * kp_cap + feats[a]) * 32,
+                                        desc + ((size_t)(frame * num_cams + views[b]) * kp_cap + feats[b]) * 32);
+#pragma unroll
+        for (int i = 1; i < NV; i++) {  // insertion sort (values only: ties are indistinguishable)
+            const int key = dd[i];
+            int jx = i - 1;
+            while (jx >= 0 && dd[jx] > key) {
+                dd[jx + 1] = dd[jx];
+                jx--;
+            }
+            dd[jx + 1] = key;
+        }
+        const int median = dd[(int)(0.5 * (NV - 1))];
+        if (median < bestMedian) {
+            bestMedian = median;
+            bestIdx = a;
+        }
+    }
+    out.rep_cam[ro] = views[bestIdx];
+    float u = 0, v = 0;
+    if (X[2] < 40 && X[2] > 0.5) {  // :308
+        out.accepted[ro] = 1;
+        atomicAdd(&out.n_accepted[frame], 1);
+        const double* K0 = calib[0].K;
+        const double px = K0[0] * X[0] + K0[1] * X[1] + K0[2] * X[2];
+        const double py = K0[3] * X[0] + K0[4] * X[1] + K0[5] * X[2];
+        const double pz = K0[6] * X[0] + K0[7] * X[1] + K0[8] * X[2];
+        u = (float)(px / pz);
+        v = (float)(py / pz);
+    }
+    out.xyz[ro * 3] = X[0];
+    out.xyz[ro * 3 + 1] = X[1];
+    out.xyz[ro * 3 + 2] = X[2];
+    out.uv_ref[ro * 2] = u;
+    out.uv_ref[ro * 2 + 1] = v;
+}
+
+// bytes of shared memory of one tri_solve4_kernel block for rigs of up to `nv` cameras
+__host__ __device__ inline size_t tri4_smem_bytes(int nv) {
+    const int M = 3 * nv, N = 4 + nv, MP = ((M + 3) / 4) * 4;
+    return nv <= 2 ? 0 : (size_t)(N * MP + 4 * N) * MCS_TRI4_ROWS * sizeof(double);
+}
+
+__global__ void __launch_bounds__(32) tri_solve4_kernel(int num_cams, int kp_cap, int row_cap, const CalibDev* __restrict__ calib,
+                                                        const KeypointPod* __restrict__ kps, const uint8_t* __restrict__ desc,
+                                                        LandmarkOut out, const int* __restrict__ lists,
+                                                        const int* __restrict__ list_count, int list_stride,
+                                                        int* __restrict__ tile_counter) {
+    extern __shared__ __align__(16) double s_tri[];
+    for (;;) {
+        int t = 0;
+        if ((threadIdx.x & 31) == 0) t = atomicAdd(tile_counter, 1);
+        t = __shfl_sync(0xFFFFFFFFu, t, 0);
+        int nv = num_cams;
+        for (; nv >= 3; nv--) {
+            const int tiles = (list_count[nv] + MCS_TRI4_ROWS - 1) / MCS_TRI4_ROWS;
+            if (t < tiles) break;
+            t -= tiles;
+        }
+        if (nv < 3) return;
+        switch (nv) {
+            case 3: tri_solve_tile4<3>(s_tri, t, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 4: tri_solve_tile4<4>(s_tri, t, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 5: tri_solve_tile4<5>(s_tri, t, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 6: tri_solve_tile4<6>(s_tri, t, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            case 7: tri_solve_tile4<7>(s_tri, t, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+            default: tri_solve_tile4<8>(s_tri, t, num_cams, kp_cap, row_cap, calib, kps, desc, out, lists, list_count, list_stride); break;
+        }
+        __syncwarp();
     }
 }
 

@@ -1247,6 +1247,8 @@ struct mcs_rig {
     int tri_list_stride = 0, sm_count = 148;
     int chunk_frames = 64;  // frames per pipelined chunk (0 = no chunking)
     int host_chunk_div = 4; // host-buffer calls use chunks of chunk_frames / host_chunk_div (MCS_HOST_CHUNK_DIV): 6 slots x quarter chunks measured best
+    int tri_lanes = -1;     // MCS_TRI_LANES: 4 = tri_solve4_kernel (four lanes per row), 1 = tri_solve_kernel (one thread per row), unset = by call size
+    int tri4_per_sm = 16;   // MCS_TRI4_PER_SM: resident tri_solve4 blocks per SM
     int tri_per_sm = 3;     // resident tri_solve blocks per SM (MCS_TRI_PER_SM; 0 = as many as shared memory holds): 3 measured best — the
                             // one-warp blocks hold 44 KB of shared memory each for the length of a Jacobi chain, which other chunks' kernels need
     bool match_imma = false; // MCS_MATCH_IMMA=1: experiment, the pair matcher on the u8 integer MMA (hamming_match_imma_kernel); not the product path
@@ -1391,6 +1393,8 @@ struct mcs_rig {
         if (const char* e = getenv("MCS_MERGE_WIDE")) merge_wide = atoi(e);
         if (const char* e = getenv("MCS_HOST_CHUNK_DIV")) host_chunk_div = std::max(1, std::min(16, atoi(e)));
         if (const char* e = getenv("MCS_TRI_PER_SM")) tri_per_sm = std::max(0, atoi(e));
+        if (const char* e = getenv("MCS_TRI_LANES")) tri_lanes = atoi(e) == 1 ? 1 : (atoi(e) == 4 ? 4 : -1);
+        if (const char* e = getenv("MCS_TRI4_PER_SM")) tri4_per_sm = std::max(1, std::min(32, atoi(e)));
         if (use_hi) {
             int lo = 0, hi = 0;
             CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -1431,6 +1435,7 @@ struct mcs_rig {
     static size_t tri_smem(int nv) { return nv <= 2 ? 0 : (size_t)(3 * nv * (4 + nv) + 4 * (4 + nv)) * sizeof(double) * MCS_TRI_NT; }
     int set_tri_smem() {
         CK(cudaFuncSetAttribute(mcs::tri_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem(MCS_MAX_CAMS)));
+        CK(cudaFuncSetAttribute(mcs::tri_solve4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mcs::tri4_smem_bytes(MCS_MAX_CAMS)));
         return 0;
     }
     void invalidate() { feat_host = rows_host = lm_host = kps_undist_host = false; }
@@ -1575,10 +1580,23 @@ struct mcs_rig {
             eng.launches++;
             CK(cudaEventRecord(S.ev_join, S.st2));
             if (C >= 3) {
-                const int per_sm = std::max(1, std::min(tri_per_sm > 0 ? tri_per_sm : 16, (int)((227 * 1024) / (tri_smem(C) + 1024))));
-                mcs::tri_solve_kernel<<<sm_count * per_sm, MCS_TRI_NT, tri_smem(C), tl>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
-                                                                                          S.d_tri_counts, tri_list_stride,
-                                                                                          S.d_tri_counts + MCS_MAX_CAMS + 1);
+                // Four lanes per row shorten the chain of one solve (one rig frame: triangulation stage 0.141 -> 0.102 ms) but repeat the
+                // scalar part of every rotation in four lanes: with more tiles than SMs that costs more than it saves (8 frames 0.148 ->
+                // 0.194 ms, 64-frame chunks -2 % throughput).  So: calls of one or two frames only, unless MCS_TRI_LANES says otherwise.
+                if (tri_lanes == 4 || (tri_lanes < 0 && n_frames <= 2)) {
+                    // 8-row tiles, one warp per block: as many blocks as there can be tiles, up to 16 per SM
+                    const size_t sm4 = mcs::tri4_smem_bytes(C);
+                    const int per_sm = std::max(1, std::min(tri4_per_sm, (int)((200 * 1024) / (sm4 + 1024))));
+                    const int tiles_max = (n_frames * row_cap + MCS_TRI4_ROWS - 1) / MCS_TRI4_ROWS + MCS_MAX_CAMS;
+                    mcs::tri_solve4_kernel<<<std::min(sm_count * per_sm, tiles_max), 32, sm4, tl>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
+                                                                                                   S.d_tri_counts, tri_list_stride,
+                                                                                                   S.d_tri_counts + MCS_MAX_CAMS + 1);
+                } else {
+                    const int per_sm = std::max(1, std::min(tri_per_sm > 0 ? tri_per_sm : 16, (int)((227 * 1024) / (tri_smem(C) + 1024))));
+                    mcs::tri_solve_kernel<<<sm_count * per_sm, MCS_TRI_NT, tri_smem(C), tl>>>(C, kp_cap, row_cap, d_calib, kps, desc, out, S.d_tri_lists,
+                                                                                              S.d_tri_counts, tri_list_stride,
+                                                                                              S.d_tri_counts + MCS_MAX_CAMS + 1);
+                }
                 eng.launches++;
             }
             CK(cudaStreamWaitEvent(tl, S.ev_join, 0));

@@ -434,22 +434,31 @@ def test_imma_matcher_experiment_equals_product_matcher(monkeypatch):
 
 
 @pytest.mark.parametrize("old", [False, True])
-def test_merge_block_width_variants(monkeypatch, old):
-    """merge_kernel<256> (the chunked pipeline's launches of many frames) and merge_kernel<1024> (launches of few frames, one query per
-    thread) are picked by launch size; MCS_MERGE_WIDE forces either.  Both against the oracle's computeIntraMatches on a 5-camera frame
-    with ~1000 features per camera (every thread of the wide block owns a query; the narrow one walks four per thread)."""
+def test_small_launch_kernel_variants(monkeypatch, old):
+    """Two kernels come in a form for launches of many frames and one for launches of few, picked by call size: merge_kernel<256> /
+    merge_kernel<1024> (one query per thread) and tri_solve_kernel (one thread per row) / tri_solve4_kernel (four lanes per row).
+    MCS_MERGE_WIDE and MCS_TRI_LANES force either.  All four combinations against the oracle on a 5-camera frame with ~1000 features
+    per camera, and the two solvers against each other: they sum a rotation's dot products in the same order (four partial sums), so
+    their points are bit-identical and the size of a call does not show in its results."""
     import mcslam_b200 as M
     import oracle_lib as O
     calib = M.synth.make_rig(5, 720, 540)
     frames = np.stack([M.synth.make_rig_frame(calib, 720, 540, frame_index=31)])
     K, D, rows, pc, tri = _oracle_frame(O, frames[0], calib, 1000, old=old)
-    assert len(rows) > 500
+    assert len(rows) > 500 and (tri["nviews"] >= 3).sum() > 100
+    xyz = {}
     for wide in ("0", "1"):
-        monkeypatch.setenv("MCS_MERGE_WIDE", wide)
-        rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=1)
-        rig.process(frames, old=old)
-        _check_frame(rig, 0, K, D, rows, tri, 5)
+        for lanes in ("1", "4"):
+            monkeypatch.setenv("MCS_MERGE_WIDE", wide)
+            monkeypatch.setenv("MCS_TRI_LANES", lanes)
+            rig = M.RigFrames(calib, 720, 540, nfeatures=1000, max_frames=1)
+            rig.process(frames, old=old)
+            _check_frame(rig, 0, K, D, rows, tri, 5)
+            xyz[lanes] = rig.landmarks(0)["xyz"].copy()
     monkeypatch.delenv("MCS_MERGE_WIDE")
+    monkeypatch.delenv("MCS_TRI_LANES")
+    ok = tri["nviews"] >= 2
+    assert np.array_equal(xyz["1"][ok], xyz["4"][ok])
 
 
 @pytest.mark.parametrize("ncam,w,h,nf,old,with_masks", [(2, 320, 240, 400, False, True), (6, 256, 192, 250, True, False), (7, 200, 160, 150, False, True)])
