@@ -618,13 +618,16 @@ __global__ void __launch_bounds__(NT) merge_kernel(int num_cams, int kp_cap, int
         }
         if (lane == 31) s_wsum[warp] = incl;
         __syncthreads();
-        int base = M + incl - my_new, total_new = 0;
+        // offsets of the warps: one shuffle scan over the (at most 32) warp sums instead of a loop over them in every thread
+        int wincl = lane < NT / 32 ? s_wsum[lane] : 0;
 #pragma unroll
-        for (int w = 0; w < NT / 32; w++) {
-            const int ws = s_wsum[w];
-            if (w < warp) base += ws;
-            total_new += ws;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, wincl, o);
+            if (lane >= o) wincl += v;
         }
+        const int total_new = __shfl_sync(0xFFFFFFFFu, wincl, 31);
+        const int wexcl = __shfl_sync(0xFFFFFFFFu, wincl, warp) - s_wsum[warp];
+        int base = M + wexcl + incl - my_new;
         // pass C: apply the decisions (they touch disjoint state)
         for (int q = q_lo; q < q_hi; q++) {
             const int kind = s_kind[q];
