@@ -1,5 +1,5 @@
 #!/bin/bash
-# gpurun payload: the whole GPU suite, smoke(), the default bench line and the reference arm
+# gpurun payload: the whole GPU suite, smoke() and the default bench line (value, e2e, fractions, latency sweep, parity block)
 set -u
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log

@@ -1,4 +1,5 @@
 #!/bin/bash
+# gpurun --gpus N payload: the bench line at N GPUs (torchrun, one rank per GPU), as the driver launches it
 set -u
 N=$1
 mkdir -p gpurun_out
