@@ -1246,6 +1246,10 @@ struct CudaBlockCtx {
         if (GTAB) atomicMin(p, v);
         else asm volatile("red.shared.min.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
     }
+    __device__ __forceinline__ void atomic_max64(unsigned long long* p, unsigned long long v) {
+        if (GTAB) atomicMax(p, v);
+        else asm volatile("red.shared.max.u64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "l"(v) : "memory");
+    }
     // in-place exclusive scan of a[0..n) (in the tables' memory); collective; returns the total
     __device__ int exclusive_scan(int* a, int n) {
         __shared__ int s_ws[34];

@@ -21,7 +21,7 @@
 //     template<F> void par(F f);            — run f() for every thread, then barrier
 //     template<F> void serial(F f);         — run f() on thread 0, then barrier
 //     int  exclusive_scan(int* a, int n);   — in-place block-wide exclusive scan, returns the total (collective)
-//     void atomic_add(int*, int), atomic_max(unsigned*, unsigned), atomic_min(unsigned*, unsigned)
+//     void atomic_add(int*, int), atomic_max64(unsigned long long*, unsigned long long)
 #ifndef MCS_OCTREE_CORE_H
 #define MCS_OCTREE_CORE_H
 
@@ -54,7 +54,8 @@ struct Params {
 struct Shared {
     Geo* geo[2];
     int* cnt[2];
-    int* cc;          // [cap*4] child key counts of nodes split this round
+    int* cc;          // [cap*4] child key counts of the nodes that may be split this round (cc2[0] or cc2[1])
+    int* cc2[2];      // two buffers: the relabelling pass of a round already counts the NEXT round's children into the other one
     uint16_t* map;    // [cap*4] (old node, quadrant) -> new node id; quadrant slot 0 for unsplit nodes
     uint8_t* flag;    // 1 = node is split this round
     uint16_t* proc;   // nodes in processing order
@@ -63,14 +64,13 @@ struct Shared {
     int* s1;
     int* s2;
     uint32_t* sortk;  // phase-2 sort keys
-    unsigned* best;   // final selection: max score per node, then min rank
-    unsigned* bestrank;
+    unsigned long long* best64;  // final selection per node: max of (score << 32 | ~rank) = highest score, then first in the reference's order
     int* vars;        // [16] block-uniform scalars
 
     static MCS_HD size_t bytes(int cap) {
         size_t b = 0;
         b += 2 * sizeof(Geo) * cap + 2 * sizeof(int) * cap;  // geo, cnt
-        b += sizeof(int) * cap * 4;                          // cc
+        b += 2 * sizeof(int) * cap * 4;                      // cc2
         b += sizeof(uint16_t) * cap * 4;                     // map
         b += sizeof(uint16_t) * cap * 3;                     // proc, exp x2
         b += sizeof(int) * cap * 3;                          // s0..s2
@@ -85,13 +85,14 @@ struct Shared {
         geo[1] = (Geo*)p; p += sizeof(Geo) * cap;
         cnt[0] = (int*)p; p += sizeof(int) * cap;
         cnt[1] = (int*)p; p += sizeof(int) * cap;
-        cc = (int*)p; p += sizeof(int) * cap * 4;
+        cc2[0] = (int*)p; p += sizeof(int) * cap * 4;
+        cc2[1] = (int*)p; p += sizeof(int) * cap * 4;
+        cc = cc2[0];
         s0 = (int*)p; p += sizeof(int) * cap;
         s1 = (int*)p; p += sizeof(int) * cap;
         s2 = (int*)p; p += sizeof(int) * cap;
         sortk = (uint32_t*)p; p += sizeof(uint32_t) * cap;
-        best = (unsigned*)p; p += sizeof(unsigned) * cap;
-        bestrank = (unsigned*)p; p += sizeof(unsigned) * cap;
+        best64 = (unsigned long long*)p; p += sizeof(unsigned long long) * cap;  // offset 72 * cap: 8-byte aligned
         vars = (int*)p; p += sizeof(int) * 16;
         map = (uint16_t*)p; p += sizeof(uint16_t) * cap * 4;
         proc = (uint16_t*)p; p += sizeof(uint16_t) * cap;
@@ -229,32 +230,39 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
                 }
             });
         }
-        // child key counts of every node that may be split
-        ctx.par([&] {
-            for (int i = ctx.tid(); i < n_cand; i += NT) {
-                int* c = &S.cc[(int)S.proc[i] * 4];
-                c[0] = c[1] = c[2] = c[3] = 0;
-            }
-        });
-        // four keys per step with all their loads issued first: the passes over the keys are bound by the latency of the
-        // knode[] / cand[] reads (global memory), not by arithmetic
-        ctx.par([&] {
-            for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
-                int nd[4];
-                uint32_t c[4];
-                for (int u = 0; u < 4; u++) {
-                    const int k = k0 + u * NT;
-                    nd[u] = k < n_keys ? (int)knode[k] : -1;
-                    c[u] = k < n_keys ? cand[k] : 0u;
+        // Child key counts of every node that may be split.  Round 0 counts them with a pass over the keys; every later round finds
+        // them ready: the nodes that may be split in a round are children created in the round before with more than one key (phase 1
+        // splits every such node, phase 2 takes its candidates from exactly that list, :688-753), so the relabelling pass of the
+        // round before, which has each key's new node in hand, counted the key's quadrant inside that node as well (cc2[round & 1]).
+        int* const ccur = S.cc2[round & 1];
+        int* const cnext = S.cc2[(round & 1) ^ 1];
+        if (round == 0) {
+            ctx.par([&] {
+                for (int i = ctx.tid(); i < n_cand; i += NT) {
+                    int* c = &ccur[(int)S.proc[i] * 4];
+                    c[0] = c[1] = c[2] = c[3] = 0;
                 }
-                for (int u = 0; u < 4; u++)
-                    if (nd[u] >= 0 && S.flag[nd[u]]) ctx.atomic_add(&S.cc[nd[u] * 4 + quadrant(geo[nd[u]], cand_x(c[u]), cand_y(c[u]))], 1);
-            }
-        });
+            });
+            // four keys per step with all their loads issued first: the passes over the keys are bound by the latency of the
+            // knode[] / cand[] reads (global memory), not by arithmetic
+            ctx.par([&] {
+                for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
+                    int nd[4];
+                    uint32_t c[4];
+                    for (int u = 0; u < 4; u++) {
+                        const int k = k0 + u * NT;
+                        nd[u] = k < n_keys ? (int)knode[k] : -1;
+                        c[u] = k < n_keys ? cand[k] : 0u;
+                    }
+                    for (int u = 0; u < 4; u++)
+                        if (nd[u] >= 0 && S.flag[nd[u]]) ctx.atomic_add(&ccur[nd[u] * 4 + quadrant(geo[nd[u]], cand_x(c[u]), cand_y(c[u]))], 1);
+                }
+            });
+        }
         // per processed node: number of non-empty children m, expandable children e
         ctx.par([&] {
             for (int p = ctx.tid(); p < n_cand; p += NT) {
-                const int* c = &S.cc[(int)S.proc[p] * 4];
+                const int* c = &ccur[(int)S.proc[p] * 4];
                 S.s0[p] = (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
                 S.s1[p] = (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1);
             }
@@ -295,7 +303,7 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
         ctx.par([&] {
             for (int p = ctx.tid(); p < n_proc; p += NT) {
                 const int nd = S.proc[p];
-                const int* c = &S.cc[nd * 4];
+                const int* c = &ccur[nd * 4];
                 int e = S.s0[p], x = S.s1[p];
                 for (int q = 0; q < 4; q++) {
                     if (c[q] > 0) {
@@ -303,7 +311,11 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
                         ngeo[id] = child_geo(geo[nd], q);
                         ncnt[id] = c[q];
                         S.map[nd * 4 + q] = (uint16_t)id;
-                        if (c[q] > 1) S.exp[nxt][x++] = (uint16_t)id;
+                        if (c[q] > 1) {
+                            S.exp[nxt][x++] = (uint16_t)id;
+                            int* cn = &cnext[id * 4];  // next round's counts of this child, filled by the relabelling pass below
+                            cn[0] = cn[1] = cn[2] = cn[3] = 0;
+                        }
                         e++;
                     }
                 }
@@ -317,6 +329,16 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
                 }
             }
         });
+        // Relabel the keys (node ids are list positions and the list was just rebuilt).  The same pass prepares what comes next with
+        // the key's new node in hand: in the last round the per-node winner (:757-775: highest response, the first in the reference's
+        // candidate order among equals) as one 64-bit atomic max of (score << 32 | ~rank); in every other round the child counts of the
+        // next round (see above).
+        const bool finish = (n_new >= P.N) || (n_new == n_list);  // :684 / :748
+        if (finish) {
+            ctx.par([&] {
+                for (int i = ctx.tid(); i < n_new; i += NT) S.best64[i] = 0ull;
+            });
+        }
         ctx.par([&] {
             for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
                 int nd[4];
@@ -328,69 +350,50 @@ MCS_HD int distribute(Ctx& ctx, const Params& P, Shared& S, const uint32_t* cand
                 }
                 for (int u = 0; u < 4; u++) {
                     if (nd[u] < 0) continue;
-                    const int q = S.flag[nd[u]] ? quadrant(geo[nd[u]], cand_x(c[u]), cand_y(c[u])) : 0;
-                    knode[k0 + u * NT] = S.map[nd[u] * 4 + q];
+                    const bool split = S.flag[nd[u]] != 0;
+                    const int x = cand_x(c[u]), y = cand_y(c[u]);
+                    const int q = split ? quadrant(geo[nd[u]], x, y) : 0;
+                    const int id = S.map[nd[u] * 4 + q];
+                    knode[k0 + u * NT] = (uint16_t)id;
+                    if (finish)
+                        ctx.atomic_max64(&S.best64[id], ((unsigned long long)cand_score(c[u]) << 32) | (0xFFFFFFFFu - cand_rank(P, rdiv, x, y)));
+                    else if (split && ncnt[id] > 1)
+                        ctx.atomic_add(&cnext[id * 4 + quadrant(ngeo[id], x, y)], 1);
                 }
             }
             if (ctx.tid() == 0) {
                 V[V_CUR] = nxt;
                 V[V_NLIST] = n_new;
                 V[V_NEXP] = E;
-                bool finish = (n_new >= P.N) || (n_new == n_list);  // :684 / :748
                 if (!finish && phase == 1 && n_new + E * 3 > P.N) V[V_PHASE] = 2;  // :688
                 V[V_FINISH] = finish ? 1 : 0;
             }
         });
-        if (V[V_FINISH]) break;
+        if (finish) break;
     }
 
-    // ---- retain the best key of every node, in list order (:757-775) ---------------------------------------------
+    // ---- the best key of every node, in list order (:757-775): the winner's record is rebuilt from its key ----------------------
     const int n_out = V[V_NLIST];
+    if (!V[V_FINISH]) {
+        // 64 rounds without reaching a stop condition cannot happen (every round splits at least one node or stops); keep the
+        // selection defined anyway
+        ctx.par([&] {
+            for (int i = ctx.tid(); i < n_out; i += NT) S.best64[i] = 0ull;
+        });
+        ctx.par([&] {
+            for (int k = ctx.tid(); k < n_keys; k += NT) {
+                const uint32_t c = cand[k];
+                ctx.atomic_max64(&S.best64[knode[k]], ((unsigned long long)cand_score(c) << 32) | (0xFFFFFFFFu - cand_rank(P, rdiv, cand_x(c), cand_y(c))));
+            }
+        });
+    }
     ctx.par([&] {
         for (int i = ctx.tid(); i < n_out; i += NT) {
-            S.best[i] = 0;
-            S.bestrank[i] = 0xFFFFFFFFu;
-        }
-    });
-    ctx.par([&] {
-        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
-            int nd[4];
-            uint32_t c[4];
-            for (int u = 0; u < 4; u++) {
-                const int k = k0 + u * NT;
-                nd[u] = k < n_keys ? (int)knode[k] : -1;
-                c[u] = k < n_keys ? cand[k] : 0u;
-            }
-            for (int u = 0; u < 4; u++)
-                if (nd[u] >= 0) ctx.atomic_max(&S.best[nd[u]], (unsigned)cand_score(c[u]));
-        }
-    });
-    ctx.par([&] {
-        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
-            int nd[4];
-            uint32_t c[4];
-            for (int u = 0; u < 4; u++) {
-                const int k = k0 + u * NT;
-                nd[u] = k < n_keys ? (int)knode[k] : -1;
-                c[u] = k < n_keys ? cand[k] : 0u;
-            }
-            for (int u = 0; u < 4; u++)
-                if (nd[u] >= 0 && (unsigned)cand_score(c[u]) == S.best[nd[u]])
-                    ctx.atomic_min(&S.bestrank[nd[u]], cand_rank(P, rdiv, cand_x(c[u]), cand_y(c[u])));
-        }
-    });
-    ctx.par([&] {
-        for (int k0 = ctx.tid(); k0 < n_keys; k0 += 4 * NT) {
-            int nd[4];
-            uint32_t c[4];
-            for (int u = 0; u < 4; u++) {
-                const int k = k0 + u * NT;
-                nd[u] = k < n_keys ? (int)knode[k] : -1;
-                c[u] = k < n_keys ? cand[k] : 0u;
-            }
-            for (int u = 0; u < 4; u++)
-                if (nd[u] >= 0 && (unsigned)cand_score(c[u]) == S.best[nd[u]] && cand_rank(P, rdiv, cand_x(c[u]), cand_y(c[u])) == S.bestrank[nd[u]])
-                    out[nd[u]] = c[u];
+            const unsigned long long b = S.best64[i];
+            const unsigned rank = 0xFFFFFFFFu - (unsigned)(b & 0xFFFFFFFFull);
+            const int cell = (int)(rank >> 14), ci = cell / P.n_cols, cj = cell - ci * P.n_cols;
+            const int y = (int)((rank >> 7) & 0x7Fu) + 3 + ci * P.h_cell, x = (int)(rank & 0x7Fu) + 3 + cj * P.w_cell;
+            out[i] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)(b >> 32) << 24);
         }
     });
     return n_out;

@@ -27,6 +27,7 @@ struct HostCtx {
     void atomic_add(int* p, int v) { *p += v; }
     void atomic_max(unsigned* p, unsigned v) { if (v > *p) *p = v; }
     void atomic_min(unsigned* p, unsigned v) { if (v < *p) *p = v; }
+    void atomic_max64(unsigned long long* p, unsigned long long v) { if (v > *p) *p = v; }
 };
 
 int main(int argc, char** argv) {
