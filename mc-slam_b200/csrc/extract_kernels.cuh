@@ -1217,7 +1217,7 @@ __global__ void __launch_bounds__(MCS_FS_NT, MCS_FT_MINB) fast_strips_tma_kernel
 #define MCS_OCT_NT_MAX 512  // the block size is a launch parameter (Engine::oct_nt): large quotas (config 4) use wider blocks
 
 // GTAB = false: the node tables live in the block's shared memory (every configuration the reference ships).  GTAB = true: a level
-// quota too large for that (one pyramid level holding ~2,600+ features) puts them in a per-block slice of global memory instead;
+// quota too large for that (one pyramid level holding ~2,150+ features) puts them in a per-block slice of global memory instead;
 // the same algorithm, generic atomics, __syncthreads() orders the block's global accesses.
 template <bool GTAB = false>
 struct CudaBlockCtx {

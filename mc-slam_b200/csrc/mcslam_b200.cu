@@ -620,7 +620,7 @@ struct Engine {
         plan = np;
         planned_w = w; planned_h = h;
         oct_smem = mcs_oct::Shared::bytes(plan.oct_cap_max);
-        // node tables of a level that do not fit a block's shared memory (a single level with ~2,600+ features: nlevels 1 or 2 with
+        // node tables of a level that do not fit a block's shared memory (a single level with ~2,150+ features: nlevels 1 or 2 with
         // thousands of features) go to a per-block slice of global memory, octree_kernel<true>
         oct_gtab = oct_smem > 200 * 1024;
         if (oct_gtab) {
