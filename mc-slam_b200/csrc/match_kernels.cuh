@@ -958,14 +958,16 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
                     yk[k] = sA[(k * N + q) * T];
                 }
                 // summation order of tri_solve4_kernel (four lanes per row: matrix rows k = j, j + 4, ... summed per lane j, then
-                // (s0 + s1) + (s2 + s3)), so that the two kernels give bit-identical points and a call's size does not show in them
+                // (s0 + s1) + (s2 + s3)), so that the two kernels give bit-identical points and a call's size does not show in them.
+                // Both use explicit fma() in the dot products and the rotation update (the build has no contraction, --fmad=false,
+                // for the sake of the reference's f32 expressions elsewhere): a third fewer f64 instructions in the chain.
                 {
                     double pa[4] = {0, 0, 0, 0}, pb[4] = {0, 0, 0, 0}, pg[4] = {0, 0, 0, 0};
 #pragma unroll
                     for (int k = 0; k < M; k++) {
-                        pa[k & 3] += xk[k] * xk[k];
-                        pb[k & 3] += yk[k] * yk[k];
-                        pg[k & 3] += xk[k] * yk[k];
+                        pa[k & 3] = fma(xk[k], xk[k], pa[k & 3]);
+                        pb[k & 3] = fma(yk[k], yk[k], pb[k & 3]);
+                        pg[k & 3] = fma(xk[k], yk[k], pg[k & 3]);
                     }
                     a = (pa[0] + pa[1]) + (pa[2] + pa[3]);
                     b = (pb[0] + pb[1]) + (pb[2] + pb[3]);
@@ -992,20 +994,20 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
                 if (g * g <= tol2 * (a * b) || g == 0) continue;
                 changed = true;
                 const double d = b - a, h = 2 * g;
-                const double tt = fabs(h) / (fabs(d) + sqrt(d * d + h * h));
+                const double tt = fabs(h) / (fabs(d) + sqrt(fma(d, d, h * h)));
                 const double t = (d != 0 && (d < 0) != (h < 0)) ? -tt : tt;
-                const double c = rsqrt(1 + t * t), sn = c * t;
+                const double c = rsqrt(fma(t, t, 1.0)), sn = c * t;
 #endif
 #pragma unroll
                 for (int k = 0; k < M; k++) {
-                    sA[(k * N + p) * T] = c * xk[k] - sn * yk[k];
-                    sA[(k * N + q) * T] = sn * xk[k] + c * yk[k];
+                    sA[(k * N + p) * T] = fma(c, xk[k], -(sn * yk[k]));
+                    sA[(k * N + q) * T] = fma(sn, xk[k], c * yk[k]);
                 }
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     const double x = sV[(k * N + p) * T], y = sV[(k * N + q) * T];
-                    sV[(k * N + p) * T] = c * x - sn * y;
-                    sV[(k * N + q) * T] = sn * x + c * y;
+                    sV[(k * N + p) * T] = fma(c, x, -(sn * y));
+                    sV[(k * N + q) * T] = fma(sn, x, c * y);
                 }
             }
         }
@@ -1019,7 +1021,7 @@ __device__ __forceinline__ void null_vector_smem(double* sA, double* sV, double*
 #pragma unroll
         for (int k = 0; k < M; k++) {
             const double v = sA[(k * N + j) * T];
-            ps[k & 3] += v * v;
+            ps[k & 3] = fma(v, v, ps[k & 3]);
         }
         const double sq = (ps[0] + ps[1]) + (ps[2] + ps[3]);
         if (bestn < 0 || sq < bestn) {
@@ -1206,9 +1208,9 @@ __device__ __forceinline__ void null_vector_smem4(double* sA, double* sV, int r,
                 }
 #pragma unroll
                 for (int i = 0; i < MI; i++) {
-                    a += xk[i] * xk[i];
-                    b += yk[i] * yk[i];
-                    g += xk[i] * yk[i];
+                    a = fma(xk[i], xk[i], a);
+                    b = fma(yk[i], yk[i], b);
+                    g = fma(xk[i], yk[i], g);
                 }
 #pragma unroll
                 for (int o = 1; o < 4; o <<= 1) {
@@ -1219,17 +1221,17 @@ __device__ __forceinline__ void null_vector_smem4(double* sA, double* sV, int r,
                 if (g * g <= tol2 * (a * b) || g == 0) continue;
                 changed = true;
                 const double d = b - a, h = 2 * g;
-                const double tt = fabs(h) / (fabs(d) + sqrt(d * d + h * h));
+                const double tt = fabs(h) / (fabs(d) + sqrt(fma(d, d, h * h)));
                 const double t = (d != 0 && (d < 0) != (h < 0)) ? -tt : tt;
-                const double c = rsqrt(1 + t * t), sn = c * t;
+                const double c = rsqrt(fma(t, t, 1.0)), sn = c * t;
 #pragma unroll
                 for (int i = 0; i < MI; i++) {
-                    a0[(p * MP + 4 * i) * R] = c * xk[i] - sn * yk[i];
-                    a0[(q * MP + 4 * i) * R] = sn * xk[i] + c * yk[i];
+                    a0[(p * MP + 4 * i) * R] = fma(c, xk[i], -(sn * yk[i]));
+                    a0[(q * MP + 4 * i) * R] = fma(sn, xk[i], c * yk[i]);
                 }
                 const double x = v0[p * 4 * R], y = v0[q * 4 * R];
-                v0[p * 4 * R] = c * x - sn * y;
-                v0[q * 4 * R] = sn * x + c * y;
+                v0[p * 4 * R] = fma(c, x, -(sn * y));
+                v0[q * 4 * R] = fma(sn, x, c * y);
             }
         }
         if (!__any_sync(0xFFFFFFFFu, changed)) break;
@@ -1242,7 +1244,7 @@ __device__ __forceinline__ void null_vector_smem4(double* sA, double* sV, int r,
 #pragma unroll
         for (int i = 0; i < MI; i++) {
             const double v = a0[(col * MP + 4 * i) * R];
-            sq += v * v;
+            sq = fma(v, v, sq);
         }
         sq += __shfl_xor_sync(0xFFFFFFFFu, sq, 1);
         sq += __shfl_xor_sync(0xFFFFFFFFu, sq, 2);
